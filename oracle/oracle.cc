@@ -1,0 +1,664 @@
+// TEST INFRASTRUCTURE -- not product code.
+//
+// CPU restatement of the reference's hot path (waabox/domain-mcp-server), used only as the
+// checker in tests/, __graft_entry__.smoke() and as the timed CPU baseline in bench.py
+// (cpu_baseline leg and --impl reference).  The product library (libdmgraph.so) never links,
+// loads or calls anything in this directory.
+//
+// Two restatements of the same semantics:
+//
+//   ref  -- data-structure faithful: string-keyed hash maps with insertion-ordered sets, the
+//           way ProjectGraph.java holds the graph.  dependents()/resolve() scan every source
+//           (ProjectGraph.java:322-326, 371-375); search lower-cases every identifier and
+//           calls find (CodeContextService.java:1511-1514).  This is "the reference's CPU
+//           path" and the baseline of record.  JVM effects (JIT, GC, String allocation) are
+//           not reproduced.
+//   csr  -- same results over integer CSR; fast enough to be the differential oracle at
+//           BASELINE.json's full sizes.
+//
+// Parity status: PINNED against the reference's own unit tests, transcribed into
+// tests/golden/reference_tests.json (tests/test_oracle_golden.py), and cross-checked against
+// the independent pure-Python restatement oracle/pyref.py.  The reference itself is Java 21
+// and cannot be compiled or run in this image (no JDK), so there is no oracle/_ref build.
+// Unpinned (no reference test exists): iteration order of dependents()/resolve() (HashMap
+// bucket order; canonical ascending vertex id is used instead) and non-ASCII lower-casing.
+//
+// Citations: PG = src/main/java/co/fanki/domainmcp/analysis/domain/ProjectGraph.java,
+// CCS = .../analysis/application/CodeContextService.java,
+// GQS = .../analysis/application/GraphQueryService.java (all under /root/reference).
+
+#include <algorithm>
+#include <atomic>
+#include <cstdint>
+#include <cstring>
+#include <deque>
+#include <string>
+#include <thread>
+#include <unordered_map>
+#include <unordered_set>
+#include <vector>
+
+namespace {
+
+// ------------------------------------------------------------------------------------------
+// helpers restating JDK string semantics (ASCII part)
+// ------------------------------------------------------------------------------------------
+inline bool java_ws(unsigned char c) { return (c >= 9 && c <= 13) || (c >= 28 && c <= 32); }
+
+bool is_blank(const char* s) {   // String.isBlank(), shared/Preconditions.java:41-47
+  for (; *s; ++s)
+    if (!java_ws((unsigned char)*s)) return false;
+  return true;
+}
+
+std::string lower_ascii(const std::string& s) {   // String.toLowerCase(), ASCII range
+  std::string r(s);
+  for (auto& c : r)
+    if (c >= 'A' && c <= 'Z') c = (char)(c + 32);
+  return r;
+}
+
+std::string simple_name(const std::string& id) {   // CCS:1538-1541, GQS:458-461
+  size_t k = id.rfind('.');
+  return k == std::string::npos ? id : id.substr(k + 1);
+}
+
+// insertion-ordered set of strings == java.util.LinkedHashSet<String>
+struct LinkedSet {
+  std::vector<std::string> order;
+  std::unordered_set<std::string> has;
+  bool add(const std::string& s) {
+    if (!has.insert(s).second) return false;
+    order.push_back(s);
+    return true;
+  }
+  bool contains(const std::string& s) const { return has.count(s) != 0; }
+};
+
+// ------------------------------------------------------------------------------------------
+// ref: one ProjectGraph (PG:88-125)
+// ------------------------------------------------------------------------------------------
+struct RefGraph {
+  std::vector<std::string> node_order;                       // LinkedHashMap key order
+  std::unordered_map<std::string, uint32_t> node_pos;        // id -> position
+  std::vector<std::string> files;
+  std::unordered_map<std::string, LinkedSet> edges;          // HashMap<String, LinkedHashSet>
+  LinkedSet entry;
+
+  bool contains(const std::string& id) const { return node_pos.count(id) != 0; }
+
+  int add_node(const char* id, const char* file) {           // PG:160-164
+    if (!id || is_blank(id) || !file || is_blank(file)) return 1;
+    auto it = node_pos.find(id);
+    if (it == node_pos.end()) {
+      node_pos.emplace(id, (uint32_t)node_order.size());
+      node_order.emplace_back(id);
+      files.emplace_back(file);
+    } else {
+      files[it->second] = file;                              // position kept, value replaced
+    }
+    return 0;
+  }
+  int add_dependency(const char* from, const char* to) {     // PG:175-183
+    if (!from || is_blank(from) || !to || is_blank(to)) return 1;
+    if (!contains(from) || !contains(to)) return 0;
+    edges[from].add(to);
+    return 0;
+  }
+  int mark_entry(const char* id) {                           // PG:190-197
+    if (!id || is_blank(id)) return 1;
+    if (contains(id)) entry.add(id);
+    return 0;
+  }
+  // PG:299-305
+  std::vector<std::string> dependencies(const char* id) const {
+    if (!id || !contains(id)) return {};
+    auto it = edges.find(id);
+    if (it == edges.end()) return {};
+    return it->second.order;
+  }
+  // PG:316-328 -- iterates EVERY entry of `edges`
+  std::vector<std::string> dependents(const char* id) const {
+    if (!id || !contains(id)) return {};
+    std::vector<std::string> r;
+    std::string key(id);
+    for (const auto& e : edges)
+      if (e.second.contains(key)) r.push_back(e.first);
+    return r;
+  }
+  // PG:359-378
+  std::vector<std::string> resolve(const char* id) const {
+    if (!id || !contains(id)) return {};
+    LinkedSet nb;
+    std::string key(id);
+    auto it = edges.find(key);
+    if (it != edges.end())
+      for (const auto& d : it->second.order) nb.add(d);
+    for (const auto& e : edges)
+      if (e.second.contains(key)) nb.add(e.first);
+    return nb.order;
+  }
+  // PG:390-421
+  std::vector<std::string> analysis_order() const {
+    if (node_order.empty()) return {};
+    LinkedSet visited;
+    std::deque<std::string> q;
+    for (const auto& ep : entry.order)
+      if (visited.add(ep)) q.push_back(ep);
+    while (!q.empty()) {
+      std::string cur = q.front();
+      q.pop_front();
+      auto it = edges.find(cur);
+      if (it == edges.end()) continue;
+      for (const auto& d : it->second.order)
+        if (visited.add(d)) q.push_back(d);
+    }
+    for (const auto& id : node_order) visited.add(id);
+    return visited.order;
+  }
+  // CCS:1507-1526 -- per identifier: lower-cased copy + contains, in nodes order
+  std::vector<std::string> search(const std::string& query) const {
+    std::string lq = lower_ascii(query);
+    std::vector<std::string> hits;
+    for (const auto& id : node_order) {
+      std::string simple = simple_name(id);
+      if (lower_ascii(id).find(lq) != std::string::npos ||
+          lower_ascii(simple).find(lq) != std::string::npos)
+        hits.push_back(id);
+    }
+    return hits;
+  }
+  // GQS:423-456; returns position or -1
+  int64_t resolve_class_name(const std::string& name) const {
+    auto it = node_pos.find(name);
+    if (it != node_pos.end()) return it->second;
+    std::string low = lower_ascii(name);
+    int64_t best = -1;
+    for (uint32_t i = 0; i < node_order.size(); ++i)
+      if (lower_ascii(simple_name(node_order[i])) == low) {
+        if (best >= 0) return best;
+        best = i;
+      }
+    if (best >= 0) return best;
+    for (uint32_t i = 0; i < node_order.size(); ++i)
+      if (lower_ascii(node_order[i]).find(low) != std::string::npos) return i;
+    return -1;
+  }
+  // SURVEY 8a T3/T4 extension: level-by-level iteration of the 1-hop primitive.
+  // mode 0 OUT (dependencies), 1 IN (dependents), 2 BOTH (resolve).
+  std::vector<std::pair<std::string, int>> khop(const std::vector<std::string>& sources, int k,
+                                                int mode, bool exclude) const {
+    LinkedSet srcs;
+    for (const auto& s : sources)
+      if (contains(s)) srcs.add(s);
+    std::unordered_set<std::string> seen;
+    if (exclude) seen = srcs.has;
+    std::vector<std::pair<std::string, int>> out;
+    std::vector<std::string> frontier = srcs.order;
+    for (int lvl = 1; lvl <= k && !frontier.empty(); ++lvl) {
+      std::vector<std::string> next;
+      for (const auto& u : frontier) {
+        std::vector<std::string> nb = mode == 0   ? dependencies(u.c_str())
+                                      : mode == 1 ? dependents(u.c_str())
+                                                  : resolve(u.c_str());
+        for (auto& v : nb)
+          if (seen.insert(v).second) {
+            out.emplace_back(v, lvl);
+            next.push_back(v);
+          }
+      }
+      frontier.swap(next);
+    }
+    return out;
+  }
+};
+
+// ------------------------------------------------------------------------------------------
+// csr: integer restatement
+// ------------------------------------------------------------------------------------------
+struct CsrGraph {
+  uint32_t V = 0;
+  std::vector<uint32_t> out_ptr, out_idx, in_ptr, in_idx, entry, part_off;
+  std::vector<uint8_t> is_entry;
+  uint64_t dropped = 0, dups = 0;
+
+  // G0 rules: edge kept only if both endpoints are vertices (PG:179-181), duplicates
+  // collapse keeping the first position (PG:182); out rows keep insertion order, in rows
+  // are canonical (ascending source id).
+  void build(uint32_t v, uint64_t e, const uint32_t* src, const uint32_t* dst, uint32_t n_entry,
+             const uint32_t* ent, uint32_t n_parts, const uint32_t* parts) {
+    V = v;
+    std::vector<uint64_t> cnt(V + 1, 0);
+    std::vector<uint8_t> keep(e, 0);
+    {
+      std::vector<std::pair<uint64_t, uint64_t>> keyed;
+      keyed.reserve(e);
+      for (uint64_t i = 0; i < e; ++i) {
+        if (src[i] >= V || dst[i] >= V) { ++dropped; continue; }
+        keyed.emplace_back(((uint64_t)src[i] << 32) | dst[i], i);
+      }
+      std::sort(keyed.begin(), keyed.end());
+      for (size_t i = 0; i < keyed.size(); ++i) {
+        if (i && keyed[i].first == keyed[i - 1].first) { ++dups; continue; }
+        keep[keyed[i].second] = 1;
+      }
+    }
+    out_ptr.assign(V + 1, 0);
+    in_ptr.assign(V + 1, 0);
+    for (uint64_t i = 0; i < e; ++i)
+      if (keep[i]) { ++out_ptr[src[i] + 1]; ++in_ptr[dst[i] + 1]; }
+    for (uint32_t i = 0; i < V; ++i) { out_ptr[i + 1] += out_ptr[i]; in_ptr[i + 1] += in_ptr[i]; }
+    out_idx.resize(out_ptr[V]);
+    in_idx.resize(in_ptr[V]);
+    std::vector<uint32_t> oc(out_ptr.begin(), out_ptr.end() - 1), ic(in_ptr.begin(), in_ptr.end() - 1);
+    for (uint64_t i = 0; i < e; ++i)
+      if (keep[i]) out_idx[oc[src[i]]++] = dst[i];
+    for (uint32_t s = 0; s < V; ++s)   // ascending source id
+      for (uint32_t j = out_ptr[s]; j < out_ptr[s + 1]; ++j) in_idx[ic[out_idx[j]]++] = s;
+    is_entry.assign(V, 0);
+    for (uint32_t i = 0; i < n_entry; ++i)   // insertion-ordered, unknown ignored, no dupes
+      if (ent[i] < V && !is_entry[ent[i]]) { is_entry[ent[i]] = 1; entry.push_back(ent[i]); }
+    if (n_parts && parts) part_off.assign(parts, parts + n_parts + 1);
+    else part_off = {0, V};
+  }
+  uint32_t part_of(uint32_t v) const {
+    return (uint32_t)(std::upper_bound(part_off.begin(), part_off.end(), v) - part_off.begin() - 1);
+  }
+};
+
+// One query of the k-hop extension over CSR. Writes (id, hop) sorted by id into `res`.
+// The query's graph is the project (partition) of its first valid source; sources that lie
+// in other projects match nothing (CCS:1426-1434, 1558).
+void csr_khop(const CsrGraph& g, int mode, int k, bool exclude, const uint32_t* src, uint32_t ns,
+              std::vector<uint8_t>& hopmap, std::vector<uint32_t>& touched,
+              std::vector<uint32_t>& frontier, std::vector<uint32_t>& next,
+              std::vector<std::pair<uint32_t, uint8_t>>& res, uint64_t* te) {
+  // hopmap: 0 unseen, 255 = source marker, else hop
+  res.clear();
+  frontier.clear();
+  touched.clear();
+  uint32_t lo = 0, hi = 0;
+  bool have = false;
+  for (uint32_t i = 0; i < ns; ++i) {
+    uint32_t s = src[i];
+    if (s >= g.V) continue;
+    if (!have) {
+      uint32_t p = g.part_of(s);
+      lo = g.part_off[p];
+      hi = g.part_off[p + 1];
+      have = true;
+    }
+    if (s < lo || s >= hi) continue;
+    if (std::find(frontier.begin(), frontier.end(), s) != frontier.end()) continue;
+    frontier.push_back(s);
+  }
+  if (exclude)
+    for (uint32_t s : frontier) { hopmap[s] = 255; touched.push_back(s); }
+  for (int lvl = 1; lvl <= k && !frontier.empty(); ++lvl) {
+    next.clear();
+    for (uint32_t u : frontier) {
+      auto visit = [&](uint32_t v) {
+        if (hopmap[v] == 0) {
+          hopmap[v] = (uint8_t)lvl;
+          touched.push_back(v);
+          next.push_back(v);
+          res.emplace_back(v, (uint8_t)lvl);
+        }
+      };
+      if (mode != 1) {
+        for (uint32_t j = g.out_ptr[u]; j < g.out_ptr[u + 1]; ++j) visit(g.out_idx[j]);
+        if (te) *te += g.out_ptr[u + 1] - g.out_ptr[u];
+      }
+      if (mode != 0) {
+        for (uint32_t j = g.in_ptr[u]; j < g.in_ptr[u + 1]; ++j) visit(g.in_idx[j]);
+        if (te) *te += g.in_ptr[u + 1] - g.in_ptr[u];
+      }
+    }
+    frontier.swap(next);
+  }
+  for (uint32_t v : touched) hopmap[v] = 0;
+  std::sort(res.begin(), res.end());
+}
+
+template <class F>
+void parallel_for(uint64_t n, int n_threads, F f) {
+  if (n_threads <= 1 || n < 2) { f(0, 0, n); return; }
+  std::vector<std::thread> th;
+  uint64_t chunk = (n + n_threads - 1) / n_threads;
+  for (int t = 0; t < n_threads; ++t) {
+    uint64_t a = std::min<uint64_t>(n, t * chunk), b = std::min<uint64_t>(n, a + chunk);
+    if (a < b) th.emplace_back([=] { f(t, a, b); });
+  }
+  for (auto& x : th) x.join();
+}
+
+// byte-substring (String.contains on pre-lowered UTF-8)
+inline bool contains_bytes(const uint8_t* h, uint64_t hn, const uint8_t* n, uint64_t nn) {
+  if (nn == 0) return true;
+  if (nn > hn) return false;
+  return memmem(h, hn, n, nn) != nullptr;
+}
+
+struct RefService {                        // GraphService: one RefGraph per project (GS:34-38)
+  std::vector<RefGraph> graphs;
+  std::vector<uint32_t> part_off;          // global id ranges of the projects
+  uint32_t part_of(uint32_t v) const {
+    return (uint32_t)(std::upper_bound(part_off.begin(), part_off.end(), v) - part_off.begin() - 1);
+  }
+};
+
+}  // namespace
+
+// ==========================================================================================
+// C interface for ctypes
+// ==========================================================================================
+extern "C" {
+
+// ---- ref: single ProjectGraph, string API (used for the golden vectors) -------------------
+void* ora_ref_new() { return new RefGraph(); }
+void ora_ref_free(void* g) { delete (RefGraph*)g; }
+int ora_ref_add_node(void* g, const char* id, const char* file) { return ((RefGraph*)g)->add_node(id, file); }
+int ora_ref_add_dependency(void* g, const char* a, const char* b) { return ((RefGraph*)g)->add_dependency(a, b); }
+int ora_ref_mark_entry(void* g, const char* id) { return ((RefGraph*)g)->mark_entry(id); }
+uint32_t ora_ref_node_count(void* g) { return (uint32_t)((RefGraph*)g)->node_order.size(); }
+uint32_t ora_ref_entry_count(void* g) { return (uint32_t)((RefGraph*)g)->entry.order.size(); }
+int ora_ref_contains(void* g, const char* id) { return id && ((RefGraph*)g)->contains(id); }
+int ora_ref_is_entry(void* g, const char* id) { return id && ((RefGraph*)g)->entry.contains(id); }
+const char* ora_ref_source_file(void* g, const char* id) {
+  auto* G = (RefGraph*)g;
+  auto it = G->node_pos.find(id);
+  return it == G->node_pos.end() ? nullptr : G->files[it->second].c_str();
+}
+const char* ora_ref_name(void* g, uint32_t pos) { return ((RefGraph*)g)->node_order[pos].c_str(); }
+
+static uint32_t emit(const RefGraph& G, const std::vector<std::string>& v, uint32_t* out, uint32_t cap) {
+  uint32_t n = 0;
+  for (const auto& s : v) {
+    if (n < cap) out[n] = G.node_pos.at(s);
+    ++n;
+  }
+  return n;
+}
+// op: 0 dependencies, 1 dependents, 2 resolve, 3 analysisOrder, 4 entryPoints, 5 identifiers,
+//     6 search(arg=query). Results as node positions, in the order the restatement yields.
+uint32_t ora_ref_query(void* g, int op, const char* arg, uint32_t* out, uint32_t cap) {
+  auto& G = *(RefGraph*)g;
+  switch (op) {
+    case 0: return emit(G, G.dependencies(arg), out, cap);
+    case 1: return emit(G, G.dependents(arg), out, cap);
+    case 2: return emit(G, G.resolve(arg), out, cap);
+    case 3: return emit(G, G.analysis_order(), out, cap);
+    case 4: return emit(G, G.entry.order, out, cap);
+    case 5: return emit(G, G.node_order, out, cap);
+    case 6: return emit(G, G.search(arg ? arg : ""), out, cap);
+  }
+  return 0;
+}
+int64_t ora_ref_resolve_class_name(void* g, const char* name) { return ((RefGraph*)g)->resolve_class_name(name); }
+// khop over names given as positions; returns count, fills ids (discovery order) + hops
+uint32_t ora_ref_khop(void* g, const uint32_t* src, uint32_t ns, int k, int mode, int exclude,
+                      uint32_t* out_ids, uint8_t* out_hop, uint32_t cap) {
+  auto& G = *(RefGraph*)g;
+  std::vector<std::string> s;
+  for (uint32_t i = 0; i < ns; ++i)
+    if (src[i] < G.node_order.size()) s.push_back(G.node_order[src[i]]);
+  auto r = G.khop(s, k, mode, exclude != 0);
+  uint32_t n = 0;
+  for (auto& p : r) {
+    if (n < cap) { out_ids[n] = G.node_pos.at(p.first); out_hop[n] = (uint8_t)p.second; }
+    ++n;
+  }
+  return n;
+}
+
+// ---- ref service: many projects, built from arrays (for timing at BASELINE sizes) ----------
+void* ora_refsvc_new(uint32_t V, const uint64_t* name_off, const uint8_t* name_bytes, uint64_t E,
+                     const uint32_t* src, const uint32_t* dst, uint32_t n_entry, const uint32_t* ent,
+                     uint32_t n_parts, const uint32_t* part_off) {
+  auto* S = new RefService();
+  if (n_parts && part_off) S->part_off.assign(part_off, part_off + n_parts + 1);
+  else S->part_off = {0, V};
+  uint32_t P = (uint32_t)S->part_off.size() - 1;
+  S->graphs.resize(P);
+  std::vector<std::string> names(V);
+  for (uint32_t v = 0; v < V; ++v)
+    names[v].assign((const char*)name_bytes + name_off[v], name_off[v + 1] - name_off[v]);
+  for (uint32_t p = 0; p < P; ++p)
+    for (uint32_t v = S->part_off[p]; v < S->part_off[p + 1]; ++v)
+      S->graphs[p].add_node(names[v].c_str(), "f");
+  for (uint64_t i = 0; i < E; ++i) {
+    if (src[i] >= V || dst[i] >= V) continue;
+    uint32_t p = S->part_of(src[i]);
+    S->graphs[p].add_dependency(names[src[i]].c_str(), names[dst[i]].c_str());
+  }
+  for (uint32_t i = 0; i < n_entry; ++i)
+    if (ent[i] < V) S->graphs[S->part_of(ent[i])].mark_entry(names[ent[i]].c_str());
+  return S;
+}
+void ora_refsvc_free(void* s) { delete (RefService*)s; }
+
+// Batched stack-trace neighbour resolution the way the reference does it, string keyed.
+// Queries [q_begin, q_end) of the batch; results are only counted (sum + xor checksum of
+// global ids*hop) so the timed region holds no result marshalling.  Returns total results.
+uint64_t ora_refsvc_khop_batch(void* s, int mode, int k, int exclude, uint64_t q_begin, uint64_t q_end,
+                               const uint32_t* q_off, const uint32_t* q_src, int n_threads,
+                               uint64_t* checksum) {
+  auto& S = *(RefService*)s;
+  std::atomic<uint64_t> total{0}, chk{0};
+  parallel_for(q_end - q_begin, n_threads, [&](int, uint64_t a, uint64_t b) {
+    uint64_t t = 0, c = 0;
+    for (uint64_t q = q_begin + a; q < q_begin + b; ++q) {
+      const uint32_t* src = q_src + q_off[q];
+      uint32_t ns = q_off[q + 1] - q_off[q];
+      if (!ns) continue;
+      uint32_t V = S.part_off.back();
+      uint32_t first = UINT32_MAX;
+      for (uint32_t i = 0; i < ns; ++i)
+        if (src[i] < V) { first = src[i]; break; }
+      if (first == UINT32_MAX) continue;
+      uint32_t p = S.part_of(first);
+      const RefGraph& G = S.graphs[p];
+      std::vector<std::string> names;
+      for (uint32_t i = 0; i < ns; ++i)
+        if (src[i] >= S.part_off[p] && src[i] < S.part_off[p + 1])
+          names.push_back(G.node_order[src[i] - S.part_off[p]]);
+      auto r = G.khop(names, k, mode, exclude != 0);
+      t += r.size();
+      for (auto& x : r) c ^= ((uint64_t)(G.node_pos.at(x.first) + S.part_off[p]) + 1) * (uint64_t)x.second * 0x9E3779B97F4A7C15ull;
+    }
+    total += t;
+    chk ^= c;
+  });
+  if (checksum) *checksum = chk.load();
+  return total.load();
+}
+
+// reference-style search over one project's identifiers (CCS:1507-1526); returns #hits
+uint64_t ora_refsvc_search_batch(void* s, uint32_t project, uint64_t q_begin, uint64_t q_end,
+                                 const uint32_t* q_off, const uint8_t* q_bytes, int n_threads) {
+  auto& S = *(RefService*)s;
+  const RefGraph& G = S.graphs[project];
+  std::atomic<uint64_t> total{0};
+  parallel_for(q_end - q_begin, n_threads, [&](int, uint64_t a, uint64_t b) {
+    uint64_t t = 0;
+    for (uint64_t q = q_begin + a; q < q_begin + b; ++q) {
+      std::string query((const char*)q_bytes + q_off[q], q_off[q + 1] - q_off[q]);
+      t += G.search(query).size();
+    }
+    total += t;
+  });
+  return total.load();
+}
+
+// ---- csr ------------------------------------------------------------------------------------
+void* ora_csr_new(uint32_t V, uint64_t E, const uint32_t* src, const uint32_t* dst, uint32_t n_entry,
+                  const uint32_t* ent, uint32_t n_parts, const uint32_t* part_off) {
+  auto* g = new CsrGraph();
+  g->build(V, E, src, dst, n_entry, ent, n_parts, part_off);
+  return g;
+}
+void ora_csr_free(void* g) { delete (CsrGraph*)g; }
+uint64_t ora_csr_edges(void* g) { return ((CsrGraph*)g)->out_idx.size(); }
+uint64_t ora_csr_dropped(void* g) { return ((CsrGraph*)g)->dropped; }
+uint64_t ora_csr_dups(void* g) { return ((CsrGraph*)g)->dups; }
+void ora_csr_arrays(void* g, const uint32_t** op, const uint32_t** oi, const uint32_t** ip, const uint32_t** ii) {
+  auto* G = (CsrGraph*)g;
+  *op = G->out_ptr.data(); *oi = G->out_idx.data(); *ip = G->in_ptr.data(); *ii = G->in_idx.data();
+}
+
+// adjacency rows (T0: dir 0 = dependencies in insertion order; T1: dir 1 = dependents, ascending
+// source id). Invalid id -> empty row. Returns needed entries; fills up to cap.
+uint64_t ora_csr_adjacency_batch(void* g, int dir, uint64_t n, const uint32_t* ids, uint64_t* out_off,
+                                 uint32_t* out_ids, uint64_t cap) {
+  auto& G = *(CsrGraph*)g;
+  const auto& ptr = dir ? G.in_ptr : G.out_ptr;
+  const auto& idx = dir ? G.in_idx : G.out_idx;
+  uint64_t w = 0;
+  for (uint64_t i = 0; i < n; ++i) {
+    out_off[i] = w;
+    if (ids[i] >= G.V) continue;
+    for (uint32_t j = ptr[ids[i]]; j < ptr[ids[i] + 1]; ++j, ++w)
+      if (w < cap) out_ids[w] = idx[j];
+  }
+  out_off[n] = w;
+  return w;
+}
+
+// k-hop batch (T2/T3/T4 ext.). Rows sorted by ascending id. Two-call protocol: pass
+// out_ids = NULL to get sizes only. Returns total results; *te = adjacency entries read.
+uint64_t ora_csr_khop_batch(void* g, int mode, int k, int exclude, uint64_t nq, const uint32_t* q_off,
+                            const uint32_t* q_src, uint64_t* out_off, uint32_t* out_ids,
+                            uint8_t* out_hop, uint64_t cap, int n_threads, uint64_t* te_out) {
+  auto& G = *(CsrGraph*)g;
+  std::vector<uint64_t> cnt(nq + 1, 0);
+  std::atomic<uint64_t> te_total{0};
+  // pass 1: sizes
+  parallel_for(nq, n_threads, [&](int, uint64_t a, uint64_t b) {
+    std::vector<uint8_t> hopmap(G.V, 0);
+    std::vector<uint32_t> touched, fr, nx;
+    std::vector<std::pair<uint32_t, uint8_t>> res;
+    uint64_t te = 0;
+    for (uint64_t q = a; q < b; ++q) {
+      csr_khop(G, mode, k, exclude != 0, q_src + q_off[q], q_off[q + 1] - q_off[q], hopmap, touched, fr, nx, res, &te);
+      cnt[q] = res.size();
+    }
+    te_total += te;
+  });
+  uint64_t w = 0;
+  for (uint64_t q = 0; q < nq; ++q) { out_off[q] = w; w += cnt[q]; }
+  out_off[nq] = w;
+  if (te_out) *te_out = te_total.load();
+  if (!out_ids || w > cap) return w;
+  parallel_for(nq, n_threads, [&](int, uint64_t a, uint64_t b) {
+    std::vector<uint8_t> hopmap(G.V, 0);
+    std::vector<uint32_t> touched, fr, nx;
+    std::vector<std::pair<uint32_t, uint8_t>> res;
+    for (uint64_t q = a; q < b; ++q) {
+      csr_khop(G, mode, k, exclude != 0, q_src + q_off[q], q_off[q + 1] - q_off[q], hopmap, touched, fr, nx, res, nullptr);
+      uint64_t o = out_off[q];
+      for (auto& p : res) { out_ids[o] = p.first; out_hop[o] = p.second; ++o; }
+    }
+  });
+  return w;
+}
+
+// closure / BFS levels from a source set over direction dir (0 out, 1 in). level = UINT32_MAX
+// if unreachable; sources are level 0. Returns number reached; *te = adjacency entries read.
+uint64_t ora_csr_closure(void* g, int dir, uint32_t ns, const uint32_t* src, uint32_t* level, uint64_t* te_out) {
+  auto& G = *(CsrGraph*)g;
+  const auto& ptr = dir ? G.in_ptr : G.out_ptr;
+  const auto& idx = dir ? G.in_idx : G.out_idx;
+  std::fill(level, level + G.V, UINT32_MAX);
+  std::vector<uint32_t> fr, nx;
+  for (uint32_t i = 0; i < ns; ++i)
+    if (src[i] < G.V && level[src[i]] == UINT32_MAX) { level[src[i]] = 0; fr.push_back(src[i]); }
+  uint64_t reached = fr.size(), te = 0;
+  for (uint32_t lvl = 1; !fr.empty(); ++lvl) {
+    nx.clear();
+    for (uint32_t u : fr) {
+      te += ptr[u + 1] - ptr[u];
+      for (uint32_t j = ptr[u]; j < ptr[u + 1]; ++j) {
+        uint32_t v = idx[j];
+        if (level[v] == UINT32_MAX) { level[v] = lvl; nx.push_back(v); }
+      }
+    }
+    reached += nx.size();
+    fr.swap(nx);
+  }
+  if (te_out) *te_out = te;
+  return reached;
+}
+
+// T5 analysisOrder (PG:390-421) over CSR: FIFO BFS from entry points (insertion order) along
+// out rows (insertion order), then every remaining vertex in id order.
+void ora_csr_analysis_order(void* g, uint32_t* order) {
+  auto& G = *(CsrGraph*)g;
+  std::vector<uint8_t> vis(G.V, 0);
+  uint64_t w = 0, head = 0;
+  for (uint32_t e : G.entry)
+    if (!vis[e]) { vis[e] = 1; order[w++] = e; }
+  while (head < w) {
+    uint32_t u = order[head++];
+    for (uint32_t j = G.out_ptr[u]; j < G.out_ptr[u + 1]; ++j) {
+      uint32_t v = G.out_idx[j];
+      if (!vis[v]) { vis[v] = 1; order[w++] = v; }
+    }
+  }
+  for (uint32_t v = 0; v < G.V; ++v)
+    if (!vis[v]) order[w++] = v;
+}
+
+uint32_t ora_csr_entry_points(void* g, uint32_t* out, uint32_t cap) {
+  auto& G = *(CsrGraph*)g;
+  for (uint32_t i = 0; i < G.entry.size() && i < cap; ++i) out[i] = G.entry[i];
+  return (uint32_t)G.entry.size();
+}
+
+// ---- search over a packed, pre-lowered arena -------------------------------------------------
+// kind 0: S1 all hits, ascending id (CCS:1511-1526).
+// kind 1: S2 step 2, first id whose simple name (after last '.') equals the query (GQS:434-446).
+// kind 2: S2 step 3, first id containing the query (GQS:449-453).
+// Vertex range [v_lo, v_hi) restricts the scan to one project. Queries are pre-lowered bytes.
+uint64_t ora_search_batch(uint32_t v_lo, uint32_t v_hi, const uint64_t* name_off, const uint8_t* lower_bytes,
+                          int kind, uint64_t nq, const uint32_t* q_off, const uint8_t* q_bytes,
+                          uint64_t* out_off, uint32_t* out_ids, uint64_t cap, int n_threads) {
+  std::vector<std::vector<uint32_t>> rows(nq);
+  parallel_for(nq, n_threads, [&](int, uint64_t a, uint64_t b) {
+    for (uint64_t q = a; q < b; ++q) {
+      const uint8_t* pat = q_bytes + q_off[q];
+      uint64_t pn = q_off[q + 1] - q_off[q];
+      auto& row = rows[q];
+      for (uint32_t v = v_lo; v < v_hi; ++v) {
+        const uint8_t* nm = lower_bytes + name_off[v];
+        uint64_t nn = name_off[v + 1] - name_off[v];
+        bool hit;
+        if (kind == 1) {
+          uint64_t st = 0;
+          for (uint64_t i = nn; i > 0; --i)
+            if (nm[i - 1] == '.') { st = i; break; }
+          hit = (nn - st == pn) && memcmp(nm + st, pat, pn) == 0;
+        } else {
+          hit = contains_bytes(nm, nn, pat, pn);
+        }
+        if (hit) {
+          row.push_back(v);
+          if (kind != 0) break;
+        }
+      }
+    }
+  });
+  uint64_t w = 0;
+  for (uint64_t q = 0; q < nq; ++q) {
+    out_off[q] = w;
+    for (uint32_t v : rows[q]) {
+      if (out_ids && w < cap) out_ids[w] = v;
+      ++w;
+    }
+  }
+  out_off[nq] = w;
+  return w;
+}
+
+int ora_hardware_threads() { return (int)std::thread::hardware_concurrency(); }
+
+}  // extern "C"
