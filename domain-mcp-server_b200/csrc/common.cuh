@@ -1,0 +1,251 @@
+// Internal declarations shared by the .cu files of libdmgraph.so (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+
+#include <atomic>
+#include <cstdarg>
+#include <cstdint>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "../../include/dmgraph.h"
+
+namespace dmg {
+
+// ---------------------------------------------------------------------------------------------
+// errors: thread-local message, status codes; nothing is ever printed (MCP stdio hygiene)
+// ---------------------------------------------------------------------------------------------
+void set_error(const char* fmt, ...);
+int32_t cuda_fail(cudaError_t e, const char* what, const char* file, int line);
+
+#define DMG_CUDA(call)                                                         \
+  do {                                                                         \
+    cudaError_t _e = (call);                                                   \
+    if (_e != cudaSuccess) return ::dmg::cuda_fail(_e, #call, __FILE__, __LINE__); \
+  } while (0)
+
+#define DMG_TRY(expr)                 \
+  do {                                \
+    int32_t _s = (expr);              \
+    if (_s != DMG_OK) return _s;      \
+  } while (0)
+
+// ---------------------------------------------------------------------------------------------
+// growable device buffer owned by a call context
+// ---------------------------------------------------------------------------------------------
+struct DevBuf {
+  void* p = nullptr;
+  size_t cap = 0;
+  int32_t reserve(size_t bytes);   // grows (never shrinks); contents are NOT preserved
+  void release();
+  template <class T> T* as() const { return reinterpret_cast<T*>(p); }
+};
+
+enum KernelId : int {
+  K_KHOP_SMALL = 0,
+  K_KHOP_GLOBAL,
+  K_ADJ_GATHER,
+  K_ENTRY_FLAGS,
+  K_CLOSURE_INIT,
+  K_CLOSURE_STEP,
+  K_CLOSURE_BOTTOMUP,
+  K_ORDER_DEG,
+  K_ORDER_MIN,
+  K_ORDER_CLAIM,
+  K_ORDER_TAIL,
+  K_SCAN_BLOCK,
+  K_SCAN_TOP,
+  K_SCAN_ADD,
+  K_SEARCH_SCAN,
+  K_SEARCH_FIRST,
+  K_SEARCH_EMIT,
+  K_FLUSH,
+  K_MISC,
+  K_COUNT
+};
+extern const char* const kKernelNames[K_COUNT];
+
+struct Engine;
+
+// Counters a kernel family reports back (device memory, zeroed per call, read back pinned).
+struct DevCounters {
+  unsigned long long ticket;     // dynamic work distribution
+  unsigned long long total;      // total entries (== out_off[n])
+  unsigned long long edges;      // adjacency entries read
+  unsigned long long rows;       // rows expanded
+  unsigned long long aux[4];
+};
+
+// One in-flight call: its own stream, workspace and event pool.  Handed out by the engine so
+// that any number of host threads can query one graph concurrently (SURVEY 8b "Threading").
+struct CallCtx {
+  Engine* eng = nullptr;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev_begin = nullptr, ev_end = nullptr;
+  DevBuf status, scratch, q_off, q_src, q_bytes, out_off, out_ids, out_hop, tmp0, tmp1, tmp2, tmp3;
+  DevCounters* d_counters = nullptr;
+  DevCounters* h_counters = nullptr;   // pinned
+  dmg_call_stats stats{};
+  struct ProfEv { int kid; cudaEvent_t a, b; };
+  std::vector<ProfEv> prof;            // events recorded during this call
+  std::vector<cudaEvent_t> ev_pool;
+  int32_t init(Engine* e);
+  void destroy();
+  cudaEvent_t get_event();
+  int32_t begin();                     // zero stats, record ev_begin
+  int32_t finish();                    // record ev_end, sync, harvest profile events
+};
+
+struct Engine {
+  int device = 0;
+  int sm_count = 148;
+  size_t smem_optin = 0;
+  size_t scratch_budget = 4ull << 30;
+  size_t l2_bytes = 0;
+  std::mutex mu;
+  std::vector<CallCtx*> free_ctx, all_ctx;
+  std::atomic<int> profile{0};
+  std::mutex prof_mu;
+  uint64_t prof_launches[K_COUNT] = {0};
+  double prof_ms[K_COUNT] = {0};
+  void* flush_buf = nullptr;
+  size_t flush_bytes = 0;
+  CallCtx* acquire();
+  void release(CallCtx* c);
+};
+
+struct CtxGuard {
+  Engine* e;
+  CallCtx* c;
+  explicit CtxGuard(Engine* en) : e(en), c(en->acquire()) {}
+  ~CtxGuard() { if (c) e->release(c); }
+};
+
+void publish_stats(const dmg_call_stats& s);   // thread-local "last call" record
+
+// Launch helper: counts the launch, brackets it with events when profiling is on.
+struct LaunchScope {
+  CallCtx* c;
+  cudaEvent_t a = nullptr, b = nullptr;
+  int kid;
+  LaunchScope(CallCtx* ctx, int kernel_id) : c(ctx), kid(kernel_id) {
+    c->stats.kernel_launches++;
+    if (c->eng->profile.load(std::memory_order_relaxed)) {
+      a = c->get_event();
+      b = c->get_event();
+      cudaEventRecord(a, c->stream);
+    }
+  }
+  ~LaunchScope() {
+    if (a) {
+      cudaEventRecord(b, c->stream);
+      c->prof.push_back({kid, a, b});
+    }
+  }
+};
+
+}  // namespace dmg
+
+// ---------------------------------------------------------------------------------------------
+// opaque handle bodies
+// ---------------------------------------------------------------------------------------------
+struct dmg_engine : dmg::Engine {};
+
+struct dmg_graph {
+  dmg_engine* eng = nullptr;
+  std::atomic<int> refs{1};
+  dmg_graph_info info{};
+  // device-resident CSR (u32 offsets: E < 2^32), SURVEY.md 8 conventions
+  uint32_t* d_out_ptr = nullptr;   // [V+1]
+  uint32_t* d_out_idx = nullptr;   // [E]   row order = addDependency order
+  uint32_t* d_in_ptr = nullptr;    // [V+1]
+  uint32_t* d_in_idx = nullptr;    // [E]   row order = ascending source id
+  uint32_t* d_part_off = nullptr;  // [P+1]
+  uint32_t* d_entry = nullptr;     // [n_entry] insertion order
+  uint32_t* d_entry_bits = nullptr;  // [ceil(V/32)]
+  uint64_t* d_name_off = nullptr;  // [V+1] or null
+  uint8_t* d_lower = nullptr;      // pre-lowered name arena (+16 B zero pad)
+  std::vector<uint32_t> h_part_off, h_entry;
+};
+
+// ---------------------------------------------------------------------------------------------
+// device helpers
+// ---------------------------------------------------------------------------------------------
+#ifdef __CUDACC__
+namespace dmg {
+
+constexpr unsigned FULL = 0xffffffffu;
+
+__device__ __forceinline__ uint64_t ld_relaxed_u64(const uint64_t* p) {
+  uint64_t v;
+  asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_relaxed_u64(uint64_t* p, uint64_t v) {
+  asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ uint64_t warp_sum_u64(uint64_t v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(FULL, v, o);
+  return v;
+}
+__device__ __forceinline__ uint32_t warp_sum_u32(uint32_t v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(FULL, v, o);
+  return v;
+}
+__device__ __forceinline__ uint32_t warp_incl_scan_u32(uint32_t v) {
+  const unsigned lane = threadIdx.x & 31;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    uint32_t t = __shfl_up_sync(FULL, v, o);
+    if (lane >= (unsigned)o) v += t;
+  }
+  return v;
+}
+__device__ __forceinline__ unsigned lanemask_lt() {
+  unsigned m;
+  asm("mov.u32 %0, %%lanemask_lt;" : "=r"(m));
+  return m;
+}
+
+// Ordered output allocation across work items that finish out of order (decoupled look-back).
+// Work item `q` (items are handed out by an atomic ticket, so every predecessor of a running
+// item has itself started) publishes how many entries it produced and learns the sum over all
+// items before it.  status[] must be zero before the launch.  One 64-bit word carries flag and
+// value, so a relaxed load sees both or neither.  Call with all 32 lanes of ONE warp.
+constexpr uint64_t LB_AGG = 1ull << 62, LB_PRE = 2ull << 62, LB_VAL = (1ull << 62) - 1;
+
+__device__ __forceinline__ uint64_t lookback_exclusive(uint64_t* status, uint64_t q, uint64_t count) {
+  const unsigned lane = threadIdx.x & 31;
+  if (q == 0) {
+    if (lane == 0) st_relaxed_u64(status, LB_PRE | count);
+    return 0;
+  }
+  if (lane == 0) st_relaxed_u64(status + q, LB_AGG | count);
+  uint64_t excl = 0;
+  long long idx = (long long)q - 1;
+  while (true) {
+    const long long j = idx - (long long)lane;
+    uint64_t v;
+    do {
+      v = (j >= 0) ? ld_relaxed_u64(status + j) : LB_PRE;
+    } while (__any_sync(FULL, (v >> 62) == 0));
+    const unsigned pm = __ballot_sync(FULL, (v >> 62) == 2);
+    if (pm) {
+      const int first = __ffs(pm) - 1;
+      excl += warp_sum_u64(((int)lane <= first) ? (v & LB_VAL) : 0ull);
+      break;
+    }
+    excl += warp_sum_u64(v & LB_VAL);
+    idx -= 32;
+  }
+  if (lane == 0) st_relaxed_u64(status + q, LB_PRE | (excl + count));
+  return excl;
+}
+
+}  // namespace dmg
+#endif

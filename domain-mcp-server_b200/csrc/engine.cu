@@ -1,0 +1,490 @@
+// Engine, call contexts, graph upload (GraphService lifecycle, GS:34-122) and small utilities.
+#include <algorithm>
+#include <new>
+
+#include "common.cuh"
+
+namespace dmg {
+
+static thread_local char g_err[512] = "";
+static thread_local dmg_call_stats g_last_stats{};
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+int32_t cuda_fail(cudaError_t e, const char* what, const char* file, int line) {
+  const char* base = strrchr(file, '/');
+  set_error("CUDA error %d (%s) at %s:%d: %s", (int)e, cudaGetErrorString(e), base ? base + 1 : file, line, what);
+  if (e == cudaErrorMemoryAllocation) {
+    cudaGetLastError();
+    return DMG_ENOMEM;
+  }
+  return (e == cudaErrorNoDevice || e == cudaErrorInsufficientDriver) ? DMG_ENODEV : DMG_ECUDA;
+}
+
+void publish_stats(const dmg_call_stats& s) { g_last_stats = s; }
+
+const char* const kKernelNames[K_COUNT] = {
+    "khop_small", "khop_global", "adjacency_gather", "entry_flags", "closure_init", "closure_topdown",
+    "closure_bottomup", "order_degrees", "order_minslot", "order_claim", "order_tail", "scan_block",
+    "scan_top", "scan_add", "search_scan", "search_first", "search_emit", "flush_l2", "misc"};
+
+int32_t DevBuf::reserve(size_t bytes) {
+  if (bytes <= cap && p) return DMG_OK;
+  if (p) {
+    cudaFree(p);
+    p = nullptr;
+    cap = 0;
+  }
+  size_t want = std::max<size_t>(bytes, 256);
+  want = (want + 255) & ~size_t(255);
+  DMG_CUDA(cudaMalloc(&p, want));
+  cap = want;
+  return DMG_OK;
+}
+void DevBuf::release() {
+  if (p) cudaFree(p);
+  p = nullptr;
+  cap = 0;
+}
+
+int32_t CallCtx::init(Engine* e) {
+  eng = e;
+  DMG_CUDA(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
+  DMG_CUDA(cudaEventCreate(&ev_begin));
+  DMG_CUDA(cudaEventCreate(&ev_end));
+  DMG_CUDA(cudaMalloc((void**)&d_counters, sizeof(DevCounters)));
+  DMG_CUDA(cudaMallocHost((void**)&h_counters, sizeof(DevCounters)));
+  return DMG_OK;
+}
+void CallCtx::destroy() {
+  for (DevBuf* b : {&status, &scratch, &q_off, &q_src, &q_bytes, &out_off, &out_ids, &out_hop, &tmp0, &tmp1, &tmp2, &tmp3})
+    b->release();
+  for (auto ev : ev_pool) cudaEventDestroy(ev);
+  for (auto& p : prof) {
+    cudaEventDestroy(p.a);
+    cudaEventDestroy(p.b);
+  }
+  if (d_counters) cudaFree(d_counters);
+  if (h_counters) cudaFreeHost(h_counters);
+  if (ev_begin) cudaEventDestroy(ev_begin);
+  if (ev_end) cudaEventDestroy(ev_end);
+  if (stream) cudaStreamDestroy(stream);
+}
+cudaEvent_t CallCtx::get_event() {
+  if (!ev_pool.empty()) {
+    cudaEvent_t e = ev_pool.back();
+    ev_pool.pop_back();
+    return e;
+  }
+  cudaEvent_t e = nullptr;
+  cudaEventCreate(&e);
+  return e;
+}
+int32_t CallCtx::begin() {
+  memset(&stats, 0, sizeof(stats));
+  DMG_CUDA(cudaSetDevice(eng->device));
+  DMG_CUDA(cudaEventRecord(ev_begin, stream));
+  return DMG_OK;
+}
+int32_t CallCtx::finish() {
+  DMG_CUDA(cudaEventRecord(ev_end, stream));
+  DMG_CUDA(cudaStreamSynchronize(stream));
+  float ms = 0.f;
+  cudaEventElapsedTime(&ms, ev_begin, ev_end);
+  stats.device_ms = ms;
+  if (!prof.empty()) {
+    std::lock_guard<std::mutex> lk(eng->prof_mu);
+    for (auto& p : prof) {
+      float t = 0.f;
+      if (cudaEventElapsedTime(&t, p.a, p.b) == cudaSuccess) {
+        eng->prof_launches[p.kid]++;
+        eng->prof_ms[p.kid] += t;
+      }
+      ev_pool.push_back(p.a);
+      ev_pool.push_back(p.b);
+    }
+    prof.clear();
+  }
+  publish_stats(stats);
+  return DMG_OK;
+}
+
+CallCtx* Engine::acquire() {
+  {
+    std::lock_guard<std::mutex> lk(mu);
+    if (!free_ctx.empty()) {
+      CallCtx* c = free_ctx.back();
+      free_ctx.pop_back();
+      return c;
+    }
+  }
+  cudaSetDevice(device);
+  CallCtx* c = new (std::nothrow) CallCtx();
+  if (!c) return nullptr;
+  if (c->init(this) != DMG_OK) {
+    c->destroy();
+    delete c;
+    return nullptr;
+  }
+  std::lock_guard<std::mutex> lk(mu);
+  all_ctx.push_back(c);
+  return c;
+}
+void Engine::release(CallCtx* c) {
+  std::lock_guard<std::mutex> lk(mu);
+  free_ctx.push_back(c);
+}
+
+__global__ void flush_kernel(uint4* p, size_t n, uint32_t salt) {
+  size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  for (; i < n; i += stride) p[i] = make_uint4(salt, (uint32_t)i, salt ^ 0x5bd1e995u, 0u);
+}
+
+}  // namespace dmg
+
+using namespace dmg;
+
+// ---- graph upload ----------------------------------------------------------------------------
+static void free_graph(dmg_graph* g) {
+  cudaSetDevice(g->eng->device);
+  for (void* p : {(void*)g->d_out_ptr, (void*)g->d_out_idx, (void*)g->d_in_ptr, (void*)g->d_in_idx,
+                  (void*)g->d_part_off, (void*)g->d_entry, (void*)g->d_entry_bits, (void*)g->d_name_off,
+                  (void*)g->d_lower})
+    if (p) cudaFree(p);
+  delete g;
+}
+
+template <class T>
+static int32_t upload(T** d, const T* h, size_t n, uint64_t* bytes) {
+  size_t b = std::max<size_t>(n * sizeof(T), 16);
+  DMG_CUDA(cudaMalloc((void**)d, b));
+  if (n) DMG_CUDA(cudaMemcpy(*d, h, n * sizeof(T), cudaMemcpyHostToDevice));
+  *bytes += b;
+  return DMG_OK;
+}
+
+// =============================================================================================
+// C ABI
+// =============================================================================================
+extern "C" {
+
+const char* dmg_last_error(void) { return g_err; }
+const char* dmg_version(void) { return "dmgraph 0.1 (sm_100a)"; }
+
+int32_t dmg_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) {
+    cudaGetLastError();
+    return 0;
+  }
+  return n;
+}
+
+int32_t dmg_engine_create(const dmg_engine_opts* opts, dmg_engine** out) {
+  if (!out) {
+    set_error("dmg_engine_create: out is NULL");
+    return DMG_EINVAL;
+  }
+  *out = nullptr;
+  int n = 0;
+  cudaError_t ce = cudaGetDeviceCount(&n);
+  if (ce != cudaSuccess || n == 0) {
+    cudaGetLastError();
+    set_error("no CUDA device: libdmgraph has no CPU fallback (%s)", ce == cudaSuccess ? "0 devices" : cudaGetErrorString(ce));
+    return DMG_ENODEV;
+  }
+  int dev = opts ? opts->device : 0;
+  if (dev < 0 || dev >= n) {
+    set_error("device ordinal %d out of range (0..%d)", dev, n - 1);
+    return DMG_EINVAL;
+  }
+  DMG_CUDA(cudaSetDevice(dev));
+  cudaDeviceProp prop;
+  DMG_CUDA(cudaGetDeviceProperties(&prop, dev));
+  if (prop.major < 10) {
+    set_error("device %d is sm_%d%d; libdmgraph is built for sm_100a only", dev, prop.major, prop.minor);
+    return DMG_ENODEV;
+  }
+  dmg_engine* e = new (std::nothrow) dmg_engine();
+  if (!e) return DMG_ENOMEM;
+  e->device = dev;
+  e->sm_count = prop.multiProcessorCount;
+  e->smem_optin = prop.sharedMemPerBlockOptin;
+  e->l2_bytes = (size_t)prop.l2CacheSize;
+  if (opts && opts->scratch_bytes) e->scratch_budget = opts->scratch_bytes;
+  *out = e;
+  return DMG_OK;
+}
+
+void dmg_engine_destroy(dmg_engine* e) {
+  if (!e) return;
+  cudaSetDevice(e->device);
+  cudaDeviceSynchronize();
+  for (CallCtx* c : e->all_ctx) {
+    c->destroy();
+    delete c;
+  }
+  if (e->flush_buf) cudaFree(e->flush_buf);
+  delete e;
+}
+
+int32_t dmg_graph_create(dmg_engine* e, const dmg_graph_desc* d, dmg_graph** out) {
+  if (!e || !d || !out) {
+    set_error("dmg_graph_create: NULL argument");
+    return DMG_EINVAL;
+  }
+  *out = nullptr;
+  const uint32_t V = d->n_vertices;
+  const uint64_t E = d->n_edges;
+  if ((E && (!d->edge_src || !d->edge_dst)) || (d->n_entry && !d->entry_ids)) {
+    set_error("dmg_graph_create: edge/entry arrays missing");
+    return DMG_EINVAL;
+  }
+  if (E >= 0xFFFFFFF0ull) {
+    set_error("dmg_graph_create: %llu edges exceed the 32-bit CSR offset range", (unsigned long long)E);
+    return DMG_EINVAL;
+  }
+  if (d->name_off && !d->name_bytes && d->name_off[V] != 0) {
+    set_error("dmg_graph_create: name_off given without name_bytes");
+    return DMG_EINVAL;
+  }
+  // partitions (projects)
+  std::vector<uint32_t> part;
+  if (d->n_parts && d->part_off) {
+    part.assign(d->part_off, d->part_off + d->n_parts + 1);
+    bool ok = part.front() == 0 && part.back() == V;
+    for (size_t i = 1; ok && i < part.size(); ++i) ok = part[i] >= part[i - 1];
+    if (!ok) {
+      set_error("dmg_graph_create: part_off must be non-decreasing from 0 to n_vertices");
+      return DMG_EINVAL;
+    }
+  } else {
+    part = {0, V};
+  }
+  std::vector<uint32_t> part_of;   // only needed to validate multi-project uploads
+  auto find_part = [&](uint32_t v) {
+    return (uint32_t)(std::upper_bound(part.begin(), part.end(), v) - part.begin() - 1);
+  };
+
+  // ---- host CSR build, O(V+E): stable counting sort by source, per-row stamp dedup ----------
+  dmg_graph* g = new (std::nothrow) dmg_graph();
+  if (!g) return DMG_ENOMEM;
+  g->eng = e;
+  uint64_t dropped = 0, dups = 0;
+  std::vector<uint32_t> out_ptr(V + 1, 0), in_ptr(V + 1, 0), out_idx, in_idx;
+  try {
+    std::vector<uint32_t> cnt(V + 1, 0);
+    for (uint64_t i = 0; i < E; ++i) {
+      if (d->edge_src[i] >= V || d->edge_dst[i] >= V) {   // PG:179-181
+        ++dropped;
+        continue;
+      }
+      ++cnt[d->edge_src[i] + 1];
+    }
+    for (uint32_t v = 0; v < V; ++v) cnt[v + 1] += cnt[v];
+    std::vector<uint32_t> raw(cnt[V]);
+    {
+      std::vector<uint32_t> cur(cnt.begin(), cnt.end() - 1);
+      for (uint64_t i = 0; i < E; ++i) {
+        if (d->edge_src[i] >= V || d->edge_dst[i] >= V) continue;
+        raw[cur[d->edge_src[i]]++] = d->edge_dst[i];
+      }
+    }
+    std::vector<uint32_t> stamp(V, 0);   // stamp[t] == s+1  <=>  edge s->t already kept
+    out_idx.reserve(raw.size());
+    for (uint32_t s = 0; s < V; ++s) {
+      for (uint32_t j = cnt[s]; j < cnt[s + 1]; ++j) {
+        const uint32_t t = raw[j];
+        if (stamp[t] == s + 1) {   // PG:182 LinkedHashSet.add: first position wins
+          ++dups;
+          continue;
+        }
+        stamp[t] = s + 1;
+        out_idx.push_back(t);
+        ++in_ptr[t + 1];
+      }
+      out_ptr[s + 1] = (uint32_t)out_idx.size();
+    }
+    for (uint32_t v = 0; v < V; ++v) in_ptr[v + 1] += in_ptr[v];
+    in_idx.resize(out_idx.size());
+    {
+      std::vector<uint32_t> cur(in_ptr.begin(), in_ptr.end() - 1);
+      for (uint32_t s = 0; s < V; ++s)   // ascending source id => canonical in-row order
+        for (uint32_t j = out_ptr[s]; j < out_ptr[s + 1]; ++j) in_idx[cur[out_idx[j]]++] = s;
+    }
+    if (part.size() > 2) {
+      for (uint32_t s = 0; s < V; ++s) {
+        if (out_ptr[s] == out_ptr[s + 1]) continue;
+        const uint32_t p = find_part(s);
+        for (uint32_t j = out_ptr[s]; j < out_ptr[s + 1]; ++j)
+          if (out_idx[j] < part[p] || out_idx[j] >= part[p + 1]) {
+            set_error("dmg_graph_create: edge %u->%u crosses project ranges", s, out_idx[j]);
+            delete g;
+            return DMG_EINVAL;
+          }
+      }
+    }
+    // entry points: insertion order, unknown ids ignored, no duplicates (PG:190-197)
+    std::vector<uint8_t> is_e(V, 0);
+    for (uint32_t i = 0; i < d->n_entry; ++i) {
+      const uint32_t v = d->entry_ids[i];
+      if (v < V && !is_e[v]) {
+        is_e[v] = 1;
+        g->h_entry.push_back(v);
+      }
+    }
+  } catch (const std::bad_alloc&) {
+    delete g;
+    set_error("dmg_graph_create: host out of memory");
+    return DMG_ENOMEM;
+  }
+  g->h_part_off = part;
+  uint32_t max_part = 0;
+  for (size_t i = 1; i < part.size(); ++i) max_part = std::max(max_part, part[i] - part[i - 1]);
+
+  // ---- upload ---------------------------------------------------------------------------------
+  cudaSetDevice(e->device);
+  uint64_t bytes = 0;
+  int32_t st = DMG_OK;
+  std::vector<uint32_t> ebits((V + 31) / 32 + 1, 0);
+  for (uint32_t v : g->h_entry) ebits[v >> 5] |= 1u << (v & 31);
+  if ((st = upload(&g->d_out_ptr, out_ptr.data(), out_ptr.size(), &bytes)) != DMG_OK ||
+      (st = upload(&g->d_out_idx, out_idx.data(), out_idx.size(), &bytes)) != DMG_OK ||
+      (st = upload(&g->d_in_ptr, in_ptr.data(), in_ptr.size(), &bytes)) != DMG_OK ||
+      (st = upload(&g->d_in_idx, in_idx.data(), in_idx.size(), &bytes)) != DMG_OK ||
+      (st = upload(&g->d_part_off, part.data(), part.size(), &bytes)) != DMG_OK ||
+      (st = upload(&g->d_entry, g->h_entry.data(), g->h_entry.size(), &bytes)) != DMG_OK ||
+      (st = upload(&g->d_entry_bits, ebits.data(), ebits.size(), &bytes)) != DMG_OK) {
+    free_graph(g);
+    return st;
+  }
+  uint64_t nbytes = 0;
+  if (d->name_off) {
+    nbytes = d->name_off[V];
+    std::vector<uint8_t> low(nbytes + 32, 0);   // zero pad so vector loads may overrun
+    const uint8_t* srcb = d->lower_bytes ? d->lower_bytes : d->name_bytes;
+    if (nbytes) memcpy(low.data(), srcb, nbytes);
+    if (!d->lower_bytes)
+      for (uint64_t i = 0; i < nbytes; ++i)
+        if (low[i] >= 'A' && low[i] <= 'Z') low[i] += 32;   // ASCII fold only
+    if ((st = upload(&g->d_name_off, d->name_off, (size_t)V + 1, &bytes)) != DMG_OK ||
+        (st = upload(&g->d_lower, low.data(), low.size(), &bytes)) != DMG_OK) {
+      free_graph(g);
+      return st;
+    }
+  }
+  g->info.n_vertices = V;
+  g->info.n_entry = (uint32_t)g->h_entry.size();
+  g->info.n_parts = (uint32_t)part.size() - 1;
+  g->info.max_part_vertices = max_part;
+  g->info.n_edges = out_idx.size();
+  g->info.dropped_edges = dropped;
+  g->info.duplicate_edges = dups;
+  g->info.name_bytes = nbytes;
+  g->info.device_bytes = bytes;
+  *out = g;
+  return DMG_OK;
+}
+
+void dmg_graph_retain(dmg_graph* g) {
+  if (g) g->refs.fetch_add(1);
+}
+void dmg_graph_release(dmg_graph* g) {
+  if (g && g->refs.fetch_sub(1) == 1) free_graph(g);
+}
+int32_t dmg_graph_info_get(const dmg_graph* g, dmg_graph_info* out) {
+  if (!g || !out) {
+    set_error("dmg_graph_info_get: NULL argument");
+    return DMG_EINVAL;
+  }
+  *out = g->info;
+  return DMG_OK;
+}
+
+// ---- stats / profiling ------------------------------------------------------------------------
+int32_t dmg_last_call_stats(dmg_engine* e, dmg_call_stats* out) {
+  if (!e || !out) return DMG_EINVAL;
+  *out = g_last_stats;
+  return DMG_OK;
+}
+int32_t dmg_profile_enable(dmg_engine* e, int32_t on) {
+  if (!e) return DMG_EINVAL;
+  e->profile.store(on ? 1 : 0);
+  return DMG_OK;
+}
+int32_t dmg_profile_reset(dmg_engine* e) {
+  if (!e) return DMG_EINVAL;
+  std::lock_guard<std::mutex> lk(e->prof_mu);
+  for (int i = 0; i < K_COUNT; ++i) {
+    e->prof_launches[i] = 0;
+    e->prof_ms[i] = 0;
+  }
+  return DMG_OK;
+}
+int32_t dmg_profile_count(dmg_engine*) { return K_COUNT; }
+int32_t dmg_profile_get(dmg_engine* e, int32_t i, const char** name, uint64_t* launches, double* ms) {
+  if (!e || i < 0 || i >= K_COUNT) return DMG_EINVAL;
+  std::lock_guard<std::mutex> lk(e->prof_mu);
+  if (name) *name = kKernelNames[i];
+  if (launches) *launches = e->prof_launches[i];
+  if (ms) *ms = e->prof_ms[i];
+  return DMG_OK;
+}
+
+// ---- memory helpers ---------------------------------------------------------------------------
+int32_t dmg_device_alloc(dmg_engine* e, uint64_t bytes, void** p) {
+  if (!e || !p) return DMG_EINVAL;
+  DMG_CUDA(cudaSetDevice(e->device));
+  DMG_CUDA(cudaMalloc(p, std::max<uint64_t>(bytes, 16)));
+  return DMG_OK;
+}
+int32_t dmg_device_free(dmg_engine* e, void* p) {
+  if (!e) return DMG_EINVAL;
+  DMG_CUDA(cudaSetDevice(e->device));
+  DMG_CUDA(cudaFree(p));
+  return DMG_OK;
+}
+int32_t dmg_copy_to_device(dmg_engine* e, void* d, const void* s, uint64_t bytes) {
+  if (!e) return DMG_EINVAL;
+  DMG_CUDA(cudaSetDevice(e->device));
+  DMG_CUDA(cudaMemcpy(d, s, bytes, cudaMemcpyHostToDevice));
+  return DMG_OK;
+}
+int32_t dmg_copy_to_host(dmg_engine* e, void* d, const void* s, uint64_t bytes) {
+  if (!e) return DMG_EINVAL;
+  DMG_CUDA(cudaSetDevice(e->device));
+  DMG_CUDA(cudaMemcpy(d, s, bytes, cudaMemcpyDeviceToHost));
+  return DMG_OK;
+}
+int32_t dmg_pinned_alloc(dmg_engine* e, uint64_t bytes, void** p) {
+  if (!e || !p) return DMG_EINVAL;
+  DMG_CUDA(cudaSetDevice(e->device));
+  DMG_CUDA(cudaMallocHost(p, std::max<uint64_t>(bytes, 16)));
+  return DMG_OK;
+}
+int32_t dmg_pinned_free(dmg_engine* e, void* p) {
+  if (!e) return DMG_EINVAL;
+  DMG_CUDA(cudaFreeHost(p));
+  return DMG_OK;
+}
+int32_t dmg_flush_l2(dmg_engine* e) {
+  if (!e) return DMG_EINVAL;
+  DMG_CUDA(cudaSetDevice(e->device));
+  if (!e->flush_buf) {
+    e->flush_bytes = std::max<size_t>(2 * e->l2_bytes, 256u << 20);
+    DMG_CUDA(cudaMalloc(&e->flush_buf, e->flush_bytes));
+  }
+  static std::atomic<uint32_t> salt{1};
+  flush_kernel<<<e->sm_count * 8, 256>>>((uint4*)e->flush_buf, e->flush_bytes / 16, salt.fetch_add(1));
+  DMG_CUDA(cudaGetLastError());
+  DMG_CUDA(cudaDeviceSynchronize());
+  return DMG_OK;
+}
+
+}  // extern "C"

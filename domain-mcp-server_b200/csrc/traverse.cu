@@ -1,0 +1,815 @@
+// Traversal kernels: adjacency rows (T0/T1), batched multi-source k-hop neighbour resolution
+// (T2/T3/T4 of SURVEY.md 8a).  Integer-only, HBM/L2-bound work: no tensor cores.
+//
+// Layout in HBM: forward CSR (out_ptr/out_idx, rows in addDependency order), reverse CSR
+// (in_ptr/in_idx, rows in ascending source id), project range table part_off.  Queries and
+// results are CSR-shaped (q_off/q_src -> out_off/out_ids/out_hop).
+//
+// Every kernel hands out work items through one atomic ticket and places its output with the
+// decoupled look-back allocator of common.cuh, so results come out packed, in query order and
+// in ONE pass over the graph data.
+#include <algorithm>
+
+#include "common.cuh"
+
+namespace dmg {
+
+struct KhopArgs {
+  const uint32_t* out_ptr;
+  const uint32_t* out_idx;
+  const uint32_t* in_ptr;
+  const uint32_t* in_idx;
+  const uint32_t* part_off;
+  uint32_t V, n_parts;
+  int mode, k, exclude;
+  unsigned long long nq;
+  const uint32_t* q_off;
+  const uint32_t* q_src;
+  unsigned long long* out_off;
+  uint32_t* out_ids;
+  uint8_t* out_hop;
+  unsigned long long cap;
+  uint64_t* status;
+  DevCounters* ctr;
+  uint32_t win_cap;   // largest project, rounded up to a multiple of 128 vertices
+};
+
+__device__ __forceinline__ void find_window(const KhopArgs& a, uint32_t qb, uint32_t qe, uint32_t* lo, uint32_t* hi) {
+  // The query's graph is the project of its first valid source (CCS:1426-1434, 1558).
+  *lo = 0;
+  *hi = 0;
+  for (uint32_t i = qb; i < qe; ++i) {
+    const uint32_t s = a.q_src[i];
+    if (s < a.V) {
+      uint32_t l = 0, r = a.n_parts;
+      while (r - l > 1) {
+        const uint32_t m = (l + r) >> 1;
+        if (a.part_off[m] <= s) l = m; else r = m;
+      }
+      *lo = a.part_off[l];
+      *hi = a.part_off[l + 1];
+      return;
+    }
+  }
+}
+
+template <int THREADS>
+__device__ __forceinline__ uint32_t block_excl_scan(uint32_t v, uint32_t* s_wsum, uint32_t* total) {
+  // exclusive scan over the block; s_wsum has THREADS/32 + 1 words; all threads must call
+  constexpr int NW = THREADS / 32;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const uint32_t inc = warp_incl_scan_u32(v);
+  if (lane == 31) s_wsum[warp] = inc;
+  __syncthreads();
+  if (warp == 0) {
+    uint32_t w = lane < NW ? s_wsum[lane] : 0;
+    const uint32_t wi = warp_incl_scan_u32(w);
+    if (lane < NW) s_wsum[lane] = wi - w;
+    if (lane == NW - 1) s_wsum[NW] = wi;
+  }
+  __syncthreads();
+  const uint32_t r = s_wsum[warp] + inc - v;
+  *total = s_wsum[NW];
+  __syncthreads();
+  return r;
+}
+
+// ---------------------------------------------------------------------------------------------
+// khop_small: one CTA per query, everything about the query lives in shared memory.
+// Used when every project has <= 8192 vertices (BASELINE config 2: 2000-vertex projects).
+//   hop8[win]   u8   0 = unseen, 255 = excluded source, else hop
+//   seen[win/32] u32 claim bitmap (atomicOr decides who enqueues a vertex)
+//   queue[2*win] u16 frontier queue, vertex ids relative to the project base; each level is the
+//                    segment the previous level appended (ballot/popc warp-aggregated append);
+//                    reused as the staging area of the ordered result
+// ---------------------------------------------------------------------------------------------
+template <int THREADS>
+__global__ void __launch_bounds__(THREADS) khop_small_kernel(const KhopArgs a) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  uint8_t* hop8 = smem;
+  uint32_t* seen = reinterpret_cast<uint32_t*>(smem + a.win_cap);
+  uint16_t* queue = reinterpret_cast<uint16_t*>(smem + a.win_cap + a.win_cap / 8);
+  __shared__ unsigned long long s_q, s_base;
+  __shared__ uint32_t s_lo, s_hi, s_tail;
+  __shared__ uint32_t s_wsum[THREADS / 32 + 1];
+  constexpr int NW = THREADS / 32;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  unsigned long long te = 0, rows = 0;
+
+  while (true) {
+    if (tid == 0) s_q = atomicAdd(&a.ctr->ticket, 1ull);
+    __syncthreads();
+    const unsigned long long q = s_q;
+    if (q >= a.nq) break;
+    const uint32_t qb = a.q_off[q], qe = a.q_off[q + 1];
+    if (tid == 0) {
+      uint32_t lo, hi;
+      find_window(a, qb, qe, &lo, &hi);
+      s_lo = lo;
+      s_hi = hi;
+      s_tail = 0;
+    }
+    __syncthreads();
+    const uint32_t lo = s_lo, hi = s_hi, wn = hi - lo;
+    const uint32_t nw4 = (wn + 3) >> 2;
+    for (uint32_t i = tid; i < nw4; i += THREADS) reinterpret_cast<uint32_t*>(hop8)[i] = 0;
+    for (uint32_t i = tid; i < ((wn + 31) >> 5); i += THREADS) seen[i] = 0;
+    __syncthreads();
+    // L0: distinct sources inside the project
+    for (uint32_t i = qb + tid; i < qe; i += THREADS) {
+      const uint32_t s = a.q_src[i];
+      if (s >= lo && s < hi) {
+        const uint32_t v = s - lo, bit = 1u << (v & 31);
+        if (!(atomicOr(&seen[v >> 5], bit) & bit)) {
+          queue[atomicAdd(&s_tail, 1u)] = (uint16_t)v;
+          if (a.exclude) hop8[v] = 255;
+        }
+      }
+    }
+    __syncthreads();
+    uint32_t head = 0, tail = s_tail;
+    __syncthreads();    // nobody appends before everybody has read s_tail
+    if (!a.exclude) {   // sources may be re-reached and reported: forget that they were seen
+      for (uint32_t i = tid; i < tail; i += THREADS) {
+        const uint32_t v = queue[i];
+        atomicAnd(&seen[v >> 5], ~(1u << (v & 31)));
+      }
+      __syncthreads();
+    }
+    for (int lvl = 1; lvl <= a.k && head < tail; ++lvl) {
+      const bool last = (lvl == a.k);
+      for (uint32_t i = head + warp; i < tail; i += NW) {
+        const uint32_t u = lo + queue[i];
+        uint32_t b0 = 0, n0 = 0, b1 = 0, n1 = 0;
+        if (a.mode != DMG_IN) {
+          b0 = a.out_ptr[u];
+          n0 = a.out_ptr[u + 1] - b0;
+        }
+        if (a.mode != DMG_OUT) {
+          b1 = a.in_ptr[u];
+          n1 = a.in_ptr[u + 1] - b1;
+        }
+        const uint32_t n = n0 + n1;
+        if (lane == 0) {
+          te += n;
+          ++rows;
+        }
+        for (uint32_t base = 0; base < n; base += 32) {
+          const uint32_t j = base + lane;
+          bool isnew = false;
+          uint32_t v = 0;
+          if (j < n) {
+            v = (j < n0 ? a.out_idx[b0 + j] : a.in_idx[b1 + (j - n0)]) - lo;
+            if (hop8[v] == 0) {
+              if (last) {
+                hop8[v] = (uint8_t)lvl;   // same value from every racer
+              } else {
+                const uint32_t bit = 1u << (v & 31);
+                if (!(atomicOr(&seen[v >> 5], bit) & bit)) {
+                  hop8[v] = (uint8_t)lvl;
+                  isnew = true;
+                }
+              }
+            }
+          }
+          if (!last) {
+            const unsigned m = __ballot_sync(FULL, isnew);
+            if (m) {
+              uint32_t pos = 0;
+              if (lane == 0) pos = atomicAdd(&s_tail, (uint32_t)__popc(m));
+              pos = __shfl_sync(FULL, pos, 0);
+              if (isnew) queue[pos + __popc(m & lanemask_lt())] = (uint16_t)v;
+            }
+          }
+        }
+      }
+      __syncthreads();
+      head = tail;
+      tail = s_tail;
+      __syncthreads();
+    }
+    // ordered result: scan hop8 in id order, compact into the staging area
+    uint16_t* st_id = queue;
+    uint8_t* st_hop = reinterpret_cast<uint8_t*>(queue + a.win_cap);
+    const uint32_t per = (nw4 + THREADS - 1) / THREADS;
+    const uint32_t w0 = min(nw4, tid * per), w1 = min(nw4, w0 + per);
+    uint32_t cnt = 0;
+    for (uint32_t w = w0; w < w1; ++w) {
+      const uint32_t x = reinterpret_cast<const uint32_t*>(hop8)[w];
+#pragma unroll
+      for (int b = 0; b < 4; ++b) {
+        const uint32_t h = (x >> (8 * b)) & 255u;
+        cnt += (h != 0 && h != 255);
+      }
+    }
+    uint32_t total;
+    uint32_t off = block_excl_scan<THREADS>(cnt, s_wsum, &total);
+    for (uint32_t w = w0; w < w1; ++w) {
+      const uint32_t x = reinterpret_cast<const uint32_t*>(hop8)[w];
+#pragma unroll
+      for (int b = 0; b < 4; ++b) {
+        const uint32_t h = (x >> (8 * b)) & 255u;
+        if (h != 0 && h != 255) {
+          st_id[off] = (uint16_t)(w * 4 + b);
+          st_hop[off] = (uint8_t)h;
+          ++off;
+        }
+      }
+    }
+    if (warp == 0) {
+      const unsigned long long excl = lookback_exclusive(a.status, q, total);
+      if (lane == 0) {
+        s_base = excl;
+        a.out_off[q] = excl;
+        if (q == a.nq - 1) {
+          a.out_off[a.nq] = excl + total;
+          a.ctr->total = excl + total;
+        }
+      }
+    }
+    __syncthreads();
+    const unsigned long long base = s_base;
+    for (uint32_t i = tid; i < total; i += THREADS) {
+      const unsigned long long pos = base + i;
+      if (pos < a.cap) {
+        a.out_ids[pos] = lo + st_id[i];
+        a.out_hop[pos] = st_hop[i];
+      }
+    }
+  }
+  te = warp_sum_u64(te);
+  rows = warp_sum_u64(rows);
+  if (lane == 0 && rows) {
+    atomicAdd(&a.ctr->edges, te);
+    atomicAdd(&a.ctr->rows, rows);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// khop_global: one CTA per query for projects too large for shared memory.  Per-CTA scratch in
+// global memory (L2-resident for the common sizes): claim bitmap over the project, a queue that
+// holds sources + every discovered vertex in discovery order (level segments), and a hop byte
+// array used only when the row is too long to sort in shared memory.  The bitmap is reset
+// sparsely (by walking the queue), so the cost of a query follows its result, not V.
+// ---------------------------------------------------------------------------------------------
+constexpr int KG_THREADS = 256;
+constexpr int KG_SORT_CAP = 4096;
+
+__global__ void __launch_bounds__(KG_THREADS) khop_global_kernel(const KhopArgs a, uint32_t* sc_seen, uint8_t* sc_hop,
+                                                                 uint32_t* sc_queue, size_t seen_words,
+                                                                 size_t hop_bytes, size_t qcap) {
+  constexpr int THREADS = KG_THREADS, NW = THREADS / 32;
+  __shared__ unsigned long long s_key[KG_SORT_CAP];
+  __shared__ unsigned long long s_q, s_base;
+  __shared__ uint32_t s_lo, s_hi, s_tail;
+  __shared__ uint32_t s_seg[DMG_MAX_HOPS + 2];
+  __shared__ uint32_t s_wsum[NW + 1];
+  uint32_t* seen = sc_seen + (size_t)blockIdx.x * seen_words;
+  uint8_t* hopg = sc_hop + (size_t)blockIdx.x * hop_bytes;
+  uint32_t* queue = sc_queue + (size_t)blockIdx.x * qcap;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  unsigned long long te = 0, rows = 0;
+
+  while (true) {
+    if (tid == 0) s_q = atomicAdd(&a.ctr->ticket, 1ull);
+    __syncthreads();
+    const unsigned long long q = s_q;
+    if (q >= a.nq) break;
+    const uint32_t qb = a.q_off[q], qe = a.q_off[q + 1];
+    if (tid == 0) {
+      uint32_t lo, hi;
+      find_window(a, qb, qe, &lo, &hi);
+      s_lo = lo;
+      s_hi = hi;
+      s_tail = 0;
+    }
+    __syncthreads();
+    const uint32_t lo = s_lo, hi = s_hi, wn = hi - lo;
+    for (uint32_t i = qb + tid; i < qe; i += THREADS) {
+      const uint32_t s = a.q_src[i];
+      if (s >= lo && s < hi) {
+        const uint32_t v = s - lo, bit = 1u << (v & 31);
+        if (!(atomicOr(&seen[v >> 5], bit) & bit)) queue[atomicAdd(&s_tail, 1u)] = v;
+      }
+    }
+    __syncthreads();
+    const uint32_t ns = s_tail;
+    uint32_t head = 0, tail = ns;
+    __syncthreads();
+    if (!a.exclude) {
+      for (uint32_t i = tid; i < ns; i += THREADS) {
+        const uint32_t v = queue[i];
+        atomicAnd(&seen[v >> 5], ~(1u << (v & 31)));
+      }
+      __threadfence_block();
+      __syncthreads();
+    }
+    if (tid == 0) s_seg[0] = ns;
+    int nlev = 0;
+    for (int lvl = 1; lvl <= a.k && head < tail; ++lvl) {
+      for (uint32_t i = head + warp; i < tail; i += NW) {
+        const uint32_t u = lo + queue[i];
+        uint32_t b0 = 0, n0 = 0, b1 = 0, n1 = 0;
+        if (a.mode != DMG_IN) {
+          b0 = a.out_ptr[u];
+          n0 = a.out_ptr[u + 1] - b0;
+        }
+        if (a.mode != DMG_OUT) {
+          b1 = a.in_ptr[u];
+          n1 = a.in_ptr[u + 1] - b1;
+        }
+        const uint32_t n = n0 + n1;
+        if (lane == 0) {
+          te += n;
+          ++rows;
+        }
+        for (uint32_t base = 0; base < n; base += 32) {
+          const uint32_t j = base + lane;
+          bool isnew = false;
+          uint32_t v = 0;
+          if (j < n) {
+            v = (j < n0 ? a.out_idx[b0 + j] : a.in_idx[b1 + (j - n0)]) - lo;
+            const uint32_t bit = 1u << (v & 31);
+            if (!(__ldcg(&seen[v >> 5]) & bit)) isnew = !(atomicOr(&seen[v >> 5], bit) & bit);
+          }
+          const unsigned m = __ballot_sync(FULL, isnew);
+          if (m) {
+            uint32_t pos = 0;
+            if (lane == 0) pos = atomicAdd(&s_tail, (uint32_t)__popc(m));
+            pos = __shfl_sync(FULL, pos, 0);
+            if (isnew) queue[pos + __popc(m & lanemask_lt())] = v;
+          }
+        }
+      }
+      __syncthreads();
+      head = tail;
+      tail = s_tail;
+      nlev = lvl;
+      if (tid == 0) s_seg[lvl] = tail;   // level lvl is queue[s_seg[lvl-1], s_seg[lvl])
+      __syncthreads();
+    }
+    __syncthreads();
+    const uint32_t total = tail - ns;
+    if (warp == 0) {
+      const unsigned long long excl = lookback_exclusive(a.status, q, total);
+      if (lane == 0) {
+        s_base = excl;
+        a.out_off[q] = excl;
+        if (q == a.nq - 1) {
+          a.out_off[a.nq] = excl + total;
+          a.ctr->total = excl + total;
+        }
+      }
+    }
+    __syncthreads();
+    const unsigned long long base = s_base;
+    if (total && total <= (uint32_t)KG_SORT_CAP) {
+      // short row: (id << 8 | hop) keys, bitonic sort in shared memory
+      uint32_t n2 = 32;
+      while (n2 < total) n2 <<= 1;
+      for (uint32_t i = tid; i < n2; i += THREADS) {
+        unsigned long long key = ~0ull;
+        if (i < total) {
+          const uint32_t p = ns + i;
+          int lv = 1;
+          while (lv < nlev && p >= s_seg[lv]) ++lv;
+          key = ((unsigned long long)queue[p] << 8) | (unsigned)lv;
+        }
+        s_key[i] = key;
+      }
+      __syncthreads();
+      for (uint32_t sz = 2; sz <= n2; sz <<= 1)
+        for (uint32_t st = sz >> 1; st > 0; st >>= 1) {
+          for (uint32_t i = tid; i < n2; i += THREADS) {
+            const uint32_t j = i ^ st;
+            if (j > i) {
+              const unsigned long long x = s_key[i], y = s_key[j];
+              const bool up = ((i & sz) == 0);
+              if ((x > y) == up) {
+                s_key[i] = y;
+                s_key[j] = x;
+              }
+            }
+          }
+          __syncthreads();
+        }
+      for (uint32_t i = tid; i < total; i += THREADS) {
+        const unsigned long long pos = base + i;
+        if (pos < a.cap) {
+          a.out_ids[pos] = lo + (uint32_t)(s_key[i] >> 8);
+          a.out_hop[pos] = (uint8_t)(s_key[i] & 255u);
+        }
+      }
+    } else if (total) {
+      // long row: hop bytes into scratch, then an ordered scan of the claim bitmap
+      for (uint32_t i = tid; i < ns; i += THREADS)
+        if (a.exclude) hopg[queue[i]] = 255;
+      __syncthreads();
+      for (uint32_t i = tid; i < total; i += THREADS) {
+        const uint32_t p = ns + i;
+        int lv = 1;
+        while (lv < nlev && p >= s_seg[lv]) ++lv;
+        hopg[queue[p]] = (uint8_t)lv;
+      }
+      __threadfence_block();
+      __syncthreads();
+      const uint32_t nwords = (wn + 31) >> 5;
+      unsigned long long run = base;
+      for (uint32_t w0 = 0; w0 < nwords; w0 += THREADS) {
+        const uint32_t w = w0 + tid;
+        uint32_t bits = (w < nwords) ? __ldcg(&seen[w]) : 0u;
+        uint32_t keep = 0;
+        for (uint32_t b = bits; b; b &= b - 1) {
+          const uint32_t v = w * 32 + (__ffs(b) - 1);
+          if (__ldcg(&hopg[v]) != 255) keep |= 1u << (v & 31);
+        }
+        uint32_t tot;
+        const uint32_t off = block_excl_scan<THREADS>(__popc(keep), s_wsum, &tot);
+        unsigned long long pos = run + off;
+        for (uint32_t b = keep; b; b &= b - 1) {
+          const uint32_t v = w * 32 + (__ffs(b) - 1);
+          if (pos < a.cap) {
+            a.out_ids[pos] = lo + v;
+            a.out_hop[pos] = __ldcg(&hopg[v]);
+          }
+          ++pos;
+        }
+        run += tot;
+      }
+    }
+    __syncthreads();
+    // sparse reset of the claim bitmap
+    for (uint32_t i = tid; i < tail; i += THREADS) seen[queue[i] >> 5] = 0;
+    __threadfence_block();
+    __syncthreads();
+  }
+  te = warp_sum_u64(te);
+  rows = warp_sum_u64(rows);
+  if (lane == 0 && rows) {
+    atomicAdd(&a.ctr->edges, te);
+    atomicAdd(&a.ctr->rows, rows);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// adjacency_gather: rows of one CSR for a batch of ids (T0 dependencies / T1 dependents).
+// One ticket = a tile of THREADS ids; the tile's rows are sized, placed by look-back, then
+// copied warp-per-row.
+// ---------------------------------------------------------------------------------------------
+constexpr int ADJ_THREADS = 256;
+
+__global__ void __launch_bounds__(ADJ_THREADS) adjacency_kernel(const uint32_t* __restrict__ ptr,
+                                                                const uint32_t* __restrict__ idx, uint32_t V,
+                                                                unsigned long long n, const uint32_t* __restrict__ ids,
+                                                                unsigned long long* out_off, uint32_t* out_ids,
+                                                                unsigned long long cap, uint64_t* status,
+                                                                DevCounters* ctr) {
+  constexpr int THREADS = ADJ_THREADS, NW = THREADS / 32;
+  __shared__ unsigned long long s_t, s_base;
+  __shared__ uint32_t s_start[THREADS], s_len[THREADS], s_off[THREADS];
+  __shared__ uint32_t s_wsum[NW + 1];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const unsigned long long n_tiles = (n + THREADS - 1) / THREADS;
+  unsigned long long te = 0;
+  while (true) {
+    if (tid == 0) s_t = atomicAdd(&ctr->ticket, 1ull);
+    __syncthreads();
+    const unsigned long long t = s_t;
+    if (t >= n_tiles) break;
+    const unsigned long long row = t * THREADS + tid;
+    uint32_t start = 0, len = 0;
+    if (row < n) {
+      const uint32_t id = ids[row];
+      if (id < V) {   // unknown id -> empty row (PG:300-302, 317-319)
+        start = ptr[id];
+        len = ptr[id + 1] - start;
+      }
+    }
+    uint32_t total;
+    const uint32_t off = block_excl_scan<THREADS>(len, s_wsum, &total);
+    s_start[tid] = start;
+    s_len[tid] = len;
+    s_off[tid] = off;
+    if (warp == 0) {
+      const unsigned long long excl = lookback_exclusive(status, t, total);
+      if (lane == 0) {
+        s_base = excl;
+        if (t == n_tiles - 1) {
+          out_off[n] = excl + total;
+          ctr->total = excl + total;
+        }
+      }
+    }
+    __syncthreads();
+    const unsigned long long base = s_base;
+    if (row < n) out_off[row] = base + off;
+    te += len;
+    for (int r = warp; r < THREADS; r += NW) {
+      const uint32_t st = s_start[r], ln = s_len[r];
+      const unsigned long long o = base + s_off[r];
+      for (uint32_t j = lane; j < ln; j += 32)
+        if (o + j < cap) out_ids[o + j] = idx[st + j];
+    }
+  }
+  te = warp_sum_u64(te);
+  if (lane == 0 && te) atomicAdd(&ctr->edges, te);
+}
+
+__global__ void entry_flags_kernel(const uint32_t* __restrict__ bits, uint32_t V, unsigned long long n,
+                                   const uint32_t* __restrict__ ids, uint8_t* out) {
+  const unsigned long long i = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x;
+  if (i < n) {
+    const uint32_t id = ids[i];
+    out[i] = (id < V) ? (uint8_t)((bits[id >> 5] >> (id & 31)) & 1u) : 0;   // PG:336-338
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------------------------
+constexpr uint32_t SMALL_WINDOW_MAX = 8192;
+constexpr int KS_THREADS = 128;
+
+static int32_t reset_counters(CallCtx* c) {
+  DMG_CUDA(cudaMemsetAsync(c->d_counters, 0, sizeof(DevCounters), c->stream));
+  return DMG_OK;
+}
+static int32_t fetch_counters(CallCtx* c) {
+  DMG_CUDA(cudaMemcpyAsync(c->h_counters, c->d_counters, sizeof(DevCounters), cudaMemcpyDeviceToHost, c->stream));
+  return DMG_OK;
+}
+
+// Runs the k-hop batch on device buffers on c->stream; leaves counters in c->h_counters after
+// the caller synchronises.
+static int32_t run_khop(CallCtx* c, dmg_graph* g, int mode, int k, int exclude, uint64_t nq,
+                        const uint32_t* d_q_off, const uint32_t* d_q_src, uint64_t* d_out_off,
+                        uint32_t* d_out_ids, uint8_t* d_out_hop, uint64_t cap) {
+  Engine* e = c->eng;
+  DMG_TRY(c->status.reserve(nq * sizeof(uint64_t)));
+  DMG_CUDA(cudaMemsetAsync(c->status.p, 0, nq * sizeof(uint64_t), c->stream));
+  DMG_TRY(reset_counters(c));
+  KhopArgs a;
+  a.out_ptr = g->d_out_ptr;
+  a.out_idx = g->d_out_idx;
+  a.in_ptr = g->d_in_ptr;
+  a.in_idx = g->d_in_idx;
+  a.part_off = g->d_part_off;
+  a.V = g->info.n_vertices;
+  a.n_parts = g->info.n_parts;
+  a.mode = mode;
+  a.k = k;
+  a.exclude = exclude ? 1 : 0;
+  a.nq = nq;
+  a.q_off = d_q_off;
+  a.q_src = d_q_src;
+  a.out_off = reinterpret_cast<unsigned long long*>(d_out_off);
+  a.out_ids = d_out_ids;
+  a.out_hop = d_out_hop;
+  a.cap = cap;
+  a.status = c->status.as<uint64_t>();
+  a.ctr = c->d_counters;
+  const uint32_t maxp = std::max<uint32_t>(g->info.max_part_vertices, 1);
+  a.win_cap = (maxp + 127u) & ~127u;
+  if (maxp <= SMALL_WINDOW_MAX) {
+    const size_t smem = (size_t)a.win_cap + a.win_cap / 8 + 4 * (size_t)a.win_cap;
+    int occ = 0;
+    DMG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, khop_small_kernel<KS_THREADS>, KS_THREADS, smem));
+    const uint64_t grid = std::min<uint64_t>(nq, (uint64_t)e->sm_count * std::max(occ, 1));
+    LaunchScope ls(c, K_KHOP_SMALL);
+    khop_small_kernel<KS_THREADS><<<(unsigned)grid, KS_THREADS, smem, c->stream>>>(a);
+  } else {
+    const size_t seen_words = (((size_t)maxp + 31) / 32 + 3) & ~size_t(3);
+    const size_t hop_bytes = ((size_t)maxp + 15) & ~size_t(15);
+    const size_t qcap = 2 * (size_t)maxp;
+    const size_t per_block = seen_words * 4 + hop_bytes + qcap * 4;
+    int occ = 0;
+    DMG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, khop_global_kernel, KG_THREADS, 0));
+    uint64_t grid = std::min<uint64_t>(nq, (uint64_t)e->sm_count * std::max(occ, 1));
+    grid = std::max<uint64_t>(1, std::min<uint64_t>(grid, e->scratch_budget / per_block));
+    DMG_TRY(c->scratch.reserve(grid * per_block));
+    uint32_t* sc_seen = c->scratch.as<uint32_t>();
+    uint8_t* sc_hop = reinterpret_cast<uint8_t*>(sc_seen + grid * seen_words);
+    uint32_t* sc_queue = reinterpret_cast<uint32_t*>(sc_hop + grid * hop_bytes);
+    DMG_CUDA(cudaMemsetAsync(sc_seen, 0, grid * seen_words * 4, c->stream));
+    LaunchScope ls(c, K_KHOP_GLOBAL);
+    khop_global_kernel<<<(unsigned)grid, KG_THREADS, 0, c->stream>>>(a, sc_seen, sc_hop, sc_queue, seen_words,
+                                                                     hop_bytes, qcap);
+  }
+  DMG_CUDA(cudaGetLastError());
+  DMG_TRY(fetch_counters(c));
+  return DMG_OK;
+}
+
+static int32_t check_khop_args(dmg_graph* g, int mode, int k, uint64_t nq, const void* q_off, const void* out_off,
+                               uint64_t* needed) {
+  if (!g || !needed || (nq && !q_off) || !out_off) {
+    set_error("dmg_neighbors_batch: NULL argument");
+    return DMG_EINVAL;
+  }
+  if (mode < DMG_OUT || mode > DMG_BOTH) {
+    set_error("dmg_neighbors_batch: mode %d is not DMG_OUT/IN/BOTH", mode);
+    return DMG_EINVAL;
+  }
+  if (k < 1 || k > DMG_MAX_HOPS) {
+    set_error("dmg_neighbors_batch: k=%d outside 1..%d", k, DMG_MAX_HOPS);
+    return DMG_EINVAL;
+  }
+  if (nq >= (1ull << 40)) {
+    set_error("dmg_neighbors_batch: too many queries");
+    return DMG_EINVAL;
+  }
+  return DMG_OK;
+}
+
+}  // namespace dmg
+
+using namespace dmg;
+
+extern "C" {
+
+int32_t dmg_neighbors_batch_dev(dmg_graph* g, int32_t mode, int32_t k, int32_t exclude_sources, uint64_t nq,
+                                const uint32_t* d_q_off, const uint32_t* d_q_src, uint64_t* d_out_off,
+                                uint32_t* d_out_ids, uint8_t* d_out_hop, uint64_t cap, uint64_t* needed) {
+  DMG_TRY(check_khop_args(g, mode, k, nq, d_q_off, d_out_off, needed));
+  CtxGuard cg(g->eng);
+  CallCtx* c = cg.c;
+  if (!c) return DMG_ECUDA;
+  DMG_TRY(c->begin());
+  *needed = 0;
+  if (nq == 0) {
+    DMG_CUDA(cudaMemsetAsync(d_out_off, 0, sizeof(uint64_t), c->stream));
+    return c->finish();
+  }
+  DMG_TRY(run_khop(c, g, mode, k, exclude_sources, nq, d_q_off, d_q_src, d_out_off, d_out_ids, d_out_hop,
+                   (d_out_ids && d_out_hop) ? cap : 0));
+  c->stats.d2h_bytes += sizeof(DevCounters);
+  DMG_TRY(c->finish());
+  *needed = c->h_counters->total;
+  c->stats.edges_traversed = c->h_counters->edges;
+  c->stats.rows_expanded = c->h_counters->rows;
+  c->stats.results = c->h_counters->total;
+  publish_stats(c->stats);
+  if (*needed > cap) {
+    set_error("dmg_neighbors_batch_dev: capacity %llu < needed %llu", (unsigned long long)cap,
+              (unsigned long long)*needed);
+    return DMG_ECAP;
+  }
+  return DMG_OK;
+}
+
+int32_t dmg_neighbors_batch(dmg_graph* g, int32_t mode, int32_t k, int32_t exclude_sources, uint64_t nq,
+                            const uint32_t* q_off, const uint32_t* q_src, uint64_t* out_off, uint32_t* out_ids,
+                            uint8_t* out_hop, uint64_t cap, uint64_t* needed) {
+  DMG_TRY(check_khop_args(g, mode, k, nq, q_off, out_off, needed));
+  *needed = 0;
+  out_off[0] = 0;
+  if (nq == 0) return DMG_OK;
+  const uint64_t n_src = q_off[nq];
+  if (n_src && !q_src) {
+    set_error("dmg_neighbors_batch: q_src is NULL");
+    return DMG_EINVAL;
+  }
+  CtxGuard cg(g->eng);
+  CallCtx* c = cg.c;
+  if (!c) return DMG_ECUDA;
+  DMG_TRY(c->begin());
+  // a row can never exceed its project, so the device buffers are bounded even for a huge cap
+  const uint64_t row_max = g->info.max_part_vertices;
+  uint64_t dev_cap = (!out_ids || !out_hop) ? 0 : cap;
+  if (row_max && nq <= UINT64_MAX / std::max<uint64_t>(row_max, 1)) dev_cap = std::min<uint64_t>(dev_cap, nq * row_max);
+  DMG_TRY(c->q_off.reserve((nq + 1) * 4));
+  DMG_TRY(c->q_src.reserve(n_src * 4));
+  DMG_TRY(c->out_off.reserve((nq + 1) * 8));
+  DMG_TRY(c->out_ids.reserve(dev_cap * 4));
+  DMG_TRY(c->out_hop.reserve(dev_cap));
+  DMG_CUDA(cudaMemcpyAsync(c->q_off.p, q_off, (nq + 1) * 4, cudaMemcpyHostToDevice, c->stream));
+  if (n_src) DMG_CUDA(cudaMemcpyAsync(c->q_src.p, q_src, n_src * 4, cudaMemcpyHostToDevice, c->stream));
+  c->stats.h2d_bytes += (nq + 1) * 4 + n_src * 4;
+  DMG_TRY(run_khop(c, g, mode, k, exclude_sources, nq, c->q_off.as<uint32_t>(), c->q_src.as<uint32_t>(),
+                   c->out_off.as<uint64_t>(), c->out_ids.as<uint32_t>(), c->out_hop.as<uint8_t>(), dev_cap));
+  DMG_CUDA(cudaMemcpyAsync(out_off, c->out_off.p, (nq + 1) * 8, cudaMemcpyDeviceToHost, c->stream));
+  DMG_CUDA(cudaStreamSynchronize(c->stream));
+  const uint64_t total = c->h_counters->total;
+  c->stats.d2h_bytes += (nq + 1) * 8 + sizeof(DevCounters);
+  *needed = total;
+  int32_t rc = DMG_OK;
+  if (total > cap || (total && (!out_ids || !out_hop))) {
+    set_error("dmg_neighbors_batch: capacity %llu < needed %llu", (unsigned long long)cap, (unsigned long long)total);
+    rc = DMG_ECAP;
+  } else if (total) {
+    DMG_CUDA(cudaMemcpyAsync(out_ids, c->out_ids.p, total * 4, cudaMemcpyDeviceToHost, c->stream));
+    DMG_CUDA(cudaMemcpyAsync(out_hop, c->out_hop.p, total, cudaMemcpyDeviceToHost, c->stream));
+    c->stats.d2h_bytes += total * 5;
+  }
+  c->stats.edges_traversed = c->h_counters->edges;
+  c->stats.rows_expanded = c->h_counters->rows;
+  c->stats.results = total;
+  DMG_TRY(c->finish());
+  return rc;
+}
+
+int32_t dmg_adjacency_batch(dmg_graph* g, int32_t dir, uint64_t n, const uint32_t* ids, uint64_t* out_off,
+                            uint32_t* out_ids, uint64_t cap, uint64_t* needed) {
+  if (!g || !out_off || !needed || (n && !ids)) {
+    set_error("dmg_adjacency_batch: NULL argument");
+    return DMG_EINVAL;
+  }
+  if (dir != DMG_OUT && dir != DMG_IN) {
+    set_error("dmg_adjacency_batch: dir %d is not DMG_OUT/DMG_IN", dir);
+    return DMG_EINVAL;
+  }
+  *needed = 0;
+  out_off[0] = 0;
+  if (n == 0) return DMG_OK;
+  CtxGuard cg(g->eng);
+  CallCtx* c = cg.c;
+  if (!c) return DMG_ECUDA;
+  DMG_TRY(c->begin());
+  const uint64_t n_tiles = (n + ADJ_THREADS - 1) / ADJ_THREADS;
+  DMG_TRY(c->q_src.reserve(n * 4));
+  DMG_TRY(c->out_off.reserve((n + 1) * 8));
+  DMG_TRY(c->status.reserve(n_tiles * 8));
+  DMG_CUDA(cudaMemcpyAsync(c->q_src.p, ids, n * 4, cudaMemcpyHostToDevice, c->stream));
+  c->stats.h2d_bytes += n * 4;
+  const uint32_t* ptr = dir == DMG_OUT ? g->d_out_ptr : g->d_in_ptr;
+  const uint32_t* idx = dir == DMG_OUT ? g->d_out_idx : g->d_in_idx;
+  const uint64_t grid = std::min<uint64_t>(n_tiles, (uint64_t)g->eng->sm_count * 8);
+  // One pass when the caller's capacity is a sane device allocation; otherwise a sizing pass
+  // (capacity 0: offsets only) followed by the gather into an exactly sized buffer.
+  const uint64_t cap_eff = out_ids ? cap : 0;
+  const bool one_pass = cap_eff * 4 <= std::max<uint64_t>(256ull << 20, c->out_ids.cap);
+  uint64_t total = 0;
+  for (int pass = one_pass ? 1 : 0; pass < 2; ++pass) {
+    const uint64_t use_cap = pass == 0 ? 0 : (one_pass ? cap_eff : std::min<uint64_t>(cap_eff, total));
+    if (use_cap) DMG_TRY(c->out_ids.reserve(use_cap * 4));
+    DMG_CUDA(cudaMemsetAsync(c->status.p, 0, n_tiles * 8, c->stream));
+    DMG_TRY(reset_counters(c));
+    {
+      LaunchScope ls(c, K_ADJ_GATHER);
+      adjacency_kernel<<<(unsigned)grid, ADJ_THREADS, 0, c->stream>>>(
+          ptr, idx, g->info.n_vertices, n, c->q_src.as<uint32_t>(), c->out_off.as<unsigned long long>(),
+          c->out_ids.as<uint32_t>(), use_cap, c->status.as<uint64_t>(), c->d_counters);
+    }
+    DMG_CUDA(cudaGetLastError());
+    DMG_TRY(fetch_counters(c));
+    DMG_CUDA(cudaStreamSynchronize(c->stream));
+    total = c->h_counters->total;
+    if (pass == 0 && (total > cap_eff || total == 0)) break;
+  }
+  DMG_CUDA(cudaMemcpyAsync(out_off, c->out_off.p, (n + 1) * 8, cudaMemcpyDeviceToHost, c->stream));
+  c->stats.d2h_bytes += (n + 1) * 8 + sizeof(DevCounters);
+  *needed = total;
+  int32_t rc = DMG_OK;
+  if (total > cap || (total && !out_ids)) {
+    set_error("dmg_adjacency_batch: capacity %llu < needed %llu", (unsigned long long)cap, (unsigned long long)total);
+    rc = DMG_ECAP;
+  } else if (total) {
+    DMG_CUDA(cudaMemcpyAsync(out_ids, c->out_ids.p, total * 4, cudaMemcpyDeviceToHost, c->stream));
+    c->stats.d2h_bytes += total * 4;
+  }
+  c->stats.edges_traversed = c->h_counters->edges;
+  c->stats.rows_expanded = n;
+  c->stats.results = total;
+  DMG_TRY(c->finish());
+  return rc;
+}
+
+int32_t dmg_entry_points(dmg_graph* g, uint32_t* out_ids, uint32_t cap, uint32_t* needed) {
+  if (!g || !needed) {
+    set_error("dmg_entry_points: NULL argument");
+    return DMG_EINVAL;
+  }
+  // the ordered entry list is tiny, immutable and kept on both sides; served from the handle
+  *needed = (uint32_t)g->h_entry.size();
+  if (*needed > cap || (*needed && !out_ids)) return DMG_ECAP;
+  if (*needed) memcpy(out_ids, g->h_entry.data(), *needed * sizeof(uint32_t));
+  return DMG_OK;
+}
+
+int32_t dmg_is_entry_point_batch(dmg_graph* g, uint64_t n, const uint32_t* ids, uint8_t* out_flags) {
+  if (!g || (n && (!ids || !out_flags))) {
+    set_error("dmg_is_entry_point_batch: NULL argument");
+    return DMG_EINVAL;
+  }
+  if (!n) return DMG_OK;
+  CtxGuard cg(g->eng);
+  CallCtx* c = cg.c;
+  if (!c) return DMG_ECUDA;
+  DMG_TRY(c->begin());
+  DMG_TRY(c->q_src.reserve(n * 4));
+  DMG_TRY(c->out_hop.reserve(n));
+  DMG_CUDA(cudaMemcpyAsync(c->q_src.p, ids, n * 4, cudaMemcpyHostToDevice, c->stream));
+  {
+    LaunchScope ls(c, K_ENTRY_FLAGS);
+    entry_flags_kernel<<<(unsigned)((n + 255) / 256), 256, 0, c->stream>>>(g->d_entry_bits, g->info.n_vertices, n,
+                                                                          c->q_src.as<uint32_t>(),
+                                                                          c->out_hop.as<uint8_t>());
+  }
+  DMG_CUDA(cudaGetLastError());
+  DMG_CUDA(cudaMemcpyAsync(out_flags, c->out_hop.p, n, cudaMemcpyDeviceToHost, c->stream));
+  c->stats.h2d_bytes += n * 4;
+  c->stats.d2h_bytes += n;
+  return c->finish();
+}
+
+}  // extern "C"

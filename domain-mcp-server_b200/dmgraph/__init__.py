@@ -1,0 +1,329 @@
+"""ctypes binding of libdmgraph.so (include/dmgraph.h) -- the harness-side stand-in for the
+Java shim that INTEGRATION.md describes.  Thin on purpose: every call goes straight to the
+C ABI; nothing here computes a result, and there is no CPU fallback -- if the CUDA library is
+missing or no device is present the calls raise.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(os.path.dirname(_HERE), "libdmgraph.so")
+
+OK, EINVAL, ENOMEM, ECAP, ECUDA, ENCCL, ENODEV = range(7)
+OUT, IN, BOTH = 0, 1, 2
+SEARCH_CONTAINS_ALL, SEARCH_SIMPLE_EQ_FIRST, SEARCH_CONTAINS_FIRST = 0, 1, 2
+LEVEL_UNREACHED = 0xFFFFFFFF
+MODES = {"out": OUT, "in": IN, "both": BOTH}
+
+
+class DmgError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__("dmgraph error %d: %s" % (code, msg))
+        self.code = code
+
+
+class EngineOpts(C.Structure):
+    _fields_ = [("device", C.c_int32), ("flags", C.c_int32), ("scratch_bytes", C.c_uint64)]
+
+
+class GraphDesc(C.Structure):
+    _fields_ = [("n_vertices", C.c_uint32), ("n_entry", C.c_uint32), ("n_parts", C.c_uint32),
+                ("reserved", C.c_uint32), ("n_edges", C.c_uint64),
+                ("name_off", C.c_void_p), ("name_bytes", C.c_void_p), ("lower_bytes", C.c_void_p),
+                ("edge_src", C.c_void_p), ("edge_dst", C.c_void_p), ("entry_ids", C.c_void_p),
+                ("part_off", C.c_void_p)]
+
+
+class GraphInfo(C.Structure):
+    _fields_ = [("n_vertices", C.c_uint32), ("n_entry", C.c_uint32), ("n_parts", C.c_uint32),
+                ("max_part_vertices", C.c_uint32), ("n_edges", C.c_uint64), ("dropped_edges", C.c_uint64),
+                ("duplicate_edges", C.c_uint64), ("name_bytes", C.c_uint64), ("device_bytes", C.c_uint64)]
+
+
+class CallStats(C.Structure):
+    _fields_ = [("kernel_launches", C.c_uint64), ("edges_traversed", C.c_uint64), ("rows_expanded", C.c_uint64),
+                ("results", C.c_uint64), ("h2d_bytes", C.c_uint64), ("d2h_bytes", C.c_uint64),
+                ("device_ms", C.c_float), ("reserved", C.c_float)]
+
+
+_lib = None
+
+
+def lib():
+    """Loads libdmgraph.so; raises if it has not been built (no fallback of any kind)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise ImportError("libdmgraph.so not built: run `make -C domain-mcp-server_b200` "
+                              "(or __graft_entry__.build())")
+        L = C.CDLL(LIB_PATH)
+        vp, u64, u32, i32 = C.c_void_p, C.c_uint64, C.c_uint32, C.c_int32
+        pu64 = C.POINTER(C.c_uint64)
+        sig = {
+            "dmg_device_count": (i32, []),
+            "dmg_engine_create": (i32, [C.POINTER(EngineOpts), C.POINTER(vp)]),
+            "dmg_engine_destroy": (None, [vp]),
+            "dmg_last_error": (C.c_char_p, []),
+            "dmg_version": (C.c_char_p, []),
+            "dmg_graph_create": (i32, [vp, C.POINTER(GraphDesc), C.POINTER(vp)]),
+            "dmg_graph_retain": (None, [vp]),
+            "dmg_graph_release": (None, [vp]),
+            "dmg_graph_info_get": (i32, [vp, C.POINTER(GraphInfo)]),
+            "dmg_adjacency_batch": (i32, [vp, i32, u64, vp, vp, vp, u64, pu64]),
+            "dmg_neighbors_batch": (i32, [vp, i32, i32, i32, u64, vp, vp, vp, vp, vp, u64, pu64]),
+            "dmg_neighbors_batch_dev": (i32, [vp, i32, i32, i32, u64, vp, vp, vp, vp, vp, u64, pu64]),
+            "dmg_closure": (i32, [vp, i32, u32, vp, vp, pu64]),
+            "dmg_analysis_order": (i32, [vp, vp]),
+            "dmg_entry_points": (i32, [vp, vp, u32, C.POINTER(u32)]),
+            "dmg_is_entry_point_batch": (i32, [vp, u64, vp, vp]),
+            "dmg_search_batch": (i32, [vp, i32, u32, u32, u64, vp, vp, vp, vp, u64, pu64]),
+            "dmg_last_call_stats": (i32, [vp, C.POINTER(CallStats)]),
+            "dmg_profile_enable": (i32, [vp, i32]),
+            "dmg_profile_reset": (i32, [vp]),
+            "dmg_profile_count": (i32, [vp]),
+            "dmg_profile_get": (i32, [vp, i32, C.POINTER(C.c_char_p), pu64, C.POINTER(C.c_double)]),
+            "dmg_device_alloc": (i32, [vp, u64, C.POINTER(vp)]),
+            "dmg_device_free": (i32, [vp, vp]),
+            "dmg_copy_to_device": (i32, [vp, vp, vp, u64]),
+            "dmg_copy_to_host": (i32, [vp, vp, vp, u64]),
+            "dmg_pinned_alloc": (i32, [vp, u64, C.POINTER(vp)]),
+            "dmg_pinned_free": (i32, [vp, vp]),
+            "dmg_flush_l2": (i32, [vp]),
+        }
+        for name, (res, args) in sig.items():
+            f = getattr(L, name)
+            f.restype = res
+            f.argtypes = args
+        _lib = L
+    return _lib
+
+
+HEADER_SYMBOLS = None
+
+
+def device_count():
+    return lib().dmg_device_count()
+
+
+def _check(rc, allow=()):
+    if rc != OK and rc not in allow:
+        raise DmgError(rc, lib().dmg_last_error().decode("utf-8", "replace"))
+    return rc
+
+
+def _arr(a, dt):
+    a = np.ascontiguousarray(a, dtype=dt)
+    return a
+
+
+def _ptr(a):
+    return a.ctypes.data if a is not None and a.size else None
+
+
+class Engine:
+    def __init__(self, device=0, scratch_bytes=0):
+        self.L = lib()
+        self.h = C.c_void_p()
+        opts = EngineOpts(device, 0, scratch_bytes)
+        _check(self.L.dmg_engine_create(C.byref(opts), C.byref(self.h)))
+        self.device = device
+
+    def close(self):
+        if self.h:
+            self.L.dmg_engine_destroy(self.h)
+            self.h = C.c_void_p()
+
+    def last_stats(self):
+        s = CallStats()
+        _check(self.L.dmg_last_call_stats(self.h, C.byref(s)))
+        return {f: getattr(s, f) for f, _ in CallStats._fields_ if f != "reserved"}
+
+    def profile(self, on=True):
+        _check(self.L.dmg_profile_enable(self.h, int(on)))
+
+    def profile_reset(self):
+        _check(self.L.dmg_profile_reset(self.h))
+
+    def profile_table(self):
+        out = {}
+        for i in range(self.L.dmg_profile_count(self.h)):
+            name, n, ms = C.c_char_p(), C.c_uint64(), C.c_double()
+            _check(self.L.dmg_profile_get(self.h, i, C.byref(name), C.byref(n), C.byref(ms)))
+            if n.value:
+                out[name.value.decode()] = (n.value, ms.value)
+        return out
+
+    def flush_l2(self):
+        _check(self.L.dmg_flush_l2(self.h))
+
+    # -- device / pinned buffers ---------------------------------------------------------------
+    def device_alloc(self, nbytes):
+        p = C.c_void_p()
+        _check(self.L.dmg_device_alloc(self.h, int(nbytes), C.byref(p)))
+        return p.value
+
+    def device_free(self, p):
+        _check(self.L.dmg_device_free(self.h, C.c_void_p(p)))
+
+    def to_device(self, arr):
+        arr = np.ascontiguousarray(arr)
+        p = self.device_alloc(max(arr.nbytes, 16))
+        if arr.nbytes:
+            _check(self.L.dmg_copy_to_device(self.h, C.c_void_p(p), arr.ctypes.data, arr.nbytes))
+        return p
+
+    def to_host(self, p, dtype, count):
+        out = np.empty(count, dtype=dtype)
+        if out.nbytes:
+            _check(self.L.dmg_copy_to_host(self.h, out.ctypes.data, C.c_void_p(p), out.nbytes))
+        return out
+
+    def pinned(self, dtype, count):
+        """numpy array over page-locked host memory (kept alive by the engine until freed)."""
+        p = C.c_void_p()
+        nbytes = max(1, int(count)) * np.dtype(dtype).itemsize
+        _check(self.L.dmg_pinned_alloc(self.h, nbytes, C.byref(p)))
+        buf = (C.c_uint8 * nbytes).from_address(p.value)
+        a = np.frombuffer(buf, dtype=dtype, count=int(count))
+        return a, p.value
+
+    def pinned_free(self, p):
+        _check(self.L.dmg_pinned_free(self.h, C.c_void_p(p)))
+
+
+class Graph:
+    """One immutable device graph (dmg_graph handle)."""
+
+    def __init__(self, engine, n_vertices, src, dst, entry=(), part_off=None, name_off=None, name_bytes=None,
+                 lower_bytes=None):
+        self.eng = engine
+        self.L = engine.L
+        src, dst = _arr(src, np.uint32), _arr(dst, np.uint32)
+        entry = _arr(entry, np.uint32)
+        keep = [src, dst, entry]
+        d = GraphDesc()
+        d.n_vertices = int(n_vertices)
+        d.n_edges = int(src.size)
+        d.edge_src, d.edge_dst = _ptr(src), _ptr(dst)
+        d.n_entry = int(entry.size)
+        d.entry_ids = _ptr(entry)
+        if part_off is not None:
+            po = _arr(part_off, np.uint32)
+            keep.append(po)
+            d.n_parts = int(po.size - 1)
+            d.part_off = _ptr(po)
+        if name_off is not None:
+            no = _arr(name_off, np.uint64)
+            nb = _arr(name_bytes, np.uint8)
+            keep += [no, nb]
+            d.name_off = no.ctypes.data
+            d.name_bytes = nb.ctypes.data if nb.size else None
+            if lower_bytes is not None:
+                lb = _arr(lower_bytes, np.uint8)
+                keep.append(lb)
+                d.lower_bytes = lb.ctypes.data if lb.size else None
+        self.h = C.c_void_p()
+        _check(self.L.dmg_graph_create(engine.h, C.byref(d), C.byref(self.h)))
+        info = GraphInfo()
+        _check(self.L.dmg_graph_info_get(self.h, C.byref(info)))
+        self.info = {f: getattr(info, f) for f, _ in GraphInfo._fields_}
+        self.V = self.info["n_vertices"]
+
+    def release(self):
+        if self.h:
+            self.L.dmg_graph_release(self.h)
+            self.h = C.c_void_p()
+
+    # -- T0/T1 ---------------------------------------------------------------------------------
+    def adjacency_batch(self, direction, ids, cap=None):
+        ids = _arr(ids, np.uint32)
+        n = ids.size
+        off = np.zeros(n + 1, np.uint64)
+        need = C.c_uint64(0)
+        if cap is None:
+            rc = self.L.dmg_adjacency_batch(self.h, direction, n, _ptr(ids), off.ctypes.data, None, 0, C.byref(need))
+            _check(rc, allow=(ECAP,))
+            cap = need.value
+        out = np.zeros(max(1, cap), np.uint32)
+        _check(self.L.dmg_adjacency_batch(self.h, direction, n, _ptr(ids), off.ctypes.data, out.ctypes.data, cap,
+                                          C.byref(need)))
+        return off, out[:need.value]
+
+    # -- T2/T3/T4 ------------------------------------------------------------------------------
+    def neighbors_batch(self, mode, k, exclude_sources, q_off, q_src, cap=None, out=None):
+        q_off, q_src = _arr(q_off, np.uint32), _arr(q_src, np.uint32)
+        nq = q_off.size - 1
+        need = C.c_uint64(0)
+        if out is not None:
+            off, ids, hop = out
+            cap = ids.size
+        else:
+            off = np.zeros(nq + 1, np.uint64)
+            if cap is None:
+                rc = self.L.dmg_neighbors_batch(self.h, mode, k, int(exclude_sources), nq, _ptr(q_off), _ptr(q_src),
+                                                off.ctypes.data, None, None, 0, C.byref(need))
+                _check(rc, allow=(ECAP,))
+                cap = need.value
+            ids = np.zeros(max(1, cap), np.uint32)
+            hop = np.zeros(max(1, cap), np.uint8)
+        _check(self.L.dmg_neighbors_batch(self.h, mode, k, int(exclude_sources), nq, _ptr(q_off), _ptr(q_src),
+                                          off.ctypes.data, ids.ctypes.data, hop.ctypes.data, cap, C.byref(need)))
+        return off, ids[:need.value], hop[:need.value]
+
+    def neighbors_batch_dev(self, mode, k, exclude_sources, nq, d_q_off, d_q_src, d_out_off, d_out_ids, d_out_hop,
+                            cap):
+        need = C.c_uint64(0)
+        rc = self.L.dmg_neighbors_batch_dev(self.h, mode, k, int(exclude_sources), nq, C.c_void_p(d_q_off),
+                                            C.c_void_p(d_q_src), C.c_void_p(d_out_off), C.c_void_p(d_out_ids),
+                                            C.c_void_p(d_out_hop), cap, C.byref(need))
+        _check(rc, allow=(ECAP,))
+        return rc, need.value
+
+    # -- T5 ------------------------------------------------------------------------------------
+    def closure(self, direction, sources):
+        s = _arr(sources, np.uint32)
+        level = np.zeros(max(1, self.V), np.uint32)
+        reached = C.c_uint64(0)
+        _check(self.L.dmg_closure(self.h, direction, s.size, _ptr(s), level.ctypes.data, C.byref(reached)))
+        return level[:self.V], reached.value
+
+    def analysis_order(self):
+        order = np.zeros(max(1, self.V), np.uint32)
+        _check(self.L.dmg_analysis_order(self.h, order.ctypes.data))
+        return order[:self.V]
+
+    def entry_points(self):
+        need = C.c_uint32(0)
+        out = np.zeros(max(1, self.info["n_entry"]), np.uint32)
+        _check(self.L.dmg_entry_points(self.h, out.ctypes.data, out.size, C.byref(need)))
+        return out[:need.value]
+
+    def is_entry_point_batch(self, ids):
+        ids = _arr(ids, np.uint32)
+        out = np.zeros(max(1, ids.size), np.uint8)
+        _check(self.L.dmg_is_entry_point_batch(self.h, ids.size, _ptr(ids), out.ctypes.data))
+        return out[:ids.size]
+
+    # -- S1/S2 ---------------------------------------------------------------------------------
+    def search_batch(self, kind, queries, v_lo=0, v_hi=None, cap=None):
+        """queries: list of bytes, already lower-cased by the host."""
+        nq = len(queries)
+        q_off = np.zeros(nq + 1, np.uint32)
+        if nq:
+            np.cumsum([len(q) for q in queries], out=q_off[1:])
+        qb = np.frombuffer(b"".join(queries) + b"\0", dtype=np.uint8).copy()
+        if v_hi is None:
+            v_hi = self.V
+        off = np.zeros(nq + 1, np.uint64)
+        need = C.c_uint64(0)
+        if cap is None:
+            rc = self.L.dmg_search_batch(self.h, kind, v_lo, v_hi, nq, q_off.ctypes.data, qb.ctypes.data,
+                                         off.ctypes.data, None, 0, C.byref(need))
+            _check(rc, allow=(ECAP,))
+            cap = need.value
+        ids = np.zeros(max(1, cap), np.uint32)
+        _check(self.L.dmg_search_batch(self.h, kind, v_lo, v_hi, nq, q_off.ctypes.data, qb.ctypes.data,
+                                       off.ctypes.data, ids.ctypes.data, cap, C.byref(need)))
+        return off, ids[:need.value]

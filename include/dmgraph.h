@@ -1,0 +1,218 @@
+/*
+ * dmgraph.h -- C ABI of libdmgraph.so, the B200-resident graph + name-search engine that
+ * stands in for the hot path of waabox/domain-mcp-server.
+ *
+ * The reference has no native seam today: its de-facto interface is the read
+ * API of ProjectGraph as consumed by CodeContextService and GraphQueryService, plus the
+ * GraphService lifecycle.  Each entry point below names the reference code it replaces
+ * (paths relative to src/main/java/co/fanki/domainmcp/ in the reference):
+ *
+ *   PG  = analysis/domain/ProjectGraph.java
+ *   GS  = analysis/domain/GraphService.java
+ *   CCS = analysis/application/CodeContextService.java
+ *   GQS = analysis/application/GraphQueryService.java
+ *
+ * Conventions
+ *   - Vertex id (uint32) = position of the identifier in the `nodes` sequence the host
+ *     supplies (PG:118 LinkedHashMap order).  The host keeps String<->id.
+ *   - Every buffer is caller-owned.  Inputs are read-only during the call.  Outputs are
+ *     caller-allocated with a capacity; if the result does not fit the call returns
+ *     DMG_ECAP, fills out_off[] and *needed, and writes no row data.
+ *   - An unknown / out-of-range vertex id in a query yields an empty row, never an error
+ *     (PG:300-302, 317-319, 360-362).
+ *   - All query entry points may be called concurrently from any number of host threads on
+ *     one graph handle (the reference's readers are lock-free, GS:34-38).
+ *   - The library never writes to stdout or stderr (MCP stdio transport) and never aborts.
+ *   - There is no CPU fallback: without a CUDA device every entry point that needs one
+ *     fails with DMG_ENODEV / DMG_ECUDA.
+ *   - Pointers named d_* are DEVICE pointers (from dmg_device_alloc); all others are host.
+ */
+#ifndef DMGRAPH_H
+#define DMGRAPH_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DMG_OK 0
+#define DMG_EINVAL 1 /* IllegalArgumentException analogue (shared/Preconditions.java:41-47) */
+#define DMG_ENOMEM 2
+#define DMG_ECAP 3   /* output capacity too small; *needed says how much */
+#define DMG_ECUDA 4
+#define DMG_ENCCL 5
+#define DMG_ENODEV 6
+
+/* traversal direction / mode */
+#define DMG_OUT 0  /* dependencies  (PG:299-305) */
+#define DMG_IN 1   /* dependents    (PG:316-328) */
+#define DMG_BOTH 2 /* resolve       (PG:359-378) */
+
+/* search kinds */
+#define DMG_SEARCH_CONTAINS_ALL 0   /* CCS:1511-1526 search_project: every hit, nodes order */
+#define DMG_SEARCH_SIMPLE_EQ_FIRST 1 /* GQS:434-446 first id whose simple name equals query */
+#define DMG_SEARCH_CONTAINS_FIRST 2 /* GQS:449-453 first id containing the query */
+
+#define DMG_MAX_HOPS 254
+#define DMG_LEVEL_UNREACHED 0xFFFFFFFFu
+
+typedef struct dmg_engine dmg_engine;
+typedef struct dmg_graph dmg_graph;
+
+typedef struct dmg_engine_opts {
+  int32_t device;         /* CUDA ordinal this engine runs on */
+  int32_t flags;          /* reserved, 0 */
+  uint64_t scratch_bytes; /* per-call traversal scratch budget; 0 = default (4 GiB) */
+} dmg_engine_opts;
+
+/* Host-side description of one immutable graph (all projects of a GraphService, or one).
+ * Replaces: new ProjectGraph() + addNode/addDependency/markAsEntryPoint (PG:160-197) followed
+ * by GraphService.put (GS:118-122).  Build rules reproduced at upload:
+ *   - an edge is kept only if both endpoints are < n_vertices (PG:179-181), else dropped
+ *     and counted; duplicates collapse, the first occurrence fixes the position (PG:182);
+ *     self-loops are legal;
+ *   - entry ids: insertion order kept, duplicates and unknown ids ignored (PG:194-196);
+ *   - parts: vertex ranges [part_off[p], part_off[p+1]) of the projects held in this graph
+ *     (GraphService keeps one ProjectGraph per project, GS:34-38).  No edge may cross a
+ *     range (DMG_EINVAL).  n_parts == 0 means one project.  A traversal query runs inside
+ *     the project of its first valid source; sources in other projects match nothing
+ *     (CCS:1426-1434, 1558).
+ *   - names are optional (NULL name_off) for graphs that are only traversed.  lower_bytes is
+ *     the host's own toLowerCase() of name_bytes with the SAME offsets (CCS:1513); if NULL
+ *     the engine folds ASCII A-Z only.
+ */
+typedef struct dmg_graph_desc {
+  uint32_t n_vertices;
+  uint32_t n_entry;
+  uint32_t n_parts;
+  uint32_t reserved;
+  uint64_t n_edges;
+  const uint64_t* name_off;   /* [n_vertices+1] byte offsets into name_bytes, or NULL */
+  const uint8_t* name_bytes;  /* UTF-8 */
+  const uint8_t* lower_bytes; /* pre-lowered copy or NULL */
+  const uint32_t* edge_src;   /* [n_edges], addDependency order */
+  const uint32_t* edge_dst;
+  const uint32_t* entry_ids;  /* [n_entry], markAsEntryPoint order */
+  const uint32_t* part_off;   /* [n_parts+1] or NULL */
+} dmg_graph_desc;
+
+typedef struct dmg_graph_info {
+  uint32_t n_vertices;
+  uint32_t n_entry;
+  uint32_t n_parts;
+  uint32_t max_part_vertices;
+  uint64_t n_edges;         /* kept */
+  uint64_t dropped_edges;   /* unknown endpoint */
+  uint64_t duplicate_edges; /* collapsed */
+  uint64_t name_bytes;
+  uint64_t device_bytes;
+} dmg_graph_info;
+
+/* Counters of the calling thread's most recent query call on this engine. */
+typedef struct dmg_call_stats {
+  uint64_t kernel_launches;  /* our kernels launched by the call */
+  uint64_t edges_traversed;  /* adjacency entries read (TE of SURVEY.md 8d) */
+  uint64_t rows_expanded;    /* vertices whose rows were read */
+  uint64_t results;          /* entries written */
+  uint64_t h2d_bytes;
+  uint64_t d2h_bytes;
+  float device_ms;           /* CUDA-event time of the device work on the call's stream */
+  float reserved;
+} dmg_call_stats;
+
+/* ---- engine (GS lifecycle: the process-wide cache, GS:34-76) ------------------------------- */
+int32_t dmg_device_count(void);
+int32_t dmg_engine_create(const dmg_engine_opts* opts, dmg_engine** out);
+void dmg_engine_destroy(dmg_engine* e);
+/* Thread-local, never NULL; valid until the thread's next failing call. */
+const char* dmg_last_error(void);
+const char* dmg_version(void);
+
+/* ---- graph handles (GS:84, 93-122: put / reload swap whole graphs) ------------------------- */
+int32_t dmg_graph_create(dmg_engine* e, const dmg_graph_desc* desc, dmg_graph** out);
+void dmg_graph_retain(dmg_graph* g);
+void dmg_graph_release(dmg_graph* g); /* frees device memory when the count reaches 0 */
+int32_t dmg_graph_info_get(const dmg_graph* g, dmg_graph_info* out);
+
+/* ---- T0 / T1: adjacency rows ---------------------------------------------------------------
+ * dependencies(id) (PG:299-305): dir = DMG_OUT, row order = addDependency order.
+ * dependents(id)   (PG:316-328): dir = DMG_IN, row order = ascending source id (the
+ *   reference's order here is HashMap bucket order, pinned by no test).
+ * Also serves vertexDeps (GQS:298-322), vertexOverview (GQS:243-265) and the all-vertex dump
+ * of executeClasses (GQS:111-150) with ids = 0..V-1.
+ * out_off has n+1 entries; row i is out_ids[out_off[i] .. out_off[i+1]).                       */
+int32_t dmg_adjacency_batch(dmg_graph* g, int32_t dir, uint64_t n, const uint32_t* ids,
+                            uint64_t* out_off, uint32_t* out_ids, uint64_t cap, uint64_t* needed);
+
+/* ---- T2 / T3 / T4: batched multi-source k-hop neighbour resolution -------------------------
+ * Query q has sources q_src[q_off[q] .. q_off[q+1]) (duplicates allowed; CCS:1563-1568 dedups
+ * them through a HashSet).  Levels: L0 = distinct valid sources,
+ * L(i+1) = (U_{u in Li} step(u)) minus everything seen so far, step = dependencies /
+ * dependents / resolve for mode OUT / IN / BOTH.  Row q = U_{1<=i<=k} Li sorted by ascending
+ * vertex id, out_hop = i.  exclude_sources != 0 seeds "seen" with L0, which at k = 1, mode
+ * BOTH is exactly resolveNeighbors (CCS:1558-1578); exclude_sources == 0 with one source and
+ * k = 1 is exactly resolve()/dependencies()/dependents() as sets (a self-loop reports the
+ * vertex itself, PG test :829-837).  1 <= k <= DMG_MAX_HOPS.                                   */
+int32_t dmg_neighbors_batch(dmg_graph* g, int32_t mode, int32_t k, int32_t exclude_sources,
+                            uint64_t n_queries, const uint32_t* q_off, const uint32_t* q_src,
+                            uint64_t* out_off, uint32_t* out_ids, uint8_t* out_hop, uint64_t cap,
+                            uint64_t* needed);
+
+/* Same, every pointer a DEVICE pointer, nothing copied; returns after the work completed on
+ * the device.  *needed (host) is always filled.  This is what bench.py times as `value`.       */
+int32_t dmg_neighbors_batch_dev(dmg_graph* g, int32_t mode, int32_t k, int32_t exclude_sources,
+                                uint64_t n_queries, const uint32_t* d_q_off, const uint32_t* d_q_src,
+                                uint64_t* d_out_off, uint32_t* d_out_ids, uint8_t* d_out_hop,
+                                uint64_t cap, uint64_t* needed);
+
+/* ---- T5: closure and analysisOrder ----------------------------------------------------------
+ * dmg_closure: BFS levels from a source set over dir (DMG_OUT / DMG_IN) on the whole graph;
+ * out_level[v] = hop distance, 0 for sources, DMG_LEVEL_UNREACHED otherwise.  *reached counts
+ * vertices with a level.  This is the reachable set of PG:390-421 with its BFS depth.
+ * dmg_analysis_order: exactly ProjectGraph.analysisOrder() (PG:390-421): FIFO BFS from the
+ * entry points in insertion order along dependencies() order, then every unvisited vertex in
+ * nodes order.  out_order has n_vertices entries.                                              */
+int32_t dmg_closure(dmg_graph* g, int32_t dir, uint32_t n_src, const uint32_t* src,
+                    uint32_t* out_level, uint64_t* reached);
+int32_t dmg_analysis_order(dmg_graph* g, uint32_t* out_order);
+
+/* entryPoints() (PG:345-347), insertion order; isEntryPoint (PG:336-338) as a byte per id. */
+int32_t dmg_entry_points(dmg_graph* g, uint32_t* out_ids, uint32_t cap, uint32_t* needed);
+int32_t dmg_is_entry_point_batch(dmg_graph* g, uint64_t n, const uint32_t* ids, uint8_t* out_flags);
+
+/* ---- S1 / S2: name scans --------------------------------------------------------------------
+ * Queries are byte strings the host has already lower-cased (CCS:1507, GQS:431); query q is
+ * q_bytes[q_off[q] .. q_off[q+1]).  The scan covers vertices [v_lo, v_hi) (one project's
+ * range, or 0..V).  kind DMG_SEARCH_CONTAINS_ALL: row q = every id whose lower-cased
+ * identifier contains the query, ascending id == nodes order (CCS:1511-1526; an empty query
+ * matches everything).  The two *_FIRST kinds return at most one id per query (GQS:434-453).  */
+int32_t dmg_search_batch(dmg_graph* g, int32_t kind, uint32_t v_lo, uint32_t v_hi, uint64_t n_queries,
+                         const uint32_t* q_off, const uint8_t* q_bytes, uint64_t* out_off,
+                         uint32_t* out_ids, uint64_t cap, uint64_t* needed);
+
+/* ---- measurement -----------------------------------------------------------------------------*/
+int32_t dmg_last_call_stats(dmg_engine* e, dmg_call_stats* out);
+/* Per-kernel CUDA-event timing (events on the stream each kernel is launched on).  While
+ * enabled every launch is bracketed by two events; read the totals with dmg_profile_get.    */
+int32_t dmg_profile_enable(dmg_engine* e, int32_t on);
+int32_t dmg_profile_reset(dmg_engine* e);
+int32_t dmg_profile_count(dmg_engine* e);
+int32_t dmg_profile_get(dmg_engine* e, int32_t index, const char** kernel_name, uint64_t* launches,
+                        double* total_ms);
+
+/* ---- device / pinned memory helpers (so a host needs no CUDA binding of its own) ------------ */
+int32_t dmg_device_alloc(dmg_engine* e, uint64_t bytes, void** d_ptr);
+int32_t dmg_device_free(dmg_engine* e, void* d_ptr);
+int32_t dmg_copy_to_device(dmg_engine* e, void* d_dst, const void* src, uint64_t bytes);
+int32_t dmg_copy_to_host(dmg_engine* e, void* dst, const void* d_src, uint64_t bytes);
+int32_t dmg_pinned_alloc(dmg_engine* e, uint64_t bytes, void** ptr);
+int32_t dmg_pinned_free(dmg_engine* e, void* ptr);
+/* Writes `bytes` of device memory (> L2) so the next timed call starts with a cold L2. */
+int32_t dmg_flush_l2(dmg_engine* e);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DMGRAPH_H */

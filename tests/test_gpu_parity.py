@@ -1,0 +1,270 @@
+"""GPU parity: the CUDA path, called through the C ABI, against the oracle and the golden
+vectors.  Bit-exact: ids, hops and orders are integers; nothing here has a tolerance."""
+import numpy as np
+import pytest
+
+import dmgraph
+import golden_runner as gr
+from dmgraph import synth
+from engine_adapter import EngineGraph
+from oracle import oracle as ora
+from oracle import pyref
+
+pytestmark = pytest.mark.gpu
+
+CASES = gr.load_cases()
+
+
+@pytest.fixture(scope="module")
+def engine():
+    e = dmgraph.Engine(0)
+    yield e
+    e.close()
+
+
+def rows(off, *arrs):
+    return [tuple(a[int(off[i]):int(off[i + 1])].tolist() for a in arrs) for i in range(len(off) - 1)]
+
+
+# ---- golden vectors transcribed from the reference's unit tests ------------------------------
+@pytest.mark.parametrize("case", CASES, ids=[c["name"] for c in CASES])
+def test_reference_unit_tests(engine, case):
+    g = gr.build(case, EngineGraph(engine))
+    gr.check(case, g)
+
+
+# ---- BASELINE config 1: the reference indexing itself, 2-hop for every class ----------------
+def _self_index(engine):
+    d = gr.load_self_index()
+    g, p = EngineGraph(engine), pyref.ProjectGraph()
+    for i, f in d["nodes"]:
+        g.add_node(i, f)
+        p.add_node(i, f)
+    for a, b in d["edges"]:
+        g.add_dependency(a, b)
+        p.add_dependency(a, b)
+    for e in d["entryPoints"]:
+        g.mark_as_entry_point(e)
+        p.mark_as_entry_point(e)
+    return g, p
+
+
+def test_config1_self_index(engine):
+    g, p = _self_index(engine)
+    names = p.identifiers()
+    assert g.node_count() == 46 and g.graph().info["n_edges"] == 77
+    assert g.analysis_order() == p.analysis_order()
+    assert g.entry_points() == p.entry_points()
+    n = len(names)
+    q_off = np.arange(n + 1, dtype=np.uint32)
+    q_src = np.arange(n, dtype=np.uint32)
+    for mode in ("out", "in", "both"):
+        for k in (1, 2, 3):
+            for excl in (True, False):
+                off, ids, hop = g.graph().neighbors_batch(dmgraph.MODES[mode], k, excl, q_off, q_src)
+                for v, nm in enumerate(names):
+                    want = pyref.khop(p, [nm], k, mode, excl)
+                    a, b = int(off[v]), int(off[v + 1])
+                    assert {names[i]: int(h) for i, h in zip(ids[a:b], hop[a:b])} == want
+                    assert list(ids[a:b]) == sorted(ids[a:b])
+    for nm in names:
+        assert g.dependencies(nm) == p.dependencies(nm)                      # exact order
+        assert g.dependents(nm) == sorted(p.dependents(nm), key=names.index)  # canonical order
+        assert sorted(g.resolve(nm)) == sorted(p.resolve(nm))
+    for q in ["Graph", "service", "", "co.fanki", "zzz", "Controller", "r", "domainmcp.shared.P"]:
+        assert g.search_project(q) == pyref.search_project(p, q)
+    for t in ["GraphService", "graphservice", "Preconditions", "Nope", "Parser", "shared"]:
+        assert g.resolve_class_name(t) == pyref.resolve_class_name(p, t)
+
+
+# ---- differential tests on seeded random graphs ----------------------------------------------
+def _random_graph(rng, n, e, n_parts=1, dup=True):
+    """Edges inside random project ranges, with duplicates, self-loops and dangling endpoints."""
+    cuts = np.sort(rng.choice(np.arange(1, n), size=min(n_parts - 1, max(n - 1, 0)), replace=False)) if n_parts > 1 else []
+    part_off = np.concatenate([[0], cuts, [n]]).astype(np.uint32)
+    part_of = np.searchsorted(part_off, np.arange(n), side="right") - 1
+    src = rng.integers(0, n, e)
+    lo, hi = part_off[part_of[src]], part_off[part_of[src] + 1]
+    dst = (lo + (rng.random(e) * (hi - lo)).astype(np.int64)).astype(np.int64)
+    if dup and e > 4:
+        k = e // 8
+        src[:k], dst[:k] = src[-k:], dst[-k:]                       # duplicates
+        bad = rng.integers(0, e, max(1, e // 20))
+        dst[bad] = n + rng.integers(0, 5, bad.size)                 # dangling
+    entry = rng.integers(0, n + 2, int(rng.integers(0, 6)))
+    return src.astype(np.uint32), dst.astype(np.uint32), entry.astype(np.uint32), part_off
+
+
+def _random_queries(rng, n, nq, max_src):
+    cnt = rng.integers(0, max_src + 1, nq)
+    q_off = np.zeros(nq + 1, np.uint32)
+    np.cumsum(cnt, out=q_off[1:])
+    q_src = rng.integers(0, n + 3, int(q_off[-1])).astype(np.uint32)   # some ids out of range
+    return q_off, q_src
+
+
+@pytest.mark.parametrize("n_parts", [1, 7])
+def test_khop_random_small_windows(engine, n_parts):
+    rng = np.random.default_rng(100 + n_parts)
+    for trial in range(12):
+        n = int(rng.integers(2, 600))
+        e = int(rng.integers(0, 8 * n))
+        src, dst, entry, part_off = _random_graph(rng, n, e, n_parts)
+        g = dmgraph.Graph(engine, n, src, dst, entry, part_off=part_off)
+        o = ora.CsrOracle(n, src, dst, entry, part_off)
+        assert g.info["n_edges"] == o.n_edges
+        q_off, q_src = _random_queries(rng, n, 200, 6)
+        for mode in (0, 1, 2):
+            for k in (1, 2, 5):
+                for excl in (0, 1):
+                    off, ids, hop = g.neighbors_batch(mode, k, excl, q_off, q_src)
+                    woff, wids, whop, wte = o.khop_batch(mode, k, excl, q_off, q_src)
+                    assert np.array_equal(off, woff)
+                    assert np.array_equal(ids, wids)
+                    assert np.array_equal(hop, whop)
+                    assert engine.last_stats()["edges_traversed"] == wte
+        g.release()
+
+
+def test_khop_random_large_window(engine):
+    """Projects above 8192 vertices take the global-scratch kernel, incl. its long-row path."""
+    rng = np.random.default_rng(5)
+    for n, e, n_parts in [(9000, 30000, 1), (20000, 150000, 1), (30000, 60000, 2)]:
+        src, dst, entry, part_off = _random_graph(rng, n, e, n_parts)
+        g = dmgraph.Graph(engine, n, src, dst, entry, part_off=part_off)
+        o = ora.CsrOracle(n, src, dst, entry, part_off)
+        q_off, q_src = _random_queries(rng, n, 300, 4)
+        for mode, k, excl in [(0, 1, 0), (1, 1, 0), (2, 1, 1), (2, 2, 1), (0, 4, 0), (2, 6, 1), (1, 3, 1)]:
+            off, ids, hop = g.neighbors_batch(mode, k, excl, q_off, q_src)
+            woff, wids, whop, wte = o.khop_batch(mode, k, excl, q_off, q_src, threads=8)
+            assert np.array_equal(off, woff)
+            assert np.array_equal(ids, wids)
+            assert np.array_equal(hop, whop)
+            assert engine.last_stats()["edges_traversed"] == wte
+        g.release()
+
+
+def test_adjacency_random(engine):
+    rng = np.random.default_rng(9)
+    for n, e in [(1, 0), (50, 400), (3000, 40000)]:
+        src, dst, entry, part_off = _random_graph(rng, n, e, 1)
+        g = dmgraph.Graph(engine, n, src, dst, entry)
+        o = ora.CsrOracle(n, src, dst, entry)
+        ids = rng.integers(0, n + 5, 1000).astype(np.uint32)
+        for d in (0, 1):
+            off, out = g.adjacency_batch(d, ids)
+            woff, wout = o.adjacency_batch(d, ids)
+            assert np.array_equal(off, woff) and np.array_equal(out, wout)
+        # all-vertex dump (classes:+dependencies:+dependents, GQS:111-150)
+        allv = np.arange(n, dtype=np.uint32)
+        for d in (0, 1):
+            off, out = g.adjacency_batch(d, allv)
+            woff, wout = o.adjacency_batch(d, allv)
+            assert np.array_equal(off, woff) and np.array_equal(out, wout)
+        assert np.array_equal(g.entry_points(), o.entry_points())
+        flags = g.is_entry_point_batch(ids)
+        es = set(o.entry_points().tolist())
+        assert flags.tolist() == [int(i in es) for i in ids.tolist()]
+        g.release()
+
+
+def test_empty_and_ragged_inputs(engine):
+    g = dmgraph.Graph(engine, 0, [], [], [])
+    off, ids, hop = g.neighbors_batch(2, 1, 1, [0, 0, 2], [0, 5])
+    assert off.tolist() == [0, 0, 0] and ids.size == 0
+    assert g.analysis_order().size == 0
+    lvl, reached = g.closure(0, [])
+    assert reached == 0
+    g.release()
+    g = dmgraph.Graph(engine, 3, [0, 1], [1, 2], [0])
+    off, ids, hop = g.neighbors_batch(2, 1, 1, [0], [])            # zero queries
+    assert off.tolist() == [0]
+    off, ids, hop = g.neighbors_batch(2, 2, 1, [0, 0, 1, 1], [1])  # empty rows around a real one
+    assert off.tolist() == [0, 0, 2, 2] and ids.tolist() == [0, 2] and hop.tolist() == [1, 1]
+    with pytest.raises(dmgraph.DmgError) as ei:
+        g.neighbors_batch(2, 0, 1, [0, 1], [0])
+    assert ei.value.code == dmgraph.EINVAL
+    with pytest.raises(dmgraph.DmgError) as ei:
+        g.neighbors_batch(2, 1, 1, [0, 1], [1], cap=1)             # needs 2
+    assert ei.value.code == dmgraph.ECAP
+    with pytest.raises(dmgraph.DmgError):                           # edge across project ranges
+        dmgraph.Graph(engine, 4, [0], [3], [], part_off=[0, 2, 4])
+    g.release()
+
+
+# ---- closure / analysisOrder ------------------------------------------------------------------
+def test_closure_and_order_random(engine):
+    rng = np.random.default_rng(21)
+    for n, e in [(2, 1), (40, 60), (500, 900), (5000, 20000), (20000, 30000)]:
+        src, dst, entry, part_off = _random_graph(rng, n, e, 1)
+        g = dmgraph.Graph(engine, n, src, dst, entry)
+        o = ora.CsrOracle(n, src, dst, entry)
+        assert np.array_equal(g.analysis_order(), o.analysis_order())
+        for d in (0, 1):
+            s = rng.integers(0, n + 2, int(rng.integers(0, 5))).astype(np.uint32)
+            lvl, reached = g.closure(d, s)
+            wl, wr, wte = o.closure(d, s)
+            assert np.array_equal(lvl, wl) and reached == wr
+            assert engine.last_stats()["edges_traversed"] == wte
+        g.release()
+
+
+def test_order_deep_chain(engine):
+    n = 3000
+    src = np.arange(n - 1)
+    g = dmgraph.Graph(engine, n, src + 1, src, [n - 1])     # n-1 -> n-2 -> ... -> 0
+    assert g.analysis_order().tolist() == list(range(n - 1, -1, -1))
+    lvl, reached = g.closure(0, [n - 1])
+    assert reached == n and lvl.tolist() == list(range(n - 1, -1, -1))
+    g.release()
+
+
+# ---- search -----------------------------------------------------------------------------------
+def test_search_random(engine):
+    rng = np.random.default_rng(33)
+    names = synth.project_names(3, 3000, rng)
+    off, arena = synth.pack_names(names)
+    low = np.frombuffer(bytes(arena).lower(), dtype=np.uint8).copy()
+    g = dmgraph.Graph(engine, len(names), [], [], [], name_off=off, name_bytes=arena)
+    queries = [b"", b"order", b"svc3", b"x", b"controller", b"zzzz", b"1", b".", b"payment12",
+               names[7].lower().encode(), names[2999].lower().encode()[-9:], b"o" * 2000]
+    queries += [names[int(i)].lower().encode()[int(a):int(a) + int(l)]
+                for i, a, l in zip(rng.integers(0, 3000, 40), rng.integers(0, 20, 40), rng.integers(1, 12, 40))]
+    for kind in (0, 1, 2):
+        for (lo, hi) in [(0, None), (100, 1700), (2999, 3000), (5, 5)]:
+            o, ids = g.search_batch(kind, queries, lo, hi)
+            wo, wids = ora.search_batch(off, low, queries, kind, lo, hi)
+            assert np.array_equal(o, wo) and np.array_equal(ids, wids)
+    g.release()
+
+
+# ---- full-size properties (BASELINE config 2 shape) -------------------------------------------
+def test_config2_full_size_properties(engine):
+    sg = synth.eco_graph()
+    g = dmgraph.Graph(engine, sg.n_vertices, sg.src, sg.dst, sg.entry, part_off=sg.part_off)
+    q_off, q_src = synth.stacktrace_queries(sg, n_queries=65536)
+    off, ids, hop = g.neighbors_batch(dmgraph.BOTH, 2, 1, q_off, q_src)
+    st = engine.last_stats()
+    nq = q_off.size - 1
+    # rows sorted, inside the query's project, never a source, hops in {1,2}
+    row = np.repeat(np.arange(nq), np.diff(off).astype(np.int64))
+    assert np.all((hop == 1) | (hop == 2))
+    part_of_row = (q_src[q_off[:-1]] // 2000)[row]
+    assert np.array_equal(ids // 2000, part_of_row)
+    same_row = row[1:] == row[:-1]
+    assert np.all(ids[1:][same_row] > ids[:-1][same_row])
+    # idempotence
+    off2, ids2, hop2 = g.neighbors_batch(dmgraph.BOTH, 2, 1, q_off, q_src)
+    assert np.array_equal(off, off2) and np.array_equal(ids, ids2) and np.array_equal(hop, hop2)
+    # k=1 is a subset with the same hop-1 set
+    off1, ids1, hop1 = g.neighbors_batch(dmgraph.BOTH, 1, 1, q_off, q_src)
+    assert np.all(hop1 == 1) and int(off1[-1]) == int((hop == 1).sum())
+    assert np.array_equal(ids1, ids[hop == 1])
+    # the oracle on a slice of the batch
+    o = ora.CsrOracle(sg.n_vertices, sg.src, sg.dst, sg.entry, sg.part_off)
+    sl = slice(0, 2048)
+    woff, wids, whop, wte = o.khop_batch(2, 2, 1, q_off[:2049] - q_off[0], q_src[:int(q_off[2048])], threads=8)
+    assert np.array_equal(off[:2049], woff)
+    assert np.array_equal(ids[:int(woff[-1])], wids) and np.array_equal(hop[:int(woff[-1])], whop)
+    assert st["results"] == int(off[-1])
+    g.release()
