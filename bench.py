@@ -255,8 +255,15 @@ def main():
     kname = max(prof, key=lambda k: prof[k][1]) if prof else "khop_small"
     kl, kms = prof.get(kname, (1, dev_ms))
     n_src_total = int(q_off[-1])
-    alg_bytes = 16 * stats["rows_expanded"] + 4 * stats["edges_traversed"] + 4 * n_src_total + 5 * stats["results"]
+    # B_q = sum over expanded u of (8R + 4 deg(u)) + 4 n_sources + 5 n_results, R = 2
+    step_bytes = 16 * stats["rows_expanded"] + 4 * stats["edges_traversed"] + 4 * n_src_total + 5 * stats["results"]
+    stage_bytes = sg.part_off[1] * nq        # one hop byte per project vertex per query
+    if kname == "khop_emit":
+        alg_bytes = int(stage_bytes + 5 * stats["results"] + 16 * nq)
+    else:
+        alg_bytes = int(step_bytes)
     achieved = alg_bytes / (kms / kl * 1e-3) / 1e9
+    actual_bytes = int(8 * stats["rows_expanded"] + 4 * stats["edges_read"] + 4 * n_src_total + stage_bytes)
     traffic = None
     tpath = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(tpath):
@@ -267,9 +274,14 @@ def main():
     roofline = {"bound": "hbm", "kernel": kname, "achieved": achieved, "peak": peak, "unit": "GB/s",
                 "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": alg_bytes, "kernel_ms_per_launch": kms / kl,
+                "bytes_actually_loaded_per_launch": actual_bytes,
+                "whole_step_algorithmic_bytes": int(step_bytes),
+                "whole_step_achieved_GBs": step_bytes / (dev_ms / args.steps * 1e-3) / 1e9,
                 "kernel_share_of_step": kms / dev_ms if dev_ms else None,
-                "note": "CSR of this config (17 MB) is L2-resident: algorithmic bytes are served mostly by "
-                        "L2, not HBM; see profiles/ for DRAM vs L2 bytes"}
+                "note": "algorithmic bytes follow SURVEY.md 8d (every adjacency entry of every expanded vertex); "
+                        "bottom-up levels stop at the first frontier member, so fewer entries are loaded "
+                        "(edges_read), and this config's CSR (25 MB) is L2-resident: frac can exceed what HBM "
+                        "alone would allow; see profiles/ for DRAM vs L2 bytes"}
 
     # ---- e2e: host buffers through the reference-facing call --------------------------------
     h_q_off, p1 = eng.pinned(np.uint32, nq + 1)
@@ -301,7 +313,7 @@ def main():
                        "timing": "CUDA events on libdmgraph's launch stream, summed over steps, max over ranks",
                        "results_per_step": int(stats["results"]), "sources_per_step": n_src_total,
                        "graph_upload_s": upload_s},
-            "gteps": gteps, "edges_traversed_per_step": int(edges),
+            "gteps": gteps, "edges_traversed_per_step": int(edges), "edges_read_per_step": int(stats["edges_read"]),
             "wall_ms_per_step": allmax(wall_ms) / args.steps,
             "roofline": roofline,
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),

@@ -47,6 +47,8 @@ struct DevBuf {
 enum KernelId : int {
   K_KHOP_SMALL = 0,
   K_KHOP_GLOBAL,
+  K_KHOP_EMIT,
+  K_SCAN_COUNTS,
   K_ADJ_GATHER,
   K_ENTRY_FLAGS,
   K_CLOSURE_INIT,
@@ -163,6 +165,8 @@ struct dmg_graph {
   uint32_t* d_out_idx = nullptr;   // [E]   row order = addDependency order
   uint32_t* d_in_ptr = nullptr;    // [V+1]
   uint32_t* d_in_idx = nullptr;    // [E]   row order = ascending source id
+  uint32_t* d_und_ptr = nullptr;   // [V+1] resolve() rows: out row followed by in row (PG:359-378)
+  uint32_t* d_und_idx = nullptr;   // [2E]
   uint32_t* d_part_off = nullptr;  // [P+1]
   uint32_t* d_entry = nullptr;     // [n_entry] insertion order
   uint32_t* d_entry_bits = nullptr;  // [ceil(V/32)]
@@ -231,9 +235,11 @@ __device__ __forceinline__ uint64_t lookback_exclusive(uint64_t* status, uint64_
   while (true) {
     const long long j = idx - (long long)lane;
     uint64_t v;
-    do {
+    v = (j >= 0) ? ld_relaxed_u64(status + j) : LB_PRE;
+    while (__any_sync(FULL, (v >> 62) == 0)) {
+      __nanosleep(100);   // predecessors are still working: do not burn issue slots spinning
       v = (j >= 0) ? ld_relaxed_u64(status + j) : LB_PRE;
-    } while (__any_sync(FULL, (v >> 62) == 0));
+    }
     const unsigned pm = __ballot_sync(FULL, (v >> 62) == 2);
     if (pm) {
       const int first = __ffs(pm) - 1;

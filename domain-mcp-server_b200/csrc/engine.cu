@@ -29,7 +29,7 @@ int32_t cuda_fail(cudaError_t e, const char* what, const char* file, int line) {
 void publish_stats(const dmg_call_stats& s) { g_last_stats = s; }
 
 const char* const kKernelNames[K_COUNT] = {
-    "khop_small", "khop_global", "adjacency_gather", "entry_flags", "closure_init", "closure_topdown",
+    "khop_small", "khop_global", "khop_emit", "scan_counts", "adjacency_gather", "entry_flags", "closure_init", "closure_topdown",
     "closure_bottomup", "order_degrees", "order_minslot", "order_claim", "order_tail", "scan_block",
     "scan_top", "scan_add", "search_scan", "search_first", "search_emit", "flush_l2", "misc"};
 
@@ -154,7 +154,7 @@ using namespace dmg;
 static void free_graph(dmg_graph* g) {
   cudaSetDevice(g->eng->device);
   for (void* p : {(void*)g->d_out_ptr, (void*)g->d_out_idx, (void*)g->d_in_ptr, (void*)g->d_in_idx,
-                  (void*)g->d_part_off, (void*)g->d_entry, (void*)g->d_entry_bits, (void*)g->d_name_off,
+                  (void*)g->d_und_ptr, (void*)g->d_und_idx, (void*)g->d_part_off, (void*)g->d_entry, (void*)g->d_entry_bits, (void*)g->d_name_off,
                   (void*)g->d_lower})
     if (p) cudaFree(p);
   delete g;
@@ -246,7 +246,7 @@ int32_t dmg_graph_create(dmg_engine* e, const dmg_graph_desc* d, dmg_graph** out
     set_error("dmg_graph_create: edge/entry arrays missing");
     return DMG_EINVAL;
   }
-  if (E >= 0xFFFFFFF0ull) {
+  if (E >= 0x7FFFFFF0ull) {
     set_error("dmg_graph_create: %llu edges exceed the 32-bit CSR offset range", (unsigned long long)E);
     return DMG_EINVAL;
   }
@@ -354,7 +354,26 @@ int32_t dmg_graph_create(dmg_engine* e, const dmg_graph_desc* d, dmg_graph** out
   int32_t st = DMG_OK;
   std::vector<uint32_t> ebits((V + 31) / 32 + 1, 0);
   for (uint32_t v : g->h_entry) ebits[v >> 5] |= 1u << (v & 31);
-  if ((st = upload(&g->d_out_ptr, out_ptr.data(), out_ptr.size(), &bytes)) != DMG_OK ||
+  // resolve() rows for mode BOTH: the out row followed by the in row of the same vertex, one
+  // contiguous range per vertex (no de-duplication: a 2-cycle appears twice, the visited
+  // set removes it, PG:366-375)
+  std::vector<uint32_t> und_ptr(V + 1, 0), und_idx;
+  try {
+    und_idx.resize(2 * out_idx.size());
+    for (uint32_t v = 0; v < V; ++v) {
+      uint32_t w = und_ptr[v];
+      for (uint32_t j = out_ptr[v]; j < out_ptr[v + 1]; ++j) und_idx[w++] = out_idx[j];
+      for (uint32_t j = in_ptr[v]; j < in_ptr[v + 1]; ++j) und_idx[w++] = in_idx[j];
+      und_ptr[v + 1] = w;
+    }
+  } catch (const std::bad_alloc&) {
+    delete g;
+    set_error("dmg_graph_create: host out of memory");
+    return DMG_ENOMEM;
+  }
+  if ((st = upload(&g->d_und_ptr, und_ptr.data(), und_ptr.size(), &bytes)) != DMG_OK ||
+      (st = upload(&g->d_und_idx, und_idx.data(), und_idx.size(), &bytes)) != DMG_OK ||
+      (st = upload(&g->d_out_ptr, out_ptr.data(), out_ptr.size(), &bytes)) != DMG_OK ||
       (st = upload(&g->d_out_idx, out_idx.data(), out_idx.size(), &bytes)) != DMG_OK ||
       (st = upload(&g->d_in_ptr, in_ptr.data(), in_ptr.size(), &bytes)) != DMG_OK ||
       (st = upload(&g->d_in_idx, in_idx.data(), in_idx.size(), &bytes)) != DMG_OK ||

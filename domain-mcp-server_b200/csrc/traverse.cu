@@ -19,6 +19,8 @@ struct KhopArgs {
   const uint32_t* out_idx;
   const uint32_t* in_ptr;
   const uint32_t* in_idx;
+  const uint32_t* und_ptr;   // resolve() rows (out row ++ in row)
+  const uint32_t* und_idx;
   const uint32_t* part_off;
   uint32_t V, n_parts;
   int mode, k, exclude;
@@ -32,6 +34,11 @@ struct KhopArgs {
   uint64_t* status;
   DevCounters* ctr;
   uint32_t win_cap;   // largest project, rounded up to a multiple of 128 vertices
+  // khop_small only: query chunk [q_begin, q_end), staging rows, row sizes, (lo, wn) per query
+  unsigned long long q_begin, q_end;
+  uint8_t* stage;
+  uint32_t* counts;
+  uint32_t* qwin;
 };
 
 __device__ __forceinline__ void find_window(const KhopArgs& a, uint32_t qb, uint32_t qe, uint32_t* lo, uint32_t* hi) {
@@ -77,30 +84,53 @@ __device__ __forceinline__ uint32_t block_excl_scan(uint32_t v, uint32_t* s_wsum
 // ---------------------------------------------------------------------------------------------
 // khop_small: one CTA per query, everything about the query lives in shared memory.
 // Used when every project has <= 8192 vertices (BASELINE config 2: 2000-vertex projects).
-//   hop8[win]   u8   0 = unseen, 255 = excluded source, else hop
-//   seen[win/32] u32 claim bitmap (atomicOr decides who enqueues a vertex)
-//   queue[2*win] u16 frontier queue, vertex ids relative to the project base; each level is the
-//                    segment the previous level appended (ballot/popc warp-aggregated append);
-//                    reused as the staging area of the ordered result
+//   hop8[win]     u8   0 = unseen, 255 = excluded source, else hop
+//   seen[win/32]  u32  claim bitmap of the top-down levels (atomicOr decides who enqueues)
+//   srcb[win/32]  u32  the distinct sources (level-0 frontier membership)
+//   queue[2*win]  u16  frontier queue, ids relative to the project base; level i is the segment
+//                      level i-1 appended (ballot/popc warp-aggregated append)
+//   ulist[win]    u16  unseen vertices of a bottom-up level
+// Level step, chosen per level (direction-optimising BFS; the result is the same set):
+//   top-down   the frontier's rows are flattened: a block scan of the row lengths gives every
+//              adjacency entry a position, each warp takes a contiguous quarter of the positions
+//              and walks it 32 at a time, so lanes stay busy whatever the degree distribution
+//   bottom-up  when the frontier's rows hold many more entries than there are unseen vertices
+//              (m_f > 24 * n_unseen) each unseen vertex looks for ONE frontier member in its
+//              reverse row instead: 8 lanes per vertex, 32-byte chunks, stop at the first hit
+// The finished hop8 array is copied to a staging row in global memory; khop_emit_kernel
+// compacts the staging rows into the packed, id-ordered output after a scan of the row sizes.
 // ---------------------------------------------------------------------------------------------
+constexpr uint32_t BU_ALPHA = 24;
+
 template <int THREADS>
 __global__ void __launch_bounds__(THREADS) khop_small_kernel(const KhopArgs a) {
   extern __shared__ __align__(16) unsigned char smem[];
+  const uint32_t WC = a.win_cap;
   uint8_t* hop8 = smem;
-  uint32_t* seen = reinterpret_cast<uint32_t*>(smem + a.win_cap);
-  uint16_t* queue = reinterpret_cast<uint16_t*>(smem + a.win_cap + a.win_cap / 8);
-  __shared__ unsigned long long s_q, s_base;
-  __shared__ uint32_t s_lo, s_hi, s_tail;
+  uint32_t* seen = reinterpret_cast<uint32_t*>(smem + WC);
+  uint32_t* srcb = reinterpret_cast<uint32_t*>(smem + WC + WC / 8);
+  uint16_t* queue = reinterpret_cast<uint16_t*>(smem + WC + WC / 4);
+  uint16_t* ulist = queue + 2 * WC;
+  __shared__ unsigned long long s_q;
+  __shared__ uint32_t s_lo, s_hi, s_tail, s_nu, s_cnt;
   __shared__ uint32_t s_wsum[THREADS / 32 + 1];
-  constexpr int NW = THREADS / 32;
+  __shared__ uint32_t s_end[THREADS], s_adj[THREADS];
+  constexpr int NW = THREADS / 32, NG = THREADS / 8;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  unsigned long long te = 0, rows = 0;
+  const int grp = tid >> 3, gl = tid & 7;
+  const unsigned gmask = 0xFFu << (8 * (grp & 3));
+  // forward rows (top-down) and reverse rows (bottom-up) for the step function of this mode
+  const uint32_t* __restrict__ fptr = a.mode == DMG_BOTH ? a.und_ptr : (a.mode == DMG_OUT ? a.out_ptr : a.in_ptr);
+  const uint32_t* __restrict__ fidx = a.mode == DMG_BOTH ? a.und_idx : (a.mode == DMG_OUT ? a.out_idx : a.in_idx);
+  const uint32_t* __restrict__ rptr = a.mode == DMG_BOTH ? a.und_ptr : (a.mode == DMG_OUT ? a.in_ptr : a.out_ptr);
+  const uint32_t* __restrict__ ridx = a.mode == DMG_BOTH ? a.und_idx : (a.mode == DMG_OUT ? a.in_idx : a.out_idx);
+  unsigned long long te = 0, rows = 0, reads = 0;
 
   while (true) {
-    if (tid == 0) s_q = atomicAdd(&a.ctr->ticket, 1ull);
+    if (tid == 0) s_q = a.q_begin + atomicAdd(&a.ctr->ticket, 1ull);
     __syncthreads();
     const unsigned long long q = s_q;
-    if (q >= a.nq) break;
+    if (q >= a.q_end) break;
     const uint32_t qb = a.q_off[q], qe = a.q_off[q + 1];
     if (tid == 0) {
       uint32_t lo, hi;
@@ -108,68 +138,174 @@ __global__ void __launch_bounds__(THREADS) khop_small_kernel(const KhopArgs a) {
       s_lo = lo;
       s_hi = hi;
       s_tail = 0;
+      s_cnt = 0;
     }
     __syncthreads();
     const uint32_t lo = s_lo, hi = s_hi, wn = hi - lo;
-    const uint32_t nw4 = (wn + 3) >> 2;
+    const uint32_t nw4 = (wn + 3) >> 2, nw32 = (wn + 31) >> 5;
     for (uint32_t i = tid; i < nw4; i += THREADS) reinterpret_cast<uint32_t*>(hop8)[i] = 0;
-    for (uint32_t i = tid; i < ((wn + 31) >> 5); i += THREADS) seen[i] = 0;
+    for (uint32_t i = tid; i < nw32; i += THREADS) {
+      seen[i] = 0;
+      srcb[i] = 0;
+    }
     __syncthreads();
     // L0: distinct sources inside the project
     for (uint32_t i = qb + tid; i < qe; i += THREADS) {
       const uint32_t s = a.q_src[i];
       if (s >= lo && s < hi) {
         const uint32_t v = s - lo, bit = 1u << (v & 31);
-        if (!(atomicOr(&seen[v >> 5], bit) & bit)) {
+        if (!(atomicOr(&srcb[v >> 5], bit) & bit)) {
           queue[atomicAdd(&s_tail, 1u)] = (uint16_t)v;
-          if (a.exclude) hop8[v] = 255;
+          if (a.exclude) {
+            hop8[v] = 255;
+            atomicOr(&seen[v >> 5], bit);
+          }
         }
       }
     }
     __syncthreads();
-    uint32_t head = 0, tail = s_tail;
-    __syncthreads();    // nobody appends before everybody has read s_tail
-    if (!a.exclude) {   // sources may be re-reached and reported: forget that they were seen
-      for (uint32_t i = tid; i < tail; i += THREADS) {
-        const uint32_t v = queue[i];
-        atomicAnd(&seen[v >> 5], ~(1u << (v & 31)));
-      }
-      __syncthreads();
-    }
+    const uint32_t ns = s_tail;
+    uint32_t head = 0, tail = ns;
+    __syncthreads();   // nobody appends before everybody has read s_tail
+
     for (int lvl = 1; lvl <= a.k && head < tail; ++lvl) {
       const bool last = (lvl == a.k);
-      for (uint32_t i = head + warp; i < tail; i += NW) {
+      // m_f = adjacency entries of the frontier's rows (this is also TE of SURVEY.md 8d)
+      uint32_t mf = 0;
+      for (uint32_t i = head + tid; i < tail; i += THREADS) {
         const uint32_t u = lo + queue[i];
-        uint32_t b0 = 0, n0 = 0, b1 = 0, n1 = 0;
-        if (a.mode != DMG_IN) {
-          b0 = a.out_ptr[u];
-          n0 = a.out_ptr[u + 1] - b0;
-        }
-        if (a.mode != DMG_OUT) {
-          b1 = a.in_ptr[u];
-          n1 = a.in_ptr[u + 1] - b1;
-        }
-        const uint32_t n = n0 + n1;
-        if (lane == 0) {
-          te += n;
-          ++rows;
-        }
-        for (uint32_t base = 0; base < n; base += 32) {
-          const uint32_t j = base + lane;
-          bool isnew = false;
-          uint32_t v = 0;
-          if (j < n) {
-            v = (j < n0 ? a.out_idx[b0 + j] : a.in_idx[b1 + (j - n0)]) - lo;
-            if (hop8[v] == 0) {
-              if (last) {
-                hop8[v] = (uint8_t)lvl;   // same value from every racer
-              } else {
-                const uint32_t bit = 1u << (v & 31);
-                if (!(atomicOr(&seen[v >> 5], bit) & bit)) {
-                  hop8[v] = (uint8_t)lvl;
-                  isnew = true;
+        mf += fptr[u + 1] - fptr[u];
+      }
+      mf = warp_sum_u32(mf);
+      if (lane == 0) s_wsum[warp] = mf;
+      if (tid == 0) s_nu = 0;
+      __syncthreads();
+      mf = 0;
+#pragma unroll
+      for (int w = 0; w < NW; ++w) mf += s_wsum[w];
+      const uint32_t marked = (a.exclude ? ns : 0u) + (tail - ns);
+      const uint32_t n_unseen = wn - min(wn, marked);
+      if (tid == 0) {
+        te += mf;
+        rows += tail - head;
+      }
+      const bool bottom_up = mf > BU_ALPHA * n_unseen;
+      __syncthreads();   // s_wsum is reused by block_excl_scan below
+
+      if (!bottom_up) {
+        for (uint32_t c0 = head; c0 < tail; c0 += THREADS) {
+          const uint32_t i = c0 + tid;
+          uint32_t b = 0, n = 0;
+          if (i < tail) {
+            const uint32_t u = lo + queue[i];
+            b = fptr[u];
+            n = fptr[u + 1] - b;
+          }
+          uint32_t T;
+          const uint32_t pre = block_excl_scan<THREADS>(n, s_wsum, &T);
+          s_end[tid] = pre + n;
+          s_adj[tid] = b - pre;
+          __syncthreads();
+          const uint32_t Tq = (((T + NW - 1) / NW) + 31u) & ~31u;
+          const uint32_t pbeg = warp * Tq, pend = min(T, pbeg + Tq);
+          if (pbeg < pend) {
+            uint32_t r = 0;   // first row whose end lies beyond pbeg
+            {
+              uint32_t l = 0, h = THREADS;
+              while (l < h) {
+                const uint32_t m = (l + h) >> 1;
+                if (s_end[m] <= pbeg) l = m + 1; else h = m;
+              }
+              r = l;
+            }
+            for (uint32_t p0 = pbeg; p0 < pend; p0 += 32) {
+              const uint32_t p = p0 + lane;
+              const bool valid = p < pend;
+              bool isnew = false;
+              uint32_t v = 0;
+              if (valid) {
+                while (s_end[r] <= p) ++r;
+                v = fidx[s_adj[r] + p] - lo;
+                ++reads;
+                if (hop8[v] == 0) {
+                  if (last) {
+                    hop8[v] = (uint8_t)lvl;   // same value from every racer
+                  } else {
+                    const uint32_t bit = 1u << (v & 31);
+                    if (!(atomicOr(&seen[v >> 5], bit) & bit)) {
+                      hop8[v] = (uint8_t)lvl;
+                      isnew = true;
+                    }
+                  }
                 }
               }
+              if (!last) {
+                const unsigned m = __ballot_sync(FULL, isnew);
+                if (m) {
+                  uint32_t pos = 0;
+                  if (lane == 0) pos = atomicAdd(&s_tail, (uint32_t)__popc(m));
+                  pos = __shfl_sync(FULL, pos, 0);
+                  if (isnew) queue[pos + __popc(m & lanemask_lt())] = (uint16_t)v;
+                }
+              }
+            }
+          }
+          __syncthreads();   // s_end / s_adj are rewritten by the next chunk
+        }
+      } else {
+        // unseen vertices -> ulist
+        for (uint32_t w0 = 0; w0 < nw4; w0 += THREADS) {
+          const uint32_t w = w0 + tid;
+          const uint32_t x = (w < nw4) ? reinterpret_cast<const uint32_t*>(hop8)[w] : 0xFFFFFFFFu;
+#pragma unroll
+          for (int bb = 0; bb < 4; ++bb) {
+            const uint32_t v = w * 4 + bb;
+            const bool un = ((x >> (8 * bb)) & 255u) == 0 && v < wn;
+            const unsigned m = __ballot_sync(FULL, un);
+            if (m) {
+              uint32_t pos = 0;
+              if (lane == 0) pos = atomicAdd(&s_nu, (uint32_t)__popc(m));
+              pos = __shfl_sync(FULL, pos, 0);
+              if (un) ulist[pos + __popc(m & lanemask_lt())] = (uint16_t)v;
+            }
+          }
+        }
+        __syncthreads();
+        const uint32_t nu = s_nu;
+        const uint32_t want = (uint32_t)(lvl - 1);
+        uint32_t i = grp, v = 0, b = 0, n = 0, j0 = 0;
+        bool active = i < nu;
+        if (active) {
+          v = ulist[i];
+          b = rptr[lo + v];
+          n = rptr[lo + v + 1] - b;
+        }
+        while (__any_sync(FULL, active)) {
+          bool hit = false;
+          if (active && j0 + gl < n) {
+            const uint32_t u = ridx[b + j0 + gl] - lo;
+            ++reads;
+            hit = (lvl == 1) ? ((srcb[u >> 5] >> (u & 31)) & 1u) : (hop8[u] == want);
+          }
+          const bool ghit = (__ballot_sync(FULL, hit) & gmask) != 0;
+          bool isnew = false;
+          uint32_t vnew = v;
+          if (active) {
+            if (ghit && gl == 0) {
+              hop8[v] = (uint8_t)lvl;
+              isnew = !last;
+            }
+            if (ghit || j0 + 8 >= n) {
+              i += NG;
+              active = i < nu;
+              j0 = 0;
+              if (active) {
+                v = ulist[i];
+                b = rptr[lo + v];
+                n = rptr[lo + v + 1] - b;
+              }
+            } else {
+              j0 += 8;
             }
           }
           if (!last) {
@@ -178,7 +314,7 @@ __global__ void __launch_bounds__(THREADS) khop_small_kernel(const KhopArgs a) {
               uint32_t pos = 0;
               if (lane == 0) pos = atomicAdd(&s_tail, (uint32_t)__popc(m));
               pos = __shfl_sync(FULL, pos, 0);
-              if (isnew) queue[pos + __popc(m & lanemask_lt())] = (uint16_t)v;
+              if (isnew) queue[pos + __popc(m & lanemask_lt())] = (uint16_t)vnew;
             }
           }
         }
@@ -188,60 +324,126 @@ __global__ void __launch_bounds__(THREADS) khop_small_kernel(const KhopArgs a) {
       tail = s_tail;
       __syncthreads();
     }
-    // ordered result: scan hop8 in id order, compact into the staging area
-    uint16_t* st_id = queue;
-    uint8_t* st_hop = reinterpret_cast<uint8_t*>(queue + a.win_cap);
-    const uint32_t per = (nw4 + THREADS - 1) / THREADS;
-    const uint32_t w0 = min(nw4, tid * per), w1 = min(nw4, w0 + per);
+
+    // stage the finished hop array and the row size; khop_emit_kernel writes the packed row
+    uint8_t* st = a.stage + (size_t)(q - a.q_begin) * WC;
     uint32_t cnt = 0;
-    for (uint32_t w = w0; w < w1; ++w) {
-      const uint32_t x = reinterpret_cast<const uint32_t*>(hop8)[w];
+    for (uint32_t i = tid; i < nw4; i += THREADS) {
+      const uint32_t x = reinterpret_cast<const uint32_t*>(hop8)[i];
+      reinterpret_cast<uint32_t*>(st)[i] = x;
 #pragma unroll
-      for (int b = 0; b < 4; ++b) {
-        const uint32_t h = (x >> (8 * b)) & 255u;
+      for (int bb = 0; bb < 4; ++bb) {
+        const uint32_t h = (x >> (8 * bb)) & 255u;
         cnt += (h != 0 && h != 255);
       }
     }
-    uint32_t total;
-    uint32_t off = block_excl_scan<THREADS>(cnt, s_wsum, &total);
-    for (uint32_t w = w0; w < w1; ++w) {
-      const uint32_t x = reinterpret_cast<const uint32_t*>(hop8)[w];
-#pragma unroll
-      for (int b = 0; b < 4; ++b) {
-        const uint32_t h = (x >> (8 * b)) & 255u;
-        if (h != 0 && h != 255) {
-          st_id[off] = (uint16_t)(w * 4 + b);
-          st_hop[off] = (uint8_t)h;
-          ++off;
-        }
-      }
-    }
-    if (warp == 0) {
-      const unsigned long long excl = lookback_exclusive(a.status, q, total);
-      if (lane == 0) {
-        s_base = excl;
-        a.out_off[q] = excl;
-        if (q == a.nq - 1) {
-          a.out_off[a.nq] = excl + total;
-          a.ctr->total = excl + total;
-        }
-      }
-    }
+    cnt = warp_sum_u32(cnt);
+    if (lane == 0 && cnt) atomicAdd(&s_cnt, cnt);
     __syncthreads();
-    const unsigned long long base = s_base;
-    for (uint32_t i = tid; i < total; i += THREADS) {
-      const unsigned long long pos = base + i;
-      if (pos < a.cap) {
-        a.out_ids[pos] = lo + st_id[i];
-        a.out_hop[pos] = st_hop[i];
-      }
+    if (tid == 0) {
+      a.counts[q] = s_cnt;
+      a.qwin[2 * q] = lo;
+      a.qwin[2 * q + 1] = wn;
     }
   }
   te = warp_sum_u64(te);
   rows = warp_sum_u64(rows);
-  if (lane == 0 && rows) {
-    atomicAdd(&a.ctr->edges, te);
-    atomicAdd(&a.ctr->rows, rows);
+  reads = warp_sum_u64(reads);
+  if (lane == 0) {
+    if (rows) {
+      atomicAdd(&a.ctr->edges, te);
+      atomicAdd(&a.ctr->rows, rows);
+    }
+    if (reads) atomicAdd(&a.ctr->aux[0], reads);
+  }
+}
+
+// Exclusive scan of the row sizes into out_off (u64), tile by tile with the look-back
+// allocator; *carry (device) holds the running total across query chunks.
+constexpr int SC_THREADS = 256, SC_ITEMS = 8;
+__global__ void __launch_bounds__(SC_THREADS) scan_counts_kernel(const uint32_t* __restrict__ counts,
+                                                                 unsigned long long n, unsigned long long* out_off,
+                                                                 unsigned long long* carry, uint64_t* status,
+                                                                 DevCounters* ctr) {
+  __shared__ unsigned long long s_t, s_base;
+  __shared__ uint32_t s_wsum[SC_THREADS / 32 + 1];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  constexpr unsigned long long TILE = (unsigned long long)SC_THREADS * SC_ITEMS;
+  const unsigned long long n_tiles = (n + TILE - 1) / TILE;
+  const unsigned long long carry_in = *carry;
+  while (true) {
+    if (tid == 0) s_t = atomicAdd(&ctr->aux[1], 1ull);
+    __syncthreads();
+    const unsigned long long t = s_t;
+    if (t >= n_tiles) break;
+    const unsigned long long i0 = t * TILE + (unsigned long long)tid * SC_ITEMS;
+    uint32_t x[SC_ITEMS], sum = 0;
+#pragma unroll
+    for (int j = 0; j < SC_ITEMS; ++j) {
+      x[j] = (i0 + j < n) ? counts[i0 + j] : 0;
+      sum += x[j];
+    }
+    uint32_t total;
+    uint32_t off = block_excl_scan<SC_THREADS>(sum, s_wsum, &total);
+    if (warp == 0) {
+      const unsigned long long excl = lookback_exclusive(status, t, total);
+      if (lane == 0) s_base = excl;
+    }
+    __syncthreads();
+    unsigned long long o = carry_in + s_base + off;
+#pragma unroll
+    for (int j = 0; j < SC_ITEMS; ++j) {
+      if (i0 + j < n) out_off[i0 + j] = o;
+      o += x[j];
+    }
+    if (t == n_tiles - 1 && tid == SC_THREADS - 1) {
+      // the last thread of the last tile holds the grand total
+      out_off[n] = o;
+      ctr->total = o;
+      __threadfence();
+      *carry = o;
+    }
+    __syncthreads();
+  }
+}
+
+// One warp per query: staging row (hop bytes in id order) -> packed (id, hop) row.
+__global__ void __launch_bounds__(256) khop_emit_kernel(const uint8_t* __restrict__ stage, uint32_t WC,
+                                                        unsigned long long q_begin, unsigned long long q_end,
+                                                        const uint32_t* __restrict__ qwin,
+                                                        const unsigned long long* __restrict__ out_off,
+                                                        uint32_t* out_ids, uint8_t* out_hop, unsigned long long cap) {
+  const int lane = threadIdx.x & 31;
+  const unsigned long long warp = (blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x) >> 5;
+  const unsigned long long nwarps = ((unsigned long long)gridDim.x * blockDim.x) >> 5;
+  for (unsigned long long q = q_begin + warp; q < q_end; q += nwarps) {
+    const uint32_t lo = qwin[2 * q], wn = qwin[2 * q + 1];
+    const uint8_t* st = stage + (size_t)(q - q_begin) * WC;
+    unsigned long long run = out_off[q];
+    for (uint32_t v0 = 0; v0 < wn; v0 += 128) {
+      const uint32_t v = v0 + lane * 4;
+      const uint32_t x = (v < wn) ? *reinterpret_cast<const uint32_t*>(st + v) : 0u;
+      uint32_t c = 0;
+#pragma unroll
+      for (int bb = 0; bb < 4; ++bb) {
+        const uint32_t h = (x >> (8 * bb)) & 255u;
+        c += (h != 0 && h != 255);
+      }
+      const uint32_t inc = warp_incl_scan_u32(c);
+      unsigned long long pos = run + inc - c;
+#pragma unroll
+      for (int bb = 0; bb < 4; ++bb) {
+        const uint32_t h = (x >> (8 * bb)) & 255u;
+        if (h != 0 && h != 255) {
+          if (pos < cap) {
+            out_ids[pos] = lo + v + bb;
+            out_hop[pos] = (uint8_t)h;
+          }
+          ++pos;
+        }
+      }
+      run += __shfl_sync(FULL, inc, 31);
+    }
   }
 }
 
@@ -447,6 +649,7 @@ __global__ void __launch_bounds__(KG_THREADS) khop_global_kernel(const KhopArgs 
   rows = warp_sum_u64(rows);
   if (lane == 0 && rows) {
     atomicAdd(&a.ctr->edges, te);
+    atomicAdd(&a.ctr->aux[0], te);   // this kernel is top-down only: read == traversed
     atomicAdd(&a.ctr->rows, rows);
   }
 }
@@ -512,7 +715,10 @@ __global__ void __launch_bounds__(ADJ_THREADS) adjacency_kernel(const uint32_t* 
     }
   }
   te = warp_sum_u64(te);
-  if (lane == 0 && te) atomicAdd(&ctr->edges, te);
+  if (lane == 0 && te) {
+    atomicAdd(&ctr->edges, te);
+    atomicAdd(&ctr->aux[0], te);
+  }
 }
 
 __global__ void entry_flags_kernel(const uint32_t* __restrict__ bits, uint32_t V, unsigned long long n,
@@ -570,13 +776,62 @@ static int32_t run_khop(CallCtx* c, dmg_graph* g, int mode, int k, int exclude, 
   a.ctr = c->d_counters;
   const uint32_t maxp = std::max<uint32_t>(g->info.max_part_vertices, 1);
   a.win_cap = (maxp + 127u) & ~127u;
+  a.und_ptr = g->d_und_ptr;
+  a.und_idx = g->d_und_idx;
+  a.q_begin = 0;
+  a.q_end = nq;
+  a.stage = nullptr;
+  a.counts = nullptr;
+  a.qwin = nullptr;
   if (maxp <= SMALL_WINDOW_MAX) {
-    const size_t smem = (size_t)a.win_cap + a.win_cap / 8 + 4 * (size_t)a.win_cap;
+    const uint32_t WC = a.win_cap;
+    const size_t smem = (size_t)WC + WC / 4 + 6 * (size_t)WC;
+    static std::atomic<size_t> smem_set{0};
+    if (smem > 48 * 1024 && smem_set.load() < smem) {
+      DMG_CUDA(cudaFuncSetAttribute(khop_small_kernel<KS_THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    (int)smem));
+      smem_set.store(smem);
+    }
     int occ = 0;
     DMG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, khop_small_kernel<KS_THREADS>, KS_THREADS, smem));
-    const uint64_t grid = std::min<uint64_t>(nq, (uint64_t)e->sm_count * std::max(occ, 1));
-    LaunchScope ls(c, K_KHOP_SMALL);
-    khop_small_kernel<KS_THREADS><<<(unsigned)grid, KS_THREADS, smem, c->stream>>>(a);
+    // staging rows (one hop byte per vertex of the project) for a chunk of queries
+    const uint64_t stage_budget = std::max<uint64_t>(std::min<uint64_t>(e->scratch_budget, 2ull << 30), WC);
+    const uint64_t chunk = std::max<uint64_t>(1, std::min<uint64_t>(nq, stage_budget / WC));
+    DMG_TRY(c->scratch.reserve(chunk * WC));
+    DMG_TRY(c->tmp0.reserve(nq * 4));        // row sizes
+    DMG_TRY(c->tmp1.reserve(nq * 8));        // (lo, wn) per query
+    const uint64_t scan_tiles = (chunk + SC_THREADS * SC_ITEMS - 1) / (SC_THREADS * SC_ITEMS);
+    DMG_TRY(c->status.reserve(scan_tiles * sizeof(uint64_t)));
+    a.stage = c->scratch.as<uint8_t>();
+    a.counts = c->tmp0.as<uint32_t>();
+    a.qwin = c->tmp1.as<uint32_t>();
+    unsigned long long* carry = &c->d_counters->aux[2];
+    for (uint64_t q0 = 0; q0 < nq; q0 += chunk) {
+      const uint64_t q1 = std::min<uint64_t>(nq, q0 + chunk);
+      a.q_begin = q0;
+      a.q_end = q1;
+      DMG_CUDA(cudaMemsetAsync(&c->d_counters->ticket, 0, 8, c->stream));
+      DMG_CUDA(cudaMemsetAsync(&c->d_counters->aux[1], 0, 8, c->stream));
+      DMG_CUDA(cudaMemsetAsync(c->status.p, 0, scan_tiles * sizeof(uint64_t), c->stream));
+      const uint64_t grid = std::min<uint64_t>(q1 - q0, (uint64_t)e->sm_count * std::max(occ, 1));
+      {
+        LaunchScope ls(c, K_KHOP_SMALL);
+        khop_small_kernel<KS_THREADS><<<(unsigned)grid, KS_THREADS, smem, c->stream>>>(a);
+      }
+      {
+        LaunchScope ls(c, K_SCAN_COUNTS);
+        const uint64_t tiles = (q1 - q0 + SC_THREADS * SC_ITEMS - 1) / (SC_THREADS * SC_ITEMS);
+        scan_counts_kernel<<<(unsigned)std::min<uint64_t>(tiles, (uint64_t)e->sm_count * 4), SC_THREADS, 0, c->stream>>>(
+            a.counts + q0, q1 - q0, a.out_off + q0, carry, c->status.as<uint64_t>(), c->d_counters);
+      }
+      {
+        LaunchScope ls(c, K_KHOP_EMIT);
+        const uint64_t warps = q1 - q0;
+        const uint64_t blocks = std::min<uint64_t>((warps + 7) / 8, (uint64_t)e->sm_count * 16);
+        khop_emit_kernel<<<(unsigned)blocks, 256, 0, c->stream>>>(a.stage, WC, q0, q1, a.qwin, a.out_off, a.out_ids,
+                                                                 a.out_hop, a.cap);
+      }
+    }
   } else {
     const size_t seen_words = (((size_t)maxp + 31) / 32 + 3) & ~size_t(3);
     const size_t hop_bytes = ((size_t)maxp + 15) & ~size_t(15);
@@ -646,6 +901,7 @@ int32_t dmg_neighbors_batch_dev(dmg_graph* g, int32_t mode, int32_t k, int32_t e
   DMG_TRY(c->finish());
   *needed = c->h_counters->total;
   c->stats.edges_traversed = c->h_counters->edges;
+  c->stats.edges_read = c->h_counters->aux[0];
   c->stats.rows_expanded = c->h_counters->rows;
   c->stats.results = c->h_counters->total;
   publish_stats(c->stats);
@@ -702,6 +958,7 @@ int32_t dmg_neighbors_batch(dmg_graph* g, int32_t mode, int32_t k, int32_t exclu
     c->stats.d2h_bytes += total * 5;
   }
   c->stats.edges_traversed = c->h_counters->edges;
+  c->stats.edges_read = c->h_counters->aux[0];
   c->stats.rows_expanded = c->h_counters->rows;
   c->stats.results = total;
   DMG_TRY(c->finish());
@@ -768,6 +1025,7 @@ int32_t dmg_adjacency_batch(dmg_graph* g, int32_t dir, uint64_t n, const uint32_
     c->stats.d2h_bytes += total * 4;
   }
   c->stats.edges_traversed = c->h_counters->edges;
+  c->stats.edges_read = c->h_counters->aux[0];
   c->stats.rows_expanded = n;
   c->stats.results = total;
   DMG_TRY(c->finish());

@@ -43,7 +43,8 @@ class GraphInfo(C.Structure):
 
 
 class CallStats(C.Structure):
-    _fields_ = [("kernel_launches", C.c_uint64), ("edges_traversed", C.c_uint64), ("rows_expanded", C.c_uint64),
+    _fields_ = [("kernel_launches", C.c_uint64), ("edges_traversed", C.c_uint64), ("edges_read", C.c_uint64),
+                ("rows_expanded", C.c_uint64),
                 ("results", C.c_uint64), ("h2d_bytes", C.c_uint64), ("d2h_bytes", C.c_uint64),
                 ("device_ms", C.c_float), ("reserved", C.c_float)]
 

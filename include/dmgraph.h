@@ -113,7 +113,10 @@ typedef struct dmg_graph_info {
 /* Counters of the calling thread's most recent query call on this engine. */
 typedef struct dmg_call_stats {
   uint64_t kernel_launches;  /* our kernels launched by the call */
-  uint64_t edges_traversed;  /* adjacency entries read (TE of SURVEY.md 8d) */
+  uint64_t edges_traversed;  /* TE of SURVEY.md 8d: sum of deg_mode(u) over every expanded frontier
+                                vertex -- the work a top-down traversal does, whatever we did */
+  uint64_t edges_read;       /* adjacency entries this call actually loaded (bottom-up levels
+                                stop at the first frontier member, so this can be far smaller) */
   uint64_t rows_expanded;    /* vertices whose rows were read */
   uint64_t results;          /* entries written */
   uint64_t h2d_bytes;

@@ -2,50 +2,28 @@
 String<->id map (the host owns `nodes`), enforces Preconditions.requireNonBlank, lower-cases
 queries, and sends every read to the device through dmgraph (include/dmgraph.h).  It computes
 no graph result itself."""
-import numpy as np
-
 import dmgraph
-from dmgraph import synth
 
-_WS = set(range(9, 14)) | set(range(28, 33))
-
-
-def _blank(s):
-    return s is None or all(ord(c) in _WS for c in s)
+from dmgraph.host import ProjectGraph
 
 
 class EngineGraph:
     def __init__(self, engine):
         self.engine = engine
-        self.names, self.ids, self.files = [], {}, []
-        self.src, self.dst, self.entry = [], [], []
+        self.pg = ProjectGraph()          # C++ host mirror: String<->id map, build rules (PG:160-197)
         self.methods = {}
         self._g = None
 
-    # -- build: the host-side half of PG:160-197 (the device applies the same rules again) -----
     def add_node(self, i, f):
-        if _blank(i) or _blank(f):
-            raise ValueError("IllegalArgumentException")
-        if i in self.ids:
-            self.files[self.ids[i]] = f
-        else:
-            self.ids[i] = len(self.names)
-            self.names.append(i)
-            self.files.append(f)
+        self.pg.add_node(i, f)
         self._drop()
 
     def add_dependency(self, a, b):
-        if _blank(a) or _blank(b):
-            raise ValueError("IllegalArgumentException")
-        # unknown endpoints are sent as an out-of-range id: the engine drops the edge (PG:179-181)
-        self.src.append(self.ids.get(a, 0xFFFFFFFF))
-        self.dst.append(self.ids.get(b, 0xFFFFFFFF))
+        self.pg.add_dependency(a, b)
         self._drop()
 
     def mark_as_entry_point(self, i):
-        if _blank(i):
-            raise ValueError("IllegalArgumentException")
-        self.entry.append(self.ids.get(i, 0xFFFFFFFF))
+        self.pg.mark_as_entry_point(i)
         self._drop()
 
     def _drop(self):
@@ -55,26 +33,29 @@ class EngineGraph:
 
     def graph(self):
         if self._g is None:
-            off, arena = synth.pack_names(self.names)
-            self._g = dmgraph.Graph(self.engine, len(self.names), self.src, self.dst, self.entry,
-                                    name_off=off, name_bytes=arena)
+            self._g = self.pg.publish(self.engine)
         return self._g
 
+    @property
+    def names(self):
+        return _Names(self.pg)
+
     def _id(self, name):
-        return 0xFFFFFFFF if name is None else self.ids.get(name, 0xFFFFFFFF)
+        v = self.pg.id_of(name)
+        return 0xFFFFFFFF if v < 0 else v
 
     # -- reads ------------------------------------------------------------------------------
     def node_count(self):
         return self.graph().info["n_vertices"]
 
     def contains(self, i):
-        return i in self.ids
+        return self.pg.contains(i)
 
     def identifiers(self):
-        return list(self.names)
+        return self.pg.identifiers()
 
     def source_file(self, i):
-        return self.files[self.ids[i]] if i in self.ids else None
+        return self.pg.source_file(i)
 
     def entry_points(self):
         return [self.names[v] for v in self.graph().entry_points()]
@@ -116,7 +97,7 @@ class EngineGraph:
 
     def resolve_class_name(self, name):
         """GQS:423-456: exact id on the host map, then the two ordered device scans."""
-        if name in self.ids:
+        if self.pg.contains(name):
             return name
         q = name.lower().encode("utf-8")
         for kind in (dmgraph.SEARCH_SIMPLE_EQ_FIRST, dmgraph.SEARCH_CONTAINS_FIRST):
@@ -124,3 +105,11 @@ class EngineGraph:
             if ids.size:
                 return self.names[ids[0]]
         return None
+
+
+class _Names:
+    def __init__(self, pg):
+        self.pg = pg
+
+    def __getitem__(self, v):
+        return self.pg.name_of(int(v))

@@ -268,3 +268,30 @@ def test_config2_full_size_properties(engine):
     assert np.array_equal(ids[:int(woff[-1])], wids) and np.array_equal(hop[:int(woff[-1])], whop)
     assert st["results"] == int(off[-1])
     g.release()
+
+
+# ---- GraphService lifecycle (GS:55-122) --------------------------------------------------------
+def test_graph_service_put_reload_swap(engine):
+    from dmgraph.host import GraphService, ProjectGraph
+    svc = GraphService(engine)
+    a = ProjectGraph()
+    a.add_node("co.fanki.A", "A.java")
+    a.add_node("co.fanki.B", "B.java")
+    a.add_dependency("co.fanki.A", "co.fanki.B")
+    svc.put("p1", "order-service", a)
+    assert svc.size() == 1 and svc.get_graph("nope") is None and svc.get_graph_by_project_name("x") is None
+    g1 = svc.get_graph_by_project_name("order-service")
+    assert g1.adjacency_batch(dmgraph.OUT, [0])[1].tolist() == [1]
+    # reload from graph_data JSON swaps the whole graph; the reader's retained handle stays valid
+    doc = '{"nodes":{"co.fanki.B":{"sourceFile":"B.java"},"co.fanki.A":{"sourceFile":"A.java"}},' \
+          '"edges":{"co.fanki.B":["co.fanki.A","co.fanki.Gone"]},"entryPoints":["co.fanki.B"]}'
+    assert svc.load_json("p1", "order-service", doc)
+    g2 = svc.get_graph("p1")
+    assert g2.info["dropped_edges"] == 1 and g2.adjacency_batch(dmgraph.OUT, [0])[1].tolist() == [1]
+    assert g2.entry_points().tolist() == [0]
+    assert g1.adjacency_batch(dmgraph.IN, [1])[1].tolist() == [0]      # old graph still alive
+    assert not svc.load_json("p2", "broken", '{"nodes":')               # logged-and-skipped analogue
+    assert svc.size() == 1
+    g1.release()
+    g2.release()
+    svc.close()
