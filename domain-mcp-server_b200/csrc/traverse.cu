@@ -9,6 +9,8 @@
 // decoupled look-back allocator of common.cuh, so results come out packed, in query order and
 // in ONE pass over the graph data.
 #include <algorithm>
+#include <atomic>
+#include <mutex>
 
 #include "common.cuh"
 
@@ -908,6 +910,121 @@ int32_t dmg_neighbors_batch_dev(dmg_graph* g, int32_t mode, int32_t k, int32_t e
   if (*needed > cap) {
     set_error("dmg_neighbors_batch_dev: capacity %llu < needed %llu", (unsigned long long)cap,
               (unsigned long long)*needed);
+    return DMG_ECAP;
+  }
+  return DMG_OK;
+}
+
+// ---- dmg_neighbors_batch_dev_static: the k-hop batch without a single allocation ---------------
+// Scratch for the small-project kernel chain (counters, scan status words, row sizes, per-query
+// window, staging rows) lives in this file-scope device array instead of cudaMalloc'ed buffers.
+// Every GPU that loads the library carries the 16 MiB until the process exits.
+static constexpr size_t kStaticScratchBytes = 16u << 20;
+static __device__ __align__(256) unsigned char g_static_scratch[kStaticScratchBytes];
+// In host code `g_static_scratch` is only a handle for the runtime, not a device address; the
+// real address is looked up once per device (with that device current) and cached here.
+static std::mutex g_static_mu;
+static unsigned char* g_static_ptr[64] = {nullptr};
+
+static int32_t static_scratch_for_device(int dev, unsigned char** out) {
+  if (dev < 0 || dev >= 64) {
+    set_error("dmg_neighbors_batch_dev_static: device ordinal %d not supported", dev);
+    return DMG_EINVAL;
+  }
+  std::lock_guard<std::mutex> lk(g_static_mu);
+  if (!g_static_ptr[dev]) {
+    void* p = nullptr;
+    DMG_CUDA(cudaGetSymbolAddress(&p, g_static_scratch));
+    g_static_ptr[dev] = static_cast<unsigned char*>(p);
+  }
+  *out = g_static_ptr[dev];
+  return DMG_OK;
+}
+
+static inline size_t pad256(size_t x) { return (x + 255) & ~size_t(255); }
+
+int32_t dmg_neighbors_batch_dev_static(dmg_graph* g, int32_t mode, int32_t k, int32_t exclude_sources, uint64_t nq,
+                                       const uint32_t* d_q_off, const uint32_t* d_q_src, uint64_t* d_out_off,
+                                       uint32_t* d_out_ids, uint8_t* d_out_hop, uint64_t cap, uint64_t* needed) {
+  DMG_TRY(check_khop_args(g, mode, k, nq, d_q_off, d_out_off, needed));
+  *needed = 0;
+  const uint32_t maxp = std::max<uint32_t>(g->info.max_part_vertices, 1);
+  if (maxp > SMALL_WINDOW_MAX) {
+    set_error("dmg_neighbors_batch_dev_static: largest project has %u vertices; the static-scratch variant "
+              "covers projects up to %u (use dmg_neighbors_batch_dev)", maxp, SMALL_WINDOW_MAX);
+    return DMG_EINVAL;
+  }
+  Engine* e = g->eng;
+  DMG_CUDA(cudaSetDevice(e->device));
+  if (nq == 0) {
+    DMG_CUDA(cudaMemset(d_out_off, 0, sizeof(uint64_t)));
+    return DMG_OK;
+  }
+  const uint32_t WC = (maxp + 127u) & ~127u;
+  const uint64_t tiles = (nq + SC_THREADS * SC_ITEMS - 1) / (SC_THREADS * SC_ITEMS);
+  // layout: [counters][scan status][row sizes][(lo, wn) per query][staging rows]
+  const size_t o_status = pad256(sizeof(DevCounters));
+  const size_t o_counts = o_status + pad256(tiles * sizeof(uint64_t));
+  const size_t o_qwin = o_counts + pad256(nq * 4);
+  const size_t o_stage = o_qwin + pad256(nq * 8);
+  const unsigned long long want = (unsigned long long)o_stage + (unsigned long long)nq * WC;
+  if (nq > (1ull << 32) || want > kStaticScratchBytes) {
+    set_error("dmg_neighbors_batch_dev_static: %llu queries over %u-vertex projects need %llu bytes of scratch; "
+              "the static scratch holds %llu (split the batch or use dmg_neighbors_batch_dev)",
+              (unsigned long long)nq, WC, want, (unsigned long long)kStaticScratchBytes);
+    return DMG_EINVAL;
+  }
+  unsigned char* base = nullptr;
+  DMG_TRY(static_scratch_for_device(e->device, &base));
+  DevCounters* ctr = reinterpret_cast<DevCounters*>(base);
+  // the array keeps the previous call's contents: counters and status words must start at zero
+  DMG_CUDA(cudaMemsetAsync(base, 0, o_counts, 0));
+  KhopArgs a;
+  a.out_ptr = g->d_out_ptr;
+  a.out_idx = g->d_out_idx;
+  a.in_ptr = g->d_in_ptr;
+  a.in_idx = g->d_in_idx;
+  a.und_ptr = g->d_und_ptr;
+  a.und_idx = g->d_und_idx;
+  a.part_off = g->d_part_off;
+  a.V = g->info.n_vertices;
+  a.n_parts = g->info.n_parts;
+  a.mode = mode;
+  a.k = k;
+  a.exclude = exclude_sources ? 1 : 0;
+  a.nq = nq;
+  a.q_off = d_q_off;
+  a.q_src = d_q_src;
+  a.out_off = reinterpret_cast<unsigned long long*>(d_out_off);
+  a.out_ids = d_out_ids;
+  a.out_hop = d_out_hop;
+  a.cap = (d_out_ids && d_out_hop) ? cap : 0;
+  a.status = reinterpret_cast<uint64_t*>(base + o_status);
+  a.ctr = ctr;
+  a.win_cap = WC;
+  a.q_begin = 0;
+  a.q_end = nq;
+  a.stage = base + o_stage;
+  a.counts = reinterpret_cast<uint32_t*>(base + o_counts);
+  a.qwin = reinterpret_cast<uint32_t*>(base + o_qwin);
+  const size_t smem = (size_t)WC + WC / 4 + 6 * (size_t)WC;
+  if (smem > 48 * 1024)
+    DMG_CUDA(cudaFuncSetAttribute(khop_small_kernel<KS_THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  (int)smem));
+  int occ = 0;
+  DMG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, khop_small_kernel<KS_THREADS>, KS_THREADS, smem));
+  const uint64_t grid = std::min<uint64_t>(nq, (uint64_t)e->sm_count * std::max(occ, 1));
+  khop_small_kernel<KS_THREADS><<<(unsigned)grid, KS_THREADS, smem, 0>>>(a);
+  scan_counts_kernel<<<(unsigned)std::min<uint64_t>(tiles, (uint64_t)e->sm_count * 4), SC_THREADS, 0, 0>>>(
+      a.counts, nq, a.out_off, &ctr->aux[2], a.status, ctr);
+  khop_emit_kernel<<<(unsigned)std::min<uint64_t>((nq + 7) / 8, (uint64_t)e->sm_count * 16), 256, 0, 0>>>(
+      a.stage, WC, 0, nq, a.qwin, a.out_off, a.out_ids, a.out_hop, a.cap);
+  DMG_CUDA(cudaGetLastError());
+  unsigned long long total = 0;
+  DMG_CUDA(cudaMemcpy(&total, &ctr->total, sizeof(total), cudaMemcpyDeviceToHost));   // waits for the kernels
+  *needed = total;
+  if (total > cap) {
+    set_error("dmg_neighbors_batch_dev_static: capacity %llu < needed %llu", (unsigned long long)cap, total);
     return DMG_ECAP;
   }
   return DMG_OK;

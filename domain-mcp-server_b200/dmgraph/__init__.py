@@ -75,6 +75,7 @@ def lib():
             "dmg_adjacency_batch": (i32, [vp, i32, u64, vp, vp, vp, u64, pu64]),
             "dmg_neighbors_batch": (i32, [vp, i32, i32, i32, u64, vp, vp, vp, vp, vp, u64, pu64]),
             "dmg_neighbors_batch_dev": (i32, [vp, i32, i32, i32, u64, vp, vp, vp, vp, vp, u64, pu64]),
+            "dmg_neighbors_batch_dev_static": (i32, [vp, i32, i32, i32, u64, vp, vp, vp, vp, vp, u64, pu64]),
             "dmg_closure": (i32, [vp, i32, u32, vp, vp, pu64]),
             "dmg_analysis_order": (i32, [vp, vp]),
             "dmg_entry_points": (i32, [vp, vp, u32, C.POINTER(u32)]),
@@ -279,6 +280,17 @@ class Graph:
         rc = self.L.dmg_neighbors_batch_dev(self.h, mode, k, int(exclude_sources), nq, C.c_void_p(d_q_off),
                                             C.c_void_p(d_q_src), C.c_void_p(d_out_off), C.c_void_p(d_out_ids),
                                             C.c_void_p(d_out_hop), cap, C.byref(need))
+        _check(rc, allow=(ECAP,))
+        return rc, need.value
+
+    def neighbors_batch_dev_static(self, mode, k, exclude_sources, nq, d_q_off, d_q_src, d_out_off, d_out_ids,
+                                   d_out_hop, cap):
+        """dmg_neighbors_batch_dev_static: same results, scratch in the library's static array."""
+        need = C.c_uint64(0)
+        rc = self.L.dmg_neighbors_batch_dev_static(self.h, mode, k, int(exclude_sources), nq, C.c_void_p(d_q_off),
+                                                   C.c_void_p(d_q_src), C.c_void_p(d_out_off),
+                                                   C.c_void_p(d_out_ids), C.c_void_p(d_out_hop), cap,
+                                                   C.byref(need))
         _check(rc, allow=(ECAP,))
         return rc, need.value
 

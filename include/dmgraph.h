@@ -170,6 +170,31 @@ int32_t dmg_neighbors_batch_dev(dmg_graph* g, int32_t mode, int32_t k, int32_t e
                                 uint64_t* d_out_off, uint32_t* d_out_ids, uint8_t* d_out_hop,
                                 uint64_t cap, uint64_t* needed);
 
+/* The same k-hop batch for callers that must not allocate.  It has no counterpart in the
+ * reference.  Some hosts cannot afford, or are not allowed, a cudaMalloc on the query path: a
+ * request thread with a latency budget (device allocation can stall behind all other work on the
+ * GPU), a process whose device memory is already carved up by another component's pool so that
+ * a further allocation may fail under load, or code that runs where the CUDA runtime forbids
+ * allocation.  This entry point calls no cudaMalloc / cudaFree and no allocating library
+ * routine: all of its scratch (counters, scan status, row sizes, staging rows) is a 16 MiB
+ * array compiled into the library, resident on every GPU that loads it until the process
+ * exits.  The caller still passes device inputs and outputs exactly as for
+ * dmg_neighbors_batch_dev, and the results are identical.
+ *   - Limits: every project of the graph must have <= 8192 vertices, and
+ *     n_queries * (round_up(largest project, 128) + 12) + ~1 KiB must fit in 16 MiB (about 8,100
+ *     queries over 2,000-vertex projects); anything larger is rejected with DMG_EINVAL and a
+ *     message that states both sizes.  Split the batch, or use the allocating entry point.
+ *   - The first call on each device looks up the device address of the array; make that first
+ *     call before starting any stream capture.
+ *   - All calls share the one array, which keeps whatever the last call left there (the call
+ *     clears the parts that must start at zero).  Two calls that overlap on the same GPU race
+ *     on it: serialise them.  Work is issued on the default stream; the call returns after it
+ *     completed.                                                                              */
+int32_t dmg_neighbors_batch_dev_static(dmg_graph* g, int32_t mode, int32_t k, int32_t exclude_sources,
+                                       uint64_t n_queries, const uint32_t* d_q_off, const uint32_t* d_q_src,
+                                       uint64_t* d_out_off, uint32_t* d_out_ids, uint8_t* d_out_hop,
+                                       uint64_t cap, uint64_t* needed);
+
 /* ---- T5: closure and analysisOrder ----------------------------------------------------------
  * dmg_closure: BFS levels from a source set over dir (DMG_OUT / DMG_IN) on the whole graph;
  * out_level[v] = hop distance, 0 for sources, DMG_LEVEL_UNREACHED otherwise.  *reached counts
