@@ -104,18 +104,17 @@ __device__ __forceinline__ uint32_t block_excl_scan(uint32_t v, uint32_t* s_wsum
 // ---------------------------------------------------------------------------------------------
 constexpr uint32_t BU_ALPHA = 24;
 
-template <int THREADS>
+template <int THREADS, int WC>
 __global__ void __launch_bounds__(THREADS) khop_small_kernel(const KhopArgs a) {
   extern __shared__ __align__(16) unsigned char smem[];
-  const uint32_t WC = a.win_cap;
-  uint8_t* hop8 = smem;
-  uint32_t* seen = reinterpret_cast<uint32_t*>(smem + WC);
-  uint32_t* srcb = reinterpret_cast<uint32_t*>(smem + WC + WC / 8);
-  uint16_t* queue = reinterpret_cast<uint16_t*>(smem + WC + WC / 4);
-  uint16_t* ulist = queue + 2 * WC;
+  uint8_t* const hop8 = smem;                                             // WC bytes
+  uint32_t* const hop32 = reinterpret_cast<uint32_t*>(smem);
+  uint32_t* const srcb = reinterpret_cast<uint32_t*>(smem + WC);          // WC/8 bytes
+  uint16_t* const list = reinterpret_cast<uint16_t*>(smem + WC + WC / 8); // WC u16: frontier or unseen list
   __shared__ unsigned long long s_q;
-  __shared__ uint32_t s_lo, s_hi, s_tail, s_nu, s_cnt;
+  __shared__ uint32_t s_lo, s_hi, s_n, s_cnt;
   __shared__ uint32_t s_wsum[THREADS / 32 + 1];
+  __shared__ uint32_t s_red[3][THREADS / 32];
   __shared__ uint32_t s_end[THREADS], s_adj[THREADS];
   constexpr int NW = THREADS / 32, NG = THREADS / 8;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -139,67 +138,106 @@ __global__ void __launch_bounds__(THREADS) khop_small_kernel(const KhopArgs a) {
       find_window(a, qb, qe, &lo, &hi);
       s_lo = lo;
       s_hi = hi;
-      s_tail = 0;
+      s_n = 0;
       s_cnt = 0;
     }
     __syncthreads();
     const uint32_t lo = s_lo, hi = s_hi, wn = hi - lo;
     const uint32_t nw4 = (wn + 3) >> 2, nw32 = (wn + 31) >> 5;
-    for (uint32_t i = tid; i < nw4; i += THREADS) reinterpret_cast<uint32_t*>(hop8)[i] = 0;
-    for (uint32_t i = tid; i < nw32; i += THREADS) {
-      seen[i] = 0;
-      srcb[i] = 0;
-    }
+    for (uint32_t i = tid; i < nw4; i += THREADS) hop32[i] = 0;
+    for (uint32_t i = tid; i < nw32; i += THREADS) srcb[i] = 0;
     __syncthreads();
-    // L0: distinct sources inside the project
+    // L0: distinct sources inside the project -> list
     for (uint32_t i = qb + tid; i < qe; i += THREADS) {
       const uint32_t s = a.q_src[i];
       if (s >= lo && s < hi) {
         const uint32_t v = s - lo, bit = 1u << (v & 31);
         if (!(atomicOr(&srcb[v >> 5], bit) & bit)) {
-          queue[atomicAdd(&s_tail, 1u)] = (uint16_t)v;
-          if (a.exclude) {
-            hop8[v] = 255;
-            atomicOr(&seen[v >> 5], bit);
-          }
+          list[atomicAdd(&s_n, 1u)] = (uint16_t)v;
+          if (a.exclude) hop8[v] = 255;
         }
       }
     }
     __syncthreads();
-    const uint32_t ns = s_tail;
-    uint32_t head = 0, tail = ns;
-    __syncthreads();   // nobody appends before everybody has read s_tail
+    const uint32_t ns = s_n;
 
-    for (int lvl = 1; lvl <= a.k && head < tail; ++lvl) {
-      const bool last = (lvl == a.k);
-      // m_f = adjacency entries of the frontier's rows (this is also TE of SURVEY.md 8d)
-      uint32_t mf = 0;
-      for (uint32_t i = head + tid; i < tail; i += THREADS) {
-        const uint32_t u = lo + queue[i];
-        mf += fptr[u + 1] - fptr[u];
+    for (int lvl = 1; lvl <= a.k; ++lvl) {
+      // ---- pass A: frontier size nf, its adjacency entries m_f (TE of SURVEY.md 8d), unseen count
+      const uint32_t want = (uint32_t)(lvl - 1);
+      uint32_t mf = 0, nf = 0, nun = 0;
+      if (lvl == 1) {
+        for (uint32_t i = tid; i < ns; i += THREADS) {
+          const uint32_t u = lo + list[i];
+          mf += fptr[u + 1] - fptr[u];
+        }
+      } else {
+        for (uint32_t w = tid; w < nw4; w += THREADS) {
+          const uint32_t x = hop32[w];
+#pragma unroll
+          for (int bb = 0; bb < 4; ++bb) {
+            const uint32_t h = (x >> (8 * bb)) & 255u, v = w * 4 + bb;
+            if (h == want) {
+              const uint32_t u = lo + v;
+              mf += fptr[u + 1] - fptr[u];
+              ++nf;
+            }
+            nun += (h == 0 && v < wn);
+          }
+        }
       }
       mf = warp_sum_u32(mf);
-      if (lane == 0) s_wsum[warp] = mf;
-      if (tid == 0) s_nu = 0;
+      nf = warp_sum_u32(nf);
+      nun = warp_sum_u32(nun);
+      if (lane == 0) {
+        s_red[0][warp] = mf;
+        s_red[1][warp] = nf;
+        s_red[2][warp] = nun;
+      }
       __syncthreads();
-      mf = 0;
+      mf = nf = nun = 0;
 #pragma unroll
-      for (int w = 0; w < NW; ++w) mf += s_wsum[w];
-      const uint32_t marked = (a.exclude ? ns : 0u) + (tail - ns);
-      const uint32_t n_unseen = wn - min(wn, marked);
+      for (int w = 0; w < NW; ++w) {
+        mf += s_red[0][w];
+        nf += s_red[1][w];
+        nun += s_red[2][w];
+      }
+      if (lvl == 1) {
+        nf = ns;
+        nun = wn - (a.exclude ? ns : 0u);
+      }
+      if (tid == 0) s_n = 0;
+      __syncthreads();   // s_red may be rewritten by the next level; s_n reset is visible
+      if (nf == 0) break;
       if (tid == 0) {
         te += mf;
-        rows += tail - head;
+        rows += nf;
       }
-      const bool bottom_up = mf > BU_ALPHA * n_unseen;
-      __syncthreads();   // s_wsum is reused by block_excl_scan below
+      const bool bottom_up = mf > BU_ALPHA * nun;
 
       if (!bottom_up) {
-        for (uint32_t c0 = head; c0 < tail; c0 += THREADS) {
+        if (lvl > 1) {   // frontier = vertices found by the previous level -> list
+          for (uint32_t w0 = 0; w0 < nw4; w0 += THREADS) {
+            const uint32_t w = w0 + tid;
+            const uint32_t x = (w < nw4) ? hop32[w] : 0u;
+#pragma unroll
+            for (int bb = 0; bb < 4; ++bb) {
+              const bool in = ((x >> (8 * bb)) & 255u) == want && w < nw4;
+              const unsigned m = __ballot_sync(FULL, in);
+              if (m) {
+                uint32_t pos = 0;
+                if (lane == 0) pos = atomicAdd(&s_n, (uint32_t)__popc(m));
+                pos = __shfl_sync(FULL, pos, 0);
+                if (in) list[pos + __popc(m & lanemask_lt())] = (uint16_t)(w * 4 + bb);
+              }
+            }
+          }
+          __syncthreads();
+        }
+        for (uint32_t c0 = 0; c0 < nf; c0 += THREADS) {
           const uint32_t i = c0 + tid;
           uint32_t b = 0, n = 0;
-          if (i < tail) {
-            const uint32_t u = lo + queue[i];
+          if (i < nf) {
+            const uint32_t u = lo + list[i];
             b = fptr[u];
             n = fptr[u + 1] - b;
           }
@@ -211,7 +249,7 @@ __global__ void __launch_bounds__(THREADS) khop_small_kernel(const KhopArgs a) {
           const uint32_t Tq = (((T + NW - 1) / NW) + 31u) & ~31u;
           const uint32_t pbeg = warp * Tq, pend = min(T, pbeg + Tq);
           if (pbeg < pend) {
-            uint32_t r = 0;   // first row whose end lies beyond pbeg
+            uint32_t r;   // first row whose end lies beyond pbeg
             {
               uint32_t l = 0, h = THREADS;
               while (l < h) {
@@ -220,45 +258,20 @@ __global__ void __launch_bounds__(THREADS) khop_small_kernel(const KhopArgs a) {
               }
               r = l;
             }
-            for (uint32_t p0 = pbeg; p0 < pend; p0 += 32) {
-              const uint32_t p = p0 + lane;
-              const bool valid = p < pend;
-              bool isnew = false;
-              uint32_t v = 0;
-              if (valid) {
-                while (s_end[r] <= p) ++r;
-                v = fidx[s_adj[r] + p] - lo;
-                ++reads;
-                if (hop8[v] == 0) {
-                  if (last) {
-                    hop8[v] = (uint8_t)lvl;   // same value from every racer
-                  } else {
-                    const uint32_t bit = 1u << (v & 31);
-                    if (!(atomicOr(&seen[v >> 5], bit) & bit)) {
-                      hop8[v] = (uint8_t)lvl;
-                      isnew = true;
-                    }
-                  }
-                }
-              }
-              if (!last) {
-                const unsigned m = __ballot_sync(FULL, isnew);
-                if (m) {
-                  uint32_t pos = 0;
-                  if (lane == 0) pos = atomicAdd(&s_tail, (uint32_t)__popc(m));
-                  pos = __shfl_sync(FULL, pos, 0);
-                  if (isnew) queue[pos + __popc(m & lanemask_lt())] = (uint16_t)v;
-                }
-              }
+            for (uint32_t p = pbeg + lane; p < pend; p += 32) {
+              while (s_end[r] <= p) ++r;
+              const uint32_t v = fidx[s_adj[r] + p] - lo;
+              ++reads;
+              if (hop8[v] == 0) hop8[v] = (uint8_t)lvl;   // same value from every racer
             }
           }
           __syncthreads();   // s_end / s_adj are rewritten by the next chunk
         }
       } else {
-        // unseen vertices -> ulist
+        // unseen vertices -> list
         for (uint32_t w0 = 0; w0 < nw4; w0 += THREADS) {
           const uint32_t w = w0 + tid;
-          const uint32_t x = (w < nw4) ? reinterpret_cast<const uint32_t*>(hop8)[w] : 0xFFFFFFFFu;
+          const uint32_t x = (w < nw4) ? hop32[w] : 0xFFFFFFFFu;
 #pragma unroll
           for (int bb = 0; bb < 4; ++bb) {
             const uint32_t v = w * 4 + bb;
@@ -266,73 +279,73 @@ __global__ void __launch_bounds__(THREADS) khop_small_kernel(const KhopArgs a) {
             const unsigned m = __ballot_sync(FULL, un);
             if (m) {
               uint32_t pos = 0;
-              if (lane == 0) pos = atomicAdd(&s_nu, (uint32_t)__popc(m));
+              if (lane == 0) pos = atomicAdd(&s_n, (uint32_t)__popc(m));
               pos = __shfl_sync(FULL, pos, 0);
-              if (un) ulist[pos + __popc(m & lanemask_lt())] = (uint16_t)v;
+              if (un) list[pos + __popc(m & lanemask_lt())] = (uint16_t)v;
             }
           }
         }
         __syncthreads();
-        const uint32_t nu = s_nu;
-        const uint32_t want = (uint32_t)(lvl - 1);
-        uint32_t i = grp, v = 0, b = 0, n = 0, j0 = 0;
-        bool active = i < nu;
-        if (active) {
-          v = ulist[i];
-          b = rptr[lo + v];
-          n = rptr[lo + v + 1] - b;
-        }
-        while (__any_sync(FULL, active)) {
-          bool hit = false;
-          if (active && j0 + gl < n) {
-            const uint32_t u = ridx[b + j0 + gl] - lo;
-            ++reads;
-            hit = (lvl == 1) ? ((srcb[u >> 5] >> (u & 31)) & 1u) : (hop8[u] == want);
-          }
-          const bool ghit = (__ballot_sync(FULL, hit) & gmask) != 0;
-          bool isnew = false;
-          uint32_t vnew = v;
-          if (active) {
-            if (ghit && gl == 0) {
-              hop8[v] = (uint8_t)lvl;
-              isnew = !last;
-            }
-            if (ghit || j0 + 8 >= n) {
-              i += NG;
-              active = i < nu;
-              j0 = 0;
-              if (active) {
-                v = ulist[i];
-                b = rptr[lo + v];
-                n = rptr[lo + v + 1] - b;
+        const uint32_t nu = s_n;
+        if (2 * nf > wn) {
+          // dense frontier: the first entry of a row is almost surely a member -> one lane per vertex
+          for (uint32_t i = tid; i < nu; i += THREADS) {
+            const uint32_t v = list[i];
+            const uint32_t b = rptr[lo + v], e = rptr[lo + v + 1];
+            for (uint32_t j = b; j < e; ++j) {
+              const uint32_t u = ridx[j] - lo;
+              ++reads;
+              const bool hit = (lvl == 1) ? ((srcb[u >> 5] >> (u & 31)) & 1u) : (hop8[u] == want);
+              if (hit) {
+                hop8[v] = (uint8_t)lvl;
+                break;
               }
-            } else {
-              j0 += 8;
             }
           }
-          if (!last) {
-            const unsigned m = __ballot_sync(FULL, isnew);
-            if (m) {
-              uint32_t pos = 0;
-              if (lane == 0) pos = atomicAdd(&s_tail, (uint32_t)__popc(m));
-              pos = __shfl_sync(FULL, pos, 0);
-              if (isnew) queue[pos + __popc(m & lanemask_lt())] = (uint16_t)vnew;
+        } else {
+          // 8 lanes per unseen vertex, 32-byte chunks of its reverse row, stop at the first member
+          uint32_t i = grp, v = 0, b = 0, n = 0, j0 = 0;
+          bool active = i < nu;
+          if (active) {
+            v = list[i];
+            b = rptr[lo + v];
+            n = rptr[lo + v + 1] - b;
+          }
+          while (__any_sync(FULL, active)) {
+            bool hit = false;
+            if (active && j0 + gl < n) {
+              const uint32_t u = ridx[b + j0 + gl] - lo;
+              ++reads;
+              hit = (lvl == 1) ? ((srcb[u >> 5] >> (u & 31)) & 1u) : (hop8[u] == want);
+            }
+            const bool ghit = (__ballot_sync(FULL, hit) & gmask) != 0;
+            if (active) {
+              if (ghit && gl == 0) hop8[v] = (uint8_t)lvl;
+              if (ghit || j0 + 8 >= n) {
+                i += NG;
+                active = i < nu;
+                j0 = 0;
+                if (active) {
+                  v = list[i];
+                  b = rptr[lo + v];
+                  n = rptr[lo + v + 1] - b;
+                }
+              } else {
+                j0 += 8;
+              }
             }
           }
         }
       }
       __syncthreads();
-      head = tail;
-      tail = s_tail;
-      __syncthreads();
     }
 
     // stage the finished hop array and the row size; khop_emit_kernel writes the packed row
-    uint8_t* st = a.stage + (size_t)(q - a.q_begin) * WC;
+    uint32_t* st = reinterpret_cast<uint32_t*>(a.stage + (size_t)(q - a.q_begin) * a.win_cap);
     uint32_t cnt = 0;
     for (uint32_t i = tid; i < nw4; i += THREADS) {
-      const uint32_t x = reinterpret_cast<const uint32_t*>(hop8)[i];
-      reinterpret_cast<uint32_t*>(st)[i] = x;
+      const uint32_t x = hop32[i];
+      st[i] = x;
 #pragma unroll
       for (int bb = 0; bb < 4; ++bb) {
         const uint32_t h = (x >> (8 * bb)) & 255u;
@@ -359,6 +372,15 @@ __global__ void __launch_bounds__(THREADS) khop_small_kernel(const KhopArgs a) {
     if (reads) atomicAdd(&a.ctr->aux[0], reads);
   }
 }
+
+// picks the instantiation whose compile-time window covers the largest project
+template <class F>
+static inline int32_t with_small_kernel(uint32_t win_cap, F f) {
+  if (win_cap <= 512) return f(khop_small_kernel<128, 512>, 512);
+  if (win_cap <= 2048) return f(khop_small_kernel<128, 2048>, 2048);
+  return f(khop_small_kernel<128, 8192>, 8192);
+}
+static inline size_t small_kernel_smem(uint32_t wc) { return (size_t)wc + wc / 8 + 2 * (size_t)wc; }
 
 // Exclusive scan of the row sizes into out_off (u64), tile by tile with the look-back
 // allocator; *carry (device) holds the running total across query chunks.
@@ -409,42 +431,64 @@ __global__ void __launch_bounds__(SC_THREADS) scan_counts_kernel(const uint32_t*
   }
 }
 
-// One warp per query: staging row (hop bytes in id order) -> packed (id, hop) row.
-__global__ void __launch_bounds__(256) khop_emit_kernel(const uint8_t* __restrict__ stage, uint32_t WC,
-                                                        unsigned long long q_begin, unsigned long long q_end,
-                                                        const uint32_t* __restrict__ qwin,
-                                                        const unsigned long long* __restrict__ out_off,
-                                                        uint32_t* out_ids, uint8_t* out_hop, unsigned long long cap) {
-  const int lane = threadIdx.x & 31;
+// One warp per query: staging row (hop bytes in id order) -> packed (id, hop) row.  A warp step
+// takes 512 vertices (one 16-byte load per lane), compacts them in id order into a per-warp
+// shared buffer (warp scan of the per-lane counts) and writes the run out coalesced.
+constexpr int EM_THREADS = 256;
+__global__ void __launch_bounds__(EM_THREADS) khop_emit_kernel(const uint8_t* __restrict__ stage, uint32_t WC,
+                                                               unsigned long long q_begin, unsigned long long q_end,
+                                                               const uint32_t* __restrict__ qwin,
+                                                               const unsigned long long* __restrict__ out_off,
+                                                               uint32_t* out_ids, uint8_t* out_hop,
+                                                               unsigned long long cap) {
+  __shared__ uint16_t s_id[EM_THREADS / 32][512];
+  __shared__ uint8_t s_hop[EM_THREADS / 32][512];
+  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
   const unsigned long long warp = (blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x) >> 5;
   const unsigned long long nwarps = ((unsigned long long)gridDim.x * blockDim.x) >> 5;
   for (unsigned long long q = q_begin + warp; q < q_end; q += nwarps) {
     const uint32_t lo = qwin[2 * q], wn = qwin[2 * q + 1];
     const uint8_t* st = stage + (size_t)(q - q_begin) * WC;
     unsigned long long run = out_off[q];
-    for (uint32_t v0 = 0; v0 < wn; v0 += 128) {
-      const uint32_t v = v0 + lane * 4;
-      const uint32_t x = (v < wn) ? *reinterpret_cast<const uint32_t*>(st + v) : 0u;
+    for (uint32_t v0 = 0; v0 < wn; v0 += 512) {
+      const uint32_t v = v0 + lane * 16;
+      uint4 x4 = make_uint4(0u, 0u, 0u, 0u);
+      if (v < wn) x4 = *reinterpret_cast<const uint4*>(st + v);
+      uint32_t x[4] = {x4.x, x4.y, x4.z, x4.w};
       uint32_t c = 0;
 #pragma unroll
-      for (int bb = 0; bb < 4; ++bb) {
-        const uint32_t h = (x >> (8 * bb)) & 255u;
-        c += (h != 0 && h != 255);
-      }
-      const uint32_t inc = warp_incl_scan_u32(c);
-      unsigned long long pos = run + inc - c;
+      for (int w = 0; w < 4; ++w) {
+        if (v + 4 * w >= wn) x[w] = 0;   // words past the row are stale staging memory
 #pragma unroll
-      for (int bb = 0; bb < 4; ++bb) {
-        const uint32_t h = (x >> (8 * bb)) & 255u;
-        if (h != 0 && h != 255) {
-          if (pos < cap) {
-            out_ids[pos] = lo + v + bb;
-            out_hop[pos] = (uint8_t)h;
-          }
-          ++pos;
+        for (int bb = 0; bb < 4; ++bb) {
+          const uint32_t h = (x[w] >> (8 * bb)) & 255u;
+          c += (h != 0 && h != 255);
         }
       }
-      run += __shfl_sync(FULL, inc, 31);
+      const uint32_t inc = warp_incl_scan_u32(c);
+      const uint32_t tot = __shfl_sync(FULL, inc, 31);
+      uint32_t o = inc - c;
+#pragma unroll
+      for (int w = 0; w < 4; ++w)
+#pragma unroll
+        for (int bb = 0; bb < 4; ++bb) {
+          const uint32_t h = (x[w] >> (8 * bb)) & 255u;
+          if (h != 0 && h != 255) {
+            s_id[wib][o] = (uint16_t)(lane * 16 + 4 * w + bb);
+            s_hop[wib][o] = (uint8_t)h;
+            ++o;
+          }
+        }
+      __syncwarp();
+      for (uint32_t i = lane; i < tot; i += 32) {
+        const unsigned long long pos = run + i;
+        if (pos < cap) {
+          out_ids[pos] = lo + v0 + s_id[wib][i];
+          out_hop[pos] = s_hop[wib][i];
+        }
+      }
+      __syncwarp();
+      run += tot;
     }
   }
 }
@@ -787,15 +831,15 @@ static int32_t run_khop(CallCtx* c, dmg_graph* g, int mode, int k, int exclude, 
   a.qwin = nullptr;
   if (maxp <= SMALL_WINDOW_MAX) {
     const uint32_t WC = a.win_cap;
-    const size_t smem = (size_t)WC + WC / 4 + 6 * (size_t)WC;
-    static std::atomic<size_t> smem_set{0};
-    if (smem > 48 * 1024 && smem_set.load() < smem) {
-      DMG_CUDA(cudaFuncSetAttribute(khop_small_kernel<KS_THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                    (int)smem));
-      smem_set.store(smem);
-    }
     int occ = 0;
-    DMG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, khop_small_kernel<KS_THREADS>, KS_THREADS, smem));
+    size_t smem = 0;
+    DMG_TRY(with_small_kernel(WC, [&](auto kern, uint32_t wc) -> int32_t {
+      smem = small_kernel_smem(wc);
+      if (smem > 48 * 1024)
+        DMG_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      DMG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, KS_THREADS, smem));
+      return DMG_OK;
+    }));
     // staging rows (one hop byte per vertex of the project) for a chunk of queries
     const uint64_t stage_budget = std::max<uint64_t>(std::min<uint64_t>(e->scratch_budget, 2ull << 30), WC);
     const uint64_t chunk = std::max<uint64_t>(1, std::min<uint64_t>(nq, stage_budget / WC));
@@ -818,7 +862,10 @@ static int32_t run_khop(CallCtx* c, dmg_graph* g, int mode, int k, int exclude, 
       const uint64_t grid = std::min<uint64_t>(q1 - q0, (uint64_t)e->sm_count * std::max(occ, 1));
       {
         LaunchScope ls(c, K_KHOP_SMALL);
-        khop_small_kernel<KS_THREADS><<<(unsigned)grid, KS_THREADS, smem, c->stream>>>(a);
+        with_small_kernel(WC, [&](auto kern, uint32_t) -> int32_t {
+          kern<<<(unsigned)grid, KS_THREADS, smem, c->stream>>>(a);
+          return DMG_OK;
+        });
       }
       {
         LaunchScope ls(c, K_SCAN_COUNTS);
@@ -830,7 +877,7 @@ static int32_t run_khop(CallCtx* c, dmg_graph* g, int mode, int k, int exclude, 
         LaunchScope ls(c, K_KHOP_EMIT);
         const uint64_t warps = q1 - q0;
         const uint64_t blocks = std::min<uint64_t>((warps + 7) / 8, (uint64_t)e->sm_count * 16);
-        khop_emit_kernel<<<(unsigned)blocks, 256, 0, c->stream>>>(a.stage, WC, q0, q1, a.qwin, a.out_off, a.out_ids,
+        khop_emit_kernel<<<(unsigned)blocks, EM_THREADS, 0, c->stream>>>(a.stage, WC, q0, q1, a.qwin, a.out_off, a.out_ids,
                                                                  a.out_hop, a.cap);
       }
     }
@@ -1007,17 +1054,23 @@ int32_t dmg_neighbors_batch_dev_static(dmg_graph* g, int32_t mode, int32_t k, in
   a.stage = base + o_stage;
   a.counts = reinterpret_cast<uint32_t*>(base + o_counts);
   a.qwin = reinterpret_cast<uint32_t*>(base + o_qwin);
-  const size_t smem = (size_t)WC + WC / 4 + 6 * (size_t)WC;
-  if (smem > 48 * 1024)
-    DMG_CUDA(cudaFuncSetAttribute(khop_small_kernel<KS_THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                  (int)smem));
   int occ = 0;
-  DMG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, khop_small_kernel<KS_THREADS>, KS_THREADS, smem));
+  size_t smem = 0;
+  DMG_TRY(with_small_kernel(WC, [&](auto kern, uint32_t wc) -> int32_t {
+    smem = small_kernel_smem(wc);
+    if (smem > 48 * 1024)
+      DMG_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    DMG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, KS_THREADS, smem));
+    return DMG_OK;
+  }));
   const uint64_t grid = std::min<uint64_t>(nq, (uint64_t)e->sm_count * std::max(occ, 1));
-  khop_small_kernel<KS_THREADS><<<(unsigned)grid, KS_THREADS, smem, 0>>>(a);
+  with_small_kernel(WC, [&](auto kern, uint32_t) -> int32_t {
+    kern<<<(unsigned)grid, KS_THREADS, smem, 0>>>(a);
+    return DMG_OK;
+  });
   scan_counts_kernel<<<(unsigned)std::min<uint64_t>(tiles, (uint64_t)e->sm_count * 4), SC_THREADS, 0, 0>>>(
       a.counts, nq, a.out_off, &ctr->aux[2], a.status, ctr);
-  khop_emit_kernel<<<(unsigned)std::min<uint64_t>((nq + 7) / 8, (uint64_t)e->sm_count * 16), 256, 0, 0>>>(
+  khop_emit_kernel<<<(unsigned)std::min<uint64_t>((nq + 7) / 8, (uint64_t)e->sm_count * 16), EM_THREADS, 0, 0>>>(
       a.stage, WC, 0, nq, a.qwin, a.out_off, a.out_ids, a.out_hop, a.cap);
   DMG_CUDA(cudaGetLastError());
   unsigned long long total = 0;
