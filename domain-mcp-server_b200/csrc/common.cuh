@@ -253,5 +253,77 @@ __device__ __forceinline__ uint64_t lookback_exclusive(uint64_t* status, uint64_
   return excl;
 }
 
+template <int THREADS>
+__device__ __forceinline__ uint32_t block_excl_scan(uint32_t v, uint32_t* s_wsum, uint32_t* total) {
+  // exclusive scan over the block; s_wsum has THREADS/32 + 1 words; all threads must call
+  constexpr int NW = THREADS / 32;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const uint32_t inc = warp_incl_scan_u32(v);
+  if (lane == 31) s_wsum[warp] = inc;
+  __syncthreads();
+  if (warp == 0) {
+    uint32_t w = lane < NW ? s_wsum[lane] : 0;
+    const uint32_t wi = warp_incl_scan_u32(w);
+    if (lane < NW) s_wsum[lane] = wi - w;
+    if (lane == NW - 1) s_wsum[NW] = wi;
+  }
+  __syncthreads();
+  const uint32_t r = s_wsum[warp] + inc - v;
+  *total = s_wsum[NW];
+  __syncthreads();
+  return r;
+}
+
+
+// Exclusive scan of the row sizes into out_off (u64), tile by tile with the look-back
+// allocator; *carry (device) holds the running total across query chunks.
+constexpr int SC_THREADS = 256, SC_ITEMS = 8;
+static __global__ void __launch_bounds__(SC_THREADS) scan_counts_kernel(const uint32_t* __restrict__ counts,
+                                                                 unsigned long long n, unsigned long long* out_off,
+                                                                 unsigned long long* carry, uint64_t* status,
+                                                                 DevCounters* ctr) {
+  __shared__ unsigned long long s_t, s_base;
+  __shared__ uint32_t s_wsum[SC_THREADS / 32 + 1];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  constexpr unsigned long long TILE = (unsigned long long)SC_THREADS * SC_ITEMS;
+  const unsigned long long n_tiles = (n + TILE - 1) / TILE;
+  const unsigned long long carry_in = *carry;
+  while (true) {
+    if (tid == 0) s_t = atomicAdd(&ctr->aux[1], 1ull);
+    __syncthreads();
+    const unsigned long long t = s_t;
+    if (t >= n_tiles) break;
+    const unsigned long long i0 = t * TILE + (unsigned long long)tid * SC_ITEMS;
+    uint32_t x[SC_ITEMS], sum = 0;
+#pragma unroll
+    for (int j = 0; j < SC_ITEMS; ++j) {
+      x[j] = (i0 + j < n) ? counts[i0 + j] : 0;
+      sum += x[j];
+    }
+    uint32_t total;
+    uint32_t off = block_excl_scan<SC_THREADS>(sum, s_wsum, &total);
+    if (warp == 0) {
+      const unsigned long long excl = lookback_exclusive(status, t, total);
+      if (lane == 0) s_base = excl;
+    }
+    __syncthreads();
+    unsigned long long o = carry_in + s_base + off;
+#pragma unroll
+    for (int j = 0; j < SC_ITEMS; ++j) {
+      if (i0 + j < n) out_off[i0 + j] = o;
+      o += x[j];
+    }
+    if (t == n_tiles - 1 && tid == SC_THREADS - 1) {
+      // the last thread of the last tile holds the grand total
+      out_off[n] = o;
+      ctr->total = o;
+      __threadfence();
+      *carry = o;
+    }
+    __syncthreads();
+  }
+}
+
+
 }  // namespace dmg
 #endif

@@ -142,6 +142,11 @@ __global__ void __launch_bounds__(SE_THREADS) search_kernel(const unsigned long 
 
 }  // namespace dmg
 
+namespace dmg {
+int32_t run_search_multi(CallCtx* c, dmg_graph* g, int kind, uint32_t v_lo, uint32_t v_hi, uint64_t nq,
+                         const uint32_t* q_off, const uint8_t* q_bytes, uint64_t dev_cap, bool sizes_only);
+}
+
 using namespace dmg;
 
 extern "C" {
@@ -179,6 +184,18 @@ int32_t dmg_search_batch(dmg_graph* g, int32_t kind, uint32_t v_lo, uint32_t v_h
   uint64_t dev_cap = out_ids ? cap : 0;
   if (kind != DMG_SEARCH_CONTAINS_ALL) dev_cap = std::min<uint64_t>(dev_cap, nq);
   else if (range == 0 || nq <= UINT64_MAX / std::max<uint64_t>(range, 1)) dev_cap = std::min<uint64_t>(dev_cap, nq * range);
+  uint64_t total = 0;
+  if (kind != DMG_SEARCH_SIMPLE_EQ_FIRST) {
+    // S1 and the containment scan of S2: one pass over the arena for the whole batch
+    const uint64_t cap_eff = out_ids ? cap : 0;
+    const bool direct = cap_eff && dev_cap * 4 <= std::max<uint64_t>(1ull << 30, c->out_ids.cap);
+    DMG_TRY(run_search_multi(c, g, kind, v_lo, v_hi, nq, q_off, q_bytes, direct ? dev_cap : 0, !direct));
+    total = c->h_counters->total;
+    if (!direct && cap_eff && total && total <= cap_eff) {
+      DMG_TRY(run_search_multi(c, g, kind, v_lo, v_hi, nq, q_off, q_bytes, total, false));
+      total = c->h_counters->total;
+    }
+  } else {
   DMG_TRY(c->q_off.reserve((nq + 1) * 4));
   DMG_TRY(c->q_bytes.reserve(qbytes + 16));
   DMG_TRY(c->out_off.reserve((nq + 1) * 8));
@@ -188,7 +205,6 @@ int32_t dmg_search_batch(dmg_graph* g, int32_t kind, uint32_t v_lo, uint32_t v_h
   DMG_CUDA(cudaMemcpyAsync(c->q_off.p, q_off, (nq + 1) * 4, cudaMemcpyHostToDevice, c->stream));
   if (qbytes) DMG_CUDA(cudaMemcpyAsync(c->q_bytes.p, q_bytes, qbytes, cudaMemcpyHostToDevice, c->stream));
   c->stats.h2d_bytes += (nq + 1) * 4 + qbytes;
-  uint64_t total = 0;
   const unsigned grid = (unsigned)std::min<uint64_t>(nq, (uint64_t)g->eng->sm_count * 8);
   for (int pass = one_pass ? 1 : 0; pass < 2; ++pass) {
     const uint64_t use_cap = pass == 0 ? 0 : (one_pass ? dev_cap : std::min<uint64_t>(dev_cap, total));
@@ -207,6 +223,7 @@ int32_t dmg_search_batch(dmg_graph* g, int32_t kind, uint32_t v_lo, uint32_t v_h
     DMG_CUDA(cudaStreamSynchronize(c->stream));
     total = c->h_counters->total;
     if (pass == 0 && (total > (out_ids ? cap : 0) || total == 0)) break;
+  }
   }
   DMG_CUDA(cudaMemcpyAsync(out_off, c->out_off.p, (nq + 1) * 8, cudaMemcpyDeviceToHost, c->stream));
   c->stats.d2h_bytes += (nq + 1) * 8 + sizeof(DevCounters);

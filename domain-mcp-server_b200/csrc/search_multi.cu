@@ -1,0 +1,518 @@
+// S1 at scale (BASELINE config 3): every query of a batch is matched in ONE pass
+// over the packed, pre-lowered name arena.
+//
+//   - the batch's distinct patterns are classed by length and keyed by their first 8 / 4 / 3 /
+//     2 / 1 bytes; per class a Bloom-style bitmap in shared memory rejects almost every text
+//     position, a small open-addressing table in L2 maps a surviving key to its patterns;
+//   - one warp owns a contiguous tile of names and walks it name by name; the 32 lanes cover
+//     the name's byte positions (aligned 4-byte loads + funnel shifts give every position its
+//     8-byte window), so the arena is read once, coalesced, whatever the number of queries;
+//   - ordered output without a sort: pass 1 counts hits per (tile, pattern); a column scan turns
+//     the counts into per-tile row cursors; pass 2 repeats the match and writes each hit at its
+//     cursor.  Tiles are name ranges in id order and a warp walks its tile in id order, so every
+//     row comes out in ascending id == `nodes` order (CCS:1511).  A pattern that occurs twice in
+//     one name is reported once (String.contains);
+//   - the "first id containing the query" scan of resolveClassName (GQS:449-453) is the same
+//     match with an atomicMin per pattern instead of rows.
+#include <algorithm>
+#include <string>
+#include <unordered_map>
+
+#include "common.cuh"
+
+namespace dmg {
+
+constexpr int SM_THREADS = 512;          // 16 warps per CTA
+constexpr int SM_WARPS = SM_THREADS / 32;
+constexpr int SM_HITBUF = 192;           // hits of one name before the exhaustive fallback
+constexpr uint32_t SM_MAX_PATTERNS = 16384;   // per round (bounds the tile x pattern matrix)
+
+struct SlotTable {
+  const unsigned long long* key;   // [size]
+  const uint32_t* start;           // [size] into bucket_pat
+  const uint32_t* count;           // [size] 0 = empty slot
+  uint32_t mask;                   // size - 1
+  uint32_t fbits;                  // log2 of the filter size in bits
+  uint32_t present;
+};
+
+struct SearchArgs {
+  const unsigned long long* name_off;
+  const uint8_t* lower;
+  uint32_t v_lo, v_hi, per_tile, n_tiles;
+  SlotTable t8, t4, t3;
+  const uint32_t* filt;             // filters of the three classes, concatenated (words)
+  uint32_t filt_words8, filt_words4, filt_words3;
+  const uint32_t* bucket_pat;
+  const unsigned long long* pk8;    // per pattern: first min(len, 8) bytes, little endian
+  const uint32_t* plen;
+  const uint32_t* poff;
+  const uint8_t* pbytes;
+  const uint32_t* tiny2;            // [65536] pattern id + 1
+  const uint32_t* tiny1;            // [256]
+  uint32_t has2, has1, empty_plus1;
+  uint32_t U;                       // patterns in this round
+  uint32_t* cnt;                    // [n_tiles][U] counts, then cursors
+  uint32_t* first;                  // [U] min id (MODE 2)
+  const uint32_t* uq_off;           // pattern -> queries that asked for it
+  const uint32_t* uq;
+  const unsigned long long* out_off;
+  uint32_t* out_ids;
+  unsigned long long cap;
+};
+
+__device__ __forceinline__ uint32_t hash_slot(unsigned long long k, uint32_t mask) {
+  return (uint32_t)((k * 0x9E3779B97F4A7C15ull) >> 40) & mask;
+}
+__device__ __forceinline__ uint32_t hash_filter(unsigned long long k, uint32_t bits) {
+  return (uint32_t)(((k ^ (k >> 29)) * 0xBF58476D1CE4E5B9ull) >> (64 - bits));
+}
+__device__ __forceinline__ bool table_find(const SlotTable& t, unsigned long long k, uint32_t* st, uint32_t* cn) {
+  uint32_t h = hash_slot(k, t.mask);
+  while (true) {
+    const uint32_t c = t.count[h];
+    if (c == 0) return false;
+    if (t.key[h] == k) {
+      *st = t.start[h];
+      *cn = c;
+      return true;
+    }
+    h = (h + 1) & t.mask;
+  }
+}
+__device__ __forceinline__ unsigned long long low_bytes_mask(uint32_t len) {
+  return len >= 8 ? ~0ull : ((1ull << (8 * len)) - 1ull);
+}
+
+template <int MODE>   // 0 count, 1 emit, 2 first
+__global__ void __launch_bounds__(SM_THREADS) search_multi_kernel(const SearchArgs a) {
+  extern __shared__ __align__(16) uint32_t sm_u32[];
+  uint32_t* f8 = sm_u32;
+  uint32_t* f4 = f8 + a.filt_words8;
+  uint32_t* f3 = f4 + a.filt_words4;
+  __shared__ uint32_t s_hits[SM_WARPS][SM_HITBUF];
+  __shared__ uint32_t s_nh[SM_WARPS];
+  const int tid = threadIdx.x, lane = tid & 31, wib = tid >> 5;
+  const uint32_t fw = a.filt_words8 + a.filt_words4 + a.filt_words3;
+  for (uint32_t i = tid; i < fw; i += SM_THREADS) sm_u32[i] = a.filt[i];
+  if (lane == 0) s_nh[wib] = 0;
+  __syncthreads();
+
+  const uint32_t tile = blockIdx.x * SM_WARPS + wib;
+  if (tile >= a.n_tiles) return;
+  const uint32_t n0 = a.v_lo + tile * a.per_tile;
+  const uint32_t n1 = min(a.v_hi, n0 + a.per_tile);
+  uint32_t* my_cnt = (MODE == 2) ? nullptr : a.cnt + (size_t)tile * a.U;
+
+  auto push = [&](uint32_t u) {
+    const uint32_t pos = atomicAdd(&s_nh[wib], 1u);
+    if (pos < SM_HITBUF) s_hits[wib][pos] = u;
+  };
+  auto deliver = [&](uint32_t u, uint32_t id) {
+    if (MODE == 0) {
+      atomicAdd(&my_cnt[u], 1u);
+    } else if (MODE == 1) {
+      const uint32_t local = atomicAdd(&my_cnt[u], 1u);
+      for (uint32_t j = a.uq_off[u]; j < a.uq_off[u + 1]; ++j) {
+        const unsigned long long pos = a.out_off[a.uq[j]] + local;
+        if (pos < a.cap) a.out_ids[pos] = id;
+      }
+    } else {
+      atomicMin(&a.first[u], id);
+    }
+  };
+
+  for (uint32_t i = n0; i < n1; ++i) {
+    const unsigned long long s = a.name_off[i], e = a.name_off[i + 1];
+    const unsigned long long ws = s & ~3ull;
+    if (a.empty_plus1 && lane == 0) push(a.empty_plus1 - 1);
+    // 29 position-carrying lanes per chunk: lanes 29..31 only feed the windows of their neighbours
+    for (unsigned long long cb = ws; cb < e; cb += 116) {
+      const unsigned long long wa = cb + 4ull * lane;
+      uint32_t w0 = 0;
+      if (wa < e + 8) w0 = *reinterpret_cast<const uint32_t*>(a.lower + wa);   // arena is zero padded
+      const uint32_t w1 = __shfl_down_sync(FULL, w0, 1);
+      const uint32_t w2 = __shfl_down_sync(FULL, w0, 2);
+      if (lane < 29) {
+#pragma unroll
+        for (int b = 0; b < 4; ++b) {
+          const unsigned long long p = wa + b;
+          if (p < s || p >= e) continue;
+          const uint32_t r = (uint32_t)min(e - p, 0xFFFFull);
+          const uint32_t lo32 = b ? __funnelshift_r(w0, w1, 8 * b) : w0;
+          const uint32_t hi32 = b ? __funnelshift_r(w1, w2, 8 * b) : w1;
+          const unsigned long long k8 = ((unsigned long long)hi32 << 32) | lo32;
+          if (a.t8.present && r >= 8) {
+            const uint32_t fi = hash_filter(k8, a.t8.fbits);
+            if ((f8[fi >> 5] >> (fi & 31)) & 1u) {
+              uint32_t st, cn;
+              if (table_find(a.t8, k8, &st, &cn))
+                for (uint32_t j = 0; j < cn; ++j) {
+                  const uint32_t u = a.bucket_pat[st + j], len = a.plen[u];
+                  if (len > r) continue;
+                  bool ok = true;
+                  const uint8_t* pb = a.pbytes + a.poff[u];
+                  for (uint32_t t = 8; t < len && ok; ++t) ok = a.lower[p + t] == pb[t];
+                  if (ok) push(u);
+                }
+            }
+          }
+          if (a.t4.present && r >= 4) {
+            const uint32_t fi = hash_filter(lo32, a.t4.fbits);
+            if ((f4[fi >> 5] >> (fi & 31)) & 1u) {
+              uint32_t st, cn;
+              if (table_find(a.t4, lo32, &st, &cn))
+                for (uint32_t j = 0; j < cn; ++j) {
+                  const uint32_t u = a.bucket_pat[st + j], len = a.plen[u];
+                  if (len <= r && (k8 & low_bytes_mask(len)) == a.pk8[u]) push(u);
+                }
+            }
+          }
+          if (a.t3.present && r >= 3) {
+            const uint32_t k3 = lo32 & 0xFFFFFFu;
+            const uint32_t fi = hash_filter(k3, a.t3.fbits);
+            if ((f3[fi >> 5] >> (fi & 31)) & 1u) {
+              uint32_t st, cn;
+              if (table_find(a.t3, k3, &st, &cn)) push(a.bucket_pat[st]);
+            }
+          }
+          if (a.has2 && r >= 2) {
+            const uint32_t u1 = a.tiny2[lo32 & 0xFFFFu];
+            if (u1) push(u1 - 1);
+          }
+          if (a.has1) {
+            const uint32_t u1 = a.tiny1[lo32 & 0xFFu];
+            if (u1) push(u1 - 1);
+          }
+        }
+      }
+    }
+    __syncwarp();
+    const uint32_t nh = s_nh[wib];
+    if (nh == 0) continue;
+    if (nh <= SM_HITBUF) {
+      // a pattern may occur at several positions of the name: report it once
+      for (uint32_t j = lane; j < nh; j += 32) {
+        const uint32_t u = s_hits[wib][j];
+        bool dup = false;
+        for (uint32_t t = 0; t < j && !dup; ++t) dup = s_hits[wib][t] == u;
+        if (!dup) deliver(u, i);
+      }
+    } else {
+      // more hits than the buffer holds (very long name): test every pattern directly
+      const uint32_t nn = (uint32_t)(e - s);
+      for (uint32_t u = lane; u < a.U; u += 32) {
+        const uint32_t len = a.plen[u];
+        bool hit = len == 0;
+        const uint8_t* pb = a.pbytes + a.poff[u];
+        for (uint32_t p = 0; !hit && p + len <= nn; ++p) {
+          uint32_t t = 0;
+          while (t < len && a.lower[s + p + t] == pb[t]) ++t;
+          hit = t == len;
+        }
+        if (hit) deliver(u, i);
+      }
+    }
+    __syncwarp();
+    if (lane == 0) s_nh[wib] = 0;
+    __syncwarp();
+  }
+}
+
+// exclusive scan of every pattern's column over the tiles; tot[u] = row length
+__global__ void search_colscan_kernel(uint32_t* cnt, uint32_t n_tiles, uint32_t U, uint32_t* tot) {
+  const uint32_t u = blockIdx.x * blockDim.x + threadIdx.x;
+  if (u >= U) return;
+  uint32_t run = 0;
+  for (uint32_t t = 0; t < n_tiles; ++t) {
+    const size_t o = (size_t)t * U + u;
+    const uint32_t c = cnt[o];
+    cnt[o] = run;
+    run += c;
+  }
+  tot[u] = run;
+}
+
+__global__ void search_query_counts_kernel(const uint32_t* __restrict__ tot, const uint32_t* __restrict__ q2u,
+                                           unsigned long long nq, uint32_t* qcnt) {
+  const unsigned long long q = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x;
+  if (q < nq) {
+    const uint32_t u = q2u[q];
+    qcnt[q] = (u == 0xFFFFFFFFu) ? 0u : tot[u];
+  }
+}
+
+__global__ void search_first_rows_kernel(const uint32_t* __restrict__ first, const uint32_t* __restrict__ q2u,
+                                         unsigned long long nq, uint32_t* qcnt) {
+  const unsigned long long q = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x;
+  if (q < nq) qcnt[q] = first[q2u[q]] != 0xFFFFFFFFu;
+}
+__global__ void search_first_emit_kernel(const uint32_t* __restrict__ first, const uint32_t* __restrict__ q2u,
+                                         unsigned long long nq, const unsigned long long* __restrict__ out_off,
+                                         uint32_t* out_ids, unsigned long long cap) {
+  const unsigned long long q = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x;
+  if (q < nq) {
+    const uint32_t f = first[q2u[q]];
+    if (f != 0xFFFFFFFFu && out_off[q] < cap) out_ids[out_off[q]] = f;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// host side: pattern tables
+// ---------------------------------------------------------------------------------------------
+struct HostTables {
+  std::vector<std::string> pats;                 // distinct patterns
+  std::vector<uint32_t> q2u;
+  std::vector<unsigned long long> key[3];        // classes 8, 4, 3
+  std::vector<uint32_t> start[3], count[3];
+  std::vector<uint32_t> bucket_pat;
+  std::vector<uint32_t> filt[3];
+  uint32_t fbits[3] = {0, 0, 0};
+  std::vector<unsigned long long> pk8;
+  std::vector<uint32_t> plen, poff;
+  std::vector<uint8_t> pbytes;
+  std::vector<uint32_t> tiny2, tiny1;
+  uint32_t empty_plus1 = 0;
+  std::vector<uint32_t> uq_off, uq;
+};
+
+static inline uint32_t h_hash_slot(unsigned long long k, uint32_t mask) {
+  return (uint32_t)((k * 0x9E3779B97F4A7C15ull) >> 40) & mask;
+}
+static inline uint32_t h_hash_filter(unsigned long long k, uint32_t bits) {
+  return (uint32_t)(((k ^ (k >> 29)) * 0xBF58476D1CE4E5B9ull) >> (64 - bits));
+}
+
+static void build_tables(uint64_t nq, const uint32_t* q_off, const uint8_t* q_bytes, HostTables& T) {
+  std::unordered_map<std::string, uint32_t> ids;
+  T.q2u.resize(nq);
+  for (uint64_t q = 0; q < nq; ++q) {
+    std::string p(reinterpret_cast<const char*>(q_bytes) + q_off[q], q_off[q + 1] - q_off[q]);
+    auto it = ids.find(p);
+    if (it == ids.end()) {
+      it = ids.emplace(p, (uint32_t)T.pats.size()).first;
+      T.pats.push_back(p);
+    }
+    T.q2u[q] = it->second;
+  }
+  const uint32_t U = (uint32_t)T.pats.size();
+  T.pk8.assign(U, 0);
+  T.plen.resize(U);
+  T.poff.resize(U + 1);
+  T.tiny2.assign(65536, 0);
+  T.tiny1.assign(256, 0);
+  std::vector<std::pair<unsigned long long, uint32_t>> cls[3];
+  for (uint32_t u = 0; u < U; ++u) {
+    const std::string& p = T.pats[u];
+    T.plen[u] = (uint32_t)p.size();
+    T.poff[u] = (uint32_t)T.pbytes.size();
+    T.pbytes.insert(T.pbytes.end(), p.begin(), p.end());
+    unsigned long long k = 0;
+    for (size_t i = 0; i < p.size() && i < 8; ++i) k |= (unsigned long long)(uint8_t)p[i] << (8 * i);
+    T.pk8[u] = k;
+    if (p.empty()) T.empty_plus1 = u + 1;
+    else if (p.size() == 1) T.tiny1[k & 0xFF] = u + 1;
+    else if (p.size() == 2) T.tiny2[k & 0xFFFF] = u + 1;
+    else if (p.size() == 3) cls[2].emplace_back(k & 0xFFFFFF, u);
+    else if (p.size() < 8) cls[1].emplace_back(k & 0xFFFFFFFFull, u);
+    else cls[0].emplace_back(k, u);
+  }
+  T.poff[U] = (uint32_t)T.pbytes.size();
+  T.pbytes.resize(T.pbytes.size() + 16, 0);
+  for (int c = 0; c < 3; ++c) {
+    auto& v = cls[c];
+    std::sort(v.begin(), v.end());
+    size_t nkeys = 0;
+    for (size_t i = 0; i < v.size(); ++i) nkeys += (i == 0 || v[i].first != v[i - 1].first);
+    uint32_t size = 16;
+    while (size < 2 * nkeys + 1) size <<= 1;
+    T.key[c].assign(size, 0);
+    T.start[c].assign(size, 0);
+    T.count[c].assign(size, 0);
+    uint32_t fb = 12;
+    while ((1ull << fb) < 32 * nkeys && fb < 18) ++fb;
+    T.fbits[c] = fb;
+    T.filt[c].assign((1u << fb) / 32, 0);
+    for (size_t i = 0; i < v.size();) {
+      size_t j = i;
+      while (j < v.size() && v[j].first == v[i].first) ++j;
+      uint32_t h = h_hash_slot(v[i].first, size - 1);
+      while (T.count[c][h]) h = (h + 1) & (size - 1);
+      T.key[c][h] = v[i].first;
+      T.start[c][h] = (uint32_t)T.bucket_pat.size();
+      T.count[c][h] = (uint32_t)(j - i);
+      for (size_t t = i; t < j; ++t) T.bucket_pat.push_back(v[t].second);
+      const uint32_t fi = h_hash_filter(v[i].first, fb);
+      T.filt[c][fi >> 5] |= 1u << (fi & 31);
+      i = j;
+    }
+  }
+  if (T.bucket_pat.empty()) T.bucket_pat.push_back(0);
+  // pattern -> queries
+  T.uq_off.assign(U + 1, 0);
+  for (uint64_t q = 0; q < nq; ++q) ++T.uq_off[T.q2u[q] + 1];
+  for (uint32_t u = 0; u < U; ++u) T.uq_off[u + 1] += T.uq_off[u];
+  T.uq.resize(nq);
+  std::vector<uint32_t> cur(T.uq_off.begin(), T.uq_off.end() - 1);
+  for (uint64_t q = 0; q < nq; ++q) T.uq[cur[T.q2u[q]]++] = (uint32_t)q;
+}
+
+template <class T>
+static int32_t put(CallCtx* c, DevBuf& arena, size_t* used, const std::vector<T>& v, const T** out) {
+  const size_t bytes = std::max<size_t>(v.size() * sizeof(T), 16);
+  const size_t at = (*used + 255) & ~size_t(255);
+  *out = reinterpret_cast<const T*>(static_cast<char*>(arena.p) + at);
+  if (!v.empty())
+    DMG_CUDA(cudaMemcpyAsync(const_cast<T*>(*out), v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice, c->stream));
+  *used = at + bytes;
+  return DMG_OK;
+}
+
+// Runs the multi-pattern search for kind CONTAINS_ALL / CONTAINS_FIRST on device buffers of the
+// context; leaves out_off / out_ids on the device and the total in c->h_counters->total.
+int32_t run_search_multi(CallCtx* c, dmg_graph* g, int kind, uint32_t v_lo, uint32_t v_hi, uint64_t nq,
+                         const uint32_t* q_off, const uint8_t* q_bytes, uint64_t dev_cap, bool sizes_only) {
+  Engine* e = c->eng;
+  HostTables T;
+  build_tables(nq, q_off, q_bytes, T);
+  const uint32_t U = (uint32_t)T.pats.size();
+  if (U > SM_MAX_PATTERNS && kind == DMG_SEARCH_CONTAINS_ALL) {
+    set_error("dmg_search_batch: %u distinct queries in one batch; split it into batches of <= %u", U, SM_MAX_PATTERNS);
+    return DMG_EINVAL;
+  }
+  // one arena for every table
+  size_t need = 4096;
+  auto sz = [&](size_t n, size_t s) { need += ((n * s + 255) & ~size_t(255)) + 256; };
+  for (int k = 0; k < 3; ++k) {
+    sz(T.key[k].size(), 8);
+    sz(T.start[k].size(), 4);
+    sz(T.count[k].size(), 4);
+    sz(T.filt[k].size(), 4);
+  }
+  sz(T.bucket_pat.size(), 4); sz(U, 8); sz(U, 4); sz(U + 1, 4); sz(T.pbytes.size(), 1);
+  sz(65536, 4); sz(256, 4); sz(U + 1, 4); sz(nq, 4); sz(nq, 4);
+  DMG_TRY(c->tmp0.reserve(need));
+  size_t used = 0;
+  SearchArgs a;
+  memset(&a, 0, sizeof(a));
+  SlotTable* st[3] = {&a.t8, &a.t4, &a.t3};
+  std::vector<uint32_t> filt_all;
+  for (int k = 0; k < 3; ++k) {
+    DMG_TRY(put(c, c->tmp0, &used, T.key[k], &st[k]->key));
+    DMG_TRY(put(c, c->tmp0, &used, T.start[k], &st[k]->start));
+    DMG_TRY(put(c, c->tmp0, &used, T.count[k], &st[k]->count));
+    st[k]->mask = (uint32_t)T.key[k].size() - 1;
+    st[k]->fbits = T.fbits[k];
+    st[k]->present = 0;
+    for (uint32_t x : T.count[k]) st[k]->present |= x != 0;
+    filt_all.insert(filt_all.end(), T.filt[k].begin(), T.filt[k].end());
+  }
+  a.filt_words8 = (uint32_t)T.filt[0].size();
+  a.filt_words4 = (uint32_t)T.filt[1].size();
+  a.filt_words3 = (uint32_t)T.filt[2].size();
+  DMG_TRY(put(c, c->tmp0, &used, filt_all, &a.filt));
+  DMG_TRY(put(c, c->tmp0, &used, T.bucket_pat, &a.bucket_pat));
+  DMG_TRY(put(c, c->tmp0, &used, T.pk8, &a.pk8));
+  DMG_TRY(put(c, c->tmp0, &used, T.plen, &a.plen));
+  DMG_TRY(put(c, c->tmp0, &used, T.poff, &a.poff));
+  DMG_TRY(put(c, c->tmp0, &used, T.pbytes, &a.pbytes));
+  DMG_TRY(put(c, c->tmp0, &used, T.tiny2, &a.tiny2));
+  DMG_TRY(put(c, c->tmp0, &used, T.tiny1, &a.tiny1));
+  DMG_TRY(put(c, c->tmp0, &used, T.uq_off, &a.uq_off));
+  DMG_TRY(put(c, c->tmp0, &used, T.uq, &a.uq));
+  const uint32_t* d_q2u = nullptr;
+  DMG_TRY(put(c, c->tmp0, &used, T.q2u, &d_q2u));
+  for (uint32_t x : T.tiny2) a.has2 |= x != 0;
+  for (uint32_t x : T.tiny1) a.has1 |= x != 0;
+  a.empty_plus1 = T.empty_plus1;
+  a.U = U;
+  a.name_off = reinterpret_cast<const unsigned long long*>(g->d_name_off);
+  a.lower = g->d_lower;
+  a.v_lo = v_lo;
+  a.v_hi = v_hi;
+  c->stats.h2d_bytes += used;
+
+  const uint32_t range = v_hi - v_lo;
+  const size_t smem = (size_t)filt_all.size() * 4;
+  if (smem > 48 * 1024) {
+    DMG_CUDA(cudaFuncSetAttribute(search_multi_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    DMG_CUDA(cudaFuncSetAttribute(search_multi_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    DMG_CUDA(cudaFuncSetAttribute(search_multi_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  }
+  int occ = 1;
+  DMG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, search_multi_kernel<0>, SM_THREADS, smem));
+  // tiles: one per resident warp, but not smaller than 64 names and bounded by the matrix budget
+  uint64_t tiles = (uint64_t)e->sm_count * std::max(occ, 1) * SM_WARPS;
+  tiles = std::min<uint64_t>(tiles, ((uint64_t)range + 63) / 64);
+  if (kind == DMG_SEARCH_CONTAINS_ALL)
+    tiles = std::min<uint64_t>(tiles, std::max<uint64_t>(1, (1ull << 30) / (4ull * std::max<uint32_t>(U, 1))));
+  tiles = std::max<uint64_t>(tiles, 1);
+  a.n_tiles = (uint32_t)tiles;
+  a.per_tile = (uint32_t)((range + tiles - 1) / tiles);
+  const unsigned blocks = (unsigned)((tiles + SM_WARPS - 1) / SM_WARPS);
+
+  DMG_TRY(c->out_off.reserve((nq + 1) * 8));
+  DMG_TRY(c->tmp2.reserve(nq * 4 + (size_t)U * 4 + 512));   // per-query counts | per-pattern totals/first
+  uint32_t* qcnt = c->tmp2.as<uint32_t>();
+  uint32_t* tot = qcnt + ((nq + 63) & ~63ull);
+  const uint64_t scan_tiles = (nq + 2047) / 2048;
+  DMG_TRY(c->status.reserve(scan_tiles * 8));
+  DMG_CUDA(cudaMemsetAsync(c->status.p, 0, scan_tiles * 8, c->stream));
+  DMG_CUDA(cudaMemsetAsync(c->d_counters, 0, sizeof(DevCounters), c->stream));
+  a.out_off = c->out_off.as<unsigned long long>();
+  a.cap = dev_cap;
+  const unsigned qb = (unsigned)((nq + 255) / 256);
+
+  if (kind == DMG_SEARCH_CONTAINS_FIRST) {
+    a.first = tot;
+    DMG_CUDA(cudaMemsetAsync(tot, 0xFF, (size_t)U * 4, c->stream));
+    if (range) {
+      LaunchScope ls(c, K_SEARCH_SCAN);
+      search_multi_kernel<2><<<blocks, SM_THREADS, smem, c->stream>>>(a);
+    }
+    {
+      LaunchScope ls(c, K_SEARCH_FIRST);
+      search_first_rows_kernel<<<qb, 256, 0, c->stream>>>(tot, d_q2u, nq, qcnt);
+    }
+    {
+      LaunchScope ls(c, K_SCAN_COUNTS);
+      scan_counts_kernel<<<(unsigned)std::min<uint64_t>(scan_tiles, 1024), 256, 0, c->stream>>>(
+          qcnt, nq, c->out_off.as<unsigned long long>(), &c->d_counters->aux[2], c->status.as<uint64_t>(), c->d_counters);
+    }
+    if (!sizes_only) {
+      DMG_TRY(c->out_ids.reserve(std::max<uint64_t>(dev_cap, 1) * 4));
+      LaunchScope ls(c, K_SEARCH_EMIT);
+      search_first_emit_kernel<<<qb, 256, 0, c->stream>>>(tot, d_q2u, nq, a.out_off, c->out_ids.as<uint32_t>(), dev_cap);
+    }
+  } else {
+    DMG_TRY(c->tmp1.reserve((size_t)tiles * U * 4 + 256));
+    a.cnt = c->tmp1.as<uint32_t>();
+    DMG_CUDA(cudaMemsetAsync(a.cnt, 0, (size_t)tiles * U * 4, c->stream));
+    if (range) {
+      LaunchScope ls(c, K_SEARCH_SCAN);
+      search_multi_kernel<0><<<blocks, SM_THREADS, smem, c->stream>>>(a);
+    }
+    {
+      LaunchScope ls(c, K_SEARCH_FIRST);
+      search_colscan_kernel<<<(U + 127) / 128, 128, 0, c->stream>>>(a.cnt, a.n_tiles, U, tot);
+      search_query_counts_kernel<<<qb, 256, 0, c->stream>>>(tot, d_q2u, nq, qcnt);
+    }
+    {
+      LaunchScope ls(c, K_SCAN_COUNTS);
+      scan_counts_kernel<<<(unsigned)std::min<uint64_t>(scan_tiles, 1024), 256, 0, c->stream>>>(
+          qcnt, nq, c->out_off.as<unsigned long long>(), &c->d_counters->aux[2], c->status.as<uint64_t>(), c->d_counters);
+    }
+    if (!sizes_only && range) {
+      DMG_TRY(c->out_ids.reserve(std::max<uint64_t>(dev_cap, 1) * 4));
+      a.out_ids = c->out_ids.as<uint32_t>();
+      LaunchScope ls(c, K_SEARCH_EMIT);
+      search_multi_kernel<1><<<blocks, SM_THREADS, smem, c->stream>>>(a);
+    }
+  }
+  DMG_CUDA(cudaGetLastError());
+  DMG_CUDA(cudaMemcpyAsync(c->h_counters, c->d_counters, sizeof(DevCounters), cudaMemcpyDeviceToHost, c->stream));
+  DMG_CUDA(cudaStreamSynchronize(c->stream));
+  return DMG_OK;
+}
+
+}  // namespace dmg

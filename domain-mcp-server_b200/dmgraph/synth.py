@@ -239,12 +239,33 @@ def pack_names(names):
     return off, np.frombuffer(b"".join(enc), dtype=np.uint8).copy()
 
 
-def catalog_names(n, seed=SEED_C3_NAMES, n_projects=50):
+SYLLABLES = ["ba", "ce", "di", "fo", "gu", "ha", "je", "ki", "lo", "mu", "na", "pe", "qui", "ro", "su", "ta",
+             "ve", "wi", "xo", "yu", "za", "bre", "cli", "dro", "fra", "gle", "pri", "sto", "tru", "vla",
+             "sha", "che", "tho", "phi", "kra", "sno", "twi", "spe", "sca", "blu"]
+
+
+def catalog_vocab(n_words=20000, seed=SEED_C3_NAMES):
+    """Synthetic stem vocabulary: 3-syllable words, 6-9 letters, capitalised ("Brecliro")."""
+    rng = np.random.Generator(np.random.PCG64(seed ^ 0x5EED))
+    ns = len(SYLLABLES)
+    seen, words = set(), []
+    while len(words) < n_words:
+        i, j, k = rng.integers(0, ns, 3)
+        w = SYLLABLES[i] + SYLLABLES[j] + SYLLABLES[k]
+        if 6 <= len(w) <= 10 and w not in seen:
+            seen.add(w)
+            words.append(w.capitalize())
+    return words
+
+
+def catalog_names(n, seed=SEED_C3_NAMES, n_projects=50, n_words=20000):
     """BASELINE config 3: method-qualified identifiers "{class}.{verb}{Noun}{n}" as a packed arena.
 
-    Built directly as bytes (10 M Python strings would take minutes): returns (name_off, bytes).
+    The class stem comes from a 20,000-word vocabulary so that a vocabulary-token query has the
+    ~1e-4 selectivity SURVEY.md 8d asks for.  Built directly as bytes: returns (name_off, bytes).
     """
     rng = np.random.Generator(np.random.PCG64(seed))
+    vocab = catalog_vocab(n_words, seed)
     chunks = []
     lens = np.empty(n, np.int64)
     step = 200000
@@ -252,11 +273,11 @@ def catalog_names(n, seed=SEED_C3_NAMES, n_projects=50):
         m = min(step, n - base)
         p = rng.integers(0, n_projects, m)
         layer = rng.integers(0, len(LAYERS), m)
-        stem = rng.integers(0, len(STEMS), m)
+        stem = rng.integers(0, len(vocab), m)
         verb = rng.integers(0, len(VERBS), m)
         noun = rng.integers(0, len(NOUNS), m)
         cls = rng.integers(0, 2000, m)
-        strs = ["co.fanki.svc%d.%s.%s%d%s.%s%s%d" % (p[i], LAYERS[layer[i]], STEMS[stem[i]], cls[i],
+        strs = ["co.fanki.svc%d.%s.%s%d%s.%s%s%d" % (p[i], LAYERS[layer[i]], vocab[stem[i]], cls[i],
                                                     SUFFIX[LAYERS[layer[i]]], VERBS[verb[i]],
                                                     NOUNS[noun[i]], base + i) for i in range(m)]
         enc = [s.encode("ascii") for s in strs]
@@ -275,8 +296,7 @@ def search_queries(name_off, name_bytes, n_queries=16384, seed=SEED_C3_QUERIES):
     """
     rng = np.random.Generator(np.random.PCG64(seed))
     n = name_off.size - 1
-    vocab = [w.lower() for w in STEMS + VERBS + NOUNS + LAYERS + ["Controller", "Repository", "Service"]]
-    vocab = [w for w in vocab if 6 <= len(w) <= 10]
+    vocab = [w.lower() for w in catalog_vocab()]
     out = []
     kinds = rng.random(n_queries)
     for qi in range(n_queries):

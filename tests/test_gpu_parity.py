@@ -295,3 +295,48 @@ def test_graph_service_put_reload_swap(engine):
     g1.release()
     g2.release()
     svc.close()
+
+
+def test_search_multi_pattern_batches(engine):
+    """S1 through the single-pass multi-pattern kernel: every length class, duplicate queries,
+    patterns that occur several times in one name, very long names (exhaustive fallback),
+    multi-byte UTF-8, ranges; ordered hits bit-exact against the oracle."""
+    rng = np.random.default_rng(77)
+    names = synth.project_names(1, 20000, rng)
+    names[5] = "aaaaaaaaaaaaaaaaaaaaaaaaaaaaaaaaaaaaaaaa"                 # same pattern at many positions
+    names[6] = "abcabcabcabc" * 40                                       # long: several 116-byte chunks
+    names[7] = "x" * 700 + "needle" + "y" * 300
+    names[11] = "co.fanki.été.Über漢字Service"    # non-ASCII bytes pass through
+    off, arena = synth.pack_names(names)
+    low = np.frombuffer(bytes(arena).lower(), dtype=np.uint8).copy()
+    g = dmgraph.Graph(engine, len(names), [], [], [], name_off=off, name_bytes=arena, lower_bytes=low)
+    lows = [bytes(low[int(off[i]):int(off[i + 1])]) for i in range(len(names))]
+    queries = [b"", b"a", b"aa", b"aaa", b"aaaa", b"aaaaaaa", b"aaaaaaaa", b"aaaaaaaaa", b"abcabca", b"bca",
+               b"needle", b"xneedley", b"x" * 700, b"y" * 301, b"zzzzzzzzzzzz", b".", b"co", b"svc1", b"order",
+               "été".encode(), "漢".encode(), b"controller", b"er", b"1", b"12", b"123"]
+    for i, a, l in zip(rng.integers(0, 20000, 300), rng.integers(0, 30, 300), rng.integers(1, 24, 300)):
+        queries.append(lows[int(i)][int(a):int(a) + int(l)])
+    queries += queries[:40]                                              # duplicates get their own rows
+    for kind in (dmgraph.SEARCH_CONTAINS_ALL, dmgraph.SEARCH_CONTAINS_FIRST):
+        for lo, hi in [(0, None), (3, 9), (1000, 17000), (19999, 20000), (8, 8)]:
+            o, ids = g.search_batch(kind, queries, lo, hi)
+            wo, wids = ora.search_batch(off, low, queries, kind, lo, hi, threads=8)
+            assert np.array_equal(o, wo) and np.array_equal(ids, wids)
+    # capacity protocol
+    with pytest.raises(dmgraph.DmgError) as ei:
+        g.search_batch(dmgraph.SEARCH_CONTAINS_ALL, [b"svc1"], cap=5)
+    assert ei.value.code == dmgraph.ECAP
+    g.release()
+
+
+def test_search_config3_shape_scaled(engine):
+    """BASELINE config 3's generator at 1/50 scale (200 k names, 1024 queries) against the oracle."""
+    off, arena = synth.catalog_names(200000)
+    low = np.frombuffer(bytes(arena).lower(), dtype=np.uint8).copy()
+    queries = synth.search_queries(off, arena, 1024)
+    g = dmgraph.Graph(engine, off.size - 1, [], [], [], name_off=off, name_bytes=arena, lower_bytes=low)
+    o, ids = g.search_batch(dmgraph.SEARCH_CONTAINS_ALL, queries)
+    wo, wids = ora.search_batch(off, low, queries, 0, threads=8)
+    assert np.array_equal(o, wo) and np.array_equal(ids, wids)
+    assert int(o[-1]) > 1024
+    g.release()
