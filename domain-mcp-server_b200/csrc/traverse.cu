@@ -636,13 +636,14 @@ __global__ void __launch_bounds__(KG_THREADS) khop_global_kernel(const KhopArgs 
 // copied warp-per-row.
 // ---------------------------------------------------------------------------------------------
 constexpr int ADJ_THREADS = 256;
+constexpr uint32_t ADJ_LONG_ROW = 2048;
 
 __global__ void __launch_bounds__(ADJ_THREADS) adjacency_kernel(const uint32_t* __restrict__ ptr,
                                                                 const uint32_t* __restrict__ idx, uint32_t V,
                                                                 unsigned long long n, const uint32_t* __restrict__ ids,
                                                                 unsigned long long* out_off, uint32_t* out_ids,
                                                                 unsigned long long cap, uint64_t* status,
-                                                                DevCounters* ctr) {
+                                                                DevCounters* ctr, unsigned long long* long_rows) {
   constexpr int THREADS = ADJ_THREADS, NW = THREADS / 32;
   __shared__ unsigned long long s_t, s_base;
   __shared__ uint32_t s_start[THREADS], s_len[THREADS], s_off[THREADS];
@@ -686,6 +687,15 @@ __global__ void __launch_bounds__(ADJ_THREADS) adjacency_kernel(const uint32_t* 
     for (int r = warp; r < THREADS; r += NW) {
       const uint32_t st = s_start[r], ln = s_len[r];
       const unsigned long long o = base + s_off[r];
+      if (ln > ADJ_LONG_ROW) {
+        // hub row (Zipf in-degree): left to adjacency_long_kernel, which spreads it over the grid
+        if (lane == 0) {
+          const unsigned long long slot = atomicAdd(&ctr->aux[1], 1ull);
+          long_rows[2 * slot] = ((unsigned long long)st << 32) | ln;
+          long_rows[2 * slot + 1] = o;
+        }
+        continue;
+      }
       for (uint32_t j = lane; j < ln; j += 32)
         if (o + j < cap) out_ids[o + j] = idx[st + j];
     }
@@ -694,6 +704,23 @@ __global__ void __launch_bounds__(ADJ_THREADS) adjacency_kernel(const uint32_t* 
   if (lane == 0 && te) {
     atomicAdd(&ctr->edges, te);
     atomicAdd(&ctr->aux[0], te);
+  }
+}
+
+// rows longer than ADJ_LONG_ROW: every CTA copies a slice of every such row (16-byte moves where
+// source and destination are co-aligned)
+__global__ void __launch_bounds__(256) adjacency_long_kernel(const uint32_t* __restrict__ idx,
+                                                             const unsigned long long* __restrict__ long_rows,
+                                                             const DevCounters* ctr, uint32_t* out_ids,
+                                                             unsigned long long cap) {
+  const unsigned long long n_long = ctr->aux[1];
+  const unsigned long long gtid = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x;
+  const unsigned long long gsz = (unsigned long long)gridDim.x * blockDim.x;
+  for (unsigned long long r = 0; r < n_long; ++r) {
+    const uint32_t st = (uint32_t)(long_rows[2 * r] >> 32), ln = (uint32_t)long_rows[2 * r];
+    const unsigned long long o = long_rows[2 * r + 1];
+    for (unsigned long long j = gtid; j < ln; j += gsz)
+      if (o + j < cap) out_ids[o + j] = idx[st + j];
   }
 }
 
@@ -1086,6 +1113,7 @@ int32_t dmg_adjacency_batch(dmg_graph* g, int32_t dir, uint64_t n, const uint32_
   DMG_TRY(c->q_src.reserve(n * 4));
   DMG_TRY(c->out_off.reserve((n + 1) * 8));
   DMG_TRY(c->status.reserve(n_tiles * 8));
+  DMG_TRY(c->tmp0.reserve(n * 16));   // (start, len, out offset) of rows left to adjacency_long_kernel
   DMG_CUDA(cudaMemcpyAsync(c->q_src.p, ids, n * 4, cudaMemcpyHostToDevice, c->stream));
   c->stats.h2d_bytes += n * 4;
   const uint32_t* ptr = dir == DMG_OUT ? g->d_out_ptr : g->d_in_ptr;
@@ -1105,7 +1133,14 @@ int32_t dmg_adjacency_batch(dmg_graph* g, int32_t dir, uint64_t n, const uint32_
       LaunchScope ls(c, K_ADJ_GATHER);
       adjacency_kernel<<<(unsigned)grid, ADJ_THREADS, 0, c->stream>>>(
           ptr, idx, g->info.n_vertices, n, c->q_src.as<uint32_t>(), c->out_off.as<unsigned long long>(),
-          c->out_ids.as<uint32_t>(), use_cap, c->status.as<uint64_t>(), c->d_counters);
+          c->out_ids.as<uint32_t>(), use_cap, c->status.as<uint64_t>(), c->d_counters,
+          c->tmp0.as<unsigned long long>());
+    }
+    if (use_cap) {
+      LaunchScope ls(c, K_ADJ_GATHER);
+      adjacency_long_kernel<<<g->eng->sm_count * 4, 256, 0, c->stream>>>(idx, c->tmp0.as<unsigned long long>(),
+                                                                       c->d_counters, c->out_ids.as<uint32_t>(),
+                                                                       use_cap);
     }
     DMG_CUDA(cudaGetLastError());
     DMG_TRY(fetch_counters(c));

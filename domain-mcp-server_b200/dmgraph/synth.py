@@ -308,9 +308,10 @@ def search_queries(name_off, name_bytes, n_queries=16384, seed=SEED_C3_QUERIES):
         elif kinds[qi] < 0.9:
             out.append(vocab[int(rng.integers(0, len(vocab)))].encode("ascii"))
         else:
-            i = int(rng.integers(0, n))
-            s = bytes(name_bytes[int(name_off[i]):int(name_off[i + 1])]).lower()
+            # 3-4 letters from inside a vocabulary stem (selectivity around 1e-2; a window over the
+            # constant "co.fanki.svc" prefix would match every name)
+            w = vocab[int(rng.integers(0, len(vocab)))]
             ln = int(rng.integers(3, 5))
-            st = int(rng.integers(0, max(1, len(s) - ln)))
-            out.append(s[st:st + ln])
+            st = int(rng.integers(0, len(w) - ln + 1))
+            out.append(w[st:st + ln].encode("ascii"))
     return out

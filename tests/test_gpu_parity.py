@@ -168,6 +168,23 @@ def test_adjacency_random(engine):
         g.release()
 
 
+def test_adjacency_hub_rows(engine):
+    """Zipf hubs: rows far above the per-warp copy limit go through the grid-wide copy."""
+    n = 9000
+    leaves = np.arange(1, n, dtype=np.uint32)
+    src = np.concatenate([leaves, np.zeros(3000, np.uint32), leaves[:4000]])
+    dst = np.concatenate([np.zeros(n - 1, np.uint32), np.arange(1, 3001, dtype=np.uint32), np.full(4000, 7, np.uint32)])
+    g = dmgraph.Graph(engine, n, src, dst, [])
+    o = ora.CsrOracle(n, src, dst, [])
+    ids = np.array([0, 7, 5, 0, 8999, 7, 9000, 1], np.uint32)
+    for d in (0, 1):
+        off, out = g.adjacency_batch(d, ids)
+        woff, wout = o.adjacency_batch(d, ids)
+        assert np.array_equal(off, woff) and np.array_equal(out, wout)
+    assert int(g.adjacency_batch(1, [0])[0][1]) == n - 1
+    g.release()
+
+
 def test_empty_and_ragged_inputs(engine):
     g = dmgraph.Graph(engine, 0, [], [], [])
     off, ids, hop = g.neighbors_batch(2, 1, 1, [0, 0, 2], [0, 5])
