@@ -1,0 +1,223 @@
+// Vertex-range partitioned closure (BASELINE config 5): every rank owns a contiguous
+// vertex range, holds the rows of its own vertices, and keeps V-bit frontier / visited bitmaps
+// that are replicated on all ranks.  One BFS level is
+//     expand (push or pull, this file)  ->  exchange (NCCL allgather, done by the host)  ->
+//     merge (this file: OR the gathered bitmaps, strike visited, stamp the owners' levels)
+// Push (top-down) is used while the frontier is small: a rank expands the frontier vertices it
+// owns and ORs their neighbours into a full-width contribution bitmap; the exchange gathers all
+// contribution bitmaps (NCCL has no bitwise-OR reduction).  Pull (bottom-up) is used when the
+// frontier is large: a rank looks, for each unvisited vertex it owns, for one frontier member in
+// the vertex's reverse row and writes only its own slice of the next bitmap; the exchange
+// gathers the slices.
+#include <algorithm>
+
+#include "common.cuh"
+
+namespace dmg {
+
+constexpr int CP_THREADS = 256;
+
+// one warp per 32-vertex word of the owned range
+__global__ void __launch_bounds__(CP_THREADS) part_push_kernel(const uint32_t* __restrict__ ptr,
+                                                               const uint32_t* __restrict__ idx, uint32_t w_lo,
+                                                               uint32_t w_hi, uint32_t v_lo, uint32_t v_hi,
+                                                               const uint32_t* __restrict__ frontier,
+                                                               uint32_t* contrib, DevCounters* ctr) {
+  const int lane = threadIdx.x & 31;
+  const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const uint32_t nwarps = (gridDim.x * blockDim.x) >> 5;
+  unsigned long long te = 0;
+  for (uint32_t w = w_lo + warp; w < w_hi; w += nwarps) {
+    uint32_t bits = frontier[w];
+    while (bits) {
+      const uint32_t u = w * 32 + (__ffs(bits) - 1);
+      bits &= bits - 1;
+      if (u < v_lo || u >= v_hi) continue;
+      const uint32_t b = ptr[u], n = ptr[u + 1] - b;
+      te += n;
+      for (uint32_t j = lane; j < n; j += 32) {
+        const uint32_t v = idx[b + j], bit = 1u << (v & 31);
+        if (!(__ldcg(&contrib[v >> 5]) & bit)) atomicOr(&contrib[v >> 5], bit);
+      }
+    }
+  }
+  if (lane == 0 && te) atomicAdd(&ctr->edges, te);
+}
+
+__global__ void __launch_bounds__(CP_THREADS) part_pull_kernel(const uint32_t* __restrict__ rptr,
+                                                               const uint32_t* __restrict__ ridx, uint32_t w_lo,
+                                                               uint32_t w_hi, uint32_t v_lo, uint32_t v_hi,
+                                                               const uint32_t* __restrict__ frontier,
+                                                               const uint32_t* __restrict__ visited,
+                                                               uint32_t* next_slice, DevCounters* ctr) {
+  const int lane = threadIdx.x & 31;
+  const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const uint32_t nwarps = (gridDim.x * blockDim.x) >> 5;
+  unsigned long long te = 0;
+  for (uint32_t w = w_lo + warp; w < w_hi; w += nwarps) {
+    uint32_t todo = ~visited[w];
+    uint32_t found = 0;
+    while (todo) {
+      const uint32_t bpos = __ffs(todo) - 1;
+      todo &= todo - 1;
+      const uint32_t v = w * 32 + bpos;
+      if (v < v_lo || v >= v_hi) continue;
+      const uint32_t b = rptr[v], n = rptr[v + 1] - b;
+      for (uint32_t j0 = 0; j0 < n; j0 += 32) {
+        bool hit = false;
+        if (j0 + lane < n) {
+          const uint32_t u = ridx[b + j0 + lane];
+          hit = (frontier[u >> 5] >> (u & 31)) & 1u;
+        }
+        te += min(32u, n - j0);
+        if (__any_sync(FULL, hit)) {
+          found |= 1u << bpos;
+          break;
+        }
+      }
+    }
+    if (lane == 0) next_slice[w - w_lo] = found;
+  }
+  if (lane == 0 && te) atomicAdd(&ctr->edges, te);
+}
+
+// next = (OR over the gathered bitmaps) & ~visited; visited |= next; owners stamp the level
+__global__ void __launch_bounds__(CP_THREADS) part_merge_kernel(const uint32_t* __restrict__ gathered,
+                                                                uint32_t n_gathered, uint32_t stride_words,
+                                                                uint32_t words, uint32_t* visited, uint32_t* next, uint32_t v_lo,
+                                                                uint32_t v_hi, uint32_t lvl, uint32_t* level_slice,
+                                                                DevCounters* ctr) {
+  const uint32_t w = blockIdx.x * blockDim.x + threadIdx.x;
+  uint32_t fresh = 0;
+  if (w < words) {
+    uint32_t x = 0;
+    for (uint32_t r = 0; r < n_gathered; ++r) x |= gathered[(size_t)r * stride_words + w];
+    const uint32_t vis = visited[w];
+    fresh = x & ~vis;
+    next[w] = fresh;
+    if (fresh) {
+      visited[w] = vis | fresh;
+      for (uint32_t b = fresh; b; b &= b - 1) {
+        const uint32_t v = w * 32 + (__ffs(b) - 1);
+        if (v >= v_lo && v < v_hi) level_slice[v - v_lo] = lvl;
+      }
+    }
+  }
+  const uint32_t c = warp_sum_u32(__popc(fresh));
+  if ((threadIdx.x & 31) == 0 && c) atomicAdd(&ctr->total, (unsigned long long)c);
+}
+
+static int32_t part_args(dmg_graph* g, int32_t dir, uint32_t v_lo, uint32_t v_hi, const char* who) {
+  if (!g) {
+    set_error("%s: NULL graph", who);
+    return DMG_EINVAL;
+  }
+  if (dir != DMG_OUT && dir != DMG_IN) {
+    set_error("%s: dir %d is not DMG_OUT/DMG_IN", who, dir);
+    return DMG_EINVAL;
+  }
+  if (v_lo > v_hi || v_hi > g->info.n_vertices || (v_lo & 31)) {
+    set_error("%s: owned range [%u, %u) must lie inside the graph and start on a multiple of 32", who, v_lo, v_hi);
+    return DMG_EINVAL;
+  }
+  return DMG_OK;
+}
+
+}  // namespace dmg
+
+using namespace dmg;
+
+extern "C" {
+
+int32_t dmg_closure_push_dev(dmg_graph* g, int32_t dir, uint32_t v_lo, uint32_t v_hi, const uint32_t* d_frontier_bits,
+                             uint32_t* d_contrib_bits, uint64_t* edges) {
+  DMG_TRY(part_args(g, dir, v_lo, v_hi, "dmg_closure_push_dev"));
+  if (!d_frontier_bits || !d_contrib_bits) {
+    set_error("dmg_closure_push_dev: NULL bitmap");
+    return DMG_EINVAL;
+  }
+  CtxGuard cg(g->eng);
+  CallCtx* c = cg.c;
+  if (!c) return DMG_ECUDA;
+  DMG_TRY(c->begin());
+  const uint32_t words = (g->info.n_vertices + 31) / 32;
+  DMG_CUDA(cudaMemsetAsync(d_contrib_bits, 0, (size_t)words * 4, c->stream));
+  DMG_CUDA(cudaMemsetAsync(c->d_counters, 0, sizeof(DevCounters), c->stream));
+  const uint32_t w_lo = v_lo / 32, w_hi = (v_hi + 31) / 32;
+  if (w_hi > w_lo) {
+    const uint32_t* ptr = dir == DMG_OUT ? g->d_out_ptr : g->d_in_ptr;
+    const uint32_t* idx = dir == DMG_OUT ? g->d_out_idx : g->d_in_idx;
+    const unsigned grid = (unsigned)std::min<uint64_t>(((uint64_t)(w_hi - w_lo) * 32 + CP_THREADS - 1) / CP_THREADS,
+                                                       (uint64_t)g->eng->sm_count * 8);
+    LaunchScope ls(c, K_CLOSURE_STEP);
+    part_push_kernel<<<grid, CP_THREADS, 0, c->stream>>>(ptr, idx, w_lo, w_hi, v_lo, v_hi, d_frontier_bits,
+                                                         d_contrib_bits, c->d_counters);
+  }
+  DMG_CUDA(cudaGetLastError());
+  DMG_CUDA(cudaMemcpyAsync(c->h_counters, c->d_counters, sizeof(DevCounters), cudaMemcpyDeviceToHost, c->stream));
+  DMG_TRY(c->finish());
+  if (edges) *edges = c->h_counters->edges;
+  c->stats.edges_traversed = c->stats.edges_read = c->h_counters->edges;
+  publish_stats(c->stats);
+  return DMG_OK;
+}
+
+int32_t dmg_closure_pull_dev(dmg_graph* g, int32_t dir, uint32_t v_lo, uint32_t v_hi, const uint32_t* d_frontier_bits,
+                             const uint32_t* d_visited_bits, uint32_t* d_next_slice, uint64_t* edges) {
+  DMG_TRY(part_args(g, dir, v_lo, v_hi, "dmg_closure_pull_dev"));
+  if (!d_frontier_bits || !d_visited_bits || !d_next_slice) {
+    set_error("dmg_closure_pull_dev: NULL bitmap");
+    return DMG_EINVAL;
+  }
+  CtxGuard cg(g->eng);
+  CallCtx* c = cg.c;
+  if (!c) return DMG_ECUDA;
+  DMG_TRY(c->begin());
+  DMG_CUDA(cudaMemsetAsync(c->d_counters, 0, sizeof(DevCounters), c->stream));
+  const uint32_t w_lo = v_lo / 32, w_hi = (v_hi + 31) / 32;
+  if (w_hi > w_lo) {
+    // closure over dir follows edges u -> v (OUT) : v is reached through its IN row, and vice versa
+    const uint32_t* rptr = dir == DMG_OUT ? g->d_in_ptr : g->d_out_ptr;
+    const uint32_t* ridx = dir == DMG_OUT ? g->d_in_idx : g->d_out_idx;
+    const unsigned grid = (unsigned)std::min<uint64_t>(((uint64_t)(w_hi - w_lo) * 32 + CP_THREADS - 1) / CP_THREADS,
+                                                       (uint64_t)g->eng->sm_count * 8);
+    LaunchScope ls(c, K_CLOSURE_BOTTOMUP);
+    part_pull_kernel<<<grid, CP_THREADS, 0, c->stream>>>(rptr, ridx, w_lo, w_hi, v_lo, v_hi, d_frontier_bits,
+                                                         d_visited_bits, d_next_slice, c->d_counters);
+  }
+  DMG_CUDA(cudaGetLastError());
+  DMG_CUDA(cudaMemcpyAsync(c->h_counters, c->d_counters, sizeof(DevCounters), cudaMemcpyDeviceToHost, c->stream));
+  DMG_TRY(c->finish());
+  if (edges) *edges = c->h_counters->edges;
+  c->stats.edges_read = c->h_counters->edges;
+  publish_stats(c->stats);
+  return DMG_OK;
+}
+
+int32_t dmg_closure_merge_dev(dmg_graph* g, uint32_t v_lo, uint32_t v_hi, uint32_t lvl, const uint32_t* d_gathered,
+                              uint32_t n_gathered, uint32_t stride_words, uint32_t* d_visited_bits, uint32_t* d_next_bits,
+                              uint32_t* d_level_slice, uint64_t* n_new) {
+  DMG_TRY(part_args(g, DMG_OUT, v_lo, v_hi, "dmg_closure_merge_dev"));
+  if (!d_gathered || !n_gathered || stride_words < (g->info.n_vertices + 31) / 32 || !d_visited_bits || !d_next_bits || !d_level_slice || !n_new) {
+    set_error("dmg_closure_merge_dev: NULL argument");
+    return DMG_EINVAL;
+  }
+  CtxGuard cg(g->eng);
+  CallCtx* c = cg.c;
+  if (!c) return DMG_ECUDA;
+  DMG_TRY(c->begin());
+  DMG_CUDA(cudaMemsetAsync(c->d_counters, 0, sizeof(DevCounters), c->stream));
+  const uint32_t words = (g->info.n_vertices + 31) / 32;
+  if (words) {
+    LaunchScope ls(c, K_MISC);
+    part_merge_kernel<<<(words + CP_THREADS - 1) / CP_THREADS, CP_THREADS, 0, c->stream>>>(
+        d_gathered, n_gathered, stride_words, words, d_visited_bits, d_next_bits, v_lo, v_hi, lvl, d_level_slice, c->d_counters);
+  }
+  DMG_CUDA(cudaGetLastError());
+  DMG_CUDA(cudaMemcpyAsync(c->h_counters, c->d_counters, sizeof(DevCounters), cudaMemcpyDeviceToHost, c->stream));
+  DMG_TRY(c->finish());
+  *n_new = c->h_counters->total;
+  return DMG_OK;
+}
+
+}  // extern "C"

@@ -78,6 +78,9 @@ def lib():
             "dmg_neighbors_batch_dev_static": (i32, [vp, i32, i32, i32, u64, vp, vp, vp, vp, vp, u64, pu64]),
             "dmg_closure": (i32, [vp, i32, u32, vp, vp, pu64]),
             "dmg_analysis_order": (i32, [vp, vp]),
+            "dmg_closure_push_dev": (i32, [vp, i32, u32, u32, vp, vp, pu64]),
+            "dmg_closure_pull_dev": (i32, [vp, i32, u32, u32, vp, vp, vp, pu64]),
+            "dmg_closure_merge_dev": (i32, [vp, u32, u32, u32, vp, u32, u32, vp, vp, vp, pu64]),
             "dmg_entry_points": (i32, [vp, vp, u32, C.POINTER(u32)]),
             "dmg_is_entry_point_batch": (i32, [vp, u64, vp, vp]),
             "dmg_search_batch": (i32, [vp, i32, u32, u32, u64, vp, vp, vp, vp, u64, pu64]),
@@ -301,6 +304,25 @@ class Graph:
         reached = C.c_uint64(0)
         _check(self.L.dmg_closure(self.h, direction, s.size, _ptr(s), level.ctypes.data, C.byref(reached)))
         return level[:self.V], reached.value
+
+    def closure_push_dev(self, direction, v_lo, v_hi, d_frontier, d_contrib):
+        e = C.c_uint64(0)
+        _check(self.L.dmg_closure_push_dev(self.h, direction, v_lo, v_hi, C.c_void_p(d_frontier),
+                                           C.c_void_p(d_contrib), C.byref(e)))
+        return e.value
+
+    def closure_pull_dev(self, direction, v_lo, v_hi, d_frontier, d_visited, d_next_slice):
+        e = C.c_uint64(0)
+        _check(self.L.dmg_closure_pull_dev(self.h, direction, v_lo, v_hi, C.c_void_p(d_frontier),
+                                           C.c_void_p(d_visited), C.c_void_p(d_next_slice), C.byref(e)))
+        return e.value
+
+    def closure_merge_dev(self, v_lo, v_hi, lvl, d_gathered, n_gathered, stride_words, d_visited, d_next, d_level):
+        n = C.c_uint64(0)
+        _check(self.L.dmg_closure_merge_dev(self.h, v_lo, v_hi, lvl, C.c_void_p(d_gathered), n_gathered,
+                                            stride_words, C.c_void_p(d_visited), C.c_void_p(d_next),
+                                            C.c_void_p(d_level), C.byref(n)))
+        return n.value
 
     def analysis_order(self):
         order = np.zeros(max(1, self.V), np.uint32)

@@ -1,0 +1,117 @@
+"""Vertex-range partitioned closure over the GPUs of one box (BASELINE config 5).
+
+One process per GPU (torchrun).  torch.distributed is the plumbing only: it owns the bitmap
+tensors and runs the per-level allgather (NCCL over NVLink; gloo in the CPU tests).  Every level's
+work -- push / pull expansion, merge, level stamping -- is the C ABI's
+dmg_closure_push_dev / dmg_closure_pull_dev / dmg_closure_merge_dev on this rank's device.
+
+    rank r owns vertex words [r*Wr, (r+1)*Wr)  (Wr = ceil(ceil(V/32) / world), 32 vertices a word)
+    frontier / visited / next : world*Wr words, replicated on every rank
+    per level:  push  -> all_gather(full contribution bitmaps) -> merge(OR of `world` bitmaps)
+                pull  -> all_gather(own slices)                -> merge(1 bitmap)
+"""
+import numpy as np
+
+OUT, IN = 0, 1
+
+
+def partition(n_vertices, rank, world):
+    """(words_per_rank, v_lo, v_hi) of `rank`; ranges start on multiples of 32."""
+    words = (n_vertices + 31) // 32
+    wr = max(1, (words + world - 1) // world)
+    v_lo = min(n_vertices, rank * wr * 32)
+    v_hi = min(n_vertices, (rank + 1) * wr * 32)
+    return wr, v_lo, v_hi
+
+
+def owned_edges(src, dst, v_lo, v_hi):
+    """Edges a rank uploads: every edge with an endpoint in its range, original order kept, so
+    the out rows and the in rows of its own vertices are complete."""
+    src = np.asarray(src)
+    dst = np.asarray(dst)
+    keep = ((src >= v_lo) & (src < v_hi)) | ((dst >= v_lo) & (dst < v_hi))
+    return src[keep], dst[keep]
+
+
+class GpuStepper:
+    """Level primitives on this rank's GPU through the C ABI; bitmaps are torch CUDA int32 tensors."""
+
+    def __init__(self, graph, v_lo, v_hi):
+        self.g, self.v_lo, self.v_hi = graph, v_lo, v_hi
+
+    def push(self, direction, frontier, contrib):
+        import torch
+        torch.cuda.current_stream().synchronize()
+        return self.g.closure_push_dev(direction, self.v_lo, self.v_hi, frontier.data_ptr(), contrib.data_ptr())
+
+    def pull(self, direction, frontier, visited, next_slice):
+        import torch
+        torch.cuda.current_stream().synchronize()
+        return self.g.closure_pull_dev(direction, self.v_lo, self.v_hi, frontier.data_ptr(), visited.data_ptr(),
+                                       next_slice.data_ptr())
+
+    def merge(self, lvl, gathered, n_gathered, stride, visited, nxt, level_slice):
+        import torch
+        torch.cuda.current_stream().synchronize()
+        return self.g.closure_merge_dev(self.v_lo, self.v_hi, lvl, gathered.data_ptr(), n_gathered, stride,
+                                        visited.data_ptr(), nxt.data_ptr(), level_slice.data_ptr())
+
+
+class PartitionedClosure:
+    """BFS levels from a source set over `direction`, the graph split by vertex range over ranks."""
+
+    PUSH_BELOW = 1.0 / 32     # push while the frontier is below this fraction of V
+
+    def __init__(self, n_vertices, rank, world, stepper, device, dist=None):
+        import torch
+        self.torch, self.dist = torch, dist
+        self.V, self.rank, self.world, self.stepper = n_vertices, rank, world, stepper
+        self.wr, self.v_lo, self.v_hi = partition(n_vertices, rank, world)
+        self.words = self.wr * world                    # padded bitmap width
+        z = lambda n: torch.zeros(max(n, 1), dtype=torch.int32, device=device)
+        self.frontier, self.visited, self.next = z(self.words), z(self.words), z(self.words)
+        self.contrib = z(self.words)
+        self.gather_push = z(self.words * world)
+        self.slice = z(self.wr)
+        self.level = torch.full((max(self.v_hi - self.v_lo, 1),), -1, dtype=torch.int32, device=device)
+        self.stats = {"levels": 0, "push_levels": 0, "pull_levels": 0, "edges": 0, "exchanged_bytes": 0}
+
+    def _allgather(self, out, inp):
+        if self.dist is None or self.world == 1:
+            out.copy_(inp.repeat(out.numel() // inp.numel())[:out.numel()] if out.numel() != inp.numel() else inp)
+        else:
+            self.dist.all_gather_into_tensor(out, inp)
+        self.stats["exchanged_bytes"] += out.numel() * 4
+
+    def run(self, sources, direction=OUT):
+        torch = self.torch
+        bits = np.zeros(self.words, np.uint32)
+        s = np.unique(np.asarray(sources, dtype=np.int64))
+        s = s[(s >= 0) & (s < self.V)]
+        np.bitwise_or.at(bits, s >> 5, (1 << (s & 31)).astype(np.uint32))
+        t = torch.from_numpy(bits.view(np.int32)).to(self.frontier.device)
+        self.frontier.copy_(t)
+        self.visited.copy_(t)
+        self.level.fill_(-1)
+        own = s[(s >= self.v_lo) & (s < self.v_hi)] - self.v_lo
+        if own.size:
+            self.level[torch.from_numpy(own).to(self.level.device)] = 0
+        n_front, reached, lvl = int(s.size), int(s.size), 1
+        while n_front > 0:
+            if n_front < self.PUSH_BELOW * self.V:
+                self.stats["edges"] += self.stepper.push(direction, self.frontier, self.contrib)
+                self._allgather(self.gather_push, self.contrib)
+                n_new = self.stepper.merge(lvl, self.gather_push, self.world, self.words, self.visited, self.next,
+                                           self.level)
+                self.stats["push_levels"] += 1
+            else:
+                self.stats["edges"] += self.stepper.pull(direction, self.frontier, self.visited, self.slice)
+                self._allgather(self.contrib, self.slice)      # contrib doubles as the gathered next bitmap
+                n_new = self.stepper.merge(lvl, self.contrib, 1, self.words, self.visited, self.next, self.level)
+                self.stats["pull_levels"] += 1
+            self.frontier, self.next = self.next, self.frontier
+            n_front = int(n_new)
+            reached += n_front
+            lvl += 1
+        self.stats["levels"] = lvl - 1
+        return self.level[: self.v_hi - self.v_lo], reached

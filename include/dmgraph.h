@@ -206,6 +206,31 @@ int32_t dmg_closure(dmg_graph* g, int32_t dir, uint32_t n_src, const uint32_t* s
                     uint32_t* out_level, uint64_t* reached);
 int32_t dmg_analysis_order(dmg_graph* g, uint32_t* out_order);
 
+/* ---- vertex-range partitioned closure (BASELINE config 5) ---------------------
+ * For the graph that is split over the GPUs of one box.  Rank r owns vertices [v_lo, v_hi)
+ * (v_lo a multiple of 32) and creates its dmg_graph from the FULL vertex count but only the
+ * edges with an endpoint in its range, so the rows of its own vertices are complete.  Frontier
+ * and visited sets are V-bit bitmaps (uint32 words, bit v&31 of word v>>5) replicated on every
+ * rank in DEVICE memory the host owns.  One level of the reference's BFS (PG:403-413) is:
+ *   push  each rank ORs the `dir` neighbours of the frontier vertices it owns into its own
+ *         full-width contribution bitmap (cleared by the call)            -> allgather all of them
+ *   pull  each rank finds, for every unvisited vertex it owns, one frontier member in the
+ *         vertex's reverse row and writes words [v_lo/32, ceil(v_hi/32)) of the next bitmap
+ *         into d_next_slice                                               -> allgather the slices
+ *   merge next = OR(gathered) & ~visited; visited |= next; the owner stamps `lvl` into
+ *         d_level_slice[v - v_lo]; *n_new = |next| (identical on all ranks)
+ * The exchange between expand and merge is the host's (ncclAllGather over NVLink in
+ * dmgraph/dist.py); push suits small frontiers, pull large ones; the results are the same.    */
+int32_t dmg_closure_push_dev(dmg_graph* g, int32_t dir, uint32_t v_lo, uint32_t v_hi,
+                             const uint32_t* d_frontier_bits, uint32_t* d_contrib_bits, uint64_t* edges);
+int32_t dmg_closure_pull_dev(dmg_graph* g, int32_t dir, uint32_t v_lo, uint32_t v_hi,
+                             const uint32_t* d_frontier_bits, const uint32_t* d_visited_bits,
+                             uint32_t* d_next_slice, uint64_t* edges);
+int32_t dmg_closure_merge_dev(dmg_graph* g, uint32_t v_lo, uint32_t v_hi, uint32_t lvl,
+                              const uint32_t* d_gathered, uint32_t n_gathered, uint32_t stride_words,
+                              uint32_t* d_visited_bits, uint32_t* d_next_bits, uint32_t* d_level_slice,
+                              uint64_t* n_new);
+
 /* entryPoints() (PG:345-347), insertion order; isEntryPoint (PG:336-338) as a byte per id. */
 int32_t dmg_entry_points(dmg_graph* g, uint32_t* out_ids, uint32_t cap, uint32_t* needed);
 int32_t dmg_is_entry_point_batch(dmg_graph* g, uint64_t n, const uint32_t* ids, uint8_t* out_flags);

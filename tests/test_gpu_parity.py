@@ -357,3 +357,65 @@ def test_search_config3_shape_scaled(engine):
     assert np.array_equal(o, wo) and np.array_equal(ids, wids)
     assert int(o[-1]) > 1024
     g.release()
+
+
+# ---- vertex-range partitioned closure, two ranks emulated on one GPU ----------------
+@pytest.mark.parametrize("direction", [0, 1])
+def test_partitioned_closure_two_ranks_lockstep(engine, direction):
+    import torch
+    from dmgraph import dist as ddist
+    rng = np.random.default_rng(40 + direction)
+    n, e = 5000, 14000
+    src, dst, entry, _ = _random_graph(rng, n, e, 1)
+    sources = rng.integers(0, n, 4).astype(np.uint32)
+    world = 2
+    ranks = []
+    for r in range(world):
+        wr, v_lo, v_hi = ddist.partition(n, r, world)
+        s_own, d_own = ddist.owned_edges(src, dst, v_lo, v_hi)
+        g = dmgraph.Graph(engine, n, s_own, d_own, [])
+        pc = ddist.PartitionedClosure(n, r, world, ddist.GpuStepper(g, v_lo, v_hi), "cuda", None)
+        ranks.append((g, pc))
+    words = ranks[0][1].words
+    bits = np.zeros(words, np.uint32)
+    s = np.unique(sources.astype(np.int64))
+    np.bitwise_or.at(bits, s >> 5, (1 << (s & 31)).astype(np.uint32))
+    for g, pc in ranks:
+        t = torch.from_numpy(bits.view(np.int32)).cuda()
+        pc.frontier.copy_(t)
+        pc.visited.copy_(t)
+        own = s[(s >= pc.v_lo) & (s < pc.v_hi)] - pc.v_lo
+        if own.size:
+            pc.level[torch.from_numpy(own).cuda()] = 0
+    lvl, n_front, reached = 1, int(s.size), int(s.size)
+    while n_front > 0:
+        news = []
+        if lvl % 2 == 1:                                                   # push level
+            for g, pc in ranks:
+                pc.stepper.push(direction, pc.frontier, pc.contrib)
+            gathered = torch.cat([pc.contrib for _g, pc in ranks])
+            for g, pc in ranks:
+                news.append(pc.stepper.merge(lvl, gathered, world, words, pc.visited, pc.next, pc.level))
+        else:                                                              # pull level
+            for g, pc in ranks:
+                pc.stepper.pull(direction, pc.frontier, pc.visited, pc.slice)
+            gathered = torch.cat([pc.slice for _g, pc in ranks])
+            for g, pc in ranks:
+                news.append(pc.stepper.merge(lvl, gathered, 1, words, pc.visited, pc.next, pc.level))
+        assert len(set(news)) == 1
+        for g, pc in ranks:
+            pc.frontier, pc.next = pc.next, pc.frontier
+        n_front = news[0]
+        reached += n_front
+        lvl += 1
+    want, wreached, _ = ora.CsrOracle(n, src, dst).closure(direction, sources)
+    level = np.concatenate([pc.level[: pc.v_hi - pc.v_lo].cpu().numpy().view(np.uint32) for _g, pc in ranks])
+    assert reached == wreached and np.array_equal(level, want)
+    # the single-rank class end to end
+    g1 = dmgraph.Graph(engine, n, src, dst, [])
+    pc1 = ddist.PartitionedClosure(n, 0, 1, ddist.GpuStepper(g1, 0, n), "cuda", None)
+    lv1, r1 = pc1.run(sources, direction)
+    assert r1 == wreached and np.array_equal(lv1.cpu().numpy().view(np.uint32), want)
+    for g, _pc in ranks:
+        g.release()
+    g1.release()
