@@ -172,6 +172,10 @@ struct dmg_graph {
   uint32_t* d_entry_bits = nullptr;  // [ceil(V/32)]
   uint64_t* d_name_off = nullptr;  // [V+1] or null
   uint8_t* d_lower = nullptr;      // pre-lowered name arena (+16 B zero pad)
+  uint32_t* d_method_off = nullptr;  // [V+1] optional method catalog (names only)
+  uint32_t* d_mname_off = nullptr;   // [M+1]
+  uint8_t* d_mname_lower = nullptr;
+  uint32_t n_methods = 0;
   std::vector<uint32_t> h_part_off, h_entry;
 };
 

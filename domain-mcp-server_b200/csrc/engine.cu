@@ -155,7 +155,7 @@ static void free_graph(dmg_graph* g) {
   cudaSetDevice(g->eng->device);
   for (void* p : {(void*)g->d_out_ptr, (void*)g->d_out_idx, (void*)g->d_in_ptr, (void*)g->d_in_idx,
                   (void*)g->d_und_ptr, (void*)g->d_und_idx, (void*)g->d_part_off, (void*)g->d_entry, (void*)g->d_entry_bits, (void*)g->d_name_off,
-                  (void*)g->d_lower})
+                  (void*)g->d_lower, (void*)g->d_method_off, (void*)g->d_mname_off, (void*)g->d_mname_lower})
     if (p) cudaFree(p);
   delete g;
 }

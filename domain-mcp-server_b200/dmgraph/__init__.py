@@ -42,6 +42,15 @@ class GraphInfo(C.Structure):
                 ("duplicate_edges", C.c_uint64), ("name_bytes", C.c_uint64), ("device_bytes", C.c_uint64)]
 
 
+class QueryOp(C.Structure):
+    _fields_ = [("opcode", C.c_uint32), ("vertex", C.c_uint32), ("mode", C.c_uint32), ("k", C.c_uint32),
+                ("exclude_sources", C.c_uint32), ("text_begin", C.c_uint32), ("text_end", C.c_uint32),
+                ("reserved", C.c_uint32)]
+
+
+OP_DEPENDENCIES, OP_DEPENDENTS, OP_OVERVIEW, OP_KHOP, OP_ENTRYPOINTS, OP_RESOLVE_NAME, OP_METHOD = range(7)
+
+
 class CallStats(C.Structure):
     _fields_ = [("kernel_launches", C.c_uint64), ("edges_traversed", C.c_uint64), ("edges_read", C.c_uint64),
                 ("rows_expanded", C.c_uint64),
@@ -84,6 +93,8 @@ def lib():
             "dmg_entry_points": (i32, [vp, vp, u32, C.POINTER(u32)]),
             "dmg_is_entry_point_batch": (i32, [vp, u64, vp, vp]),
             "dmg_search_batch": (i32, [vp, i32, u32, u32, u64, vp, vp, vp, vp, u64, pu64]),
+            "dmg_query_batch": (i32, [vp, u64, vp, vp, vp, vp, vp, u64, pu64]),
+            "dmg_graph_set_methods": (i32, [vp, vp, vp, vp]),
             "dmg_last_call_stats": (i32, [vp, C.POINTER(CallStats)]),
             "dmg_profile_enable": (i32, [vp, i32]),
             "dmg_profile_reset": (i32, [vp]),
@@ -340,6 +351,47 @@ class Graph:
         out = np.zeros(max(1, ids.size), np.uint8)
         _check(self.L.dmg_is_entry_point_batch(self.h, ids.size, _ptr(ids), out.ctypes.data))
         return out[:ids.size]
+
+    # -- Q1 ------------------------------------------------------------------------------------
+    def set_methods(self, methods_per_vertex):
+        """methods_per_vertex: list (len V) of lists of method names; lower-cased here (ASCII)."""
+        mo = np.zeros(self.V + 1, np.uint32)
+        names = []
+        for v, ms in enumerate(methods_per_vertex):
+            names.extend(ms)
+            mo[v + 1] = len(names)
+        enc = [m.lower().encode("utf-8") for m in names]
+        no = np.zeros(len(enc) + 1, np.uint32)
+        if enc:
+            np.cumsum([len(b) for b in enc], out=no[1:])
+        lb = np.frombuffer(b"".join(enc) + b"\0", dtype=np.uint8).copy()
+        _check(self.L.dmg_graph_set_methods(self.h, mo.ctypes.data, no.ctypes.data, lb.ctypes.data))
+
+    def query_batch(self, ops):
+        """ops: list of dicts {op, vertex?, mode?, k?, exclude?, text?(bytes)}; returns rows of (id, aux)."""
+        n = len(ops)
+        arr = (QueryOp * max(n, 1))()
+        text = bytearray()
+        for i, o in enumerate(ops):
+            a = arr[i]
+            a.opcode = o["op"]
+            a.vertex = o.get("vertex", 0xFFFFFFFF)
+            a.mode, a.k, a.exclude_sources = o.get("mode", 0), o.get("k", 1), int(o.get("exclude", 0))
+            t = o.get("text", b"")
+            a.text_begin = len(text)
+            text += t
+            a.text_end = len(text)
+        tb = np.frombuffer(bytes(text) + b"\0", dtype=np.uint8).copy()
+        off = np.zeros(n + 1, np.uint64)
+        need = C.c_uint64(0)
+        rc = self.L.dmg_query_batch(self.h, n, arr, tb.ctypes.data, off.ctypes.data, None, None, 0, C.byref(need))
+        _check(rc, allow=(ECAP,))
+        cap = need.value
+        ids, aux = np.zeros(max(1, cap), np.uint32), np.zeros(max(1, cap), np.uint8)
+        _check(self.L.dmg_query_batch(self.h, n, arr, tb.ctypes.data, off.ctypes.data, ids.ctypes.data,
+                                      aux.ctypes.data, cap, C.byref(need)))
+        return [(ids[int(off[i]):int(off[i + 1])].tolist(), aux[int(off[i]):int(off[i + 1])].tolist())
+                for i in range(n)]
 
     # -- S1/S2 ---------------------------------------------------------------------------------
     def search_batch(self, kind, queries, v_lo=0, v_hi=None, cap=None):

@@ -245,6 +245,51 @@ int32_t dmg_search_batch(dmg_graph* g, int32_t kind, uint32_t v_lo, uint32_t v_h
                          const uint32_t* q_off, const uint8_t* q_bytes, uint64_t* out_off,
                          uint32_t* out_ids, uint64_t cap, uint64_t* needed);
 
+/* ---- Q1: graph_query execution (GQS:53-73, 111-150, 195-394) ---------------------------------
+ * The DSL lexer (GraphQuery.parse, GQ:95-163) stays in the host; what reaches the engine is a
+ * batch of already-tokenised operations.  Row i of the output answers ops[i]:
+ *   DMG_OP_DEPENDENCIES  vertexDeps(outgoing)  GQS:298-322  ids in addDependency order, aux 0
+ *   DMG_OP_DEPENDENTS    vertexDeps(incoming)  GQS:298-322  ids ascending, aux 0
+ *   DMG_OP_OVERVIEW      vertexOverview        GQS:243-265  dependencies (aux 0) then dependents (aux 1)
+ *   DMG_OP_KHOP          directed / undirected k-hop extension of the same primitives (SURVEY.md
+ *                        8a T4; k = 1 is the reference): mode in `mode`, hops in `k`, aux = hop
+ *   DMG_OP_ENTRYPOINTS   executeEntrypoints    GQS:152-191  entry ids in insertion order, aux 0
+ *   DMG_OP_RESOLVE_NAME  resolveClassName steps 2 and 3, GQS:431-453 (the exact-id step 1 is the
+ *                        host's map lookup): text = lower-cased target; at most one id; aux = 2 when
+ *                        the simple name matched, 3 when only the containment scan did
+ *   DMG_OP_METHOD        executeMethodCheck / vertexSingleMethod, GQS:324-394: text = lower-cased
+ *                        method name; the row holds the catalog index of the first method of
+ *                        `vertex` whose lower-cased name equals it (empty row = not found)
+ * text of an op is text_bytes[text_begin .. text_end).  Unknown vertices give empty rows.      */
+#define DMG_OP_DEPENDENCIES 0
+#define DMG_OP_DEPENDENTS 1
+#define DMG_OP_OVERVIEW 2
+#define DMG_OP_KHOP 3
+#define DMG_OP_ENTRYPOINTS 4
+#define DMG_OP_RESOLVE_NAME 5
+#define DMG_OP_METHOD 6
+
+typedef struct dmg_query_op {
+  uint32_t opcode;
+  uint32_t vertex;
+  uint32_t mode;            /* DMG_OP_KHOP: DMG_OUT / DMG_IN / DMG_BOTH */
+  uint32_t k;               /* DMG_OP_KHOP: hops */
+  uint32_t exclude_sources; /* DMG_OP_KHOP */
+  uint32_t text_begin;
+  uint32_t text_end;
+  uint32_t reserved;
+} dmg_query_op;
+
+int32_t dmg_query_batch(dmg_graph* g, uint64_t n_ops, const dmg_query_op* ops, const uint8_t* text_bytes,
+                        uint64_t* out_off, uint32_t* out_ids, uint8_t* out_aux, uint64_t cap, uint64_t* needed);
+
+/* Method catalog of a graph (ProjectGraph.methodInfoMap, PG:112; names only -- descriptions and
+ * business logic stay host payload): methods of vertex v are catalog entries
+ * [method_off[v], method_off[v+1]), entry m's lower-cased name is
+ * lower_bytes[name_off[m] .. name_off[m+1]).  Optional; needed only by DMG_OP_METHOD.           */
+int32_t dmg_graph_set_methods(dmg_graph* g, const uint32_t* method_off, const uint32_t* name_off,
+                              const uint8_t* lower_bytes);
+
 /* ---- measurement -----------------------------------------------------------------------------*/
 int32_t dmg_last_call_stats(dmg_engine* e, dmg_call_stats* out);
 /* Per-kernel CUDA-event timing (events on the stream each kernel is launched on).  While

@@ -113,3 +113,58 @@ class _Names:
 
     def __getitem__(self, v):
         return self.pg.name_of(int(v))
+
+
+class EngineQueryService:
+    """GraphQueryService.execute (GQS:53-73) over dmg_query_batch: the lexer and the exact-id lookup
+    stay on the host (here: oracle-free Python), every graph read is one batched device call."""
+
+    def __init__(self, eg, methods=None):
+        self.eg = eg
+        self.methods = methods or {}
+        names = eg.identifiers()
+        eg.graph().set_methods([self.methods.get(n, []) for n in names])
+        self.catalog = [m for n in names for m in self.methods.get(n, [])]
+
+    def resolve(self, target):
+        if self.eg.pg.contains(target):
+            return self.eg.pg.id_of(target)
+        (ids, aux), = self.eg.graph().query_batch([{"op": dmgraph.OP_RESOLVE_NAME, "text": target.lower().encode()}])
+        return ids[0] if ids else None
+
+    def execute(self, tokens):
+        """tokens: [(kind, value)] after the project segment, as GraphQuery.parse yields them."""
+        g, names = self.eg.graph(), self.eg.names
+        navs = [v for k, v in tokens if k == "NAVIGATE"]
+        checks = [v for k, v in tokens if k == "CHECK"]
+        head = navs[0].lower()
+        if head == "entrypoints":
+            (ids, _), = g.query_batch([{"op": dmgraph.OP_ENTRYPOINTS}])
+            return "entrypoints", [names[i] for i in ids]
+        if head == "classes":
+            return "classes", self.eg.identifiers()
+        v = self.resolve(navs[0])
+        if v is None:
+            raise LookupError("CLASS_NOT_FOUND")
+        if checks:
+            (ids, _), = g.query_batch([{"op": dmgraph.OP_METHOD, "vertex": v, "text": checks[0].lower().encode()}])
+            return "check", (bool(ids), self.catalog[ids[0]] if ids else None)
+        sub = navs[1].lower() if len(navs) > 1 else None
+        if sub == "dependencies":
+            (ids, _), = g.query_batch([{"op": dmgraph.OP_DEPENDENCIES, "vertex": v}])
+            return "dependencies", [names[i] for i in ids]
+        if sub == "dependents":
+            (ids, _), = g.query_batch([{"op": dmgraph.OP_DEPENDENTS, "vertex": v}])
+            return "dependents", [names[i] for i in ids]
+        if sub == "method":
+            if len(navs) < 3:
+                raise ValueError("INVALID_QUERY")
+            (ids, _), = g.query_batch([{"op": dmgraph.OP_METHOD, "vertex": v, "text": navs[2].lower().encode()}])
+            if not ids:
+                raise LookupError("METHOD_NOT_FOUND")
+            return "method", self.catalog[ids[0]]
+        if sub == "methods":
+            return "methods", self.methods.get(names[v], [])
+        (ids, aux), = g.query_batch([{"op": dmgraph.OP_OVERVIEW, "vertex": v}])
+        return "class", {"className": names[v], "dependencies": [names[i] for i, a in zip(ids, aux) if a == 0],
+                         "dependents": [names[i] for i, a in zip(ids, aux) if a == 1]}

@@ -252,13 +252,13 @@ case("gq_vertex_unknown", GQT + ":288-298", GQ_GRAPH,
 case("gq_vertex_dependencies", GQT + ":329-343", GQ_GRAPH,
      [{"op": "vertexDeps", "arg": "UserController", "outgoing": True, "count": 1,
        "list": ["co.fanki.UserService"]}])
-case("gq_vertex_dependents", GQT + ":346-358", GQ_GRAPH,
+case("gq_vertex_dependents", GQT + ":345-358", GQ_GRAPH,
      [{"op": "vertexDeps", "arg": "UserService", "outgoing": False, "count": 1,
        "list": ["co.fanki.UserController"]}])
-case("gq_check_exists", GQT + ":414-431", GQ_GRAPH,
+case("gq_check_exists", GQT + ":414-428", GQ_GRAPH,
      [{"op": "methodCheck", "arg": "UserController", "check": "createUser", "exists": True,
        "methodName": "createUser"}], methods=GQ_METHODS)
-case("gq_check_missing", GQT + ":434-446", GQ_GRAPH,
+case("gq_check_missing", GQT + ":431-443", GQ_GRAPH,
      [{"op": "methodCheck", "arg": "UserController", "check": "deleteUser", "exists": False}],
      methods=GQ_METHODS)
 

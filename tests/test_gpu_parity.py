@@ -419,3 +419,92 @@ def test_partitioned_closure_two_ranks_lockstep(engine, direction):
     for g, _pc in ranks:
         g.release()
     g1.release()
+
+
+# ---- Q1: graph_query execution (GraphQueryServiceTest.java) -----------------------------------
+def _gq_service(engine):
+    from engine_adapter import EngineQueryService
+    case = next(c for c in CASES if c["name"] == "gq_check_exists")
+    eg = gr.build(case, EngineGraph(engine))
+    return EngineQueryService(eg, case["methods"])
+
+
+def test_graph_query_cases_from_reference_tests(engine):
+    svc = _gq_service(engine)
+    run = lambda q: svc.execute(pyref.parse_graph_query(q)[1])
+    assert run("my-project:classes") == ("classes", ["co.fanki.UserController", "co.fanki.UserService",
+                                                     "co.fanki.UserRepository", "co.fanki.UserDto"])   # GQT:163-175
+    assert run("my-project:entrypoints") == ("entrypoints", ["co.fanki.UserController"])               # GQT:222-236
+    assert run("my-project:UserService")[1]["className"] == "co.fanki.UserService"                     # GQT:258-271
+    assert run("my-project:co.fanki.UserService")[1]["className"] == "co.fanki.UserService"            # GQT:274-285
+    with pytest.raises(LookupError):                                                                    # GQT:288-298
+        run("my-project:Unknown")
+    assert run("my-project:UserController:dependencies") == ("dependencies", ["co.fanki.UserService"])  # GQT:329-343
+    assert run("my-project:UserService:dependents") == ("dependents", ["co.fanki.UserController"])      # GQT:346-358
+    assert run("my-project:UserController:method:createUser") == ("method", "createUser")               # GQT:361-376
+    with pytest.raises(LookupError):                                                                    # GQT:379-391
+        run("my-project:UserController:method:nope")
+    ov = run("my-project:UserController")                                                               # GQT:394-411
+    assert ov[0] == "class" and ov[1]["dependencies"] == ["co.fanki.UserService"] and ov[1]["dependents"] == []
+    assert run("my-project:UserController:?createUser") == ("check", (True, "createUser"))              # GQT:414-428
+    assert run("my-project:UserController:?deleteUser") == ("check", (False, None))                     # GQT:431-443
+    assert run("my-project:UserController:?getUsers") == ("check", (True, "getUsers"))                  # GQT:446-460
+    assert run("my-project:UserController:?GETUSERS") == ("check", (True, "getUsers"))                  # GQS:366-371
+    assert run("my-project:usercontroller:DEPENDENCIES")[1] == ["co.fanki.UserService"]                 # case-insensitive
+    assert run("my-project:UserController:whatever")[0] == "class"                                      # GQS:238-239
+
+
+def test_query_batch_mixed_ops_against_oracle(engine):
+    """A BASELINE config 4 style mix in ONE call; every row against the restatements."""
+    rng = np.random.default_rng(4)
+    n, e = 4000, 30000
+    src, dst, entry, _ = _random_graph(rng, n, e, 1)
+    names = ["p.k%d.Cls%d" % (i % 7, i if i % 50 else i // 50) for i in range(n)]     # repeated simple names
+    off, arena = synth.pack_names(names)
+    low = np.frombuffer(bytes(arena).lower(), dtype=np.uint8).copy()
+    g = dmgraph.Graph(engine, n, src, dst, entry, name_off=off, name_bytes=arena)
+    meths = [["m%d" % j if (v + j) % 3 else "Handle%d" % (v % 5) for j in range(v % 4)] for v in range(n)]
+    g.set_methods(meths)
+    catalog = [m for ms in meths for m in ms]
+    o = ora.CsrOracle(n, src, dst, entry)
+    ops, want = [], []
+    for i in range(600):
+        kind = i % 7
+        v = int(rng.integers(0, n + 2))
+        if kind == 0:
+            ops.append({"op": dmgraph.OP_DEPENDENCIES, "vertex": v})
+            want.append((o.adjacency_batch(0, [v])[1].tolist(), None))
+        elif kind == 1:
+            ops.append({"op": dmgraph.OP_DEPENDENTS, "vertex": v})
+            want.append((o.adjacency_batch(1, [v])[1].tolist(), None))
+        elif kind == 2:
+            ops.append({"op": dmgraph.OP_OVERVIEW, "vertex": v})
+            a, b = o.adjacency_batch(0, [v])[1].tolist(), o.adjacency_batch(1, [v])[1].tolist()
+            want.append((a + b, [0] * len(a) + [1] * len(b)))
+        elif kind == 3:
+            mode, k, ex = int(rng.integers(0, 3)), int(rng.integers(1, 4)), int(rng.integers(0, 2))
+            ops.append({"op": dmgraph.OP_KHOP, "vertex": v, "mode": mode, "k": k, "exclude": ex})
+            _o, ids, hop, _ = o.khop_batch(mode, k, ex, [0, 1], [v])
+            want.append((ids.tolist(), hop.tolist()))
+        elif kind == 4:
+            ops.append({"op": dmgraph.OP_ENTRYPOINTS})
+            want.append((o.entry_points().tolist(), None))
+        elif kind == 5:
+            t = ["cls%d" % rng.integers(0, 90), "k3.cls", "nosuch", "CLS7".lower(), "p.k1"][int(rng.integers(0, 5))].encode()
+            ops.append({"op": dmgraph.OP_RESOLVE_NAME, "text": t})
+            _o1, i1 = ora.search_batch(off, low, [t], 1)
+            _o2, i2 = ora.search_batch(off, low, [t], 2)
+            want.append(([int(i1[0])], [2]) if i1.size else (([int(i2[0])], [3]) if i2.size else ([], [])))
+        else:
+            t = ["m1", "handle%d" % (v % 5), "zzz", "M2".lower()][int(rng.integers(0, 4))]
+            ops.append({"op": dmgraph.OP_METHOD, "vertex": v, "text": t.encode()})
+            base = sum(len(ms) for ms in meths[:v]) if v < n else 0
+            hit = next((j for j, m in enumerate(meths[v] if v < n else []) if m.lower() == t), None)
+            want.append(([base + hit], None) if hit is not None else ([], None))
+    got = g.query_batch(ops)
+    for (gi, ga), (wi, wa) in zip(got, want):
+        assert gi == wi
+        if wa is not None:
+            assert ga == wa
+    assert catalog[got[6][0][0]].lower() == ops[6]["text"].decode() if got[6][0] else True
+    g.release()
