@@ -508,3 +508,48 @@ def test_query_batch_mixed_ops_against_oracle(engine):
             assert ga == wa
     assert catalog[got[6][0][0]].lower() == ops[6]["text"].decode() if got[6][0] else True
     g.release()
+
+
+# ---- concurrency: many host threads on one handle (SURVEY 8b "Threading"; GS:34-38) ------------
+def test_concurrent_readers_one_graph(engine):
+    import threading
+    sg = synth.eco_graph(n_projects=8, v_per=600, e_per=6000, cap=100, seed=5)
+    names = sg.names
+    off, arena = synth.pack_names(names)
+    g = dmgraph.Graph(engine, sg.n_vertices, sg.src, sg.dst, sg.entry, part_off=sg.part_off,
+                      name_off=off, name_bytes=arena)
+    q_off, q_src = synth.stacktrace_queries(sg, n_queries=2000, seed=9)
+    want_k = g.neighbors_batch(dmgraph.BOTH, 2, 1, q_off, q_src)
+    ids = np.arange(0, sg.n_vertices, 3, dtype=np.uint32)
+    want_a = g.adjacency_batch(dmgraph.IN, ids)
+    want_s = g.search_batch(dmgraph.SEARCH_CONTAINS_ALL, [b"order", b"svc3", b"x"])
+    want_c = g.closure(dmgraph.OUT, sg.entry[:5])
+    errors = []
+
+    def worker(kind):
+        try:
+            for _ in range(6):
+                if kind == 0:
+                    got = g.neighbors_batch(dmgraph.BOTH, 2, 1, q_off, q_src)
+                    ok = all(np.array_equal(a, b) for a, b in zip(got, want_k))
+                elif kind == 1:
+                    got = g.adjacency_batch(dmgraph.IN, ids)
+                    ok = all(np.array_equal(a, b) for a, b in zip(got, want_a))
+                elif kind == 2:
+                    got = g.search_batch(dmgraph.SEARCH_CONTAINS_ALL, [b"order", b"svc3", b"x"])
+                    ok = all(np.array_equal(a, b) for a, b in zip(got, want_s))
+                else:
+                    got = g.closure(dmgraph.OUT, sg.entry[:5])
+                    ok = np.array_equal(got[0], want_c[0]) and got[1] == want_c[1]
+                if not ok:
+                    errors.append("mismatch in worker %d" % kind)
+        except Exception as ex:      # noqa: BLE001
+            errors.append(repr(ex))
+
+    threads = [threading.Thread(target=worker, args=(i % 4,)) for i in range(12)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    assert not errors, errors[:3]
+    g.release()
