@@ -27,10 +27,24 @@ constexpr int SM_WARPS = SM_THREADS / 32;
 constexpr int SM_HITBUF = 192;           // hits of one name before the exhaustive fallback
 constexpr uint32_t SM_MAX_PATTERNS = 16384;   // per round (bounds the tile x pattern matrix)
 
+constexpr uint32_t PAT_NIL = 0xFFFFFFFFu;
+struct __align__(16) PatSlot {     // one probe = one 16-byte load
+  unsigned long long key;
+  uint32_t first;                  // first pattern with this key, PAT_NIL = empty slot
+  uint32_t pad;
+};
+struct __align__(16) PatInfo {     // one 16-byte load per candidate pattern
+  unsigned long long pk8;          // first min(len, 8) bytes, little endian
+  uint32_t len;
+  uint32_t next;                   // next pattern with the same key, PAT_NIL = end of chain
+};
+struct __align__(16) PatRow {      // where a pattern's hits go (single-query patterns: one load)
+  unsigned long long row_base;     // out_off of the pattern's first query
+  uint32_t n_queries;
+  uint32_t uq_begin;
+};
 struct SlotTable {
-  const unsigned long long* key;   // [size]
-  const uint32_t* start;           // [size] into bucket_pat
-  const uint32_t* count;           // [size] 0 = empty slot
+  const PatSlot* slot;             // [size]
   uint32_t mask;                   // size - 1
   uint32_t fbits;                  // log2 of the filter size in bits
   uint32_t present;
@@ -43,16 +57,15 @@ struct SearchArgs {
   SlotTable t8, t4, t3;
   const uint32_t* filt;             // filters of the three classes, concatenated (words)
   uint32_t filt_words8, filt_words4, filt_words3;
-  const uint32_t* bucket_pat;
-  const unsigned long long* pk8;    // per pattern: first min(len, 8) bytes, little endian
-  const uint32_t* plen;
+  const PatInfo* pat;               // [U]
+  PatRow* prow;                     // [U] filled by search_rows_kernel once out_off is known
   const uint32_t* poff;
   const uint8_t* pbytes;
   const uint32_t* tiny2;            // [65536] pattern id + 1
   const uint32_t* tiny1;            // [256]
   uint32_t has2, has1, empty_plus1;
   uint32_t U;                       // patterns in this round
-  uint32_t* cnt;                    // [n_tiles][U] counts, then cursors
+  uint32_t* cnt;                    // [U][n_tiles] counts, then cursors (a pattern's tiles are contiguous)
   uint32_t* first;                  // [U] min id (MODE 2)
   const uint32_t* uq_off;           // pattern -> queries that asked for it
   const uint32_t* uq;
@@ -67,18 +80,22 @@ __device__ __forceinline__ uint32_t hash_slot(unsigned long long k, uint32_t mas
 __device__ __forceinline__ uint32_t hash_filter(unsigned long long k, uint32_t bits) {
   return (uint32_t)(((k ^ (k >> 29)) * 0xBF58476D1CE4E5B9ull) >> (64 - bits));
 }
-__device__ __forceinline__ bool table_find(const SlotTable& t, unsigned long long k, uint32_t* st, uint32_t* cn) {
+__device__ __forceinline__ uint32_t table_find(const SlotTable& t, unsigned long long k) {
   uint32_t h = hash_slot(k, t.mask);
   while (true) {
-    const uint32_t c = t.count[h];
-    if (c == 0) return false;
-    if (t.key[h] == k) {
-      *st = t.start[h];
-      *cn = c;
-      return true;
-    }
+    const uint4 raw = __ldg(reinterpret_cast<const uint4*>(t.slot + h));
+    if (raw.z == PAT_NIL) return PAT_NIL;
+    if ((((unsigned long long)raw.y << 32) | raw.x) == k) return raw.z;
     h = (h + 1) & t.mask;
   }
+}
+__device__ __forceinline__ PatInfo load_pat(const PatInfo* p, uint32_t u) {
+  const uint4 raw = __ldg(reinterpret_cast<const uint4*>(p + u));
+  PatInfo r;
+  r.pk8 = ((unsigned long long)raw.y << 32) | raw.x;
+  r.len = raw.z;
+  r.next = raw.w;
+  return r;
 }
 __device__ __forceinline__ unsigned long long low_bytes_mask(uint32_t len) {
   return len >= 8 ? ~0ull : ((1ull << (8 * len)) - 1ull);
@@ -102,7 +119,7 @@ __global__ void __launch_bounds__(SM_THREADS) search_multi_kernel(const SearchAr
   if (tile >= a.n_tiles) return;
   const uint32_t n0 = a.v_lo + tile * a.per_tile;
   const uint32_t n1 = min(a.v_hi, n0 + a.per_tile);
-  uint32_t* my_cnt = (MODE == 2) ? nullptr : a.cnt + (size_t)tile * a.U;
+  uint32_t* my_cnt = (MODE == 2) ? nullptr : a.cnt + tile;   // element of pattern u: my_cnt[u * n_tiles]
 
   auto push = [&](uint32_t u) {
     const uint32_t pos = atomicAdd(&s_nh[wib], 1u);
@@ -110,11 +127,14 @@ __global__ void __launch_bounds__(SM_THREADS) search_multi_kernel(const SearchAr
   };
   auto deliver = [&](uint32_t u, uint32_t id) {
     if (MODE == 0) {
-      atomicAdd(&my_cnt[u], 1u);
+      atomicAdd(&my_cnt[(size_t)u * a.n_tiles], 1u);
     } else if (MODE == 1) {
-      const uint32_t local = atomicAdd(&my_cnt[u], 1u);
-      for (uint32_t j = a.uq_off[u]; j < a.uq_off[u + 1]; ++j) {
-        const unsigned long long pos = a.out_off[a.uq[j]] + local;
+      const uint4 raw = __ldg(reinterpret_cast<const uint4*>(a.prow + u));   // independent of the atomic
+      const uint32_t local = atomicAdd(&my_cnt[(size_t)u * a.n_tiles], 1u);
+      unsigned long long pos = (((unsigned long long)raw.y << 32) | raw.x) + local;
+      if (pos < a.cap) a.out_ids[pos] = id;
+      for (uint32_t j = 1; j < raw.z; ++j) {   // the same text asked more than once
+        pos = a.out_off[a.uq[raw.w + j]] + local;
         if (pos < a.cap) a.out_ids[pos] = id;
       }
     } else {
@@ -145,35 +165,36 @@ __global__ void __launch_bounds__(SM_THREADS) search_multi_kernel(const SearchAr
           if (a.t8.present && r >= 8) {
             const uint32_t fi = hash_filter(k8, a.t8.fbits);
             if ((f8[fi >> 5] >> (fi & 31)) & 1u) {
-              uint32_t st, cn;
-              if (table_find(a.t8, k8, &st, &cn))
-                for (uint32_t j = 0; j < cn; ++j) {
-                  const uint32_t u = a.bucket_pat[st + j], len = a.plen[u];
-                  if (len > r) continue;
+              for (uint32_t u = table_find(a.t8, k8); u != PAT_NIL;) {
+                const PatInfo pi = load_pat(a.pat, u);
+                if (pi.len <= r) {
                   bool ok = true;
-                  const uint8_t* pb = a.pbytes + a.poff[u];
-                  for (uint32_t t = 8; t < len && ok; ++t) ok = a.lower[p + t] == pb[t];
+                  if (pi.len > 8) {
+                    const uint8_t* pb = a.pbytes + a.poff[u];
+                    for (uint32_t t = 8; t < pi.len && ok; ++t) ok = a.lower[p + t] == pb[t];
+                  }
                   if (ok) push(u);
                 }
+                u = pi.next;
+              }
             }
           }
           if (a.t4.present && r >= 4) {
             const uint32_t fi = hash_filter(lo32, a.t4.fbits);
             if ((f4[fi >> 5] >> (fi & 31)) & 1u) {
-              uint32_t st, cn;
-              if (table_find(a.t4, lo32, &st, &cn))
-                for (uint32_t j = 0; j < cn; ++j) {
-                  const uint32_t u = a.bucket_pat[st + j], len = a.plen[u];
-                  if (len <= r && (k8 & low_bytes_mask(len)) == a.pk8[u]) push(u);
-                }
+              for (uint32_t u = table_find(a.t4, lo32); u != PAT_NIL;) {
+                const PatInfo pi = load_pat(a.pat, u);
+                if (pi.len <= r && (k8 & low_bytes_mask(pi.len)) == pi.pk8) push(u);
+                u = pi.next;
+              }
             }
           }
           if (a.t3.present && r >= 3) {
             const uint32_t k3 = lo32 & 0xFFFFFFu;
             const uint32_t fi = hash_filter(k3, a.t3.fbits);
             if ((f3[fi >> 5] >> (fi & 31)) & 1u) {
-              uint32_t st, cn;
-              if (table_find(a.t3, k3, &st, &cn)) push(a.bucket_pat[st]);
+              const uint32_t u = table_find(a.t3, k3);   // a 3-byte key is the whole pattern
+              if (u != PAT_NIL) push(u);
             }
           }
           if (a.has2 && r >= 2) {
@@ -202,7 +223,7 @@ __global__ void __launch_bounds__(SM_THREADS) search_multi_kernel(const SearchAr
       // more hits than the buffer holds (very long name): test every pattern directly
       const uint32_t nn = (uint32_t)(e - s);
       for (uint32_t u = lane; u < a.U; u += 32) {
-        const uint32_t len = a.plen[u];
+        const uint32_t len = a.pat[u].len;
         bool hit = len == 0;
         const uint8_t* pb = a.pbytes + a.poff[u];
         for (uint32_t p = 0; !hit && p + len <= nn; ++p) {
@@ -219,18 +240,35 @@ __global__ void __launch_bounds__(SM_THREADS) search_multi_kernel(const SearchAr
   }
 }
 
-// exclusive scan of every pattern's column over the tiles; tot[u] = row length
-__global__ void search_colscan_kernel(uint32_t* cnt, uint32_t n_tiles, uint32_t U, uint32_t* tot) {
+// exclusive scan of every pattern's tile counts (one warp per pattern, the pattern's tiles are
+// contiguous); tot[u] = row length
+__global__ void __launch_bounds__(256) search_colscan_kernel(uint32_t* cnt, uint32_t n_tiles, uint32_t U,
+                                                             uint32_t* tot) {
+  const int lane = threadIdx.x & 31;
+  const uint32_t u = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (u >= U) return;
+  uint32_t* row = cnt + (size_t)u * n_tiles;
+  uint32_t run = 0;
+  for (uint32_t t0 = 0; t0 < n_tiles; t0 += 32) {
+    const uint32_t t = t0 + lane;
+    const uint32_t c = t < n_tiles ? row[t] : 0;
+    const uint32_t inc = warp_incl_scan_u32(c);
+    if (t < n_tiles) row[t] = run + inc - c;
+    run += __shfl_sync(FULL, inc, 31);
+  }
+  if (lane == 0) tot[u] = run;
+}
+
+// once out_off is known: where each pattern's hits go
+__global__ void search_rows_kernel(const uint32_t* __restrict__ uq_off, const uint32_t* __restrict__ uq,
+                                   const unsigned long long* __restrict__ out_off, uint32_t U, PatRow* prow) {
   const uint32_t u = blockIdx.x * blockDim.x + threadIdx.x;
   if (u >= U) return;
-  uint32_t run = 0;
-  for (uint32_t t = 0; t < n_tiles; ++t) {
-    const size_t o = (size_t)t * U + u;
-    const uint32_t c = cnt[o];
-    cnt[o] = run;
-    run += c;
-  }
-  tot[u] = run;
+  PatRow r;
+  r.uq_begin = uq_off[u];
+  r.n_queries = uq_off[u + 1] - r.uq_begin;
+  r.row_base = r.n_queries ? out_off[uq[r.uq_begin]] : 0;
+  prow[u] = r;
 }
 
 __global__ void search_query_counts_kernel(const uint32_t* __restrict__ tot, const uint32_t* __restrict__ q2u,
@@ -263,13 +301,11 @@ __global__ void search_first_emit_kernel(const uint32_t* __restrict__ first, con
 struct HostTables {
   std::vector<std::string> pats;                 // distinct patterns
   std::vector<uint32_t> q2u;
-  std::vector<unsigned long long> key[3];        // classes 8, 4, 3
-  std::vector<uint32_t> start[3], count[3];
-  std::vector<uint32_t> bucket_pat;
+  std::vector<PatSlot> slot[3];                  // classes 8, 4, 3
+  std::vector<PatInfo> pat;
   std::vector<uint32_t> filt[3];
   uint32_t fbits[3] = {0, 0, 0};
-  std::vector<unsigned long long> pk8;
-  std::vector<uint32_t> plen, poff;
+  std::vector<uint32_t> poff;
   std::vector<uint8_t> pbytes;
   std::vector<uint32_t> tiny2, tiny1;
   uint32_t empty_plus1 = 0;
@@ -296,20 +332,20 @@ static void build_tables(uint64_t nq, const uint32_t* q_off, const uint8_t* q_by
     T.q2u[q] = it->second;
   }
   const uint32_t U = (uint32_t)T.pats.size();
-  T.pk8.assign(U, 0);
-  T.plen.resize(U);
+  T.pat.resize(U);
   T.poff.resize(U + 1);
   T.tiny2.assign(65536, 0);
   T.tiny1.assign(256, 0);
   std::vector<std::pair<unsigned long long, uint32_t>> cls[3];
   for (uint32_t u = 0; u < U; ++u) {
     const std::string& p = T.pats[u];
-    T.plen[u] = (uint32_t)p.size();
+    T.pat[u].len = (uint32_t)p.size();
+    T.pat[u].next = PAT_NIL;
     T.poff[u] = (uint32_t)T.pbytes.size();
     T.pbytes.insert(T.pbytes.end(), p.begin(), p.end());
     unsigned long long k = 0;
     for (size_t i = 0; i < p.size() && i < 8; ++i) k |= (unsigned long long)(uint8_t)p[i] << (8 * i);
-    T.pk8[u] = k;
+    T.pat[u].pk8 = k;
     if (p.empty()) T.empty_plus1 = u + 1;
     else if (p.size() == 1) T.tiny1[k & 0xFF] = u + 1;
     else if (p.size() == 2) T.tiny2[k & 0xFFFF] = u + 1;
@@ -326,28 +362,28 @@ static void build_tables(uint64_t nq, const uint32_t* q_off, const uint8_t* q_by
     for (size_t i = 0; i < v.size(); ++i) nkeys += (i == 0 || v[i].first != v[i - 1].first);
     uint32_t size = 16;
     while (size < 2 * nkeys + 1) size <<= 1;
-    T.key[c].assign(size, 0);
-    T.start[c].assign(size, 0);
-    T.count[c].assign(size, 0);
+    PatSlot empty;
+    empty.key = 0;
+    empty.first = PAT_NIL;
+    empty.pad = 0;
+    T.slot[c].assign(size, empty);
     uint32_t fb = 12;
-    while ((1ull << fb) < 32 * nkeys && fb < 18) ++fb;
+    while ((1ull << fb) < 32 * nkeys && fb < 16) ++fb;
     T.fbits[c] = fb;
     T.filt[c].assign((1u << fb) / 32, 0);
     for (size_t i = 0; i < v.size();) {
       size_t j = i;
       while (j < v.size() && v[j].first == v[i].first) ++j;
       uint32_t h = h_hash_slot(v[i].first, size - 1);
-      while (T.count[c][h]) h = (h + 1) & (size - 1);
-      T.key[c][h] = v[i].first;
-      T.start[c][h] = (uint32_t)T.bucket_pat.size();
-      T.count[c][h] = (uint32_t)(j - i);
-      for (size_t t = i; t < j; ++t) T.bucket_pat.push_back(v[t].second);
+      while (T.slot[c][h].first != PAT_NIL) h = (h + 1) & (size - 1);
+      T.slot[c][h].key = v[i].first;
+      T.slot[c][h].first = v[i].second;
+      for (size_t t = i; t + 1 < j; ++t) T.pat[v[t].second].next = v[t + 1].second;   // chain, shortest id first
       const uint32_t fi = h_hash_filter(v[i].first, fb);
       T.filt[c][fi >> 5] |= 1u << (fi & 31);
       i = j;
     }
   }
-  if (T.bucket_pat.empty()) T.bucket_pat.push_back(0);
   // pattern -> queries
   T.uq_off.assign(U + 1, 0);
   for (uint64_t q = 0; q < nq; ++q) ++T.uq_off[T.q2u[q] + 1];
@@ -384,12 +420,10 @@ int32_t run_search_multi(CallCtx* c, dmg_graph* g, int kind, uint32_t v_lo, uint
   size_t need = 4096;
   auto sz = [&](size_t n, size_t s) { need += ((n * s + 255) & ~size_t(255)) + 256; };
   for (int k = 0; k < 3; ++k) {
-    sz(T.key[k].size(), 8);
-    sz(T.start[k].size(), 4);
-    sz(T.count[k].size(), 4);
+    sz(T.slot[k].size(), 16);
     sz(T.filt[k].size(), 4);
   }
-  sz(T.bucket_pat.size(), 4); sz(U, 8); sz(U, 4); sz(U + 1, 4); sz(T.pbytes.size(), 1);
+  sz(U, 16); sz(U, 16); sz(3 * 65536, 4); sz(U + 1, 4); sz(T.pbytes.size(), 1);
   sz(65536, 4); sz(256, 4); sz(U + 1, 4); sz(nq, 4); sz(nq, 4);
   DMG_TRY(c->tmp0.reserve(need));
   size_t used = 0;
@@ -398,22 +432,24 @@ int32_t run_search_multi(CallCtx* c, dmg_graph* g, int kind, uint32_t v_lo, uint
   SlotTable* st[3] = {&a.t8, &a.t4, &a.t3};
   std::vector<uint32_t> filt_all;
   for (int k = 0; k < 3; ++k) {
-    DMG_TRY(put(c, c->tmp0, &used, T.key[k], &st[k]->key));
-    DMG_TRY(put(c, c->tmp0, &used, T.start[k], &st[k]->start));
-    DMG_TRY(put(c, c->tmp0, &used, T.count[k], &st[k]->count));
-    st[k]->mask = (uint32_t)T.key[k].size() - 1;
+    DMG_TRY(put(c, c->tmp0, &used, T.slot[k], &st[k]->slot));
+    st[k]->mask = (uint32_t)T.slot[k].size() - 1;
     st[k]->fbits = T.fbits[k];
     st[k]->present = 0;
-    for (uint32_t x : T.count[k]) st[k]->present |= x != 0;
+    for (const PatSlot& x : T.slot[k]) st[k]->present |= x.first != PAT_NIL;
     filt_all.insert(filt_all.end(), T.filt[k].begin(), T.filt[k].end());
   }
   a.filt_words8 = (uint32_t)T.filt[0].size();
   a.filt_words4 = (uint32_t)T.filt[1].size();
   a.filt_words3 = (uint32_t)T.filt[2].size();
   DMG_TRY(put(c, c->tmp0, &used, filt_all, &a.filt));
-  DMG_TRY(put(c, c->tmp0, &used, T.bucket_pat, &a.bucket_pat));
-  DMG_TRY(put(c, c->tmp0, &used, T.pk8, &a.pk8));
-  DMG_TRY(put(c, c->tmp0, &used, T.plen, &a.plen));
+  DMG_TRY(put(c, c->tmp0, &used, T.pat, &a.pat));
+  {
+    std::vector<PatRow> rows(U);
+    const PatRow* prow_c = nullptr;
+    DMG_TRY(put(c, c->tmp0, &used, rows, &prow_c));   // space only; search_rows_kernel fills it
+    a.prow = const_cast<PatRow*>(prow_c);
+  }
   DMG_TRY(put(c, c->tmp0, &used, T.poff, &a.poff));
   DMG_TRY(put(c, c->tmp0, &used, T.pbytes, &a.pbytes));
   DMG_TRY(put(c, c->tmp0, &used, T.tiny2, &a.tiny2));
@@ -494,7 +530,7 @@ int32_t run_search_multi(CallCtx* c, dmg_graph* g, int kind, uint32_t v_lo, uint
     }
     {
       LaunchScope ls(c, K_SEARCH_FIRST);
-      search_colscan_kernel<<<(U + 127) / 128, 128, 0, c->stream>>>(a.cnt, a.n_tiles, U, tot);
+      search_colscan_kernel<<<(U + 7) / 8, 256, 0, c->stream>>>(a.cnt, a.n_tiles, U, tot);
       search_query_counts_kernel<<<qb, 256, 0, c->stream>>>(tot, d_q2u, nq, qcnt);
     }
     {
@@ -505,6 +541,7 @@ int32_t run_search_multi(CallCtx* c, dmg_graph* g, int kind, uint32_t v_lo, uint
     if (!sizes_only && range) {
       DMG_TRY(c->out_ids.reserve(std::max<uint64_t>(dev_cap, 1) * 4));
       a.out_ids = c->out_ids.as<uint32_t>();
+      search_rows_kernel<<<(U + 255) / 256, 256, 0, c->stream>>>(a.uq_off, a.uq, a.out_off, U, a.prow);
       LaunchScope ls(c, K_SEARCH_EMIT);
       search_multi_kernel<1><<<blocks, SM_THREADS, smem, c->stream>>>(a);
     }

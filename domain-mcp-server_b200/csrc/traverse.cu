@@ -365,7 +365,7 @@ static inline size_t small_kernel_smem(uint32_t wc) { return (size_t)wc + wc / 8
 // takes 512 vertices (one 16-byte load per lane), compacts them in id order into a per-warp
 // shared buffer (warp scan of the per-lane counts) and writes the run out coalesced.
 constexpr int EM_THREADS = 256;
-__global__ void __launch_bounds__(EM_THREADS) khop_emit_kernel(const uint8_t* __restrict__ stage, uint32_t WC,
+__global__ void __launch_bounds__(EM_THREADS, 6) khop_emit_kernel(const uint8_t* __restrict__ stage, uint32_t WC,
                                                                unsigned long long q_begin, unsigned long long q_end,
                                                                const uint32_t* __restrict__ qwin,
                                                                const unsigned long long* __restrict__ out_off,
