@@ -22,9 +22,9 @@
 
 namespace dmg {
 
-constexpr int SM_THREADS = 512;          // 16 warps per CTA
+constexpr int SM_THREADS = 256;          // 8 warps per CTA
 constexpr int SM_WARPS = SM_THREADS / 32;
-constexpr int SM_HITBUF = 192;           // hits of one name before the exhaustive fallback
+constexpr int SM_HITBUF = 64;            // distinct patterns of one name before the exhaustive fallback
 constexpr uint32_t SM_MAX_PATTERNS = 16384;   // per round (bounds the tile x pattern matrix)
 
 constexpr uint32_t PAT_NIL = 0xFFFFFFFFu;
@@ -54,9 +54,9 @@ struct SearchArgs {
   const unsigned long long* name_off;
   const uint8_t* lower;
   uint32_t v_lo, v_hi, per_tile, n_tiles;
-  SlotTable t8, t4, t3;
-  const uint32_t* filt;             // filters of the three classes, concatenated (words)
-  uint32_t filt_words8, filt_words4, filt_words3;
+  SlotTable t16, t12, t8, t4, t3;   // classes by pattern length: >=16, 12..15, 8..11, 4..7, 3
+  const uint32_t* filt;             // filters of the five classes, concatenated (words)
+  uint32_t filt_words16, filt_words12, filt_words8, filt_words4, filt_words3;
   const PatInfo* pat;               // [U]
   PatRow* prow;                     // [U] filled by search_rows_kernel once out_off is known
   const uint32_t* poff;
@@ -97,22 +97,36 @@ __device__ __forceinline__ PatInfo load_pat(const PatInfo* p, uint32_t u) {
   r.next = raw.w;
   return r;
 }
+// key of the long classes: a 64-bit mix of the first 16 (12) bytes, so that patterns sharing a
+// popular 8-byte prefix ("createor...") do not pile up in one chain
+__host__ __device__ __forceinline__ unsigned long long mix_key(unsigned long long a, unsigned long long b) {
+  unsigned long long x = a * 0x9E3779B97F4A7C15ull ^ (b + 0x7F4A7C159E3779B9ull);
+  x ^= x >> 32;
+  x *= 0xD6E8FEB86659FD93ull;
+  x ^= x >> 29;
+  return x;
+}
 __device__ __forceinline__ unsigned long long low_bytes_mask(uint32_t len) {
   return len >= 8 ? ~0ull : ((1ull << (8 * len)) - 1ull);
 }
 
+// One lane per name: the 32 lanes of a warp scan 32 consecutive names in lock step, so the
+// (frequent) hit path runs with many lanes active.  A lane collects the distinct patterns of its
+// name in shared memory; after the step the warp delivers the 32 lists in lane order == name
+// order, which keeps every row ascending.
 template <int MODE>   // 0 count, 1 emit, 2 first
 __global__ void __launch_bounds__(SM_THREADS) search_multi_kernel(const SearchArgs a) {
   extern __shared__ __align__(16) uint32_t sm_u32[];
-  uint32_t* f8 = sm_u32;
+  uint32_t* f16 = sm_u32;
+  uint32_t* f12 = f16 + a.filt_words16;
+  uint32_t* f8 = f12 + a.filt_words12;
   uint32_t* f4 = f8 + a.filt_words8;
   uint32_t* f3 = f4 + a.filt_words4;
-  __shared__ uint32_t s_hits[SM_WARPS][SM_HITBUF];
-  __shared__ uint32_t s_nh[SM_WARPS];
+  __shared__ uint16_t s_hits[SM_WARPS][32][SM_HITBUF];
+  __shared__ uint32_t s_nh[SM_WARPS][32];
   const int tid = threadIdx.x, lane = tid & 31, wib = tid >> 5;
-  const uint32_t fw = a.filt_words8 + a.filt_words4 + a.filt_words3;
+  const uint32_t fw = a.filt_words16 + a.filt_words12 + a.filt_words8 + a.filt_words4 + a.filt_words3;
   for (uint32_t i = tid; i < fw; i += SM_THREADS) sm_u32[i] = a.filt[i];
-  if (lane == 0) s_nh[wib] = 0;
   __syncthreads();
 
   const uint32_t tile = blockIdx.x * SM_WARPS + wib;
@@ -120,122 +134,172 @@ __global__ void __launch_bounds__(SM_THREADS) search_multi_kernel(const SearchAr
   const uint32_t n0 = a.v_lo + tile * a.per_tile;
   const uint32_t n1 = min(a.v_hi, n0 + a.per_tile);
   uint32_t* my_cnt = (MODE == 2) ? nullptr : a.cnt + tile;   // element of pattern u: my_cnt[u * n_tiles]
+  uint16_t* mine = s_hits[wib][lane];
 
-  auto push = [&](uint32_t u) {
-    const uint32_t pos = atomicAdd(&s_nh[wib], 1u);
-    if (pos < SM_HITBUF) s_hits[wib][pos] = u;
-  };
-  auto deliver = [&](uint32_t u, uint32_t id) {
-    if (MODE == 0) {
-      atomicAdd(&my_cnt[(size_t)u * a.n_tiles], 1u);
-    } else if (MODE == 1) {
-      const uint4 raw = __ldg(reinterpret_cast<const uint4*>(a.prow + u));   // independent of the atomic
-      const uint32_t local = atomicAdd(&my_cnt[(size_t)u * a.n_tiles], 1u);
-      unsigned long long pos = (((unsigned long long)raw.y << 32) | raw.x) + local;
-      if (pos < a.cap) a.out_ids[pos] = id;
-      for (uint32_t j = 1; j < raw.z; ++j) {   // the same text asked more than once
-        pos = a.out_off[a.uq[raw.w + j]] + local;
-        if (pos < a.cap) a.out_ids[pos] = id;
-      }
-    } else {
-      atomicMin(&a.first[u], id);
-    }
-  };
-
-  for (uint32_t i = n0; i < n1; ++i) {
-    const unsigned long long s = a.name_off[i], e = a.name_off[i + 1];
-    const unsigned long long ws = s & ~3ull;
-    if (a.empty_plus1 && lane == 0) push(a.empty_plus1 - 1);
-    // 29 position-carrying lanes per chunk: lanes 29..31 only feed the windows of their neighbours
-    for (unsigned long long cb = ws; cb < e; cb += 116) {
-      const unsigned long long wa = cb + 4ull * lane;
-      uint32_t w0 = 0;
-      if (wa < e + 8) w0 = *reinterpret_cast<const uint32_t*>(a.lower + wa);   // arena is zero padded
-      const uint32_t w1 = __shfl_down_sync(FULL, w0, 1);
-      const uint32_t w2 = __shfl_down_sync(FULL, w0, 2);
-      if (lane < 29) {
-#pragma unroll
-        for (int b = 0; b < 4; ++b) {
-          const unsigned long long p = wa + b;
-          if (p < s || p >= e) continue;
-          const uint32_t r = (uint32_t)min(e - p, 0xFFFFull);
-          const uint32_t lo32 = b ? __funnelshift_r(w0, w1, 8 * b) : w0;
-          const uint32_t hi32 = b ? __funnelshift_r(w1, w2, 8 * b) : w1;
-          const unsigned long long k8 = ((unsigned long long)hi32 << 32) | lo32;
-          if (a.t8.present && r >= 8) {
-            const uint32_t fi = hash_filter(k8, a.t8.fbits);
-            if ((f8[fi >> 5] >> (fi & 31)) & 1u) {
-              for (uint32_t u = table_find(a.t8, k8); u != PAT_NIL;) {
-                const PatInfo pi = load_pat(a.pat, u);
-                if (pi.len <= r) {
-                  bool ok = true;
-                  if (pi.len > 8) {
-                    const uint8_t* pb = a.pbytes + a.poff[u];
-                    for (uint32_t t = 8; t < pi.len && ok; ++t) ok = a.lower[p + t] == pb[t];
-                  }
-                  if (ok) push(u);
+  for (uint32_t i0 = n0; i0 < n1; i0 += 32) {
+    const uint32_t i = i0 + lane;
+    uint32_t nh = 0;
+    // a pattern may occur at several positions of the name: keep it once; nh > SM_HITBUF = overflow
+    auto add = [&](uint32_t u) {
+      for (uint32_t t = 0; t < nh && t < SM_HITBUF; ++t)
+        if (mine[t] == (uint16_t)u) return;
+      if (nh < SM_HITBUF) mine[nh] = (uint16_t)u;
+      ++nh;
+    };
+    if (i < n1) {
+      const unsigned long long s = a.name_off[i], e = a.name_off[i + 1];
+      const uint32_t len = (uint32_t)min(e - s, 0xFFFFFFFFull);
+      if (a.empty_plus1) add(a.empty_plus1 - 1);
+      const uint8_t* wp = a.lower + (s & ~3ull);   // arena is zero padded: reading past e is safe
+      uint32_t sh = (uint32_t)(s & 3ull) * 8;
+      uint32_t w0 = __ldg(reinterpret_cast<const uint32_t*>(wp));
+      uint32_t w1 = __ldg(reinterpret_cast<const uint32_t*>(wp + 4));
+      uint32_t w2 = __ldg(reinterpret_cast<const uint32_t*>(wp + 8));
+      uint32_t w3 = __ldg(reinterpret_cast<const uint32_t*>(wp + 12));
+      uint32_t w4 = __ldg(reinterpret_cast<const uint32_t*>(wp + 16));
+      wp += 20;
+      // a pattern of the long classes: first 8 bytes already equal (or hashed): check the rest
+      auto long_class = [&](const SlotTable& tb, unsigned long long key, unsigned long long k8a, uint32_t r, uint32_t p) {
+        for (uint32_t u = table_find(tb, key); u != PAT_NIL;) {
+          const PatInfo pi = load_pat(a.pat, u);
+          if (pi.len <= r && pi.pk8 == k8a) {
+            bool ok = true;
+            const uint8_t* pb = a.pbytes + a.poff[u];
+            const uint8_t* nb = a.lower + s + p;
+            for (uint32_t t = 8; t < pi.len && ok; ++t) ok = nb[t] == pb[t];
+            if (ok) add(u);
+          }
+          u = pi.next;
+        }
+      };
+      for (uint32_t p = 0; p < len; ++p) {
+        const uint32_t r = len - p;
+        const uint32_t lo32 = sh ? __funnelshift_r(w0, w1, sh) : w0;
+        const uint32_t hi32 = sh ? __funnelshift_r(w1, w2, sh) : w1;
+        const unsigned long long k8 = ((unsigned long long)hi32 << 32) | lo32;
+        if ((a.t16.present | a.t12.present) && r >= 12) {
+          const uint32_t lo2 = sh ? __funnelshift_r(w2, w3, sh) : w2;
+          const uint32_t hi2 = sh ? __funnelshift_r(w3, w4, sh) : w3;
+          if (a.t16.present && r >= 16) {
+            const unsigned long long key = mix_key(k8, ((unsigned long long)hi2 << 32) | lo2);
+            const uint32_t fi = hash_filter(key, a.t16.fbits);
+            if ((f16[fi >> 5] >> (fi & 31)) & 1u) long_class(a.t16, key, k8, r, p);
+          }
+          if (a.t12.present) {
+            const unsigned long long key = mix_key(k8, lo2);
+            const uint32_t fi = hash_filter(key, a.t12.fbits);
+            if ((f12[fi >> 5] >> (fi & 31)) & 1u) long_class(a.t12, key, k8, r, p);
+          }
+        }
+        if (a.t8.present && r >= 8) {
+          const uint32_t fi = hash_filter(k8, a.t8.fbits);
+          if ((f8[fi >> 5] >> (fi & 31)) & 1u) {
+            for (uint32_t u = table_find(a.t8, k8); u != PAT_NIL;) {
+              const PatInfo pi = load_pat(a.pat, u);
+              if (pi.len <= r) {
+                bool ok = true;
+                if (pi.len > 8) {
+                  const uint8_t* pb = a.pbytes + a.poff[u];
+                  const uint8_t* nb = a.lower + s + p;
+                  for (uint32_t t = 8; t < pi.len && ok; ++t) ok = nb[t] == pb[t];
                 }
-                u = pi.next;
+                if (ok) add(u);
               }
+              u = pi.next;
             }
           }
-          if (a.t4.present && r >= 4) {
-            const uint32_t fi = hash_filter(lo32, a.t4.fbits);
-            if ((f4[fi >> 5] >> (fi & 31)) & 1u) {
-              for (uint32_t u = table_find(a.t4, lo32); u != PAT_NIL;) {
-                const PatInfo pi = load_pat(a.pat, u);
-                if (pi.len <= r && (k8 & low_bytes_mask(pi.len)) == pi.pk8) push(u);
-                u = pi.next;
-              }
+        }
+        if (a.t4.present && r >= 4) {
+          const uint32_t fi = hash_filter(lo32, a.t4.fbits);
+          if ((f4[fi >> 5] >> (fi & 31)) & 1u) {
+            for (uint32_t u = table_find(a.t4, lo32); u != PAT_NIL;) {
+              const PatInfo pi = load_pat(a.pat, u);
+              if (pi.len <= r && (k8 & low_bytes_mask(pi.len)) == pi.pk8) add(u);
+              u = pi.next;
             }
           }
-          if (a.t3.present && r >= 3) {
-            const uint32_t k3 = lo32 & 0xFFFFFFu;
-            const uint32_t fi = hash_filter(k3, a.t3.fbits);
-            if ((f3[fi >> 5] >> (fi & 31)) & 1u) {
-              const uint32_t u = table_find(a.t3, k3);   // a 3-byte key is the whole pattern
-              if (u != PAT_NIL) push(u);
+        }
+        if (a.t3.present && r >= 3) {
+          const uint32_t k3 = lo32 & 0xFFFFFFu;
+          const uint32_t fi = hash_filter(k3, a.t3.fbits);
+          if ((f3[fi >> 5] >> (fi & 31)) & 1u) {
+            const uint32_t u = table_find(a.t3, k3);   // a 3-byte key is the whole pattern
+            if (u != PAT_NIL) add(u);
+          }
+        }
+        if (a.has2 && r >= 2) {
+          const uint32_t u1 = a.tiny2[lo32 & 0xFFFFu];
+          if (u1) add(u1 - 1);
+        }
+        if (a.has1) {
+          const uint32_t u1 = a.tiny1[lo32 & 0xFFu];
+          if (u1) add(u1 - 1);
+        }
+        sh += 8;
+        if (sh == 32) {
+          sh = 0;
+          w0 = w1;
+          w1 = w2;
+          w2 = w3;
+          w3 = w4;
+          w4 = __ldg(reinterpret_cast<const uint32_t*>(wp));
+          wp += 4;
+        }
+      }
+    }
+    s_nh[wib][lane] = nh;
+    __syncwarp();
+    // deliver in lane order == name order
+    for (int l = 0; l < 32; ++l) {
+      const uint32_t n_l = s_nh[wib][l];
+      const uint32_t id = i0 + l;
+      if (n_l == 0) continue;
+      if (n_l <= SM_HITBUF) {
+        for (uint32_t j = lane; j < n_l; j += 32) {
+          const uint32_t u = s_hits[wib][l][j];
+          if (MODE == 0) {
+            atomicAdd(&my_cnt[(size_t)u * a.n_tiles], 1u);
+          } else if (MODE == 1) {
+            const uint4 raw = __ldg(reinterpret_cast<const uint4*>(a.prow + u));
+            const uint32_t local = atomicAdd(&my_cnt[(size_t)u * a.n_tiles], 1u);
+            unsigned long long pos = (((unsigned long long)raw.y << 32) | raw.x) + local;
+            if (pos < a.cap) a.out_ids[pos] = id;
+            for (uint32_t t = 1; t < raw.z; ++t) {   // the same text asked more than once
+              pos = a.out_off[a.uq[raw.w + t]] + local;
+              if (pos < a.cap) a.out_ids[pos] = id;
             }
+          } else {
+            atomicMin(&a.first[u], id);
           }
-          if (a.has2 && r >= 2) {
-            const uint32_t u1 = a.tiny2[lo32 & 0xFFFFu];
-            if (u1) push(u1 - 1);
+        }
+      } else {
+        // more distinct patterns than the list holds: test every pattern against this name
+        const unsigned long long s = a.name_off[id], e = a.name_off[id + 1];
+        const uint32_t nn = (uint32_t)(e - s);
+        for (uint32_t u = lane; u < a.U; u += 32) {
+          const uint32_t len = a.pat[u].len;
+          bool hit = len == 0;
+          const uint8_t* pb = a.pbytes + a.poff[u];
+          for (uint32_t p = 0; !hit && p + len <= nn; ++p) {
+            uint32_t t = 0;
+            while (t < len && a.lower[s + p + t] == pb[t]) ++t;
+            hit = t == len;
           }
-          if (a.has1) {
-            const uint32_t u1 = a.tiny1[lo32 & 0xFFu];
-            if (u1) push(u1 - 1);
+          if (!hit) continue;
+          if (MODE == 0) {
+            atomicAdd(&my_cnt[(size_t)u * a.n_tiles], 1u);
+          } else if (MODE == 1) {
+            const uint32_t local = atomicAdd(&my_cnt[(size_t)u * a.n_tiles], 1u);
+            for (uint32_t t = a.uq_off[u]; t < a.uq_off[u + 1]; ++t) {
+              const unsigned long long pos = a.out_off[a.uq[t]] + local;
+              if (pos < a.cap) a.out_ids[pos] = id;
+            }
+          } else {
+            atomicMin(&a.first[u], id);
           }
         }
       }
     }
-    __syncwarp();
-    const uint32_t nh = s_nh[wib];
-    if (nh == 0) continue;
-    if (nh <= SM_HITBUF) {
-      // a pattern may occur at several positions of the name: report it once
-      for (uint32_t j = lane; j < nh; j += 32) {
-        const uint32_t u = s_hits[wib][j];
-        bool dup = false;
-        for (uint32_t t = 0; t < j && !dup; ++t) dup = s_hits[wib][t] == u;
-        if (!dup) deliver(u, i);
-      }
-    } else {
-      // more hits than the buffer holds (very long name): test every pattern directly
-      const uint32_t nn = (uint32_t)(e - s);
-      for (uint32_t u = lane; u < a.U; u += 32) {
-        const uint32_t len = a.pat[u].len;
-        bool hit = len == 0;
-        const uint8_t* pb = a.pbytes + a.poff[u];
-        for (uint32_t p = 0; !hit && p + len <= nn; ++p) {
-          uint32_t t = 0;
-          while (t < len && a.lower[s + p + t] == pb[t]) ++t;
-          hit = t == len;
-        }
-        if (hit) deliver(u, i);
-      }
-    }
-    __syncwarp();
-    if (lane == 0) s_nh[wib] = 0;
     __syncwarp();
   }
 }
@@ -301,10 +365,10 @@ __global__ void search_first_emit_kernel(const uint32_t* __restrict__ first, con
 struct HostTables {
   std::vector<std::string> pats;                 // distinct patterns
   std::vector<uint32_t> q2u;
-  std::vector<PatSlot> slot[3];                  // classes 8, 4, 3
+  std::vector<PatSlot> slot[5];                  // classes 16, 12, 8, 4, 3
   std::vector<PatInfo> pat;
-  std::vector<uint32_t> filt[3];
-  uint32_t fbits[3] = {0, 0, 0};
+  std::vector<uint32_t> filt[5];
+  uint32_t fbits[5] = {0, 0, 0, 0, 0};
   std::vector<uint32_t> poff;
   std::vector<uint8_t> pbytes;
   std::vector<uint32_t> tiny2, tiny1;
@@ -332,11 +396,26 @@ static void build_tables(uint64_t nq, const uint32_t* q_off, const uint8_t* q_by
     T.q2u[q] = it->second;
   }
   const uint32_t U = (uint32_t)T.pats.size();
+  {
+    // short patterns hit most often: give them the low ids so that the cells of the cursor
+    // matrix that are touched all the time sit together (and stay in L2)
+    std::vector<uint32_t> order(U), rank(U);
+    for (uint32_t u = 0; u < U; ++u) order[u] = u;
+    std::stable_sort(order.begin(), order.end(),
+                     [&](uint32_t x, uint32_t y) { return T.pats[x].size() < T.pats[y].size(); });
+    std::vector<std::string> sorted(U);
+    for (uint32_t r = 0; r < U; ++r) {
+      rank[order[r]] = r;
+      sorted[r] = std::move(T.pats[order[r]]);
+    }
+    T.pats.swap(sorted);
+    for (uint64_t q = 0; q < nq; ++q) T.q2u[q] = rank[T.q2u[q]];
+  }
   T.pat.resize(U);
   T.poff.resize(U + 1);
   T.tiny2.assign(65536, 0);
   T.tiny1.assign(256, 0);
-  std::vector<std::pair<unsigned long long, uint32_t>> cls[3];
+  std::vector<std::pair<unsigned long long, uint32_t>> cls[5];
   for (uint32_t u = 0; u < U; ++u) {
     const std::string& p = T.pats[u];
     T.pat[u].len = (uint32_t)p.size();
@@ -349,13 +428,19 @@ static void build_tables(uint64_t nq, const uint32_t* q_off, const uint8_t* q_by
     if (p.empty()) T.empty_plus1 = u + 1;
     else if (p.size() == 1) T.tiny1[k & 0xFF] = u + 1;
     else if (p.size() == 2) T.tiny2[k & 0xFFFF] = u + 1;
-    else if (p.size() == 3) cls[2].emplace_back(k & 0xFFFFFF, u);
-    else if (p.size() < 8) cls[1].emplace_back(k & 0xFFFFFFFFull, u);
-    else cls[0].emplace_back(k, u);
+    else if (p.size() == 3) cls[4].emplace_back(k & 0xFFFFFF, u);
+    else if (p.size() < 8) cls[3].emplace_back(k & 0xFFFFFFFFull, u);
+    else if (p.size() < 12) cls[2].emplace_back(k, u);
+    else {
+      unsigned long long k2 = 0;
+      const size_t lim = p.size() < 16 ? 12 : 16;
+      for (size_t i = 8; i < lim; ++i) k2 |= (unsigned long long)(uint8_t)p[i] << (8 * (i - 8));
+      cls[p.size() < 16 ? 1 : 0].emplace_back(mix_key(k, k2), u);
+    }
   }
   T.poff[U] = (uint32_t)T.pbytes.size();
   T.pbytes.resize(T.pbytes.size() + 16, 0);
-  for (int c = 0; c < 3; ++c) {
+  for (int c = 0; c < 5; ++c) {
     auto& v = cls[c];
     std::sort(v.begin(), v.end());
     size_t nkeys = 0;
@@ -368,7 +453,7 @@ static void build_tables(uint64_t nq, const uint32_t* q_off, const uint8_t* q_by
     empty.pad = 0;
     T.slot[c].assign(size, empty);
     uint32_t fb = 12;
-    while ((1ull << fb) < 32 * nkeys && fb < 16) ++fb;
+    while ((1ull << fb) < 32 * nkeys && fb < (c == 0 ? 17u : 15u)) ++fb;
     T.fbits[c] = fb;
     T.filt[c].assign((1u << fb) / 32, 0);
     for (size_t i = 0; i < v.size();) {
@@ -419,7 +504,7 @@ int32_t run_search_multi(CallCtx* c, dmg_graph* g, int kind, uint32_t v_lo, uint
   // one arena for every table
   size_t need = 4096;
   auto sz = [&](size_t n, size_t s) { need += ((n * s + 255) & ~size_t(255)) + 256; };
-  for (int k = 0; k < 3; ++k) {
+  for (int k = 0; k < 5; ++k) {
     sz(T.slot[k].size(), 16);
     sz(T.filt[k].size(), 4);
   }
@@ -429,9 +514,9 @@ int32_t run_search_multi(CallCtx* c, dmg_graph* g, int kind, uint32_t v_lo, uint
   size_t used = 0;
   SearchArgs a;
   memset(&a, 0, sizeof(a));
-  SlotTable* st[3] = {&a.t8, &a.t4, &a.t3};
+  SlotTable* st[5] = {&a.t16, &a.t12, &a.t8, &a.t4, &a.t3};
   std::vector<uint32_t> filt_all;
-  for (int k = 0; k < 3; ++k) {
+  for (int k = 0; k < 5; ++k) {
     DMG_TRY(put(c, c->tmp0, &used, T.slot[k], &st[k]->slot));
     st[k]->mask = (uint32_t)T.slot[k].size() - 1;
     st[k]->fbits = T.fbits[k];
@@ -439,9 +524,11 @@ int32_t run_search_multi(CallCtx* c, dmg_graph* g, int kind, uint32_t v_lo, uint
     for (const PatSlot& x : T.slot[k]) st[k]->present |= x.first != PAT_NIL;
     filt_all.insert(filt_all.end(), T.filt[k].begin(), T.filt[k].end());
   }
-  a.filt_words8 = (uint32_t)T.filt[0].size();
-  a.filt_words4 = (uint32_t)T.filt[1].size();
-  a.filt_words3 = (uint32_t)T.filt[2].size();
+  a.filt_words16 = (uint32_t)T.filt[0].size();
+  a.filt_words12 = (uint32_t)T.filt[1].size();
+  a.filt_words8 = (uint32_t)T.filt[2].size();
+  a.filt_words4 = (uint32_t)T.filt[3].size();
+  a.filt_words3 = (uint32_t)T.filt[4].size();
   DMG_TRY(put(c, c->tmp0, &used, filt_all, &a.filt));
   DMG_TRY(put(c, c->tmp0, &used, T.pat, &a.pat));
   {
@@ -470,7 +557,7 @@ int32_t run_search_multi(CallCtx* c, dmg_graph* g, int kind, uint32_t v_lo, uint
 
   const uint32_t range = v_hi - v_lo;
   const size_t smem = (size_t)filt_all.size() * 4;
-  if (smem > 48 * 1024) {
+  {
     DMG_CUDA(cudaFuncSetAttribute(search_multi_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     DMG_CUDA(cudaFuncSetAttribute(search_multi_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     DMG_CUDA(cudaFuncSetAttribute(search_multi_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
