@@ -919,6 +919,111 @@ int32_t dmg_neighbors_batch_dev(dmg_graph* g, int32_t mode, int32_t k, int32_t e
   return DMG_OK;
 }
 
+// ---- dmg_neighbors_batch_rows: dense result rows (one hop byte per project vertex) ---------------
+int32_t dmg_neighbors_batch_rows(dmg_graph* g, int32_t mode, int32_t k, int32_t exclude_sources, uint64_t nq,
+                                 const uint32_t* q_off, const uint32_t* q_src, uint32_t* out_row_stride,
+                                 uint32_t* out_win, uint8_t* out_rows, uint64_t cap_bytes, uint64_t* needed_bytes) {
+  if (!out_row_stride || !needed_bytes) {
+    set_error("dmg_neighbors_batch_rows: NULL argument");
+    return DMG_EINVAL;
+  }
+  uint64_t dummy_off = 0;
+  DMG_TRY(check_khop_args(g, mode, k, nq, q_off, &dummy_off, needed_bytes));
+  const uint32_t maxp = std::max<uint32_t>(g->info.max_part_vertices, 1);
+  if (maxp > SMALL_WINDOW_MAX) {
+    set_error("dmg_neighbors_batch_rows: dense rows need projects of <= %u vertices (largest has %u)", SMALL_WINDOW_MAX, maxp);
+    return DMG_EINVAL;
+  }
+  const uint32_t WC = (maxp + 127u) & ~127u;
+  *out_row_stride = WC;
+  *needed_bytes = nq * (uint64_t)WC;
+  if (nq == 0) return DMG_OK;
+  if (!out_win || !out_rows || cap_bytes < *needed_bytes) {
+    set_error("dmg_neighbors_batch_rows: capacity %llu < needed %llu bytes", (unsigned long long)cap_bytes,
+              (unsigned long long)*needed_bytes);
+    return DMG_ECAP;
+  }
+  const uint64_t n_src = q_off[nq];
+  if (n_src && !q_src) {
+    set_error("dmg_neighbors_batch_rows: q_src is NULL");
+    return DMG_EINVAL;
+  }
+  Engine* e = g->eng;
+  CtxGuard cg(e);
+  CallCtx* c = cg.c;
+  if (!c) return DMG_ECUDA;
+  DMG_TRY(c->begin());
+  DMG_TRY(c->q_off.reserve((nq + 1) * 4));
+  DMG_TRY(c->q_src.reserve(n_src * 4));
+  DMG_CUDA(cudaMemcpyAsync(c->q_off.p, q_off, (nq + 1) * 4, cudaMemcpyHostToDevice, c->stream));
+  if (n_src) DMG_CUDA(cudaMemcpyAsync(c->q_src.p, q_src, n_src * 4, cudaMemcpyHostToDevice, c->stream));
+  c->stats.h2d_bytes += (nq + 1) * 4 + n_src * 4;
+  const uint64_t stage_budget = std::max<uint64_t>(std::min<uint64_t>(e->scratch_budget, 2ull << 30), WC);
+  const uint64_t chunk = std::max<uint64_t>(1, std::min<uint64_t>(nq, stage_budget / WC));
+  DMG_TRY(c->scratch.reserve(chunk * WC));
+  DMG_TRY(c->tmp0.reserve(nq * 4));
+  DMG_TRY(c->tmp1.reserve(nq * 8));
+  DMG_TRY(reset_counters(c));
+  KhopArgs a;
+  memset(&a, 0, sizeof(a));
+  a.out_ptr = g->d_out_ptr;
+  a.out_idx = g->d_out_idx;
+  a.in_ptr = g->d_in_ptr;
+  a.in_idx = g->d_in_idx;
+  a.und_ptr = g->d_und_ptr;
+  a.und_idx = g->d_und_idx;
+  a.part_off = g->d_part_off;
+  a.V = g->info.n_vertices;
+  a.n_parts = g->info.n_parts;
+  a.mode = mode;
+  a.k = k;
+  a.exclude = exclude_sources ? 1 : 0;
+  a.nq = nq;
+  a.q_off = c->q_off.as<uint32_t>();
+  a.q_src = c->q_src.as<uint32_t>();
+  a.ctr = c->d_counters;
+  a.win_cap = WC;
+  a.stage = c->scratch.as<uint8_t>();
+  a.counts = c->tmp0.as<uint32_t>();
+  a.qwin = c->tmp1.as<uint32_t>();
+  int occ = 0;
+  size_t smem = 0;
+  DMG_TRY(with_small_kernel(WC, [&](auto kern, uint32_t wc) -> int32_t {
+    smem = small_kernel_smem(wc);
+    if (smem > 48 * 1024)
+      DMG_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    DMG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, KS_THREADS, smem));
+    return DMG_OK;
+  }));
+  for (uint64_t q0 = 0; q0 < nq; q0 += chunk) {
+    const uint64_t q1 = std::min<uint64_t>(nq, q0 + chunk);
+    a.q_begin = q0;
+    a.q_end = q1;
+    DMG_CUDA(cudaMemsetAsync(&c->d_counters->ticket, 0, 8, c->stream));
+    DMG_CUDA(cudaMemsetAsync(a.stage, 0, (q1 - q0) * WC, c->stream));   // bytes past a project's end read 0
+    const uint64_t grid = std::min<uint64_t>(q1 - q0, (uint64_t)e->sm_count * std::max(occ, 1));
+    {
+      LaunchScope ls(c, K_KHOP_SMALL);
+      with_small_kernel(WC, [&](auto kern, uint32_t) -> int32_t {
+        kern<<<(unsigned)grid, KS_THREADS, smem, c->stream>>>(a);
+        return DMG_OK;
+      });
+    }
+    DMG_CUDA(cudaGetLastError());
+    DMG_CUDA(cudaMemcpyAsync(out_rows + q0 * WC, a.stage, (q1 - q0) * WC, cudaMemcpyDeviceToHost, c->stream));
+    if (q1 < nq) DMG_CUDA(cudaStreamSynchronize(c->stream));   // the staging rows are reused by the next chunk
+  }
+  DMG_CUDA(cudaMemcpyAsync(out_win, a.qwin, nq * 8, cudaMemcpyDeviceToHost, c->stream));
+  DMG_TRY(fetch_counters(c));
+  c->stats.d2h_bytes += nq * (uint64_t)WC + nq * 8 + sizeof(DevCounters);
+  DMG_TRY(c->finish());
+  c->stats.edges_traversed = c->h_counters->edges;
+  c->stats.edges_read = c->h_counters->aux[0];
+  c->stats.rows_expanded = c->h_counters->rows;
+  publish_stats(c->stats);
+  return DMG_OK;
+}
+
 // ---- dmg_neighbors_batch_dev_static: the k-hop batch without a single allocation ---------------
 // Scratch for the small-project kernel chain (counters, scan status words, row sizes, per-query
 // window, staging rows) lives in this file-scope device array instead of cudaMalloc'ed buffers.

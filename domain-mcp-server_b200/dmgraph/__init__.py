@@ -84,6 +84,7 @@ def lib():
             "dmg_adjacency_batch": (i32, [vp, i32, u64, vp, vp, vp, u64, pu64]),
             "dmg_neighbors_batch": (i32, [vp, i32, i32, i32, u64, vp, vp, vp, vp, vp, u64, pu64]),
             "dmg_neighbors_batch_dev": (i32, [vp, i32, i32, i32, u64, vp, vp, vp, vp, vp, u64, pu64]),
+            "dmg_neighbors_batch_rows": (i32, [vp, i32, i32, i32, u64, vp, vp, C.POINTER(u32), vp, vp, u64, pu64]),
             "dmg_neighbors_batch_dev_static": (i32, [vp, i32, i32, i32, u64, vp, vp, vp, vp, vp, u64, pu64]),
             "dmg_closure": (i32, [vp, i32, u32, vp, vp, pu64]),
             "dmg_analysis_order": (i32, [vp, vp]),
@@ -296,6 +297,24 @@ class Graph:
                                             C.c_void_p(d_out_hop), cap, C.byref(need))
         _check(rc, allow=(ECAP,))
         return rc, need.value
+
+    def neighbors_batch_rows(self, mode, k, exclude_sources, q_off, q_src, out=None):
+        """Dense rows: returns (stride, win[nq,2], rows[nq,stride]) -- one hop byte per project vertex."""
+        q_off, q_src = _arr(q_off, np.uint32), _arr(q_src, np.uint32)
+        nq = q_off.size - 1
+        stride, need = C.c_uint32(0), C.c_uint64(0)
+        rc = self.L.dmg_neighbors_batch_rows(self.h, mode, k, int(exclude_sources), nq, _ptr(q_off), _ptr(q_src),
+                                             C.byref(stride), None, None, 0, C.byref(need))
+        _check(rc, allow=(ECAP,))
+        if out is None:
+            win = np.zeros((max(nq, 1), 2), np.uint32)
+            rows = np.zeros(max(need.value, 1), np.uint8)
+        else:
+            win, rows = out
+        _check(self.L.dmg_neighbors_batch_rows(self.h, mode, k, int(exclude_sources), nq, _ptr(q_off), _ptr(q_src),
+                                               C.byref(stride), win.ctypes.data, rows.ctypes.data, rows.size,
+                                               C.byref(need)))
+        return stride.value, win[:nq], rows[:need.value].reshape(nq, stride.value) if nq else rows[:0]
 
     def neighbors_batch_dev_static(self, mode, k, exclude_sources, nq, d_q_off, d_q_src, d_out_off, d_out_ids,
                                    d_out_hop, cap):

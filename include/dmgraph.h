@@ -170,6 +170,17 @@ int32_t dmg_neighbors_batch_dev(dmg_graph* g, int32_t mode, int32_t k, int32_t e
                                 uint64_t* d_out_off, uint32_t* d_out_ids, uint8_t* d_out_hop,
                                 uint64_t cap, uint64_t* needed);
 
+/* Dense form of the same result, for graphs whose projects have <= 8192 vertices: row q is
+ * *out_row_stride bytes, byte (v - lo_q) = hop of vertex v (0 = not a neighbour, 255 = excluded
+ * source), with out_win[2q] = lo_q (first vertex of the query's project) and out_win[2q+1] = the
+ * project's vertex count; bytes past the project's end are 0.  When k hops cover most of a project
+ * (BASELINE config 2: ~1,990 of 2,000 vertices) this is 5x fewer bytes over PCIe than (id, hop)
+ * pairs, and the host walks the row in id order.  cap_bytes / needed_bytes count bytes of out_rows. */
+int32_t dmg_neighbors_batch_rows(dmg_graph* g, int32_t mode, int32_t k, int32_t exclude_sources,
+                                 uint64_t n_queries, const uint32_t* q_off, const uint32_t* q_src,
+                                 uint32_t* out_row_stride, uint32_t* out_win, uint8_t* out_rows,
+                                 uint64_t cap_bytes, uint64_t* needed_bytes);
+
 /* The same k-hop batch for callers that must not allocate.  It has no counterpart in the
  * reference.  Some hosts cannot afford, or are not allowed, a cudaMalloc on the query path: a
  * request thread with a latency budget (device allocation can stall behind all other work on the

@@ -553,3 +553,22 @@ def test_concurrent_readers_one_graph(engine):
         t.join()
     assert not errors, errors[:3]
     g.release()
+
+
+def test_dense_rows_equal_packed_rows(engine):
+    """dmg_neighbors_batch_rows carries the same sets and hops as dmg_neighbors_batch."""
+    sg = synth.eco_graph(n_projects=5, v_per=900, e_per=7000, cap=100, seed=12)
+    g = dmgraph.Graph(engine, sg.n_vertices, sg.src, sg.dst, sg.entry, part_off=sg.part_off)
+    q_off, q_src = synth.stacktrace_queries(sg, n_queries=700, frames=5, seed=13)
+    q_src[3] = 0xFFFFFFF0                                   # an unknown frame
+    for mode, k, excl in [(2, 2, 1), (0, 3, 0), (1, 1, 1)]:
+        off, ids, hop = g.neighbors_batch(mode, k, excl, q_off, q_src)
+        stride, win, rows = g.neighbors_batch_rows(mode, k, excl, q_off, q_src)
+        assert stride == 1024 and rows.shape == (700, 1024)
+        for q in range(700):
+            r = rows[q]
+            loc = np.nonzero((r != 0) & (r != 255))[0]
+            a, b = int(off[q]), int(off[q + 1])
+            assert np.array_equal(loc + win[q, 0], ids[a:b]) and np.array_equal(r[loc], hop[a:b])
+            assert win[q, 1] in (0, 900) and not r[900:].any()
+    g.release()
