@@ -7,6 +7,7 @@
 namespace dmg {
 
 constexpr int CL_THREADS = 256;
+constexpr uint32_t HYBRID_MIN_VERTICES = 1u << 15;
 
 struct LevelCounters {
   unsigned int next_count;
@@ -207,6 +208,11 @@ __global__ void order_seed_kernel(const uint32_t* __restrict__ entry, uint32_t n
 
 }  // namespace dmg
 
+namespace dmg {
+int32_t closure_hybrid(CallCtx* c, dmg_graph* g, int dir, uint32_t n_src, const uint32_t* d_src, uint32_t* level,
+                       uint64_t* reached, uint64_t* te_out, uint64_t* read_out, uint64_t* rows_out);
+}
+
 using namespace dmg;
 
 extern "C" {
@@ -229,9 +235,23 @@ int32_t dmg_closure(dmg_graph* g, int32_t dir, uint32_t n_src, const uint32_t* s
   if (!c) return DMG_ECUDA;
   DMG_TRY(c->begin());
   DMG_TRY(c->tmp0.reserve((size_t)V * 4));   // level
+  DMG_TRY(c->q_src.reserve((size_t)std::max<uint32_t>(n_src, 1) * 4));
+  if (V >= HYBRID_MIN_VERTICES) {
+    // large graphs: bitmap frontiers, push while the frontier is small, pull when it is large
+    if (n_src) DMG_CUDA(cudaMemcpyAsync(c->q_src.p, src, (size_t)n_src * 4, cudaMemcpyHostToDevice, c->stream));
+    c->stats.h2d_bytes += (uint64_t)n_src * 4;
+    uint64_t te = 0, rd = 0, rows = 0;
+    DMG_TRY(closure_hybrid(c, g, dir, n_src, c->q_src.as<uint32_t>(), c->tmp0.as<uint32_t>(), reached, &te, &rd, &rows));
+    DMG_CUDA(cudaMemcpyAsync(out_level, c->tmp0.p, (size_t)V * 4, cudaMemcpyDeviceToHost, c->stream));
+    c->stats.d2h_bytes += (uint64_t)V * 4;
+    c->stats.edges_traversed = te;
+    c->stats.edges_read = rd;
+    c->stats.rows_expanded = rows;
+    c->stats.results = *reached;
+    return c->finish();
+  }
   DMG_TRY(c->tmp1.reserve((size_t)V * 4));   // frontier A
   DMG_TRY(c->tmp2.reserve((size_t)V * 4));   // frontier B
-  DMG_TRY(c->q_src.reserve((size_t)std::max<uint32_t>(n_src, 1) * 4));
   uint32_t* level = c->tmp0.as<uint32_t>();
   uint32_t* fa = c->tmp1.as<uint32_t>();
   uint32_t* fb = c->tmp2.as<uint32_t>();

@@ -107,6 +107,98 @@ __global__ void __launch_bounds__(CP_THREADS) part_merge_kernel(const uint32_t* 
   if ((threadIdx.x & 31) == 0 && c) atomicAdd(&ctr->total, (unsigned long long)c);
 }
 
+// sum of the row lengths of the frontier's vertices (the TE figure of a pull level)
+__global__ void __launch_bounds__(CP_THREADS) frontier_degree_kernel(const uint32_t* __restrict__ ptr, uint32_t words,
+                                                                     uint32_t V, const uint32_t* __restrict__ frontier,
+                                                                     DevCounters* ctr) {
+  const uint32_t w = blockIdx.x * blockDim.x + threadIdx.x;
+  unsigned long long te = 0, rows = 0;
+  if (w < words)
+    for (uint32_t b = frontier[w]; b; b &= b - 1) {
+      const uint32_t v = w * 32 + (__ffs(b) - 1);
+      if (v < V) {
+        te += ptr[v + 1] - ptr[v];
+        ++rows;
+      }
+    }
+  te = warp_sum_u64(te);
+  rows = warp_sum_u64(rows);
+  if ((threadIdx.x & 31) == 0 && rows) {
+    atomicAdd(&ctr->aux[0], te);
+    atomicAdd(&ctr->rows, rows);
+  }
+}
+
+__global__ void source_bits_kernel(const uint32_t* __restrict__ src, uint32_t ns, uint32_t V, uint32_t* bits) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < ns && src[i] < V) atomicOr(&bits[src[i] >> 5], 1u << (src[i] & 31));
+}
+
+// Direction-optimising closure on one GPU over bitmaps: the same push / pull / merge kernels as
+// the partitioned closure with the whole vertex range owned here.  Leaves levels in `level`.
+int32_t closure_hybrid(CallCtx* c, dmg_graph* g, int dir, uint32_t n_src, const uint32_t* d_src, uint32_t* level,
+                       uint64_t* reached, uint64_t* te_out, uint64_t* read_out, uint64_t* rows_out) {
+  const uint32_t V = g->info.n_vertices, words = (V + 31) / 32;
+  DMG_TRY(c->tmp1.reserve((size_t)words * 4 * 4 + 64));
+  uint32_t* frontier = c->tmp1.as<uint32_t>();
+  uint32_t* visited = frontier + words;
+  uint32_t* next = visited + words;
+  uint32_t* contrib = next + words;
+  DMG_CUDA(cudaMemsetAsync(frontier, 0, (size_t)words * 16, c->stream));
+  DMG_CUDA(cudaMemsetAsync(level, 0xFF, (size_t)V * 4, c->stream));
+  const uint32_t* ptr = dir == DMG_OUT ? g->d_out_ptr : g->d_in_ptr;
+  const uint32_t* idx = dir == DMG_OUT ? g->d_out_idx : g->d_in_idx;
+  const uint32_t* rptr = dir == DMG_OUT ? g->d_in_ptr : g->d_out_ptr;
+  const uint32_t* ridx = dir == DMG_OUT ? g->d_in_idx : g->d_out_idx;
+  const unsigned wgrid = (words + CP_THREADS - 1) / CP_THREADS;
+  const unsigned xgrid = (unsigned)std::min<uint64_t>(((uint64_t)words * 32 + CP_THREADS - 1) / CP_THREADS,
+                                                      (uint64_t)g->eng->sm_count * 8);
+  auto merge = [&](uint32_t lvl, uint64_t* n_new) -> int32_t {
+    DMG_CUDA(cudaMemsetAsync(&c->d_counters->total, 0, 8, c->stream));
+    {
+      LaunchScope ls(c, K_MISC);
+      part_merge_kernel<<<wgrid, CP_THREADS, 0, c->stream>>>(contrib, 1, words, words, visited, next, 0, V, lvl, level,
+                                                             c->d_counters);
+    }
+    DMG_CUDA(cudaGetLastError());
+    DMG_CUDA(cudaMemcpyAsync(c->h_counters, c->d_counters, sizeof(DevCounters), cudaMemcpyDeviceToHost, c->stream));
+    DMG_CUDA(cudaStreamSynchronize(c->stream));
+    *n_new = c->h_counters->total;
+    return DMG_OK;
+  };
+  DMG_CUDA(cudaMemsetAsync(c->d_counters, 0, sizeof(DevCounters), c->stream));
+  if (n_src) {
+    LaunchScope ls(c, K_CLOSURE_INIT);
+    source_bits_kernel<<<(n_src + 255) / 256, 256, 0, c->stream>>>(d_src, n_src, V, contrib);
+  }
+  uint64_t n_front = 0, total = 0;
+  DMG_TRY(merge(0, &n_front));
+  total = n_front;
+  for (uint32_t lvl = 1; n_front > 0; ++lvl) {
+    std::swap(frontier, next);
+    {
+      LaunchScope ls(c, K_ORDER_DEG);
+      frontier_degree_kernel<<<wgrid, CP_THREADS, 0, c->stream>>>(ptr, words, V, frontier, c->d_counters);
+    }
+    if (n_front * 32 < V) {
+      DMG_CUDA(cudaMemsetAsync(contrib, 0, (size_t)words * 4, c->stream));
+      LaunchScope ls(c, K_CLOSURE_STEP);
+      part_push_kernel<<<xgrid, CP_THREADS, 0, c->stream>>>(ptr, idx, 0, words, 0, V, frontier, contrib, c->d_counters);
+    } else {
+      LaunchScope ls(c, K_CLOSURE_BOTTOMUP);
+      part_pull_kernel<<<xgrid, CP_THREADS, 0, c->stream>>>(rptr, ridx, 0, words, 0, V, frontier, visited, contrib,
+                                                            c->d_counters);
+    }
+    DMG_TRY(merge(lvl, &n_front));
+    total += n_front;
+  }
+  *reached = total;
+  *te_out = c->h_counters->aux[0];
+  *read_out = c->h_counters->edges;
+  *rows_out = c->h_counters->rows;
+  return DMG_OK;
+}
+
 static int32_t part_args(dmg_graph* g, int32_t dir, uint32_t v_lo, uint32_t v_hi, const char* who) {
   if (!g) {
     set_error("%s: NULL graph", who);

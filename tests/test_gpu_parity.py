@@ -212,7 +212,7 @@ def test_empty_and_ragged_inputs(engine):
 # ---- closure / analysisOrder ------------------------------------------------------------------
 def test_closure_and_order_random(engine):
     rng = np.random.default_rng(21)
-    for n, e in [(2, 1), (40, 60), (500, 900), (5000, 20000), (20000, 30000)]:
+    for n, e in [(2, 1), (40, 60), (500, 900), (5000, 20000), (20000, 30000), (40000, 90000), (150000, 900000)]:
         src, dst, entry, part_off = _random_graph(rng, n, e, 1)
         g = dmgraph.Graph(engine, n, src, dst, entry)
         o = ora.CsrOracle(n, src, dst, entry)
@@ -233,6 +233,32 @@ def test_order_deep_chain(engine):
     assert g.analysis_order().tolist() == list(range(n - 1, -1, -1))
     lvl, reached = g.closure(0, [n - 1])
     assert reached == n and lvl.tolist() == list(range(n - 1, -1, -1))
+    g.release()
+
+
+def test_closure_hybrid_shapes(engine):
+    """>= 32768 vertices take the bitmap push/pull closure: a deep chain (push only), a star and a
+    dense random graph (pull levels), all four direction / source combinations."""
+    n = 40000
+    chain = np.arange(n - 1, dtype=np.uint32)
+    g = dmgraph.Graph(engine, n, chain, chain + 1, [])
+    lvl, reached = g.closure(0, [0])
+    assert reached == n and np.array_equal(lvl, np.arange(n, dtype=np.uint32))
+    lvl, reached = g.closure(1, [n - 1, n + 5])
+    assert reached == n and np.array_equal(lvl, np.arange(n - 1, -1, -1, dtype=np.uint32))
+    g.release()
+    rng = np.random.default_rng(8)
+    src = rng.integers(0, n, 600000).astype(np.uint32)
+    dst = rng.integers(0, n, 600000).astype(np.uint32)
+    g = dmgraph.Graph(engine, n, src, dst, [])
+    o = ora.CsrOracle(n, src, dst, [])
+    for d in (0, 1):
+        for s in ([7], list(range(0, n, 3))):
+            lvl, reached = g.closure(d, s)
+            wl, wr, wte = o.closure(d, s)
+            assert reached == wr and np.array_equal(lvl, wl)
+            st = engine.last_stats()
+            assert st["edges_traversed"] == wte and st["edges_read"] <= 2 * wte + n
     g.release()
 
 
