@@ -432,20 +432,27 @@ __global__ void __launch_bounds__(EM_THREADS, 6) khop_emit_kernel(const uint8_t*
 // ---------------------------------------------------------------------------------------------
 constexpr int KG_THREADS = 256;
 constexpr int KG_SORT_CAP = 4096;
+constexpr int KG_BUCKETS = 1024;
+constexpr uint32_t KG_BUCKET_MAX = 48;   // longest bucket a single thread insertion-sorts
 
 __global__ void __launch_bounds__(KG_THREADS) khop_global_kernel(const KhopArgs a, uint32_t* sc_seen, uint8_t* sc_hop,
                                                                  uint32_t* sc_queue, size_t seen_words,
                                                                  size_t hop_bytes, size_t qcap) {
   constexpr int THREADS = KG_THREADS, NW = THREADS / 32;
-  __shared__ unsigned long long s_key[KG_SORT_CAP];
+  __shared__ uint32_t s_ids[KG_SORT_CAP];
+  __shared__ uint8_t s_hopv[KG_SORT_CAP];
+  __shared__ uint32_t s_hist[KG_BUCKETS + 1], s_cur[KG_BUCKETS];
   __shared__ unsigned long long s_q, s_base;
-  __shared__ uint32_t s_lo, s_hi, s_tail;
+  __shared__ uint32_t s_lo, s_hi, s_tail, s_flag;
   __shared__ uint32_t s_seg[DMG_MAX_HOPS + 2];
   __shared__ uint32_t s_wsum[NW + 1];
+  __shared__ uint32_t s_end[THREADS], s_adj[THREADS];
   uint32_t* seen = sc_seen + (size_t)blockIdx.x * seen_words;
   uint8_t* hopg = sc_hop + (size_t)blockIdx.x * hop_bytes;
   uint32_t* queue = sc_queue + (size_t)blockIdx.x * qcap;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const uint32_t* __restrict__ fptr = a.mode == DMG_BOTH ? a.und_ptr : (a.mode == DMG_OUT ? a.out_ptr : a.in_ptr);
+  const uint32_t* __restrict__ fidx = a.mode == DMG_BOTH ? a.und_idx : (a.mode == DMG_OUT ? a.out_idx : a.in_idx);
   unsigned long long te = 0, rows = 0;
 
   while (true) {
@@ -485,48 +492,63 @@ __global__ void __launch_bounds__(KG_THREADS) khop_global_kernel(const KhopArgs 
     if (tid == 0) s_seg[0] = ns;
     int nlev = 0;
     for (int lvl = 1; lvl <= a.k && head < tail; ++lvl) {
-      for (uint32_t i = head + warp; i < tail; i += NW) {
-        const uint32_t u = lo + queue[i];
-        uint32_t b0 = 0, n0 = 0, b1 = 0, n1 = 0;
-        if (a.mode != DMG_IN) {
-          b0 = a.out_ptr[u];
-          n0 = a.out_ptr[u + 1] - b0;
+      // the frontier's rows are flattened chunk by chunk (see khop_small_kernel)
+      for (uint32_t c0 = head; c0 < tail; c0 += THREADS) {
+        const uint32_t i = c0 + tid;
+        uint32_t b = 0, n = 0;
+        if (i < tail) {
+          const uint32_t u = lo + queue[i];
+          b = fptr[u];
+          n = fptr[u + 1] - b;
         }
-        if (a.mode != DMG_OUT) {
-          b1 = a.in_ptr[u];
-          n1 = a.in_ptr[u + 1] - b1;
+        uint32_t T;
+        const uint32_t pre = block_excl_scan<THREADS>(n, s_wsum, &T);
+        s_end[tid] = pre + n;
+        s_adj[tid] = b - pre;
+        if (tid == 0) {
+          te += T;
+          rows += min(tail - c0, (uint32_t)THREADS);
         }
-        const uint32_t n = n0 + n1;
-        if (lane == 0) {
-          te += n;
-          ++rows;
-        }
-        for (uint32_t base = 0; base < n; base += 32) {
-          const uint32_t j = base + lane;
-          bool isnew = false;
-          uint32_t v = 0;
-          if (j < n) {
-            v = (j < n0 ? a.out_idx[b0 + j] : a.in_idx[b1 + (j - n0)]) - lo;
-            const uint32_t bit = 1u << (v & 31);
-            if (!(__ldcg(&seen[v >> 5]) & bit)) isnew = !(atomicOr(&seen[v >> 5], bit) & bit);
+        __syncthreads();
+        const uint32_t Tq = (((T + NW - 1) / NW) + 31u) & ~31u;
+        const uint32_t pbeg = warp * Tq, pend = min(T, pbeg + Tq);
+        if (pbeg < pend) {
+          uint32_t r;
+          {
+            uint32_t l = 0, h = THREADS;
+            while (l < h) {
+              const uint32_t m = (l + h) >> 1;
+              if (s_end[m] <= pbeg) l = m + 1; else h = m;
+            }
+            r = l;
           }
-          const unsigned m = __ballot_sync(FULL, isnew);
-          if (m) {
-            uint32_t pos = 0;
-            if (lane == 0) pos = atomicAdd(&s_tail, (uint32_t)__popc(m));
-            pos = __shfl_sync(FULL, pos, 0);
-            if (isnew) queue[pos + __popc(m & lanemask_lt())] = v;
+          for (uint32_t p0 = pbeg; p0 < pend; p0 += 32) {
+            const uint32_t p = p0 + lane;
+            bool isnew = false;
+            uint32_t v = 0;
+            if (p < pend) {
+              while (s_end[r] <= p) ++r;
+              v = fidx[s_adj[r] + p] - lo;
+              const uint32_t bit = 1u << (v & 31);
+              if (!(__ldcg(&seen[v >> 5]) & bit)) isnew = !(atomicOr(&seen[v >> 5], bit) & bit);
+            }
+            const unsigned m = __ballot_sync(FULL, isnew);
+            if (m) {
+              uint32_t pos = 0;
+              if (lane == 0) pos = atomicAdd(&s_tail, (uint32_t)__popc(m));
+              pos = __shfl_sync(FULL, pos, 0);
+              if (isnew) queue[pos + __popc(m & lanemask_lt())] = v;
+            }
           }
         }
+        __syncthreads();
       }
-      __syncthreads();
       head = tail;
       tail = s_tail;
       nlev = lvl;
       if (tid == 0) s_seg[lvl] = tail;   // level lvl is queue[s_seg[lvl-1], s_seg[lvl])
       __syncthreads();
     }
-    __syncthreads();
     const uint32_t total = tail - ns;
     if (warp == 0) {
       const unsigned long long excl = lookback_exclusive(a.status, q, total);
@@ -539,46 +561,75 @@ __global__ void __launch_bounds__(KG_THREADS) khop_global_kernel(const KhopArgs 
         }
       }
     }
+    if (tid == 0) s_flag = 0;
+    for (uint32_t i = tid; i <= KG_BUCKETS; i += THREADS) s_hist[i] = 0;
     __syncthreads();
     const unsigned long long base = s_base;
-    if (total && total <= (uint32_t)KG_SORT_CAP) {
-      // short row: (id << 8 | hop) keys, bitonic sort in shared memory
-      uint32_t n2 = 32;
-      while (n2 < total) n2 <<= 1;
-      for (uint32_t i = tid; i < n2; i += THREADS) {
-        unsigned long long key = ~0ull;
-        if (i < total) {
-          const uint32_t p = ns + i;
-          int lv = 1;
-          while (lv < nlev && p >= s_seg[lv]) ++lv;
-          key = ((unsigned long long)queue[p] << 8) | (unsigned)lv;
+    bool scan_path = total > (uint32_t)KG_SORT_CAP;
+    if (total && !scan_path) {
+      // short row: one MSD radix pass into <= 1024 id buckets, then each bucket is a handful of
+      // ids that one thread orders in place
+      uint32_t sh = 0;
+      while ((wn >> sh) > (uint32_t)KG_BUCKETS) ++sh;
+      for (uint32_t i = tid; i < total; i += THREADS) atomicAdd(&s_hist[queue[ns + i] >> sh], 1u);
+      __syncthreads();
+      {
+        uint32_t x[4], sum = 0;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          x[j] = s_hist[tid * 4 + j];
+          sum += x[j];
         }
-        s_key[i] = key;
+        uint32_t tot;
+        uint32_t off = block_excl_scan<THREADS>(sum, s_wsum, &tot);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          s_hist[tid * 4 + j] = off;
+          s_cur[tid * 4 + j] = off;
+          if (x[j] > KG_BUCKET_MAX) s_flag = 1;
+          off += x[j];
+        }
+        if (tid == THREADS - 1) s_hist[KG_BUCKETS] = off;
       }
       __syncthreads();
-      for (uint32_t sz = 2; sz <= n2; sz <<= 1)
-        for (uint32_t st = sz >> 1; st > 0; st >>= 1) {
-          for (uint32_t i = tid; i < n2; i += THREADS) {
-            const uint32_t j = i ^ st;
-            if (j > i) {
-              const unsigned long long x = s_key[i], y = s_key[j];
-              const bool up = ((i & sz) == 0);
-              if ((x > y) == up) {
-                s_key[i] = y;
-                s_key[j] = x;
-              }
-            }
-          }
-          __syncthreads();
-        }
       for (uint32_t i = tid; i < total; i += THREADS) {
-        const unsigned long long pos = base + i;
-        if (pos < a.cap) {
-          a.out_ids[pos] = lo + (uint32_t)(s_key[i] >> 8);
-          a.out_hop[pos] = (uint8_t)(s_key[i] & 255u);
-        }
+        const uint32_t p = ns + i, v = queue[p];
+        int lv = 1;
+        while (lv < nlev && p >= s_seg[lv]) ++lv;
+        const uint32_t pos = atomicAdd(&s_cur[v >> sh], 1u);
+        s_ids[pos] = v;
+        s_hopv[pos] = (uint8_t)lv;
       }
-    } else if (total) {
+      __syncthreads();
+      if (!s_flag) {
+        for (uint32_t bkt = tid; bkt < (uint32_t)KG_BUCKETS; bkt += THREADS) {
+          const uint32_t b0 = s_hist[bkt], b1 = s_hist[bkt + 1];
+          for (uint32_t i = b0 + 1; i < b1; ++i) {
+            const uint32_t v = s_ids[i];
+            const uint8_t h = s_hopv[i];
+            uint32_t j = i;
+            while (j > b0 && s_ids[j - 1] > v) {
+              s_ids[j] = s_ids[j - 1];
+              s_hopv[j] = s_hopv[j - 1];
+              --j;
+            }
+            s_ids[j] = v;
+            s_hopv[j] = h;
+          }
+        }
+        __syncthreads();
+        for (uint32_t i = tid; i < total; i += THREADS) {
+          const unsigned long long pos = base + i;
+          if (pos < a.cap) {
+            a.out_ids[pos] = lo + s_ids[i];
+            a.out_hop[pos] = s_hopv[i];
+          }
+        }
+      } else {
+        scan_path = true;   // ids clustered in few buckets: use the bitmap scan instead
+      }
+    }
+    if (total && scan_path) {
       // long row: hop bytes into scratch, then an ordered scan of the claim bitmap
       for (uint32_t i = tid; i < ns; i += THREADS)
         if (a.exclude) hopg[queue[i]] = 255;
@@ -597,15 +648,15 @@ __global__ void __launch_bounds__(KG_THREADS) khop_global_kernel(const KhopArgs 
         const uint32_t w = w0 + tid;
         uint32_t bits = (w < nwords) ? __ldcg(&seen[w]) : 0u;
         uint32_t keep = 0;
-        for (uint32_t b = bits; b; b &= b - 1) {
-          const uint32_t v = w * 32 + (__ffs(b) - 1);
+        for (uint32_t bb = bits; bb; bb &= bb - 1) {
+          const uint32_t v = w * 32 + (__ffs(bb) - 1);
           if (__ldcg(&hopg[v]) != 255) keep |= 1u << (v & 31);
         }
         uint32_t tot;
         const uint32_t off = block_excl_scan<THREADS>(__popc(keep), s_wsum, &tot);
         unsigned long long pos = run + off;
-        for (uint32_t b = keep; b; b &= b - 1) {
-          const uint32_t v = w * 32 + (__ffs(b) - 1);
+        for (uint32_t bb = keep; bb; bb &= bb - 1) {
+          const uint32_t v = w * 32 + (__ffs(bb) - 1);
           if (pos < a.cap) {
             a.out_ids[pos] = lo + v;
             a.out_hop[pos] = __ldcg(&hopg[v]);
