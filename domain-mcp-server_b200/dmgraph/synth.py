@@ -184,6 +184,29 @@ def big_graph(n_vertices, n_edges, cap, entry_frac, seed, with_names=False):
     return SynthGraph(names, s, d, entry, np.array([0, n_vertices]))
 
 
+def big_graph_fast(n_vertices, n_edges, cap, entry_frac, seed):
+    """Config-5-sized graphs (20 M / 500 M): same out-degree law and Zipf(s=1) target ranking as
+    big_graph, but targets are drawn WITH replacement in one vectorised pass (the exact
+    without-replacement rejection loop needs several sorts of 10^9 keys).  Repeated (src, dst) pairs
+    are legal input -- addDependency collapses them (ProjectGraph.java:182) and so does
+    dmg_graph_create -- so the graph the engine holds has slightly fewer edges than drawn; the
+    kept count is in dmg_graph_info."""
+    rng = np.random.Generator(np.random.PCG64(seed))
+    deg = _degrees(rng, n_vertices, n_edges, cap)
+    perm = rng.permutation(n_vertices).astype(np.uint32)
+    cdf = np.cumsum(1.0 / np.arange(1, n_vertices + 1))
+    cdf /= cdf[-1]
+    src = np.repeat(np.arange(n_vertices, dtype=np.uint32), deg)
+    dst = np.empty(src.size, np.uint32)
+    step = 50_000_000
+    for a in range(0, src.size, step):
+        b = min(src.size, a + step)
+        dst[a:b] = perm[np.searchsorted(cdf, rng.random(b - a), side="left").clip(0, n_vertices - 1)]
+    ne = max(1, int(round(entry_frac * n_vertices)))
+    entry = np.sort(rng.choice(n_vertices, ne, replace=False))
+    return SynthGraph(None, src, dst, entry, np.array([0, n_vertices]))
+
+
 def out_csr(g):
     """Forward CSR of a SynthGraph (host-side helper for the query generators)."""
     n = g.n_vertices
