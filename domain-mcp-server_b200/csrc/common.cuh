@@ -15,6 +15,19 @@
 
 namespace dmg {
 
+// FNV-1a over the bytes, then a finaliser; the same function builds the tables on the host and
+// probes them on the device
+#ifdef __CUDACC__
+__host__ __device__
+#endif
+inline uint32_t name_hash(const uint8_t* p, uint32_t n) {
+  unsigned long long h = 0xCBF29CE484222325ull;
+  for (uint32_t i = 0; i < n; ++i) h = (h ^ p[i]) * 0x100000001B3ull;
+  h ^= h >> 32;
+  h *= 0xD6E8FEB86659FD93ull;
+  return (uint32_t)(h >> 32);
+}
+
 // ---------------------------------------------------------------------------------------------
 // errors: thread-local message, status codes; nothing is ever printed (MCP stdio hygiene)
 // ---------------------------------------------------------------------------------------------
@@ -171,7 +184,11 @@ struct dmg_graph {
   uint32_t* d_entry = nullptr;     // [n_entry] insertion order
   uint32_t* d_entry_bits = nullptr;  // [ceil(V/32)]
   uint64_t* d_name_off = nullptr;  // [V+1] or null
-  uint8_t* d_lower = nullptr;      // pre-lowered name arena (+16 B zero pad)
+  uint8_t* d_lower = nullptr;      // pre-lowered name arena (+32 B zero pad)
+  uint8_t* d_names = nullptr;      // original name arena (exact identifier lookups are case sensitive)
+  uint32_t* d_full_tbl = nullptr;  // open addressing: hash(identifier) -> vertex id, 0xFFFFFFFF = empty
+  uint32_t* d_simple_tbl = nullptr;  // hash(lower-cased simple name) -> vertex id
+  uint32_t tbl_mask = 0;
   uint32_t* d_method_off = nullptr;  // [V+1] optional method catalog (names only)
   uint32_t* d_mname_off = nullptr;   // [M+1]
   uint8_t* d_mname_lower = nullptr;

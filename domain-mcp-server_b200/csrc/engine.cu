@@ -155,7 +155,7 @@ static void free_graph(dmg_graph* g) {
   cudaSetDevice(g->eng->device);
   for (void* p : {(void*)g->d_out_ptr, (void*)g->d_out_idx, (void*)g->d_in_ptr, (void*)g->d_in_idx,
                   (void*)g->d_und_ptr, (void*)g->d_und_idx, (void*)g->d_part_off, (void*)g->d_entry, (void*)g->d_entry_bits, (void*)g->d_name_off,
-                  (void*)g->d_lower, (void*)g->d_method_off, (void*)g->d_mname_off, (void*)g->d_mname_lower})
+                  (void*)g->d_lower, (void*)g->d_names, (void*)g->d_full_tbl, (void*)g->d_simple_tbl, (void*)g->d_method_off, (void*)g->d_mname_off, (void*)g->d_mname_lower})
     if (p) cudaFree(p);
   delete g;
 }
@@ -392,8 +392,34 @@ int32_t dmg_graph_create(dmg_engine* e, const dmg_graph_desc* d, dmg_graph** out
     if (!d->lower_bytes)
       for (uint64_t i = 0; i < nbytes; ++i)
         if (low[i] >= 'A' && low[i] <= 'Z') low[i] += 32;   // ASCII fold only
+    // name -> id tables: exact identifier (nodes.containsKey, case
+    // sensitive) and lower-cased simple name (GQS:434-446); linear probing, load <= 0.5
+    uint32_t size = 16;
+    while (size < 2ull * V + 1) size <<= 1;
+    std::vector<uint32_t> full_tbl(size, 0xFFFFFFFFu), simple_tbl(size, 0xFFFFFFFFu);
+    std::vector<uint8_t> orig(nbytes + 32, 0);
+    if (nbytes) memcpy(orig.data(), d->name_bytes, nbytes);
+    for (uint32_t v = 0; v < V; ++v) {
+      const uint64_t b = d->name_off[v], e2 = d->name_off[v + 1];
+      uint32_t h = name_hash(orig.data() + b, (uint32_t)(e2 - b)) & (size - 1);
+      while (full_tbl[h] != 0xFFFFFFFFu) h = (h + 1) & (size - 1);
+      full_tbl[h] = v;
+      uint64_t sb = b;
+      for (uint64_t i = e2; i > b; --i)
+        if (low[i - 1] == '.') {   // extractSimpleName: after the last '.' (GQS:458-461)
+          sb = i;
+          break;
+        }
+      h = name_hash(low.data() + sb, (uint32_t)(e2 - sb)) & (size - 1);
+      while (simple_tbl[h] != 0xFFFFFFFFu) h = (h + 1) & (size - 1);
+      simple_tbl[h] = v;
+    }
+    g->tbl_mask = size - 1;
     if ((st = upload(&g->d_name_off, d->name_off, (size_t)V + 1, &bytes)) != DMG_OK ||
-        (st = upload(&g->d_lower, low.data(), low.size(), &bytes)) != DMG_OK) {
+        (st = upload(&g->d_lower, low.data(), low.size(), &bytes)) != DMG_OK ||
+        (st = upload(&g->d_names, orig.data(), orig.size(), &bytes)) != DMG_OK ||
+        (st = upload(&g->d_full_tbl, full_tbl.data(), full_tbl.size(), &bytes)) != DMG_OK ||
+        (st = upload(&g->d_simple_tbl, simple_tbl.data(), simple_tbl.size(), &bytes)) != DMG_OK) {
       free_graph(g);
       return st;
     }

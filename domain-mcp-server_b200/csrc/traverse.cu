@@ -84,7 +84,7 @@ __device__ __forceinline__ void find_window(const KhopArgs& a, uint32_t qb, uint
 constexpr uint32_t BU_ALPHA = 24;
 
 template <int THREADS, int WC>
-__global__ void __launch_bounds__(THREADS) khop_small_kernel(const KhopArgs a) {
+__global__ void __launch_bounds__(THREADS, 12) khop_small_kernel(const KhopArgs a) {
   extern __shared__ __align__(16) unsigned char smem[];
   uint8_t* const hop8 = smem;                                             // WC bytes
   uint32_t* const hop32 = reinterpret_cast<uint32_t*>(smem);
@@ -431,17 +431,19 @@ __global__ void __launch_bounds__(EM_THREADS, 6) khop_emit_kernel(const uint8_t*
 // sparsely (by walking the queue), so the cost of a query follows its result, not V.
 // ---------------------------------------------------------------------------------------------
 constexpr int KG_THREADS = 256;
-constexpr int KG_SORT_CAP = 4096;
-constexpr int KG_BUCKETS = 1024;
+constexpr int KG_SORT_CAP = 16384;   // rows up to this length are ordered in shared memory
+constexpr int KG_BUCKETS = 2048;
 constexpr uint32_t KG_BUCKET_MAX = 48;   // longest bucket a single thread insertion-sorts
 
 __global__ void __launch_bounds__(KG_THREADS) khop_global_kernel(const KhopArgs a, uint32_t* sc_seen, uint8_t* sc_hop,
                                                                  uint32_t* sc_queue, size_t seen_words,
                                                                  size_t hop_bytes, size_t qcap) {
   constexpr int THREADS = KG_THREADS, NW = THREADS / 32;
-  __shared__ uint32_t s_ids[KG_SORT_CAP];
-  __shared__ uint8_t s_hopv[KG_SORT_CAP];
-  __shared__ uint32_t s_hist[KG_BUCKETS + 1], s_cur[KG_BUCKETS];
+  extern __shared__ __align__(16) unsigned char kg_smem[];
+  uint32_t* s_ids = reinterpret_cast<uint32_t*>(kg_smem);                    // [KG_SORT_CAP]
+  uint32_t* s_hist = s_ids + KG_SORT_CAP;                                    // [KG_BUCKETS + 1]
+  uint32_t* s_cur = s_hist + KG_BUCKETS + 8;                                 // [KG_BUCKETS]
+  uint8_t* s_hopv = reinterpret_cast<uint8_t*>(s_cur + KG_BUCKETS);          // [KG_SORT_CAP]
   __shared__ unsigned long long s_q, s_base;
   __shared__ uint32_t s_lo, s_hi, s_tail, s_flag;
   __shared__ uint32_t s_seg[DMG_MAX_HOPS + 2];
@@ -574,18 +576,19 @@ __global__ void __launch_bounds__(KG_THREADS) khop_global_kernel(const KhopArgs 
       for (uint32_t i = tid; i < total; i += THREADS) atomicAdd(&s_hist[queue[ns + i] >> sh], 1u);
       __syncthreads();
       {
-        uint32_t x[4], sum = 0;
+        constexpr int PER = KG_BUCKETS / THREADS;
+        uint32_t x[PER], sum = 0;
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          x[j] = s_hist[tid * 4 + j];
+        for (int j = 0; j < PER; ++j) {
+          x[j] = s_hist[tid * PER + j];
           sum += x[j];
         }
         uint32_t tot;
         uint32_t off = block_excl_scan<THREADS>(sum, s_wsum, &tot);
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          s_hist[tid * 4 + j] = off;
-          s_cur[tid * 4 + j] = off;
+        for (int j = 0; j < PER; ++j) {
+          s_hist[tid * PER + j] = off;
+          s_cur[tid * PER + j] = off;
           if (x[j] > KG_BUCKET_MAX) s_flag = 1;
           off += x[j];
         }
@@ -644,24 +647,34 @@ __global__ void __launch_bounds__(KG_THREADS) khop_global_kernel(const KhopArgs 
       __syncthreads();
       const uint32_t nwords = (wn + 31) >> 5;
       unsigned long long run = base;
-      for (uint32_t w0 = 0; w0 < nwords; w0 += THREADS) {
-        const uint32_t w = w0 + tid;
-        uint32_t bits = (w < nwords) ? __ldcg(&seen[w]) : 0u;
-        uint32_t keep = 0;
-        for (uint32_t bb = bits; bb; bb &= bb - 1) {
-          const uint32_t v = w * 32 + (__ffs(bb) - 1);
-          if (__ldcg(&hopg[v]) != 255) keep |= 1u << (v & 31);
+      constexpr uint32_t WPT = 4;   // bitmap words per thread per step
+      for (uint32_t w0 = 0; w0 < nwords; w0 += THREADS * WPT) {
+        uint32_t keep[WPT], cnt = 0;
+#pragma unroll
+        for (uint32_t j = 0; j < WPT; ++j) {
+          const uint32_t w = w0 + tid * WPT + j;
+          const uint32_t bits = (w < nwords) ? __ldcg(&seen[w]) : 0u;
+          keep[j] = 0;
+          for (uint32_t bb = bits; bb; bb &= bb - 1) {
+            const uint32_t v = w * 32 + (__ffs(bb) - 1);
+            if (__ldcg(&hopg[v]) != 255) keep[j] |= 1u << (v & 31);
+          }
+          cnt += __popc(keep[j]);
         }
         uint32_t tot;
-        const uint32_t off = block_excl_scan<THREADS>(__popc(keep), s_wsum, &tot);
+        const uint32_t off = block_excl_scan<THREADS>(cnt, s_wsum, &tot);
         unsigned long long pos = run + off;
-        for (uint32_t bb = keep; bb; bb &= bb - 1) {
-          const uint32_t v = w * 32 + (__ffs(bb) - 1);
-          if (pos < a.cap) {
-            a.out_ids[pos] = lo + v;
-            a.out_hop[pos] = __ldcg(&hopg[v]);
+#pragma unroll
+        for (uint32_t j = 0; j < WPT; ++j) {
+          const uint32_t w = w0 + tid * WPT + j;
+          for (uint32_t bb = keep[j]; bb; bb &= bb - 1) {
+            const uint32_t v = w * 32 + (__ffs(bb) - 1);
+            if (pos < a.cap) {
+              a.out_ids[pos] = lo + v;
+              a.out_hop[pos] = __ldcg(&hopg[v]);
+            }
+            ++pos;
           }
-          ++pos;
         }
         run += tot;
       }
@@ -895,7 +908,9 @@ static int32_t run_khop(CallCtx* c, dmg_graph* g, int mode, int k, int exclude, 
     const size_t qcap = 2 * (size_t)maxp;
     const size_t per_block = seen_words * 4 + hop_bytes + qcap * 4;
     int occ = 0;
-    DMG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, khop_global_kernel, KG_THREADS, 0));
+    const size_t kg_smem = (size_t)KG_SORT_CAP * 5 + (2 * (size_t)KG_BUCKETS + 8) * 4;
+    DMG_CUDA(cudaFuncSetAttribute(khop_global_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kg_smem));
+    DMG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, khop_global_kernel, KG_THREADS, kg_smem));
     uint64_t grid = std::min<uint64_t>(nq, (uint64_t)e->sm_count * std::max(occ, 1));
     grid = std::max<uint64_t>(1, std::min<uint64_t>(grid, e->scratch_budget / per_block));
     DMG_TRY(c->scratch.reserve(grid * per_block));
@@ -904,7 +919,7 @@ static int32_t run_khop(CallCtx* c, dmg_graph* g, int mode, int k, int exclude, 
     uint32_t* sc_queue = reinterpret_cast<uint32_t*>(sc_hop + grid * hop_bytes);
     DMG_CUDA(cudaMemsetAsync(sc_seen, 0, grid * seen_words * 4, c->stream));
     LaunchScope ls(c, K_KHOP_GLOBAL);
-    khop_global_kernel<<<(unsigned)grid, KG_THREADS, 0, c->stream>>>(a, sc_seen, sc_hop, sc_queue, seen_words,
+    khop_global_kernel<<<(unsigned)grid, KG_THREADS, kg_smem, c->stream>>>(a, sc_seen, sc_hop, sc_queue, seen_words,
                                                                      hop_bytes, qcap);
   }
   DMG_CUDA(cudaGetLastError());

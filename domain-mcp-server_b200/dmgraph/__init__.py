@@ -15,6 +15,7 @@ OK, EINVAL, ENOMEM, ECAP, ECUDA, ENCCL, ENODEV = range(7)
 OUT, IN, BOTH = 0, 1, 2
 SEARCH_CONTAINS_ALL, SEARCH_SIMPLE_EQ_FIRST, SEARCH_CONTAINS_FIRST = 0, 1, 2
 LEVEL_UNREACHED = 0xFFFFFFFF
+LOOKUP_EXACT, LOOKUP_SIMPLE_FIRST = 0, 1
 MODES = {"out": OUT, "in": IN, "both": BOTH}
 
 
@@ -94,6 +95,7 @@ def lib():
             "dmg_entry_points": (i32, [vp, vp, u32, C.POINTER(u32)]),
             "dmg_is_entry_point_batch": (i32, [vp, u64, vp, vp]),
             "dmg_search_batch": (i32, [vp, i32, u32, u32, u64, vp, vp, vp, vp, u64, pu64]),
+            "dmg_lookup_batch": (i32, [vp, i32, u32, u32, u64, vp, vp, vp]),
             "dmg_query_batch": (i32, [vp, u64, vp, vp, vp, vp, vp, u64, pu64]),
             "dmg_graph_set_methods": (i32, [vp, vp, vp, vp]),
             "dmg_last_call_stats": (i32, [vp, C.POINTER(CallStats)]),
@@ -370,6 +372,18 @@ class Graph:
         out = np.zeros(max(1, ids.size), np.uint8)
         _check(self.L.dmg_is_entry_point_batch(self.h, ids.size, _ptr(ids), out.ctypes.data))
         return out[:ids.size]
+
+    def lookup_batch(self, kind, texts, v_lo=0, v_hi=None):
+        """texts: list of bytes. Returns uint32 ids, 0xFFFFFFFF = not found."""
+        n = len(texts)
+        t_off = np.zeros(n + 1, np.uint32)
+        if n:
+            np.cumsum([len(t) for t in texts], out=t_off[1:])
+        tb = np.frombuffer(b"".join(texts) + b"\0", dtype=np.uint8).copy()
+        out = np.zeros(max(n, 1), np.uint32)
+        _check(self.L.dmg_lookup_batch(self.h, kind, v_lo, self.V if v_hi is None else v_hi, n, t_off.ctypes.data,
+                                       tb.ctypes.data, out.ctypes.data))
+        return out[:n]
 
     # -- Q1 ------------------------------------------------------------------------------------
     def set_methods(self, methods_per_vertex):

@@ -256,6 +256,19 @@ int32_t dmg_search_batch(dmg_graph* g, int32_t kind, uint32_t v_lo, uint32_t v_h
                          const uint32_t* q_off, const uint8_t* q_bytes, uint64_t* out_off,
                          uint32_t* out_ids, uint64_t cap, uint64_t* needed);
 
+/* ---- name -> id lookups on the device ---------------------------------
+ * DMG_LOOKUP_EXACT: out_ids[i] = the vertex whose identifier equals text i byte for byte
+ *   (nodes.containsKey / contains, PG:464; the per-frame class lookup that precedes
+ *   resolveNeighbors, CCS:1404-1438, without one host HashMap probe or SQL round trip per frame);
+ * DMG_LOOKUP_SIMPLE_FIRST: text i is a LOWER-CASED simple name; out_ids[i] = the first vertex in
+ *   nodes order whose lower-cased simple name (text after the last '.') equals it (GQS:434-446).
+ * Only vertices in [v_lo, v_hi) are considered (one project of a multi-project handle: the same
+ * FQCN may exist in two projects).  0xFFFFFFFF = not found.                   */
+#define DMG_LOOKUP_EXACT 0
+#define DMG_LOOKUP_SIMPLE_FIRST 1
+int32_t dmg_lookup_batch(dmg_graph* g, int32_t kind, uint32_t v_lo, uint32_t v_hi, uint64_t n,
+                         const uint32_t* t_off, const uint8_t* t_bytes, uint32_t* out_ids);
+
 /* ---- Q1: graph_query execution (GQS:53-73, 111-150, 195-394) ---------------------------------
  * The DSL lexer (GraphQuery.parse, GQ:95-163) stays in the host; what reaches the engine is a
  * batch of already-tokenised operations.  Row i of the output answers ops[i]:

@@ -598,3 +598,39 @@ def test_dense_rows_equal_packed_rows(engine):
             assert np.array_equal(loc + win[q, 0], ids[a:b]) and np.array_equal(r[loc], hop[a:b])
             assert win[q, 1] in (0, 900) and not r[900:].any()
     g.release()
+
+
+# ---- name -> id lookups ------------------------------------------------------
+def test_lookup_batch_exact_and_simple(engine):
+    rng = np.random.default_rng(3)
+    parts = [synth.project_names(p, 1500, rng) for p in range(3)]
+    parts[1][10] = parts[0][7]                        # the same FQCN in two projects
+    parts[2][5] = "co.fanki.X.Dup"
+    parts[2][900] = "other.pkg.dup"                   # same lower-cased simple name, later id
+    names = [n for p in parts for n in p]
+    off, arena = synth.pack_names(names)
+    g = dmgraph.Graph(engine, len(names), [], [], [], part_off=[0, 1500, 3000, 4500], name_off=off, name_bytes=arena)
+    ids = {}
+    for i, n in enumerate(names):
+        ids.setdefault(n, i)
+    q = [names[i] for i in rng.integers(0, 4500, 300)] + ["nope.Missing", "", names[7].upper(), names[7]]
+    got = g.lookup_batch(dmgraph.LOOKUP_EXACT, [x.encode() for x in q])
+    want = [ids.get(x, 0xFFFFFFFF) if x in ids and names[ids[x]] == x else 0xFFFFFFFF for x in q]
+    assert got.tolist() == want
+    # project-scoped: the duplicate FQCN resolves inside the asked project
+    assert g.lookup_batch(dmgraph.LOOKUP_EXACT, [names[7].encode()], 1500, 3000).tolist() == [1510]
+    assert g.lookup_batch(dmgraph.LOOKUP_EXACT, [names[7].encode()], 3000, 4500).tolist() == [0xFFFFFFFF]
+    # simple names: first id in nodes order, case-insensitive through the host's lowering
+    low = [n.lower() for n in names]
+    simple = lambda s: s[s.rfind(".") + 1:]
+    qs = [simple(low[i]) for i in rng.integers(0, 4500, 200)] + ["dup", "zzz", ""]
+    got = g.lookup_batch(dmgraph.LOOKUP_SIMPLE_FIRST, [x.encode() for x in qs])
+    want = [next((i for i, n in enumerate(low) if simple(n) == x), 0xFFFFFFFF) for x in qs]
+    assert got.tolist() == want
+    assert g.lookup_batch(dmgraph.LOOKUP_SIMPLE_FIRST, [b"dup"], 3006, 4500).tolist() == [3900]
+    # and through dmg_search_batch(SIMPLE_EQ_FIRST), which now probes the same table
+    lowb = np.frombuffer(bytes(arena).lower(), dtype=np.uint8).copy()
+    o, i1 = g.search_batch(dmgraph.SEARCH_SIMPLE_EQ_FIRST, [x.encode() for x in qs], 100, 4400)
+    wo, wi = ora.search_batch(off, lowb, [x.encode() for x in qs], 1, 100, 4400)
+    assert np.array_equal(o, wo) and np.array_equal(i1, wi)
+    g.release()
