@@ -41,6 +41,10 @@ struct KhopArgs {
   uint8_t* stage;
   uint32_t* counts;
   uint32_t* qwin;
+  // khop_global only: rows are written where an atomic cursor puts them (tmp_*), then gathered
+  unsigned long long* tmp_start;
+  uint32_t* tmp_ids;
+  uint8_t* tmp_hop;
 };
 
 __device__ __forceinline__ void find_window(const KhopArgs& a, uint32_t qb, uint32_t qe, uint32_t* lo, uint32_t* hi) {
@@ -431,8 +435,8 @@ __global__ void __launch_bounds__(EM_THREADS, 6) khop_emit_kernel(const uint8_t*
 // sparsely (by walking the queue), so the cost of a query follows its result, not V.
 // ---------------------------------------------------------------------------------------------
 constexpr int KG_THREADS = 256;
-constexpr int KG_SORT_CAP = 16384;   // rows up to this length are ordered in shared memory
-constexpr int KG_BUCKETS = 2048;
+constexpr int KG_SORT_CAP = 4096;    // rows up to this length are ordered in shared memory
+constexpr int KG_BUCKETS = 1024;
 constexpr uint32_t KG_BUCKET_MAX = 48;   // longest bucket a single thread insertion-sorts
 
 __global__ void __launch_bounds__(KG_THREADS) khop_global_kernel(const KhopArgs a, uint32_t* sc_seen, uint8_t* sc_hop,
@@ -552,16 +556,13 @@ __global__ void __launch_bounds__(KG_THREADS) khop_global_kernel(const KhopArgs 
       __syncthreads();
     }
     const uint32_t total = tail - ns;
-    if (warp == 0) {
-      const unsigned long long excl = lookback_exclusive(a.status, q, total);
-      if (lane == 0) {
-        s_base = excl;
-        a.out_off[q] = excl;
-        if (q == a.nq - 1) {
-          a.out_off[a.nq] = excl + total;
-          a.ctr->total = excl + total;
-        }
-      }
+    if (tid == 0) {
+      // rows land wherever the cursor is (no waiting for earlier queries); khop_gather_kernel puts
+      // them in query order once scan_counts_kernel has turned the sizes into out_off
+      const unsigned long long at = atomicAdd(&a.ctr->aux[3], (unsigned long long)total);
+      s_base = at;
+      a.tmp_start[q] = at;
+      a.counts[q] = total;
     }
     if (tid == 0) s_flag = 0;
     for (uint32_t i = tid; i <= KG_BUCKETS; i += THREADS) s_hist[i] = 0;
@@ -624,8 +625,8 @@ __global__ void __launch_bounds__(KG_THREADS) khop_global_kernel(const KhopArgs 
         for (uint32_t i = tid; i < total; i += THREADS) {
           const unsigned long long pos = base + i;
           if (pos < a.cap) {
-            a.out_ids[pos] = lo + s_ids[i];
-            a.out_hop[pos] = s_hopv[i];
+            a.tmp_ids[pos] = lo + s_ids[i];
+            a.tmp_hop[pos] = s_hopv[i];
           }
         }
       } else {
@@ -670,8 +671,8 @@ __global__ void __launch_bounds__(KG_THREADS) khop_global_kernel(const KhopArgs 
           for (uint32_t bb = keep[j]; bb; bb &= bb - 1) {
             const uint32_t v = w * 32 + (__ffs(bb) - 1);
             if (pos < a.cap) {
-              a.out_ids[pos] = lo + v;
-              a.out_hop[pos] = __ldcg(&hopg[v]);
+              a.tmp_ids[pos] = lo + v;
+              a.tmp_hop[pos] = __ldcg(&hopg[v]);
             }
             ++pos;
           }
@@ -691,6 +692,26 @@ __global__ void __launch_bounds__(KG_THREADS) khop_global_kernel(const KhopArgs 
     atomicAdd(&a.ctr->edges, te);
     atomicAdd(&a.ctr->aux[0], te);   // this kernel is top-down only: read == traversed
     atomicAdd(&a.ctr->rows, rows);
+  }
+}
+
+// rows of khop_global_kernel from cursor order into query order (one warp per query)
+__global__ void __launch_bounds__(256) khop_gather_kernel(unsigned long long nq,
+                                                          const unsigned long long* __restrict__ tmp_start,
+                                                          const unsigned long long* __restrict__ out_off,
+                                                          const uint32_t* __restrict__ tmp_ids,
+                                                          const uint8_t* __restrict__ tmp_hop, uint32_t* out_ids,
+                                                          uint8_t* out_hop, unsigned long long cap) {
+  const int lane = threadIdx.x & 31;
+  const unsigned long long warp = (blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x) >> 5;
+  const unsigned long long nwarps = ((unsigned long long)gridDim.x * blockDim.x) >> 5;
+  for (unsigned long long q = warp; q < nq; q += nwarps) {
+    const unsigned long long from = tmp_start[q], to = out_off[q], n = out_off[q + 1] - to;
+    for (unsigned long long i = lane; i < n; i += 32)
+      if (to + i < cap && from + i < cap) {
+        out_ids[to + i] = tmp_ids[from + i];
+        out_hop[to + i] = tmp_hop[from + i];
+      }
   }
 }
 
@@ -918,9 +939,33 @@ static int32_t run_khop(CallCtx* c, dmg_graph* g, int mode, int k, int exclude, 
     uint8_t* sc_hop = reinterpret_cast<uint8_t*>(sc_seen + grid * seen_words);
     uint32_t* sc_queue = reinterpret_cast<uint32_t*>(sc_hop + grid * hop_bytes);
     DMG_CUDA(cudaMemsetAsync(sc_seen, 0, grid * seen_words * 4, c->stream));
-    LaunchScope ls(c, K_KHOP_GLOBAL);
-    khop_global_kernel<<<(unsigned)grid, KG_THREADS, kg_smem, c->stream>>>(a, sc_seen, sc_hop, sc_queue, seen_words,
-                                                                     hop_bytes, qcap);
+    // rows are first written in cursor order into temporaries of the caller's capacity
+    DMG_TRY(c->tmp0.reserve(nq * 4));
+    DMG_TRY(c->tmp1.reserve(nq * 8));
+    DMG_TRY(c->tmp2.reserve(std::max<uint64_t>(cap, 1) * 4));
+    DMG_TRY(c->tmp3.reserve(std::max<uint64_t>(cap, 1)));
+    a.counts = c->tmp0.as<uint32_t>();
+    a.tmp_start = c->tmp1.as<unsigned long long>();
+    a.tmp_ids = c->tmp2.as<uint32_t>();
+    a.tmp_hop = c->tmp3.as<uint8_t>();
+    {
+      LaunchScope ls(c, K_KHOP_GLOBAL);
+      khop_global_kernel<<<(unsigned)grid, KG_THREADS, kg_smem, c->stream>>>(a, sc_seen, sc_hop, sc_queue, seen_words,
+                                                                           hop_bytes, qcap);
+    }
+    const uint64_t scan_tiles = (nq + SC_THREADS * SC_ITEMS - 1) / (SC_THREADS * SC_ITEMS);
+    DMG_TRY(c->status.reserve(scan_tiles * sizeof(uint64_t)));
+    DMG_CUDA(cudaMemsetAsync(c->status.p, 0, scan_tiles * sizeof(uint64_t), c->stream));
+    {
+      LaunchScope ls(c, K_SCAN_COUNTS);
+      scan_counts_kernel<<<(unsigned)std::min<uint64_t>(scan_tiles, (uint64_t)e->sm_count * 4), SC_THREADS, 0, c->stream>>>(
+          a.counts, nq, a.out_off, &c->d_counters->aux[2], c->status.as<uint64_t>(), c->d_counters);
+    }
+    if (cap) {
+      LaunchScope ls(c, K_KHOP_EMIT);
+      khop_gather_kernel<<<(unsigned)std::min<uint64_t>((nq + 7) / 8, (uint64_t)e->sm_count * 16), 256, 0, c->stream>>>(
+          nq, a.tmp_start, a.out_off, a.tmp_ids, a.tmp_hop, a.out_ids, a.out_hop, cap);
+    }
   }
   DMG_CUDA(cudaGetLastError());
   DMG_TRY(fetch_counters(c));
