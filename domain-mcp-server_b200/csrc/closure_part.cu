@@ -10,6 +10,7 @@
 // the vertex's reverse row and writes only its own slice of the next bitmap; the exchange
 // gathers the slices.
 #include <algorithm>
+#include <cstddef>
 
 #include "common.cuh"
 
@@ -309,6 +310,80 @@ int32_t dmg_closure_merge_dev(dmg_graph* g, uint32_t v_lo, uint32_t v_hi, uint32
   DMG_CUDA(cudaMemcpyAsync(c->h_counters, c->d_counters, sizeof(DevCounters), cudaMemcpyDeviceToHost, c->stream));
   DMG_TRY(c->finish());
   *n_new = c->h_counters->total;
+  return DMG_OK;
+}
+
+
+// ---- stream-ordered forms: no context, no synchronisation, no host readback -----------------------
+// The host (dmgraph/dist.py) enqueues expand -> ncclAllGather -> merge on ONE stream it owns and
+// reads *d_n_new once per level; d_edges (may be NULL) accumulates the adjacency entries read.
+int32_t dmg_closure_push_async(dmg_graph* g, int32_t dir, uint32_t v_lo, uint32_t v_hi, const uint32_t* d_frontier_bits,
+                               uint32_t* d_contrib_bits, unsigned long long* d_edges, void* cuda_stream) {
+  DMG_TRY(part_args(g, dir, v_lo, v_hi, "dmg_closure_push_async"));
+  if (!d_frontier_bits || !d_contrib_bits || !d_edges) {
+    set_error("dmg_closure_push_async: NULL argument");
+    return DMG_EINVAL;
+  }
+  cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
+  const uint32_t words = (g->info.n_vertices + 31) / 32;
+  DMG_CUDA(cudaMemsetAsync(d_contrib_bits, 0, (size_t)words * 4, st));
+  const uint32_t w_lo = v_lo / 32, w_hi = (v_hi + 31) / 32;
+  if (w_hi > w_lo) {
+    const uint32_t* ptr = dir == DMG_OUT ? g->d_out_ptr : g->d_in_ptr;
+    const uint32_t* idx = dir == DMG_OUT ? g->d_out_idx : g->d_in_idx;
+    const unsigned grid = (unsigned)std::min<uint64_t>(((uint64_t)(w_hi - w_lo) * 32 + CP_THREADS - 1) / CP_THREADS,
+                                                       (uint64_t)g->eng->sm_count * 8);
+    // DevCounters::edges sits 16 bytes into the struct: hand the kernel a base that makes it d_edges
+    DevCounters* fake = reinterpret_cast<DevCounters*>(reinterpret_cast<char*>(d_edges) - offsetof(DevCounters, edges));
+    part_push_kernel<<<grid, CP_THREADS, 0, st>>>(ptr, idx, w_lo, w_hi, v_lo, v_hi, d_frontier_bits, d_contrib_bits,
+                                                  fake);
+  }
+  DMG_CUDA(cudaGetLastError());
+  return DMG_OK;
+}
+
+int32_t dmg_closure_pull_async(dmg_graph* g, int32_t dir, uint32_t v_lo, uint32_t v_hi, const uint32_t* d_frontier_bits,
+                               const uint32_t* d_visited_bits, uint32_t* d_next_slice, unsigned long long* d_edges,
+                               void* cuda_stream) {
+  DMG_TRY(part_args(g, dir, v_lo, v_hi, "dmg_closure_pull_async"));
+  if (!d_frontier_bits || !d_visited_bits || !d_next_slice || !d_edges) {
+    set_error("dmg_closure_pull_async: NULL argument");
+    return DMG_EINVAL;
+  }
+  cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
+  const uint32_t w_lo = v_lo / 32, w_hi = (v_hi + 31) / 32;
+  if (w_hi > w_lo) {
+    const uint32_t* rptr = dir == DMG_OUT ? g->d_in_ptr : g->d_out_ptr;
+    const uint32_t* ridx = dir == DMG_OUT ? g->d_in_idx : g->d_out_idx;
+    const unsigned grid = (unsigned)std::min<uint64_t>(((uint64_t)(w_hi - w_lo) * 32 + CP_THREADS - 1) / CP_THREADS,
+                                                       (uint64_t)g->eng->sm_count * 8);
+    DevCounters* fake = reinterpret_cast<DevCounters*>(reinterpret_cast<char*>(d_edges) - offsetof(DevCounters, edges));
+    part_pull_kernel<<<grid, CP_THREADS, 0, st>>>(rptr, ridx, w_lo, w_hi, v_lo, v_hi, d_frontier_bits, d_visited_bits,
+                                                  d_next_slice, fake);
+  }
+  DMG_CUDA(cudaGetLastError());
+  return DMG_OK;
+}
+
+int32_t dmg_closure_merge_async(dmg_graph* g, uint32_t v_lo, uint32_t v_hi, uint32_t lvl, const uint32_t* d_gathered,
+                                uint32_t n_gathered, uint32_t stride_words, uint32_t* d_visited_bits,
+                                uint32_t* d_next_bits, uint32_t* d_level_slice, unsigned long long* d_n_new,
+                                void* cuda_stream) {
+  DMG_TRY(part_args(g, DMG_OUT, v_lo, v_hi, "dmg_closure_merge_async"));
+  if (!d_gathered || !n_gathered || stride_words < (g->info.n_vertices + 31) / 32 || !d_visited_bits || !d_next_bits ||
+      !d_level_slice || !d_n_new) {
+    set_error("dmg_closure_merge_async: NULL argument");
+    return DMG_EINVAL;
+  }
+  cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
+  const uint32_t words = (g->info.n_vertices + 31) / 32;
+  DMG_CUDA(cudaMemsetAsync(d_n_new, 0, 8, st));
+  if (words) {
+    DevCounters* fake = reinterpret_cast<DevCounters*>(reinterpret_cast<char*>(d_n_new) - offsetof(DevCounters, total));
+    part_merge_kernel<<<(words + CP_THREADS - 1) / CP_THREADS, CP_THREADS, 0, st>>>(
+        d_gathered, n_gathered, stride_words, words, d_visited_bits, d_next_bits, v_lo, v_hi, lvl, d_level_slice, fake);
+  }
+  DMG_CUDA(cudaGetLastError());
   return DMG_OK;
 }
 

@@ -91,6 +91,9 @@ def lib():
             "dmg_analysis_order": (i32, [vp, vp]),
             "dmg_closure_push_dev": (i32, [vp, i32, u32, u32, vp, vp, pu64]),
             "dmg_closure_pull_dev": (i32, [vp, i32, u32, u32, vp, vp, vp, pu64]),
+            "dmg_closure_push_async": (i32, [vp, i32, u32, u32, vp, vp, vp, vp]),
+            "dmg_closure_pull_async": (i32, [vp, i32, u32, u32, vp, vp, vp, vp, vp]),
+            "dmg_closure_merge_async": (i32, [vp, u32, u32, u32, vp, u32, u32, vp, vp, vp, vp, vp]),
             "dmg_closure_merge_dev": (i32, [vp, u32, u32, u32, vp, u32, u32, vp, vp, vp, pu64]),
             "dmg_entry_points": (i32, [vp, vp, u32, C.POINTER(u32)]),
             "dmg_is_entry_point_batch": (i32, [vp, u64, vp, vp]),

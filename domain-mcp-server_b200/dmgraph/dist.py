@@ -57,6 +57,51 @@ class GpuStepper:
                                         visited.data_ptr(), nxt.data_ptr(), level_slice.data_ptr())
 
 
+class GpuStreamStepper:
+    """The same primitives enqueued on torch's current CUDA stream (the stream NCCL runs on): no
+    synchronisation inside a level; PartitionedClosure reads |next| once per level."""
+
+    asynchronous = True
+
+    def __init__(self, graph, v_lo, v_hi):
+        import ctypes as C
+        import torch
+        self.g, self.v_lo, self.v_hi, self.C, self.torch = graph, v_lo, v_hi, C, torch
+        self.edges = torch.zeros(1, dtype=torch.int64, device="cuda")
+        self.n_new = torch.zeros(1, dtype=torch.int64, device="cuda")
+
+    def _stream(self):
+        return self.C.c_void_p(self.torch.cuda.current_stream().cuda_stream)
+
+    def _p(self, t):
+        return self.C.c_void_p(t.data_ptr())
+
+    def push(self, direction, frontier, contrib):
+        from dmgraph import _check
+        _check(self.g.L.dmg_closure_push_async(self.g.h, direction, self.v_lo, self.v_hi, self._p(frontier),
+                                               self._p(contrib), self._p(self.edges), self._stream()))
+        return 0
+
+    def pull(self, direction, frontier, visited, next_slice):
+        from dmgraph import _check
+        _check(self.g.L.dmg_closure_pull_async(self.g.h, direction, self.v_lo, self.v_hi, self._p(frontier),
+                                               self._p(visited), self._p(next_slice), self._p(self.edges),
+                                               self._stream()))
+        return 0
+
+    def merge(self, lvl, gathered, n_gathered, stride, visited, nxt, level_slice):
+        from dmgraph import _check
+        _check(self.g.L.dmg_closure_merge_async(self.g.h, self.v_lo, self.v_hi, lvl, self._p(gathered), n_gathered,
+                                                stride, self._p(visited), self._p(nxt), self._p(level_slice),
+                                                self._p(self.n_new), self._stream()))
+        return int(self.n_new.item())          # the one synchronisation of the level
+
+    def take_edges(self):
+        e = int(self.edges.item())
+        self.edges.zero_()
+        return e
+
+
 class PartitionedClosure:
     """BFS levels from a source set over `direction`, the graph split by vertex range over ranks."""
 
@@ -114,4 +159,6 @@ class PartitionedClosure:
             reached += n_front
             lvl += 1
         self.stats["levels"] = lvl - 1
+        if hasattr(self.stepper, "take_edges"):
+            self.stats["edges"] += self.stepper.take_edges()
         return self.level[: self.v_hi - self.v_lo], reached

@@ -242,6 +242,21 @@ int32_t dmg_closure_merge_dev(dmg_graph* g, uint32_t v_lo, uint32_t v_hi, uint32
                               uint32_t* d_visited_bits, uint32_t* d_next_bits, uint32_t* d_level_slice,
                               uint64_t* n_new);
 
+/* Stream-ordered forms of the three level primitives: work is only ENQUEUED on `cuda_stream` (a
+ * cudaStream_t the host owns, e.g. the stream its NCCL calls run on); nothing is synchronised or
+ * copied to the host.  *d_edges (device, 8 bytes) accumulates adjacency entries read; *d_n_new
+ * (device, 8 bytes) receives |next| -- the host reads it once per level to test for termination.   */
+int32_t dmg_closure_push_async(dmg_graph* g, int32_t dir, uint32_t v_lo, uint32_t v_hi,
+                               const uint32_t* d_frontier_bits, uint32_t* d_contrib_bits,
+                               unsigned long long* d_edges, void* cuda_stream);
+int32_t dmg_closure_pull_async(dmg_graph* g, int32_t dir, uint32_t v_lo, uint32_t v_hi,
+                               const uint32_t* d_frontier_bits, const uint32_t* d_visited_bits,
+                               uint32_t* d_next_slice, unsigned long long* d_edges, void* cuda_stream);
+int32_t dmg_closure_merge_async(dmg_graph* g, uint32_t v_lo, uint32_t v_hi, uint32_t lvl,
+                                const uint32_t* d_gathered, uint32_t n_gathered, uint32_t stride_words,
+                                uint32_t* d_visited_bits, uint32_t* d_next_bits, uint32_t* d_level_slice,
+                                unsigned long long* d_n_new, void* cuda_stream);
+
 /* entryPoints() (PG:345-347), insertion order; isEntryPoint (PG:336-338) as a byte per id. */
 int32_t dmg_entry_points(dmg_graph* g, uint32_t* out_ids, uint32_t cap, uint32_t* needed);
 int32_t dmg_is_entry_point_batch(dmg_graph* g, uint64_t n, const uint32_t* ids, uint8_t* out_flags);

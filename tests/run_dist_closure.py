@@ -25,6 +25,7 @@ def main():
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--check", default="oracle", choices=["oracle", "single", "none"],
                     help="oracle: CSR oracle on rank 0; single: dmg_closure on the whole graph on rank 0's GPU")
+    ap.add_argument("--sync-stepper", action="store_true", help="use the synchronous *_dev primitives")
     ap.add_argument("--fast-gen", action="store_true", help="with-replacement targets (config 5 sizes)")
     args = ap.parse_args()
     import torch
@@ -47,7 +48,8 @@ def main():
     t_up = time.perf_counter()
     g = dmgraph.Graph(eng, V, s_own, d_own, [])
     t_up = time.perf_counter() - t_up
-    pc = ddist.PartitionedClosure(V, rank, world, ddist.GpuStepper(g, v_lo, v_hi), "cuda", dist if world > 1 else None)
+    stepper = (ddist.GpuStepper if args.sync_stepper else ddist.GpuStreamStepper)(g, v_lo, v_hi)
+    pc = ddist.PartitionedClosure(V, rank, world, stepper, "cuda", dist if world > 1 else None)
     times = []
     for it in range(1 + args.steps):
         pc.stats = {k: 0 for k in pc.stats}
@@ -107,7 +109,7 @@ def main():
                           "seconds": float(tmax.item()), "edges_read_all_ranks": float(edges.item()),
                           "gteps_read": float(edges.item()) / float(tmax.item()) / 1e9,
                           "exchanged_bytes_per_rank": pc.stats["exchanged_bytes"], "generate_s": t_gen,
-                          "upload_s_rank0": t_up, "checked_against": args.check, "matches": ok,
+                          "upload_s_rank0": t_up, "stepper": "sync" if args.sync_stepper else "stream-ordered", "checked_against": args.check, "matches": ok,
                           "single_gpu": single}), flush=True)
         assert ok is not False
     if world > 1:

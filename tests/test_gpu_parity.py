@@ -442,6 +442,10 @@ def test_partitioned_closure_two_ranks_lockstep(engine, direction):
     pc1 = ddist.PartitionedClosure(n, 0, 1, ddist.GpuStepper(g1, 0, n), "cuda", None)
     lv1, r1 = pc1.run(sources, direction)
     assert r1 == wreached and np.array_equal(lv1.cpu().numpy().view(np.uint32), want)
+    # the stream-ordered primitives (what the multi-GPU runs use)
+    pc2 = ddist.PartitionedClosure(n, 0, 1, ddist.GpuStreamStepper(g1, 0, n), "cuda", None)
+    lv2, r2 = pc2.run(sources, direction)
+    assert r2 == wreached and np.array_equal(lv2.cpu().numpy().view(np.uint32), want) and pc2.stats["edges"] > 0
     for g, _pc in ranks:
         g.release()
     g1.release()
