@@ -193,6 +193,7 @@ struct dmg_graph {
   uint32_t* d_mname_off = nullptr;   // [M+1]
   uint8_t* d_mname_lower = nullptr;
   uint32_t n_methods = 0;
+  std::vector<uint32_t> h_endpoint_methods;   // catalog indices of HTTP endpoint methods, ascending
   std::vector<uint32_t> h_part_off, h_entry;
 };
 

@@ -169,6 +169,133 @@ static int32_t upload(T** d, const T* h, size_t n, uint64_t* bytes) {
   return DMG_OK;
 }
 
+// Second half of every upload path (edge list or snapshot): derives the resolve rows, the entry
+// bitmap and the name tables from the CSR and copies everything to the device.  Takes ownership
+// of `g` (freed on failure).
+static int32_t finish_upload(dmg_engine* e, dmg_graph* g, uint32_t V, const std::vector<uint32_t>& out_ptr,
+                             const std::vector<uint32_t>& out_idx, const std::vector<uint32_t>& in_ptr,
+                             const std::vector<uint32_t>& in_idx, const std::vector<uint32_t>& part,
+                             const uint64_t* name_off, const uint8_t* name_bytes, const uint8_t* lower_bytes,
+                             uint64_t dropped, uint64_t dups, dmg_graph** out) {
+  struct Desc {
+    const uint64_t* name_off;
+    const uint8_t* name_bytes;
+    const uint8_t* lower_bytes;
+  } dd{name_off, name_bytes, lower_bytes};
+  const Desc* d = &dd;
+  g->h_part_off = part;
+  uint32_t max_part = 0;
+  for (size_t i = 1; i < part.size(); ++i) max_part = std::max(max_part, part[i] - part[i - 1]);
+
+  // ---- upload ---------------------------------------------------------------------------------
+  cudaSetDevice(e->device);
+  uint64_t bytes = 0;
+  int32_t st = DMG_OK;
+  std::vector<uint32_t> ebits((V + 31) / 32 + 1, 0);
+  for (uint32_t v : g->h_entry) ebits[v >> 5] |= 1u << (v & 31);
+  // resolve() rows for mode BOTH: the out row followed by the in row of the same vertex, one
+  // contiguous range per vertex (no de-duplication: a 2-cycle appears twice, the visited
+  // set removes it, PG:366-375)
+  std::vector<uint32_t> und_ptr(V + 1, 0), und_idx;
+  try {
+    und_idx.resize(2 * out_idx.size());
+    for (uint32_t v = 0; v < V; ++v) {
+      uint32_t w = und_ptr[v];
+      for (uint32_t j = out_ptr[v]; j < out_ptr[v + 1]; ++j) und_idx[w++] = out_idx[j];
+      for (uint32_t j = in_ptr[v]; j < in_ptr[v + 1]; ++j) und_idx[w++] = in_idx[j];
+      und_ptr[v + 1] = w;
+    }
+  } catch (const std::bad_alloc&) {
+    delete g;
+    set_error("dmg_graph_create: host out of memory");
+    return DMG_ENOMEM;
+  }
+  if ((st = upload(&g->d_und_ptr, und_ptr.data(), und_ptr.size(), &bytes)) != DMG_OK ||
+      (st = upload(&g->d_und_idx, und_idx.data(), und_idx.size(), &bytes)) != DMG_OK ||
+      (st = upload(&g->d_out_ptr, out_ptr.data(), out_ptr.size(), &bytes)) != DMG_OK ||
+      (st = upload(&g->d_out_idx, out_idx.data(), out_idx.size(), &bytes)) != DMG_OK ||
+      (st = upload(&g->d_in_ptr, in_ptr.data(), in_ptr.size(), &bytes)) != DMG_OK ||
+      (st = upload(&g->d_in_idx, in_idx.data(), in_idx.size(), &bytes)) != DMG_OK ||
+      (st = upload(&g->d_part_off, part.data(), part.size(), &bytes)) != DMG_OK ||
+      (st = upload(&g->d_entry, g->h_entry.data(), g->h_entry.size(), &bytes)) != DMG_OK ||
+      (st = upload(&g->d_entry_bits, ebits.data(), ebits.size(), &bytes)) != DMG_OK) {
+    free_graph(g);
+    return st;
+  }
+  uint64_t nbytes = 0;
+  if (d->name_off) {
+    nbytes = d->name_off[V];
+    std::vector<uint8_t> low(nbytes + 32, 0);   // zero pad so vector loads may overrun
+    const uint8_t* srcb = d->lower_bytes ? d->lower_bytes : d->name_bytes;
+    if (nbytes) memcpy(low.data(), srcb, nbytes);
+    if (!d->lower_bytes)
+      for (uint64_t i = 0; i < nbytes; ++i)
+        if (low[i] >= 'A' && low[i] <= 'Z') low[i] += 32;   // ASCII fold only (SURVEY 7.3-2)
+    // name -> id tables (SURVEY.md 8f rank 1): exact identifier (nodes.containsKey, case
+    // sensitive) and lower-cased simple name (GQS:434-446); linear probing, load <= 0.5
+    uint32_t size = 16;
+    while (size < 2ull * V + 1) size <<= 1;
+    std::vector<uint32_t> full_tbl(size, 0xFFFFFFFFu), simple_tbl(size, 0xFFFFFFFFu);
+    std::vector<uint8_t> orig(nbytes + 32, 0);
+    if (nbytes) memcpy(orig.data(), d->name_bytes, nbytes);
+    for (uint32_t v = 0; v < V; ++v) {
+      const uint64_t b = d->name_off[v], e2 = d->name_off[v + 1];
+      uint32_t h = name_hash(orig.data() + b, (uint32_t)(e2 - b)) & (size - 1);
+      while (full_tbl[h] != 0xFFFFFFFFu) h = (h + 1) & (size - 1);
+      full_tbl[h] = v;
+      uint64_t sb = b;
+      for (uint64_t i = e2; i > b; --i)
+        if (low[i - 1] == '.') {   // extractSimpleName: after the last '.' (GQS:458-461)
+          sb = i;
+          break;
+        }
+      h = name_hash(low.data() + sb, (uint32_t)(e2 - sb)) & (size - 1);
+      while (simple_tbl[h] != 0xFFFFFFFFu) h = (h + 1) & (size - 1);
+      simple_tbl[h] = v;
+    }
+    g->tbl_mask = size - 1;
+    if ((st = upload(&g->d_name_off, d->name_off, (size_t)V + 1, &bytes)) != DMG_OK ||
+        (st = upload(&g->d_lower, low.data(), low.size(), &bytes)) != DMG_OK ||
+        (st = upload(&g->d_names, orig.data(), orig.size(), &bytes)) != DMG_OK ||
+        (st = upload(&g->d_full_tbl, full_tbl.data(), full_tbl.size(), &bytes)) != DMG_OK ||
+        (st = upload(&g->d_simple_tbl, simple_tbl.data(), simple_tbl.size(), &bytes)) != DMG_OK) {
+      free_graph(g);
+      return st;
+    }
+  }
+  g->info.n_vertices = V;
+  g->info.n_entry = (uint32_t)g->h_entry.size();
+  g->info.n_parts = (uint32_t)part.size() - 1;
+  g->info.max_part_vertices = max_part;
+  g->info.n_edges = out_idx.size();
+  g->info.dropped_edges = dropped;
+  g->info.duplicate_edges = dups;
+  g->info.name_bytes = nbytes;
+  g->info.device_bytes = bytes;
+  *out = g;
+  return DMG_OK;
+}
+
+// helpers of the binary CSR snapshot
+namespace {
+struct SnapHeader {
+  char magic[8];
+  uint32_t V, n_entry, n_parts, has_names;
+  uint64_t E, name_bytes, dropped, dups;
+};
+template <class T>
+bool put_dev(FILE* f, const T* d, size_t n) {
+  std::vector<T> h(n);
+  if (n && cudaMemcpy(h.data(), d, n * sizeof(T), cudaMemcpyDeviceToHost) != cudaSuccess) return false;
+  return !n || fwrite(h.data(), sizeof(T), n, f) == n;
+}
+template <class T>
+bool get_vec(FILE* f, std::vector<T>& v, size_t n) {
+  v.resize(n);
+  return !n || fread(v.data(), sizeof(T), n, f) == n;
+}
+}  // namespace
+
 // =============================================================================================
 // C ABI
 // =============================================================================================
@@ -344,97 +471,87 @@ int32_t dmg_graph_create(dmg_engine* e, const dmg_graph_desc* d, dmg_graph** out
     set_error("dmg_graph_create: host out of memory");
     return DMG_ENOMEM;
   }
-  g->h_part_off = part;
-  uint32_t max_part = 0;
-  for (size_t i = 1; i < part.size(); ++i) max_part = std::max(max_part, part[i] - part[i - 1]);
+  return finish_upload(e, g, V, out_ptr, out_idx, in_ptr, in_idx, part, d->name_off, d->name_bytes, d->lower_bytes,
+                       dropped, dups, out);
+}
 
-  // ---- upload ---------------------------------------------------------------------------------
-  cudaSetDevice(e->device);
-  uint64_t bytes = 0;
-  int32_t st = DMG_OK;
-  std::vector<uint32_t> ebits((V + 31) / 32 + 1, 0);
-  for (uint32_t v : g->h_entry) ebits[v >> 5] |= 1u << (v & 31);
-  // resolve() rows for mode BOTH: the out row followed by the in row of the same vertex, one
-  // contiguous range per vertex (no de-duplication: a 2-cycle appears twice, the visited
-  // set removes it, PG:366-375)
-  std::vector<uint32_t> und_ptr(V + 1, 0), und_idx;
-  try {
-    und_idx.resize(2 * out_idx.size());
-    for (uint32_t v = 0; v < V; ++v) {
-      uint32_t w = und_ptr[v];
-      for (uint32_t j = out_ptr[v]; j < out_ptr[v + 1]; ++j) und_idx[w++] = out_idx[j];
-      for (uint32_t j = in_ptr[v]; j < in_ptr[v + 1]; ++j) und_idx[w++] = in_idx[j];
-      und_ptr[v + 1] = w;
-    }
-  } catch (const std::bad_alloc&) {
-    delete g;
-    set_error("dmg_graph_create: host out of memory");
-    return DMG_ENOMEM;
+// ---- binary CSR snapshot ------------------------------------------------
+int32_t dmg_graph_save(dmg_graph* g, const char* path) {
+  if (!g || !path) {
+    set_error("dmg_graph_save: NULL argument");
+    return DMG_EINVAL;
   }
-  if ((st = upload(&g->d_und_ptr, und_ptr.data(), und_ptr.size(), &bytes)) != DMG_OK ||
-      (st = upload(&g->d_und_idx, und_idx.data(), und_idx.size(), &bytes)) != DMG_OK ||
-      (st = upload(&g->d_out_ptr, out_ptr.data(), out_ptr.size(), &bytes)) != DMG_OK ||
-      (st = upload(&g->d_out_idx, out_idx.data(), out_idx.size(), &bytes)) != DMG_OK ||
-      (st = upload(&g->d_in_ptr, in_ptr.data(), in_ptr.size(), &bytes)) != DMG_OK ||
-      (st = upload(&g->d_in_idx, in_idx.data(), in_idx.size(), &bytes)) != DMG_OK ||
-      (st = upload(&g->d_part_off, part.data(), part.size(), &bytes)) != DMG_OK ||
-      (st = upload(&g->d_entry, g->h_entry.data(), g->h_entry.size(), &bytes)) != DMG_OK ||
-      (st = upload(&g->d_entry_bits, ebits.data(), ebits.size(), &bytes)) != DMG_OK) {
-    free_graph(g);
-    return st;
+  DMG_CUDA(cudaSetDevice(g->eng->device));
+  FILE* f = fopen(path, "wb");
+  if (!f) {
+    set_error("dmg_graph_save: cannot open %s", path);
+    return DMG_EINVAL;
   }
-  uint64_t nbytes = 0;
-  if (d->name_off) {
-    nbytes = d->name_off[V];
-    std::vector<uint8_t> low(nbytes + 32, 0);   // zero pad so vector loads may overrun
-    const uint8_t* srcb = d->lower_bytes ? d->lower_bytes : d->name_bytes;
-    if (nbytes) memcpy(low.data(), srcb, nbytes);
-    if (!d->lower_bytes)
-      for (uint64_t i = 0; i < nbytes; ++i)
-        if (low[i] >= 'A' && low[i] <= 'Z') low[i] += 32;   // ASCII fold only (SURVEY 7.3-2)
-    // name -> id tables (SURVEY.md 8f rank 1): exact identifier (nodes.containsKey, case
-    // sensitive) and lower-cased simple name (GQS:434-446); linear probing, load <= 0.5
-    uint32_t size = 16;
-    while (size < 2ull * V + 1) size <<= 1;
-    std::vector<uint32_t> full_tbl(size, 0xFFFFFFFFu), simple_tbl(size, 0xFFFFFFFFu);
-    std::vector<uint8_t> orig(nbytes + 32, 0);
-    if (nbytes) memcpy(orig.data(), d->name_bytes, nbytes);
-    for (uint32_t v = 0; v < V; ++v) {
-      const uint64_t b = d->name_off[v], e2 = d->name_off[v + 1];
-      uint32_t h = name_hash(orig.data() + b, (uint32_t)(e2 - b)) & (size - 1);
-      while (full_tbl[h] != 0xFFFFFFFFu) h = (h + 1) & (size - 1);
-      full_tbl[h] = v;
-      uint64_t sb = b;
-      for (uint64_t i = e2; i > b; --i)
-        if (low[i - 1] == '.') {   // extractSimpleName: after the last '.' (GQS:458-461)
-          sb = i;
-          break;
-        }
-      h = name_hash(low.data() + sb, (uint32_t)(e2 - sb)) & (size - 1);
-      while (simple_tbl[h] != 0xFFFFFFFFu) h = (h + 1) & (size - 1);
-      simple_tbl[h] = v;
-    }
-    g->tbl_mask = size - 1;
-    if ((st = upload(&g->d_name_off, d->name_off, (size_t)V + 1, &bytes)) != DMG_OK ||
-        (st = upload(&g->d_lower, low.data(), low.size(), &bytes)) != DMG_OK ||
-        (st = upload(&g->d_names, orig.data(), orig.size(), &bytes)) != DMG_OK ||
-        (st = upload(&g->d_full_tbl, full_tbl.data(), full_tbl.size(), &bytes)) != DMG_OK ||
-        (st = upload(&g->d_simple_tbl, simple_tbl.data(), simple_tbl.size(), &bytes)) != DMG_OK) {
-      free_graph(g);
-      return st;
-    }
+  SnapHeader h;
+  memcpy(h.magic, "DMGCSR1", 8);
+  h.V = g->info.n_vertices;
+  h.n_entry = g->info.n_entry;
+  h.n_parts = g->info.n_parts;
+  h.has_names = g->d_name_off != nullptr;
+  h.E = g->info.n_edges;
+  h.name_bytes = g->info.name_bytes;
+  h.dropped = g->info.dropped_edges;
+  h.dups = g->info.duplicate_edges;
+  bool ok = fwrite(&h, sizeof(h), 1, f) == 1 && put_dev(f, g->d_out_ptr, (size_t)h.V + 1) &&
+            put_dev(f, g->d_out_idx, h.E) && put_dev(f, g->d_in_ptr, (size_t)h.V + 1) && put_dev(f, g->d_in_idx, h.E) &&
+            fwrite(g->h_part_off.data(), 4, g->h_part_off.size(), f) == g->h_part_off.size() &&
+            (g->h_entry.empty() || fwrite(g->h_entry.data(), 4, g->h_entry.size(), f) == g->h_entry.size());
+  if (ok && h.has_names)
+    ok = put_dev(f, g->d_name_off, (size_t)h.V + 1) && put_dev(f, g->d_names, h.name_bytes) &&
+         put_dev(f, g->d_lower, h.name_bytes);
+  ok = (fclose(f) == 0) && ok;
+  if (!ok) {
+    set_error("dmg_graph_save: write to %s failed", path);
+    return DMG_EINVAL;
   }
-  g->info.n_vertices = V;
-  g->info.n_entry = (uint32_t)g->h_entry.size();
-  g->info.n_parts = (uint32_t)part.size() - 1;
-  g->info.max_part_vertices = max_part;
-  g->info.n_edges = out_idx.size();
-  g->info.dropped_edges = dropped;
-  g->info.duplicate_edges = dups;
-  g->info.name_bytes = nbytes;
-  g->info.device_bytes = bytes;
-  *out = g;
   return DMG_OK;
+}
+
+int32_t dmg_graph_load(dmg_engine* e, const char* path, dmg_graph** out) {
+  if (!e || !path || !out) {
+    set_error("dmg_graph_load: NULL argument");
+    return DMG_EINVAL;
+  }
+  *out = nullptr;
+  FILE* f = fopen(path, "rb");
+  if (!f) {
+    set_error("dmg_graph_load: cannot open %s", path);
+    return DMG_EINVAL;
+  }
+  SnapHeader h;
+  std::vector<uint32_t> out_ptr, out_idx, in_ptr, in_idx, part, entry;
+  std::vector<uint64_t> name_off;
+  std::vector<uint8_t> names, lower;
+  bool ok = fread(&h, sizeof(h), 1, f) == 1 && memcmp(h.magic, "DMGCSR1", 8) == 0 && h.E < 0x7FFFFFF0ull;
+  ok = ok && get_vec(f, out_ptr, (size_t)h.V + 1) && get_vec(f, out_idx, h.E) && get_vec(f, in_ptr, (size_t)h.V + 1) &&
+       get_vec(f, in_idx, h.E) && get_vec(f, part, (size_t)h.n_parts + 1) && get_vec(f, entry, h.n_entry);
+  if (ok && h.has_names)
+    ok = get_vec(f, name_off, (size_t)h.V + 1) && get_vec(f, names, h.name_bytes) && get_vec(f, lower, h.name_bytes);
+  fclose(f);
+  // the snapshot is trusted only as far as its shape: offsets must be monotone and in range
+  ok = ok && out_ptr[h.V] == h.E && in_ptr[h.V] == h.E && part.front() == 0 && part.back() == h.V;
+  for (uint32_t v = 0; ok && v < h.V; ++v) ok = out_ptr[v] <= out_ptr[v + 1] && in_ptr[v] <= in_ptr[v + 1];
+  for (uint64_t i = 0; ok && i < h.E; ++i) ok = out_idx[i] < h.V && in_idx[i] < h.V;
+  for (uint32_t i = 0; ok && i < h.n_entry; ++i) ok = entry[i] < h.V;
+  if (ok && h.has_names) {
+    ok = name_off[h.V] == h.name_bytes;
+    for (uint32_t v = 0; ok && v < h.V; ++v) ok = name_off[v] <= name_off[v + 1];
+  }
+  if (!ok) {
+    set_error("dmg_graph_load: %s is not a valid dmgraph snapshot", path);
+    return DMG_EINVAL;
+  }
+  dmg_graph* g = new (std::nothrow) dmg_graph();
+  if (!g) return DMG_ENOMEM;
+  g->eng = e;
+  g->h_entry = entry;
+  return finish_upload(e, g, h.V, out_ptr, out_idx, in_ptr, in_idx, part, h.has_names ? name_off.data() : nullptr,
+                       names.data(), h.has_names ? lower.data() : nullptr, h.dropped, h.dups, out);
 }
 
 void dmg_graph_retain(dmg_graph* g) {

@@ -78,6 +78,17 @@ int32_t dmg_graph_set_methods(dmg_graph* g, const uint32_t* method_off, const ui
   return DMG_OK;
 }
 
+int32_t dmg_graph_set_method_flags(dmg_graph* g, const uint8_t* flags) {
+  if (!g || !g->d_method_off || (g->n_methods && !flags)) {
+    set_error("dmg_graph_set_method_flags: needs dmg_graph_set_methods first and a flag per method");
+    return DMG_EINVAL;
+  }
+  g->h_endpoint_methods.clear();
+  for (uint32_t m = 0; m < g->n_methods; ++m)
+    if (flags[m] & 1u) g->h_endpoint_methods.push_back(m);   // MethodInfo.isHttpEndpoint(), PG:75-77
+  return DMG_OK;
+}
+
 int32_t dmg_query_batch(dmg_graph* g, uint64_t n_ops, const dmg_query_op* ops, const uint8_t* text_bytes,
                         uint64_t* out_off, uint32_t* out_ids, uint8_t* out_aux, uint64_t cap, uint64_t* needed) {
   if (!g || !out_off || !needed || (n_ops && !ops)) {
@@ -92,7 +103,7 @@ int32_t dmg_query_batch(dmg_graph* g, uint64_t n_ops, const dmg_query_op* ops, c
     std::vector<uint32_t> ids;
     std::vector<uint8_t> aux;
   };
-  std::vector<uint64_t> adj_out, adj_in, names, methods, entries;
+  std::vector<uint64_t> adj_out, adj_in, names, methods, entries, endpoints;
   struct KhopKey {
     uint32_t mode, k, excl;
     bool operator<(const KhopKey& o) const {
@@ -114,6 +125,7 @@ int32_t dmg_query_batch(dmg_graph* g, uint64_t n_ops, const dmg_query_op* ops, c
         khops.push_back({{op.mode, op.k, op.exclude_sources ? 1u : 0u}, i});
         break;
       case DMG_OP_ENTRYPOINTS: entries.push_back(i); break;
+      case DMG_OP_ENDPOINTS: endpoints.push_back(i); break;
       case DMG_OP_RESOLVE_NAME:
       case DMG_OP_METHOD:
         if (op.text_end < op.text_begin || (op.text_end > op.text_begin && !text_bytes)) {
@@ -264,6 +276,7 @@ int32_t dmg_query_batch(dmg_graph* g, uint64_t n_ops, const dmg_query_op* ops, c
     for (size_t j = 0; j < m; ++j) cnt[methods[j]] = method_idx[j] != 0xFFFFFFFFu;
   }
   for (uint64_t i : entries) cnt[i] = g->h_entry.size();
+  for (uint64_t i : endpoints) cnt[i] = g->h_endpoint_methods.size();
 
   // ---- lay the rows out in operation order ---------------------------------------------------
   uint64_t total = 0;
@@ -298,6 +311,7 @@ int32_t dmg_query_batch(dmg_graph* g, uint64_t n_ops, const dmg_query_op* ops, c
   for (size_t j = 0; j < methods.size(); ++j)
     if (method_idx[j] != 0xFFFFFFFFu) put(methods[j], &method_idx[j], 1, 0, nullptr);
   for (uint64_t i : entries) put(i, g->h_entry.data(), g->h_entry.size(), 0, nullptr);
+  for (uint64_t i : endpoints) put(i, g->h_endpoint_methods.data(), g->h_endpoint_methods.size(), 0, nullptr);
   return DMG_OK;
 }
 

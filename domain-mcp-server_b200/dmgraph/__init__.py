@@ -49,7 +49,7 @@ class QueryOp(C.Structure):
                 ("reserved", C.c_uint32)]
 
 
-OP_DEPENDENCIES, OP_DEPENDENTS, OP_OVERVIEW, OP_KHOP, OP_ENTRYPOINTS, OP_RESOLVE_NAME, OP_METHOD = range(7)
+OP_DEPENDENCIES, OP_DEPENDENTS, OP_OVERVIEW, OP_KHOP, OP_ENTRYPOINTS, OP_RESOLVE_NAME, OP_METHOD, OP_ENDPOINTS = range(8)
 
 
 class CallStats(C.Structure):
@@ -81,6 +81,8 @@ def lib():
             "dmg_graph_create": (i32, [vp, C.POINTER(GraphDesc), C.POINTER(vp)]),
             "dmg_graph_retain": (None, [vp]),
             "dmg_graph_release": (None, [vp]),
+            "dmg_graph_save": (i32, [vp, C.c_char_p]),
+            "dmg_graph_load": (i32, [vp, C.c_char_p, C.POINTER(vp)]),
             "dmg_graph_info_get": (i32, [vp, C.POINTER(GraphInfo)]),
             "dmg_adjacency_batch": (i32, [vp, i32, u64, vp, vp, vp, u64, pu64]),
             "dmg_neighbors_batch": (i32, [vp, i32, i32, i32, u64, vp, vp, vp, vp, vp, u64, pu64]),
@@ -101,6 +103,7 @@ def lib():
             "dmg_lookup_batch": (i32, [vp, i32, u32, u32, u64, vp, vp, vp]),
             "dmg_query_batch": (i32, [vp, u64, vp, vp, vp, vp, vp, u64, pu64]),
             "dmg_graph_set_methods": (i32, [vp, vp, vp, vp]),
+            "dmg_graph_set_method_flags": (i32, [vp, vp]),
             "dmg_last_call_stats": (i32, [vp, C.POINTER(CallStats)]),
             "dmg_profile_enable": (i32, [vp, i32]),
             "dmg_profile_reset": (i32, [vp]),
@@ -258,6 +261,21 @@ class Graph:
             self.L.dmg_graph_release(self.h)
             self.h = C.c_void_p()
 
+    def save(self, path):
+        _check(self.L.dmg_graph_save(self.h, path.encode()))
+
+    @classmethod
+    def load(cls, engine, path):
+        h = C.c_void_p()
+        _check(engine.L.dmg_graph_load(engine.h, path.encode(), C.byref(h)))
+        g = cls.__new__(cls)
+        g.eng, g.L, g.h = engine, engine.L, h
+        info = GraphInfo()
+        _check(g.L.dmg_graph_info_get(g.h, C.byref(info)))
+        g.info = {f: getattr(info, f) for f, _ in GraphInfo._fields_}
+        g.V = g.info["n_vertices"]
+        return g
+
     # -- T0/T1 ---------------------------------------------------------------------------------
     def adjacency_batch(self, direction, ids, cap=None):
         ids = _arr(ids, np.uint32)
@@ -402,6 +420,10 @@ class Graph:
             np.cumsum([len(b) for b in enc], out=no[1:])
         lb = np.frombuffer(b"".join(enc) + b"\0", dtype=np.uint8).copy()
         _check(self.L.dmg_graph_set_methods(self.h, mo.ctypes.data, no.ctypes.data, lb.ctypes.data))
+
+    def set_method_flags(self, flags):
+        f = np.ascontiguousarray(flags, dtype=np.uint8)
+        _check(self.L.dmg_graph_set_method_flags(self.h, f.ctypes.data if f.size else None))
 
     def query_batch(self, ops):
         """ops: list of dicts {op, vertex?, mode?, k?, exclude?, text?(bytes)}; returns rows of (id, aux)."""

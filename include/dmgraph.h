@@ -139,6 +139,14 @@ void dmg_graph_retain(dmg_graph* g);
 void dmg_graph_release(dmg_graph* g); /* frees device memory when the count reaches 0 */
 int32_t dmg_graph_info_get(const dmg_graph* g, dmg_graph_info* out);
 
+/* Binary CSR snapshot: dmg_graph_save writes the graph exactly as the
+ * device holds it (forward + reverse CSR, project ranges, entry list, names and their lower-cased
+ * copy); dmg_graph_load uploads it again without JSON parsing, string hashing of edges or CSR
+ * construction -- the startup path GraphService.loadAll (GS:55-76) pays per project today.  The
+ * file is host-endian and meant as a sidecar of graph_data, rebuilt whenever the graph is.      */
+int32_t dmg_graph_save(dmg_graph* g, const char* path);
+int32_t dmg_graph_load(dmg_engine* e, const char* path, dmg_graph** out);
+
 /* ---- T0 / T1: adjacency rows ---------------------------------------------------------------
  * dependencies(id) (PG:299-305): dir = DMG_OUT, row order = addDependency order.
  * dependents(id)   (PG:316-328): dir = DMG_IN, row order = ascending source id (the
@@ -299,6 +307,10 @@ int32_t dmg_lookup_batch(dmg_graph* g, int32_t kind, uint32_t v_lo, uint32_t v_h
  *   DMG_OP_METHOD        executeMethodCheck / vertexSingleMethod, GQS:324-394: text = lower-cased
  *                        method name; the row holds the catalog index of the first method of
  *                        `vertex` whose lower-cased name equals it (empty row = not found)
+ *   DMG_OP_ENDPOINTS     executeEndpoints / ProjectGraph.allEndpoints, GQS:77-109, PG:606-618: catalog
+ *                        indices of the methods flagged as HTTP endpoints (dmg_graph_set_method_flags),
+ *                        ascending = vertex order then method order (the reference walks a HashMap
+ *                        here; its order is pinned by no test)
  * text of an op is text_bytes[text_begin .. text_end).  Unknown vertices give empty rows.      */
 #define DMG_OP_DEPENDENCIES 0
 #define DMG_OP_DEPENDENTS 1
@@ -307,6 +319,7 @@ int32_t dmg_lookup_batch(dmg_graph* g, int32_t kind, uint32_t v_lo, uint32_t v_h
 #define DMG_OP_ENTRYPOINTS 4
 #define DMG_OP_RESOLVE_NAME 5
 #define DMG_OP_METHOD 6
+#define DMG_OP_ENDPOINTS 7
 
 typedef struct dmg_query_op {
   uint32_t opcode;
@@ -328,6 +341,9 @@ int32_t dmg_query_batch(dmg_graph* g, uint64_t n_ops, const dmg_query_op* ops, c
  * lower_bytes[name_off[m] .. name_off[m+1]).  Optional; needed only by DMG_OP_METHOD.           */
 int32_t dmg_graph_set_methods(dmg_graph* g, const uint32_t* method_off, const uint32_t* name_off,
                               const uint8_t* lower_bytes);
+/* One byte per catalog entry; bit 0 = MethodInfo.isHttpEndpoint() (httpMethod and httpPath present,
+ * PG:75-77).  Needs dmg_graph_set_methods first.                                                 */
+int32_t dmg_graph_set_method_flags(dmg_graph* g, const uint8_t* flags);
 
 /* ---- measurement -----------------------------------------------------------------------------*/
 int32_t dmg_last_call_stats(dmg_engine* e, dmg_call_stats* out);

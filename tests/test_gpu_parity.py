@@ -531,6 +531,10 @@ def test_query_batch_mixed_ops_against_oracle(engine):
             base = sum(len(ms) for ms in meths[:v]) if v < n else 0
             hit = next((j for j, m in enumerate(meths[v] if v < n else []) if m.lower() == t), None)
             want.append(([base + hit], None) if hit is not None else ([], None))
+    flags = [int(m.startswith("Handle")) for m in catalog]
+    g.set_method_flags(flags)
+    ops.append({"op": dmgraph.OP_ENDPOINTS})
+    want.append(([i for i, f in enumerate(flags) if f], None))
     got = g.query_batch(ops)
     for (gi, ga), (wi, wa) in zip(got, want):
         assert gi == wi
@@ -638,3 +642,33 @@ def test_lookup_batch_exact_and_simple(engine):
     wo, wi = ora.search_batch(off, lowb, [x.encode() for x in qs], 1, 100, 4400)
     assert np.array_equal(o, wo) and np.array_equal(i1, wi)
     g.release()
+
+
+# ---- binary CSR snapshot ------------------------------------------------------
+def test_snapshot_save_load_round_trip(engine, tmp_path):
+    sg = synth.eco_graph(n_projects=3, v_per=400, e_per=3000, cap=60, seed=21)
+    off, arena = synth.pack_names(sg.names)
+    g = dmgraph.Graph(engine, sg.n_vertices, sg.src, sg.dst, sg.entry, part_off=sg.part_off,
+                      name_off=off, name_bytes=arena)
+    path = str(tmp_path / "eco.dmgcsr")
+    g.save(path)
+    r = dmgraph.Graph.load(engine, path)
+    assert {k: v for k, v in r.info.items() if k != "device_bytes"} == {k: v for k, v in g.info.items() if k != "device_bytes"}
+    q_off, q_src = synth.stacktrace_queries(sg, n_queries=300, seed=2)
+    for a, b in zip(g.neighbors_batch(2, 2, 1, q_off, q_src), r.neighbors_batch(2, 2, 1, q_off, q_src)):
+        assert np.array_equal(a, b)
+    ids = np.arange(sg.n_vertices, dtype=np.uint32)
+    for d in (0, 1):
+        for a, b in zip(g.adjacency_batch(d, ids), r.adjacency_batch(d, ids)):
+            assert np.array_equal(a, b)
+    assert np.array_equal(g.analysis_order(), r.analysis_order())
+    assert np.array_equal(g.entry_points(), r.entry_points())
+    for a, b in zip(g.search_batch(0, [b"order", b"svc1", b""]), r.search_batch(0, [b"order", b"svc1", b""])):
+        assert np.array_equal(a, b)
+    assert np.array_equal(g.lookup_batch(0, [sg.names[5].encode()]), r.lookup_batch(0, [sg.names[5].encode()]))
+    bad = tmp_path / "bad.dmgcsr"
+    bad.write_bytes(b"not a snapshot")
+    with pytest.raises(dmgraph.DmgError):
+        dmgraph.Graph.load(engine, str(bad))
+    g.release()
+    r.release()
