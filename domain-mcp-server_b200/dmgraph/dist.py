@@ -141,8 +141,12 @@ class PartitionedClosure:
         own = s[(s >= self.v_lo) & (s < self.v_hi)] - self.v_lo
         if own.size:
             self.level[torch.from_numpy(own).to(self.level.device)] = 0
+        import time
         n_front, reached, lvl = int(s.size), int(s.size), 1
+        self.stats["level_ms"] = []
         while n_front > 0:
+            t_lvl = time.perf_counter()
+            mode = "push" if n_front < self.PUSH_BELOW * self.V else "pull"
             if n_front < self.PUSH_BELOW * self.V:
                 self.stats["edges"] += self.stepper.push(direction, self.frontier, self.contrib)
                 self._allgather(self.gather_push, self.contrib)
@@ -155,6 +159,7 @@ class PartitionedClosure:
                 n_new = self.stepper.merge(lvl, self.contrib, 1, self.words, self.visited, self.next, self.level)
                 self.stats["pull_levels"] += 1
             self.frontier, self.next = self.next, self.frontier
+            self.stats["level_ms"].append((mode, n_front, round(1e3 * (time.perf_counter() - t_lvl), 3)))
             n_front = int(n_new)
             reached += n_front
             lvl += 1

@@ -52,7 +52,7 @@ def main():
     pc = ddist.PartitionedClosure(V, rank, world, stepper, "cuda", dist if world > 1 else None)
     times = []
     for it in range(1 + args.steps):
-        pc.stats = {k: 0 for k in pc.stats}
+        pc.stats = {k: 0 for k in pc.stats if k != "level_ms"}
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
@@ -108,7 +108,7 @@ def main():
                           "push_levels": pc.stats["push_levels"], "pull_levels": pc.stats["pull_levels"],
                           "seconds": float(tmax.item()), "edges_read_all_ranks": float(edges.item()),
                           "gteps_read": float(edges.item()) / float(tmax.item()) / 1e9,
-                          "exchanged_bytes_per_rank": pc.stats["exchanged_bytes"], "generate_s": t_gen,
+                          "exchanged_bytes_per_rank": pc.stats["exchanged_bytes"], "level_ms_rank0": pc.stats.get("level_ms"), "generate_s": t_gen,
                           "upload_s_rank0": t_up, "stepper": "sync" if args.sync_stepper else "stream-ordered", "checked_against": args.check, "matches": ok,
                           "single_gpu": single}), flush=True)
         assert ok is not False
