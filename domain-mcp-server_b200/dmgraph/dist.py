@@ -130,17 +130,21 @@ class PartitionedClosure:
 
     def run(self, sources, direction=OUT):
         torch = self.torch
-        bits = np.zeros(self.words, np.uint32)
-        s = np.unique(np.asarray(sources, dtype=np.int64))
-        s = s[(s >= 0) & (s < self.V)]
-        np.bitwise_or.at(bits, s >> 5, (1 << (s & 31)).astype(np.uint32))
-        t = torch.from_numpy(bits.view(np.int32)).to(self.frontier.device)
-        self.frontier.copy_(t)
-        self.visited.copy_(t)
+        # source bitmap, built where the bitmaps live (no host-side bit twiddling on V-sized arrays)
+        dev = self.frontier.device
+        s = torch.as_tensor(np.asarray(sources, dtype=np.int64), device=dev)
+        s = torch.unique(s[(s >= 0) & (s < self.V)])
+        mask = torch.zeros(self.words * 32, dtype=torch.int64, device=dev)
+        mask[s] = 1
+        packed = (mask.view(-1, 32) << torch.arange(32, dtype=torch.int64, device=dev)).sum(dim=1)
+        packed = torch.where(packed >= 2 ** 31, packed - 2 ** 32, packed).to(torch.int32)
+        self.frontier.copy_(packed)
+        self.visited.copy_(packed)
         self.level.fill_(-1)
         own = s[(s >= self.v_lo) & (s < self.v_hi)] - self.v_lo
-        if own.size:
-            self.level[torch.from_numpy(own).to(self.level.device)] = 0
+        if own.numel():
+            self.level[own] = 0
+        s = s.cpu().numpy()
         import time
         n_front, reached, lvl = int(s.size), int(s.size), 1
         self.stats["level_ms"] = []
