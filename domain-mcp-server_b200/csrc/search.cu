@@ -40,6 +40,29 @@ int32_t dmg_search_batch(dmg_graph* g, int32_t kind, uint32_t v_lo, uint32_t v_h
   *needed = 0;
   out_off[0] = 0;
   if (nq == 0) return DMG_OK;
+  constexpr uint64_t SLICE = 16384;   // distinct patterns one pass over the arena handles
+  if (nq > SLICE) {
+    // larger batches run slice by slice; rows are appended in query order
+    uint64_t total = 0;
+    int32_t rc = DMG_OK;
+    std::vector<uint64_t> off(SLICE + 1);
+    for (uint64_t q0 = 0; q0 < nq; q0 += SLICE) {
+      const uint64_t n = std::min<uint64_t>(SLICE, nq - q0);
+      uint64_t need = 0;
+      const uint64_t room = (rc == DMG_OK && out_ids && cap > total) ? cap - total : 0;
+      const int32_t st = dmg_search_batch(g, kind, v_lo, v_hi, n, q_off + q0, q_bytes, off.data(),
+                                          room ? out_ids + total : nullptr, room, &need);
+      if (st != DMG_OK && st != DMG_ECAP) return st;
+      if (st == DMG_ECAP) rc = DMG_ECAP;
+      for (uint64_t j = 0; j < n; ++j) out_off[q0 + j] = total + off[j];
+      total += need;
+    }
+    out_off[nq] = total;
+    *needed = total;
+    if (rc == DMG_ECAP)
+      set_error("dmg_search_batch: capacity %llu < needed %llu", (unsigned long long)cap, (unsigned long long)total);
+    return rc;
+  }
   const uint64_t qbytes = q_off[nq];
   if (qbytes && !q_bytes) {
     set_error("dmg_search_batch: q_bytes is NULL (a null query is the host's NullPointerException, CCS:1507)");

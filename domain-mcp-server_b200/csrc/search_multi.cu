@@ -72,6 +72,13 @@ struct SearchArgs {
   const unsigned long long* out_off;
   uint32_t* out_ids;
   unsigned long long cap;
+  // hit log of the count pass (see search_multi_kernel)
+  uint32_t* log;
+  unsigned long long log_cap;
+  unsigned long long* log_used;
+  unsigned long long* step_base;
+  uint32_t* step_cnt;
+  uint32_t steps_per_tile;
 };
 
 __device__ __forceinline__ uint32_t hash_slot(unsigned long long k, uint32_t mask) {
@@ -110,36 +117,14 @@ __device__ __forceinline__ unsigned long long low_bytes_mask(uint32_t len) {
   return len >= 8 ? ~0ull : ((1ull << (8 * len)) - 1ull);
 }
 
-// One lane per name: the 32 lanes of a warp scan 32 consecutive names in lock step, so the
-// (frequent) hit path runs with many lanes active.  A lane collects the distinct patterns of its
-// name in shared memory; after the step the warp delivers the 32 lists in lane order == name
-// order, which keeps every row ascending.
-template <int MODE>   // 0 count, 1 emit, 2 first
-__global__ void __launch_bounds__(SM_THREADS) search_multi_kernel(const SearchArgs a) {
-  extern __shared__ __align__(16) uint32_t sm_u32[];
-  uint32_t* f16 = sm_u32;
-  uint32_t* f12 = f16 + a.filt_words16;
-  uint32_t* f8 = f12 + a.filt_words12;
-  uint32_t* f4 = f8 + a.filt_words8;
-  uint32_t* f3 = f4 + a.filt_words4;
-  __shared__ uint16_t s_hits[SM_WARPS][32][SM_HITBUF];
-  __shared__ uint32_t s_nh[SM_WARPS][32];
-  const int tid = threadIdx.x, lane = tid & 31, wib = tid >> 5;
-  const uint32_t fw = a.filt_words16 + a.filt_words12 + a.filt_words8 + a.filt_words4 + a.filt_words3;
-  for (uint32_t i = tid; i < fw; i += SM_THREADS) sm_u32[i] = a.filt[i];
-  __syncthreads();
-
-  const uint32_t tile = blockIdx.x * SM_WARPS + wib;
-  if (tile >= a.n_tiles) return;
-  const uint32_t n0 = a.v_lo + tile * a.per_tile;
-  const uint32_t n1 = min(a.v_hi, n0 + a.per_tile);
-  uint32_t* my_cnt = (MODE == 2) ? nullptr : a.cnt + tile;   // element of pattern u: my_cnt[u * n_tiles]
-  uint16_t* mine = s_hits[wib][lane];
-
-  for (uint32_t i0 = n0; i0 < n1; i0 += 32) {
-    const uint32_t i = i0 + lane;
+// Scans the name of this lane (vertex i, if i < n1) and collects the distinct patterns it contains in
+// `mine` (shared memory, SM_HITBUF entries).  Returns their number; a value above SM_HITBUF means the
+// list overflowed and the name has to be tested against every pattern.
+__device__ __forceinline__ uint32_t match_name(const SearchArgs& a, const uint32_t* f16, const uint32_t* f12,
+                                               const uint32_t* f8, const uint32_t* f4, const uint32_t* f3,
+                                               uint32_t i, uint32_t n1, uint16_t* mine) {
     uint32_t nh = 0;
-    // a pattern may occur at several positions of the name: keep it once; nh > SM_HITBUF = overflow
+    // a pattern may occur at several positions of the name: keep it once
     auto add = [&](uint32_t u) {
       for (uint32_t t = 0; t < nh && t < SM_HITBUF; ++t)
         if (mine[t] == (uint16_t)u) return;
@@ -247,57 +232,123 @@ __global__ void __launch_bounds__(SM_THREADS) search_multi_kernel(const SearchAr
         }
       }
     }
+    return nh;
+}
+
+// every pattern against one name, by the whole warp (names whose list overflowed)
+template <class F>
+__device__ __forceinline__ void exhaustive_name(const SearchArgs& a, uint32_t id, int lane, F deliver) {
+  const unsigned long long s = a.name_off[id], e = a.name_off[id + 1];
+  const uint32_t nn = (uint32_t)(e - s);
+  for (uint32_t u = lane; u < a.U; u += 32) {
+    const uint32_t len = a.pat[u].len;
+    bool hit = len == 0;
+    const uint8_t* pb = a.pbytes + a.poff[u];
+    for (uint32_t p = 0; !hit && p + len <= nn; ++p) {
+      uint32_t t = 0;
+      while (t < len && a.lower[s + p + t] == pb[t]) ++t;
+      hit = t == len;
+    }
+    if (hit) deliver(u, id);
+  }
+}
+
+// One lane per name: the 32 lanes of a warp scan 32 consecutive names in lock step, so the
+// (frequent) hit path runs with many lanes active.  A lane collects the distinct patterns of its
+// name in shared memory; the warp then handles the 32 lists in lane order == name order, which keeps
+// every row ascending.
+//   MODE 0  count: per (pattern, tile) counters, and the lists are appended to a hit log so that
+//           the emit pass does not have to match again
+//   MODE 1  emit: streams the log (32 hits per warp step; hits of one pattern inside a step get
+//           consecutive slots through __match_any_sync), re-matching only the steps that were
+//           not logged (log full, or a name with more than SM_HITBUF patterns)
+//   MODE 2  first: atomicMin per pattern
+template <int MODE>
+__global__ void __launch_bounds__(SM_THREADS) search_multi_kernel(const SearchArgs a) {
+  extern __shared__ __align__(16) uint32_t sm_u32[];
+  uint32_t* f16 = sm_u32;
+  uint32_t* f12 = f16 + a.filt_words16;
+  uint32_t* f8 = f12 + a.filt_words12;
+  uint32_t* f4 = f8 + a.filt_words8;
+  uint32_t* f3 = f4 + a.filt_words4;
+  __shared__ uint16_t s_hits[SM_WARPS][32][SM_HITBUF];
+  __shared__ uint32_t s_nh[SM_WARPS][32];
+  const int tid = threadIdx.x, lane = tid & 31, wib = tid >> 5;
+  const uint32_t fw = a.filt_words16 + a.filt_words12 + a.filt_words8 + a.filt_words4 + a.filt_words3;
+  for (uint32_t i = tid; i < fw; i += SM_THREADS) sm_u32[i] = a.filt[i];
+  __syncthreads();
+
+  const uint32_t tile = blockIdx.x * SM_WARPS + wib;
+  if (tile >= a.n_tiles) return;
+  const uint32_t n0 = a.v_lo + tile * a.per_tile;
+  const uint32_t n1 = min(a.v_hi, n0 + a.per_tile);
+  uint32_t* my_cnt = (MODE == 2) ? nullptr : a.cnt + tile;   // element of pattern u: my_cnt[u * n_tiles]
+  uint16_t* mine = s_hits[wib][lane];
+
+  auto write_rows = [&](uint32_t u, uint32_t id, uint32_t local) {
+    const uint4 raw = __ldg(reinterpret_cast<const uint4*>(a.prow + u));
+    unsigned long long pos = (((unsigned long long)raw.y << 32) | raw.x) + local;
+    if (pos < a.cap) a.out_ids[pos] = id;
+    for (uint32_t t = 1; t < raw.z; ++t) {   // the same text asked more than once
+      pos = a.out_off[a.uq[raw.w + t]] + local;
+      if (pos < a.cap) a.out_ids[pos] = id;
+    }
+  };
+  auto deliver = [&](uint32_t u, uint32_t id) {
+    if (MODE == 0) atomicAdd(&my_cnt[(size_t)u * a.n_tiles], 1u);
+    else if (MODE == 1) write_rows(u, id, atomicAdd(&my_cnt[(size_t)u * a.n_tiles], 1u));
+    else atomicMin(&a.first[u], id);
+  };
+
+  for (uint32_t i0 = n0; i0 < n1; i0 += 32) {
+    const size_t step = (size_t)tile * a.steps_per_tile + (i0 - n0) / 32;
+    if (MODE == 1) {
+      const uint32_t logged = a.step_cnt[step];
+      if (logged != 0xFFFFFFFFu) {
+        const unsigned long long b = a.step_base[step];
+        for (uint32_t j0 = 0; j0 < logged; j0 += 32) {
+          const uint32_t j = j0 + lane;
+          const bool valid = j < logged;
+          const uint32_t ent = valid ? a.log[b + j] : 0u;
+          const uint32_t u = ent & 0xFFFFu;
+          const unsigned peers = __match_any_sync(FULL, valid ? u : (0x10000u + lane));
+          const int leader = __ffs(peers) - 1;
+          uint32_t base = 0;
+          if (valid && lane == leader) base = atomicAdd(&my_cnt[(size_t)u * a.n_tiles], (uint32_t)__popc(peers));
+          base = __shfl_sync(FULL, base, leader);
+          if (valid) write_rows(u, i0 + (ent >> 16), base + __popc(peers & lanemask_lt()));
+        }
+        continue;
+      }
+    }
+    const uint32_t nh = match_name(a, f16, f12, f8, f4, f3, i0 + lane, n1, mine);
     s_nh[wib][lane] = nh;
     __syncwarp();
-    // deliver in lane order == name order
+    if (MODE == 0) {
+      // hit log: lists of the 32 names back to back, in lane order
+      const bool overflow = __any_sync(FULL, nh > SM_HITBUF);
+      const uint32_t inc = warp_incl_scan_u32(nh);
+      const uint32_t tot = __shfl_sync(FULL, inc, 31);
+      unsigned long long b = 0;
+      if (lane == 0 && !overflow && tot) b = atomicAdd(a.log_used, (unsigned long long)tot);
+      b = __shfl_sync(FULL, b, 0);
+      const bool fits = !overflow && b + tot <= a.log_cap;
+      if (fits)
+        for (uint32_t t = 0; t < nh; ++t) a.log[b + (inc - nh) + t] = ((uint32_t)lane << 16) | mine[t];
+      if (lane == 0) {
+        a.step_base[step] = b;
+        a.step_cnt[step] = fits ? tot : 0xFFFFFFFFu;
+      }
+    }
+    // counters / rows / minima, in lane order == name order
     for (int l = 0; l < 32; ++l) {
       const uint32_t n_l = s_nh[wib][l];
       const uint32_t id = i0 + l;
       if (n_l == 0) continue;
       if (n_l <= SM_HITBUF) {
-        for (uint32_t j = lane; j < n_l; j += 32) {
-          const uint32_t u = s_hits[wib][l][j];
-          if (MODE == 0) {
-            atomicAdd(&my_cnt[(size_t)u * a.n_tiles], 1u);
-          } else if (MODE == 1) {
-            const uint4 raw = __ldg(reinterpret_cast<const uint4*>(a.prow + u));
-            const uint32_t local = atomicAdd(&my_cnt[(size_t)u * a.n_tiles], 1u);
-            unsigned long long pos = (((unsigned long long)raw.y << 32) | raw.x) + local;
-            if (pos < a.cap) a.out_ids[pos] = id;
-            for (uint32_t t = 1; t < raw.z; ++t) {   // the same text asked more than once
-              pos = a.out_off[a.uq[raw.w + t]] + local;
-              if (pos < a.cap) a.out_ids[pos] = id;
-            }
-          } else {
-            atomicMin(&a.first[u], id);
-          }
-        }
+        for (uint32_t j = lane; j < n_l; j += 32) deliver(s_hits[wib][l][j], id);
       } else {
-        // more distinct patterns than the list holds: test every pattern against this name
-        const unsigned long long s = a.name_off[id], e = a.name_off[id + 1];
-        const uint32_t nn = (uint32_t)(e - s);
-        for (uint32_t u = lane; u < a.U; u += 32) {
-          const uint32_t len = a.pat[u].len;
-          bool hit = len == 0;
-          const uint8_t* pb = a.pbytes + a.poff[u];
-          for (uint32_t p = 0; !hit && p + len <= nn; ++p) {
-            uint32_t t = 0;
-            while (t < len && a.lower[s + p + t] == pb[t]) ++t;
-            hit = t == len;
-          }
-          if (!hit) continue;
-          if (MODE == 0) {
-            atomicAdd(&my_cnt[(size_t)u * a.n_tiles], 1u);
-          } else if (MODE == 1) {
-            const uint32_t local = atomicAdd(&my_cnt[(size_t)u * a.n_tiles], 1u);
-            for (uint32_t t = a.uq_off[u]; t < a.uq_off[u + 1]; ++t) {
-              const unsigned long long pos = a.out_off[a.uq[t]] + local;
-              if (pos < a.cap) a.out_ids[pos] = id;
-            }
-          } else {
-            atomicMin(&a.first[u], id);
-          }
-        }
+        exhaustive_name(a, id, lane, deliver);
       }
     }
     __syncwarp();
@@ -572,6 +623,23 @@ int32_t run_search_multi(CallCtx* c, dmg_graph* g, int kind, uint32_t v_lo, uint
   tiles = std::max<uint64_t>(tiles, 1);
   a.n_tiles = (uint32_t)tiles;
   a.per_tile = (uint32_t)((range + tiles - 1) / tiles);
+  a.steps_per_tile = (a.per_tile + 31) / 32;
+  {
+    // hit log of the count pass: the emit pass streams it instead of matching again.  Sized for 32
+    // hits per name; steps that do not fit are simply matched again by the emit pass.
+    const size_t n_steps = (size_t)tiles * std::max<uint32_t>(a.steps_per_tile, 1);
+    DMG_TRY(c->tmp3.reserve(n_steps * 12 + 64));
+    a.step_base = c->tmp3.as<unsigned long long>();
+    a.step_cnt = reinterpret_cast<uint32_t*>(a.step_base + n_steps);
+    a.log_used = &c->d_counters->aux[3];
+    a.log_cap = 0;
+    if (kind == DMG_SEARCH_CONTAINS_ALL && !sizes_only) {
+      const uint64_t want = std::min<uint64_t>(e->scratch_budget / 4, std::max<uint64_t>(1u << 20, 32ull * range));
+      DMG_TRY(c->scratch.reserve(want * 4));
+      a.log = c->scratch.as<uint32_t>();
+      a.log_cap = want;
+    }
+  }
   const unsigned blocks = (unsigned)((tiles + SM_WARPS - 1) / SM_WARPS);
 
   DMG_TRY(c->out_off.reserve((nq + 1) * 8));

@@ -672,3 +672,21 @@ def test_snapshot_save_load_round_trip(engine, tmp_path):
         dmgraph.Graph.load(engine, str(bad))
     g.release()
     r.release()
+
+
+def test_search_batches_larger_than_one_pass(engine):
+    """More queries than one pass over the arena handles (16384 distinct patterns): sliced internally."""
+    rng = np.random.default_rng(5)
+    names = synth.project_names(2, 4000, rng)
+    off, arena = synth.pack_names(names)
+    low = np.frombuffer(bytes(arena).lower(), dtype=np.uint8).copy()
+    g = dmgraph.Graph(engine, len(names), [], [], [], name_off=off, name_bytes=arena)
+    lows = [bytes(low[int(off[i]):int(off[i + 1])]) for i in range(len(names))]
+    queries = [lows[int(i)][int(a):int(a) + int(l)] + (b"" if j % 3 else str(j).encode())
+               for j, (i, a, l) in enumerate(zip(rng.integers(0, 4000, 40000), rng.integers(0, 25, 40000),
+                                                 rng.integers(2, 14, 40000)))]
+    for kind in (dmgraph.SEARCH_CONTAINS_ALL, dmgraph.SEARCH_CONTAINS_FIRST):
+        o, ids = g.search_batch(kind, queries)
+        wo, wids = ora.search_batch(off, low, queries, kind, threads=8)
+        assert np.array_equal(o, wo) and np.array_equal(ids, wids)
+    g.release()
