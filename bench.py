@@ -301,7 +301,6 @@ def main():
             e2e_ms += dt
             st = eng.last_stats()
             h2d, d2h = st["h2d_bytes"], st["d2h_bytes"]
-            launches += 0
     e2e_ms_max = allmax(e2e_ms)
     e2e_value = total_queries / (e2e_ms_max * 1e-3)
     assert int(h_off[-1]) == cap

@@ -71,13 +71,9 @@ enum KernelId : int {
   K_ORDER_MIN,
   K_ORDER_CLAIM,
   K_ORDER_TAIL,
-  K_SCAN_BLOCK,
-  K_SCAN_TOP,
-  K_SCAN_ADD,
   K_SEARCH_SCAN,
   K_SEARCH_FIRST,
   K_SEARCH_EMIT,
-  K_FLUSH,
   K_MISC,
   K_COUNT
 };

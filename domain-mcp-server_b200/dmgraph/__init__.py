@@ -125,9 +125,6 @@ def lib():
     return _lib
 
 
-HEADER_SYMBOLS = None
-
-
 def device_count():
     return lib().dmg_device_count()
 

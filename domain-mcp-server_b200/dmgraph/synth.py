@@ -74,8 +74,6 @@ def _zipf_targets(rng, n, deg):
     got_src = [np.empty(0, np.int64)]
     got_dst = [np.empty(0, np.int64)]
     got_seq = [np.empty(0, np.int64)]
-    have = np.zeros(n, np.int64)
-    taken = set()
     seq_base = 0
     keys_seen = np.empty(0, np.int64)
     while need.sum() > 0:
@@ -108,15 +106,7 @@ def _zipf_targets(rng, n, deg):
     dst = np.concatenate(got_dst)
     seq = np.concatenate(got_seq)
     o = np.lexsort((seq, src))
-    del taken, have
     return src[o], dst[o]
-
-
-def _java_names(p, n, rng):
-    layer = rng.integers(0, len(LAYERS), n)
-    stem = rng.integers(0, len(STEMS), n)
-    return ["co.fanki.svc%d.%s.%s%d%s" % (p, LAYERS[l], STEMS[s], i, SUFFIX[LAYERS[l]])
-            for i, (l, s) in enumerate(zip(layer, stem))]
 
 
 def project_names(p, n, rng):

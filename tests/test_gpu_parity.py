@@ -22,10 +22,6 @@ def engine():
     e.close()
 
 
-def rows(off, *arrs):
-    return [tuple(a[int(off[i]):int(off[i + 1])].tolist() for a in arrs) for i in range(len(off) - 1)]
-
-
 # ---- golden vectors transcribed from the reference's unit tests ------------------------------
 @pytest.mark.parametrize("case", CASES, ids=[c["name"] for c in CASES])
 def test_reference_unit_tests(engine, case):
