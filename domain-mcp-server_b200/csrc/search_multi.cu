@@ -31,7 +31,7 @@ constexpr uint32_t PAT_NIL = 0xFFFFFFFFu;
 struct __align__(16) PatSlot {     // one probe = one 16-byte load
   unsigned long long key;
   uint32_t first;                  // first pattern with this key, PAT_NIL = empty slot
-  uint32_t pad;
+  uint32_t fp;                     // fingerprint the key was inserted with (compared too)
 };
 struct __align__(16) PatInfo {     // one 16-byte load per candidate pattern
   unsigned long long pk8;          // first min(len, 8) bytes, little endian
@@ -81,18 +81,51 @@ struct SearchArgs {
   uint32_t steps_per_tile;
 };
 
-__device__ __forceinline__ uint32_t hash_slot(unsigned long long k, uint32_t mask) {
-  return (uint32_t)((k * 0x9E3779B97F4A7C15ull) >> 40) & mask;
+// Everything on the per-position path is 32-bit arithmetic (64-bit multiplies cost several
+// instructions each).  A class turns its window words into a table key (64 bits, compared exactly)
+// and a 32-bit fingerprint; the filter index and the slot index are cheap functions of the fingerprint.
+struct KeyFp {
+  unsigned long long key;
+  uint32_t fp;
+};
+__host__ __device__ __forceinline__ KeyFp class_key(int cls, uint32_t lo, uint32_t hi, uint32_t lo2, uint32_t hi2) {
+  KeyFp r;
+  switch (cls) {
+    case 0:   // >= 16 bytes: first 16
+      r.key = ((unsigned long long)(hi ^ (lo2 * 0x85EBCA6Bu)) << 32) | (lo ^ (hi2 * 0xC2B2AE35u));
+      r.fp = (lo * 0x9E3779B1u) ^ (hi * 0x85EBCA77u) ^ (lo2 * 0xC2B2AE3Du) ^ (hi2 * 0x27D4EB2Fu);
+      break;
+    case 1:   // 12..15 bytes: first 12
+      r.key = ((unsigned long long)(hi ^ (lo2 * 0x85EBCA6Bu)) << 32) | lo;
+      r.fp = (lo * 0x9E3779B1u) ^ (hi * 0x85EBCA77u) ^ (lo2 * 0xC2B2AE3Du);
+      break;
+    case 2:   // 8..11 bytes: first 8
+      r.key = ((unsigned long long)hi << 32) | lo;
+      r.fp = (lo * 0x9E3779B1u) ^ (hi * 0x85EBCA77u);
+      break;
+    case 3:   // 4..7 bytes: first 4
+      r.key = lo;
+      r.fp = lo * 0x9E3779B1u;
+      break;
+    default:  // exactly 3 bytes
+      r.key = lo & 0xFFFFFFu;
+      r.fp = (lo & 0xFFFFFFu) * 0x9E3779B1u;
+  }
+  r.fp ^= r.fp >> 15;
+  return r;
 }
-__device__ __forceinline__ uint32_t hash_filter(unsigned long long k, uint32_t bits) {
-  return (uint32_t)(((k ^ (k >> 29)) * 0xBF58476D1CE4E5B9ull) >> (64 - bits));
+__host__ __device__ __forceinline__ uint32_t hash_slot(uint32_t fp, uint32_t mask) {
+  return ((fp * 0x2C1B3C6Du) >> 9) & mask;
 }
-__device__ __forceinline__ uint32_t table_find(const SlotTable& t, unsigned long long k) {
-  uint32_t h = hash_slot(k, t.mask);
+__host__ __device__ __forceinline__ uint32_t hash_filter(uint32_t fp, uint32_t bits) {
+  return (fp * 0x297A2D39u) >> (32 - bits);
+}
+__device__ __forceinline__ uint32_t table_find(const SlotTable& t, unsigned long long k, uint32_t fp) {
+  uint32_t h = hash_slot(fp, t.mask);
   while (true) {
     const uint4 raw = __ldg(reinterpret_cast<const uint4*>(t.slot + h));
     if (raw.z == PAT_NIL) return PAT_NIL;
-    if ((((unsigned long long)raw.y << 32) | raw.x) == k) return raw.z;
+    if ((((unsigned long long)raw.y << 32) | raw.x) == k && raw.w == fp) return raw.z;
     h = (h + 1) & t.mask;
   }
 }
@@ -103,15 +136,6 @@ __device__ __forceinline__ PatInfo load_pat(const PatInfo* p, uint32_t u) {
   r.len = raw.z;
   r.next = raw.w;
   return r;
-}
-// key of the long classes: a 64-bit mix of the first 16 (12) bytes, so that patterns sharing a
-// popular 8-byte prefix ("createor...") do not pile up in one chain
-__host__ __device__ __forceinline__ unsigned long long mix_key(unsigned long long a, unsigned long long b) {
-  unsigned long long x = a * 0x9E3779B97F4A7C15ull ^ (b + 0x7F4A7C159E3779B9ull);
-  x ^= x >> 32;
-  x *= 0xD6E8FEB86659FD93ull;
-  x ^= x >> 29;
-  return x;
 }
 __device__ __forceinline__ unsigned long long low_bytes_mask(uint32_t len) {
   return len >= 8 ? ~0ull : ((1ull << (8 * len)) - 1ull);
@@ -144,8 +168,8 @@ __device__ __forceinline__ uint32_t match_name(const SearchArgs& a, const uint32
       uint32_t w4 = __ldg(reinterpret_cast<const uint32_t*>(wp + 16));
       wp += 20;
       // a pattern of the long classes: first 8 bytes already equal (or hashed): check the rest
-      auto long_class = [&](const SlotTable& tb, unsigned long long key, unsigned long long k8a, uint32_t r, uint32_t p) {
-        for (uint32_t u = table_find(tb, key); u != PAT_NIL;) {
+      auto long_class = [&](const SlotTable& tb, const KeyFp& kf, unsigned long long k8a, uint32_t r, uint32_t p) {
+        for (uint32_t u = table_find(tb, kf.key, kf.fp); u != PAT_NIL;) {
           const PatInfo pi = load_pat(a.pat, u);
           if (pi.len <= r && pi.pk8 == k8a) {
             bool ok = true;
@@ -166,20 +190,21 @@ __device__ __forceinline__ uint32_t match_name(const SearchArgs& a, const uint32
           const uint32_t lo2 = sh ? __funnelshift_r(w2, w3, sh) : w2;
           const uint32_t hi2 = sh ? __funnelshift_r(w3, w4, sh) : w3;
           if (a.t16.present && r >= 16) {
-            const unsigned long long key = mix_key(k8, ((unsigned long long)hi2 << 32) | lo2);
-            const uint32_t fi = hash_filter(key, a.t16.fbits);
-            if ((f16[fi >> 5] >> (fi & 31)) & 1u) long_class(a.t16, key, k8, r, p);
+            const KeyFp kf = class_key(0, lo32, hi32, lo2, hi2);
+            const uint32_t fi = hash_filter(kf.fp, a.t16.fbits);
+            if ((f16[fi >> 5] >> (fi & 31)) & 1u) long_class(a.t16, kf, k8, r, p);
           }
           if (a.t12.present) {
-            const unsigned long long key = mix_key(k8, lo2);
-            const uint32_t fi = hash_filter(key, a.t12.fbits);
-            if ((f12[fi >> 5] >> (fi & 31)) & 1u) long_class(a.t12, key, k8, r, p);
+            const KeyFp kf = class_key(1, lo32, hi32, lo2, 0u);
+            const uint32_t fi = hash_filter(kf.fp, a.t12.fbits);
+            if ((f12[fi >> 5] >> (fi & 31)) & 1u) long_class(a.t12, kf, k8, r, p);
           }
         }
         if (a.t8.present && r >= 8) {
-          const uint32_t fi = hash_filter(k8, a.t8.fbits);
+          const KeyFp kf = class_key(2, lo32, hi32, 0u, 0u);
+          const uint32_t fi = hash_filter(kf.fp, a.t8.fbits);
           if ((f8[fi >> 5] >> (fi & 31)) & 1u) {
-            for (uint32_t u = table_find(a.t8, k8); u != PAT_NIL;) {
+            for (uint32_t u = table_find(a.t8, kf.key, kf.fp); u != PAT_NIL;) {
               const PatInfo pi = load_pat(a.pat, u);
               if (pi.len <= r) {
                 bool ok = true;
@@ -195,9 +220,10 @@ __device__ __forceinline__ uint32_t match_name(const SearchArgs& a, const uint32
           }
         }
         if (a.t4.present && r >= 4) {
-          const uint32_t fi = hash_filter(lo32, a.t4.fbits);
+          const KeyFp kf = class_key(3, lo32, 0u, 0u, 0u);
+          const uint32_t fi = hash_filter(kf.fp, a.t4.fbits);
           if ((f4[fi >> 5] >> (fi & 31)) & 1u) {
-            for (uint32_t u = table_find(a.t4, lo32); u != PAT_NIL;) {
+            for (uint32_t u = table_find(a.t4, kf.key, kf.fp); u != PAT_NIL;) {
               const PatInfo pi = load_pat(a.pat, u);
               if (pi.len <= r && (k8 & low_bytes_mask(pi.len)) == pi.pk8) add(u);
               u = pi.next;
@@ -205,10 +231,10 @@ __device__ __forceinline__ uint32_t match_name(const SearchArgs& a, const uint32
           }
         }
         if (a.t3.present && r >= 3) {
-          const uint32_t k3 = lo32 & 0xFFFFFFu;
-          const uint32_t fi = hash_filter(k3, a.t3.fbits);
+          const KeyFp kf = class_key(4, lo32, 0u, 0u, 0u);
+          const uint32_t fi = hash_filter(kf.fp, a.t3.fbits);
           if ((f3[fi >> 5] >> (fi & 31)) & 1u) {
-            const uint32_t u = table_find(a.t3, k3);   // a 3-byte key is the whole pattern
+            const uint32_t u = table_find(a.t3, kf.key, kf.fp);   // a 3-byte key is the whole pattern
             if (u != PAT_NIL) add(u);
           }
         }
@@ -427,13 +453,6 @@ struct HostTables {
   std::vector<uint32_t> uq_off, uq;
 };
 
-static inline uint32_t h_hash_slot(unsigned long long k, uint32_t mask) {
-  return (uint32_t)((k * 0x9E3779B97F4A7C15ull) >> 40) & mask;
-}
-static inline uint32_t h_hash_filter(unsigned long long k, uint32_t bits) {
-  return (uint32_t)(((k ^ (k >> 29)) * 0xBF58476D1CE4E5B9ull) >> (64 - bits));
-}
-
 static void build_tables(uint64_t nq, const uint32_t* q_off, const uint8_t* q_bytes, HostTables& T) {
   std::unordered_map<std::string, uint32_t> ids;
   T.q2u.resize(nq);
@@ -466,7 +485,12 @@ static void build_tables(uint64_t nq, const uint32_t* q_off, const uint8_t* q_by
   T.poff.resize(U + 1);
   T.tiny2.assign(65536, 0);
   T.tiny1.assign(256, 0);
-  std::vector<std::pair<unsigned long long, uint32_t>> cls[5];
+  struct KeyedPat {
+    unsigned long long key;
+    uint32_t fp, u;
+    bool operator<(const KeyedPat& o) const { return key != o.key ? key < o.key : (fp != o.fp ? fp < o.fp : u < o.u); }
+  };
+  std::vector<KeyedPat> cls[5];
   for (uint32_t u = 0; u < U; ++u) {
     const std::string& p = T.pats[u];
     T.pat[u].len = (uint32_t)p.size();
@@ -479,14 +503,12 @@ static void build_tables(uint64_t nq, const uint32_t* q_off, const uint8_t* q_by
     if (p.empty()) T.empty_plus1 = u + 1;
     else if (p.size() == 1) T.tiny1[k & 0xFF] = u + 1;
     else if (p.size() == 2) T.tiny2[k & 0xFFFF] = u + 1;
-    else if (p.size() == 3) cls[4].emplace_back(k & 0xFFFFFF, u);
-    else if (p.size() < 8) cls[3].emplace_back(k & 0xFFFFFFFFull, u);
-    else if (p.size() < 12) cls[2].emplace_back(k, u);
     else {
       unsigned long long k2 = 0;
-      const size_t lim = p.size() < 16 ? 12 : 16;
-      for (size_t i = 8; i < lim; ++i) k2 |= (unsigned long long)(uint8_t)p[i] << (8 * (i - 8));
-      cls[p.size() < 16 ? 1 : 0].emplace_back(mix_key(k, k2), u);
+      for (size_t i = 8; i < p.size() && i < 16; ++i) k2 |= (unsigned long long)(uint8_t)p[i] << (8 * (i - 8));
+      const int c = p.size() >= 16 ? 0 : p.size() >= 12 ? 1 : p.size() >= 8 ? 2 : p.size() >= 4 ? 3 : 4;
+      const KeyFp kf = class_key(c, (uint32_t)k, (uint32_t)(k >> 32), (uint32_t)k2, c == 0 ? (uint32_t)(k2 >> 32) : 0u);
+      cls[c].push_back({kf.key, kf.fp, u});
     }
   }
   T.poff[U] = (uint32_t)T.pbytes.size();
@@ -495,13 +517,13 @@ static void build_tables(uint64_t nq, const uint32_t* q_off, const uint8_t* q_by
     auto& v = cls[c];
     std::sort(v.begin(), v.end());
     size_t nkeys = 0;
-    for (size_t i = 0; i < v.size(); ++i) nkeys += (i == 0 || v[i].first != v[i - 1].first);
+    for (size_t i = 0; i < v.size(); ++i) nkeys += (i == 0 || v[i].key != v[i - 1].key || v[i].fp != v[i - 1].fp);
     uint32_t size = 16;
     while (size < 2 * nkeys + 1) size <<= 1;
     PatSlot empty;
     empty.key = 0;
     empty.first = PAT_NIL;
-    empty.pad = 0;
+    empty.fp = 0;
     T.slot[c].assign(size, empty);
     uint32_t fb = 12;
     while ((1ull << fb) < 32 * nkeys && fb < (c == 0 ? 17u : 15u)) ++fb;
@@ -509,13 +531,14 @@ static void build_tables(uint64_t nq, const uint32_t* q_off, const uint8_t* q_by
     T.filt[c].assign((1u << fb) / 32, 0);
     for (size_t i = 0; i < v.size();) {
       size_t j = i;
-      while (j < v.size() && v[j].first == v[i].first) ++j;
-      uint32_t h = h_hash_slot(v[i].first, size - 1);
+      while (j < v.size() && v[j].key == v[i].key && v[j].fp == v[i].fp) ++j;
+      uint32_t h = hash_slot(v[i].fp, size - 1);
       while (T.slot[c][h].first != PAT_NIL) h = (h + 1) & (size - 1);
-      T.slot[c][h].key = v[i].first;
-      T.slot[c][h].first = v[i].second;
-      for (size_t t = i; t + 1 < j; ++t) T.pat[v[t].second].next = v[t + 1].second;   // chain, shortest id first
-      const uint32_t fi = h_hash_filter(v[i].first, fb);
+      T.slot[c][h].key = v[i].key;
+      T.slot[c][h].first = v[i].u;
+      T.slot[c][h].fp = v[i].fp;
+      for (size_t t = i; t + 1 < j; ++t) T.pat[v[t].u].next = v[t + 1].u;   // patterns sharing the key
+      const uint32_t fi = hash_filter(v[i].fp, fb);
       T.filt[c][fi >> 5] |= 1u << (fi & 31);
       i = j;
     }
