@@ -80,15 +80,26 @@ __device__ __forceinline__ void find_window(const KhopArgs& a, uint32_t qb, uint
 //              adjacency entry a position, each warp takes a contiguous quarter of the positions
 //              and walks it 32 at a time, so lanes stay busy whatever the degree distribution
 //   bottom-up  when the frontier's rows hold many more entries than there are unseen vertices
-//              (m_f > 24 * n_unseen) each unseen vertex looks for ONE frontier member in its
+//              (m_f > BU_ALPHA * n_unseen, BU_ALPHA = 12) each unseen vertex looks for ONE frontier member in its
 //              reverse row instead: 8 lanes per vertex, 32-byte chunks, stop at the first hit
 // The finished hop8 array is copied to a staging row in global memory; khop_emit_kernel
 // compacts the staging rows into the packed, id-ordered output after a scan of the row sizes.
 // ---------------------------------------------------------------------------------------------
-constexpr uint32_t BU_ALPHA = 24;
+// tuning knobs of khop_small_kernel (compile time; variants are built with -D for experiments)
+#ifndef DMG_KS_THREADS
+#define DMG_KS_THREADS 128
+#endif
+#ifndef DMG_KS_MINB
+#define DMG_KS_MINB 16
+#endif
+constexpr int KS_THREADS = DMG_KS_THREADS;   // threads per query CTA
+#ifndef DMG_BU_ALPHA
+#define DMG_BU_ALPHA 12
+#endif
+constexpr uint32_t BU_ALPHA = DMG_BU_ALPHA;
 
 template <int THREADS, int WC>
-__global__ void __launch_bounds__(THREADS, 12) khop_small_kernel(const KhopArgs a) {
+__global__ void __launch_bounds__(THREADS, DMG_KS_MINB) khop_small_kernel(const KhopArgs a) {
   extern __shared__ __align__(16) unsigned char smem[];
   uint8_t* const hop8 = smem;                                             // WC bytes
   uint32_t* const hop32 = reinterpret_cast<uint32_t*>(smem);
@@ -359,9 +370,9 @@ __global__ void __launch_bounds__(THREADS, 12) khop_small_kernel(const KhopArgs 
 // picks the instantiation whose compile-time window covers the largest project
 template <class F>
 static inline int32_t with_small_kernel(uint32_t win_cap, F f) {
-  if (win_cap <= 512) return f(khop_small_kernel<128, 512>, 512);
-  if (win_cap <= 2048) return f(khop_small_kernel<128, 2048>, 2048);
-  return f(khop_small_kernel<128, 8192>, 8192);
+  if (win_cap <= 512) return f(khop_small_kernel<KS_THREADS, 512>, 512);
+  if (win_cap <= 2048) return f(khop_small_kernel<KS_THREADS, 2048>, 2048);
+  return f(khop_small_kernel<KS_THREADS, 8192>, 8192);
 }
 static inline size_t small_kernel_smem(uint32_t wc) { return (size_t)wc + wc / 8 + 2 * (size_t)wc; }
 
@@ -822,7 +833,7 @@ __global__ void entry_flags_kernel(const uint32_t* __restrict__ bits, uint32_t V
 // host side
 // ---------------------------------------------------------------------------------------------
 constexpr uint32_t SMALL_WINDOW_MAX = 8192;
-constexpr int KS_THREADS = 128;
+
 
 static int32_t reset_counters(CallCtx* c) {
   DMG_CUDA(cudaMemsetAsync(c->d_counters, 0, sizeof(DevCounters), c->stream));

@@ -9,7 +9,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(os.path.dirname(_HERE), "libdmgraph.so")
+LIB_PATH = os.environ.get("DMG_LIB") or os.path.join(os.path.dirname(_HERE), "libdmgraph.so")   # DMG_LIB: tuning builds
 
 OK, EINVAL, ENOMEM, ECAP, ECUDA, ENCCL, ENODEV = range(7)
 OUT, IN, BOTH = 0, 1, 2
