@@ -377,63 +377,61 @@ static inline int32_t with_small_kernel(uint32_t win_cap, F f) {
 static inline size_t small_kernel_smem(uint32_t wc) { return (size_t)wc + wc / 8 + 2 * (size_t)wc; }
 
 // One warp per query: staging row (hop bytes in id order) -> packed (id, hop) row.  A warp step
-// takes 512 vertices (one 16-byte load per lane), compacts them in id order into a per-warp
-// shared buffer (warp scan of the per-lane counts) and writes the run out coalesced.
+// takes 512 vertices as four coalesced word loads per lane; each word is then dealt out 32
+// vertices at a time (one shuffle puts vertex 32r+lane in lane `lane`), a ballot ranks the
+// members, and the ids / hops go straight to the packed row as contiguous warp-wide stores.
+// The kernel is bound by the write-only HBM rate (profiles/write_bw_probe.py: a plain 600 MB
+// fill runs at 3.7 TB/s on this part, against 5.9 TB/s for a copy), not by its instructions:
+// a shared-memory compaction, this version and a software-pipelined one all take 0.24 ms on
+// config 2.  Running these writes underneath the traversal (one persistent launch with
+// interleaved traverse / emit tickets and a per-chunk scan) was measured too: 1.14-1.23 ms per
+// step against 1.12 ms for the three launches, because the traversal is latency-bound and
+// loses the warp slots the emit work holds.
 constexpr int EM_THREADS = 256;
-__global__ void __launch_bounds__(EM_THREADS, 6) khop_emit_kernel(const uint8_t* __restrict__ stage, uint32_t WC,
+constexpr int EM_BLOCKS_PER_SM = 8;   // resident CTAs; the grid is one wave of them
+__global__ void __launch_bounds__(EM_THREADS, EM_BLOCKS_PER_SM) khop_emit_kernel(const uint8_t* __restrict__ stage, uint32_t WC,
                                                                unsigned long long q_begin, unsigned long long q_end,
                                                                const uint32_t* __restrict__ qwin,
                                                                const unsigned long long* __restrict__ out_off,
                                                                uint32_t* out_ids, uint8_t* out_hop,
                                                                unsigned long long cap) {
-  __shared__ uint16_t s_id[EM_THREADS / 32][512];
-  __shared__ uint8_t s_hop[EM_THREADS / 32][512];
-  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
   const unsigned long long warp = (blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x) >> 5;
   const unsigned long long nwarps = ((unsigned long long)gridDim.x * blockDim.x) >> 5;
+  const uint32_t src_lane = (uint32_t)lane >> 2, sh = 8u * ((uint32_t)lane & 3u);
+  const unsigned lt = lanemask_lt();
   for (unsigned long long q = q_begin + warp; q < q_end; q += nwarps) {
-    const uint32_t lo = qwin[2 * q], wn = qwin[2 * q + 1];
-    const uint8_t* st = stage + (size_t)(q - q_begin) * WC;
-    unsigned long long run = out_off[q];
-    for (uint32_t v0 = 0; v0 < wn; v0 += 512) {
-      const uint32_t v = v0 + lane * 16;
-      uint4 x4 = make_uint4(0u, 0u, 0u, 0u);
-      if (v < wn) x4 = *reinterpret_cast<const uint4*>(st + v);
-      uint32_t x[4] = {x4.x, x4.y, x4.z, x4.w};
-      uint32_t c = 0;
+    const uint32_t lo = qwin[2 * q], wn = qwin[2 * q + 1], nw4 = (wn + 3) >> 2;
+    const uint32_t* __restrict__ st = reinterpret_cast<const uint32_t*>(stage + (size_t)(q - q_begin) * WC);
+    const unsigned long long row = out_off[q];
+    if (row >= cap) continue;
+    const uint32_t room = (uint32_t)min(cap - row, 0xFFFFFFFFull);   // entries of this row that fit
+    uint32_t* __restrict__ ids = out_ids + row;
+    uint8_t* __restrict__ hops = out_hop + row;
+    uint32_t run = 0;
+    for (uint32_t w0 = 0; w0 < nw4; w0 += 128) {
+      uint32_t x[4];
 #pragma unroll
-      for (int w = 0; w < 4; ++w) {
-        if (v + 4 * w >= wn) x[w] = 0;   // words past the row are stale staging memory
-#pragma unroll
-        for (int bb = 0; bb < 4; ++bb) {
-          const uint32_t h = (x[w] >> (8 * bb)) & 255u;
-          c += (h != 0 && h != 255);
-        }
+      for (int k = 0; k < 4; ++k) {   // words past the row are stale staging memory
+        const uint32_t w = w0 + 32 * k + lane;
+        x[k] = (w < nw4) ? st[w] : 0u;
       }
-      const uint32_t inc = warp_incl_scan_u32(c);
-      const uint32_t tot = __shfl_sync(FULL, inc, 31);
-      uint32_t o = inc - c;
 #pragma unroll
-      for (int w = 0; w < 4; ++w)
+      for (int k = 0; k < 4; ++k) {
+        if (w0 + 32 * k >= nw4) break;
 #pragma unroll
-        for (int bb = 0; bb < 4; ++bb) {
-          const uint32_t h = (x[w] >> (8 * bb)) & 255u;
-          if (h != 0 && h != 255) {
-            s_id[wib][o] = (uint16_t)(lane * 16 + 4 * w + bb);
-            s_hop[wib][o] = (uint8_t)h;
-            ++o;
+        for (int r = 0; r < 4; ++r) {
+          const uint32_t h = (__shfl_sync(FULL, x[k], 8 * r + src_lane) >> sh) & 255u;
+          const bool member = (h - 1u) < 254u;   // 0 = not reached, 255 = excluded source
+          const unsigned m = __ballot_sync(FULL, member);
+          const uint32_t o = run + __popc(m & lt);
+          if (member && o < room) {
+            ids[o] = lo + 4 * (w0 + 32 * k) + 32 * r + lane;
+            hops[o] = (uint8_t)h;
           }
-        }
-      __syncwarp();
-      for (uint32_t i = lane; i < tot; i += 32) {
-        const unsigned long long pos = run + i;
-        if (pos < cap) {
-          out_ids[pos] = lo + v0 + s_id[wib][i];
-          out_hop[pos] = s_hop[wib][i];
+          run += __popc(m);
         }
       }
-      __syncwarp();
-      run += tot;
     }
   }
 }
@@ -929,7 +927,7 @@ static int32_t run_khop(CallCtx* c, dmg_graph* g, int mode, int k, int exclude, 
       {
         LaunchScope ls(c, K_KHOP_EMIT);
         const uint64_t warps = q1 - q0;
-        const uint64_t blocks = std::min<uint64_t>((warps + 7) / 8, (uint64_t)e->sm_count * 16);
+        const uint64_t blocks = std::min<uint64_t>((warps + 7) / 8, (uint64_t)e->sm_count * EM_BLOCKS_PER_SM);
         khop_emit_kernel<<<(unsigned)blocks, EM_THREADS, 0, c->stream>>>(a.stage, WC, q0, q1, a.qwin, a.out_off, a.out_ids,
                                                                  a.out_hop, a.cap);
       }
@@ -1254,7 +1252,7 @@ int32_t dmg_neighbors_batch_dev_static(dmg_graph* g, int32_t mode, int32_t k, in
   });
   scan_counts_kernel<<<(unsigned)std::min<uint64_t>(tiles, (uint64_t)e->sm_count * 4), SC_THREADS, 0, 0>>>(
       a.counts, nq, a.out_off, &ctr->aux[2], a.status, ctr);
-  khop_emit_kernel<<<(unsigned)std::min<uint64_t>((nq + 7) / 8, (uint64_t)e->sm_count * 16), EM_THREADS, 0, 0>>>(
+  khop_emit_kernel<<<(unsigned)std::min<uint64_t>((nq + 7) / 8, (uint64_t)e->sm_count * EM_BLOCKS_PER_SM), EM_THREADS, 0, 0>>>(
       a.stage, WC, 0, nq, a.qwin, a.out_off, a.out_ids, a.out_hop, a.cap);
   DMG_CUDA(cudaGetLastError());
   unsigned long long total = 0;
