@@ -109,7 +109,7 @@ __global__ void __launch_bounds__(THREADS, DMG_KS_MINB) khop_small_kernel(const 
   __shared__ uint32_t s_lo, s_hi, s_n, s_cnt;
   __shared__ uint32_t s_wsum[THREADS / 32 + 1];
   __shared__ uint32_t s_red[3][THREADS / 32];
-  __shared__ uint32_t s_end[THREADS], s_adj[THREADS];
+  __shared__ uint2 s_row[THREADS];   // flattened frontier rows of a chunk: (end position, idx offset - start position)
   constexpr int NW = THREADS / 32, NG = THREADS / 8;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int grp = tid >> 3, gl = tid & 7;
@@ -237,29 +237,29 @@ __global__ void __launch_bounds__(THREADS, DMG_KS_MINB) khop_small_kernel(const 
           }
           uint32_t T;
           const uint32_t pre = block_excl_scan<THREADS>(n, s_wsum, &T);
-          s_end[tid] = pre + n;
-          s_adj[tid] = b - pre;
+          s_row[tid] = make_uint2(pre + n, b - pre);
           __syncthreads();
           const uint32_t Tq = (((T + NW - 1) / NW) + 31u) & ~31u;
           const uint32_t pbeg = warp * Tq, pend = min(T, pbeg + Tq);
-          if (pbeg < pend) {
+          if (pbeg + lane < pend) {
             uint32_t r;   // first row whose end lies beyond pbeg
             {
               uint32_t l = 0, h = THREADS;
               while (l < h) {
                 const uint32_t m = (l + h) >> 1;
-                if (s_end[m] <= pbeg) l = m + 1; else h = m;
+                if (s_row[m].x <= pbeg) l = m + 1; else h = m;
               }
               r = l;
             }
+            reads += (pend - pbeg - lane + 31u) >> 5;
+            uint2 row = s_row[r];   // stays in registers while the lane's positions stay inside the row
             for (uint32_t p = pbeg + lane; p < pend; p += 32) {
-              while (s_end[r] <= p) ++r;
-              const uint32_t v = fidx[s_adj[r] + p] - lo;
-              ++reads;
+              while (row.x <= p) row = s_row[++r];
+              const uint32_t v = fidx[row.y + p] - lo;
               if (hop8[v] == 0) hop8[v] = (uint8_t)lvl;   // same value from every racer
             }
           }
-          __syncthreads();   // s_end / s_adj are rewritten by the next chunk
+          __syncthreads();   // s_row is rewritten by the next chunk
         }
       } else {
         // unseen vertices -> list
@@ -388,7 +388,8 @@ static inline size_t small_kernel_smem(uint32_t wc) { return (size_t)wc + wc / 8
 // step against 1.12 ms for the three launches, because the traversal is latency-bound and
 // loses the warp slots the emit work holds.
 constexpr int EM_THREADS = 256;
-constexpr int EM_BLOCKS_PER_SM = 8;   // resident CTAs; the grid is one wave of them
+constexpr int EM_BLOCKS_PER_SM = 8;   // resident CTAs
+constexpr int EM_GRID_PER_SM = 64;    // grid cap: several small waves balance better than one (0.240 vs 0.256 ms)
 __global__ void __launch_bounds__(EM_THREADS, EM_BLOCKS_PER_SM) khop_emit_kernel(const uint8_t* __restrict__ stage, uint32_t WC,
                                                                unsigned long long q_begin, unsigned long long q_end,
                                                                const uint32_t* __restrict__ qwin,
@@ -927,7 +928,7 @@ static int32_t run_khop(CallCtx* c, dmg_graph* g, int mode, int k, int exclude, 
       {
         LaunchScope ls(c, K_KHOP_EMIT);
         const uint64_t warps = q1 - q0;
-        const uint64_t blocks = std::min<uint64_t>((warps + 7) / 8, (uint64_t)e->sm_count * EM_BLOCKS_PER_SM);
+        const uint64_t blocks = std::min<uint64_t>((warps + 7) / 8, (uint64_t)e->sm_count * EM_GRID_PER_SM);
         khop_emit_kernel<<<(unsigned)blocks, EM_THREADS, 0, c->stream>>>(a.stage, WC, q0, q1, a.qwin, a.out_off, a.out_ids,
                                                                  a.out_hop, a.cap);
       }
@@ -1252,7 +1253,7 @@ int32_t dmg_neighbors_batch_dev_static(dmg_graph* g, int32_t mode, int32_t k, in
   });
   scan_counts_kernel<<<(unsigned)std::min<uint64_t>(tiles, (uint64_t)e->sm_count * 4), SC_THREADS, 0, 0>>>(
       a.counts, nq, a.out_off, &ctr->aux[2], a.status, ctr);
-  khop_emit_kernel<<<(unsigned)std::min<uint64_t>((nq + 7) / 8, (uint64_t)e->sm_count * EM_BLOCKS_PER_SM), EM_THREADS, 0, 0>>>(
+  khop_emit_kernel<<<(unsigned)std::min<uint64_t>((nq + 7) / 8, (uint64_t)e->sm_count * EM_GRID_PER_SM), EM_THREADS, 0, 0>>>(
       a.stage, WC, 0, nq, a.qwin, a.out_off, a.out_ids, a.out_hop, a.cap);
   DMG_CUDA(cudaGetLastError());
   unsigned long long total = 0;
