@@ -98,6 +98,38 @@ constexpr int KS_THREADS = DMG_KS_THREADS;   // threads per query CTA
 #endif
 constexpr uint32_t BU_ALPHA = DMG_BU_ALPHA;
 
+// SWAR helpers on a word of four hop bytes: bit 7 of a byte is set in the result where ...
+__device__ __forceinline__ uint32_t hop_bytes_eq(uint32_t x, uint32_t pattern4) {   // ... the byte equals pattern4's
+  const uint32_t y = x ^ pattern4;
+  return ~(((y & 0x7f7f7f7fu) + 0x7f7f7f7fu) | y) & 0x80808080u;
+}
+__device__ __forceinline__ uint32_t hop_bytes_member(uint32_t x) {   // ... the byte is neither 0 nor 255
+  const uint32_t y = ~x;
+  const uint32_t nz = ((x & 0x7f7f7f7fu) + 0x7f7f7f7fu) | x;
+  const uint32_t nf = ((y & 0x7f7f7f7fu) + 0x7f7f7f7fu) | y;
+  return nz & nf & 0x80808080u;
+}
+// Whole warp: appends the vertices (4w + byte) whose byte is marked in m to list[*n ...]; one
+// shared atomic per warp call, the order inside the list is immaterial (it is a set).
+__device__ __forceinline__ void append_marked(uint16_t* list, uint32_t* n, uint32_t w, uint32_t m, int lane) {
+  const uint32_t c = __popc(m);
+  const uint32_t inc = warp_incl_scan_u32(c);
+  const uint32_t tot = __shfl_sync(FULL, inc, 31);
+  if (tot == 0) return;
+  uint32_t pos = 0;
+  if (lane == 31) pos = atomicAdd(n, tot);
+  pos = __shfl_sync(FULL, pos, 31) + inc - c;
+  while (m) {
+    list[pos++] = (uint16_t)(4 * w + ((__ffs(m) - 1) >> 3));
+    m &= m - 1;
+  }
+}
+// keeps the bytes of word w that are vertices of a window of wn vertices (w < ceil(wn / 4))
+__device__ __forceinline__ uint32_t hop_bytes_inside(uint32_t w, uint32_t wn) {
+  const uint32_t n = min(4u, wn - 4u * w);
+  return 0x80808080u >> (8u * (4u - n));
+}
+
 template <int THREADS, int WC>
 __global__ void __launch_bounds__(THREADS, DMG_KS_MINB) khop_small_kernel(const KhopArgs a) {
   extern __shared__ __align__(16) unsigned char smem[];
@@ -157,7 +189,7 @@ __global__ void __launch_bounds__(THREADS, DMG_KS_MINB) khop_small_kernel(const 
 
     for (int lvl = 1; lvl <= a.k; ++lvl) {
       // ---- pass A: frontier size nf, its adjacency entries m_f (TE of SURVEY.md 8d), unseen count
-      const uint32_t want = (uint32_t)(lvl - 1);
+      const uint32_t want = (uint32_t)(lvl - 1), want4 = want * 0x01010101u;
       uint32_t mf = 0, nf = 0, nun = 0;
       if (lvl == 1) {
         for (uint32_t i = tid; i < ns; i += THREADS) {
@@ -167,15 +199,13 @@ __global__ void __launch_bounds__(THREADS, DMG_KS_MINB) khop_small_kernel(const 
       } else {
         for (uint32_t w = tid; w < nw4; w += THREADS) {
           const uint32_t x = hop32[w];
-#pragma unroll
-          for (int bb = 0; bb < 4; ++bb) {
-            const uint32_t h = (x >> (8 * bb)) & 255u, v = w * 4 + bb;
-            if (h == want) {
-              const uint32_t u = lo + v;
-              mf += fptr[u + 1] - fptr[u];
-              ++nf;
-            }
-            nun += (h == 0 && v < wn);
+          uint32_t fm = hop_bytes_eq(x, want4);
+          nf += __popc(fm);
+          nun += __popc(hop_bytes_eq(x, 0u) & hop_bytes_inside(w, wn));
+          while (fm) {
+            const uint32_t u = lo + 4 * w + ((__ffs(fm) - 1) >> 3);
+            fm &= fm - 1;
+            mf += fptr[u + 1] - fptr[u];
           }
         }
       }
@@ -212,18 +242,7 @@ __global__ void __launch_bounds__(THREADS, DMG_KS_MINB) khop_small_kernel(const 
         if (lvl > 1) {   // frontier = vertices found by the previous level -> list
           for (uint32_t w0 = 0; w0 < nw4; w0 += THREADS) {
             const uint32_t w = w0 + tid;
-            const uint32_t x = (w < nw4) ? hop32[w] : 0u;
-#pragma unroll
-            for (int bb = 0; bb < 4; ++bb) {
-              const bool in = ((x >> (8 * bb)) & 255u) == want && w < nw4;
-              const unsigned m = __ballot_sync(FULL, in);
-              if (m) {
-                uint32_t pos = 0;
-                if (lane == 0) pos = atomicAdd(&s_n, (uint32_t)__popc(m));
-                pos = __shfl_sync(FULL, pos, 0);
-                if (in) list[pos + __popc(m & lanemask_lt())] = (uint16_t)(w * 4 + bb);
-              }
-            }
+            append_marked(list, &s_n, w, (w < nw4) ? hop_bytes_eq(hop32[w], want4) : 0u, lane);
           }
           __syncthreads();
         }
@@ -265,19 +284,7 @@ __global__ void __launch_bounds__(THREADS, DMG_KS_MINB) khop_small_kernel(const 
         // unseen vertices -> list
         for (uint32_t w0 = 0; w0 < nw4; w0 += THREADS) {
           const uint32_t w = w0 + tid;
-          const uint32_t x = (w < nw4) ? hop32[w] : 0xFFFFFFFFu;
-#pragma unroll
-          for (int bb = 0; bb < 4; ++bb) {
-            const uint32_t v = w * 4 + bb;
-            const bool un = ((x >> (8 * bb)) & 255u) == 0 && v < wn;
-            const unsigned m = __ballot_sync(FULL, un);
-            if (m) {
-              uint32_t pos = 0;
-              if (lane == 0) pos = atomicAdd(&s_n, (uint32_t)__popc(m));
-              pos = __shfl_sync(FULL, pos, 0);
-              if (un) list[pos + __popc(m & lanemask_lt())] = (uint16_t)v;
-            }
-          }
+          append_marked(list, &s_n, w, (w < nw4) ? (hop_bytes_eq(hop32[w], 0u) & hop_bytes_inside(w, wn)) : 0u, lane);
         }
         __syncthreads();
         const uint32_t nu = s_n;
@@ -340,11 +347,7 @@ __global__ void __launch_bounds__(THREADS, DMG_KS_MINB) khop_small_kernel(const 
     for (uint32_t i = tid; i < nw4; i += THREADS) {
       const uint32_t x = hop32[i];
       st[i] = x;
-#pragma unroll
-      for (int bb = 0; bb < 4; ++bb) {
-        const uint32_t h = (x >> (8 * bb)) & 255u;
-        cnt += (h != 0 && h != 255);
-      }
+      cnt += __popc(hop_bytes_member(x));
     }
     cnt = warp_sum_u32(cnt);
     if (lane == 0 && cnt) atomicAdd(&s_cnt, cnt);
@@ -462,7 +465,7 @@ __global__ void __launch_bounds__(KG_THREADS) khop_global_kernel(const KhopArgs 
   __shared__ uint32_t s_lo, s_hi, s_tail, s_flag;
   __shared__ uint32_t s_seg[DMG_MAX_HOPS + 2];
   __shared__ uint32_t s_wsum[NW + 1];
-  __shared__ uint32_t s_end[THREADS], s_adj[THREADS];
+  __shared__ uint2 s_row[THREADS];   // (end position, idx offset - start position) per flattened row
   uint32_t* seen = sc_seen + (size_t)blockIdx.x * seen_words;
   uint8_t* hopg = sc_hop + (size_t)blockIdx.x * hop_bytes;
   uint32_t* queue = sc_queue + (size_t)blockIdx.x * qcap;
@@ -519,8 +522,7 @@ __global__ void __launch_bounds__(KG_THREADS) khop_global_kernel(const KhopArgs 
         }
         uint32_t T;
         const uint32_t pre = block_excl_scan<THREADS>(n, s_wsum, &T);
-        s_end[tid] = pre + n;
-        s_adj[tid] = b - pre;
+        s_row[tid] = make_uint2(pre + n, b - pre);
         if (tid == 0) {
           te += T;
           rows += min(tail - c0, (uint32_t)THREADS);
@@ -534,17 +536,18 @@ __global__ void __launch_bounds__(KG_THREADS) khop_global_kernel(const KhopArgs 
             uint32_t l = 0, h = THREADS;
             while (l < h) {
               const uint32_t m = (l + h) >> 1;
-              if (s_end[m] <= pbeg) l = m + 1; else h = m;
+              if (s_row[m].x <= pbeg) l = m + 1; else h = m;
             }
             r = l;
           }
+          uint2 row = s_row[r];   // stays in registers while the lane's positions stay inside the row
           for (uint32_t p0 = pbeg; p0 < pend; p0 += 32) {
             const uint32_t p = p0 + lane;
             bool isnew = false;
             uint32_t v = 0;
             if (p < pend) {
-              while (s_end[r] <= p) ++r;
-              v = fidx[s_adj[r] + p] - lo;
+              while (row.x <= p) row = s_row[++r];
+              v = fidx[row.y + p] - lo;
               const uint32_t bit = 1u << (v & 31);
               if (!(__ldcg(&seen[v >> 5]) & bit)) isnew = !(atomicOr(&seen[v >> 5], bit) & bit);
             }
