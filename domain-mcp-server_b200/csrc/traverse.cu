@@ -452,9 +452,8 @@ constexpr int KG_SORT_CAP = 4096;    // rows up to this length are ordered in sh
 constexpr int KG_BUCKETS = 1024;
 constexpr uint32_t KG_BUCKET_MAX = 48;   // longest bucket a single thread insertion-sorts
 
-__global__ void __launch_bounds__(KG_THREADS) khop_global_kernel(const KhopArgs a, uint32_t* sc_seen, uint8_t* sc_hop,
-                                                                 uint32_t* sc_queue, size_t seen_words,
-                                                                 size_t hop_bytes, size_t qcap) {
+__global__ void __launch_bounds__(KG_THREADS) khop_global_kernel(const KhopArgs a, uint32_t* sc_seen, uint32_t* sc_rank,
+                                                                 uint32_t* sc_queue, size_t seen_words, size_t qcap) {
   constexpr int THREADS = KG_THREADS, NW = THREADS / 32;
   extern __shared__ __align__(16) unsigned char kg_smem[];
   uint32_t* s_ids = reinterpret_cast<uint32_t*>(kg_smem);                    // [KG_SORT_CAP]
@@ -467,7 +466,7 @@ __global__ void __launch_bounds__(KG_THREADS) khop_global_kernel(const KhopArgs 
   __shared__ uint32_t s_wsum[NW + 1];
   __shared__ uint2 s_row[THREADS];   // (end position, idx offset - start position) per flattened row
   uint32_t* seen = sc_seen + (size_t)blockIdx.x * seen_words;
-  uint8_t* hopg = sc_hop + (size_t)blockIdx.x * hop_bytes;
+  uint32_t* rankw = sc_rank + (size_t)blockIdx.x * seen_words;   // per-word exclusive popcounts of a long row
   uint32_t* queue = sc_queue + (size_t)blockIdx.x * qcap;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const uint32_t* __restrict__ fptr = a.mode == DMG_BOTH ? a.und_ptr : (a.mode == DMG_OUT ? a.out_ptr : a.in_ptr);
@@ -647,50 +646,45 @@ __global__ void __launch_bounds__(KG_THREADS) khop_global_kernel(const KhopArgs 
       }
     }
     if (total && scan_path) {
-      // long row: hop bytes into scratch, then an ordered scan of the claim bitmap
-      for (uint32_t i = tid; i < ns; i += THREADS)
-        if (a.exclude) hopg[queue[i]] = 255;
-      __syncthreads();
-      for (uint32_t i = tid; i < total; i += THREADS) {
-        const uint32_t p = ns + i;
-        int lv = 1;
-        while (lv < nlev && p >= s_seg[lv]) ++lv;
-        hopg[queue[p]] = (uint8_t)lv;
+      // long row: every discovered vertex is RANKED inside the claim bitmap instead of sorted.
+      // Pass 1 turns the bitmap into per-word exclusive popcounts (coalesced, uniform work);
+      // pass 2 streams the queue and drops (id, hop) at base + rank(id).  No hop array, no
+      // per-bit lookups, one barrier pair per 4096 bitmap words.
+      if (a.exclude) {   // excluded sources keep their claim bit during the traversal; they are not results
+        for (uint32_t i = tid; i < ns; i += THREADS) {
+          const uint32_t v = queue[i];
+          atomicAnd(&seen[v >> 5], ~(1u << (v & 31)));
+        }
+        __threadfence_block();
+        __syncthreads();
+      }
+      const uint32_t nquads = (wn + 127) >> 7;   // the bitmap is padded with zero words to a multiple of 4
+      const uint4* seen4 = reinterpret_cast<const uint4*>(seen);
+      uint4* rank4 = reinterpret_cast<uint4*>(rankw);
+      uint32_t run = 0;
+      for (uint32_t g0 = 0; g0 < nquads; g0 += THREADS) {
+        const uint32_t gq = g0 + tid;
+        uint4 c = make_uint4(0u, 0u, 0u, 0u);
+        if (gq < nquads) {
+          const uint4 x = __ldcg(seen4 + gq);
+          c = make_uint4(__popc(x.x), __popc(x.y), __popc(x.z), __popc(x.w));
+        }
+        uint32_t tot;
+        const uint32_t off = run + block_excl_scan<THREADS>(c.x + c.y + c.z + c.w, s_wsum, &tot);
+        if (gq < nquads) rank4[gq] = make_uint4(off, off + c.x, off + c.x + c.y, off + c.x + c.y + c.z);
+        run += tot;
       }
       __threadfence_block();
       __syncthreads();
-      const uint32_t nwords = (wn + 31) >> 5;
-      unsigned long long run = base;
-      constexpr uint32_t WPT = 4;   // bitmap words per thread per step
-      for (uint32_t w0 = 0; w0 < nwords; w0 += THREADS * WPT) {
-        uint32_t keep[WPT], cnt = 0;
-#pragma unroll
-        for (uint32_t j = 0; j < WPT; ++j) {
-          const uint32_t w = w0 + tid * WPT + j;
-          const uint32_t bits = (w < nwords) ? __ldcg(&seen[w]) : 0u;
-          keep[j] = 0;
-          for (uint32_t bb = bits; bb; bb &= bb - 1) {
-            const uint32_t v = w * 32 + (__ffs(bb) - 1);
-            if (__ldcg(&hopg[v]) != 255) keep[j] |= 1u << (v & 31);
-          }
-          cnt += __popc(keep[j]);
+      for (uint32_t i = tid; i < total; i += THREADS) {
+        const uint32_t p = ns + i, v = queue[p], w = v >> 5;
+        int lv = 1;
+        while (lv < nlev && p >= s_seg[lv]) ++lv;
+        const unsigned long long pos = base + __ldcg(&rankw[w]) + __popc(__ldcg(&seen[w]) & ((1u << (v & 31)) - 1u));
+        if (pos < a.cap) {
+          a.tmp_ids[pos] = lo + v;
+          a.tmp_hop[pos] = (uint8_t)lv;
         }
-        uint32_t tot;
-        const uint32_t off = block_excl_scan<THREADS>(cnt, s_wsum, &tot);
-        unsigned long long pos = run + off;
-#pragma unroll
-        for (uint32_t j = 0; j < WPT; ++j) {
-          const uint32_t w = w0 + tid * WPT + j;
-          for (uint32_t bb = keep[j]; bb; bb &= bb - 1) {
-            const uint32_t v = w * 32 + (__ffs(bb) - 1);
-            if (pos < a.cap) {
-              a.tmp_ids[pos] = lo + v;
-              a.tmp_hop[pos] = __ldcg(&hopg[v]);
-            }
-            ++pos;
-          }
-        }
-        run += tot;
       }
     }
     __syncthreads();
@@ -708,7 +702,10 @@ __global__ void __launch_bounds__(KG_THREADS) khop_global_kernel(const KhopArgs 
   }
 }
 
-// rows of khop_global_kernel from cursor order into query order (one warp per query)
+// Rows of khop_global_kernel from cursor order into query order.  Work is split by OUTPUT
+// position, not by query (rows run from nothing to a whole project): a warp takes 2048 output
+// positions, finds the row of the first one by bisection over out_off and walks forward.
+constexpr int GA_CHUNK = 2048;
 __global__ void __launch_bounds__(256) khop_gather_kernel(unsigned long long nq,
                                                           const unsigned long long* __restrict__ tmp_start,
                                                           const unsigned long long* __restrict__ out_off,
@@ -718,13 +715,26 @@ __global__ void __launch_bounds__(256) khop_gather_kernel(unsigned long long nq,
   const int lane = threadIdx.x & 31;
   const unsigned long long warp = (blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x) >> 5;
   const unsigned long long nwarps = ((unsigned long long)gridDim.x * blockDim.x) >> 5;
-  for (unsigned long long q = warp; q < nq; q += nwarps) {
-    const unsigned long long from = tmp_start[q], to = out_off[q], n = out_off[q + 1] - to;
-    for (unsigned long long i = lane; i < n; i += 32)
-      if (to + i < cap && from + i < cap) {
-        out_ids[to + i] = tmp_ids[from + i];
-        out_hop[to + i] = tmp_hop[from + i];
+  const unsigned long long total = min(out_off[nq], cap);
+  for (unsigned long long P = warp * GA_CHUNK; P < total; P += nwarps * GA_CHUNK) {
+    const unsigned long long Pend = min(total, P + GA_CHUNK);
+    unsigned long long q = 0, hi = nq;   // first row whose end lies beyond P (empty rows are skipped)
+    while (q < hi) {
+      const unsigned long long mid = (q + hi) >> 1;
+      if (out_off[mid + 1] <= P) q = mid + 1; else hi = mid;
+    }
+    unsigned long long row_end = out_off[q + 1], from = tmp_start[q] - out_off[q];   // u64 wrap-around is intended
+    for (unsigned long long p = P + lane; p < Pend; p += 32) {
+      while (p >= row_end) {
+        ++q;
+        row_end = out_off[q + 1];
+        from = tmp_start[q] - out_off[q];
       }
+      if (p + from < cap) {
+        out_ids[p] = tmp_ids[p + from];
+        out_hop[p] = tmp_hop[p + from];
+      }
+    }
   }
 }
 
@@ -938,19 +948,22 @@ static int32_t run_khop(CallCtx* c, dmg_graph* g, int mode, int k, int exclude, 
     }
   } else {
     const size_t seen_words = (((size_t)maxp + 31) / 32 + 3) & ~size_t(3);
-    const size_t hop_bytes = ((size_t)maxp + 15) & ~size_t(15);
     const size_t qcap = 2 * (size_t)maxp;
-    const size_t per_block = seen_words * 4 + hop_bytes + qcap * 4;
+    const size_t per_block = 2 * seen_words * 4 + qcap * 4;   // claim bitmap, rank words, queue
     int occ = 0;
     const size_t kg_smem = (size_t)KG_SORT_CAP * 5 + (2 * (size_t)KG_BUCKETS + 8) * 4;
     DMG_CUDA(cudaFuncSetAttribute(khop_global_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kg_smem));
     DMG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, khop_global_kernel, KG_THREADS, kg_smem));
     uint64_t grid = std::min<uint64_t>(nq, (uint64_t)e->sm_count * std::max(occ, 1));
+    // every CTA hits its claim bitmap and rank words at random: keep those of all resident CTAs
+    // inside ~3/4 of L2 (1M-vertex project on B200: 372 CTAs run 7.1 ms where 888 run 11 ms)
+    const uint64_t l2_fit = (uint64_t)e->l2_bytes * 3 / 4 / (2 * seen_words * 4);
+    grid = std::min<uint64_t>(grid, std::max<uint64_t>(l2_fit, (uint64_t)e->sm_count));
     grid = std::max<uint64_t>(1, std::min<uint64_t>(grid, e->scratch_budget / per_block));
     DMG_TRY(c->scratch.reserve(grid * per_block));
     uint32_t* sc_seen = c->scratch.as<uint32_t>();
-    uint8_t* sc_hop = reinterpret_cast<uint8_t*>(sc_seen + grid * seen_words);
-    uint32_t* sc_queue = reinterpret_cast<uint32_t*>(sc_hop + grid * hop_bytes);
+    uint32_t* sc_rank = sc_seen + grid * seen_words;
+    uint32_t* sc_queue = sc_rank + grid * seen_words;
     DMG_CUDA(cudaMemsetAsync(sc_seen, 0, grid * seen_words * 4, c->stream));
     // rows are first written in cursor order into temporaries of the caller's capacity
     DMG_TRY(c->tmp0.reserve(nq * 4));
@@ -963,8 +976,8 @@ static int32_t run_khop(CallCtx* c, dmg_graph* g, int mode, int k, int exclude, 
     a.tmp_hop = c->tmp3.as<uint8_t>();
     {
       LaunchScope ls(c, K_KHOP_GLOBAL);
-      khop_global_kernel<<<(unsigned)grid, KG_THREADS, kg_smem, c->stream>>>(a, sc_seen, sc_hop, sc_queue, seen_words,
-                                                                           hop_bytes, qcap);
+      khop_global_kernel<<<(unsigned)grid, KG_THREADS, kg_smem, c->stream>>>(a, sc_seen, sc_rank, sc_queue, seen_words,
+                                                                           qcap);
     }
     const uint64_t scan_tiles = (nq + SC_THREADS * SC_ITEMS - 1) / (SC_THREADS * SC_ITEMS);
     DMG_TRY(c->status.reserve(scan_tiles * sizeof(uint64_t)));
@@ -976,8 +989,9 @@ static int32_t run_khop(CallCtx* c, dmg_graph* g, int mode, int k, int exclude, 
     }
     if (cap) {
       LaunchScope ls(c, K_KHOP_EMIT);
-      khop_gather_kernel<<<(unsigned)std::min<uint64_t>((nq + 7) / 8, (uint64_t)e->sm_count * 16), 256, 0, c->stream>>>(
-          nq, a.tmp_start, a.out_off, a.tmp_ids, a.tmp_hop, a.out_ids, a.out_hop, cap);
+      // the row total is only known on the device: one resident wave, warps stride over the output
+      khop_gather_kernel<<<(unsigned)e->sm_count * 8, 256, 0, c->stream>>>(nq, a.tmp_start, a.out_off, a.tmp_ids,
+                                                                         a.tmp_hop, a.out_ids, a.out_hop, cap);
     }
   }
   DMG_CUDA(cudaGetLastError());
