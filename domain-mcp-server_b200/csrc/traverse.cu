@@ -272,10 +272,17 @@ __global__ void __launch_bounds__(THREADS, DMG_KS_MINB) khop_small_kernel(const 
             }
             reads += (pend - pbeg - lane + 31u) >> 5;
             uint2 row = s_row[r];   // stays in registers while the lane's positions stay inside the row
-            for (uint32_t p = pbeg + lane; p < pend; p += 32) {
+            for (uint32_t p = pbeg + lane; p < pend; p += 64) {   // two entries in flight per lane
               while (row.x <= p) row = s_row[++r];
-              const uint32_t v = fidx[row.y + p] - lo;
-              if (hop8[v] == 0) hop8[v] = (uint8_t)lvl;   // same value from every racer
+              const uint32_t i0 = fidx[row.y + p];
+              const uint32_t p1 = p + 32;
+              if (p1 < pend) {
+                while (row.x <= p1) row = s_row[++r];
+                const uint32_t v1 = fidx[row.y + p1] - lo;
+                if (hop8[v1] == 0) hop8[v1] = (uint8_t)lvl;
+              }
+              const uint32_t v0 = i0 - lo;
+              if (hop8[v0] == 0) hop8[v0] = (uint8_t)lvl;   // same value from every racer
             }
           }
           __syncthreads();   // s_row is rewritten by the next chunk
