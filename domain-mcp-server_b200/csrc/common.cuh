@@ -74,6 +74,7 @@ enum KernelId : int {
   K_SEARCH_SCAN,
   K_SEARCH_FIRST,
   K_SEARCH_EMIT,
+  K_KHOP_WINDOWS,
   K_MISC,
   K_COUNT
 };

@@ -66,6 +66,21 @@ __device__ __forceinline__ void find_window(const KhopArgs& a, uint32_t qb, uint
   }
 }
 
+// (lo, wn) of every query of [q_begin, q_end), one thread per query, ahead of khop_small: the
+// bisection over part_off is a chain of dependent loads that would otherwise sit at the head of
+// every query with 127 threads of its CTA waiting for it.
+__global__ void __launch_bounds__(256) khop_windows_kernel(const KhopArgs a) {
+  const unsigned long long q = a.q_begin + blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x;
+  if (q >= a.q_end) return;
+  uint32_t lo, hi;
+  find_window(a, a.q_off[q], a.q_off[q + 1], &lo, &hi);
+  reinterpret_cast<uint2*>(a.qwin)[q] = make_uint2(lo, hi - lo);
+}
+static inline void launch_windows(const KhopArgs& a, cudaStream_t stream) {
+  const unsigned long long n = a.q_end - a.q_begin;
+  if (n) khop_windows_kernel<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>(a);
+}
+
 // ---------------------------------------------------------------------------------------------
 // khop_small: one CTA per query, everything about the query lives in shared memory.
 // Used when every project has <= 8192 vertices (BASELINE config 2: 2000-vertex projects).
@@ -138,7 +153,7 @@ __global__ void __launch_bounds__(THREADS, DMG_KS_MINB) khop_small_kernel(const 
   uint32_t* const srcb = reinterpret_cast<uint32_t*>(smem + WC);          // WC/8 bytes
   uint16_t* const list = reinterpret_cast<uint16_t*>(smem + WC + WC / 8); // WC u16: frontier or unseen list
   __shared__ unsigned long long s_q;
-  __shared__ uint32_t s_lo, s_hi, s_n, s_cnt;
+  __shared__ uint32_t s_n, s_cnt;
   __shared__ uint32_t s_wsum[THREADS / 32 + 1];
   __shared__ uint32_t s_red[3][THREADS / 32];
   __shared__ uint2 s_row[THREADS];   // flattened frontier rows of a chunk: (end position, idx offset - start position)
@@ -151,27 +166,32 @@ __global__ void __launch_bounds__(THREADS, DMG_KS_MINB) khop_small_kernel(const 
   const uint32_t* __restrict__ fidx = a.mode == DMG_BOTH ? a.und_idx : (a.mode == DMG_OUT ? a.out_idx : a.in_idx);
   const uint32_t* __restrict__ rptr = a.mode == DMG_BOTH ? a.und_ptr : (a.mode == DMG_OUT ? a.in_ptr : a.out_ptr);
   const uint32_t* __restrict__ ridx = a.mode == DMG_BOTH ? a.und_idx : (a.mode == DMG_OUT ? a.in_idx : a.out_idx);
-  unsigned long long te = 0, rows = 0, reads = 0;
+  // statistics live in shared memory (thread 0 / one atomic per warp and query): registers are
+  // what limits this kernel to 16 CTAs per SM
+  __shared__ unsigned long long s_te, s_rows, s_reads;
+  if (tid == 0) s_te = s_rows = s_reads = 0;
+  // The ticket of the NEXT query is claimed while the current one is processed.  Tickets are
+  // the low word of ctr->ticket (zeroed per launch; a launch covers far fewer than 2^32 queries).
+  uint32_t next = 0;
+  if (tid == 0) next = atomicAdd(reinterpret_cast<unsigned int*>(&a.ctr->ticket), 1u);
 
   while (true) {
-    if (tid == 0) s_q = a.q_begin + atomicAdd(&a.ctr->ticket, 1ull);
-    __syncthreads();
-    const unsigned long long q = s_q;
-    if (q >= a.q_end) break;
-    const uint32_t qb = a.q_off[q], qe = a.q_off[q + 1];
     if (tid == 0) {
-      uint32_t lo, hi;
-      find_window(a, qb, qe, &lo, &hi);
-      s_lo = lo;
-      s_hi = hi;
+      s_q = a.q_begin + next;
       s_n = 0;
       s_cnt = 0;
     }
     __syncthreads();
-    const uint32_t lo = s_lo, hi = s_hi, wn = hi - lo;
-    const uint32_t nw4 = (wn + 3) >> 2, nw32 = (wn + 31) >> 5;
-    for (uint32_t i = tid; i < nw4; i += THREADS) hop32[i] = 0;
-    for (uint32_t i = tid; i < nw32; i += THREADS) srcb[i] = 0;
+    const unsigned long long q = s_q;
+    if (q >= a.q_end) break;
+    if (tid == 0) next = atomicAdd(reinterpret_cast<unsigned int*>(&a.ctr->ticket), 1u);
+    uint32_t reads = 0;
+    const uint2 win = reinterpret_cast<const uint2*>(a.qwin)[q];   // written by khop_windows_kernel
+    const uint32_t qb = a.q_off[q], qe = a.q_off[q + 1];
+    // hop bytes and source bitmap are contiguous: clear all of both while those loads are in flight
+    for (uint32_t i = tid; i < (WC + WC / 8) / 16; i += THREADS) reinterpret_cast<uint4*>(smem)[i] = make_uint4(0u, 0u, 0u, 0u);
+    const uint32_t lo = win.x, wn = win.y, hi = lo + wn;
+    const uint32_t nw4 = (wn + 3) >> 2;
     __syncthreads();
     // L0: distinct sources inside the project -> list
     for (uint32_t i = qb + tid; i < qe; i += THREADS) {
@@ -233,8 +253,8 @@ __global__ void __launch_bounds__(THREADS, DMG_KS_MINB) khop_small_kernel(const 
       __syncthreads();   // s_red may be rewritten by the next level; s_n reset is visible
       if (nf == 0) break;
       if (tid == 0) {
-        te += mf;
-        rows += nf;
+        s_te += mf;
+        s_rows += nf;
       }
       const bool bottom_up = mf > BU_ALPHA * nun;
 
@@ -357,23 +377,20 @@ __global__ void __launch_bounds__(THREADS, DMG_KS_MINB) khop_small_kernel(const 
       cnt += __popc(hop_bytes_member(x));
     }
     cnt = warp_sum_u32(cnt);
-    if (lane == 0 && cnt) atomicAdd(&s_cnt, cnt);
+    reads = warp_sum_u32(reads);
+    if (lane == 0) {
+      if (cnt) atomicAdd(&s_cnt, cnt);
+      if (reads) atomicAdd(&s_reads, (unsigned long long)reads);
+    }
     __syncthreads();
-    if (tid == 0) {
-      a.counts[q] = s_cnt;
-      a.qwin[2 * q] = lo;
-      a.qwin[2 * q + 1] = wn;
-    }
+    if (tid == 0) a.counts[q] = s_cnt;
   }
-  te = warp_sum_u64(te);
-  rows = warp_sum_u64(rows);
-  reads = warp_sum_u64(reads);
-  if (lane == 0) {
-    if (rows) {
-      atomicAdd(&a.ctr->edges, te);
-      atomicAdd(&a.ctr->rows, rows);
+  if (tid == 0) {   // the barrier that ended the loop follows every update of the three tallies
+    if (s_rows) {
+      atomicAdd(&a.ctr->edges, s_te);
+      atomicAdd(&a.ctr->rows, s_rows);
     }
-    if (reads) atomicAdd(&a.ctr->aux[0], reads);
+    if (s_reads) atomicAdd(&a.ctr->aux[0], s_reads);
   }
 }
 
@@ -933,6 +950,10 @@ static int32_t run_khop(CallCtx* c, dmg_graph* g, int mode, int k, int exclude, 
       DMG_CUDA(cudaMemsetAsync(c->status.p, 0, scan_tiles * sizeof(uint64_t), c->stream));
       const uint64_t grid = std::min<uint64_t>(q1 - q0, (uint64_t)e->sm_count * std::max(occ, 1));
       {
+        LaunchScope ls(c, K_KHOP_WINDOWS);
+        launch_windows(a, c->stream);
+      }
+      {
         LaunchScope ls(c, K_KHOP_SMALL);
         with_small_kernel(WC, [&](auto kern, uint32_t) -> int32_t {
           kern<<<(unsigned)grid, KS_THREADS, smem, c->stream>>>(a);
@@ -1148,6 +1169,10 @@ int32_t dmg_neighbors_batch_rows(dmg_graph* g, int32_t mode, int32_t k, int32_t 
     DMG_CUDA(cudaMemsetAsync(a.stage, 0, (q1 - q0) * WC, c->stream));   // bytes past a project's end read 0
     const uint64_t grid = std::min<uint64_t>(q1 - q0, (uint64_t)e->sm_count * std::max(occ, 1));
     {
+      LaunchScope ls(c, K_KHOP_WINDOWS);
+      launch_windows(a, c->stream);
+    }
+    {
       LaunchScope ls(c, K_KHOP_SMALL);
       with_small_kernel(WC, [&](auto kern, uint32_t) -> int32_t {
         kern<<<(unsigned)grid, KS_THREADS, smem, c->stream>>>(a);
@@ -1271,6 +1296,7 @@ int32_t dmg_neighbors_batch_dev_static(dmg_graph* g, int32_t mode, int32_t k, in
     return DMG_OK;
   }));
   const uint64_t grid = std::min<uint64_t>(nq, (uint64_t)e->sm_count * std::max(occ, 1));
+  launch_windows(a, 0);
   with_small_kernel(WC, [&](auto kern, uint32_t) -> int32_t {
     kern<<<(unsigned)grid, KS_THREADS, smem, 0>>>(a);
     return DMG_OK;
