@@ -84,21 +84,26 @@ static inline void launch_windows(const KhopArgs& a, cudaStream_t stream) {
 // ---------------------------------------------------------------------------------------------
 // khop_small: one CTA per query, everything about the query lives in shared memory.
 // Used when every project has <= 8192 vertices (BASELINE config 2: 2000-vertex projects).
-//   hop8[win]     u8   0 = unseen, 255 = excluded source, else hop
-//   seen[win/32]  u32  claim bitmap of the top-down levels (atomicOr decides who enqueues)
-//   srcb[win/32]  u32  the distinct sources (level-0 frontier membership)
-//   queue[2*win]  u16  frontier queue, ids relative to the project base; level i is the segment
-//                      level i-1 appended (ballot/popc warp-aggregated append)
-//   ulist[win]    u16  unseen vertices of a bottom-up level
+//   hop8[WC]      u8   0 = unseen, 255 = excluded source, else hop; the only per-vertex state
+//                      (a level's frontier is "hop == level - 1", found again by a SWAR sweep)
+//   srcb[WC/32]   u32  the distinct sources (level-0 frontier membership for bottom-up level 1)
+//   list[WC]      u16  ids relative to the project base: the frontier of a top-down level or the
+//                      unseen vertices of a bottom-up level (one shared atomic per warp sweep step)
 // Level step, chosen per level (direction-optimising BFS; the result is the same set):
 //   top-down   the frontier's rows are flattened: a block scan of the row lengths gives every
 //              adjacency entry a position, each warp takes a contiguous quarter of the positions
-//              and walks it 32 at a time, so lanes stay busy whatever the degree distribution
+//              and walks it 64 at a time with the current row's (end, offset) record in
+//              registers, so lanes stay busy whatever the degree distribution
 //   bottom-up  when the frontier's rows hold many more entries than there are unseen vertices
-//              (m_f > BU_ALPHA * n_unseen, BU_ALPHA = 12) each unseen vertex looks for ONE frontier member in its
-//              reverse row instead: 8 lanes per vertex, 32-byte chunks, stop at the first hit
+//              (m_f > BU_ALPHA * n_unseen, BU_ALPHA = 12) each unseen vertex looks for ONE
+//              frontier member in its reverse row instead: 8 lanes per vertex, 32-byte chunks,
+//              stop at the first hit (one lane per vertex when most vertices are frontier)
 // The finished hop8 array is copied to a staging row in global memory; khop_emit_kernel
 // compacts the staging rows into the packed, id-ordered output after a scan of the row sizes.
+// What bounds it (ncu, config 2): ~80% issue utilisation at 16 CTAs/SM with the 25 MB CSR in L2;
+// the kernel answers to instruction count AND to the length of the per-query dependency chain
+// (barriers, dependent loads) - folding the frontier-list build into the degree pass removed
+// instructions but added a barrier to the chain and ran 10% slower.
 // ---------------------------------------------------------------------------------------------
 // tuning knobs of khop_small_kernel (compile time; variants are built with -D for experiments)
 #ifndef DMG_KS_THREADS
