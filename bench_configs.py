@@ -4,6 +4,7 @@ One JSON line per run; results are kept under profiles/.
 
   python bench_configs.py c3 [--names N] [--queries Q]     search_project scan (S1)
   python bench_configs.py c4 [--vertices V] [--edges E]    adjacency rows + directed k-hop on one big graph
+  python bench_configs.py c4mix [--ops N]                  the SURVEY 8d config-4 DSL mix in one dmg_query_batch
   python bench_configs.py c5 [--vertices V] [--edges E]    closure levels + exact analysisOrder
 
 Per-kernel times are CUDA events on the library's launch stream (dmg_profile_*); e2e is the
@@ -147,6 +148,118 @@ def run_c4(args):
     eng.close()
 
 
+def run_c4mix(args):
+    """BASELINE config 4 as SURVEY.md 8d states it: one 1 M / 30 M graph, a batch of resolved DSL
+    queries in the stated mix (40 % dependencies, 20 % dependents, 15 % overview, 10 % k-hop OUT
+    k in {2,3,4}, 5 % simple-name resolution, 5 % ?check, 3 % entrypoints, 2 % endpoints) through ONE
+    dmg_query_batch call with host buffers."""
+    from oracle import oracle as ora
+    eng = dmgraph.Engine(0)
+    t0 = time.perf_counter()
+    sg = synth.big_graph(args.vertices, args.edges, cap=500, entry_frac=0.01, seed=synth.SEED_C4, with_names=True)
+    V = sg.n_vertices
+    off, arena = synth.pack_names(sg.names)
+    low = np.frombuffer(bytes(arena).lower(), dtype=np.uint8).copy()
+    # 10 methods per vertex, 8 lower-case bytes each: 4-letter verb + 4 hex digits of (7 v + j)
+    verbs = np.frombuffer(b"findsavelistloadsendreadpushpullopenstop", dtype=np.uint8).reshape(10, 4)
+    num = ((np.arange(V, dtype=np.int64)[:, None] * 7 + np.arange(10)[None, :]) & 0xFFFF)
+    hexd = np.frombuffer(b"0123456789abcdef", dtype=np.uint8)
+    digits = hexd[(num[:, :, None] >> np.array([12, 8, 4, 0])[None, None, :]) & 15]
+    mbytes = np.concatenate([np.broadcast_to(verbs[None, :, :], (V, 10, 4)), digits], axis=2).reshape(-1)
+    gen_s = time.perf_counter() - t0
+    t0 = time.perf_counter()
+    g = dmgraph.Graph(eng, V, sg.src, sg.dst, sg.entry, name_off=off, name_bytes=arena, lower_bytes=low)
+    g.set_methods_packed(np.arange(V + 1, dtype=np.uint32) * 10, np.arange(10 * V + 1, dtype=np.uint32) * 8, mbytes)
+    rng = np.random.Generator(np.random.PCG64(synth.SEED_C4 + 2))
+    ctrl = rng.random(V) < 0.01                                  # 1 % controllers: all their methods are endpoints
+    g.set_method_flags(np.repeat(ctrl.astype(np.uint8), 10))
+    upload_s = time.perf_counter() - t0
+
+    def make_ops(n):
+        r = np.random.Generator(np.random.PCG64(synth.SEED_C4 + 3))
+        u = r.random(n)
+        edges_ = np.cumsum([0.40, 0.20, 0.15, 0.10, 0.05, 0.05, 0.03, 0.02])
+        kind = np.searchsorted(edges_, u, side="right").clip(0, 7)
+        opcode = np.array([dmgraph.OP_DEPENDENCIES, dmgraph.OP_DEPENDENTS, dmgraph.OP_OVERVIEW, dmgraph.OP_KHOP,
+                           dmgraph.OP_RESOLVE_NAME, dmgraph.OP_METHOD, dmgraph.OP_ENTRYPOINTS, dmgraph.OP_ENDPOINTS],
+                          np.uint32)[kind]
+        ops = np.zeros(n, dmgraph.Graph.QUERY_OP_DTYPE)
+        ops["opcode"] = opcode
+        ops["vertex"] = r.integers(0, V, n)
+        ops["mode"] = dmgraph.OUT
+        ops["k"] = np.where(opcode == dmgraph.OP_KHOP, r.integers(2, 5, n), 1)
+        text = bytearray()
+        for i in np.flatnonzero((opcode == dmgraph.OP_RESOLVE_NAME) | (opcode == dmgraph.OP_METHOD)):
+            v = int(ops["vertex"][i])
+            if opcode[i] == dmgraph.OP_RESOLVE_NAME:
+                t = sg.names[v].rsplit(".", 1)[-1].lower().encode()
+            elif r.random() < 0.8:
+                j = int(r.integers(0, 10))
+                t = bytes(mbytes[(v * 10 + j) * 8:(v * 10 + j + 1) * 8])
+            else:
+                t = b"nosuchmethod"
+            ops["text_begin"][i] = len(text)
+            text += t
+            ops["text_end"][i] = len(text)
+        return ops, np.frombuffer(bytes(text) + b"\0", dtype=np.uint8).copy(), kind
+
+    n = args.ops
+    while True:
+        ops, text, kind = make_ops(n)
+        t0 = time.perf_counter()
+        need = g.query_batch_packed(ops, text)
+        size_s = time.perf_counter() - t0
+        if need <= args.max_results or n <= 1024:
+            break
+        n //= 2
+    off_o = np.zeros(n + 1, np.uint64)
+    ids = np.zeros(max(need, 1), np.uint32)
+    aux = np.zeros(max(need, 1), np.uint8)
+    eng.profile(True)
+    ts = []
+    for it in range(1 + args.steps):
+        eng.profile_reset()
+        t0 = time.perf_counter()
+        got = g.query_batch_packed(ops, text, out=(off_o, ids, aux))
+        ts.append(time.perf_counter() - t0)
+    assert got == need
+    kt = kernels(eng)
+    kms = sum(v["ms_total"] for v in kt.values())
+    # spot check against the csr restatement
+    o = ora.CsrOracle(V, sg.src, sg.dst, sg.entry)
+    checked = 0
+    for i in np.random.Generator(np.random.PCG64(1)).choice(n, min(n, 300), replace=False):
+        a, b = int(off_o[i]), int(off_o[i + 1])
+        v, op = int(ops["vertex"][i]), int(ops["opcode"][i])
+        if op == dmgraph.OP_DEPENDENCIES:
+            assert ids[a:b].tolist() == o.adjacency_batch(0, [v])[1].tolist()
+        elif op == dmgraph.OP_DEPENDENTS:
+            assert ids[a:b].tolist() == o.adjacency_batch(1, [v])[1].tolist()
+        elif op == dmgraph.OP_KHOP:
+            _o, wi, wh, _te = o.khop_batch(0, int(ops["k"][i]), 0, [0, 1], [v])
+            assert ids[a:b].tolist() == wi.tolist() and aux[a:b].tolist() == wh.tolist()
+        elif op == dmgraph.OP_ENTRYPOINTS:
+            assert ids[a:b].tolist() == o.entry_points().tolist()
+        else:
+            continue
+        checked += 1
+    names_k = ["dependencies", "dependents", "overview", "khop", "resolve_name", "method", "entrypoints", "endpoints"]
+    line = {"config": "c4mix", "workload": "one graph %d V / %d E, %d DSL ops in the SURVEY 8d mix, one dmg_query_batch call "
+                                           "(host buffers, pageable)" % (V, g.info["n_edges"], n),
+            "ops_requested": args.ops, "ops_run": n, "results": int(need),
+            "op_counts": {names_k[k]: int((kind == k).sum()) for k in range(8)},
+            "metric": "dsl_ops_per_sec", "unit": "ops/s",
+            "e2e": {"value": n / float(np.median(ts[1:])), "ms_per_batch": 1e3 * float(np.median(ts[1:])),
+                    "sizing_call_ms": 1e3 * size_s, "result_bytes": int(5 * need + 8 * (n + 1))},
+            "kernel_ms_per_batch": kms, "kernels": kt, "rows_checked_against_oracle": checked,
+            "note": "the executor groups ops by kind, runs each group through the batch primitives and lays the rows "
+                    "out in op order on the host; e2e minus kernel time is host grouping, PCIe and that layout",
+            "generate_s": gen_s, "upload_s": upload_s}
+    print(json.dumps(line), flush=True)
+    g.release()
+    eng.close()
+
+
 def run_c5(args):
     from oracle import oracle as ora
     eng = dmgraph.Engine(0)
@@ -194,15 +307,18 @@ def run_c5(args):
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("config", choices=["c3", "c4", "c5"])
+    ap.add_argument("config", choices=["c3", "c4", "c4mix", "c5"])
     ap.add_argument("--names", type=int, default=10_000_000)
     ap.add_argument("--queries", type=int, default=16384)
     ap.add_argument("--vertices", type=int, default=1_000_000)
     ap.add_argument("--edges", type=int, default=30_000_000)
+    ap.add_argument("--ops", type=int, default=262_144)
+    ap.add_argument("--max-results", type=int, default=600_000_000,
+                    help="c4mix: halve the batch until the packed result has at most this many entries")
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=2)
     args = ap.parse_args()
-    {"c3": run_c3, "c4": run_c4, "c5": run_c5}[args.config](args)
+    {"c3": run_c3, "c4": run_c4, "c4mix": run_c4mix, "c5": run_c5}[args.config](args)
 
 
 if __name__ == "__main__":

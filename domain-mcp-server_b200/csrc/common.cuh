@@ -184,7 +184,8 @@ struct dmg_graph {
   uint8_t* d_lower = nullptr;      // pre-lowered name arena (+32 B zero pad)
   uint8_t* d_names = nullptr;      // original name arena (exact identifier lookups are case sensitive)
   uint32_t* d_full_tbl = nullptr;  // open addressing: hash(identifier) -> vertex id, 0xFFFFFFFF = empty
-  uint32_t* d_simple_tbl = nullptr;  // hash(lower-cased simple name) -> vertex id
+  uint32_t* d_simple_tbl = nullptr;  // hash(lower-cased simple name) -> FIRST vertex of each project with that simple name
+  uint32_t* d_simple_next = nullptr; // next vertex (ascending id) of the same project with the same simple name
   uint32_t tbl_mask = 0;
   uint32_t* d_method_off = nullptr;  // [V+1] optional method catalog (names only)
   uint32_t* d_mname_off = nullptr;   // [M+1]

@@ -155,7 +155,7 @@ static void free_graph(dmg_graph* g) {
   cudaSetDevice(g->eng->device);
   for (void* p : {(void*)g->d_out_ptr, (void*)g->d_out_idx, (void*)g->d_in_ptr, (void*)g->d_in_idx,
                   (void*)g->d_und_ptr, (void*)g->d_und_idx, (void*)g->d_part_off, (void*)g->d_entry, (void*)g->d_entry_bits, (void*)g->d_name_off,
-                  (void*)g->d_lower, (void*)g->d_names, (void*)g->d_full_tbl, (void*)g->d_simple_tbl, (void*)g->d_method_off, (void*)g->d_mname_off, (void*)g->d_mname_lower})
+                  (void*)g->d_lower, (void*)g->d_names, (void*)g->d_full_tbl, (void*)g->d_simple_tbl, (void*)g->d_simple_next, (void*)g->d_method_off, (void*)g->d_mname_off, (void*)g->d_mname_lower})
     if (p) cudaFree(p);
   delete g;
 }
@@ -232,12 +232,19 @@ static int32_t finish_upload(dmg_engine* e, dmg_graph* g, uint32_t V, const std:
       for (uint64_t i = 0; i < nbytes; ++i)
         if (low[i] >= 'A' && low[i] <= 'Z') low[i] += 32;   // ASCII fold only
     // name -> id tables: exact identifier (nodes.containsKey, case
-    // sensitive) and lower-cased simple name (GQS:434-446); linear probing, load <= 0.5
+    // sensitive) and lower-cased simple name (GQS:434-446); linear probing, load <= 0.5.
+    // Simple names repeat (every TS module id ends in its kind, Go ids share "com/..." tails):
+    // the table holds only the FIRST vertex of each (project, simple name); later ones hang off
+    // it in ascending id order through simple_next, so neither the build nor a lookup walks a
+    // probe run of thousands of equal names.
     uint32_t size = 16;
     while (size < 2ull * V + 1) size <<= 1;
     std::vector<uint32_t> full_tbl(size, 0xFFFFFFFFu), simple_tbl(size, 0xFFFFFFFFu);
+    std::vector<uint32_t> simple_next(std::max<uint32_t>(V, 1), 0xFFFFFFFFu);
+    std::vector<uint32_t> slot_hash(size, 0), tail(V), sb_rel(V);
     std::vector<uint8_t> orig(nbytes + 32, 0);
     if (nbytes) memcpy(orig.data(), d->name_bytes, nbytes);
+    uint32_t part = 0;
     for (uint32_t v = 0; v < V; ++v) {
       const uint64_t b = d->name_off[v], e2 = d->name_off[v + 1];
       uint32_t h = name_hash(orig.data() + b, (uint32_t)(e2 - b)) & (size - 1);
@@ -249,16 +256,35 @@ static int32_t finish_upload(dmg_engine* e, dmg_graph* g, uint32_t V, const std:
           sb = i;
           break;
         }
-      h = name_hash(low.data() + sb, (uint32_t)(e2 - sb)) & (size - 1);
-      while (simple_tbl[h] != 0xFFFFFFFFu) h = (h + 1) & (size - 1);
-      simple_tbl[h] = v;
+      sb_rel[v] = (uint32_t)(sb - b);
+      while (part + 1 < g->h_part_off.size() - 1 && v >= g->h_part_off[part + 1]) ++part;
+      const uint32_t part_lo = g->h_part_off[part], len = (uint32_t)(e2 - sb);
+      const uint32_t hv = name_hash(low.data() + sb, len);
+      bool chained = false;
+      for (h = hv & (size - 1); simple_tbl[h] != 0xFFFFFFFFu; h = (h + 1) & (size - 1)) {
+        const uint32_t u = simple_tbl[h];
+        if (slot_hash[h] != hv || u < part_lo) continue;
+        const uint64_t ub = d->name_off[u] + sb_rel[u], ue = d->name_off[u + 1];
+        if (ue - ub == len && memcmp(low.data() + ub, low.data() + sb, len) == 0) {
+          simple_next[tail[u]] = v;
+          tail[u] = v;
+          chained = true;
+          break;
+        }
+      }
+      if (!chained) {
+        simple_tbl[h] = v;
+        slot_hash[h] = hv;
+        tail[v] = v;
+      }
     }
     g->tbl_mask = size - 1;
     if ((st = upload(&g->d_name_off, d->name_off, (size_t)V + 1, &bytes)) != DMG_OK ||
         (st = upload(&g->d_lower, low.data(), low.size(), &bytes)) != DMG_OK ||
         (st = upload(&g->d_names, orig.data(), orig.size(), &bytes)) != DMG_OK ||
         (st = upload(&g->d_full_tbl, full_tbl.data(), full_tbl.size(), &bytes)) != DMG_OK ||
-        (st = upload(&g->d_simple_tbl, simple_tbl.data(), simple_tbl.size(), &bytes)) != DMG_OK) {
+        (st = upload(&g->d_simple_tbl, simple_tbl.data(), simple_tbl.size(), &bytes)) != DMG_OK ||
+        (st = upload(&g->d_simple_next, simple_next.data(), simple_next.size(), &bytes)) != DMG_OK) {
       free_graph(g);
       return st;
     }

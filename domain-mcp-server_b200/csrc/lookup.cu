@@ -8,7 +8,9 @@ namespace dmg {
 __global__ void __launch_bounds__(256) lookup_kernel(const unsigned long long* __restrict__ name_off,
                                                      const uint8_t* __restrict__ names,
                                                      const uint8_t* __restrict__ lower,
-                                                     const uint32_t* __restrict__ tbl, uint32_t mask, int kind,
+                                                     const uint32_t* __restrict__ tbl, uint32_t mask,
+                                                     const uint32_t* __restrict__ simple_next,
+                                                     const uint32_t* __restrict__ part_off, uint32_t n_parts, int kind,
                                                      uint32_t v_lo, uint32_t v_hi, unsigned long long n,
                                                      const uint32_t* __restrict__ t_off,
                                                      const uint8_t* __restrict__ text, uint32_t* out) {
@@ -20,7 +22,8 @@ __global__ void __launch_bounds__(256) lookup_kernel(const unsigned long long* _
   for (uint32_t h = name_hash(q, qn) & mask;; h = (h + 1) & mask) {
     const uint32_t v = tbl[h];
     if (v == 0xFFFFFFFFu) break;
-    if (v < v_lo || v >= v_hi || v >= best) continue;
+    // the simple table holds chain heads: everything chained behind v has a larger id
+    if (v >= v_hi || v >= best || (kind == DMG_LOOKUP_EXACT && v < v_lo)) continue;
     const unsigned long long b = name_off[v], e = name_off[v + 1];
     unsigned long long s = b;
     const uint8_t* arena = names;
@@ -35,10 +38,22 @@ __global__ void __launch_bounds__(256) lookup_kernel(const unsigned long long* _
     if (e - s != qn) continue;
     uint32_t j = 0;
     while (j < qn && arena[s + j] == q[j]) ++j;
-    if (j == qn) {
+    if (j != qn) continue;
+    if (v >= v_lo) {
       best = v;
       if (kind == DMG_LOOKUP_EXACT) break;   // identifiers are unique inside a project
+      continue;
     }
+    // SIMPLE_FIRST, head before the range: its project may still reach into the range
+    uint32_t l = 0, r = n_parts;
+    while (r - l > 1) {
+      const uint32_t m = (l + r) >> 1;
+      if (part_off[m] <= v) l = m; else r = m;
+    }
+    if (part_off[l + 1] <= v_lo) continue;
+    uint32_t w = simple_next[v];
+    while (w != 0xFFFFFFFFu && w < v_lo) w = simple_next[w];
+    if (w < v_hi && w < best) best = w;   // 0xFFFFFFFF fails both tests
   }
   out[i] = best;
 }
@@ -50,8 +65,8 @@ int32_t run_lookup(CallCtx* c, dmg_graph* g, int kind, uint32_t v_lo, uint32_t v
   LaunchScope ls(c, K_SEARCH_FIRST);
   lookup_kernel<<<(unsigned)((n + 255) / 256), 256, 0, c->stream>>>(
       reinterpret_cast<const unsigned long long*>(g->d_name_off), g->d_names, g->d_lower,
-      kind == DMG_LOOKUP_EXACT ? g->d_full_tbl : g->d_simple_tbl, g->tbl_mask, kind, v_lo, v_hi, n, d_t_off, d_text,
-      d_out);
+      kind == DMG_LOOKUP_EXACT ? g->d_full_tbl : g->d_simple_tbl, g->tbl_mask, g->d_simple_next, g->d_part_off,
+      g->info.n_parts, kind, v_lo, v_hi, n, d_t_off, d_text, d_out);
   DMG_CUDA(cudaGetLastError());
   return DMG_OK;
 }

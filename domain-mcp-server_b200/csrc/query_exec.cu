@@ -3,6 +3,8 @@
 // batch on the device primitives (adjacency rows, k-hop, name scans, method lookup), and the rows
 // are put back in operation order.
 #include <algorithm>
+#include <cstring>
+#include <memory>
 #include <vector>
 
 #include "common.cuh"
@@ -99,10 +101,9 @@ int32_t dmg_query_batch(dmg_graph* g, uint64_t n_ops, const dmg_query_op* ops, c
   out_off[0] = 0;
   if (!n_ops) return DMG_OK;
   // ---- group the operations ----------------------------------------------------------------
-  struct Row {
-    std::vector<uint32_t> ids;
-    std::vector<uint8_t> aux;
-  };
+  // group results are overwritten in full by the primitives: no zero fill of gigabytes
+  auto raw_u32 = [](uint64_t n) { return std::unique_ptr<uint32_t[]>(new uint32_t[std::max<uint64_t>(n, 1)]); };
+  auto raw_u8 = [](uint64_t n) { return std::unique_ptr<uint8_t[]>(new uint8_t[std::max<uint64_t>(n, 1)]); };
   std::vector<uint64_t> adj_out, adj_in, names, methods, entries, endpoints;
   struct KhopKey {
     uint32_t mode, k, excl;
@@ -144,21 +145,26 @@ int32_t dmg_query_batch(dmg_graph* g, uint64_t n_ops, const dmg_query_op* ops, c
     return DMG_EINVAL;
   }
   std::vector<uint64_t> cnt(n_ops, 0);
+  // a call without output buffers only sizes the result: the groups' rows are counted, not fetched
+  const bool sizing_only = !out_ids || !out_aux || cap == 0;
   // per-group results, kept until the rows are laid out in operation order
   std::vector<uint64_t> o_off, i_off, k_off_all;
-  std::vector<uint32_t> o_ids, i_ids;
+  std::unique_ptr<uint32_t[]> o_ids, i_ids;
   uint64_t nd = 0;
   int32_t st;
-  auto adjacency = [&](int dir, const std::vector<uint64_t>& who, std::vector<uint64_t>& off, std::vector<uint32_t>& ids) {
+  auto adjacency = [&](int dir, const std::vector<uint64_t>& who, std::vector<uint64_t>& off, std::unique_ptr<uint32_t[]>& ids) {
     if (who.empty()) return (int32_t)DMG_OK;
     std::vector<uint32_t> v(who.size());
     for (size_t j = 0; j < who.size(); ++j) v[j] = ops[who[j]].vertex;
     off.assign(who.size() + 1, 0);
     int32_t s2 = dmg_adjacency_batch(g, dir, who.size(), v.data(), off.data(), nullptr, 0, &nd);
     if (s2 != DMG_OK && s2 != DMG_ECAP) return s2;
-    ids.assign(std::max<uint64_t>(nd, 1), 0);
-    if (nd) s2 = dmg_adjacency_batch(g, dir, who.size(), v.data(), off.data(), ids.data(), nd, &nd);
-    else s2 = DMG_OK;
+    if (nd && !sizing_only) {
+      ids = raw_u32(nd);
+      s2 = dmg_adjacency_batch(g, dir, who.size(), v.data(), off.data(), ids.get(), nd, &nd);
+    } else {
+      s2 = DMG_OK;
+    }
     for (size_t j = 0; j < who.size(); ++j) cnt[who[j]] += off[j + 1] - off[j];
     return s2;
   };
@@ -169,8 +175,8 @@ int32_t dmg_query_batch(dmg_graph* g, uint64_t n_ops, const dmg_query_op* ops, c
   struct KGroup {
     size_t begin, end;
     std::vector<uint64_t> off;
-    std::vector<uint32_t> ids;
-    std::vector<uint8_t> hop;
+    std::unique_ptr<uint32_t[]> ids;
+    std::unique_ptr<uint8_t[]> hop;
   };
   std::vector<KGroup> kgroups;
   for (size_t a = 0; a < khops.size();) {
@@ -190,11 +196,11 @@ int32_t dmg_query_batch(dmg_graph* g, uint64_t n_ops, const dmg_query_op* ops, c
     const KhopKey& key = khops[a].first;
     st = dmg_neighbors_batch(g, key.mode, key.k, key.excl, m, qo.data(), qs.data(), kg.off.data(), nullptr, nullptr, 0, &nd);
     if (st != DMG_OK && st != DMG_ECAP) return st;
-    kg.ids.assign(std::max<uint64_t>(nd, 1), 0);
-    kg.hop.assign(std::max<uint64_t>(nd, 1), 0);
-    if (nd) {
-      st = dmg_neighbors_batch(g, key.mode, key.k, key.excl, m, qo.data(), qs.data(), kg.off.data(), kg.ids.data(),
-                               kg.hop.data(), nd, &nd);
+    if (nd && !sizing_only) {
+      kg.ids = raw_u32(nd);
+      kg.hop = raw_u8(nd);
+      st = dmg_neighbors_batch(g, key.mode, key.k, key.excl, m, qo.data(), qs.data(), kg.off.data(), kg.ids.get(),
+                               kg.hop.get(), nd, &nd);
       if (st != DMG_OK) return st;
     }
     for (size_t j = 0; j < m; ++j) cnt[khops[a + j].second] = kg.off[j + 1] - kg.off[j];
@@ -292,20 +298,20 @@ int32_t dmg_query_batch(dmg_graph* g, uint64_t n_ops, const dmg_query_op* ops, c
   }
   std::vector<uint64_t> cur(out_off, out_off + n_ops);
   auto put = [&](uint64_t op, const uint32_t* ids, uint64_t n, uint8_t aux, const uint8_t* auxv) {
+    if (!n) return;
     uint64_t& w = cur[op];
-    for (uint64_t j = 0; j < n; ++j) {
-      out_ids[w] = ids[j];
-      out_aux[w] = auxv ? auxv[j] : aux;
-      ++w;
-    }
+    std::memcpy(out_ids + w, ids, n * sizeof(uint32_t));
+    if (auxv) std::memcpy(out_aux + w, auxv, n);
+    else std::memset(out_aux + w, aux, n);
+    w += n;
   };
-  for (size_t j = 0; j < adj_out.size(); ++j) put(adj_out[j], o_ids.data() + o_off[j], o_off[j + 1] - o_off[j], 0, nullptr);
+  for (size_t j = 0; j < adj_out.size(); ++j) put(adj_out[j], o_ids.get() + o_off[j], o_off[j + 1] - o_off[j], 0, nullptr);
   for (size_t j = 0; j < adj_in.size(); ++j)
-    put(adj_in[j], i_ids.data() + i_off[j], i_off[j + 1] - i_off[j], ops[adj_in[j]].opcode == DMG_OP_OVERVIEW ? 1 : 0,
+    put(adj_in[j], i_ids.get() + i_off[j], i_off[j + 1] - i_off[j], ops[adj_in[j]].opcode == DMG_OP_OVERVIEW ? 1 : 0,
         nullptr);
   for (const KGroup& kg : kgroups)
     for (size_t j = 0; j + kg.begin < kg.end; ++j)
-      put(khops[kg.begin + j].second, kg.ids.data() + kg.off[j], kg.off[j + 1] - kg.off[j], 0, kg.hop.data() + kg.off[j]);
+      put(khops[kg.begin + j].second, kg.ids.get() + kg.off[j], kg.off[j + 1] - kg.off[j], 0, kg.hop.get() + kg.off[j]);
   for (size_t j = 0; j < names.size(); ++j)
     if (name_id[j] != 0xFFFFFFFFu) put(names[j], &name_id[j], 1, name_how[j], nullptr);
   for (size_t j = 0; j < methods.size(); ++j)

@@ -418,6 +418,14 @@ class Graph:
         lb = np.frombuffer(b"".join(enc) + b"\0", dtype=np.uint8).copy()
         _check(self.L.dmg_graph_set_methods(self.h, mo.ctypes.data, no.ctypes.data, lb.ctypes.data))
 
+    def set_methods_packed(self, method_off, name_off, lower_bytes):
+        """Array form of set_methods for large catalogs (u32 offsets, lower-cased bytes)."""
+        mo = np.ascontiguousarray(method_off, dtype=np.uint32)
+        no = np.ascontiguousarray(name_off, dtype=np.uint32)
+        lb = np.ascontiguousarray(lower_bytes, dtype=np.uint8)
+        assert mo.size == self.V + 1 and no.size == int(mo[-1]) + 1
+        _check(self.L.dmg_graph_set_methods(self.h, mo.ctypes.data, no.ctypes.data, lb.ctypes.data))
+
     def set_method_flags(self, flags):
         f = np.ascontiguousarray(flags, dtype=np.uint8)
         _check(self.L.dmg_graph_set_method_flags(self.h, f.ctypes.data if f.size else None))
@@ -447,6 +455,31 @@ class Graph:
                                       aux.ctypes.data, cap, C.byref(need)))
         return [(ids[int(off[i]):int(off[i + 1])].tolist(), aux[int(off[i]):int(off[i + 1])].tolist())
                 for i in range(n)]
+
+    QUERY_OP_DTYPE = np.dtype([("opcode", "<u4"), ("vertex", "<u4"), ("mode", "<u4"), ("k", "<u4"),
+                               ("exclude_sources", "<u4"), ("text_begin", "<u4"), ("text_end", "<u4"),
+                               ("reserved", "<u4")])
+
+    def query_batch_packed(self, ops, text, out=None):
+        """ops: structured array of QUERY_OP_DTYPE (== dmg_query_op), text: uint8 array.
+        out=None sizes the result (returns needed); out=(off u64[n+1], ids u32[cap], aux u8[cap])
+        runs the batch into those buffers and returns needed."""
+        ops = np.ascontiguousarray(ops, dtype=self.QUERY_OP_DTYPE)
+        tb = np.ascontiguousarray(text, dtype=np.uint8)
+        if tb.size == 0:
+            tb = np.zeros(1, np.uint8)
+        n = ops.size
+        need = C.c_uint64(0)
+        if out is None:
+            off = np.zeros(n + 1, np.uint64)
+            rc = self.L.dmg_query_batch(self.h, n, ops.ctypes.data, tb.ctypes.data, off.ctypes.data, None, None, 0,
+                                        C.byref(need))
+            _check(rc, allow=(ECAP,))
+            return need.value
+        off, ids, aux = out
+        _check(self.L.dmg_query_batch(self.h, n, ops.ctypes.data, tb.ctypes.data, off.ctypes.data, ids.ctypes.data,
+                                      aux.ctypes.data, ids.size, C.byref(need)))
+        return need.value
 
     # -- S1/S2 ---------------------------------------------------------------------------------
     def search_batch(self, kind, queries, v_lo=0, v_hi=None, cap=None):
