@@ -103,7 +103,9 @@ static inline void launch_windows(const KhopArgs& a, cudaStream_t stream) {
 // What bounds it (ncu, config 2): ~80% issue utilisation at 16 CTAs/SM with the 25 MB CSR in L2;
 // the kernel answers to instruction count AND to the length of the per-query dependency chain
 // (barriers, dependent loads) - folding the frontier-list build into the degree pass removed
-// instructions but added a barrier to the chain and ran 10% slower.
+// instructions but added a barrier to the chain and ran 10% slower; building the frontier list
+// and the unseen list in one sweep (one array filled from both ends) saved a sweep and a barrier
+// but appends ~1,800 unseen vertices per level that a top-down level never reads: also 10% slower.
 // ---------------------------------------------------------------------------------------------
 // tuning knobs of khop_small_kernel (compile time; variants are built with -D for experiments)
 #ifndef DMG_KS_THREADS

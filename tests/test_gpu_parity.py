@@ -637,6 +637,14 @@ def test_lookup_batch_exact_and_simple(engine):
     o, i1 = g.search_batch(dmgraph.SEARCH_SIMPLE_EQ_FIRST, [x.encode() for x in qs], 100, 4400)
     wo, wi = ora.search_batch(off, lowb, [x.encode() for x in qs], 1, 100, 4400)
     assert np.array_equal(o, wo) and np.array_equal(i1, wi)
+    # heavily repeated simple names (TS kinds) over ranges that cut into projects: the table keeps
+    # one head per (project, simple name) and walks a chain of later duplicates
+    hot = sorted({simple(n) for n in low if n.startswith("modules.")})[:6] + ["dup"]
+    for _ in range(40):
+        a, b = sorted(int(x) for x in rng.integers(0, 4501, 2))
+        got = g.lookup_batch(dmgraph.LOOKUP_SIMPLE_FIRST, [x.encode() for x in hot], a, b)
+        want = [next((i for i in range(a, b) if simple(low[i]) == x), 0xFFFFFFFF) for x in hot]
+        assert got.tolist() == want
     g.release()
 
 
