@@ -893,8 +893,11 @@ static int32_t run_khop(CallCtx* c, dmg_graph* g, int mode, int k, int exclude, 
                         const uint32_t* d_q_off, const uint32_t* d_q_src, uint64_t* d_out_off,
                         uint32_t* d_out_ids, uint8_t* d_out_hop, uint64_t cap) {
   Engine* e = c->eng;
-  DMG_TRY(c->status.reserve(nq * sizeof(uint64_t)));
-  DMG_CUDA(cudaMemsetAsync(c->status.p, 0, nq * sizeof(uint64_t), c->stream));
+  // scan_counts' look-back words for the whole batch (a staging-limited chunk needs fewer); zeroed
+  // here together with the counters, so the first chunk launches without further memsets
+  const uint64_t scan_tiles_all = (nq + SC_THREADS * SC_ITEMS - 1) / (SC_THREADS * SC_ITEMS);
+  DMG_TRY(c->status.reserve(scan_tiles_all * sizeof(uint64_t)));
+  DMG_CUDA(cudaMemsetAsync(c->status.p, 0, scan_tiles_all * sizeof(uint64_t), c->stream));
   DMG_TRY(reset_counters(c));
   KhopArgs a;
   a.out_ptr = g->d_out_ptr;
@@ -943,7 +946,6 @@ static int32_t run_khop(CallCtx* c, dmg_graph* g, int mode, int k, int exclude, 
     DMG_TRY(c->tmp0.reserve(nq * 4));        // row sizes
     DMG_TRY(c->tmp1.reserve(nq * 8));        // (lo, wn) per query
     const uint64_t scan_tiles = (chunk + SC_THREADS * SC_ITEMS - 1) / (SC_THREADS * SC_ITEMS);
-    DMG_TRY(c->status.reserve(scan_tiles * sizeof(uint64_t)));
     a.stage = c->scratch.as<uint8_t>();
     a.counts = c->tmp0.as<uint32_t>();
     a.qwin = c->tmp1.as<uint32_t>();
@@ -952,9 +954,11 @@ static int32_t run_khop(CallCtx* c, dmg_graph* g, int mode, int k, int exclude, 
       const uint64_t q1 = std::min<uint64_t>(nq, q0 + chunk);
       a.q_begin = q0;
       a.q_end = q1;
-      DMG_CUDA(cudaMemsetAsync(&c->d_counters->ticket, 0, 8, c->stream));
-      DMG_CUDA(cudaMemsetAsync(&c->d_counters->aux[1], 0, 8, c->stream));
-      DMG_CUDA(cudaMemsetAsync(c->status.p, 0, scan_tiles * sizeof(uint64_t), c->stream));
+      if (q0) {   // later chunks reuse the ticket, the scan ticket and the look-back words
+        DMG_CUDA(cudaMemsetAsync(&c->d_counters->ticket, 0, 8, c->stream));
+        DMG_CUDA(cudaMemsetAsync(&c->d_counters->aux[1], 0, 8, c->stream));
+        DMG_CUDA(cudaMemsetAsync(c->status.p, 0, scan_tiles * sizeof(uint64_t), c->stream));
+      }
       const uint64_t grid = std::min<uint64_t>(q1 - q0, (uint64_t)e->sm_count * std::max(occ, 1));
       {
         LaunchScope ls(c, K_KHOP_WINDOWS);
@@ -1014,12 +1018,9 @@ static int32_t run_khop(CallCtx* c, dmg_graph* g, int mode, int k, int exclude, 
       khop_global_kernel<<<(unsigned)grid, KG_THREADS, kg_smem, c->stream>>>(a, sc_seen, sc_rank, sc_queue, seen_words,
                                                                            qcap);
     }
-    const uint64_t scan_tiles = (nq + SC_THREADS * SC_ITEMS - 1) / (SC_THREADS * SC_ITEMS);
-    DMG_TRY(c->status.reserve(scan_tiles * sizeof(uint64_t)));
-    DMG_CUDA(cudaMemsetAsync(c->status.p, 0, scan_tiles * sizeof(uint64_t), c->stream));
     {
       LaunchScope ls(c, K_SCAN_COUNTS);
-      scan_counts_kernel<<<(unsigned)std::min<uint64_t>(scan_tiles, (uint64_t)e->sm_count * 4), SC_THREADS, 0, c->stream>>>(
+      scan_counts_kernel<<<(unsigned)std::min<uint64_t>(scan_tiles_all, (uint64_t)e->sm_count * 4), SC_THREADS, 0, c->stream>>>(
           a.counts, nq, a.out_off, &c->d_counters->aux[2], c->status.as<uint64_t>(), c->d_counters);
     }
     if (cap) {
