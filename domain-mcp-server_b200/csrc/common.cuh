@@ -75,6 +75,7 @@ enum KernelId : int {
   K_SEARCH_FIRST,
   K_SEARCH_EMIT,
   K_KHOP_WINDOWS,
+  K_QUERY_ROWS,
   K_MISC,
   K_COUNT
 };

@@ -1,7 +1,8 @@
 // Q1 of SURVEY.md 8a: batched execution of tokenised graph_query operations
-// (GraphQueryService.execute, GQS:53-73).  Operations are grouped by kind, each group runs as ONE
-// batch on the device primitives (adjacency rows, k-hop, name scans, method lookup), and the rows
-// are put back in operation order.
+// (GraphQueryService.execute, GQS:53-73).  k-hop operations run as one device batch per (mode, k,
+// exclude) and their rows stay on the device; names and methods are resolved by the lookup / scan
+// primitives; adjacency rows, the entry list and the endpoint list are read where they already
+// live.  The packed result (rows in operation order) is assembled on the device and copied once.
 #include <algorithm>
 #include <cstring>
 #include <memory>
@@ -36,6 +37,130 @@ __global__ void method_lookup_kernel(const uint32_t* __restrict__ method_off, co
   }
   out[i] = res;
 }
+
+// ---- device-side row assembly -------------------------------------------------------------------
+// Every operation's row is at most two segments of existing device memory (a CSR row, the entry
+// list, a row of a k-hop group's buffers, a single resolved id): qx_describe_kernel writes the
+// segments and the row length, scan_counts_kernel turns lengths into out_off, qx_fill_kernel copies
+// the segments into the packed result, which leaves the device in ONE copy.
+struct QxSeg {
+  const uint32_t* ids;
+  const uint8_t* aux;   // nullptr: every entry gets aux_const
+  uint32_t len, aux_const;
+};
+struct QxRow {
+  QxSeg s[2];
+};
+struct QxArgs {
+  const dmg_query_op* ops;
+  const unsigned long long* ref_a;
+  const uint32_t *ref_b, *ref_g;
+  const uint32_t* const* grp_ids;
+  const uint8_t* const* grp_hop;
+  const uint32_t *out_ptr, *out_idx, *in_ptr, *in_idx;
+  uint32_t V;
+  const uint32_t* entry;
+  uint32_t n_entry;
+  const uint32_t* endpoints;
+  uint32_t n_endpoints;
+  QxRow* rows;
+  uint32_t* cnt;
+  unsigned long long n;
+};
+
+__global__ void __launch_bounds__(256) qx_describe_kernel(const QxArgs a) {
+  const unsigned long long i = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x;
+  if (i >= a.n) return;
+  const dmg_query_op op = a.ops[i];
+  QxRow r;
+  r.s[0] = QxSeg{nullptr, nullptr, 0u, 0u};
+  r.s[1] = QxSeg{nullptr, nullptr, 0u, 0u};
+  const bool known = op.vertex < a.V;   // unknown vertices give empty rows
+  switch (op.opcode) {
+    case DMG_OP_DEPENDENCIES:
+    case DMG_OP_OVERVIEW:
+      if (known) {
+        const uint32_t b = a.out_ptr[op.vertex];
+        r.s[0] = QxSeg{a.out_idx + b, nullptr, a.out_ptr[op.vertex + 1] - b, 0u};
+      }
+      if (op.opcode == DMG_OP_DEPENDENCIES) break;
+      // overview: dependencies (aux 0) then dependents (aux 1)
+    case DMG_OP_DEPENDENTS:
+      if (known) {
+        const uint32_t b = a.in_ptr[op.vertex];
+        r.s[op.opcode == DMG_OP_OVERVIEW ? 1 : 0] =
+            QxSeg{a.in_idx + b, nullptr, a.in_ptr[op.vertex + 1] - b, op.opcode == DMG_OP_OVERVIEW ? 1u : 0u};
+      }
+      break;
+    case DMG_OP_KHOP: {
+      const uint32_t grp = a.ref_g[i];
+      const unsigned long long at = a.ref_a[i];
+      const uint32_t len = a.grp_ids[grp] ? a.ref_b[i] : 0u;
+      r.s[0] = QxSeg{a.grp_ids[grp] + at, a.grp_hop[grp] + at, len, 0u};
+      if (!a.grp_ids[grp]) r.s[0] = QxSeg{nullptr, nullptr, a.ref_b[i], 0u};   // sizing call: length only
+      break;
+    }
+    case DMG_OP_ENTRYPOINTS: r.s[0] = QxSeg{a.entry, nullptr, a.n_entry, 0u}; break;
+    case DMG_OP_ENDPOINTS: r.s[0] = QxSeg{a.endpoints, nullptr, a.n_endpoints, 0u}; break;
+    case DMG_OP_RESOLVE_NAME:
+    case DMG_OP_METHOD:
+      // the resolved id sits in the low word of the op's ref_a slot
+      r.s[0] = QxSeg{reinterpret_cast<const uint32_t*>(a.ref_a + i), nullptr, a.ref_b[i],
+                     op.opcode == DMG_OP_RESOLVE_NAME ? a.ref_g[i] : 0u};
+      break;
+    default: break;
+  }
+  a.rows[i] = r;
+  a.cnt[i] = r.s[0].len + r.s[1].len;
+}
+
+// Work is split by OUTPUT position (rows run from nothing to a whole project): a warp takes 2048
+// positions, finds the row of the first one by bisection over out_off and walks forward.
+__global__ void __launch_bounds__(256) qx_fill_kernel(const QxRow* __restrict__ rows,
+                                                      const unsigned long long* __restrict__ out_off,
+                                                      unsigned long long n_ops, uint32_t* out_ids, uint8_t* out_aux,
+                                                      unsigned long long total) {
+  constexpr unsigned long long CHUNK = 2048;
+  const int lane = threadIdx.x & 31;
+  const unsigned long long warp = (blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x) >> 5;
+  const unsigned long long nwarps = ((unsigned long long)gridDim.x * blockDim.x) >> 5;
+  for (unsigned long long P = warp * CHUNK; P < total; P += nwarps * CHUNK) {
+    const unsigned long long Pend = min(total, P + CHUNK);
+    unsigned long long q = 0, hi = n_ops;   // first row whose end lies beyond P (empty rows are skipped)
+    while (q < hi) {
+      const unsigned long long mid = (q + hi) >> 1;
+      if (out_off[mid + 1] <= P) q = mid + 1; else hi = mid;
+    }
+    unsigned long long row_begin = out_off[q], row_end = out_off[q + 1];
+    QxRow r = rows[q];
+    for (unsigned long long p = P + lane; p < Pend; p += 32) {
+      while (p >= row_end) {
+        ++q;
+        row_begin = row_end;
+        row_end = out_off[q + 1];
+        if (p < row_end) r = rows[q];
+      }
+      uint32_t j = (uint32_t)(p - row_begin);
+      const int sg = j < r.s[0].len ? 0 : 1;
+      if (sg) j -= r.s[0].len;
+      out_ids[p] = r.s[sg].ids[j];
+      out_aux[p] = r.s[sg].aux ? r.s[sg].aux[j] : (uint8_t)r.s[sg].aux_const;
+    }
+  }
+}
+
+// device allocation that frees itself on every exit path of the executor
+struct DevMem {
+  void* p = nullptr;
+  ~DevMem() {
+    if (p) cudaFree(p);
+  }
+  int32_t alloc(size_t bytes) {
+    DMG_CUDA(cudaMalloc(&p, std::max<size_t>(bytes, 256)));
+    return DMG_OK;
+  }
+  template <class T> T* as() const { return reinterpret_cast<T*>(p); }
+};
 
 }  // namespace dmg
 
@@ -100,11 +225,14 @@ int32_t dmg_query_batch(dmg_graph* g, uint64_t n_ops, const dmg_query_op* ops, c
   *needed = 0;
   out_off[0] = 0;
   if (!n_ops) return DMG_OK;
+  if (n_ops >= (1ull << 32)) {
+    set_error("dmg_query_batch: too many operations");
+    return DMG_EINVAL;
+  }
+  // a call without output buffers only sizes the result: k-hop groups are counted, not fetched
+  const bool sizing_only = !out_ids || !out_aux || cap == 0;
   // ---- group the operations ----------------------------------------------------------------
-  // group results are overwritten in full by the primitives: no zero fill of gigabytes
-  auto raw_u32 = [](uint64_t n) { return std::unique_ptr<uint32_t[]>(new uint32_t[std::max<uint64_t>(n, 1)]); };
-  auto raw_u8 = [](uint64_t n) { return std::unique_ptr<uint8_t[]>(new uint8_t[std::max<uint64_t>(n, 1)]); };
-  std::vector<uint64_t> adj_out, adj_in, names, methods, entries, endpoints;
+  std::vector<uint64_t> names, methods;
   struct KhopKey {
     uint32_t mode, k, excl;
     bool operator<(const KhopKey& o) const {
@@ -112,12 +240,15 @@ int32_t dmg_query_batch(dmg_graph* g, uint64_t n_ops, const dmg_query_op* ops, c
     }
   };
   std::vector<std::pair<KhopKey, uint64_t>> khops;
+  bool want_endpoints = false;
   for (uint64_t i = 0; i < n_ops; ++i) {
     const dmg_query_op& op = ops[i];
     switch (op.opcode) {
-      case DMG_OP_DEPENDENCIES: adj_out.push_back(i); break;
-      case DMG_OP_DEPENDENTS: adj_in.push_back(i); break;
-      case DMG_OP_OVERVIEW: adj_out.push_back(i); adj_in.push_back(i); break;
+      case DMG_OP_DEPENDENCIES:
+      case DMG_OP_DEPENDENTS:
+      case DMG_OP_OVERVIEW:
+      case DMG_OP_ENTRYPOINTS: break;
+      case DMG_OP_ENDPOINTS: want_endpoints = true; break;
       case DMG_OP_KHOP:
         if (op.mode > DMG_BOTH || op.k < 1 || op.k > DMG_MAX_HOPS) {
           set_error("dmg_query_batch: op %llu: bad k-hop mode/k", (unsigned long long)i);
@@ -125,8 +256,6 @@ int32_t dmg_query_batch(dmg_graph* g, uint64_t n_ops, const dmg_query_op* ops, c
         }
         khops.push_back({{op.mode, op.k, op.exclude_sources ? 1u : 0u}, i});
         break;
-      case DMG_OP_ENTRYPOINTS: entries.push_back(i); break;
-      case DMG_OP_ENDPOINTS: endpoints.push_back(i); break;
       case DMG_OP_RESOLVE_NAME:
       case DMG_OP_METHOD:
         if (op.text_end < op.text_begin || (op.text_end > op.text_begin && !text_bytes)) {
@@ -144,72 +273,57 @@ int32_t dmg_query_batch(dmg_graph* g, uint64_t n_ops, const dmg_query_op* ops, c
     set_error("dmg_query_batch: DMG_OP_METHOD needs dmg_graph_set_methods");
     return DMG_EINVAL;
   }
-  std::vector<uint64_t> cnt(n_ops, 0);
-  // a call without output buffers only sizes the result: the groups' rows are counted, not fetched
-  const bool sizing_only = !out_ids || !out_aux || cap == 0;
-  // per-group results, kept until the rows are laid out in operation order
-  std::vector<uint64_t> o_off, i_off, k_off_all;
-  std::unique_ptr<uint32_t[]> o_ids, i_ids;
+  DMG_CUDA(cudaSetDevice(g->eng->device));
+  // what the host learns about an op before the rows are described on the device:
+  //   k-hop: ref_a = start of its row in the group's buffers, ref_b = row length, ref_g = group
+  //   name / method: ref_a = the resolved id, ref_b = 0 or 1, ref_g = aux value
+  std::vector<unsigned long long> ref_a(n_ops, 0);
+  std::vector<uint32_t> ref_b(n_ops, 0), ref_g(n_ops, 0);
   uint64_t nd = 0;
   int32_t st;
-  auto adjacency = [&](int dir, const std::vector<uint64_t>& who, std::vector<uint64_t>& off, std::unique_ptr<uint32_t[]>& ids) {
-    if (who.empty()) return (int32_t)DMG_OK;
-    std::vector<uint32_t> v(who.size());
-    for (size_t j = 0; j < who.size(); ++j) v[j] = ops[who[j]].vertex;
-    off.assign(who.size() + 1, 0);
-    int32_t s2 = dmg_adjacency_batch(g, dir, who.size(), v.data(), off.data(), nullptr, 0, &nd);
-    if (s2 != DMG_OK && s2 != DMG_ECAP) return s2;
-    if (nd && !sizing_only) {
-      ids = raw_u32(nd);
-      s2 = dmg_adjacency_batch(g, dir, who.size(), v.data(), off.data(), ids.get(), nd, &nd);
-    } else {
-      s2 = DMG_OK;
-    }
-    for (size_t j = 0; j < who.size(); ++j) cnt[who[j]] += off[j + 1] - off[j];
-    return s2;
-  };
-  if ((st = adjacency(DMG_OUT, adj_out, o_off, o_ids)) != DMG_OK) return st;
-  if ((st = adjacency(DMG_IN, adj_in, i_off, i_ids)) != DMG_OK) return st;
-  // k-hop groups: one batch per (mode, k, exclude)
+
+  // ---- k-hop groups: one device batch per (mode, k, exclude); the rows stay on the device -----
   std::sort(khops.begin(), khops.end());
   struct KGroup {
-    size_t begin, end;
-    std::vector<uint64_t> off;
-    std::unique_ptr<uint32_t[]> ids;
-    std::unique_ptr<uint8_t[]> hop;
+    DevMem q, off, ids, hop;
   };
-  std::vector<KGroup> kgroups;
+  std::vector<std::unique_ptr<KGroup>> kgroups;
   for (size_t a = 0; a < khops.size();) {
     size_t b = a;
     while (b < khops.size() && !(khops[a].first < khops[b].first) && !(khops[b].first < khops[a].first)) ++b;
-    KGroup kg;
-    kg.begin = a;
-    kg.end = b;
     const size_t m = b - a;
-    std::vector<uint32_t> qo(m + 1), qs(m);
-    for (size_t j = 0; j < m; ++j) {
-      qo[j] = (uint32_t)j;
-      qs[j] = ops[khops[a + j].second].vertex;
-    }
-    qo[m] = (uint32_t)m;
-    kg.off.assign(m + 1, 0);
+    std::unique_ptr<KGroup> kg(new KGroup);
+    std::vector<uint32_t> q(2 * m + 1);   // q_off = 0..m, then q_src
+    for (size_t j = 0; j <= m; ++j) q[j] = (uint32_t)j;
+    for (size_t j = 0; j < m; ++j) q[m + 1 + j] = ops[khops[a + j].second].vertex;
+    DMG_TRY(kg->q.alloc(q.size() * 4));
+    DMG_TRY(kg->off.alloc((m + 1) * 8));
+    DMG_CUDA(cudaMemcpy(kg->q.p, q.data(), q.size() * 4, cudaMemcpyHostToDevice));
     const KhopKey& key = khops[a].first;
-    st = dmg_neighbors_batch(g, key.mode, key.k, key.excl, m, qo.data(), qs.data(), kg.off.data(), nullptr, nullptr, 0, &nd);
+    const uint32_t* d_qo = kg->q.as<uint32_t>();
+    st = dmg_neighbors_batch_dev(g, key.mode, key.k, key.excl, m, d_qo, d_qo + m + 1, kg->off.as<uint64_t>(), nullptr,
+                                 nullptr, 0, &nd);
     if (st != DMG_OK && st != DMG_ECAP) return st;
     if (nd && !sizing_only) {
-      kg.ids = raw_u32(nd);
-      kg.hop = raw_u8(nd);
-      st = dmg_neighbors_batch(g, key.mode, key.k, key.excl, m, qo.data(), qs.data(), kg.off.data(), kg.ids.get(),
-                               kg.hop.get(), nd, &nd);
+      DMG_TRY(kg->ids.alloc(nd * 4));
+      DMG_TRY(kg->hop.alloc(nd));
+      st = dmg_neighbors_batch_dev(g, key.mode, key.k, key.excl, m, d_qo, d_qo + m + 1, kg->off.as<uint64_t>(),
+                                   kg->ids.as<uint32_t>(), kg->hop.as<uint8_t>(), nd, &nd);
       if (st != DMG_OK) return st;
     }
-    for (size_t j = 0; j < m; ++j) cnt[khops[a + j].second] = kg.off[j + 1] - kg.off[j];
+    std::vector<uint64_t> off(m + 1);
+    DMG_CUDA(cudaMemcpy(off.data(), kg->off.p, (m + 1) * 8, cudaMemcpyDeviceToHost));
+    for (size_t j = 0; j < m; ++j) {
+      const uint64_t op = khops[a + j].second;
+      ref_a[op] = off[j];
+      ref_b[op] = (uint32_t)(off[j + 1] - off[j]);
+      ref_g[op] = (uint32_t)kgroups.size();
+    }
     kgroups.push_back(std::move(kg));
     a = b;
   }
-  // name resolution: simple-name equality first, containment for the misses (GQS:431-453)
-  std::vector<uint32_t> name_id(names.size(), 0xFFFFFFFFu);
-  std::vector<uint8_t> name_how(names.size(), 0);
+
+  // ---- name resolution: simple-name equality first, containment for the misses (GQS:431-453) ---
   if (!names.empty()) {
     if (!g->d_name_off) {
       set_error("dmg_query_batch: DMG_OP_RESOLVE_NAME needs a graph with names");
@@ -235,25 +349,26 @@ int32_t dmg_query_batch(dmg_graph* g, uint64_t n_ops, const dmg_query_op* ops, c
       std::vector<size_t> miss;
       for (size_t j = 0; j < todo.size(); ++j) {
         if (off[j + 1] > off[j]) {
-          name_id[todo[j]] = ids[off[j]];
-          name_how[todo[j]] = pass == 0 ? 2 : 3;
+          const uint64_t op = names[todo[j]];
+          ref_a[op] = ids[off[j]];
+          ref_b[op] = 1;
+          ref_g[op] = pass == 0 ? 2 : 3;
         } else {
           miss.push_back(todo[j]);
         }
       }
       todo.swap(miss);
     }
-    for (size_t j = 0; j < names.size(); ++j) cnt[names[j]] = name_id[j] != 0xFFFFFFFFu;
   }
-  // method lookups
-  std::vector<uint32_t> method_idx(methods.size(), 0xFFFFFFFFu);
+
+  CtxGuard cg(g->eng);
+  CallCtx* c = cg.c;
+  if (!c) return DMG_ECUDA;
+  DMG_TRY(c->begin());
+  // ---- method lookups ------------------------------------------------------------------------
   if (!methods.empty()) {
-    CtxGuard cg(g->eng);
-    CallCtx* c = cg.c;
-    if (!c) return DMG_ECUDA;
-    DMG_TRY(c->begin());
     const size_t m = methods.size();
-    std::vector<uint32_t> v(m), tb(m), te(m);
+    std::vector<uint32_t> v(m), tb(m), te(m), method_idx(m, 0xFFFFFFFFu);
     std::vector<uint8_t> txt;
     for (size_t j = 0; j < m; ++j) {
       const dmg_query_op& op = ops[methods[j]];
@@ -278,47 +393,101 @@ int32_t dmg_query_batch(dmg_graph* g, uint64_t n_ops, const dmg_query_op* ops, c
     }
     DMG_CUDA(cudaGetLastError());
     DMG_CUDA(cudaMemcpyAsync(method_idx.data(), d_out, m * 4, cudaMemcpyDeviceToHost, c->stream));
-    DMG_TRY(c->finish());
-    for (size_t j = 0; j < m; ++j) cnt[methods[j]] = method_idx[j] != 0xFFFFFFFFu;
+    DMG_CUDA(cudaStreamSynchronize(c->stream));
+    for (size_t j = 0; j < m; ++j)
+      if (method_idx[j] != 0xFFFFFFFFu) {
+        ref_a[methods[j]] = method_idx[j];
+        ref_b[methods[j]] = 1;
+      }
   }
-  for (uint64_t i : entries) cnt[i] = g->h_entry.size();
-  for (uint64_t i : endpoints) cnt[i] = g->h_endpoint_methods.size();
 
-  // ---- lay the rows out in operation order ---------------------------------------------------
-  uint64_t total = 0;
-  for (uint64_t i = 0; i < n_ops; ++i) {
-    out_off[i] = total;
-    total += cnt[i];
+  // ---- describe every row on the device, scan the sizes, fill the packed result -----------------
+  const size_t n_grp = kgroups.size();
+  std::vector<const uint32_t*> grp_ids(std::max<size_t>(n_grp, 1), nullptr);
+  std::vector<const uint8_t*> grp_hop(std::max<size_t>(n_grp, 1), nullptr);
+  for (size_t j = 0; j < n_grp; ++j) {
+    grp_ids[j] = kgroups[j]->ids.as<uint32_t>();
+    grp_hop[j] = kgroups[j]->hop.as<uint8_t>();
   }
-  out_off[n_ops] = total;
+  const size_t n_endp = want_endpoints ? g->h_endpoint_methods.size() : 0;
+  // one upload buffer: ops | ref_a | ref_b | ref_g | group pointers | endpoint list
+  const size_t o_ops = 0, o_ra = o_ops + n_ops * sizeof(dmg_query_op), o_rb = o_ra + n_ops * 8, o_rg = o_rb + n_ops * 4,
+               o_gi = (o_rg + n_ops * 4 + 15) & ~size_t(15), o_gh = o_gi + grp_ids.size() * 8,
+               o_ep = o_gh + grp_hop.size() * 8, up_bytes = o_ep + n_endp * 4;
+  DMG_TRY(c->q_src.reserve(up_bytes));
+  uint8_t* up = c->q_src.as<uint8_t>();
+  DMG_CUDA(cudaMemcpyAsync(up + o_ops, ops, n_ops * sizeof(dmg_query_op), cudaMemcpyHostToDevice, c->stream));
+  DMG_CUDA(cudaMemcpyAsync(up + o_ra, ref_a.data(), n_ops * 8, cudaMemcpyHostToDevice, c->stream));
+  DMG_CUDA(cudaMemcpyAsync(up + o_rb, ref_b.data(), n_ops * 4, cudaMemcpyHostToDevice, c->stream));
+  DMG_CUDA(cudaMemcpyAsync(up + o_rg, ref_g.data(), n_ops * 4, cudaMemcpyHostToDevice, c->stream));
+  DMG_CUDA(cudaMemcpyAsync(up + o_gi, grp_ids.data(), grp_ids.size() * 8, cudaMemcpyHostToDevice, c->stream));
+  DMG_CUDA(cudaMemcpyAsync(up + o_gh, grp_hop.data(), grp_hop.size() * 8, cudaMemcpyHostToDevice, c->stream));
+  if (n_endp)
+    DMG_CUDA(cudaMemcpyAsync(up + o_ep, g->h_endpoint_methods.data(), n_endp * 4, cudaMemcpyHostToDevice, c->stream));
+  c->stats.h2d_bytes += up_bytes;
+  const uint64_t scan_tiles = (n_ops + SC_THREADS * SC_ITEMS - 1) / (SC_THREADS * SC_ITEMS);
+  DMG_TRY(c->tmp1.reserve(n_ops * sizeof(QxRow)));
+  DMG_TRY(c->tmp2.reserve(n_ops * 4));
+  DMG_TRY(c->out_off.reserve((n_ops + 1) * 8));
+  DMG_TRY(c->status.reserve(scan_tiles * 8));
+  DMG_CUDA(cudaMemsetAsync(c->status.p, 0, scan_tiles * 8, c->stream));
+  DMG_CUDA(cudaMemsetAsync(c->d_counters, 0, sizeof(DevCounters), c->stream));
+  QxArgs qa;
+  qa.ops = reinterpret_cast<const dmg_query_op*>(up + o_ops);
+  qa.ref_a = reinterpret_cast<const unsigned long long*>(up + o_ra);
+  qa.ref_b = reinterpret_cast<const uint32_t*>(up + o_rb);
+  qa.ref_g = reinterpret_cast<const uint32_t*>(up + o_rg);
+  qa.grp_ids = reinterpret_cast<const uint32_t* const*>(up + o_gi);
+  qa.grp_hop = reinterpret_cast<const uint8_t* const*>(up + o_gh);
+  qa.out_ptr = g->d_out_ptr;
+  qa.out_idx = g->d_out_idx;
+  qa.in_ptr = g->d_in_ptr;
+  qa.in_idx = g->d_in_idx;
+  qa.V = g->info.n_vertices;
+  qa.entry = g->d_entry;
+  qa.n_entry = (uint32_t)g->h_entry.size();
+  qa.endpoints = reinterpret_cast<const uint32_t*>(up + o_ep);
+  qa.n_endpoints = (uint32_t)g->h_endpoint_methods.size();
+  qa.rows = c->tmp1.as<QxRow>();
+  qa.cnt = c->tmp2.as<uint32_t>();
+  qa.n = n_ops;
+  {
+    LaunchScope ls(c, K_QUERY_ROWS);
+    qx_describe_kernel<<<(unsigned)((n_ops + 255) / 256), 256, 0, c->stream>>>(qa);
+  }
+  {
+    LaunchScope ls(c, K_SCAN_COUNTS);
+    scan_counts_kernel<<<(unsigned)std::min<uint64_t>(scan_tiles, (uint64_t)g->eng->sm_count * 4), SC_THREADS, 0, c->stream>>>(
+        qa.cnt, n_ops, c->out_off.as<unsigned long long>(), &c->d_counters->aux[2], c->status.as<uint64_t>(),
+        c->d_counters);
+  }
+  DMG_CUDA(cudaGetLastError());
+  DMG_CUDA(cudaMemcpyAsync(c->h_counters, c->d_counters, sizeof(DevCounters), cudaMemcpyDeviceToHost, c->stream));
+  DMG_CUDA(cudaMemcpyAsync(out_off, c->out_off.p, (n_ops + 1) * 8, cudaMemcpyDeviceToHost, c->stream));
+  DMG_CUDA(cudaStreamSynchronize(c->stream));
+  const uint64_t total = c->h_counters->total;
+  c->stats.d2h_bytes += (n_ops + 1) * 8 + sizeof(DevCounters);
+  c->stats.results = total;
   *needed = total;
-  if (total > cap || (total && (!out_ids || !out_aux))) {
+  if (total > cap || (total && sizing_only)) {
+    DMG_TRY(c->finish());
     set_error("dmg_query_batch: capacity %llu < needed %llu", (unsigned long long)cap, (unsigned long long)total);
     return DMG_ECAP;
   }
-  std::vector<uint64_t> cur(out_off, out_off + n_ops);
-  auto put = [&](uint64_t op, const uint32_t* ids, uint64_t n, uint8_t aux, const uint8_t* auxv) {
-    if (!n) return;
-    uint64_t& w = cur[op];
-    std::memcpy(out_ids + w, ids, n * sizeof(uint32_t));
-    if (auxv) std::memcpy(out_aux + w, auxv, n);
-    else std::memset(out_aux + w, aux, n);
-    w += n;
-  };
-  for (size_t j = 0; j < adj_out.size(); ++j) put(adj_out[j], o_ids.get() + o_off[j], o_off[j + 1] - o_off[j], 0, nullptr);
-  for (size_t j = 0; j < adj_in.size(); ++j)
-    put(adj_in[j], i_ids.get() + i_off[j], i_off[j + 1] - i_off[j], ops[adj_in[j]].opcode == DMG_OP_OVERVIEW ? 1 : 0,
-        nullptr);
-  for (const KGroup& kg : kgroups)
-    for (size_t j = 0; j + kg.begin < kg.end; ++j)
-      put(khops[kg.begin + j].second, kg.ids.get() + kg.off[j], kg.off[j + 1] - kg.off[j], 0, kg.hop.get() + kg.off[j]);
-  for (size_t j = 0; j < names.size(); ++j)
-    if (name_id[j] != 0xFFFFFFFFu) put(names[j], &name_id[j], 1, name_how[j], nullptr);
-  for (size_t j = 0; j < methods.size(); ++j)
-    if (method_idx[j] != 0xFFFFFFFFu) put(methods[j], &method_idx[j], 1, 0, nullptr);
-  for (uint64_t i : entries) put(i, g->h_entry.data(), g->h_entry.size(), 0, nullptr);
-  for (uint64_t i : endpoints) put(i, g->h_endpoint_methods.data(), g->h_endpoint_methods.size(), 0, nullptr);
-  return DMG_OK;
+  if (total) {
+    DMG_TRY(c->out_ids.reserve(total * 4));
+    DMG_TRY(c->out_hop.reserve(total));
+    {
+      LaunchScope ls(c, K_QUERY_ROWS);
+      qx_fill_kernel<<<(unsigned)g->eng->sm_count * 8, 256, 0, c->stream>>>(
+          qa.rows, c->out_off.as<unsigned long long>(), n_ops, c->out_ids.as<uint32_t>(), c->out_hop.as<uint8_t>(), total);
+    }
+    DMG_CUDA(cudaGetLastError());
+    DMG_CUDA(cudaMemcpyAsync(out_ids, c->out_ids.p, total * 4, cudaMemcpyDeviceToHost, c->stream));
+    DMG_CUDA(cudaMemcpyAsync(out_aux, c->out_hop.p, total, cudaMemcpyDeviceToHost, c->stream));
+    c->stats.d2h_bytes += total * 5;
+  }
+  return c->finish();
 }
 
 }  // extern "C"
