@@ -97,6 +97,7 @@ __global__ void __launch_bounds__(CL_THREADS) order_claim_kernel(const uint32_t*
   __shared__ uint32_t s_cnt[OC_TILE], s_off[OC_TILE];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const uint32_t n_tiles = (nf + OC_TILE - 1) / OC_TILE;
+  unsigned long long te = 0;   // lane 0 of each warp: adjacency entries of the parents it handled
   while (true) {
     if (tid == 0) s_t = atomicAdd(&ctr->ticket, 1ull);
     __syncthreads();
@@ -109,6 +110,7 @@ __global__ void __launch_bounds__(CL_THREADS) order_claim_kernel(const uint32_t*
       if (i < nf) {
         const uint32_t u = frontier[i];
         const uint32_t b = ptr[u], n = ptr[u + 1] - b;
+        te += n;
         for (uint32_t j = lane; j < n; j += 32) {
           const uint32_t v = idx[b + j];
           c += (key[v] == (((unsigned long long)i << 32) | j)) && (__ldcg(&level[v]) == DMG_LEVEL_UNREACHED);
@@ -161,6 +163,7 @@ __global__ void __launch_bounds__(CL_THREADS) order_claim_kernel(const uint32_t*
     }
     __syncthreads();
   }
+  if (lane == 0 && te) atomicAdd(&ctr->edges, te);
 }
 
 // orphans: every vertex the BFS did not reach, in nodes order (PG:415-418)
@@ -350,6 +353,7 @@ int32_t dmg_analysis_order(dmg_graph* g, uint32_t* out_order) {
     DMG_CUDA(cudaMemcpyAsync(c->h_counters, c->d_counters, sizeof(DevCounters), cudaMemcpyDeviceToHost, c->stream));
     DMG_CUDA(cudaStreamSynchronize(c->stream));
     nf = (uint32_t)c->h_counters->total;
+    edges += c->h_counters->edges;   // adjacency entries of this level's parents (TE of SURVEY.md 8d)
     done += nf;
     std::swap(fa, fb);
   }

@@ -213,6 +213,8 @@ def test_closure_and_order_random(engine):
         g = dmgraph.Graph(engine, n, src, dst, entry)
         o = ora.CsrOracle(n, src, dst, entry)
         assert np.array_equal(g.analysis_order(), o.analysis_order())
+        # the BFS part of analysisOrder is the OUT closure of the entry points: same TE
+        assert engine.last_stats()["edges_traversed"] == o.closure(0, entry)[2]
         for d in (0, 1):
             s = rng.integers(0, n + 2, int(rng.integers(0, 5))).astype(np.uint32)
             lvl, reached = g.closure(d, s)
