@@ -155,7 +155,12 @@ struct DevMem {
   ~DevMem() {
     if (p) cudaFree(p);
   }
+  void reset() {
+    if (p) cudaFree(p);
+    p = nullptr;
+  }
   int32_t alloc(size_t bytes) {
+    reset();
     DMG_CUDA(cudaMalloc(&p, std::max<size_t>(bytes, 256)));
     return DMG_OK;
   }
@@ -301,15 +306,32 @@ int32_t dmg_query_batch(dmg_graph* g, uint64_t n_ops, const dmg_query_op* ops, c
     DMG_CUDA(cudaMemcpy(kg->q.p, q.data(), q.size() * 4, cudaMemcpyHostToDevice));
     const KhopKey& key = khops[a].first;
     const uint32_t* d_qo = kg->q.as<uint32_t>();
-    st = dmg_neighbors_batch_dev(g, key.mode, key.k, key.excl, m, d_qo, d_qo + m + 1, kg->off.as<uint64_t>(), nullptr,
-                                 nullptr, 0, &nd);
-    if (st != DMG_OK && st != DMG_ECAP) return st;
-    if (nd && !sizing_only) {
-      DMG_TRY(kg->ids.alloc(nd * 4));
-      DMG_TRY(kg->hop.alloc(nd));
+    // A group can never hold more than the caller's capacity (or the batch is too large anyway)
+    // nor more than a project per query: with buffers of that size ONE traversal both sizes and
+    // fetches the group.  Only a guess cut short by free memory needs a second, exactly sized run.
+    uint64_t bound = sizing_only ? 0 : cap;
+    const uint64_t maxp = g->info.max_part_vertices;
+    if (maxp && m <= UINT64_MAX / maxp) bound = std::min<uint64_t>(bound, m * maxp);
+    uint64_t guess = bound;
+    if (guess) {
+      size_t free_b = 0, total_b = 0;
+      DMG_CUDA(cudaMemGetInfo(&free_b, &total_b));
+      guess = std::min<uint64_t>(guess, free_b / 20);   // ids + hops here, the traversal's temporaries, and headroom
+      guess = std::min<uint64_t>(guess, 1ull << 30);     // a caller with an "unbounded" capacity does not get 40 GB of guess
+    }
+    for (int attempt = 0; attempt < 2; ++attempt) {
+      if (guess) {
+        DMG_TRY(kg->ids.alloc(guess * 4));
+        DMG_TRY(kg->hop.alloc(guess));
+      }
       st = dmg_neighbors_batch_dev(g, key.mode, key.k, key.excl, m, d_qo, d_qo + m + 1, kg->off.as<uint64_t>(),
-                                   kg->ids.as<uint32_t>(), kg->hop.as<uint8_t>(), nd, &nd);
-      if (st != DMG_OK) return st;
+                                   kg->ids.as<uint32_t>(), kg->hop.as<uint8_t>(), guess, &nd);
+      if (st == DMG_OK) break;
+      if (st != DMG_ECAP) return st;
+      kg->ids.reset();   // rows did not fit: the offsets are valid, the buffers are not
+      kg->hop.reset();
+      if (attempt == 1 || nd > bound) break;   // sizing call, or more than the caller can take: count only
+      guess = nd;
     }
     std::vector<uint64_t> off(m + 1);
     DMG_CUDA(cudaMemcpy(off.data(), kg->off.p, (m + 1) * 8, cudaMemcpyDeviceToHost));
