@@ -406,6 +406,7 @@ template <class F>
 static inline int32_t with_small_kernel(uint32_t win_cap, F f) {
   if (win_cap <= 512) return f(khop_small_kernel<KS_THREADS, 512>, 512);
   if (win_cap <= 2048) return f(khop_small_kernel<KS_THREADS, 2048>, 2048);
+  if (win_cap <= 4096) return f(khop_small_kernel<KS_THREADS, 4096>, 4096);   // 12.5 KB: still 16 CTAs/SM
   return f(khop_small_kernel<KS_THREADS, 8192>, 8192);
 }
 static inline size_t small_kernel_smem(uint32_t wc) { return (size_t)wc + wc / 8 + 2 * (size_t)wc; }

@@ -122,6 +122,31 @@ def test_khop_random_small_windows(engine, n_parts):
         g.release()
 
 
+@pytest.mark.parametrize("n", [2100, 4000, 4200, 8192])
+def test_khop_random_mid_windows(engine, n):
+    """Projects of 2049..8192 vertices: the 4096 and 8192 shared-memory classes of khop_small."""
+    rng = np.random.default_rng(n)
+    src, dst, entry, part_off = _random_graph(rng, n, 6 * n, 1)
+    g = dmgraph.Graph(engine, n, src, dst, entry, part_off=part_off)
+    o = ora.CsrOracle(n, src, dst, entry, part_off)
+    q_off, q_src = _random_queries(rng, n, 150, 8)
+    for mode, k, excl in [(0, 1, 0), (1, 2, 1), (2, 1, 1), (2, 2, 0), (2, 3, 1), (0, 5, 1)]:
+        off, ids, hop = g.neighbors_batch(mode, k, excl, q_off, q_src)
+        woff, wids, whop, wte = o.khop_batch(mode, k, excl, q_off, q_src, threads=8)
+        assert np.array_equal(off, woff)
+        assert np.array_equal(ids, wids)
+        assert np.array_equal(hop, whop)
+        assert engine.last_stats()["edges_traversed"] == wte
+    _stride, win, rows = g.neighbors_batch_rows(2, 2, 1, q_off, q_src)
+    woff, wids, whop, _ = o.khop_batch(2, 2, 1, q_off, q_src, threads=8)
+    for q in range(q_off.size - 1):
+        a, b = int(woff[q]), int(woff[q + 1])
+        r = rows[q]
+        got = np.flatnonzero((r != 0) & (r != 255))
+        assert np.array_equal(got + int(win[q, 0]), wids[a:b]) and np.array_equal(r[got], whop[a:b])
+    g.release()
+
+
 def test_khop_random_large_window(engine):
     """Projects above 8192 vertices take the global-scratch kernel, incl. its long-row path."""
     rng = np.random.default_rng(5)
