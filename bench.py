@@ -264,11 +264,13 @@ def main():
         alg_bytes = int(step_bytes)
     achieved = alg_bytes / (kms / kl * 1e-3) / 1e9
     actual_bytes = int(8 * stats["rows_expanded"] + 4 * stats["edges_read"] + 4 * n_src_total + stage_bytes)
-    traffic = None
+    traffic, issue_pct = None, None
     tpath = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(tpath):
         try:
-            traffic = json.load(open(tpath)).get(kname)
+            tj = json.load(open(tpath))
+            traffic = tj.get(kname)
+            issue_pct = tj.get("issue_active_pct", {}).get(kname)
         except Exception:
             traffic = None
     roofline = {"bound": "hbm", "kernel": kname, "achieved": achieved, "peak": peak, "unit": "GB/s",
@@ -278,6 +280,7 @@ def main():
                 "whole_step_algorithmic_bytes": int(step_bytes),
                 "whole_step_achieved_GBs": step_bytes / (dev_ms / args.steps * 1e-3) / 1e9,
                 "kernel_share_of_step": kms / dev_ms if dev_ms else None,
+                "ncu_issue_active_pct": issue_pct,   # from the committed ncu capture, not measured in this run
                 "note": "algorithmic bytes follow SURVEY.md 8d (every adjacency entry of every expanded vertex); "
                         "bottom-up levels stop at the first frontier member, so fewer entries are loaded "
                         "(edges_read), and this config's CSR (25 MB) is L2-resident: frac can exceed what HBM "
