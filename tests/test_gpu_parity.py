@@ -147,6 +147,25 @@ def test_khop_random_mid_windows(engine, n):
     g.release()
 
 
+def test_khop_large_batch(engine):
+    """A batch of several waves of CTAs over many projects, an unknown frame, and the ECAP answer."""
+    sg = synth.eco_graph(n_projects=8, v_per=600, e_per=5000, cap=80, seed=31)
+    g = dmgraph.Graph(engine, sg.n_vertices, sg.src, sg.dst, sg.entry, part_off=sg.part_off)
+    o = ora.CsrOracle(sg.n_vertices, sg.src, sg.dst, sg.entry, sg.part_off)
+    q_off, q_src = synth.stacktrace_queries(sg, n_queries=21000, frames=6, seed=32)
+    q_src[17] = 0xFFFFFFF0
+    for mode, k, excl in [(2, 2, 1), (0, 2, 0), (2, 1, 1)]:
+        off, ids, hop = g.neighbors_batch(mode, k, excl, q_off, q_src)
+        woff, wids, whop, wte = o.khop_batch(mode, k, excl, q_off, q_src, threads=8)
+        assert np.array_equal(off, woff) and np.array_equal(ids, wids) and np.array_equal(hop, whop)
+        assert engine.last_stats()["edges_traversed"] == wte
+        assert engine.last_stats()["d2h_bytes"] >= 5 * ids.size
+    with pytest.raises(dmgraph.DmgError) as ei:
+        g.neighbors_batch(2, 2, 1, q_off, q_src, cap=int(woff[-1]) // 2)
+    assert ei.value.code == dmgraph.ECAP
+    g.release()
+
+
 def test_khop_random_large_window(engine):
     """Projects above 8192 vertices take the global-scratch kernel, incl. its long-row path."""
     rng = np.random.default_rng(5)
