@@ -479,7 +479,10 @@ __global__ void __launch_bounds__(EM_THREADS, EM_BLOCKS_PER_SM) khop_emit_kernel
 // array used only when the row is too long to sort in shared memory.  The bitmap is reset
 // sparsely (by walking the queue), so the cost of a query follows its result, not V.
 // ---------------------------------------------------------------------------------------------
-constexpr int KG_THREADS = 256;
+#ifndef DMG_KG_THREADS
+#define DMG_KG_THREADS 512
+#endif
+constexpr int KG_THREADS = DMG_KG_THREADS;   // threads per query CTA (tuning knob, like DMG_KS_*)
 constexpr int KG_SORT_CAP = 4096;    // rows up to this length are ordered in shared memory
 constexpr int KG_BUCKETS = 1024;
 constexpr uint32_t KG_BUCKET_MAX = 48;   // longest bucket a single thread insertion-sorts
