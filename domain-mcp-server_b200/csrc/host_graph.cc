@@ -92,9 +92,11 @@ struct JsonIn {
             put_utf8(*out, cp);
             break;
           }
-          default: *out += c;   // \" \\ \/
+          case '"': case '\\': case '/': *out += c; break;
+          default: return ok = false;   // Jackson: "Unrecognized character escape"
         }
       } else {
+        if ((unsigned char)*p < 0x20) return ok = false;   // Jackson: "Illegal unquoted character"
         *out += *p++;
       }
     }
@@ -128,11 +130,38 @@ struct JsonIn {
           return ok = false;
         }
       }
-    } else {
-      while (p < end && *p != ',' && *p != '}' && *p != ']' && *p != ' ' && *p != '\n' && *p != '\r' && *p != '\t') ++p;
-      if (p == s) return ok = false;
+    } else if (!scalar()) {
+      return ok = false;
     }
     if (raw) raw->assign(s, p - s);
+    return true;
+  }
+  // true / false / null / a JSON number, nothing else (Jackson rejects everything else too)
+  bool scalar() {
+    for (const char* lit : {"true", "false", "null"}) {
+      const size_t n = strlen(lit);
+      if ((size_t)(end - p) >= n && strncmp(p, lit, n) == 0) {
+        p += n;
+        return true;
+      }
+    }
+    const char* q = p;
+    if (q < end && *q == '-') ++q;
+    if (q >= end || *q < '0' || *q > '9') return false;
+    if (*q == '0') ++q;
+    else while (q < end && *q >= '0' && *q <= '9') ++q;
+    if (q < end && *q == '.') {
+      ++q;
+      if (q >= end || *q < '0' || *q > '9') return false;
+      while (q < end && *q >= '0' && *q <= '9') ++q;
+    }
+    if (q < end && (*q == 'e' || *q == 'E')) {
+      ++q;
+      if (q < end && (*q == '+' || *q == '-')) ++q;
+      if (q >= end || *q < '0' || *q > '9') return false;
+      while (q < end && *q >= '0' && *q <= '9') ++q;
+    }
+    p = q;
     return true;
   }
 };
@@ -168,6 +197,7 @@ void json_escape(std::string& o, const std::string& s) {
 // (the reference's HashMap order is unpinned).
 struct dmg_pgraph {
   std::vector<std::string> names, files, class_ids;
+  std::vector<char> has_class_id;   // classIdMapping.containsKey: an empty string is a value too (PG:641-644, 775-778)
   std::unordered_map<std::string, uint32_t> pos;
   struct Row {
     std::string src;
@@ -224,6 +254,7 @@ int32_t dmg_pg_add_node(dmg_pgraph* pg, const char* id, const char* file) {
     pg->names.emplace_back(id);
     pg->files.emplace_back(file);
     pg->class_ids.emplace_back();
+    pg->has_class_id.push_back(0);
   } else {
     pg->files[it->second] = file;   // LinkedHashMap.put: position kept, value replaced
   }
@@ -321,7 +352,7 @@ int32_t dmg_pg_to_json(const dmg_pgraph* pg, char** out_json) {
     json_escape(o, pg->names[v]);
     o += ":{\"sourceFile\":";
     json_escape(o, pg->files[v]);
-    if (!pg->class_ids[v].empty()) {
+    if (pg->has_class_id[v]) {
       o += ",\"classId\":";
       json_escape(o, pg->class_ids[v]);
     }
@@ -370,13 +401,13 @@ int32_t dmg_pg_from_json(const char* json, dmg_pgraph** out) {
   if (!in.eat('}')) {
     while (true) {
       std::string key;
-      if (!in.string(&key) || !in.eat(':')) break;
+      if (!in.string(&key) || !in.eat(':')) { in.ok = false; break; }
       if (key == "nodes") {
         if (!in.eat('{')) { in.ok = false; break; }
         if (!in.eat('}'))
           while (true) {
             std::string id, file, cid;
-            bool have_file = false;
+            bool have_file = false, have_cid = false;
             if (!in.string(&id) || !in.eat(':') || !in.eat('{')) { in.ok = false; break; }
             if (!in.eat('}'))
               while (true) {
@@ -386,7 +417,7 @@ int32_t dmg_pg_from_json(const char* json, dmg_pgraph** out) {
                 if (in.p < in.end && *in.p == '"') {
                   if (!in.string(&v2)) break;
                   if (k2 == "sourceFile") { file = v2; have_file = true; }
-                  else if (k2 == "classId") cid = v2;
+                  else if (k2 == "classId") { cid = v2; have_cid = true; }
                 } else if (!in.skip(nullptr)) break;
                 if (in.eat(',')) continue;
                 if (in.eat('}')) break;
@@ -401,9 +432,11 @@ int32_t dmg_pg_from_json(const char* json, dmg_pgraph** out) {
               pg->names.push_back(id);
               pg->files.push_back(file);
               pg->class_ids.push_back(cid);
+              pg->has_class_id.push_back(have_cid ? 1 : 0);
             } else {
               pg->files[it->second] = file;
               pg->class_ids[it->second] = cid;
+              pg->has_class_id[it->second] = have_cid ? 1 : 0;
             }
             if (in.eat(',')) continue;
             if (in.eat('}')) break;

@@ -95,3 +95,70 @@ def test_from_json_old_format_and_metadata_passthrough():
     for bad in ("", "   ", "[1,2]", '{"nodes":{"a":{}}}', '{"nodes":'):
         with pytest.raises(ValueError):
             ProjectGraph.from_json(bad)
+
+
+# ---- W0 fuzz: arbitrary reference-shaped documents survive the C++ reader / writer --------------
+try:
+    from hypothesis import given, settings, strategies as st
+    _HAVE_HYPOTHESIS = True
+except Exception:                                          # pragma: no cover
+    _HAVE_HYPOTHESIS = False
+
+if _HAVE_HYPOTHESIS:
+    _name = st.text(alphabet=st.characters(blacklist_categories=("Cs",), min_codepoint=1), min_size=1, max_size=12) \
+        .filter(lambda s: s.strip() != "")
+    _scalar = st.one_of(st.none(), st.booleans(), st.integers(-2**31, 2**31), st.text(max_size=8))
+    _meta = st.recursive(_scalar, lambda c: st.one_of(st.lists(c, max_size=3),
+                                                      st.dictionaries(st.text(max_size=6), c, max_size=3)), max_leaves=8)
+
+    @st.composite
+    def _documents(draw):
+        ids = draw(st.lists(_name, min_size=1, max_size=8, unique=True))
+        nodes = {}
+        for i in ids:
+            n = {"sourceFile": draw(st.text(min_size=1, max_size=10).filter(lambda s: s.strip() != ""))}
+            if draw(st.booleans()):
+                n["classId"] = draw(st.text(max_size=6))
+            nodes[i] = n
+        edges = {}
+        for s in draw(st.lists(st.sampled_from(ids), max_size=4, unique=True)):
+            edges[s] = draw(st.lists(st.sampled_from(ids), max_size=5, unique=True))
+        doc = {"nodes": nodes, "edges": edges,
+               "entryPoints": draw(st.lists(st.sampled_from(ids), max_size=3, unique=True))}
+        if draw(st.booleans()):                            # new-format sections are opaque host payload
+            doc["methodParameters"] = draw(st.dictionaries(st.sampled_from(ids), _meta, max_size=2))
+            doc["nodeInfo"] = draw(st.dictionaries(st.sampled_from(ids), _meta, max_size=2))
+            doc["methodInfo"] = draw(st.dictionaries(st.sampled_from(ids), _meta, max_size=2))
+        return doc
+
+    @settings(max_examples=120, deadline=None)
+    @given(_documents(), st.booleans())
+    def test_json_fuzz_round_trip(doc, ascii_only):
+        text = json.dumps(doc, ensure_ascii=ascii_only)    # \\uXXXX escapes (incl. surrogate pairs) or raw UTF-8
+        g = ProjectGraph.from_json(text)
+        assert g.identifiers() == list(doc["nodes"])
+        assert g.edge_count() == sum(len(v) for v in doc["edges"].values())
+        back = json.loads(g.to_json())
+        assert back["nodes"] == doc["nodes"] and list(back["nodes"]) == list(doc["nodes"])
+        assert {k: v for k, v in back["edges"].items() if v} == {k: v for k, v in doc["edges"].items() if v}
+        assert back["entryPoints"] == doc["entryPoints"]
+        for sec in ("methodParameters", "nodeInfo", "methodInfo"):
+            assert back[sec] == doc.get(sec, {})
+
+    @settings(max_examples=150, deadline=None)
+    @given(_documents(), st.integers(0, 400), st.sampled_from(["cut", "flip", "drop"]))
+    def test_json_fuzz_malformed_never_crashes(doc, pos, how):
+        text = json.dumps(doc)
+        pos %= max(len(text), 1)
+        bad = {"cut": text[:pos], "flip": text[:pos] + "\\x" + text[pos + 1:], "drop": text[:pos] + text[pos + 1:]}[how]
+        try:
+            json.loads(bad)
+            still_json = True
+        except Exception:
+            still_json = False
+        try:
+            ProjectGraph.from_json(bad)                    # either loads or raises ValueError; never aborts
+        except ValueError:
+            assert True
+        else:
+            assert still_json or how == "drop"             # the reader is no stricter than it needs to be
