@@ -162,3 +162,38 @@ if _HAVE_HYPOTHESIS:
             assert True
         else:
             assert still_json or how == "drop"             # the reader is no stricter than it needs to be
+
+
+if _HAVE_HYPOTHESIS:
+    _ids = st.sampled_from(["a.A", "a.B", "b.C", "b.c", "x/y", "Z", "é.É", "a.A "])
+    _ops = st.lists(st.one_of(
+        st.tuples(st.just("node"), _ids, st.sampled_from(["f1", "f2", "dir/f 3"])),
+        st.tuples(st.just("dep"), _ids, _ids),
+        st.tuples(st.just("entry"), _ids)), max_size=40)
+
+    @settings(max_examples=200, deadline=None)
+    @given(_ops)
+    def test_builder_fuzz_against_python_restatement(ops):
+        """Random addNode / addDependency / markAsEntryPoint sequences (re-adds, unknown endpoints,
+        self-loops, duplicates): the C++ mirror and the Python restatement of PG:160-197 agree on
+        order, files, edges and entry points, and the JSON round trip keeps all of it."""
+        g, p = ProjectGraph(), pyref.ProjectGraph()
+        for op in ops:
+            for t in (g, p):
+                if op[0] == "node":
+                    t.add_node(op[1], op[2])
+                elif op[0] == "dep":
+                    t.add_dependency(op[1], op[2])
+                else:
+                    t.mark_as_entry_point(op[1])
+        assert g.identifiers() == p.identifiers()
+        assert g.node_count() == len(p.identifiers()) and g.entry_point_count() == p.entry_point_count()
+        assert g.edge_count() == sum(len(v) for v in p.edges.values())
+        doc = json.loads(g.to_json())
+        assert {k: v["sourceFile"] for k, v in doc["nodes"].items()} == p.nodes
+        assert {k: list(v) for k, v in doc["edges"].items() if v} == {k: list(v) for k, v in p.edges.items() if v}
+        assert doc["entryPoints"] == p.entry_points()
+        for i, name in enumerate(p.identifiers()):
+            assert g.id_of(name) == i and g.name_of(i) == name and g.contains(name)
+        r = ProjectGraph.from_json(g.to_json())
+        assert json.loads(r.to_json()) == doc

@@ -177,3 +177,45 @@ def test_search_restatements_agree():
         o2, i2 = ora.search_batch(off, low, [t.lower().encode()], kind=2)
         got = names[i1[0]] if i1.size else (names[i2[0]] if i2.size else None)
         assert got == want
+
+
+# ---- S1 / S2 fuzz: the C++ scans against the one-line Python definitions -------------------------
+try:
+    from hypothesis import given, settings, strategies as st
+
+    _seg = st.text(alphabet="abAB.x/_1", min_size=0, max_size=6)
+    _names = st.lists(st.builds(lambda a, b: (a + "." + b) if a else b, _seg, _seg.filter(lambda s: s != "")),
+                      min_size=1, max_size=12)
+
+    @settings(max_examples=150, deadline=None)
+    @given(_names, st.lists(st.text(alphabet="abAB.x/_1", max_size=4), min_size=1, max_size=6), st.data())
+    def test_search_fuzz_against_definitions(names, extra, data):
+        from dmgraph import synth
+        off, arena = synth.pack_names(names)
+        low = np.frombuffer(bytes(arena).lower(), dtype=np.uint8).copy()
+        lows = [n.lower() for n in names]
+        subs = []
+        for _ in range(4):                                   # substrings of real names hit; random text mostly misses
+            n = data.draw(st.sampled_from(lows))
+            a = data.draw(st.integers(0, len(n)))
+            b = data.draw(st.integers(a, len(n)))
+            subs.append(n[a:b])
+        queries = [q.lower() for q in extra] + subs
+        qb = [q.encode() for q in queries]
+        v_lo = data.draw(st.integers(0, len(names)))
+        v_hi = data.draw(st.integers(v_lo, len(names)))
+        simple = lambda s: s[s.rfind(".") + 1:]
+        for lo, hi in ((0, len(names)), (v_lo, v_hi)):
+            o, ids = ora.search_batch(off, low, qb, 0, lo, hi)
+            for qi, q in enumerate(queries):                 # CCS:1511-1526: nodes order, "" matches everything
+                assert ids[o[qi]:o[qi + 1]].tolist() == [i for i in range(lo, hi) if q in lows[i]]
+            o, ids = ora.search_batch(off, low, qb, 1, lo, hi)
+            for qi, q in enumerate(queries):                 # GQS:434-446: first simple-name equality
+                want = next((i for i in range(lo, hi) if simple(lows[i]) == q), None)
+                assert ids[o[qi]:o[qi + 1]].tolist() == ([] if want is None else [want])
+            o, ids = ora.search_batch(off, low, qb, 2, lo, hi)
+            for qi, q in enumerate(queries):                 # GQS:449-453: first containment
+                want = next((i for i in range(lo, hi) if q in lows[i]), None)
+                assert ids[o[qi]:o[qi + 1]].tolist() == ([] if want is None else [want])
+except ImportError:                                          # pragma: no cover
+    pass
