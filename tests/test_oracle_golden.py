@@ -219,3 +219,42 @@ try:
                 assert ids[o[qi]:o[qi + 1]].tolist() == ([] if want is None else [want])
 except ImportError:                                          # pragma: no cover
     pass
+
+
+def test_multi_project_windows_against_single_project_restatement():
+    """One handle over several projects (quirk 6, CCS:1426-1434, 1558): a query runs in
+    the project of its first known source, sources of other projects match nothing.  The csr
+    restatement with part_off must equal the Python restatement run on that one project."""
+    rng = np.random.default_rng(77)
+    for trial in range(25):
+        n_parts = int(rng.integers(1, 5))
+        sizes = rng.integers(1, 12, n_parts)
+        part_off = np.concatenate([[0], np.cumsum(sizes)]).astype(np.uint32)
+        V = int(part_off[-1])
+        graphs, src, dst = [], [], []
+        for p in range(n_parts):
+            g = PyAdapter()
+            base, n = int(part_off[p]), int(sizes[p])
+            for i in range(n):
+                g.add_node("v%d" % (base + i), "f")
+            for _ in range(int(rng.integers(0, 3 * n + 1))):
+                a, b = int(rng.integers(0, n)), int(rng.integers(0, n))
+                g.add_dependency("v%d" % (base + a), "v%d" % (base + b))
+                src.append(base + a)
+                dst.append(base + b)
+            graphs.append(g)
+        csr = ora.CsrOracle(V, np.array(src, np.uint32), np.array(dst, np.uint32), [], part_off)
+        for _ in range(12):
+            s = rng.integers(0, V + 2, int(rng.integers(0, 6)))          # ids >= V are unknown frames
+            k, mi, excl = int(rng.integers(1, 4)), int(rng.integers(0, 3)), bool(rng.integers(0, 2))
+            off, oid, hop, _te = csr.khop_batch(mi, k, excl, [0, s.size], s)
+            known = [int(x) for x in s if x < V]
+            if not known:
+                assert oid.size == 0
+                continue
+            p = int(np.searchsorted(part_off, known[0], side="right") - 1)
+            lo, hi = int(part_off[p]), int(part_off[p + 1])
+            inside = ["v%d" % x for x in known if lo <= x < hi]
+            want = pyref.khop(graphs[p], inside, k, ["out", "in", "both"][mi], excl)
+            assert {"v%d" % i: int(h) for i, h in zip(oid, hop)} == want
+            assert oid.tolist() == sorted(oid.tolist())
