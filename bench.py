@@ -135,7 +135,7 @@ def run_reference(args, rank, world):
     name_off, arena = synth.pack_names(sg.names)
     svc = ora.RefService(name_off, arena, sg.src, sg.dst, sg.entry, sg.part_off)
     per_step = max(threads, 2 * threads)
-    times = []
+    times, counts = [], []
     pos = 0
     for s in range(args.warmup + args.steps):
         t0 = time.perf_counter()
@@ -144,9 +144,10 @@ def run_reference(args, rank, world):
         pos = (pos + per_step) % (N_QUERIES - per_step)
         if s >= args.warmup:
             times.append(dt)
+            counts.append(per_step)
         if s == 0 and dt * (args.warmup + args.steps) > 240:      # keep the whole run within minutes
             per_step = max(threads, int(per_step * 240 / (dt * (args.warmup + args.steps))))
-    qps = per_step * len(times) / sum(times)
+    qps = sum(counts) / sum(times)
     line = {"impl": "reference", "metric": METRIC, "value": qps, "unit": UNIT, "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * sum(times) / len(times),
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u32",
