@@ -192,20 +192,20 @@ int32_t dmg_graph_set_methods(dmg_graph* g, const uint32_t* method_off, const ui
     return DMG_EINVAL;
   }
   DMG_CUDA(cudaSetDevice(g->eng->device));
-  uint32_t *d_mo = nullptr, *d_no = nullptr;
-  uint8_t* d_b = nullptr;
-  DMG_CUDA(cudaMalloc((void**)&d_mo, ((size_t)V + 1) * 4));
-  DMG_CUDA(cudaMalloc((void**)&d_no, ((size_t)M + 1) * 4));
-  DMG_CUDA(cudaMalloc((void**)&d_b, (size_t)bytes + 16));
-  DMG_CUDA(cudaMemcpy(d_mo, method_off, ((size_t)V + 1) * 4, cudaMemcpyHostToDevice));
-  DMG_CUDA(cudaMemcpy(d_no, name_off, ((size_t)M + 1) * 4, cudaMemcpyHostToDevice));
-  if (bytes) DMG_CUDA(cudaMemcpy(d_b, lower_bytes, bytes, cudaMemcpyHostToDevice));
+  DevMem mo, no, lb;   // freed on every failure path; handed to the graph only when all three are filled
+  DMG_TRY(mo.alloc(((size_t)V + 1) * 4));
+  DMG_TRY(no.alloc(((size_t)M + 1) * 4));
+  DMG_TRY(lb.alloc((size_t)bytes + 16));
+  DMG_CUDA(cudaMemcpy(mo.p, method_off, ((size_t)V + 1) * 4, cudaMemcpyHostToDevice));
+  DMG_CUDA(cudaMemcpy(no.p, name_off, ((size_t)M + 1) * 4, cudaMemcpyHostToDevice));
+  if (bytes) DMG_CUDA(cudaMemcpy(lb.p, lower_bytes, bytes, cudaMemcpyHostToDevice));
   if (g->d_method_off) cudaFree(g->d_method_off);
   if (g->d_mname_off) cudaFree(g->d_mname_off);
   if (g->d_mname_lower) cudaFree(g->d_mname_lower);
-  g->d_method_off = d_mo;
-  g->d_mname_off = d_no;
-  g->d_mname_lower = d_b;
+  g->d_method_off = mo.as<uint32_t>();
+  g->d_mname_off = no.as<uint32_t>();
+  g->d_mname_lower = lb.as<uint8_t>();
+  mo.p = no.p = lb.p = nullptr;   // ownership moved to the graph
   g->n_methods = M;
   return DMG_OK;
 }
