@@ -11,6 +11,13 @@ A "step" is one pass of the hot path over one batch.  Three measurements, one JS
   cpu_baseline  the structure-faithful CPU restatement of the Java path (oracle `ref`) on a bounded
          sample of the same batch, all host cores (rank 0, N = 1 only)
 
+  cpu_baseline_csr  the integer-CSR CPU restatement on the WHOLE batch (context: what a CPU does with
+         the same data structure the GPU uses)
+  parity_checked    after the timed region the resident result of the last timed step is copied to the
+         host and a seeded sample of >= 4,096 rows is compared with the oracle, bit for bit
+  configs  (N = 1) BASELINE configs 3, 4, 5 -- the HBM-bound ones -- measured by bench_configs.py, each
+         with its SURVEY 8d bytes, kernel time, roofline fraction, e2e and its own oracle check
+
 N > 1 (torchrun): the CSR is replicated, every rank runs its own 65,536-query batch (weak
 scaling, no data-path collective); value = all queries / max-over-ranks time.
 
@@ -61,7 +68,7 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.Q,
-                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                          "--format=csv,noheader,nounits", "-lms", "20"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             threading.Thread(target=self._pump, daemon=True).start()
         except Exception:
@@ -125,6 +132,20 @@ def cpu_reference(sg, q_off, q_src, budget_s=15.0, threads=None):
                  "results_per_query": res / n}
 
 
+def cpu_csr(sg, q_off, q_src, threads=None):
+    """The integer-CSR restatement on the whole batch; returns (dict, oracle handle, result)."""
+    from oracle import oracle as ora
+    threads = threads or ora.hardware_threads()
+    o = ora.CsrOracle(sg.n_vertices, sg.src, sg.dst, sg.entry, sg.part_off)
+    t0 = time.perf_counter()
+    res = o.khop_batch(2, K_HOPS, 1, q_off, q_src, threads=threads)
+    dt = time.perf_counter() - t0
+    nq = q_off.size - 1
+    return ({"value": nq / dt, "unit": UNIT, "cores": threads, "kind": "port",
+             "sample": "all %d queries, %.1f s wall; integer-CSR restatement (same results as the string-keyed one, "
+                       "none of its hashing): context, not the baseline of record" % (nq, dt)}, o, res)
+
+
 def run_reference(args, rank, world):
     if rank != 0:
         return
@@ -134,7 +155,7 @@ def run_reference(args, rank, world):
     from dmgraph import synth
     name_off, arena = synth.pack_names(sg.names)
     svc = ora.RefService(name_off, arena, sg.src, sg.dst, sg.entry, sg.part_off)
-    per_step = max(threads, 2 * threads)
+    per_step = 16 * threads      # ~5 s per step at ~50 queries/s on 16 threads; shrunk below if the run would not fit
     times, counts = [], []
     pos = 0
     for s in range(args.warmup + args.steps):
@@ -152,6 +173,7 @@ def run_reference(args, rank, world):
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * sum(times) / len(times),
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u32",
             "data": "synthetic", "config": {"workload": WORKLOAD},
+            "sample_queries_per_step": per_step,
             "cpu_baseline": {"value": qps, "unit": UNIT, "cores": threads, "kind": "port",
                              "sample": "%d queries per step (bounded sample of the 65536-query batch), all host "
                                        "threads; C++ restatement of the Java path, no JVM in this image" % per_step},
@@ -167,6 +189,11 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--cpu-budget", type=float, default=15.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--configs", default="c3,c4,c5", help="N=1: extra BASELINE configs to measure ('' = none)")
+    ap.add_argument("--c3-names", type=int, default=10_000_000)
+    ap.add_argument("--c5-vertices", type=int, default=4_000_000)
+    ap.add_argument("--c5-edges", type=int, default=100_000_000)
+    ap.add_argument("--parity-rows", type=int, default=4096)
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     rank = int(os.environ.get("RANK", "0"))
@@ -225,13 +252,13 @@ def main():
         assert rc == 0 and n == cap
         return eng.last_stats()
 
+    sampler = ClockSampler(local_rank)
+    sampler.start()                         # sampled from warm-up to the end of the e2e loops (20 ms period)
     for _ in range(args.warmup):
         eng.flush_l2()
         step_dev()
     eng.profile(True)
     eng.profile_reset()
-    sampler = ClockSampler(local_rank)
-    sampler.start()
     barrier()
     dev_ms, wall_ms, launches, stats = 0.0, 0.0, 0, None
     for _ in range(args.steps):
@@ -242,7 +269,6 @@ def main():
         dev_ms += stats["device_ms"]
         launches += stats["kernel_launches"]
     barrier()
-    clocks = sampler.stop()
     prof = eng.profile_table()
     eng.profile(False)
     dev_ms_max = allmax(dev_ms)
@@ -253,39 +279,46 @@ def main():
 
     # ---- roofline of the dominant kernel ----------------------------------------------------
     peak, peak_src = peaks()
-    kname = max(prof, key=lambda k: prof[k][1]) if prof else "khop_small"
+    kname = max(prof, key=lambda k: prof[k][1]) if prof else "khop"
     kl, kms = prof.get(kname, (1, dev_ms))
     n_src_total = int(q_off[-1])
+    n_res = int(stats["results"])
     # B_q = sum over expanded u of (8R + 4 deg(u)) + 4 n_sources + 5 n_results, R = 2
-    step_bytes = 16 * stats["rows_expanded"] + 4 * stats["edges_traversed"] + 4 * n_src_total + 5 * stats["results"]
-    stage_bytes = sg.part_off[1] * nq        # one hop byte per project vertex per query
-    if kname == "khop_emit":
-        alg_bytes = int(stage_bytes + 5 * stats["results"] + 16 * nq)
-    else:
-        alg_bytes = int(step_bytes)
-    achieved = alg_bytes / (kms / kl * 1e-3) / 1e9
-    actual_bytes = int(8 * stats["rows_expanded"] + 4 * stats["edges_read"] + 4 * n_src_total + stage_bytes)
-    traffic, issue_pct = None, None
+    step_bytes = 16 * stats["rows_expanded"] + 4 * stats["edges_traversed"] + 4 * n_src_total + 5 * n_res
+    # bytes no implementation can avoid moving once per step: the CSR the step reads (resolve rows:
+    # und_ptr + und_idx), the query batch, the packed result (4 B id + 1 B hop per entry + 8 B row offset)
+    csr_bytes = 4 * (sg.n_vertices + 1) + 4 * 2 * int(g.info["n_edges"])
+    compulsory = csr_bytes + 4 * (nq + 1) + 4 * n_src_total + 5 * n_res + 8 * (nq + 1)
+    step_ms = dev_ms / args.steps
+    traffic, tsrc = None, None
     tpath = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(tpath):
         try:
             tj = json.load(open(tpath))
-            traffic = tj.get(kname)
-            issue_pct = tj.get("issue_active_pct", {}).get(kname)
+            traffic = tj.get("kernels", tj).get(kname)
+            tsrc = tj.get("source")
         except Exception:
             traffic = None
-    roofline = {"bound": "hbm", "kernel": kname, "achieved": achieved, "peak": peak, "unit": "GB/s",
-                "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
-                "algorithmic_bytes_per_launch": alg_bytes, "kernel_ms_per_launch": kms / kl,
-                "bytes_actually_loaded_per_launch": actual_bytes,
-                "whole_step_algorithmic_bytes": int(step_bytes),
-                "whole_step_achieved_GBs": step_bytes / (dev_ms / args.steps * 1e-3) / 1e9,
+    kernel_ms = kms / kl
+    kernel_launches_per_step = kl / args.steps
+    roofline = {"bound": "hbm", "kernel": kname, "achieved": step_bytes / (kernel_ms * kernel_launches_per_step * 1e-3) / 1e9,
+                "peak": peak, "unit": "GB/s", "traffic": traffic, "traffic_source": tsrc, "peak_source": peak_src,
+                "algorithmic_bytes_per_step": int(step_bytes), "kernel_ms_per_launch": kernel_ms,
+                "kernel_launches_per_step": kernel_launches_per_step,
                 "kernel_share_of_step": kms / dev_ms if dev_ms else None,
-                "ncu_issue_active_pct": issue_pct,   # from the committed ncu capture, not measured in this run
-                "note": "algorithmic bytes follow SURVEY.md 8d (every adjacency entry of every expanded vertex); "
-                        "bottom-up levels stop at the first frontier member, so fewer entries are loaded "
-                        "(edges_read), and this config's CSR (25 MB) is L2-resident: frac can exceed what HBM "
-                        "alone would allow; see profiles/ for DRAM vs L2 bytes"}
+                "cache_resident": True,
+                "compulsory_bytes": int(compulsory),
+                "compulsory_breakdown": {"csr": int(csr_bytes), "queries": int(4 * (nq + 1) + 4 * n_src_total),
+                                         "packed_result": int(5 * n_res + 8 * (nq + 1))},
+                "frac_compulsory": compulsory / (step_ms * 1e-3) / 1e9 / peak,
+                "whole_step_ms": step_ms,
+                "edges_loaded_per_step": int(stats["edges_read"]),
+                "note": "frac = SURVEY 8d definitional bytes (every adjacency entry of every expanded vertex, per query) "
+                        "over the dominant kernel's time: this config's 25 MB CSR is L2-resident and shared by all "
+                        "queries of a project, so frac is NOT an HBM fraction (cache_resident). frac_compulsory = bytes "
+                        "the step cannot avoid (CSR once + queries + packed result) over the WHOLE step's time: that "
+                        "one is a fraction of the HBM roofline. HBM-bound configs: see configs.c3/c4/c5"}
+    roofline["frac"] = roofline["achieved"] / peak
 
     # ---- e2e: host buffers through the reference-facing call --------------------------------
     h_q_off, p1 = eng.pinned(np.uint32, nq + 1)
@@ -323,14 +356,36 @@ def main():
             dense_ms += dt
             dense_d2h = eng.last_stats()["d2h_bytes"]
     dense_ms_max = allmax(dense_ms)
+    clocks = sampler.stop()
+
+    # ---- parity of what was just timed: last step's resident result vs the oracle --------------
+    parity = None
+    csr_line = None
+    if rank == 0 and not args.no_cpu_baseline:
+        from oracle import checks
+        off_h = eng.to_host(d_out_off, np.uint64, nq + 1)
+        ids_h = eng.to_host(d_out_ids, np.uint32, cap)
+        hop_h = eng.to_host(d_out_hop, np.uint8, cap)
+        if world == 1:
+            csr_line, o, res = cpu_csr(sg, q_off, q_src)
+            assert np.array_equal(off_h, res[0]) and np.array_equal(ids_h, res[1]) and np.array_equal(hop_h, res[2]), \
+                "bench: the timed result differs from the oracle"
+            parity = {"rows": int(nq), "against": "oracle csr, whole batch (ids, hops, offsets bit-exact)"}
+        else:
+            from oracle import oracle as ora
+            o = ora.CsrOracle(sg.n_vertices, sg.src, sg.dst, sg.entry, sg.part_off)
+            rows = np.sort(np.random.Generator(np.random.PCG64(7)).choice(nq, min(nq, args.parity_rows), replace=False))
+            n_chk = checks.check_khop_rows(o, 2, K_HOPS, 1, q_off, q_src, off_h, ids_h, hop_h, rows=rows)
+            parity = {"rows": int(n_chk), "against": "oracle csr, seeded row sample of rank 0's batch"}
+
 
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": dev_ms_max / args.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "u32", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "l2": "flushed before every timed step (write of 2x L2 size)",
-                       "timing": "CUDA events on libdmgraph's launch stream, summed over steps, max over ranks",
-                       "results_per_step": int(stats["results"]), "sources_per_step": n_src_total,
-                       "graph_upload_s": upload_s},
+            "config": {"workload": WORKLOAD},
+            "details": {"l2": "flushed before every timed step (write of 2x L2 size)",
+                        "timing": "CUDA events on libdmgraph's launch stream, summed over steps, max over ranks",
+                        "results_per_step": n_res, "sources_per_step": n_src_total, "graph_upload_s": upload_s},
             "gteps": gteps, "edges_traversed_per_step": int(edges), "edges_read_per_step": int(stats["edges_read"]),
             "wall_ms_per_step": allmax(wall_ms) / args.steps,
             "roofline": roofline,
@@ -340,18 +395,43 @@ def main():
                                "ms_per_step": dense_ms_max / args.steps, "d2h_bytes_per_step": int(dense_d2h),
                                "call": "dmg_neighbors_batch_rows (same sets and hops, one byte per project vertex)"},
             "gpu_launches": int(launches), "clocks": clocks,
+            "parity_checked": parity["rows"] if parity else 0, "parity": parity,
             "kernels": {k: {"launches": int(v[0]), "ms_per_launch": v[1] / v[0]} for k, v in prof.items()}}
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         _qps, cb = cpu_reference(sg, q_off, q_src, budget_s=args.cpu_budget)
         line["cpu_baseline"] = cb
+        line["cpu_baseline_csr"] = csr_line
     elif rank == 0:
         line["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": 0, "kind": "port",
                                 "sample": "measured at N=1 only"}
-    if rank == 0:
-        print(json.dumps(line), flush=True)
     for p in (p1, p2, p3, p4, p5, p6, p7):
         eng.pinned_free(p)
     g.release()
+    for d in (d_q_off, d_q_src, d_out_off, d_out_ids, d_out_hop):
+        eng.device_free(d)
+
+    # ---- the HBM-bound configs (N = 1): each block carries its own roofline, e2e and oracle check ----
+    if rank == 0 and world == 1 and args.configs:
+        import bench_configs as bc
+        blocks = {}
+        for name in [c for c in args.configs.split(",") if c]:
+            t0 = time.perf_counter()
+            try:
+                if name == "c3":
+                    blocks[name] = bc.run_c3(eng, args.c3_names)
+                elif name == "c4":
+                    blocks[name] = bc.run_c4(eng)
+                elif name == "c5":
+                    blocks[name] = bc.run_c5(eng, args.c5_vertices, args.c5_edges)
+                else:
+                    blocks[name] = {"error": "unknown config"}
+            except Exception as ex:      # the headline line must survive a failing block, and show it
+                blocks[name] = {"error": "%s: %s" % (type(ex).__name__, ex)}
+            blocks[name]["block_wall_s"] = time.perf_counter() - t0
+        line["configs"] = blocks
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    eng.close()
     if dist is not None:
         dist.destroy_process_group()
 

@@ -1,15 +1,18 @@
 #!/usr/bin/env python3
-"""Measurements for the BASELINE configs that bench.py (config 2, the headline) does not cover.
-One JSON line per run; results are kept under profiles/.
+"""Measurements for the BASELINE configs beside the headline (config 2): the HBM-bound ones.
+bench.py calls these at N = 1 and puts their dicts under "configs" in its JSON line; run alone,
+one JSON line per config is printed (kept under profiles/).
 
   python bench_configs.py c3 [--names N] [--queries Q]     search_project scan (S1)
-  python bench_configs.py c4 [--vertices V] [--edges E]    adjacency rows + directed k-hop on one big graph
-  python bench_configs.py c4mix [--ops N]                  the SURVEY 8d config-4 DSL mix in one dmg_query_batch
+  python bench_configs.py c4 [--vertices V] [--edges E]    adjacency rows, directed k-hop, the DSL mix
   python bench_configs.py c5 [--vertices V] [--edges E]    closure levels + exact analysisOrder
 
-Per-kernel times are CUDA events on the library's launch stream (dmg_profile_*); e2e is the
-wall clock of the host-pointer C-ABI call.  The CPU numbers are the oracle's restatements on the
-box's host cores (test infrastructure used as the timed baseline only).
+Every block reports: kernel time per batch (CUDA events on the library's launch stream, L2 flushed
+before each timed call), SURVEY.md 8d algorithmic bytes and their fraction of the measured HBM peak,
+e2e through the host-pointer C-ABI call (pinned host buffers, copies inside the timed region), an
+oracle check of the very results that were timed (`parity_checked` = rows compared), and a CPU figure
+from the oracle's restatements on the box's host cores (test infrastructure used as checker and
+timed baseline only).
 """
 import argparse
 import json
@@ -33,292 +36,287 @@ except Exception:
     pass
 
 
-def kernels(eng):
-    return {k: {"launches": int(v[0]), "ms_total": v[1]} for k, v in eng.profile_table().items()}
+def kernels(eng, steps=1):
+    return {k: {"launches": int(v[0]), "ms_per_batch": v[1] / steps} for k, v in eng.profile_table().items()}
 
 
-def run_c3(args):
-    from oracle import oracle as ora
-    eng = dmgraph.Engine(0)
-    t0 = time.perf_counter()
-    off, arena = synth.catalog_names(args.names)
-    low = np.frombuffer(bytes(arena).lower(), dtype=np.uint8).copy()
-    queries = synth.search_queries(off, arena, args.queries)
-    gen_s = time.perf_counter() - t0
-    g = dmgraph.Graph(eng, off.size - 1, [], [], [], name_off=off, name_bytes=arena, lower_bytes=low)
-    qbytes = sum(len(q) for q in queries)
-    # sizing call, then timed calls with an exact capacity
-    o, ids = g.search_batch(dmgraph.SEARCH_CONTAINS_ALL, queries)
-    H = int(o[-1])
-    times, dev = [], []
+def roofline(alg_bytes, kernel_ms, **extra):
+    ach = alg_bytes / (kernel_ms * 1e-3) / 1e9 if kernel_ms else None
+    d = {"bound": "hbm", "unit": "GB/s", "peak": HBM, "algorithmic_bytes": int(alg_bytes), "kernel_ms": kernel_ms,
+         "achieved": ach, "frac": ach / HBM if ach else None}
+    d.update(extra)
+    return d
+
+
+def timed_calls(eng, fn, steps, warmup=1):
+    """fn() is one host-pointer C-ABI call.  Returns (kernel ms per call from the per-launch events,
+    per-kernel table, median wall ms, stats of the last call, last return value)."""
+    r = None
+    for _ in range(warmup):
+        r = fn()
     eng.profile(True)
     eng.profile_reset()
-    for it in range(args.warmup + args.steps):
+    wall = []
+    for _ in range(steps):
         eng.flush_l2()
-        if it == args.warmup:
-            eng.profile_reset()
         t0 = time.perf_counter()
-        o2, ids2 = g.search_batch(dmgraph.SEARCH_CONTAINS_ALL, queries, cap=H)
-        dt = time.perf_counter() - t0
-        if it >= args.warmup:
-            times.append(dt)
-            dev.append(eng.last_stats()["device_ms"])
-    kt = kernels(eng)
-    assert np.array_equal(o, o2) and np.array_equal(ids, ids2)
-    kernel_ms = sum(v["ms_total"] for v in kt.values()) / args.steps
-    A = int(off[-1])
-    N = off.size - 1
-    alg = A + 4 * (N + 1) + qbytes + 4 * H + 4 * (len(queries) + 1)      # SURVEY.md 8d, single-pass minimum
-    scan_ms = kt.get("search_scan", {"ms_total": 0})["ms_total"] / args.steps
-    emit_ms = kt.get("search_emit", {"ms_total": 0})["ms_total"] / args.steps
-    # CPU: csr-style (memmem over the lowered arena) on a query sample, all threads
-    threads = ora.hardware_threads()
-    ns = max(threads, min(len(queries), 4 * threads))
-    t0 = time.perf_counter()
-    ora.search_batch(off, low, queries[:ns], 0, threads=threads)
-    cpu_s = time.perf_counter() - t0
-    line = {"config": "c3", "workload": "search_project scan: %d names (%.0f MB arena), %d queries, %d hits" % (N, A / 1e6, len(queries), H),
-            "metric": "search_queries_per_sec", "unit": "queries/s",
-            "value_kernels": len(queries) / (kernel_ms * 1e-3), "kernel_ms_per_batch": kernel_ms,
-            "e2e": {"value": len(queries) / np.median(times), "ms_per_batch": 1e3 * float(np.median(times)),
-                    "device_ms": float(np.median(dev)), "d2h_bytes": 4 * H + 8 * (len(queries) + 1)},
-            "roofline": {"bound": "hbm", "unit": "GB/s", "peak": HBM, "algorithmic_bytes": alg,
-                         "achieved_whole_batch": alg / (kernel_ms * 1e-3) / 1e9,
-                         "frac_whole_batch": alg / (kernel_ms * 1e-3) / 1e9 / HBM,
-                         "match_pass_GBs": (A + 4 * N) / (scan_ms * 1e-3) / 1e9 if scan_ms else None,
-                         "emit_pass_GBs": (A + 4 * N + 4 * H) / (emit_ms * 1e-3) / 1e9 if emit_ms else None,
-                         "effective_scan_rate_TBs": len(queries) * A / (kernel_ms * 1e-3) / 1e12},
-            "kernels": kt,
-            "cpu_baseline": {"kind": "port", "cores": threads, "unit": "queries/s", "value": ns / cpu_s,
-                             "sample": "%d of %d queries over all %d names, memmem over the pre-lowered arena (csr "
-                                       "restatement; the string-allocating ref variant is slower)" % (ns, len(queries), N)},
-            "generate_s": gen_s}
-    print(json.dumps(line), flush=True)
-    g.release()
-    eng.close()
+        r = fn()
+        wall.append(1e3 * (time.perf_counter() - t0))
+    st = eng.last_stats()
+    kt = kernels(eng, steps)
+    eng.profile(False)
+    return sum(v["ms_per_batch"] for v in kt.values()), kt, float(np.median(wall)), st, r
 
 
-def run_c4(args):
+# ---------------------------------------------------------------------------------------------------
+def run_c3(eng, names=10_000_000, n_queries=16384, steps=3, check_queries=4096, cpu_budget_s=10.0):
     from oracle import oracle as ora
-    eng = dmgraph.Engine(0)
     t0 = time.perf_counter()
-    sg = synth.big_graph(args.vertices, args.edges, cap=500, entry_frac=0.01, seed=synth.SEED_C4)
+    off, arena = synth.catalog_names(names)
+    low = np.frombuffer(bytes(arena).lower(), dtype=np.uint8).copy()
+    queries = synth.search_queries(off, arena, n_queries)
     gen_s = time.perf_counter() - t0
     t0 = time.perf_counter()
-    g = dmgraph.Graph(eng, sg.n_vertices, sg.src, sg.dst, sg.entry)
+    g = dmgraph.Graph(eng, off.size - 1, [], [], [], name_off=off, name_bytes=arena, lower_bytes=low)
     upload_s = time.perf_counter() - t0
-    rng = np.random.Generator(np.random.PCG64(synth.SEED_C4 + 1))
-    nq = args.queries
-    ids = rng.integers(0, sg.n_vertices, nq).astype(np.uint32)
-    out = {"config": "c4", "workload": "one graph %d V / %d E, %d ids per primitive batch" % (sg.n_vertices, g.info["n_edges"], nq),
-           "generate_s": gen_s, "upload_s": upload_s, "primitives": {}}
-    eng.profile(True)
-
-    def timed(name, fn, bytes_fn):
-        fn()
-        eng.profile_reset()
-        ts = []
-        for _ in range(args.steps):
-            eng.flush_l2()
-            t0 = time.perf_counter()
-            r = fn()
-            ts.append(time.perf_counter() - t0)
-        st = eng.last_stats()
-        kt = kernels(eng)
-        kms = sum(v["ms_total"] for v in kt.values()) / args.steps
-        b = bytes_fn(st)
-        out["primitives"][name] = {"queries_per_s_kernels": nq / (kms * 1e-3), "kernel_ms": kms,
-                                   "e2e_ms": 1e3 * float(np.median(ts)), "results": int(st["results"]),
-                                   "edges_traversed": int(st["edges_traversed"]),
-                                   "gteps": st["edges_traversed"] / (kms * 1e-3) / 1e9,
-                                   "algorithmic_bytes": int(b), "achieved_GBs": b / (kms * 1e-3) / 1e9,
-                                   "frac_of_hbm": b / (kms * 1e-3) / 1e9 / HBM, "kernels": kt}
-        return r
-
-    q_off = np.arange(nq + 1, dtype=np.uint32)
-    timed("dependencies (adjacency OUT)", lambda: g.adjacency_batch(dmgraph.OUT, ids),
-          lambda st: 12 * nq + 8 * st["results"] + 8 * nq)
-    timed("dependents (adjacency IN)", lambda: g.adjacency_batch(dmgraph.IN, ids),
-          lambda st: 12 * nq + 8 * st["results"] + 8 * nq)
-    for k in (1, 2, 3):
-        timed("k-hop OUT k=%d" % k, lambda k=k: g.neighbors_batch(dmgraph.OUT, k, 0, q_off[:nq // 8 + 1], ids[:nq // 8]),
-              lambda st: 8 * st["rows_expanded"] + 4 * st["edges_traversed"] + 4 * (nq // 8) + 5 * st["results"])
-    print(json.dumps(out), flush=True)
-    g.release()
-    eng.close()
-
-
-def run_c4mix(args):
-    """BASELINE config 4 as SURVEY.md 8d states it: one 1 M / 30 M graph, a batch of resolved DSL
-    queries in the stated mix (40 % dependencies, 20 % dependents, 15 % overview, 10 % k-hop OUT
-    k in {2,3,4}, 5 % simple-name resolution, 5 % ?check, 3 % entrypoints, 2 % endpoints) through ONE
-    dmg_query_batch call with host buffers."""
-    from oracle import oracle as ora
-    eng = dmgraph.Engine(0)
+    q_off = np.zeros(len(queries) + 1, np.uint32)
+    np.cumsum([len(q) for q in queries], out=q_off[1:])
+    qb = np.frombuffer(b"".join(queries) + b"\0", dtype=np.uint8).copy()
+    # sizing call (capacity 0 answers DMG_ECAP with `needed`), then timed calls into pinned buffers
+    import ctypes as C
+    need = C.c_uint64(0)
+    off0 = np.zeros(len(queries) + 1, np.uint64)
+    g.L.dmg_search_batch(g.h, dmgraph.SEARCH_CONTAINS_ALL, 0, g.V, len(queries), q_off.ctypes.data, qb.ctypes.data,
+                         off0.ctypes.data, None, 0, C.byref(need))
+    H = int(need.value)
+    h_off, p1 = eng.pinned(np.uint64, len(queries) + 1)
+    h_ids, p2 = eng.pinned(np.uint32, max(H, 1))
+    kms, kt, wall_ms, st, _r = timed_calls(
+        eng, lambda: g.search_batch(dmgraph.SEARCH_CONTAINS_ALL, (q_off, qb), out=(h_off, h_ids)), steps)
+    A, N, Q = int(off[-1]), off.size - 1, len(queries)
+    alg = A + 4 * (N + 1) + int(q_off[-1]) + 4 * H + 4 * (Q + 1)          # SURVEY.md 8d, single-pass minimum
+    # oracle check of the timed result: Aho-Corasick over ALL names for a seeded sample of the queries
+    threads = ora.hardware_threads()
+    rng = np.random.Generator(np.random.PCG64(33))
+    sample = np.sort(rng.choice(Q, min(Q, check_queries), replace=False))
     t0 = time.perf_counter()
-    sg = synth.big_graph(args.vertices, args.edges, cap=500, entry_frac=0.01, seed=synth.SEED_C4, with_names=True)
+    wo, wids = ora.search_batch_ac(off, low, [queries[i] for i in sample], threads=threads)
+    check_s = time.perf_counter() - t0
+    for j, i in enumerate(sample):
+        a, b = int(h_off[i]), int(h_off[i + 1])
+        assert b - a == int(wo[j + 1] - wo[j]) and np.array_equal(h_ids[a:b], wids[int(wo[j]):int(wo[j + 1])]), \
+            "c3: hits of query %d differ from the oracle" % i
+    # CPU baseline: the restatement's loop (one contains() per query and name) on a bounded sample
+    ns = threads
+    t0 = time.perf_counter()
+    ora.search_batch(off, low, queries[:ns], 0, threads=threads)
+    dt = time.perf_counter() - t0
+    ns2 = int(min(Q, max(threads, (cpu_budget_s / max(dt, 1e-6)) * ns)) // threads * threads)
+    if ns2 > ns:
+        t0 = time.perf_counter()
+        ora.search_batch(off, low, queries[:ns2], 0, threads=threads)
+        dt, ns = time.perf_counter() - t0, ns2
+    out = {"workload": "c3: search_project scan, %d names (%.0f MB arena), %d queries, %d ordered hits" % (N, A / 1e6, Q, H),
+           "metric": "search_queries_per_sec", "unit": "queries/s", "value": Q / (kms * 1e-3),
+           "kernel_ms_per_batch": kms, "kernels": kt,
+           "roofline": roofline(alg, kms, effective_scan_rate_TBs=Q * A / (kms * 1e-3) / 1e12,
+                                note="bytes = arena + offsets + query text + 4 B per hit + row offsets (one pass)"),
+           "e2e": {"value": Q / (wall_ms * 1e-3), "unit": "queries/s", "ms_per_batch": wall_ms,
+                   "device_ms": st["device_ms"], "h2d_bytes": int(st["h2d_bytes"]), "d2h_bytes": int(st["d2h_bytes"]),
+                   "host_buffers": "pinned"},
+           "parity_checked": int(sample.size), "parity_against": "oracle (Aho-Corasick form, all names)",
+           "parity_check_s": check_s,
+           "cpu_baseline": {"kind": "port", "cores": threads, "unit": "queries/s", "value": ns / dt,
+                            "sample": "%d of %d queries over all %d names: contains() per (query, name) on the "
+                                      "pre-lowered arena, %.1f s" % (ns, Q, N, dt)},
+           "generate_s": gen_s, "upload_s": upload_s}
+    eng.pinned_free(p1)
+    eng.pinned_free(p2)
+    g.release()
+    return out
+
+
+# ---------------------------------------------------------------------------------------------------
+def run_c4(eng, vertices=1_000_000, edges=30_000_000, n_ids=262_144, n_khop=32_768, n_ops=262_144, steps=3,
+           ops_per_call=16_384, check_rows=4096):
+    from oracle import checks
+    from oracle import oracle as ora
+    threads = ora.hardware_threads()
+    t0 = time.perf_counter()
+    sg = synth.big_graph(vertices, edges, cap=500, entry_frac=0.01, seed=synth.SEED_C4, with_names=True)
     V = sg.n_vertices
     off, arena = synth.pack_names(sg.names)
     low = np.frombuffer(bytes(arena).lower(), dtype=np.uint8).copy()
-    # 10 methods per vertex, 8 lower-case bytes each: 4-letter verb + 4 hex digits of (7 v + j)
-    verbs = np.frombuffer(b"findsavelistloadsendreadpushpullopenstop", dtype=np.uint8).reshape(10, 4)
-    num = ((np.arange(V, dtype=np.int64)[:, None] * 7 + np.arange(10)[None, :]) & 0xFFFF)
-    hexd = np.frombuffer(b"0123456789abcdef", dtype=np.uint8)
-    digits = hexd[(num[:, :, None] >> np.array([12, 8, 4, 0])[None, None, :]) & 15]
-    mbytes = np.concatenate([np.broadcast_to(verbs[None, :, :], (V, 10, 4)), digits], axis=2).reshape(-1)
+    mo, no, mbytes = synth.method_catalog(V)
     gen_s = time.perf_counter() - t0
     t0 = time.perf_counter()
     g = dmgraph.Graph(eng, V, sg.src, sg.dst, sg.entry, name_off=off, name_bytes=arena, lower_bytes=low)
-    g.set_methods_packed(np.arange(V + 1, dtype=np.uint32) * 10, np.arange(10 * V + 1, dtype=np.uint32) * 8, mbytes)
+    g.set_methods_packed(mo, no, mbytes)
     rng = np.random.Generator(np.random.PCG64(synth.SEED_C4 + 2))
-    ctrl = rng.random(V) < 0.01                                  # 1 % controllers: all their methods are endpoints
-    g.set_method_flags(np.repeat(ctrl.astype(np.uint8), 10))
+    flags = np.repeat((rng.random(V) < 0.01).astype(np.uint8), 10)      # 1 % controllers: their methods are endpoints
+    g.set_method_flags(flags)
+    endpoint_methods = np.flatnonzero(flags).astype(np.uint32)
     upload_s = time.perf_counter() - t0
-
-    def make_ops(n):
-        r = np.random.Generator(np.random.PCG64(synth.SEED_C4 + 3))
-        u = r.random(n)
-        edges_ = np.cumsum([0.40, 0.20, 0.15, 0.10, 0.05, 0.05, 0.03, 0.02])
-        kind = np.searchsorted(edges_, u, side="right").clip(0, 7)
-        opcode = np.array([dmgraph.OP_DEPENDENCIES, dmgraph.OP_DEPENDENTS, dmgraph.OP_OVERVIEW, dmgraph.OP_KHOP,
-                           dmgraph.OP_RESOLVE_NAME, dmgraph.OP_METHOD, dmgraph.OP_ENTRYPOINTS, dmgraph.OP_ENDPOINTS],
-                          np.uint32)[kind]
-        ops = np.zeros(n, dmgraph.Graph.QUERY_OP_DTYPE)
-        ops["opcode"] = opcode
-        ops["vertex"] = r.integers(0, V, n)
-        ops["mode"] = dmgraph.OUT
-        ops["k"] = np.where(opcode == dmgraph.OP_KHOP, r.integers(2, 5, n), 1)
-        text = bytearray()
-        for i in np.flatnonzero((opcode == dmgraph.OP_RESOLVE_NAME) | (opcode == dmgraph.OP_METHOD)):
-            v = int(ops["vertex"][i])
-            if opcode[i] == dmgraph.OP_RESOLVE_NAME:
-                t = sg.names[v].rsplit(".", 1)[-1].lower().encode()
-            elif r.random() < 0.8:
-                j = int(r.integers(0, 10))
-                t = bytes(mbytes[(v * 10 + j) * 8:(v * 10 + j + 1) * 8])
-            else:
-                t = b"nosuchmethod"
-            ops["text_begin"][i] = len(text)
-            text += t
-            ops["text_end"][i] = len(text)
-        return ops, np.frombuffer(bytes(text) + b"\0", dtype=np.uint8).copy(), kind
-
-    n = args.ops
-    while True:
-        ops, text, kind = make_ops(n)
-        t0 = time.perf_counter()
-        need = g.query_batch_packed(ops, text)
-        size_s = time.perf_counter() - t0
-        if need <= args.max_results or n <= 1024:
-            break
-        n //= 2
-    off_o, _p0 = eng.pinned(np.uint64, n + 1)
-    ids, _p1 = eng.pinned(np.uint32, max(need, 1))
-    aux, _p2 = eng.pinned(np.uint8, max(need, 1))
-    eng.profile(True)
-    ts = []
-    for it in range(1 + args.steps):
-        eng.profile_reset()
-        t0 = time.perf_counter()
-        got = g.query_batch_packed(ops, text, out=(off_o, ids, aux))
-        ts.append(time.perf_counter() - t0)
-    assert got == need
-    kt = kernels(eng)
-    kms = sum(v["ms_total"] for v in kt.values())
-    # spot check against the csr restatement
     o = ora.CsrOracle(V, sg.src, sg.dst, sg.entry)
+    rng = np.random.Generator(np.random.PCG64(synth.SEED_C4 + 1))
+    ids = rng.integers(0, V, n_ids).astype(np.uint32)
+    out = {"workload": "c4: one graph %d V / %d E; %d ids per adjacency batch, %d queries per k-hop batch, "
+                       "%d DSL ops in the SURVEY 8d mix" % (V, g.info["n_edges"], n_ids, n_khop, n_ops),
+           "generate_s": gen_s, "upload_s": upload_s, "primitives": {}}
     checked = 0
-    for i in np.random.Generator(np.random.PCG64(1)).choice(n, min(n, 300), replace=False):
-        a, b = int(off_o[i]), int(off_o[i + 1])
-        v, op = int(ops["vertex"][i]), int(ops["opcode"][i])
-        if op == dmgraph.OP_DEPENDENCIES:
-            assert ids[a:b].tolist() == o.adjacency_batch(0, [v])[1].tolist()
-        elif op == dmgraph.OP_DEPENDENTS:
-            assert ids[a:b].tolist() == o.adjacency_batch(1, [v])[1].tolist()
-        elif op == dmgraph.OP_KHOP:
-            _o, wi, wh, _te = o.khop_batch(0, int(ops["k"][i]), 0, [0, 1], [v])
-            assert ids[a:b].tolist() == wi.tolist() and aux[a:b].tolist() == wh.tolist()
-        elif op == dmgraph.OP_ENTRYPOINTS:
-            assert ids[a:b].tolist() == o.entry_points().tolist()
-        else:
-            continue
-        checked += 1
-    names_k = ["dependencies", "dependents", "overview", "khop", "resolve_name", "method", "entrypoints", "endpoints"]
-    line = {"config": "c4mix", "workload": "one graph %d V / %d E, %d DSL ops in the SURVEY 8d mix, one dmg_query_batch call "
-                                           "(pinned host buffers)" % (V, g.info["n_edges"], n),
-            "ops_requested": args.ops, "ops_run": n, "results": int(need),
-            "op_counts": {names_k[k]: int((kind == k).sum()) for k in range(8)},
-            "metric": "dsl_ops_per_sec", "unit": "ops/s",
-            "e2e": {"value": n / float(np.median(ts[1:])), "ms_per_batch": 1e3 * float(np.median(ts[1:])),
-                    "sizing_call_ms": 1e3 * size_s, "result_bytes": int(5 * need + 8 * (n + 1))},
-            "kernel_ms_per_batch": kms, "kernels": kt, "rows_checked_against_oracle": checked,
-            "note": "k-hop groups run as device batches (count pass + fetch pass), rows are assembled on the device; "
-                    "e2e minus kernel time is host grouping, per-call allocations and the PCIe copy of the result",
-            "generate_s": gen_s, "upload_s": upload_s}
-    print(json.dumps(line), flush=True)
-    g.release()
-    eng.close()
 
+    def record(name, nq, kms, kt, wall_ms, st, alg):
+        out["primitives"][name] = {
+            "queries_per_s": nq / (kms * 1e-3), "kernel_ms": kms, "kernels": kt, "results": int(st["results"]),
+            "edges_traversed": int(st["edges_traversed"]), "gteps": st["edges_traversed"] / (kms * 1e-3) / 1e9,
+            "roofline": roofline(alg, kms),
+            "e2e": {"ms": wall_ms, "h2d_bytes": int(st["h2d_bytes"]), "d2h_bytes": int(st["d2h_bytes"])}}
 
-def run_c5(args):
-    from oracle import oracle as ora
-    eng = dmgraph.Engine(0)
+    pins = []
+
+    def pinned_out(n_rows, entries, with_hop):
+        bufs = [eng.pinned(np.uint64, n_rows + 1), eng.pinned(np.uint32, max(entries, 1))]
+        if with_hop:
+            bufs.append(eng.pinned(np.uint8, max(entries, 1)))
+        pins.extend(p for _a, p in bufs)
+        return tuple(a for a, _p in bufs)
+
+    for name, d in (("dependencies", dmgraph.OUT), ("dependents", dmgraph.IN)):
+        n_res = int(g.adjacency_batch(d, ids)[0][-1])                       # sizing, untimed
+        bufs = pinned_out(n_ids, n_res, False)
+        kms, kt, wall, st, r = timed_calls(eng, lambda d=d, bufs=bufs: g.adjacency_batch(d, ids, out=bufs), steps)
+        # SURVEY 8d per id: 8 B row pointers + 4 B per entry read, 4 B per entry + 8 B offset written, 4 B id
+        record(name, n_ids, kms, kt, wall, st, 20 * n_ids + 8 * st["results"])
+        woff, wids = o.adjacency_batch(d, ids)
+        assert np.array_equal(r[0], woff) and np.array_equal(r[1], wids), "c4 %s differs from the oracle" % name
+        checked += n_ids
+    q_off = np.arange(n_khop + 1, dtype=np.uint32)
+    ksrc = ids[:n_khop]
+    for k in (1, 2, 3):
+        n_res = int(g.neighbors_batch(dmgraph.OUT, k, 0, q_off, ksrc)[0][-1])   # sizing, untimed
+        bufs = pinned_out(n_khop, n_res, True)
+        kms, kt, wall, st, r = timed_calls(
+            eng, lambda k=k, bufs=bufs: g.neighbors_batch(dmgraph.OUT, k, 0, q_off, ksrc, out=bufs), steps)
+        record("khop_out_k%d" % k, n_khop, kms, kt, wall, st,
+               8 * st["rows_expanded"] + 4 * st["edges_traversed"] + 4 * n_khop + 5 * st["results"])
+        rows = np.sort(np.random.Generator(np.random.PCG64(k)).choice(n_khop, min(n_khop, 1024), replace=False))
+        checked += checks.check_khop_rows(o, 0, k, 0, q_off, ksrc, r[0], r[1], r[2], rows=rows, threads=threads)
+
+    # the DSL mix at the stated batch size, in calls of ops_per_call operations (one call's packed result
+    # has to fit the host's buffers: the endpoint / entry-point rows alone are ~100 k entries each)
+    ops, text, kind = synth.c4_mix_ops(n_ops, sg.names, mbytes, dmgraph.Graph.QUERY_OP_DTYPE)
+    chunks = [(a, min(n_ops, a + ops_per_call)) for a in range(0, n_ops, ops_per_call)]
     t0 = time.perf_counter()
-    sg = synth.big_graph(args.vertices, args.edges, cap=2000, entry_frac=0.01, seed=synth.SEED_C5)
+    needs = [g.query_batch_packed(ops[a:b], text) for a, b in chunks]
+    sizing_s = time.perf_counter() - t0
+    cap = max(max(needs), 1)
+    h_off, p1 = eng.pinned(np.uint64, ops_per_call + 1)
+    h_ids, p2 = eng.pinned(np.uint32, cap)
+    h_aux, p3 = eng.pinned(np.uint8, cap)
+    rng = np.random.Generator(np.random.PCG64(5))
+    want_rows = np.sort(rng.choice(n_ops, min(n_ops, check_rows), replace=False))
+    eng.profile(True)
+    eng.profile_reset()
+    mix_checked, d2h, h2d = 0, 0, 0
+    t0 = time.perf_counter()
+    call_s = 0.0
+    for (a, b), need in zip(chunks, needs):
+        t1 = time.perf_counter()
+        got = g.query_batch_packed(ops[a:b], text, out=(h_off[:b - a + 1], h_ids, h_aux))
+        call_s += time.perf_counter() - t1
+        assert got == need
+        st = eng.last_stats()
+        d2h += st["d2h_bytes"]
+        h2d += st["h2d_bytes"]
+        rows = want_rows[(want_rows >= a) & (want_rows < b)] - a
+        mix_checked += checks.check_query_mix(o, ops[a:b], text, h_off, h_ids, h_aux, off, low, mbytes,
+                                              endpoint_methods, rows=rows, threads=threads)
+    kt = kernels(eng)
+    eng.profile(False)
+    kms = sum(v["ms_per_batch"] for v in kt.values())
+    total = int(sum(needs))
+    names_k = [k for k, _ in synth.C4_MIX]
+    out["mix"] = {"ops": n_ops, "calls": len(chunks), "results": total,
+                  "op_counts": {names_k[k]: int((kind == k).sum()) for k in range(8)},
+                  "metric": "dsl_ops_per_sec", "unit": "ops/s", "value": n_ops / (kms * 1e-3), "kernel_ms": kms,
+                  "kernels": kt,
+                  "roofline": roofline(5 * total + 8 * (n_ops + len(chunks)) + 32 * n_ops, kms,
+                                       note="bytes = packed result (4 B id + 1 B aux per entry) + offsets + ops; "
+                                            "the rows are copies of resident CSR rows / k-hop rows"),
+                  "e2e": {"value": n_ops / call_s, "unit": "ops/s", "ms": 1e3 * call_s, "h2d_bytes": int(h2d),
+                          "d2h_bytes": int(d2h), "host_buffers": "pinned", "sizing_calls_s": sizing_s},
+                  "parity_checked": int(mix_checked), "opcodes_checked": sorted({names_k[k] for k in kind[want_rows]})}
+    out["parity_checked"] = int(checked + mix_checked)
+    out["parity_against"] = "oracle csr (adjacency: whole batches; k-hop and mix: seeded row samples, every opcode)"
+    for p in [p1, p2, p3] + pins:
+        eng.pinned_free(p)
+    g.release()
+    return out
+
+
+# ---------------------------------------------------------------------------------------------------
+def run_c5(eng, vertices=4_000_000, edges=100_000_000, steps=3):
+    from oracle import oracle as ora
+    t0 = time.perf_counter()
+    sg = synth.big_graph_fast(vertices, edges, cap=2000, entry_frac=0.01, seed=synth.SEED_C5)
     gen_s = time.perf_counter() - t0
     t0 = time.perf_counter()
     g = dmgraph.Graph(eng, sg.n_vertices, sg.src, sg.dst, sg.entry)
     upload_s = time.perf_counter() - t0
-    eng.profile(True)
-    out = {"config": "c5", "workload": "closure on %d V / %d E (single GPU, replicated)" % (sg.n_vertices, g.info["n_edges"]),
-           "generate_s": gen_s, "upload_s": upload_s}
     V = sg.n_vertices
-    for name, fn in [("closure_from_entry_points", lambda: g.closure(dmgraph.OUT, sg.entry)),
-                     ("analysis_order_exact", lambda: g.analysis_order())]:
-        fn()
-        eng.profile_reset()
-        ts = []
-        for _ in range(args.steps):
-            eng.flush_l2()
-            t0 = time.perf_counter()
-            r = fn()
-            ts.append(time.perf_counter() - t0)
-        st = eng.last_stats()
-        kt = kernels(eng)
-        kms = sum(v["ms_total"] for v in kt.values()) / args.steps
-        te = st["edges_traversed"]
-        reached = st["results"]
-        b = 8 * st["rows_expanded"] + 4 * te + 4 * V
-        out[name] = {"kernel_ms": kms, "e2e_ms": 1e3 * float(np.median(ts)), "edges_traversed": int(te),
-                     "gteps": te / (kms * 1e-3) / 1e9 if te else None, "reached": int(reached),
-                     "algorithmic_bytes": int(b), "achieved_GBs": b / (kms * 1e-3) / 1e9,
-                     "frac_of_hbm": b / (kms * 1e-3) / 1e9 / HBM, "kernels": kt}
-    # CPU csr closure for context
+    out = {"workload": "c5: closure from %d entry points on %d V / %d E kept (%d drawn), one GPU; the stated 20 M / "
+                       "500 M graph is the 8-GPU partitioned run" % (sg.entry.size, V, g.info["n_edges"], sg.n_edges),
+           "generate_s": gen_s, "upload_s": upload_s, "device_bytes": int(g.info["device_bytes"])}
     o = ora.CsrOracle(V, sg.src, sg.dst, sg.entry)
     t0 = time.perf_counter()
-    lvl, reached, te = o.closure(0, sg.entry)
-    out["cpu_csr_closure"] = {"seconds": time.perf_counter() - t0, "cores": 1, "reached": int(reached), "edges": int(te)}
-    glvl, greached = g.closure(dmgraph.OUT, sg.entry)
-    assert greached == reached and np.array_equal(glvl, lvl)
-    print(json.dumps(out), flush=True)
+    wlvl, wreached, wte = o.closure(0, sg.entry)
+    cpu_closure_s = time.perf_counter() - t0
+    t0 = time.perf_counter()
+    worder = o.analysis_order()
+    cpu_order_s = time.perf_counter() - t0
+    kms, kt, wall, st, r = timed_calls(eng, lambda: g.closure(dmgraph.OUT, sg.entry), steps)
+    assert r[1] == wreached and np.array_equal(r[0], wlvl), "c5: closure levels differ from the oracle"
+    te, rows = st["edges_traversed"], st["rows_expanded"]
+    levels = int(wlvl[wlvl != 0xFFFFFFFF].max()) + 1
+    alg = 8 * rows + 4 * te + (V // 8) * levels + 4 * V                       # SURVEY.md 8d closure bytes
+    out["closure"] = {"kernel_ms": kms, "kernels": kt, "reached": int(r[1]), "levels": levels,
+                      "edges_traversed": int(te), "edges_read": int(st["edges_read"]),
+                      "gteps": te / (kms * 1e-3) / 1e9, "gteps_read": st["edges_read"] / (kms * 1e-3) / 1e9,
+                      "roofline": roofline(alg, kms), "e2e": {"ms": wall, "d2h_bytes": int(st["d2h_bytes"])}}
+    kms, kt, wall, st, r = timed_calls(eng, lambda: g.analysis_order(), steps)
+    assert np.array_equal(r, worder), "c5: analysisOrder differs from the oracle"
+    alg = 2 * (8 * rows + 4 * te) + 4 * V + 4 * V
+    out["analysis_order"] = {"kernel_ms": kms, "kernels": kt, "roofline": roofline(alg, kms),
+                             "e2e": {"ms": wall, "d2h_bytes": int(st["d2h_bytes"])}}
+    out["parity_checked"] = 2 * V
+    out["parity_against"] = "oracle csr: every level word and the whole exact order"
+    out["cpu_baseline"] = {"kind": "port", "cores": 1, "closure_s": cpu_closure_s, "analysis_order_s": cpu_order_s,
+                           "gteps_closure": wte / cpu_closure_s / 1e9,
+                           "sample": "the whole graph, integer-CSR restatement of PG:390-421 (single thread, as the reference)"}
     g.release()
-    eng.close()
+    return out
 
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("config", choices=["c3", "c4", "c4mix", "c5"])
+    ap.add_argument("config", choices=["c3", "c4", "c5"])
     ap.add_argument("--names", type=int, default=10_000_000)
     ap.add_argument("--queries", type=int, default=16384)
-    ap.add_argument("--vertices", type=int, default=1_000_000)
-    ap.add_argument("--edges", type=int, default=30_000_000)
+    ap.add_argument("--vertices", type=int, default=None)
+    ap.add_argument("--edges", type=int, default=None)
     ap.add_argument("--ops", type=int, default=262_144)
-    ap.add_argument("--max-results", type=int, default=600_000_000,
-                    help="c4mix: halve the batch until the packed result has at most this many entries")
-    ap.add_argument("--steps", type=int, default=5)
-    ap.add_argument("--warmup", type=int, default=2)
+    ap.add_argument("--steps", type=int, default=3)
     args = ap.parse_args()
-    {"c3": run_c3, "c4": run_c4, "c4mix": run_c4mix, "c5": run_c5}[args.config](args)
+    eng = dmgraph.Engine(0)
+    if args.config == "c3":
+        line = run_c3(eng, args.names, args.queries, args.steps)
+    elif args.config == "c4":
+        line = run_c4(eng, args.vertices or 1_000_000, args.edges or 30_000_000, n_ops=args.ops, steps=args.steps)
+    else:
+        line = run_c5(eng, args.vertices or 4_000_000, args.edges or 100_000_000, args.steps)
+    line["config"] = args.config
+    print(json.dumps(line), flush=True)
+    eng.close()
 
 
 if __name__ == "__main__":

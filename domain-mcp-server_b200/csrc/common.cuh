@@ -134,7 +134,18 @@ struct CtxGuard {
   Engine* e;
   CallCtx* c;
   explicit CtxGuard(Engine* en) : e(en), c(en->acquire()) {}
-  ~CtxGuard() { if (c) e->release(c); }
+  // A call that fails half way (a reserve() that runs out of memory after kernels or copies were
+  // queued) returns through here with work still in flight on the context's stream: wait for it
+  // before another thread may acquire the context and reallocate or overwrite its buffers.  On
+  // the normal path finish() has already synchronised and the query returns at once.
+  ~CtxGuard() {
+    if (!c) return;
+    if (cudaStreamQuery(c->stream) != cudaSuccess) {
+      cudaStreamSynchronize(c->stream);
+      cudaGetLastError();
+    }
+    e->release(c);
+  }
 };
 
 void publish_stats(const dmg_call_stats& s);   // thread-local "last call" record
@@ -180,6 +191,7 @@ struct dmg_graph {
   uint32_t* d_und_idx = nullptr;   // [2E]
   uint32_t* d_part_off = nullptr;  // [P+1]
   uint32_t* d_entry = nullptr;     // [n_entry] insertion order
+  uint32_t* d_entry_by_part = nullptr;   // [n_entry] grouped by project, insertion order inside each
   uint32_t* d_entry_bits = nullptr;  // [ceil(V/32)]
   uint64_t* d_name_off = nullptr;  // [V+1] or null
   uint8_t* d_lower = nullptr;      // pre-lowered name arena (+32 B zero pad)
@@ -194,6 +206,8 @@ struct dmg_graph {
   uint32_t n_methods = 0;
   std::vector<uint32_t> h_endpoint_methods;   // catalog indices of HTTP endpoint methods, ascending
   std::vector<uint32_t> h_part_off, h_entry;
+  std::vector<uint32_t> h_entry_part_off;   // [P+1] slices of d_entry_by_part
+  std::vector<uint32_t> h_method_off;       // host copy of the method catalog offsets (project slices of the endpoint list)
 };
 
 // ---------------------------------------------------------------------------------------------
@@ -274,6 +288,40 @@ __device__ __forceinline__ uint64_t lookback_exclusive(uint64_t* status, uint64_
   return excl;
 }
 
+__device__ __forceinline__ unsigned long long warp_incl_scan_u64(unsigned long long v) {
+  const unsigned lane = threadIdx.x & 31;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    unsigned long long t = __shfl_up_sync(FULL, v, o);
+    if (lane >= (unsigned)o) v += t;
+  }
+  return v;
+}
+
+// 64-bit exclusive scan over the block (row sizes can sum past 2^32 inside one tile: a batch may
+// repeat a hub id, and k-hop rows of a multi-million-vertex project are each millions long);
+// s_wsum has THREADS/32 + 1 words; all threads must call
+template <int THREADS>
+__device__ __forceinline__ unsigned long long block_excl_scan_u64(unsigned long long v, unsigned long long* s_wsum,
+                                                                  unsigned long long* total) {
+  constexpr int NW = THREADS / 32;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const unsigned long long inc = warp_incl_scan_u64(v);
+  if (lane == 31) s_wsum[warp] = inc;
+  __syncthreads();
+  if (warp == 0) {
+    unsigned long long w = lane < NW ? s_wsum[lane] : 0;
+    const unsigned long long wi = warp_incl_scan_u64(w);
+    if (lane < NW) s_wsum[lane] = wi - w;
+    if (lane == NW - 1) s_wsum[NW] = wi;
+  }
+  __syncthreads();
+  const unsigned long long r = s_wsum[warp] + inc - v;
+  *total = s_wsum[NW];
+  __syncthreads();
+  return r;
+}
+
 template <int THREADS>
 __device__ __forceinline__ uint32_t block_excl_scan(uint32_t v, uint32_t* s_wsum, uint32_t* total) {
   // exclusive scan over the block; s_wsum has THREADS/32 + 1 words; all threads must call
@@ -304,7 +352,7 @@ static __global__ void __launch_bounds__(SC_THREADS) scan_counts_kernel(const ui
                                                                  unsigned long long* carry, uint64_t* status,
                                                                  DevCounters* ctr) {
   __shared__ unsigned long long s_t, s_base;
-  __shared__ uint32_t s_wsum[SC_THREADS / 32 + 1];
+  __shared__ unsigned long long s_wsum[SC_THREADS / 32 + 1];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   constexpr unsigned long long TILE = (unsigned long long)SC_THREADS * SC_ITEMS;
   const unsigned long long n_tiles = (n + TILE - 1) / TILE;
@@ -315,14 +363,15 @@ static __global__ void __launch_bounds__(SC_THREADS) scan_counts_kernel(const ui
     const unsigned long long t = s_t;
     if (t >= n_tiles) break;
     const unsigned long long i0 = t * TILE + (unsigned long long)tid * SC_ITEMS;
-    uint32_t x[SC_ITEMS], sum = 0;
+    uint32_t x[SC_ITEMS];
+    unsigned long long sum = 0;
 #pragma unroll
     for (int j = 0; j < SC_ITEMS; ++j) {
       x[j] = (i0 + j < n) ? counts[i0 + j] : 0;
       sum += x[j];
     }
-    uint32_t total;
-    uint32_t off = block_excl_scan<SC_THREADS>(sum, s_wsum, &total);
+    unsigned long long total;
+    const unsigned long long off = block_excl_scan_u64<SC_THREADS>(sum, s_wsum, &total);
     if (warp == 0) {
       const unsigned long long excl = lookback_exclusive(status, t, total);
       if (lane == 0) s_base = excl;

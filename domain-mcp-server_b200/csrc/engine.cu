@@ -154,7 +154,7 @@ using namespace dmg;
 static void free_graph(dmg_graph* g) {
   cudaSetDevice(g->eng->device);
   for (void* p : {(void*)g->d_out_ptr, (void*)g->d_out_idx, (void*)g->d_in_ptr, (void*)g->d_in_idx,
-                  (void*)g->d_und_ptr, (void*)g->d_und_idx, (void*)g->d_part_off, (void*)g->d_entry, (void*)g->d_entry_bits, (void*)g->d_name_off,
+                  (void*)g->d_und_ptr, (void*)g->d_und_idx, (void*)g->d_part_off, (void*)g->d_entry, (void*)g->d_entry_by_part, (void*)g->d_entry_bits, (void*)g->d_name_off,
                   (void*)g->d_lower, (void*)g->d_names, (void*)g->d_full_tbl, (void*)g->d_simple_tbl, (void*)g->d_simple_next, (void*)g->d_method_off, (void*)g->d_mname_off, (void*)g->d_mname_lower})
     if (p) cudaFree(p);
   delete g;
@@ -172,11 +172,11 @@ static int32_t upload(T** d, const T* h, size_t n, uint64_t* bytes) {
 // Second half of every upload path (edge list or snapshot): derives the resolve rows, the entry
 // bitmap and the name tables from the CSR and copies everything to the device.  Takes ownership
 // of `g` (freed on failure).
-static int32_t finish_upload(dmg_engine* e, dmg_graph* g, uint32_t V, const std::vector<uint32_t>& out_ptr,
-                             const std::vector<uint32_t>& out_idx, const std::vector<uint32_t>& in_ptr,
-                             const std::vector<uint32_t>& in_idx, const std::vector<uint32_t>& part,
-                             const uint64_t* name_off, const uint8_t* name_bytes, const uint8_t* lower_bytes,
-                             uint64_t dropped, uint64_t dups, dmg_graph** out) {
+static int32_t finish_upload_impl(dmg_engine* e, dmg_graph* g, uint32_t V, const std::vector<uint32_t>& out_ptr,
+                                  const std::vector<uint32_t>& out_idx, const std::vector<uint32_t>& in_ptr,
+                                  const std::vector<uint32_t>& in_idx, const std::vector<uint32_t>& part,
+                                  const uint64_t* name_off, const uint8_t* name_bytes, const uint8_t* lower_bytes,
+                                  uint64_t dropped, uint64_t dups, dmg_graph** out, bool* g_freed) {
   struct Desc {
     const uint64_t* name_off;
     const uint8_t* name_bytes;
@@ -193,6 +193,19 @@ static int32_t finish_upload(dmg_engine* e, dmg_graph* g, uint32_t V, const std:
   int32_t st = DMG_OK;
   std::vector<uint32_t> ebits((V + 31) / 32 + 1, 0);
   for (uint32_t v : g->h_entry) ebits[v >> 5] |= 1u << (v & 31);
+  // entry points grouped by project (stable, so each project keeps markAsEntryPoint order, PG:190-197):
+  // executeEntrypoints (GQS:152-191) lists ONE project's graph
+  const size_t P = part.size() - 1;
+  std::vector<uint32_t> entry_by_part(g->h_entry.size());
+  g->h_entry_part_off.assign(P + 1, 0);
+  {
+    auto part_of = [&](uint32_t v) { return (size_t)(std::upper_bound(part.begin(), part.end(), v) - part.begin() - 1); };
+    // zero-width ranges share a boundary: upper_bound lands on the last of them, whose range holds v
+    for (uint32_t v : g->h_entry) ++g->h_entry_part_off[std::min(part_of(v), P - 1) + 1];
+    for (size_t p = 0; p < P; ++p) g->h_entry_part_off[p + 1] += g->h_entry_part_off[p];
+    std::vector<uint32_t> cur(g->h_entry_part_off.begin(), g->h_entry_part_off.end() - 1);
+    for (uint32_t v : g->h_entry) entry_by_part[cur[std::min(part_of(v), P - 1)]++] = v;
+  }
   // resolve() rows for mode BOTH: the out row followed by the in row of the same vertex, one
   // contiguous range per vertex (no de-duplication: a 2-cycle appears twice, the visited
   // set removes it, PG:366-375)
@@ -206,6 +219,7 @@ static int32_t finish_upload(dmg_engine* e, dmg_graph* g, uint32_t V, const std:
       und_ptr[v + 1] = w;
     }
   } catch (const std::bad_alloc&) {
+    *g_freed = true;
     delete g;
     set_error("dmg_graph_create: host out of memory");
     return DMG_ENOMEM;
@@ -218,7 +232,9 @@ static int32_t finish_upload(dmg_engine* e, dmg_graph* g, uint32_t V, const std:
       (st = upload(&g->d_in_idx, in_idx.data(), in_idx.size(), &bytes)) != DMG_OK ||
       (st = upload(&g->d_part_off, part.data(), part.size(), &bytes)) != DMG_OK ||
       (st = upload(&g->d_entry, g->h_entry.data(), g->h_entry.size(), &bytes)) != DMG_OK ||
+      (st = upload(&g->d_entry_by_part, entry_by_part.data(), entry_by_part.size(), &bytes)) != DMG_OK ||
       (st = upload(&g->d_entry_bits, ebits.data(), ebits.size(), &bytes)) != DMG_OK) {
+    *g_freed = true;
     free_graph(g);
     return st;
   }
@@ -285,6 +301,7 @@ static int32_t finish_upload(dmg_engine* e, dmg_graph* g, uint32_t V, const std:
         (st = upload(&g->d_full_tbl, full_tbl.data(), full_tbl.size(), &bytes)) != DMG_OK ||
         (st = upload(&g->d_simple_tbl, simple_tbl.data(), simple_tbl.size(), &bytes)) != DMG_OK ||
         (st = upload(&g->d_simple_next, simple_next.data(), simple_next.size(), &bytes)) != DMG_OK) {
+      *g_freed = true;
       free_graph(g);
       return st;
     }
@@ -300,6 +317,24 @@ static int32_t finish_upload(dmg_engine* e, dmg_graph* g, uint32_t V, const std:
   g->info.device_bytes = bytes;
   *out = g;
   return DMG_OK;
+}
+
+// No C++ exception may cross the extern "C" boundary (it would terminate the host JVM): every
+// host allocation of the upload (entry bitmap, resolve rows, name tables) is made under this try.
+static int32_t finish_upload(dmg_engine* e, dmg_graph* g, uint32_t V, const std::vector<uint32_t>& out_ptr,
+                             const std::vector<uint32_t>& out_idx, const std::vector<uint32_t>& in_ptr,
+                             const std::vector<uint32_t>& in_idx, const std::vector<uint32_t>& part,
+                             const uint64_t* name_off, const uint8_t* name_bytes, const uint8_t* lower_bytes,
+                             uint64_t dropped, uint64_t dups, dmg_graph** out) {
+  bool g_freed = false;
+  try {
+    return finish_upload_impl(e, g, V, out_ptr, out_idx, in_ptr, in_idx, part, name_off, name_bytes, lower_bytes,
+                              dropped, dups, out, &g_freed);
+  } catch (const std::exception&) {   // bad_alloc, length_error
+    if (!g_freed) free_graph(g);
+    set_error("graph upload: host out of memory");
+    return DMG_ENOMEM;
+  }
 }
 
 // helpers of the binary CSR snapshot
@@ -387,7 +422,16 @@ void dmg_engine_destroy(dmg_engine* e) {
   delete e;
 }
 
+static int32_t graph_create_impl(dmg_engine* e, const dmg_graph_desc* d, dmg_graph** out);
 int32_t dmg_graph_create(dmg_engine* e, const dmg_graph_desc* d, dmg_graph** out) {
+  try {
+    return graph_create_impl(e, d, out);
+  } catch (const std::exception&) {   // the vectors sized from V before the build's own try block
+    set_error("dmg_graph_create: host out of memory");
+    return DMG_ENOMEM;
+  }
+}
+static int32_t graph_create_impl(dmg_engine* e, const dmg_graph_desc* d, dmg_graph** out) {
   if (!e || !d || !out) {
     set_error("dmg_graph_create: NULL argument");
     return DMG_EINVAL;
@@ -426,11 +470,11 @@ int32_t dmg_graph_create(dmg_engine* e, const dmg_graph_desc* d, dmg_graph** out
   };
 
   // ---- host CSR build, O(V+E): stable counting sort by source, per-row stamp dedup ----------
+  uint64_t dropped = 0, dups = 0;
+  std::vector<uint32_t> out_ptr(V + 1, 0), in_ptr(V + 1, 0), out_idx, in_idx;
   dmg_graph* g = new (std::nothrow) dmg_graph();
   if (!g) return DMG_ENOMEM;
   g->eng = e;
-  uint64_t dropped = 0, dups = 0;
-  std::vector<uint32_t> out_ptr(V + 1, 0), in_ptr(V + 1, 0), out_idx, in_idx;
   try {
     std::vector<uint32_t> cnt(V + 1, 0);
     for (uint64_t i = 0; i < E; ++i) {
@@ -538,6 +582,79 @@ int32_t dmg_graph_save(dmg_graph* g, const char* path) {
   return DMG_OK;
 }
 
+// A snapshot is a file somebody else may have truncated, edited or written for another graph:
+// it is held to everything dmg_graph_create guarantees (kernels index shared memory with
+// `id - project base` unchecked), and no allocation is sized from a header field before the
+// file's length has confirmed it.
+static int32_t load_snapshot(dmg_engine* e, const char* path, FILE* f, dmg_graph** out) {
+  SnapHeader h;
+  std::vector<uint32_t> out_ptr, out_idx, in_ptr, in_idx, part, entry;
+  std::vector<uint64_t> name_off;
+  std::vector<uint8_t> names, lower;
+  bool ok = fread(&h, sizeof(h), 1, f) == 1 && memcmp(h.magic, "DMGCSR1", 8) == 0 && h.E < 0x7FFFFFF0ull &&
+            h.n_parts >= 1 && h.has_names <= 1;
+  if (ok) {
+    unsigned long long want = sizeof(h) + 2ull * ((unsigned long long)h.V + 1) * 4 + 2ull * h.E * 4 +
+                              ((unsigned long long)h.n_parts + 1) * 4 + (unsigned long long)h.n_entry * 4;
+    if (h.has_names) {
+      ok = h.name_bytes < (1ull << 40);
+      want += ((unsigned long long)h.V + 1) * 8 + 2ull * h.name_bytes;
+    }
+    long long size = -1;
+    if (fseek(f, 0, SEEK_END) == 0) size = ftell(f);
+    ok = ok && size >= 0 && (unsigned long long)size == want && fseek(f, (long)sizeof(h), SEEK_SET) == 0;
+  }
+  ok = ok && get_vec(f, out_ptr, (size_t)h.V + 1) && get_vec(f, out_idx, h.E) && get_vec(f, in_ptr, (size_t)h.V + 1) &&
+       get_vec(f, in_idx, h.E) && get_vec(f, part, (size_t)h.n_parts + 1) && get_vec(f, entry, h.n_entry);
+  if (ok && h.has_names)
+    ok = get_vec(f, name_off, (size_t)h.V + 1) && get_vec(f, names, h.name_bytes) && get_vec(f, lower, h.name_bytes);
+  // shape: offsets monotone and in range, project ranges non-decreasing from 0 to V
+  ok = ok && out_ptr[0] == 0 && in_ptr[0] == 0 && out_ptr[h.V] == h.E && in_ptr[h.V] == h.E && part.front() == 0 &&
+       part.back() == h.V;
+  for (uint32_t v = 0; ok && v < h.V; ++v) ok = out_ptr[v] <= out_ptr[v + 1] && in_ptr[v] <= in_ptr[v + 1];
+  for (size_t i = 1; ok && i < part.size(); ++i) ok = part[i] >= part[i - 1];
+  for (uint64_t i = 0; ok && i < h.E; ++i) ok = out_idx[i] < h.V;
+  // every edge stays inside the project of its source (what dmg_graph_create rejects)
+  if (ok) {
+    size_t p = 0;
+    for (uint32_t s = 0; ok && s < h.V; ++s) {
+      while (s >= part[p + 1]) ++p;
+      for (uint32_t j = out_ptr[s]; ok && j < out_ptr[s + 1]; ++j) ok = out_idx[j] >= part[p] && out_idx[j] < part[p + 1];
+    }
+  }
+  // the reverse CSR must be the transpose of the forward one, rows in ascending source id
+  if (ok) {
+    std::vector<uint32_t> cur((size_t)h.V + 1, 0);
+    for (uint64_t i = 0; i < h.E; ++i) ++cur[out_idx[i] + 1];
+    for (uint32_t v = 0; v < h.V; ++v) cur[v + 1] += cur[v];
+    ok = memcmp(cur.data(), in_ptr.data(), ((size_t)h.V + 1) * 4) == 0;
+    for (uint32_t s = 0; ok && s < h.V; ++s)
+      for (uint32_t j = out_ptr[s]; ok && j < out_ptr[s + 1]; ++j) ok = in_idx[cur[out_idx[j]]++] == s;
+  }
+  // entry points: known ids, no repeats (PG:190-197)
+  if (ok) {
+    std::vector<uint8_t> seen(h.V, 0);
+    for (uint32_t i = 0; ok && i < h.n_entry; ++i) {
+      ok = entry[i] < h.V && !seen[entry[i]];
+      if (ok) seen[entry[i]] = 1;
+    }
+  }
+  if (ok && h.has_names) {
+    ok = name_off[0] == 0 && name_off[h.V] == h.name_bytes;
+    for (uint32_t v = 0; ok && v < h.V; ++v) ok = name_off[v] <= name_off[v + 1];
+  }
+  if (!ok) {
+    set_error("dmg_graph_load: %s is not a valid dmgraph snapshot", path);
+    return DMG_EINVAL;
+  }
+  dmg_graph* g = new (std::nothrow) dmg_graph();
+  if (!g) return DMG_ENOMEM;
+  g->eng = e;
+  g->h_entry.swap(entry);   // no allocation: nothing can throw between `new` and finish_upload
+  return finish_upload(e, g, h.V, out_ptr, out_idx, in_ptr, in_idx, part, h.has_names ? name_off.data() : nullptr,
+                       names.data(), h.has_names ? lower.data() : nullptr, h.dropped, h.dups, out);
+}
+
 int32_t dmg_graph_load(dmg_engine* e, const char* path, dmg_graph** out) {
   if (!e || !path || !out) {
     set_error("dmg_graph_load: NULL argument");
@@ -549,35 +666,15 @@ int32_t dmg_graph_load(dmg_engine* e, const char* path, dmg_graph** out) {
     set_error("dmg_graph_load: cannot open %s", path);
     return DMG_EINVAL;
   }
-  SnapHeader h;
-  std::vector<uint32_t> out_ptr, out_idx, in_ptr, in_idx, part, entry;
-  std::vector<uint64_t> name_off;
-  std::vector<uint8_t> names, lower;
-  bool ok = fread(&h, sizeof(h), 1, f) == 1 && memcmp(h.magic, "DMGCSR1", 8) == 0 && h.E < 0x7FFFFFF0ull;
-  ok = ok && get_vec(f, out_ptr, (size_t)h.V + 1) && get_vec(f, out_idx, h.E) && get_vec(f, in_ptr, (size_t)h.V + 1) &&
-       get_vec(f, in_idx, h.E) && get_vec(f, part, (size_t)h.n_parts + 1) && get_vec(f, entry, h.n_entry);
-  if (ok && h.has_names)
-    ok = get_vec(f, name_off, (size_t)h.V + 1) && get_vec(f, names, h.name_bytes) && get_vec(f, lower, h.name_bytes);
+  int32_t rc;
+  try {
+    rc = load_snapshot(e, path, f, out);
+  } catch (const std::exception&) {
+    set_error("dmg_graph_load: host out of memory reading %s", path);
+    rc = DMG_ENOMEM;
+  }
   fclose(f);
-  // the snapshot is trusted only as far as its shape: offsets must be monotone and in range
-  ok = ok && out_ptr[h.V] == h.E && in_ptr[h.V] == h.E && part.front() == 0 && part.back() == h.V;
-  for (uint32_t v = 0; ok && v < h.V; ++v) ok = out_ptr[v] <= out_ptr[v + 1] && in_ptr[v] <= in_ptr[v + 1];
-  for (uint64_t i = 0; ok && i < h.E; ++i) ok = out_idx[i] < h.V && in_idx[i] < h.V;
-  for (uint32_t i = 0; ok && i < h.n_entry; ++i) ok = entry[i] < h.V;
-  if (ok && h.has_names) {
-    ok = name_off[h.V] == h.name_bytes;
-    for (uint32_t v = 0; ok && v < h.V; ++v) ok = name_off[v] <= name_off[v + 1];
-  }
-  if (!ok) {
-    set_error("dmg_graph_load: %s is not a valid dmgraph snapshot", path);
-    return DMG_EINVAL;
-  }
-  dmg_graph* g = new (std::nothrow) dmg_graph();
-  if (!g) return DMG_ENOMEM;
-  g->eng = e;
-  g->h_entry = entry;
-  return finish_upload(e, g, h.V, out_ptr, out_idx, in_ptr, in_idx, part, h.has_names ? name_off.data() : nullptr,
-                       names.data(), h.has_names ? lower.data() : nullptr, h.dropped, h.dups, out);
+  return rc;
 }
 
 void dmg_graph_retain(dmg_graph* g) {

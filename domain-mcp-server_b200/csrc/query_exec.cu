@@ -59,10 +59,8 @@ struct QxArgs {
   const uint8_t* const* grp_hop;
   const uint32_t *out_ptr, *out_idx, *in_ptr, *in_idx;
   uint32_t V;
-  const uint32_t* entry;
-  uint32_t n_entry;
-  const uint32_t* endpoints;
-  uint32_t n_endpoints;
+  const uint32_t* entry;       // entry points grouped by project (insertion order inside each)
+  const uint32_t* endpoints;   // endpoint methods, ascending catalog index
   QxRow* rows;
   uint32_t* cnt;
   unsigned long long n;
@@ -100,8 +98,9 @@ __global__ void __launch_bounds__(256) qx_describe_kernel(const QxArgs a) {
       if (!a.grp_ids[grp]) r.s[0] = QxSeg{nullptr, nullptr, a.ref_b[i], 0u};   // sizing call: length only
       break;
     }
-    case DMG_OP_ENTRYPOINTS: r.s[0] = QxSeg{a.entry, nullptr, a.n_entry, 0u}; break;
-    case DMG_OP_ENDPOINTS: r.s[0] = QxSeg{a.endpoints, nullptr, a.n_endpoints, 0u}; break;
+    // the op's project owns a contiguous slice of each list (host: ref_a = first entry, ref_b = length)
+    case DMG_OP_ENTRYPOINTS: r.s[0] = QxSeg{a.entry + a.ref_a[i], nullptr, a.ref_b[i], 0u}; break;
+    case DMG_OP_ENDPOINTS: r.s[0] = QxSeg{a.endpoints + a.ref_a[i], nullptr, a.ref_b[i], 0u}; break;
     case DMG_OP_RESOLVE_NAME:
     case DMG_OP_METHOD:
       // the resolved id sits in the low word of the op's ref_a slot
@@ -207,6 +206,12 @@ int32_t dmg_graph_set_methods(dmg_graph* g, const uint32_t* method_off, const ui
   g->d_mname_lower = lb.as<uint8_t>();
   mo.p = no.p = lb.p = nullptr;   // ownership moved to the graph
   g->n_methods = M;
+  try {
+    g->h_method_off.assign(method_off, method_off + (size_t)V + 1);
+  } catch (const std::exception&) {
+    set_error("dmg_graph_set_methods: host out of memory");
+    return DMG_ENOMEM;
+  }
   return DMG_OK;
 }
 
@@ -246,8 +251,17 @@ int32_t dmg_query_batch(dmg_graph* g, uint64_t n_ops, const dmg_query_op* ops, c
   };
   std::vector<std::pair<KhopKey, uint64_t>> khops;
   bool want_endpoints = false;
+  const uint32_t n_parts = g->info.n_parts;
   for (uint64_t i = 0; i < n_ops; ++i) {
     const dmg_query_op& op = ops[i];
+    // The reference answers graph_query from ONE project's graph (GQS:56-62): the three operations
+    // that range over a whole graph are scoped to the op's project of this handle.
+    if ((op.opcode == DMG_OP_ENTRYPOINTS || op.opcode == DMG_OP_ENDPOINTS || op.opcode == DMG_OP_RESOLVE_NAME) &&
+        op.project >= n_parts) {
+      set_error("dmg_query_batch: op %llu: project %u out of range (graph holds %u)", (unsigned long long)i,
+                op.project, n_parts);
+      return DMG_EINVAL;
+    }
     switch (op.opcode) {
       case DMG_OP_DEPENDENCIES:
       case DMG_OP_DEPENDENTS:
@@ -351,35 +365,61 @@ int32_t dmg_query_batch(dmg_graph* g, uint64_t n_ops, const dmg_query_op* ops, c
       set_error("dmg_query_batch: DMG_OP_RESOLVE_NAME needs a graph with names");
       return DMG_EINVAL;
     }
-    std::vector<size_t> todo(names.size());
-    for (size_t j = 0; j < names.size(); ++j) todo[j] = j;
-    for (int pass = 0; pass < 2 && !todo.empty(); ++pass) {
-      std::vector<uint32_t> qo(todo.size() + 1, 0);
-      std::vector<uint8_t> qb;
-      for (size_t j = 0; j < todo.size(); ++j) {
-        const dmg_query_op& op = ops[names[todo[j]]];
-        qb.insert(qb.end(), text_bytes + op.text_begin, text_bytes + op.text_end);
-        qo[j + 1] = (uint32_t)qb.size();
-      }
-      qb.push_back(0);
-      std::vector<uint64_t> off(todo.size() + 1, 0);
-      std::vector<uint32_t> ids(todo.size() + 1, 0);
-      st = dmg_search_batch(g, pass == 0 ? DMG_SEARCH_SIMPLE_EQ_FIRST : DMG_SEARCH_CONTAINS_FIRST, 0,
-                            g->info.n_vertices, todo.size(), qo.data(), qb.data(), off.data(), ids.data(),
-                            todo.size(), &nd);
-      if (st != DMG_OK) return st;
-      std::vector<size_t> miss;
-      for (size_t j = 0; j < todo.size(); ++j) {
-        if (off[j + 1] > off[j]) {
-          const uint64_t op = names[todo[j]];
-          ref_a[op] = ids[off[j]];
-          ref_b[op] = 1;
-          ref_g[op] = pass == 0 ? 2 : 3;
-        } else {
-          miss.push_back(todo[j]);
+    // one scan per project that has name ops (a scan covers one vertex range)
+    std::stable_sort(names.begin(), names.end(),
+                     [&](uint64_t x, uint64_t y) { return ops[x].project < ops[y].project; });
+    for (size_t n0 = 0; n0 < names.size();) {
+      size_t n1 = n0;
+      const uint32_t proj = ops[names[n0]].project;
+      while (n1 < names.size() && ops[names[n1]].project == proj) ++n1;
+      const uint32_t v_lo = g->h_part_off[proj], v_hi = g->h_part_off[proj + 1];
+      std::vector<size_t> todo(n1 - n0);
+      for (size_t j = 0; j < todo.size(); ++j) todo[j] = n0 + j;
+      for (int pass = 0; pass < 2 && !todo.empty(); ++pass) {
+        std::vector<uint32_t> qo(todo.size() + 1, 0);
+        std::vector<uint8_t> qb;
+        for (size_t j = 0; j < todo.size(); ++j) {
+          const dmg_query_op& op = ops[names[todo[j]]];
+          qb.insert(qb.end(), text_bytes + op.text_begin, text_bytes + op.text_end);
+          qo[j + 1] = (uint32_t)qb.size();
         }
+        qb.push_back(0);
+        std::vector<uint64_t> off(todo.size() + 1, 0);
+        std::vector<uint32_t> ids(todo.size() + 1, 0);
+        st = dmg_search_batch(g, pass == 0 ? DMG_SEARCH_SIMPLE_EQ_FIRST : DMG_SEARCH_CONTAINS_FIRST, v_lo, v_hi,
+                              todo.size(), qo.data(), qb.data(), off.data(), ids.data(), todo.size(), &nd);
+        if (st != DMG_OK) return st;
+        std::vector<size_t> miss;
+        for (size_t j = 0; j < todo.size(); ++j) {
+          if (off[j + 1] > off[j]) {
+            const uint64_t op = names[todo[j]];
+            ref_a[op] = ids[off[j]];
+            ref_b[op] = 1;
+            ref_g[op] = pass == 0 ? 2 : 3;
+          } else {
+            miss.push_back(todo[j]);
+          }
+        }
+        todo.swap(miss);
       }
-      todo.swap(miss);
+      n0 = n1;
+    }
+  }
+
+  // ---- entry points / endpoints: the slice of the op's project ---------------------------------
+  for (uint64_t i = 0; i < n_ops; ++i) {
+    const dmg_query_op& op = ops[i];
+    if (op.opcode == DMG_OP_ENTRYPOINTS) {
+      ref_a[i] = g->h_entry_part_off[op.project];
+      ref_b[i] = g->h_entry_part_off[op.project + 1] - g->h_entry_part_off[op.project];
+    } else if (op.opcode == DMG_OP_ENDPOINTS && !g->h_method_off.empty()) {
+      // catalog indices ascend with the vertex id, so a project's endpoints are one run of the list
+      const uint32_t m_lo = g->h_method_off[g->h_part_off[op.project]], m_hi = g->h_method_off[g->h_part_off[op.project + 1]];
+      const auto& ep = g->h_endpoint_methods;
+      const size_t a0 = std::lower_bound(ep.begin(), ep.end(), m_lo) - ep.begin();
+      const size_t a1 = std::lower_bound(ep.begin(), ep.end(), m_hi) - ep.begin();
+      ref_a[i] = a0;
+      ref_b[i] = (uint32_t)(a1 - a0);
     }
   }
 
@@ -466,10 +506,8 @@ int32_t dmg_query_batch(dmg_graph* g, uint64_t n_ops, const dmg_query_op* ops, c
   qa.in_ptr = g->d_in_ptr;
   qa.in_idx = g->d_in_idx;
   qa.V = g->info.n_vertices;
-  qa.entry = g->d_entry;
-  qa.n_entry = (uint32_t)g->h_entry.size();
+  qa.entry = g->d_entry_by_part;
   qa.endpoints = reinterpret_cast<const uint32_t*>(up + o_ep);
-  qa.n_endpoints = (uint32_t)g->h_endpoint_methods.size();
   qa.rows = c->tmp1.as<QxRow>();
   qa.cnt = c->tmp2.as<uint32_t>();
   qa.n = n_ops;

@@ -619,8 +619,8 @@ __global__ void __launch_bounds__(KG_THREADS) khop_global_kernel(const KhopArgs 
     if (total && !scan_path) {
       // short row: one MSD radix pass into <= 1024 id buckets, then each bucket is a handful of
       // ids that one thread orders in place
-      uint32_t sh = 0;
-      while ((wn >> sh) > (uint32_t)KG_BUCKETS) ++sh;
+      uint32_t sh = 0;   // the largest id, wn - 1, must land in bucket KG_BUCKETS - 1 at most
+      while (((wn - 1) >> sh) >= (uint32_t)KG_BUCKETS) ++sh;
       for (uint32_t i = tid; i < total; i += THREADS) atomicAdd(&s_hist[queue[ns + i] >> sh], 1u);
       __syncthreads();
       {
@@ -789,8 +789,9 @@ __global__ void __launch_bounds__(ADJ_THREADS) adjacency_kernel(const uint32_t* 
                                                                 DevCounters* ctr, unsigned long long* long_rows) {
   constexpr int THREADS = ADJ_THREADS, NW = THREADS / 32;
   __shared__ unsigned long long s_t, s_base;
-  __shared__ uint32_t s_start[THREADS], s_len[THREADS], s_off[THREADS];
-  __shared__ uint32_t s_wsum[NW + 1];
+  __shared__ uint32_t s_start[THREADS], s_len[THREADS];
+  __shared__ unsigned long long s_off[THREADS];
+  __shared__ unsigned long long s_wsum[NW + 1];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const unsigned long long n_tiles = (n + THREADS - 1) / THREADS;
   unsigned long long te = 0;
@@ -808,8 +809,8 @@ __global__ void __launch_bounds__(ADJ_THREADS) adjacency_kernel(const uint32_t* 
         len = ptr[id + 1] - start;
       }
     }
-    uint32_t total;
-    const uint32_t off = block_excl_scan<THREADS>(len, s_wsum, &total);
+    unsigned long long total;   // 64 bits: a tile of repeated hub ids can exceed 2^32 entries
+    const unsigned long long off = block_excl_scan_u64<THREADS>(len, s_wsum, &total);
     s_start[tid] = start;
     s_len[tid] = len;
     s_off[tid] = off;
@@ -1234,21 +1235,17 @@ static int32_t static_scratch_for_device(int dev, unsigned char** out) {
 
 static inline size_t pad256(size_t x) { return (x + 255) & ~size_t(255); }
 
-int32_t dmg_neighbors_batch_dev_static(dmg_graph* g, int32_t mode, int32_t k, int32_t exclude_sources, uint64_t nq,
-                                       const uint32_t* d_q_off, const uint32_t* d_q_src, uint64_t* d_out_off,
-                                       uint32_t* d_out_ids, uint8_t* d_out_hop, uint64_t cap, uint64_t* needed) {
-  DMG_TRY(check_khop_args(g, mode, k, nq, d_q_off, d_out_off, needed));
-  *needed = 0;
-  const uint32_t maxp = std::max<uint32_t>(g->info.max_part_vertices, 1);
-  if (maxp > SMALL_WINDOW_MAX) {
-    set_error("dmg_neighbors_batch_dev_static: largest project has %u vertices; the static-scratch variant "
-              "covers projects up to %u (use dmg_neighbors_batch_dev)", maxp, SMALL_WINDOW_MAX);
-    return DMG_EINVAL;
-  }
+// The part of the static entry point that runs with the engine's device current and may have queued
+// work on the default stream when it fails; the wrapper below waits for that work and puts the
+// caller's device back whatever this returns.
+static int32_t static_khop_on_device(dmg_graph* g, int32_t mode, int32_t k, int32_t exclude_sources, uint64_t nq,
+                                     const uint32_t* d_q_off, const uint32_t* d_q_src, uint64_t* d_out_off,
+                                     uint32_t* d_out_ids, uint8_t* d_out_hop, uint64_t cap, uint64_t* needed) {
   Engine* e = g->eng;
-  DMG_CUDA(cudaSetDevice(e->device));
+  const uint32_t maxp = std::max<uint32_t>(g->info.max_part_vertices, 1);
   if (nq == 0) {
-    DMG_CUDA(cudaMemset(d_out_off, 0, sizeof(uint64_t)));
+    DMG_CUDA(cudaMemsetAsync(d_out_off, 0, sizeof(uint64_t), 0));
+    DMG_CUDA(cudaStreamSynchronize(0));
     return DMG_OK;
   }
   const uint32_t WC = (maxp + 127u) & ~127u;
@@ -1298,6 +1295,9 @@ int32_t dmg_neighbors_batch_dev_static(dmg_graph* g, int32_t mode, int32_t k, in
   a.stage = base + o_stage;
   a.counts = reinterpret_cast<uint32_t*>(base + o_counts);
   a.qwin = reinterpret_cast<uint32_t*>(base + o_qwin);
+  a.tmp_start = nullptr;
+  a.tmp_ids = nullptr;
+  a.tmp_hop = nullptr;
   int occ = 0;
   size_t smem = 0;
   DMG_TRY(with_small_kernel(WC, [&](auto kern, uint32_t wc) -> int32_t {
@@ -1326,6 +1326,33 @@ int32_t dmg_neighbors_batch_dev_static(dmg_graph* g, int32_t mode, int32_t k, in
     return DMG_ECAP;
   }
   return DMG_OK;
+}
+
+int32_t dmg_neighbors_batch_dev_static(dmg_graph* g, int32_t mode, int32_t k, int32_t exclude_sources, uint64_t nq,
+                                       const uint32_t* d_q_off, const uint32_t* d_q_src, uint64_t* d_out_off,
+                                       uint32_t* d_out_ids, uint8_t* d_out_hop, uint64_t cap, uint64_t* needed) {
+  DMG_TRY(check_khop_args(g, mode, k, nq, d_q_off, d_out_off, needed));
+  *needed = 0;
+  const uint32_t maxp = std::max<uint32_t>(g->info.max_part_vertices, 1);
+  if (maxp > SMALL_WINDOW_MAX) {
+    set_error("dmg_neighbors_batch_dev_static: largest project has %u vertices; the static-scratch variant "
+              "covers projects up to %u (use dmg_neighbors_batch_dev)", maxp, SMALL_WINDOW_MAX);
+    return DMG_EINVAL;
+  }
+  // The work runs on the engine's device; the caller's current device is put back before returning.
+  int prev_dev = -1;
+  cudaGetDevice(&prev_dev);
+  DMG_CUDA(cudaSetDevice(g->eng->device));
+  const int32_t rc = static_khop_on_device(g, mode, k, exclude_sources, nq, d_q_off, d_q_src, d_out_off, d_out_ids,
+                                           d_out_hop, cap, needed);
+  if (rc != DMG_OK && rc != DMG_ECAP) {
+    // a failure after the first launch leaves kernels running over the shared array: wait for them,
+    // so that the caller may retry or issue another call at once
+    cudaStreamSynchronize(0);
+    cudaGetLastError();
+  }
+  if (prev_dev >= 0 && prev_dev != g->eng->device) cudaSetDevice(prev_dev);
+  return rc;
 }
 
 int32_t dmg_neighbors_batch(dmg_graph* g, int32_t mode, int32_t k, int32_t exclude_sources, uint64_t nq,

@@ -46,7 +46,7 @@ class GraphInfo(C.Structure):
 class QueryOp(C.Structure):
     _fields_ = [("opcode", C.c_uint32), ("vertex", C.c_uint32), ("mode", C.c_uint32), ("k", C.c_uint32),
                 ("exclude_sources", C.c_uint32), ("text_begin", C.c_uint32), ("text_end", C.c_uint32),
-                ("reserved", C.c_uint32)]
+                ("project", C.c_uint32)]
 
 
 OP_DEPENDENCIES, OP_DEPENDENTS, OP_OVERVIEW, OP_KHOP, OP_ENTRYPOINTS, OP_RESOLVE_NAME, OP_METHOD, OP_ENDPOINTS = range(8)
@@ -274,11 +274,16 @@ class Graph:
         return g
 
     # -- T0/T1 ---------------------------------------------------------------------------------
-    def adjacency_batch(self, direction, ids, cap=None):
+    def adjacency_batch(self, direction, ids, cap=None, out=None):
         ids = _arr(ids, np.uint32)
         n = ids.size
-        off = np.zeros(n + 1, np.uint64)
         need = C.c_uint64(0)
+        if out is not None:                      # caller buffers (e.g. pinned): (off u64[n+1], ids u32[cap])
+            off, o_ids = out
+            _check(self.L.dmg_adjacency_batch(self.h, direction, n, _ptr(ids), off.ctypes.data, o_ids.ctypes.data,
+                                              o_ids.size, C.byref(need)))
+            return off, o_ids[:need.value]
+        off = np.zeros(n + 1, np.uint64)
         if cap is None:
             rc = self.L.dmg_adjacency_batch(self.h, direction, n, _ptr(ids), off.ctypes.data, None, 0, C.byref(need))
             _check(rc, allow=(ECAP,))
@@ -431,7 +436,7 @@ class Graph:
         _check(self.L.dmg_graph_set_method_flags(self.h, f.ctypes.data if f.size else None))
 
     def query_batch(self, ops):
-        """ops: list of dicts {op, vertex?, mode?, k?, exclude?, text?(bytes)}; returns rows of (id, aux)."""
+        """ops: list of dicts {op, vertex?, mode?, k?, exclude?, text?(bytes), project?}; returns rows of (id, aux)."""
         n = len(ops)
         arr = (QueryOp * max(n, 1))()
         text = bytearray()
@@ -440,6 +445,7 @@ class Graph:
             a.opcode = o["op"]
             a.vertex = o.get("vertex", 0xFFFFFFFF)
             a.mode, a.k, a.exclude_sources = o.get("mode", 0), o.get("k", 1), int(o.get("exclude", 0))
+            a.project = o.get("project", 0)
             t = o.get("text", b"")
             a.text_begin = len(text)
             text += t
@@ -458,7 +464,7 @@ class Graph:
 
     QUERY_OP_DTYPE = np.dtype([("opcode", "<u4"), ("vertex", "<u4"), ("mode", "<u4"), ("k", "<u4"),
                                ("exclude_sources", "<u4"), ("text_begin", "<u4"), ("text_end", "<u4"),
-                               ("reserved", "<u4")])
+                               ("project", "<u4")])
 
     def query_batch_packed(self, ops, text, out=None):
         """ops: structured array of QUERY_OP_DTYPE (== dmg_query_op), text: uint8 array.
@@ -482,17 +488,27 @@ class Graph:
         return need.value
 
     # -- S1/S2 ---------------------------------------------------------------------------------
-    def search_batch(self, kind, queries, v_lo=0, v_hi=None, cap=None):
-        """queries: list of bytes, already lower-cased by the host."""
-        nq = len(queries)
-        q_off = np.zeros(nq + 1, np.uint32)
-        if nq:
-            np.cumsum([len(q) for q in queries], out=q_off[1:])
-        qb = np.frombuffer(b"".join(queries) + b"\0", dtype=np.uint8).copy()
+    def search_batch(self, kind, queries, v_lo=0, v_hi=None, cap=None, out=None):
+        """queries: list of bytes, already lower-cased by the host, or a packed (q_off u32[nq+1], q_bytes u8[])
+        pair.  out=(off u64[nq+1], ids u32[cap]) runs into caller buffers (e.g. pinned ones)."""
+        if isinstance(queries, tuple):
+            q_off, qb = queries
+            nq = q_off.size - 1
+        else:
+            nq = len(queries)
+            q_off = np.zeros(nq + 1, np.uint32)
+            if nq:
+                np.cumsum([len(q) for q in queries], out=q_off[1:])
+            qb = np.frombuffer(b"".join(queries) + b"\0", dtype=np.uint8).copy()
         if v_hi is None:
             v_hi = self.V
-        off = np.zeros(nq + 1, np.uint64)
         need = C.c_uint64(0)
+        if out is not None:
+            off, ids = out
+            _check(self.L.dmg_search_batch(self.h, kind, v_lo, v_hi, nq, q_off.ctypes.data, qb.ctypes.data,
+                                           off.ctypes.data, ids.ctypes.data, ids.size, C.byref(need)))
+            return off, ids[:need.value]
+        off = np.zeros(nq + 1, np.uint64)
         if cap is None:
             rc = self.L.dmg_search_batch(self.h, kind, v_lo, v_hi, nq, q_off.ctypes.data, qb.ctypes.data,
                                          off.ctypes.data, None, 0, C.byref(need))

@@ -174,13 +174,17 @@ def big_graph(n_vertices, n_edges, cap, entry_frac, seed, with_names=False):
     return SynthGraph(names, s, d, entry, np.array([0, n_vertices]))
 
 
-def big_graph_fast(n_vertices, n_edges, cap, entry_frac, seed):
+def big_graph_fast(n_vertices, n_edges, cap, entry_frac, seed, threads=None):
     """Config-5-sized graphs (20 M / 500 M): same out-degree law and Zipf(s=1) target ranking as
     big_graph, but targets are drawn WITH replacement in one vectorised pass (the exact
     without-replacement rejection loop needs several sorts of 10^9 keys).  Repeated (src, dst) pairs
     are legal input -- addDependency collapses them (ProjectGraph.java:182) and so does
     dmg_graph_create -- so the graph the engine holds has slightly fewer edges than drawn; the
-    kept count is in dmg_graph_info."""
+    kept count is in dmg_graph_info.  Targets are drawn in fixed chunks of 8 M edges, chunk i from
+    the i-th jump of the seed's PCG64 stream, on a thread pool (numpy releases the GIL): the
+    result depends on the seed only, not on the thread count."""
+    import os
+    from concurrent.futures import ThreadPoolExecutor
     rng = np.random.Generator(np.random.PCG64(seed))
     deg = _degrees(rng, n_vertices, n_edges, cap)
     perm = rng.permutation(n_vertices).astype(np.uint32)
@@ -188,10 +192,17 @@ def big_graph_fast(n_vertices, n_edges, cap, entry_frac, seed):
     cdf /= cdf[-1]
     src = np.repeat(np.arange(n_vertices, dtype=np.uint32), deg)
     dst = np.empty(src.size, np.uint32)
-    step = 50_000_000
-    for a in range(0, src.size, step):
-        b = min(src.size, a + step)
-        dst[a:b] = perm[np.searchsorted(cdf, rng.random(b - a), side="left").clip(0, n_vertices - 1)]
+    step = 8_000_000
+    base = np.random.PCG64(seed ^ 0xD57)
+
+    def fill(i):
+        a, b = i * step, min(src.size, (i + 1) * step)
+        r = np.random.Generator(base.jumped(i + 1))
+        dst[a:b] = perm[np.searchsorted(cdf, r.random(b - a), side="left").clip(0, n_vertices - 1)]
+
+    n_chunks = (src.size + step - 1) // step
+    with ThreadPoolExecutor(max_workers=threads or min(16, os.cpu_count() or 1)) as ex:
+        list(ex.map(fill, range(n_chunks)))
     ne = max(1, int(round(entry_frac * n_vertices)))
     entry = np.sort(rng.choice(n_vertices, ne, replace=False))
     return SynthGraph(None, src, dst, entry, np.array([0, n_vertices]))
@@ -328,3 +339,53 @@ def search_queries(name_off, name_bytes, n_queries=16384, seed=SEED_C3_QUERIES):
             st = int(rng.integers(0, len(w) - ln + 1))
             out.append(w[st:st + ln].encode("ascii"))
     return out
+
+
+# ---- BASELINE config 4: the graph_query DSL mix ------------------------------------
+C4_MIX = [("dependencies", 0.40), ("dependents", 0.20), ("overview", 0.15), ("khop", 0.10),
+          ("resolve_name", 0.05), ("method", 0.05), ("entrypoints", 0.03), ("endpoints", 0.02)]
+C4_OPCODES = [0, 1, 2, 3, 5, 6, 4, 7]   # DMG_OP_* of the kinds above, in C4_MIX order
+
+
+def method_catalog(n_vertices, per_vertex=10):
+    """10 methods per vertex held host-side: 8 lower-case bytes each, a 4-letter verb +
+    4 hex digits of (7 v + j).  Returns (method_off u32[V+1], name_off u32[M+1], lower bytes u8[8 M])."""
+    V = n_vertices
+    verbs = np.frombuffer(b"findsavelistloadsendreadpushpullopenstop", dtype=np.uint8).reshape(10, 4)[:per_vertex]
+    num = ((np.arange(V, dtype=np.int64)[:, None] * 7 + np.arange(per_vertex)[None, :]) & 0xFFFF)
+    hexd = np.frombuffer(b"0123456789abcdef", dtype=np.uint8)
+    digits = hexd[(num[:, :, None] >> np.array([12, 8, 4, 0])[None, None, :]) & 15]
+    mbytes = np.concatenate([np.broadcast_to(verbs[None, :, :], (V, per_vertex, 4)), digits], axis=2).reshape(-1)
+    return (np.arange(V + 1, dtype=np.uint32) * per_vertex, np.arange(per_vertex * V + 1, dtype=np.uint32) * 8,
+            np.ascontiguousarray(mbytes))
+
+
+def c4_mix_ops(n, names, mbytes, op_dtype, seed=SEED_C4 + 3, mode=0):
+    """`n` tokenised graph_query operations in the SURVEY 8d config-4 mix over one graph of
+    len(names) vertices: 40 % dependencies, 20 % dependents, 15 % overview, 10 % k-hop OUT k in
+    {2,3,4}, 5 % simple-name resolution, 5 % ?check, 3 % entrypoints, 2 % endpoints.  Returns
+    (ops structured array of op_dtype == dmg_query_op, text u8[], kind index per op into C4_MIX)."""
+    V = len(names)
+    r = np.random.Generator(np.random.PCG64(seed))
+    u = r.random(n)
+    kind = np.searchsorted(np.cumsum([w for _, w in C4_MIX]), u, side="right").clip(0, 7)
+    opcode = np.array(C4_OPCODES, np.uint32)[kind]
+    ops = np.zeros(n, op_dtype)
+    ops["opcode"] = opcode
+    ops["vertex"] = r.integers(0, V, n)
+    ops["mode"] = mode
+    ops["k"] = np.where(opcode == 3, r.integers(2, 5, n), 1)
+    text = bytearray()
+    for i in np.flatnonzero((opcode == 5) | (opcode == 6)):
+        v = int(ops["vertex"][i])
+        if opcode[i] == 5:
+            t = names[v].rsplit(".", 1)[-1].lower().encode()
+        elif r.random() < 0.8:
+            j = int(r.integers(0, 10))
+            t = bytes(mbytes[(v * 10 + j) * 8:(v * 10 + j + 1) * 8])
+        else:
+            t = b"nosuchmethod"
+        ops["text_begin"][i] = len(text)
+        text += t
+        ops["text_end"][i] = len(text)
+    return ops, np.frombuffer(bytes(text) + b"\0", dtype=np.uint8).copy(), kind

@@ -311,7 +311,10 @@ int32_t dmg_lookup_batch(dmg_graph* g, int32_t kind, uint32_t v_lo, uint32_t v_h
  *                        indices of the methods flagged as HTTP endpoints (dmg_graph_set_method_flags),
  *                        ascending = vertex order then method order (the reference walks a HashMap
  *                        here; its order is pinned by no test)
- * text of an op is text_bytes[text_begin .. text_end).  Unknown vertices give empty rows.      */
+ * text of an op is text_bytes[text_begin .. text_end).  Unknown vertices give empty rows.
+ * On a handle that holds several projects, ENTRYPOINTS, ENDPOINTS and RESOLVE_NAME answer for the
+ * project named by op.project only (the reference resolves the project first and then works on
+ * that project's ProjectGraph, GQS:56-62, 423-456); vertex-addressed ops need no scope.         */
 #define DMG_OP_DEPENDENCIES 0
 #define DMG_OP_DEPENDENTS 1
 #define DMG_OP_OVERVIEW 2
@@ -329,7 +332,9 @@ typedef struct dmg_query_op {
   uint32_t exclude_sources; /* DMG_OP_KHOP */
   uint32_t text_begin;
   uint32_t text_end;
-  uint32_t reserved;
+  uint32_t project;         /* DMG_OP_ENTRYPOINTS / ENDPOINTS / RESOLVE_NAME: index of the project range
+                               (dmg_graph_desc.part_off) the op is asked of -- graph_query names ONE
+                               project (GQS:56-62); 0 on a single-project handle; out of range = DMG_EINVAL */
 } dmg_query_op;
 
 int32_t dmg_query_batch(dmg_graph* g, uint64_t n_ops, const dmg_query_op* ops, const uint8_t* text_bytes,

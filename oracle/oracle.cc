@@ -28,6 +28,7 @@
 // GQS = .../analysis/application/GraphQueryService.java (all under /root/reference).
 
 #include <algorithm>
+#include <array>
 #include <atomic>
 #include <cstdint>
 #include <cstring>
@@ -654,6 +655,108 @@ uint64_t ora_search_batch(uint32_t v_lo, uint32_t v_hi, const uint64_t* name_off
       if (out_ids && w < cap) out_ids[w] = v;
       ++w;
     }
+  }
+  out_off[nq] = w;
+  return w;
+}
+
+// ---- the same kind-0 result (CCS:1511-1526: every id whose lower-cased identifier contains the
+// query, nodes order) computed by ONE Aho-Corasick pass over the arena instead of one
+// contains() per (query, name).  Not a restatement of the reference's loop -- it exists so that
+// BASELINE config 3 (10 M names x 16,384 queries) can be checked at full size in seconds; the CPU
+// tests hold it to ora_search_batch, which IS the restatement, on random inputs.
+uint64_t ora_search_batch_ac(uint32_t v_lo, uint32_t v_hi, const uint64_t* name_off, const uint8_t* lower_bytes,
+                             uint64_t nq, const uint32_t* q_off, const uint8_t* q_bytes, uint64_t* out_off,
+                             uint32_t* out_ids, uint64_t cap, int n_threads) {
+  // distinct patterns; queries with the same text share one
+  std::unordered_map<std::string, uint32_t> pat_id;
+  std::vector<std::string> pats;
+  std::vector<uint32_t> q_pat(nq);
+  std::vector<uint64_t> empty_q;
+  for (uint64_t q = 0; q < nq; ++q) {
+    std::string t(reinterpret_cast<const char*>(q_bytes) + q_off[q], q_off[q + 1] - q_off[q]);
+    auto it = pat_id.find(t);
+    if (it == pat_id.end()) {
+      it = pat_id.emplace(t, (uint32_t)pats.size()).first;
+      pats.push_back(t);
+    }
+    q_pat[q] = it->second;
+  }
+  const uint32_t np = (uint32_t)pats.size();
+  // trie with dense 256-way goto (built to a DFA), output = pattern ending here + dictionary link
+  std::vector<std::array<int32_t, 256>> go(1);
+  go[0].fill(-1);
+  std::vector<int32_t> out_pat(1, -1), fail(1, 0), dict(1, -1);
+  int32_t empty_pat = -1;
+  for (uint32_t p = 0; p < np; ++p) {
+    if (pats[p].empty()) { empty_pat = (int32_t)p; continue; }
+    int32_t s = 0;
+    for (unsigned char ch : pats[p]) {
+      if (go[s][ch] < 0) {
+        go[s][ch] = (int32_t)go.size();
+        go.emplace_back();
+        go.back().fill(-1);
+        out_pat.push_back(-1);
+        fail.push_back(0);
+        dict.push_back(-1);
+      }
+      s = go[s][ch];
+    }
+    out_pat[s] = (int32_t)p;
+  }
+  {
+    std::vector<int32_t> bfs;
+    for (int c = 0; c < 256; ++c) {
+      if (go[0][c] < 0) go[0][c] = 0; else { fail[go[0][c]] = 0; bfs.push_back(go[0][c]); }
+    }
+    for (size_t h = 0; h < bfs.size(); ++h) {
+      const int32_t s = bfs[h];
+      const int32_t f = fail[s];
+      dict[s] = out_pat[f] >= 0 ? f : dict[f];
+      for (int c = 0; c < 256; ++c) {
+        const int32_t t = go[s][c];
+        if (t < 0) go[s][c] = go[f][c];
+        else { fail[t] = go[f][c]; bfs.push_back(t); }
+      }
+    }
+  }
+  // scan: every thread owns a contiguous id range and logs (pattern, id) once per name
+  const uint64_t nv = v_hi > v_lo ? v_hi - v_lo : 0;
+  const int T = std::max(1, n_threads);
+  std::vector<std::vector<std::pair<uint32_t, uint32_t>>> hits(T);
+  parallel_for(nv, T, [&](int t, uint64_t a, uint64_t b) {
+    std::vector<uint32_t> stamp(np, 0xFFFFFFFFu);
+    auto& h = hits[t];
+    for (uint64_t i = a; i < b; ++i) {
+      const uint32_t v = v_lo + (uint32_t)i;
+      if (empty_pat >= 0) h.emplace_back((uint32_t)empty_pat, v);   // "".contains is true for every name
+      int32_t s = 0;
+      for (uint64_t j = name_off[v]; j < name_off[v + 1]; ++j) {
+        s = go[s][lower_bytes[j]];
+        for (int32_t o = out_pat[s] >= 0 ? s : dict[s]; o >= 0; o = dict[o]) {
+          const uint32_t p = (uint32_t)out_pat[o];
+          if (stamp[p] != v) { stamp[p] = v; h.emplace_back(p, v); }
+        }
+      }
+    }
+  });
+  // per-pattern rows: thread chunks are ascending id ranges in thread order
+  std::vector<uint64_t> pcount(np + 1, 0);
+  for (auto& h : hits) for (auto& e : h) ++pcount[e.first + 1];
+  for (uint32_t p = 0; p < np; ++p) pcount[p + 1] += pcount[p];
+  std::vector<uint32_t> prow(pcount[np]);
+  {
+    std::vector<uint64_t> cur(pcount.begin(), pcount.end() - 1);
+    for (auto& h : hits) for (auto& e : h) prow[cur[e.first]++] = e.second;
+  }
+  uint64_t w = 0;
+  for (uint64_t q = 0; q < nq; ++q) {
+    out_off[q] = w;
+    const uint32_t p = q_pat[q];
+    const uint64_t n = pcount[p + 1] - pcount[p];
+    if (out_ids)
+      for (uint64_t j = 0; j < n && w + j < cap; ++j) out_ids[w + j] = prow[pcount[p] + j];
+    w += n;
   }
   out_off[nq] = w;
   return w;

@@ -77,6 +77,9 @@ def lib():
         L.ora_search_batch.argtypes = [C.c_uint32, C.c_uint32, u64p, u8p, C.c_int, C.c_uint64, u32p, u8p, u64p,
                                        C.c_void_p, C.c_uint64, C.c_int]
         L.ora_search_batch.restype = C.c_uint64
+        L.ora_search_batch_ac.argtypes = [C.c_uint32, C.c_uint32, u64p, u8p, C.c_uint64, u32p, u8p, u64p,
+                                          C.c_void_p, C.c_uint64, C.c_int]
+        L.ora_search_batch_ac.restype = C.c_uint64
         L.ora_hardware_threads.restype = C.c_int
         _LIB = L
     return _LIB
@@ -285,4 +288,26 @@ def search_batch(name_off, lower_bytes, queries, kind=0, v_lo=0, v_hi=None, thre
     need = L.ora_search_batch(v_lo, v_hi, no, lb, kind, nq, q_off, qb, off, None, 0, threads)
     ids = np.zeros(max(1, need), np.uint32)
     L.ora_search_batch(v_lo, v_hi, no, lb, kind, nq, q_off, qb, off, ids.ctypes.data, need, threads)
+    return off, ids[:need]
+
+
+def search_batch_ac(name_off, lower_bytes, queries, v_lo=0, v_hi=None, threads=1):
+    """kind-0 search (all hits, nodes order) by one Aho-Corasick pass over the arena: the same rows as
+    search_batch(kind=0), fast enough for BASELINE config 3 at full size.  The CPU tests hold it to
+    search_batch (the restatement of the reference's per-identifier contains loop)."""
+    L = lib()
+    nq = len(queries)
+    q_off = np.zeros(nq + 1, np.uint32)
+    np.cumsum([len(q) for q in queries], out=q_off[1:])
+    qb = np.frombuffer(b"".join(queries) + b"\0", dtype=np.uint8).copy()
+    if v_hi is None:
+        v_hi = name_off.size - 1
+    off = np.zeros(nq + 1, np.uint64)
+    lb = np.ascontiguousarray(lower_bytes, np.uint8)
+    if lb.size == 0:
+        lb = np.zeros(1, np.uint8)
+    no = np.ascontiguousarray(name_off, np.uint64)
+    need = L.ora_search_batch_ac(v_lo, v_hi, no, lb, nq, q_off, qb, off, None, 0, threads)
+    ids = np.zeros(max(1, need), np.uint32)
+    L.ora_search_batch_ac(v_lo, v_hi, no, lb, nq, q_off, qb, off, ids.ctypes.data, need, threads)
     return off, ids[:need]

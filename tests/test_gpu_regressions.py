@@ -1,0 +1,145 @@
+"""GPU regression tests for faults found by review: each case failed, or
+could fail, before the fix it names.  All calls go through the C ABI; results are compared with
+the oracle bit for bit."""
+import struct
+
+import numpy as np
+import pytest
+
+import dmgraph
+from dmgraph import synth
+from oracle import oracle as ora
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def engine():
+    e = dmgraph.Engine(0)
+    yield e
+    e.close()
+
+
+# ---- khop_global_kernel: bucket index of the last vertices of a project --------------------------
+@pytest.mark.parametrize("n", [8193, 8199, 16385, 16399, 24577])
+def test_khop_global_last_vertices_of_project(engine, n):
+    """Project sizes just above 1024 << sh: ids n-1, n-2, ... used to land in radix bucket 1024 (one
+    past the table).  Queries whose short rows contain exactly those vertices."""
+    rng = np.random.default_rng(n)
+    tail = np.arange(n - 8, n)
+    hubs = rng.integers(0, n - 8, 64)
+    src = np.concatenate([np.repeat(hubs, 8), rng.integers(0, n, 4 * n), tail, tail])
+    dst = np.concatenate([np.tile(tail, 64), rng.integers(0, n, 4 * n), np.roll(tail, 1), rng.integers(0, n, 8)])
+    entry = np.array([0, n - 1], np.uint32)
+    g = dmgraph.Graph(engine, n, src, dst, entry)
+    o = ora.CsrOracle(n, src, dst, entry)
+    qs = np.concatenate([hubs, tail, rng.integers(0, n, 64)]).astype(np.uint32)
+    q_off = np.arange(qs.size + 1, dtype=np.uint32)
+    for mode, k, excl in [(0, 1, 0), (1, 1, 0), (2, 1, 1), (0, 2, 0), (2, 2, 1), (2, 3, 0)]:
+        off, ids, hop = g.neighbors_batch(mode, k, excl, q_off, qs)
+        woff, wids, whop, _ = o.khop_batch(mode, k, excl, q_off, qs, threads=8)
+        assert np.array_equal(off, woff) and np.array_equal(ids, wids) and np.array_equal(hop, whop)
+        assert (ids == n - 1).any()
+    g.release()
+
+
+# ---- dmg_query_batch on a handle that holds several projects -------------------------------------
+def test_query_batch_scopes_graph_wide_ops_to_one_project(engine):
+    """ENTRYPOINTS / ENDPOINTS / RESOLVE_NAME answer for op.project only (GQS:56-62: graph_query
+    resolves the project, then works on that project's graph): the multi-project handle must give
+    what a handle holding just that project gives."""
+    sg = synth.eco_graph(n_projects=4, v_per=300, e_per=2000, cap=50, seed=77)
+    # the same simple names in every project, so an unscoped lookup would answer from project 0
+    names = ["p%d.pkg%d.Cls%d" % (v // 300, v % 3, (v % 300) // 2) for v in range(sg.n_vertices)]
+    off, arena = synth.pack_names(names)
+    low = np.frombuffer(bytes(arena).lower(), dtype=np.uint8).copy()
+    rng = np.random.default_rng(3)
+    entry = rng.permutation(sg.n_vertices)[:40].astype(np.uint32)       # interleaved across projects
+    g = dmgraph.Graph(engine, sg.n_vertices, sg.src, sg.dst, entry, part_off=sg.part_off, name_off=off,
+                      name_bytes=arena)
+    meths = [["m%d" % j for j in range(v % 3)] for v in range(sg.n_vertices)]
+    g.set_methods(meths)
+    flags = [int((i * 7) % 5 == 0) for i in range(sum(len(m) for m in meths))]
+    g.set_method_flags(flags)
+    mbase = np.concatenate([[0], np.cumsum([len(m) for m in meths])])
+    texts = [b"cls7", b"cls149", b"pkg1.cls", b"nosuch", b"p2.pkg"]
+    for p in range(4):
+        lo, hi = int(sg.part_off[p]), int(sg.part_off[p + 1])
+        ops = [{"op": dmgraph.OP_ENTRYPOINTS, "project": p}, {"op": dmgraph.OP_ENDPOINTS, "project": p}]
+        ops += [{"op": dmgraph.OP_RESOLVE_NAME, "project": p, "text": t} for t in texts]
+        got = g.query_batch(ops)
+        assert got[0][0] == [int(v) for v in entry if lo <= v < hi]              # insertion order kept
+        assert got[1][0] == [i for i, f in enumerate(flags) if f and mbase[lo] <= i < mbase[hi]]
+        for t, (ids, aux) in zip(texts, got[2:]):
+            _o1, i1 = ora.search_batch(off, low, [t], 1, lo, hi)
+            _o2, i2 = ora.search_batch(off, low, [t], 2, lo, hi)
+            want = ([int(i1[0])], [2]) if i1.size else (([int(i2[0])], [3]) if i2.size else ([], []))
+            assert (ids, aux) == want
+    with pytest.raises(dmgraph.DmgError) as ei:
+        g.query_batch([{"op": dmgraph.OP_ENTRYPOINTS, "project": 4}])
+    assert ei.value.code == dmgraph.EINVAL
+    g.release()
+
+
+# ---- dmg_graph_load: a snapshot is untrusted input -----------------------------------------------
+def test_snapshot_load_rejects_damaged_files(engine, tmp_path):
+    sg = synth.eco_graph(n_projects=3, v_per=200, e_per=1500, cap=40, seed=5)
+    off, arena = synth.pack_names(sg.names)
+    g = dmgraph.Graph(engine, sg.n_vertices, sg.src, sg.dst, sg.entry, part_off=sg.part_off, name_off=off,
+                      name_bytes=arena)
+    path = tmp_path / "ok.dmgcsr"
+    g.save(str(path))
+    good = path.read_bytes()
+    hdr = struct.Struct("<8sIIIIQQQQ")
+    magic, V, n_entry, n_parts, has_names, E, name_bytes, dropped, dups = hdr.unpack_from(good)
+    o_out_ptr = hdr.size
+    o_out_idx = o_out_ptr + 4 * (V + 1)
+    o_in_ptr = o_out_idx + 4 * E
+    o_in_idx = o_in_ptr + 4 * (V + 1)
+    o_part = o_in_idx + 4 * E
+
+    def damaged(edit):
+        b = bytearray(good)
+        edit(b)
+        p = tmp_path / "bad.dmgcsr"
+        p.write_bytes(bytes(b))
+        with pytest.raises(dmgraph.DmgError) as ei:
+            dmgraph.Graph.load(engine, str(p))
+        assert ei.value.code in (dmgraph.EINVAL, dmgraph.ENOMEM)
+
+    def put32(b, at, v):
+        struct.pack_into("<I", b, at, v)
+
+    out_idx = np.frombuffer(good, np.uint32, E, o_out_idx)
+    in_idx = np.frombuffer(good, np.uint32, E, o_in_idx)
+    damaged(lambda b: b.__delitem__(slice(len(b) - 10, len(b))))                       # truncated
+    damaged(lambda b: struct.pack_into("<I", b, 8, 0x7FFFFFFF))                         # V inflated: no huge allocation
+    damaged(lambda b: struct.pack_into("<Q", b, 24, 0x7FFFFFE0))                        # E inflated
+    damaged(lambda b: put32(b, 16, 0))                                                  # n_parts = 0
+    damaged(lambda b: put32(b, o_part + 4, 500))                                        # part_off not monotone
+    damaged(lambda b: put32(b, o_out_idx, int(out_idx[0]) % 200 + 200))                 # edge leaves its project
+    damaged(lambda b: put32(b, o_in_idx, (int(in_idx[0]) + 1) % 200))                   # reverse CSR not the transpose
+    damaged(lambda b: put32(b, o_out_ptr + 8, 0xFFFFFFF0))                              # offsets not monotone
+    r = dmgraph.Graph.load(engine, str(path))                                           # the intact file still loads
+    assert r.info["n_edges"] == g.info["n_edges"]
+    r.release()
+    g.release()
+
+
+# ---- row sizes that sum past 2^32 inside one scan tile -------------------------------------------
+def test_adjacency_tile_sum_above_u32(engine):
+    """256 copies of a hub row of > 2^24 entries put more than 2^32 entries in one 256-id tile: the
+    offsets and `needed` must not wrap (only sized here: capacity 0)."""
+    n = (1 << 24) + 4096
+    src = np.arange(1, n, dtype=np.uint32)
+    dst = np.zeros(n - 1, np.uint32)
+    g = dmgraph.Graph(engine, n, src, dst, [])
+    ids = np.zeros(300, np.uint32)
+    off = np.zeros(ids.size + 1, np.uint64)
+    import ctypes as C
+    need = C.c_uint64(0)
+    rc = g.L.dmg_adjacency_batch(g.h, dmgraph.IN, ids.size, ids.ctypes.data, off.ctypes.data, None, 0, C.byref(need))
+    assert rc == dmgraph.ECAP
+    assert need.value == 300 * (n - 1)
+    assert np.array_equal(off, np.arange(301, dtype=np.uint64) * np.uint64(n - 1))
+    g.release()
