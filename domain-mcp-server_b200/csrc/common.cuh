@@ -155,8 +155,8 @@ struct LaunchScope {
   CallCtx* c;
   cudaEvent_t a = nullptr, b = nullptr;
   int kid;
-  LaunchScope(CallCtx* ctx, int kernel_id) : c(ctx), kid(kernel_id) {
-    c->stats.kernel_launches++;
+  LaunchScope(CallCtx* ctx, int kernel_id, bool count = true, int launches = 1) : c(ctx), kid(kernel_id) {
+    if (count) c->stats.kernel_launches += launches;
     if (c->eng->profile.load(std::memory_order_relaxed)) {
       a = c->get_event();
       b = c->get_event();
@@ -200,6 +200,17 @@ struct dmg_graph {
   uint32_t* d_simple_tbl = nullptr;  // hash(lower-cased simple name) -> FIRST vertex of each project with that simple name
   uint32_t* d_simple_next = nullptr; // next vertex (ascending id) of the same project with the same simple name
   uint32_t tbl_mask = 0;
+  // Per-project sliced-ELL copies of the three row sets the bit-parallel k-hop pulls from (see
+  // khop_bits.cuh); built only when every project has <= 4096 vertices.  [0] = resolve rows (mode
+  // BOTH), [1] = in rows (mode OUT pulls through dependents), [2] = out rows (mode IN).
+  struct Ell {
+    uint32_t* d_proj_slice = nullptr;   // [P+1] first slice of each project
+    uint32_t* d_slice_off = nullptr;    // [S+1] start of each slice in d_data, in uint2 units
+    uint32_t* d_vrow = nullptr;         // [S*32] (forward degree << 16) | vertex - project base; 0xFFFF = no row
+    uint2* d_data = nullptr;            // slice = L/4 x 32 lanes x 4 u16 ids (lane-major inside a step); pad id = win_cap
+    uint64_t entries = 0;               // padded size in ids
+  } ell[3];
+  bool has_ell = false;
   uint32_t* d_method_off = nullptr;  // [V+1] optional method catalog (names only)
   uint32_t* d_mname_off = nullptr;   // [M+1]
   uint8_t* d_mname_lower = nullptr;

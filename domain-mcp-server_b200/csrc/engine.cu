@@ -157,6 +157,9 @@ static void free_graph(dmg_graph* g) {
                   (void*)g->d_und_ptr, (void*)g->d_und_idx, (void*)g->d_part_off, (void*)g->d_entry, (void*)g->d_entry_by_part, (void*)g->d_entry_bits, (void*)g->d_name_off,
                   (void*)g->d_lower, (void*)g->d_names, (void*)g->d_full_tbl, (void*)g->d_simple_tbl, (void*)g->d_simple_next, (void*)g->d_method_off, (void*)g->d_mname_off, (void*)g->d_mname_lower})
     if (p) cudaFree(p);
+  for (auto& el : g->ell)
+    for (void* p : {(void*)el.d_proj_slice, (void*)el.d_slice_off, (void*)el.d_vrow, (void*)el.d_data})
+      if (p) cudaFree(p);
   delete g;
 }
 
@@ -166,6 +169,60 @@ static int32_t upload(T** d, const T* h, size_t n, uint64_t* bytes) {
   DMG_CUDA(cudaMalloc((void**)d, b));
   if (n) DMG_CUDA(cudaMemcpy(*d, h, n * sizeof(T), cudaMemcpyHostToDevice));
   *bytes += b;
+  return DMG_OK;
+}
+
+// Sliced-ELL form of one row set, per project (khop_bits.cuh reads it): rows longer than ELL_ROW_CAP
+// are cut into virtual rows, the virtual rows of a project are sorted by length (longest first) and
+// packed 32 to a slice; inside a slice lane l owns virtual row l and step j holds the j-th id of
+// every lane, four steps packed into one uint2 per lane -- so a warp reads a slice with coalesced
+// 8-byte loads and every lane ORs its own row without any cross-lane step.  Ids are relative to the
+// project base (u16: projects here have <= 4096 vertices); short rows are padded with `pad_id`, the
+// index of an all-zero word the kernel keeps behind each set.  fwd_ptr gives the FORWARD degree of
+// the row's vertex for the TE count (the pull reads reverse rows).
+constexpr uint32_t ELL_ROW_CAP = 256;
+static int32_t build_ell(dmg_graph::Ell* out, const std::vector<uint32_t>& ptr, const std::vector<uint32_t>& idx,
+                         const std::vector<uint32_t>& fwd_ptr, const std::vector<uint32_t>& part, uint32_t pad_id,
+                         uint64_t* bytes) {
+  const size_t P = part.size() - 1;
+  std::vector<uint32_t> proj_slice(P + 1, 0), slice_off(1, 0), vrow;
+  std::vector<uint16_t> data;
+  struct VR { uint32_t len, v, start; };
+  std::vector<VR> vr;
+  for (size_t p = 0; p < P; ++p) {
+    const uint32_t lo = part[p], hi = part[p + 1];
+    vr.clear();
+    for (uint32_t v = lo; v < hi; ++v)
+      for (uint32_t b = ptr[v]; b < ptr[v + 1]; b += ELL_ROW_CAP) vr.push_back({std::min(ELL_ROW_CAP, ptr[v + 1] - b), v, b});
+    std::stable_sort(vr.begin(), vr.end(), [](const VR& a, const VR& b) { return a.len > b.len; });
+    while (vr.size() % 32) vr.push_back({0u, 0xFFFFFFFFu, 0u});
+    for (size_t s0 = 0; s0 < vr.size(); s0 += 32) {
+      const uint32_t L = (vr[s0].len + 3u) & ~3u;   // longest row of the slice, padded to whole uint2 steps
+      const size_t base = data.size();
+      data.resize(base + (size_t)L * 32, (uint16_t)pad_id);
+      for (uint32_t l = 0; l < 32; ++l) {
+        const VR& r = vr[s0 + l];
+        if (r.v == 0xFFFFFFFFu) {
+          vrow.push_back(0xFFFFu);
+          continue;
+        }
+        const uint32_t deg = std::min<uint32_t>(fwd_ptr[r.v + 1] - fwd_ptr[r.v], 0xFFFFu);
+        vrow.push_back((deg << 16) | (r.v - lo));
+        for (uint32_t j = 0; j < r.len; ++j)   // step j of lane l: uint2 (j/4)*32 + l, u16 slot j%4
+          data[base + ((size_t)(j >> 2) * 32 + l) * 4 + (j & 3)] = (uint16_t)(idx[r.start + j] - lo);
+      }
+      slice_off.push_back((uint32_t)(data.size() / 4));
+    }
+    proj_slice[p + 1] = (uint32_t)(slice_off.size() - 1);
+  }
+  if (data.empty()) data.resize(4, (uint16_t)pad_id);
+  out->entries = data.size();
+  int32_t st;
+  if ((st = upload(&out->d_proj_slice, proj_slice.data(), proj_slice.size(), bytes)) != DMG_OK ||
+      (st = upload(&out->d_slice_off, slice_off.data(), slice_off.size(), bytes)) != DMG_OK ||
+      (st = upload(&out->d_vrow, vrow.data(), vrow.size(), bytes)) != DMG_OK ||
+      (st = upload(reinterpret_cast<uint16_t**>(&out->d_data), data.data(), data.size(), bytes)) != DMG_OK)
+    return st;
   return DMG_OK;
 }
 
@@ -237,6 +294,17 @@ static int32_t finish_upload_impl(dmg_engine* e, dmg_graph* g, uint32_t V, const
     *g_freed = true;
     free_graph(g);
     return st;
+  }
+  if (max_part <= 4096 && V > 0) {   // MB_MAX_WINDOW of khop_bits.cuh
+    const uint32_t pad_id = (std::max<uint32_t>(max_part, 1) + 127u) & ~127u;
+    if ((st = build_ell(&g->ell[0], und_ptr, und_idx, und_ptr, part, pad_id, &bytes)) != DMG_OK ||
+        (st = build_ell(&g->ell[1], in_ptr, in_idx, out_ptr, part, pad_id, &bytes)) != DMG_OK ||
+        (st = build_ell(&g->ell[2], out_ptr, out_idx, in_ptr, part, pad_id, &bytes)) != DMG_OK) {
+      *g_freed = true;
+      free_graph(g);
+      return st;
+    }
+    g->has_ell = true;
   }
   uint64_t nbytes = 0;
   if (d->name_off) {

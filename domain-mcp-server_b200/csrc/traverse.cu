@@ -9,6 +9,7 @@
 // decoupled look-back allocator of common.cuh, so results come out packed, in query order and
 // in ONE pass over the graph data.
 #include <algorithm>
+#include <cstdlib>
 #include <atomic>
 #include <mutex>
 
@@ -80,6 +81,10 @@ static inline void launch_windows(const KhopArgs& a, cudaStream_t stream) {
   const unsigned long long n = a.q_end - a.q_begin;
   if (n) khop_windows_kernel<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>(a);
 }
+
+}  // namespace dmg
+#include "khop_bits.cuh"
+namespace dmg {
 
 // ---------------------------------------------------------------------------------------------
 // khop_small: one CTA per query, everything about the query lives in shared memory.
@@ -892,6 +897,128 @@ static int32_t fetch_counters(CallCtx* c) {
   return DMG_OK;
 }
 
+// planes needed for hop codes 1..k (binary-coded): k = 1 -> 1, k <= 3 -> 2, k <= 7 -> 3
+static inline int hop_planes(int k) { return k <= 1 ? 1 : (k <= 3 ? 2 : (k <= 7 ? 3 : 8)); }
+
+// Set-word width of the bit-parallel path: 128 queries per group when the sets fit shared memory,
+// else 64; 0 = the path does not apply (project too large, too many hops, no ELL copy).
+static inline int bit_parallel_w64(const dmg_graph* g, int k) {
+  const Engine* e = g->eng;
+  const uint32_t maxp = std::max<uint32_t>(g->info.max_part_vertices, 1);
+  if (!g->has_ell || maxp > MB_MAX_WINDOW || hop_planes(k) > MB_MAX_PLANES) return 0;
+  const uint32_t wc = (maxp + 127u) & ~127u;
+  static const int forced = [] {
+    const char* s = getenv("DMG_MB_W64");   // tuning runs only
+    return s ? atoi(s) : 0;
+  }();
+  for (int w64 = 2; w64 >= 1; --w64) {
+    if (forced && w64 != forced) continue;
+    if (msbfs_smem(wc, hop_planes(k), k, w64) + 2048 <= e->smem_optin) return w64;
+  }
+  return 0;
+}
+
+template <class F>
+static inline int32_t with_planes(int np, int w64, F f) {
+  if (w64 == 2) {
+    if (np == 1) return f(khop_msbfs_kernel<1, 2>, khop_emit_bits_kernel<1>);
+    if (np == 2) return f(khop_msbfs_kernel<2, 2>, khop_emit_bits_kernel<2>);
+    return f(khop_msbfs_kernel<3, 2>, khop_emit_bits_kernel<3>);
+  }
+  if (np == 1) return f(khop_msbfs_kernel<1, 1>, khop_emit_bits_kernel<1>);
+  if (np == 2) return f(khop_msbfs_kernel<2, 1>, khop_emit_bits_kernel<2>);
+  return f(khop_msbfs_kernel<3, 1>, khop_emit_bits_kernel<3>);
+}
+
+// Layout of the grouping scratch of one chunk of queries (all u32 unless noted).
+struct MbLayout {
+  size_t o_qpart, o_qrank, o_hist, o_gbase, o_ngroups, o_grp_win, o_grp_part, o_grp_q, bytes;
+  uint64_t max_groups;
+  MbLayout(uint64_t nq, uint32_t n_parts, uint32_t slots) {
+    auto pad = [](size_t x) { return (x + 255) & ~size_t(255); };
+    max_groups = nq / slots + n_parts + 1;
+    o_qpart = 0;
+    o_qrank = pad(o_qpart + nq * 4);
+    o_hist = pad(o_qrank + nq * 4);
+    o_gbase = pad(o_hist + (size_t)n_parts * 4);
+    o_ngroups = pad(o_gbase + ((size_t)n_parts + 1) * 4);
+    o_grp_win = pad(o_ngroups + 4);
+    o_grp_part = pad(o_grp_win + max_groups * 8);
+    o_grp_q = pad(o_grp_part + max_groups * 4);
+    bytes = pad(o_grp_q + max_groups * slots * 4);
+  }
+};
+
+// The bit-parallel path (khop_bits.cuh) for one chunk [q0, q1) of the batch: classify + group the
+// queries by project, traverse 64 / 128 queries of a project per CTA into bit rows + row sizes.  `bits`
+// receives (q1 - q0) rows of np * WB words; counts / qwin are indexed by absolute query.
+static int32_t launch_bit_traversal(CallCtx* c, dmg_graph* g, int w64, int mode, int k, int exclude, uint64_t q0,
+                                    uint64_t q1, const uint32_t* d_q_off, const uint32_t* d_q_src, uint32_t* bits,
+                                    uint32_t* counts, uint32_t* qwin, unsigned char* grp_scratch, DevCounters* ctr,
+                                    cudaStream_t stream) {
+  Engine* e = g->eng;
+  const uint64_t n = q1 - q0;
+  const uint32_t maxp = std::max<uint32_t>(g->info.max_part_vertices, 1);
+  const int np = hop_planes(k);
+  const uint32_t slots = 64u * (uint32_t)w64;
+  const MbLayout L(n, g->info.n_parts, slots);
+  const dmg_graph::Ell& el = g->ell[mode == DMG_BOTH ? 0 : (mode == DMG_OUT ? 1 : 2)];
+  MbArgs a;
+  a.fptr = mode == DMG_BOTH ? g->d_und_ptr : (mode == DMG_OUT ? g->d_out_ptr : g->d_in_ptr);
+  a.ell_proj_slice = el.d_proj_slice;
+  a.ell_slice_off = el.d_slice_off;
+  a.ell_vrow = el.d_vrow;
+  a.ell_data = el.d_data;
+  a.slots = slots;
+  a.part_off = g->d_part_off;
+  a.V = g->info.n_vertices;
+  a.n_parts = g->info.n_parts;
+  a.k = k;
+  a.exclude = exclude ? 1 : 0;
+  a.nq = n;
+  a.q_off = d_q_off + q0;
+  a.q_src = d_q_src;
+  a.win_cap = (maxp + 127u) & ~127u;
+  a.WB = a.win_cap / 32;
+  a.qpart = reinterpret_cast<uint32_t*>(grp_scratch + L.o_qpart);
+  a.qrank = reinterpret_cast<uint32_t*>(grp_scratch + L.o_qrank);
+  a.qwin = qwin + 2 * q0;
+  a.part_hist = reinterpret_cast<uint32_t*>(grp_scratch + L.o_hist);
+  a.part_gbase = reinterpret_cast<uint32_t*>(grp_scratch + L.o_gbase);
+  a.n_groups = reinterpret_cast<uint32_t*>(grp_scratch + L.o_ngroups);
+  a.grp_win = reinterpret_cast<uint2*>(grp_scratch + L.o_grp_win);
+  a.grp_part = reinterpret_cast<uint32_t*>(grp_scratch + L.o_grp_part);
+  a.grp_q = reinterpret_cast<uint32_t*>(grp_scratch + L.o_grp_q);
+  a.bits = bits;
+  a.counts = counts + q0;
+  a.ctr = ctr;
+  DMG_CUDA(cudaMemsetAsync(a.part_hist, 0, (size_t)a.n_parts * 4, stream));
+  DMG_CUDA(cudaMemsetAsync(a.grp_q, 0xFF, L.max_groups * slots * 4, stream));
+  const size_t smem = msbfs_smem(a.win_cap, np, k, w64);
+  int occ = 1;
+  DMG_TRY(with_planes(np, w64, [&](auto kern, auto) -> int32_t {
+    DMG_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    DMG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, MB_THREADS, smem));
+    return DMG_OK;
+  }));
+  const unsigned qblocks = (unsigned)((n + 255) / 256);
+  {
+    LaunchScope ls(c, K_KHOP_WINDOWS, true, 3);
+    mb_classify_kernel<<<qblocks, 256, 0, stream>>>(a);
+    mb_groups_kernel<<<1, 1024, 0, stream>>>(a);
+    mb_scatter_kernel<<<qblocks, 256, 0, stream>>>(a);
+  }
+  const uint64_t grid = std::min<uint64_t>(L.max_groups, (uint64_t)e->sm_count * std::max(occ, 1));
+  {
+    LaunchScope ls(c, K_KHOP_SMALL);
+    with_planes(np, w64, [&](auto kern, auto) -> int32_t {
+      kern<<<(unsigned)grid, MB_THREADS, smem, stream>>>(a);
+      return DMG_OK;
+    });
+  }
+  return DMG_OK;
+}
+
 // Runs the k-hop batch on device buffers on c->stream; leaves counters in c->h_counters after
 // the caller synchronises.
 static int32_t run_khop(CallCtx* c, dmg_graph* g, int mode, int k, int exclude, uint64_t nq,
@@ -933,7 +1060,48 @@ static int32_t run_khop(CallCtx* c, dmg_graph* g, int mode, int k, int exclude, 
   a.stage = nullptr;
   a.counts = nullptr;
   a.qwin = nullptr;
-  if (maxp <= SMALL_WINDOW_MAX) {
+  if (const int w64 = bit_parallel_w64(g, k)) {
+    // 64 / 128 queries of one project per CTA -> bit rows + row sizes; scan; bit rows -> packed rows
+    const int np = hop_planes(k);
+    const uint32_t WB = a.win_cap / 32;
+    const uint64_t row_bytes = (uint64_t)np * WB * 4;
+    const uint64_t budget = std::max<uint64_t>(std::min<uint64_t>(e->scratch_budget, 2ull << 30), row_bytes);
+    const uint64_t chunk = std::max<uint64_t>(1, std::min<uint64_t>(nq, budget / row_bytes));
+    const MbLayout L(chunk, g->info.n_parts, 64u * (uint32_t)w64);
+    DMG_TRY(c->scratch.reserve(chunk * row_bytes));
+    DMG_TRY(c->tmp0.reserve(nq * 4));        // row sizes
+    DMG_TRY(c->tmp1.reserve(nq * 8));        // (lo, wn) per query
+    DMG_TRY(c->tmp2.reserve(L.bytes));       // grouping scratch
+    const uint64_t scan_tiles = (chunk + SC_THREADS * SC_ITEMS - 1) / (SC_THREADS * SC_ITEMS);
+    uint32_t* counts = c->tmp0.as<uint32_t>();
+    uint32_t* qwin = c->tmp1.as<uint32_t>();
+    unsigned long long* carry = &c->d_counters->aux[2];
+    for (uint64_t q0 = 0; q0 < nq; q0 += chunk) {
+      const uint64_t q1 = std::min<uint64_t>(nq, q0 + chunk);
+      if (q0) {   // later chunks reuse the ticket, the scan ticket and the look-back words
+        DMG_CUDA(cudaMemsetAsync(&c->d_counters->ticket, 0, 8, c->stream));
+        DMG_CUDA(cudaMemsetAsync(&c->d_counters->aux[1], 0, 8, c->stream));
+        DMG_CUDA(cudaMemsetAsync(c->status.p, 0, scan_tiles * sizeof(uint64_t), c->stream));
+      }
+      DMG_TRY(launch_bit_traversal(c, g, w64, mode, k, exclude, q0, q1, d_q_off, d_q_src, c->scratch.as<uint32_t>(), counts,
+                                   qwin, c->tmp2.as<unsigned char>(), c->d_counters, c->stream));
+      {
+        LaunchScope ls(c, K_SCAN_COUNTS);
+        const uint64_t tiles = (q1 - q0 + SC_THREADS * SC_ITEMS - 1) / (SC_THREADS * SC_ITEMS);
+        scan_counts_kernel<<<(unsigned)std::min<uint64_t>(tiles, (uint64_t)e->sm_count * 4), SC_THREADS, 0, c->stream>>>(
+            counts + q0, q1 - q0, a.out_off + q0, carry, c->status.as<uint64_t>(), c->d_counters);
+      }
+      if (a.cap) {
+        LaunchScope ls(c, K_KHOP_EMIT);
+        const uint64_t blocks = std::min<uint64_t>((q1 - q0 + 7) / 8, (uint64_t)e->sm_count * EM_GRID_PER_SM);
+        with_planes(np, w64, [&](auto, auto emit) -> int32_t {
+          emit<<<(unsigned)blocks, 256, 0, c->stream>>>(c->scratch.as<uint32_t>(), WB, q1 - q0, qwin + 2 * q0, counts + q0,
+                                                        a.out_off + q0, a.out_ids, a.out_hop, a.cap);
+          return DMG_OK;
+        });
+      }
+    }
+  } else if (maxp <= SMALL_WINDOW_MAX) {
     const uint32_t WC = a.win_cap;
     int occ = 0;
     size_t smem = 0;
