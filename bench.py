@@ -342,20 +342,29 @@ def main():
     e2e_value = total_queries / (e2e_ms_max * 1e-3)
     assert int(h_off[-1]) == cap
 
-    # the same answer as dense rows (one hop byte per project vertex): 5x fewer bytes over PCIe
-    stride = int(sg.part_off[1] + 127) & ~127
-    h_rows, p6 = eng.pinned(np.uint8, nq * stride)
+    # the same answer as bit rows (dmg_neighbors_batch_bits: two hop-code planes over the project's
+    # vertices, 512 B per query) and their expansion to the same (off, ids, hop) arrays by host threads
+    # (dmg_bits_decode): 20x fewer PCIe bytes, the arrays the packed call delivers
+    planes, words, _w, _c, _b = g.neighbors_batch_bits(dmgraph.BOTH, K_HOPS, 1, h_q_off[:2], h_q_src[:int(h_q_off[1])])
+    h_bits, p6 = eng.pinned(np.uint32, nq * planes * words)
     h_win, p7 = eng.pinned(np.uint32, nq * 2)
-    dense_ms = 0.0
+    h_cnt, p8 = eng.pinned(np.uint32, nq)
+    bits_ms, dec_ms, bits_d2h = 0.0, 0.0, 0
     for it in range(2 + args.steps):
         barrier()
         t0 = time.perf_counter()
-        g.neighbors_batch_rows(dmgraph.BOTH, K_HOPS, 1, h_q_off, h_q_src, out=(h_win.reshape(nq, 2), h_rows))
-        dt = 1e3 * (time.perf_counter() - t0)
+        g.neighbors_batch_bits(dmgraph.BOTH, K_HOPS, 1, h_q_off, h_q_src, out=(h_win.reshape(nq, 2), h_cnt, h_bits))
+        t1 = time.perf_counter()
+        bits_d2h = eng.last_stats()["d2h_bytes"]
+        h_off[:] = 0
+        dmgraph.bits_decode(planes, words, h_win, h_cnt, h_bits, out=(h_off, h_ids, h_hop))
+        t2 = time.perf_counter()
         if it >= 2:
-            dense_ms += dt
-            dense_d2h = eng.last_stats()["d2h_bytes"]
-    dense_ms_max = allmax(dense_ms)
+            bits_ms += 1e3 * (t1 - t0)
+            dec_ms += 1e3 * (t2 - t1)
+    assert int(h_off[-1]) == cap
+    bits_ms_max, both_ms_max = allmax(bits_ms), allmax(bits_ms + dec_ms)
+    h_bits_check = (h_off.copy(), h_ids.copy(), h_hop.copy()) if (rank == 0 and not args.no_cpu_baseline) else None
     clocks = sampler.stop()
 
     # ---- parity of what was just timed: last step's resident result vs the oracle --------------
@@ -370,7 +379,10 @@ def main():
             csr_line, o, res = cpu_csr(sg, q_off, q_src)
             assert np.array_equal(off_h, res[0]) and np.array_equal(ids_h, res[1]) and np.array_equal(hop_h, res[2]), \
                 "bench: the timed result differs from the oracle"
-            parity = {"rows": int(nq), "against": "oracle csr, whole batch (ids, hops, offsets bit-exact)"}
+            assert all(np.array_equal(x, y) for x, y in zip(h_bits_check, res[:3])), \
+                "bench: the decoded bit rows differ from the oracle"
+            parity = {"rows": int(nq), "against": "oracle csr, whole batch (ids, hops, offsets bit-exact), both the "
+                                                  "resident packed result and the decoded bit rows of the e2e call"}
         else:
             from oracle import oracle as ora
             o = ora.CsrOracle(sg.n_vertices, sg.src, sg.dst, sg.entry, sg.part_off)
@@ -389,11 +401,21 @@ def main():
             "gteps": gteps, "edges_traversed_per_step": int(edges), "edges_read_per_step": int(stats["edges_read"]),
             "wall_ms_per_step": allmax(wall_ms) / args.steps,
             "roofline": roofline,
-            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
-                    "ms_per_step": e2e_ms_max / args.steps, "host_buffers": "pinned"},
-            "e2e_dense_rows": {"value": total_queries / (dense_ms_max * 1e-3), "unit": UNIT,
-                               "ms_per_step": dense_ms_max / args.steps, "d2h_bytes_per_step": int(dense_d2h),
-                               "call": "dmg_neighbors_batch_rows (same sets and hops, one byte per project vertex)"},
+            "e2e": {"value": total_queries / (both_ms_max * 1e-3), "unit": UNIT, "h2d_bytes_per_step": int(h2d),
+                    "d2h_bytes_per_step": int(bits_d2h), "ms_per_step": both_ms_max / args.steps,
+                    "host_buffers": "pinned",
+                    "call": "dmg_neighbors_batch_bits (bit rows over PCIe) + dmg_bits_decode (host threads expand "
+                            "them to the (off, ids, hop) arrays dmg_neighbors_batch delivers); both inside the "
+                            "timed region",
+                    "transfer_ms_per_step": bits_ms_max / args.steps,
+                    "decode_ms_per_step": allmax(dec_ms) / args.steps, "decode_threads": os.cpu_count()},
+            "e2e_packed": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d),
+                           "d2h_bytes_per_step": int(d2h), "ms_per_step": e2e_ms_max / args.steps,
+                           "call": "dmg_neighbors_batch (packed (id, hop) rows over PCIe)"},
+            "e2e_bits_only": {"value": total_queries / (bits_ms_max * 1e-3), "unit": UNIT,
+                              "ms_per_step": bits_ms_max / args.steps, "d2h_bytes_per_step": int(bits_d2h),
+                              "call": "dmg_neighbors_batch_bits alone: a host that walks the neighbours reads the "
+                                      "planes directly"},
             "gpu_launches": int(launches), "clocks": clocks,
             "parity_checked": parity["rows"] if parity else 0, "parity": parity,
             "kernels": {k: {"launches": int(v[0]), "ms_per_launch": v[1] / v[0]} for k, v in prof.items()}}
@@ -404,7 +426,7 @@ def main():
     elif rank == 0:
         line["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": 0, "kind": "port",
                                 "sample": "measured at N=1 only"}
-    for p in (p1, p2, p3, p4, p5, p6, p7):
+    for p in (p1, p2, p3, p4, p5, p6, p7, p8):
         eng.pinned_free(p)
     g.release()
     for d in (d_q_off, d_q_src, d_out_off, d_out_ids, d_out_hop):

@@ -1,0 +1,113 @@
+// Host-side expansion of the bit rows of dmg_neighbors_batch_bits into CSR-shaped (id, hop) rows.
+// Pure host code (no CUDA): a consumer that wants arrays pays for writing ~5 bytes per neighbour here
+// instead of moving them over PCIe; a consumer that walks the neighbours can read the planes directly.
+#include <immintrin.h>
+
+#include <algorithm>
+#include <cstdint>
+#include <thread>
+#include <vector>
+
+#include "../../include/dmgraph.h"
+
+namespace dmg {
+void set_error(const char* fmt, ...);
+}
+
+namespace {
+
+// One row, scalar: every set bit of the member word becomes (id, code).
+void decode_row_scalar(uint32_t planes, uint32_t plane_words, uint32_t lo, uint32_t nw, const uint32_t* row,
+                       uint32_t* ids, uint8_t* hop) {
+  for (uint32_t j = 0; j < nw; ++j) {
+    uint32_t m = 0;
+    for (uint32_t p = 0; p < planes; ++p) m |= row[(size_t)p * plane_words + j];
+    while (m) {
+      const int i = __builtin_ctz(m);
+      m &= m - 1;
+      uint32_t code = 0;
+      for (uint32_t p = 0; p < planes; ++p) code |= ((row[(size_t)p * plane_words + j] >> i) & 1u) << p;
+      *ids++ = lo + 32 * j + (uint32_t)i;
+      *hop++ = (uint8_t)code;
+    }
+  }
+}
+
+// One row with AVX-512 compress stores: 32 vertices per step -- the member word is the mask of two
+// 16-lane id compresses and of one 32-byte code compress (codes = plane bits expanded to bytes).
+__attribute__((target("avx512f,avx512bw,avx512vl,avx512vbmi2"))) void decode_row_avx512(
+    uint32_t planes, uint32_t plane_words, uint32_t lo, uint32_t nw, const uint32_t* row, uint32_t* ids, uint8_t* hop) {
+  const __m512i iota = _mm512_setr_epi32(0, 1, 2, 3, 4, 5, 6, 7, 8, 9, 10, 11, 12, 13, 14, 15);
+  for (uint32_t j = 0; j < nw; ++j) {
+    uint32_t m = 0;
+    __m256i code = _mm256_setzero_si256();
+    for (uint32_t p = 0; p < planes; ++p) {
+      const uint32_t w = row[(size_t)p * plane_words + j];
+      m |= w;
+      code = _mm256_or_si256(code, _mm256_maskz_set1_epi8((__mmask32)w, (char)(1u << p)));
+    }
+    if (!m) continue;
+    const __m512i base = _mm512_add_epi32(iota, _mm512_set1_epi32((int)(lo + 32 * j)));
+    const __mmask16 m0 = (__mmask16)(m & 0xFFFFu), m1 = (__mmask16)(m >> 16);
+    _mm512_mask_compressstoreu_epi32(ids, m0, base);
+    ids += __builtin_popcount(m0);
+    _mm512_mask_compressstoreu_epi32(ids, m1, _mm512_add_epi32(base, _mm512_set1_epi32(16)));
+    ids += __builtin_popcount(m1);
+    _mm256_mask_compressstoreu_epi8(hop, (__mmask32)m, code);
+    hop += __builtin_popcount(m);
+  }
+}
+
+}  // namespace
+
+extern "C" int32_t dmg_bits_decode(uint32_t planes, uint32_t plane_words, uint64_t nq, const uint32_t* win,
+                                   const uint32_t* counts, const uint32_t* bits, uint64_t* out_off, uint32_t* out_ids,
+                                   uint8_t* out_hop, uint64_t cap, uint64_t* needed, int32_t n_threads) {
+  if (!out_off || !needed || (nq && (!win || !counts || !bits)) || planes < 1 || planes > 8) {
+    dmg::set_error("dmg_bits_decode: bad argument");
+    return DMG_EINVAL;
+  }
+  uint64_t total = 0;
+  for (uint64_t q = 0; q < nq; ++q) {
+    out_off[q] = total;
+    total += counts[q];
+  }
+  out_off[nq] = total;
+  *needed = total;
+  if (total > cap || (total && (!out_ids || !out_hop))) {
+    dmg::set_error("dmg_bits_decode: capacity %llu < needed %llu", (unsigned long long)cap, (unsigned long long)total);
+    return DMG_ECAP;
+  }
+  int T = n_threads > 0 ? n_threads : (int)std::thread::hardware_concurrency();
+  T = (int)std::max<uint64_t>(1, std::min<uint64_t>((uint64_t)std::max(T, 1), nq / 64 + 1));
+  const size_t row_words = (size_t)planes * plane_words;
+  static const bool simd = __builtin_cpu_supports("avx512f") && __builtin_cpu_supports("avx512bw") &&
+                           __builtin_cpu_supports("avx512vl") && __builtin_cpu_supports("avx512vbmi2");
+  auto work = [&](uint64_t a, uint64_t b) {
+    for (uint64_t q = a; q < b; ++q) {
+      if (!counts[q]) continue;
+      const uint32_t lo = win[2 * q], nw = (win[2 * q + 1] + 31) >> 5;
+      const uint32_t* row = bits + q * row_words;
+      uint32_t* ids = out_ids + out_off[q];
+      uint8_t* hop = out_hop + out_off[q];
+      if (simd) decode_row_avx512(planes, plane_words, lo, nw, row, ids, hop);
+      else decode_row_scalar(planes, plane_words, lo, nw, row, ids, hop);
+    }
+  };
+  if (T == 1) {
+    work(0, nq);
+  } else {
+    // split by output volume, not by query count
+    std::vector<std::thread> th;
+    uint64_t a = 0;
+    for (int t = 0; t < T; ++t) {
+      const uint64_t want = total / T * (t + 1);
+      uint64_t b = t == T - 1 ? nq : (uint64_t)(std::upper_bound(out_off, out_off + nq + 1, want) - out_off);
+      b = std::min(std::max(b, a), nq);
+      if (b > a) th.emplace_back(work, a, b);
+      a = b;
+    }
+    for (auto& x : th) x.join();
+  }
+  return DMG_OK;
+}

@@ -69,29 +69,49 @@ struct MbArgs {
 };
 
 // ---- grouping: queries -> (project, 64-slot group) ------------------------------------------------
+constexpr uint32_t MB_HIST = 2048;   // projects counted in shared memory first
 __global__ void __launch_bounds__(256) mb_classify_kernel(const MbArgs a) {
-  const unsigned long long q = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x;
-  if (q >= a.nq) return;
-  // The query's graph is the project of its first valid source (CCS:1426-1434, 1558).
-  uint32_t part = MB_NONE, lo = 0, hi = 0;
-  for (uint32_t i = a.q_off[q], e = a.q_off[q + 1]; i < e; ++i) {
-    const uint32_t s = a.q_src[i];
-    if (s < a.V) {
-      uint32_t l = 0, r = a.n_parts;
-      while (r - l > 1) {
-        const uint32_t m = (l + r) >> 1;
-        if (a.part_off[m] <= s) l = m; else r = m;
-      }
-      part = l;
-      lo = a.part_off[l];
-      hi = a.part_off[l + 1];
-      break;
-    }
+  // Arrival order inside a project: counted per block in shared memory (a few thousand queries hit
+  // each of config 2's 50 counters), then one global add per (block, project) fetches the block's base.
+  __shared__ uint32_t s_hist[MB_HIST];
+  const bool in_smem = a.n_parts <= MB_HIST;
+  if (in_smem) {
+    for (uint32_t p = threadIdx.x; p < a.n_parts; p += blockDim.x) s_hist[p] = 0;
+    __syncthreads();
   }
-  a.qpart[q] = part;
-  reinterpret_cast<uint2*>(a.qwin)[q] = make_uint2(lo, hi - lo);
-  if (part != MB_NONE) a.qrank[q] = atomicAdd(&a.part_hist[part], 1u);
-  else a.counts[q] = 0;   // no valid source: empty row, no group
+  const unsigned long long q = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x;
+  // The query's graph is the project of its first valid source (CCS:1426-1434, 1558).
+  uint32_t part = MB_NONE, lo = 0, hi = 0, local = 0;
+  if (q < a.nq) {
+    for (uint32_t i = a.q_off[q], e = a.q_off[q + 1]; i < e; ++i) {
+      const uint32_t s = a.q_src[i];
+      if (s < a.V) {
+        uint32_t l = 0, r = a.n_parts;
+        while (r - l > 1) {
+          const uint32_t m = (l + r) >> 1;
+          if (a.part_off[m] <= s) l = m; else r = m;
+        }
+        part = l;
+        lo = a.part_off[l];
+        hi = a.part_off[l + 1];
+        break;
+      }
+    }
+    a.qpart[q] = part;
+    reinterpret_cast<uint2*>(a.qwin)[q] = make_uint2(lo, hi - lo);
+    if (part == MB_NONE) a.counts[q] = 0;   // no valid source: empty row, no group
+    else local = atomicAdd(in_smem ? &s_hist[part] : &a.part_hist[part], 1u);
+  }
+  if (in_smem) {
+    __syncthreads();
+    for (uint32_t p = threadIdx.x; p < a.n_parts; p += blockDim.x) {
+      const uint32_t c = s_hist[p];
+      if (c) s_hist[p] = atomicAdd(&a.part_hist[p], c);
+    }
+    __syncthreads();
+    if (part != MB_NONE) local += s_hist[part];
+  }
+  if (part != MB_NONE) a.qrank[q] = local;
 }
 
 // One CTA: groups per project = ceil(queries / slots), scanned into part_gbase; every group learns its window.
@@ -146,7 +166,7 @@ template <> struct SetVec<1> { using type = uint2; };
 template <> struct SetVec<2> { using type = uint4; };
 
 template <int NP, int W64>
-__global__ void __launch_bounds__(MB_THREADS) khop_msbfs_kernel(const MbArgs a) {
+__global__ void __launch_bounds__(MB_THREADS, 2) khop_msbfs_kernel(const MbArgs a) {
   constexpr int THREADS = MB_THREADS, NW = THREADS / 32;
   constexpr int W32 = 2 * W64;          // 32-bit words per set word
   constexpr int SLOTS = 64 * W64;
@@ -286,48 +306,58 @@ __global__ void __launch_bounds__(MB_THREADS) khop_msbfs_kernel(const MbArgs a) 
       }
       if (!__syncthreads_or(any)) break;   // no query of the group found anything new
     }
-    // ---- bit rows: transposition by ballot.  Work item = (8 slots, 32 words of every plane). ----
+    // ---- bit rows: the sets are vertex-major (word v, bit = slot), a row is query-major (word j, bit =
+    // vertex 32 j + i).  A warp loads 32 consecutive vertex words (lane = vertex, one LDS per plane) and
+    // transposes each 32 x 32 bit block across its lanes in five shuffle stages, after which lane s holds
+    // word j of slot s; two consecutive j are kept so that every lane stores 8 bytes of its row. ----
     const uint32_t WB = a.WB;
-    const uint32_t n_jb = (WB + 31) / 32;
-    constexpr uint32_t N_OCT = SLOTS / 8;
-    for (uint32_t item = warp; item < N_OCT * n_jb; item += NW) {
-      const uint32_t oct = item % N_OCT, jb = item / N_OCT;
-      uint32_t w[NP][8];
-      uint32_t cnt[8];
+    // per-lane constants of the five butterfly stages (j = 16, 8, 4, 2, 1): rotate amount and keep-mask
+    uint32_t rot[5], keep[5];
 #pragma unroll
-      for (int s = 0; s < 8; ++s) {
-        cnt[s] = 0;
+    for (int st = 0; st < 5; ++st) {
+      const uint32_t j = 16u >> st;
+      const uint32_t m = st == 0 ? 0x0000FFFFu : st == 1 ? 0x00FF00FFu : st == 2 ? 0x0F0F0F0Fu : st == 3 ? 0x33333333u : 0x55555555u;
+      const bool upper = (lane & j) != 0;
+      rot[st] = upper ? 32u - j : j;   // partner's bits move up for the lower lane, down for the upper one
+      keep[st] = upper ? ~m : m;       // own bits that stay
+    }
+    for (uint32_t item = warp; item < WB / 2; item += NW) {   // WB is a multiple of 4 (win_cap of 128)
+      uint32_t r[2][W32][NP];
 #pragma unroll
-        for (int b = 0; b < NP; ++b) w[b][s] = 0;
+      for (int t = 0; t < 2; ++t) {
+        const uint32_t v = (item * 2 + t) * 32 + lane;
+#pragma unroll
+        for (int b = 0; b < NP; ++b) {
+          const Vec x = reinterpret_cast<const Vec*>(plane + (size_t)b * WS * W32)[v];
+          const uint32_t* xw = reinterpret_cast<const uint32_t*>(&x);
+#pragma unroll
+          for (int w = 0; w < W32; ++w) {
+            uint32_t y = xw[w];
+#pragma unroll
+            for (int st = 0; st < 5; ++st) {
+              const uint32_t o = __shfl_xor_sync(FULL, y, 16 >> st);
+              y = (y & keep[st]) | (__funnelshift_l(o, o, rot[st]) & ~keep[st]);
+            }
+            r[t][w][b] = y;
+          }
+        }
       }
-      const uint32_t jn = min(32u, WB - jb * 32);
-      for (uint32_t jj = 0; jj < jn; ++jj) {
-        const uint32_t v = (jb * 32 + jj) * 32 + lane;
-        uint32_t x[NP];
 #pragma unroll
-        for (int b = 0; b < NP; ++b)
-          x[b] = (plane[(size_t)b * WS * W32 + (size_t)v * W32 + (oct >> 2)] >> (8 * (oct & 3))) & 0xFFu;
+      for (int w = 0; w < W32; ++w) {
+        const uint32_t q = s_slot_q[32 * w + lane];
+        if (q == MB_NONE) continue;
+        uint32_t c = 0;
 #pragma unroll
-        for (int s = 0; s < 8; ++s) {
+        for (int t = 0; t < 2; ++t) {
           uint32_t un = 0;
 #pragma unroll
-          for (int b = 0; b < NP; ++b) {
-            const uint32_t bal = __ballot_sync(FULL, (x[b] >> s) & 1u);
-            un |= bal;
-            if (lane == (int)jj) w[b][s] = bal;
-          }
-          cnt[s] += __popc(un);
+          for (int b = 0; b < NP; ++b) un |= r[t][w][b];
+          c += __popc(un);
         }
-      }
 #pragma unroll
-      for (int s = 0; s < 8; ++s) {
-        const uint32_t q = s_slot_q[8 * oct + s];
-        if (q == MB_NONE) continue;
-        if (lane < (int)jn) {
-#pragma unroll
-          for (int b = 0; b < NP; ++b) a.bits[((size_t)q * NP + b) * WB + jb * 32 + lane] = w[b][s];
-        }
-        if (lane == 0 && cnt[s]) atomicAdd(&s_cnt[8 * oct + s], cnt[s]);
+        for (int b = 0; b < NP; ++b)
+          *reinterpret_cast<uint2*>(a.bits + ((size_t)q * NP + b) * WB + item * 2) = make_uint2(r[0][w][b], r[1][w][b]);
+        if (c) atomicAdd(&s_cnt[32 * w + lane], c);
       }
     }
     te = warp_sum_u64(te);
@@ -352,7 +382,33 @@ __global__ void __launch_bounds__(MB_THREADS) khop_msbfs_kernel(const MbArgs a) 
   }
 }
 
+// rows of queries that joined no group (no valid source) are all zero in the host-facing bit rows
+__global__ void __launch_bounds__(256) mb_zero_orphan_rows_kernel(const uint32_t* __restrict__ qpart, unsigned long long nq,
+                                                                  uint32_t* bits, uint32_t row_words) {
+  const int lane = threadIdx.x & 31;
+  const unsigned long long warp = (blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x) >> 5;
+  if (warp >= nq || qpart[warp] != MB_NONE) return;
+  for (uint32_t i = lane; i < row_words; i += 32) bits[(size_t)warp * row_words + i] = 0;
+}
+
+// 32 x 32 bit transpose across the lanes of a warp: lane i gives row i, receives column i.
+__device__ __forceinline__ uint32_t warp_transpose32(uint32_t y, int lane) {
+#pragma unroll
+  for (int st = 0; st < 5; ++st) {
+    const uint32_t j = 16u >> st;
+    const uint32_t m = st == 0 ? 0x0000FFFFu : st == 1 ? 0x00FF00FFu : st == 2 ? 0x0F0F0F0Fu : st == 3 ? 0x33333333u : 0x55555555u;
+    const bool upper = (lane & j) != 0;
+    const uint32_t o = __shfl_xor_sync(FULL, y, j);
+    const uint32_t keep = upper ? ~m : m;
+    y = (y & keep) | (__funnelshift_l(o, o, upper ? 32u - j : j) & ~keep);
+  }
+  return y;
+}
+
 // ---- bit rows -> packed (id, hop) rows in ascending id: one warp per query ---------------------------
+// A warp takes 32 words of every plane (1,024 vertices), transposes them across its lanes so that lane i
+// holds, bit by bit, the codes of vertices 32 jj + i, and then walks jj: one ballot ranks the members of
+// the 32 vertices of a step, and ids / hops go out as contiguous warp-wide stores.
 template <int NP>
 __global__ void __launch_bounds__(256, 8) khop_emit_bits_kernel(const uint32_t* __restrict__ bits, uint32_t WB,
                                                                  unsigned long long nq, const uint32_t* __restrict__ qwin,
@@ -365,32 +421,35 @@ __global__ void __launch_bounds__(256, 8) khop_emit_bits_kernel(const uint32_t* 
   const unsigned long long nwarps = ((unsigned long long)gridDim.x * blockDim.x) >> 5;
   const unsigned lt = lanemask_lt();
   for (unsigned long long q = warp; q < nq; q += nwarps) {
-    if (counts[q] == 0) continue;   // also: queries without a valid source have no bit row
+    const uint32_t cnt = counts[q];
+    if (cnt == 0) continue;   // also: queries without a valid source have no bit row
     const unsigned long long row = out_off[q];
     if (row >= cap) continue;
-    const uint32_t room = (uint32_t)min(cap - row, 0xFFFFFFFFull);
+    // entries of this row that fit (all of them unless the caller's capacity ends inside the row)
+    const uint32_t room = (uint32_t)min(cap - row, (unsigned long long)cnt);
     const uint32_t lo = qwin[2 * q], wn = qwin[2 * q + 1], nw = (wn + 31) >> 5;
     const uint32_t* __restrict__ br = bits + (size_t)q * NP * WB;
     uint32_t* __restrict__ ids = out_ids + row;
     uint8_t* __restrict__ hops = out_hop + row;
     uint32_t run = 0;
     for (uint32_t j0 = 0; j0 < nw; j0 += 32) {
-      uint32_t x[NP];
+      uint32_t t[NP];
 #pragma unroll
-      for (int b = 0; b < NP; ++b) x[b] = (j0 + lane < nw) ? br[(size_t)b * WB + j0 + lane] : 0u;
+      for (int b = 0; b < NP; ++b) t[b] = warp_transpose32((j0 + lane < nw) ? br[(size_t)b * WB + j0 + lane] : 0u, lane);
       const uint32_t jn = min(32u, nw - j0);
-      for (uint32_t jj = 0; jj < jn; ++jj) {
-        uint32_t m = 0, code = 0;
+      uint32_t id = lo + j0 * 32 + lane;
+#pragma unroll 4
+      for (uint32_t jj = 0; jj < jn; ++jj, id += 32) {
+        uint32_t code = 0;
 #pragma unroll
         for (int b = 0; b < NP; ++b) {
-          const uint32_t wd = __shfl_sync(FULL, x[b], jj);
-          m |= wd;
-          code |= ((wd >> lane) & 1u) << b;
+          code |= (t[b] & 1u) << b;
+          t[b] >>= 1;
         }
-        if (m == 0) continue;   // warp-uniform
+        const uint32_t m = __ballot_sync(FULL, code != 0);
         const uint32_t o = run + __popc(m & lt);
         if (code && o < room) {
-          ids[o] = lo + (j0 + jj) * 32 + lane;
+          ids[o] = id;
           hops[o] = (uint8_t)code;
         }
         run += __popc(m);

@@ -1375,6 +1375,87 @@ int32_t dmg_neighbors_batch_rows(dmg_graph* g, int32_t mode, int32_t k, int32_t 
   return DMG_OK;
 }
 
+// ---- dmg_neighbors_batch_bits: bit rows (binary-coded hop planes over the project's vertices) --------
+int32_t dmg_neighbors_batch_bits(dmg_graph* g, int32_t mode, int32_t k, int32_t exclude_sources, uint64_t nq,
+                                 const uint32_t* q_off, const uint32_t* q_src, uint32_t* out_planes,
+                                 uint32_t* out_plane_words, uint32_t* out_win, uint32_t* out_counts, uint32_t* out_bits,
+                                 uint64_t cap_bytes, uint64_t* needed_bytes) {
+  if (!out_planes || !out_plane_words || !needed_bytes) {
+    set_error("dmg_neighbors_batch_bits: NULL argument");
+    return DMG_EINVAL;
+  }
+  uint64_t dummy_off = 0;
+  DMG_TRY(check_khop_args(g, mode, k, nq, q_off, &dummy_off, needed_bytes));
+  const int w64 = bit_parallel_w64(g, k);
+  if (!w64) {
+    set_error("dmg_neighbors_batch_bits: bit rows need projects of <= %u vertices and k <= 7 (largest project %u, k = %d)",
+              MB_MAX_WINDOW, g->info.max_part_vertices, k);
+    return DMG_EINVAL;
+  }
+  const uint32_t maxp = std::max<uint32_t>(g->info.max_part_vertices, 1);
+  const uint32_t WB = ((maxp + 127u) & ~127u) / 32;
+  const int np = hop_planes(k);
+  const uint64_t row_bytes = (uint64_t)np * WB * 4;
+  *out_planes = (uint32_t)np;
+  *out_plane_words = WB;
+  *needed_bytes = nq * row_bytes;
+  if (nq == 0) return DMG_OK;
+  if (!out_win || !out_counts || !out_bits || cap_bytes < *needed_bytes) {
+    set_error("dmg_neighbors_batch_bits: capacity %llu < needed %llu bytes", (unsigned long long)cap_bytes,
+              (unsigned long long)*needed_bytes);
+    return DMG_ECAP;
+  }
+  const uint64_t n_src = q_off[nq];
+  if (n_src && !q_src) {
+    set_error("dmg_neighbors_batch_bits: q_src is NULL");
+    return DMG_EINVAL;
+  }
+  Engine* e = g->eng;
+  CtxGuard cg(e);
+  CallCtx* c = cg.c;
+  if (!c) return DMG_ECUDA;
+  DMG_TRY(c->begin());
+  DMG_TRY(c->q_off.reserve((nq + 1) * 4));
+  DMG_TRY(c->q_src.reserve(n_src * 4));
+  DMG_CUDA(cudaMemcpyAsync(c->q_off.p, q_off, (nq + 1) * 4, cudaMemcpyHostToDevice, c->stream));
+  if (n_src) DMG_CUDA(cudaMemcpyAsync(c->q_src.p, q_src, n_src * 4, cudaMemcpyHostToDevice, c->stream));
+  c->stats.h2d_bytes += (nq + 1) * 4 + n_src * 4;
+  const uint64_t budget = std::max<uint64_t>(std::min<uint64_t>(e->scratch_budget, 2ull << 30), row_bytes);
+  const uint64_t chunk = std::max<uint64_t>(1, std::min<uint64_t>(nq, budget / row_bytes));
+  const MbLayout L(chunk, g->info.n_parts, 64u * (uint32_t)w64);
+  DMG_TRY(c->scratch.reserve(chunk * row_bytes));
+  DMG_TRY(c->tmp0.reserve(nq * 4));
+  DMG_TRY(c->tmp1.reserve(nq * 8));
+  DMG_TRY(c->tmp2.reserve(L.bytes));
+  DMG_TRY(reset_counters(c));
+  for (uint64_t q0 = 0; q0 < nq; q0 += chunk) {
+    const uint64_t q1 = std::min<uint64_t>(nq, q0 + chunk);
+    if (q0) DMG_CUDA(cudaMemsetAsync(&c->d_counters->ticket, 0, 8, c->stream));
+    DMG_TRY(launch_bit_traversal(c, g, w64, mode, k, exclude_sources, q0, q1, c->q_off.as<uint32_t>(),
+                                 c->q_src.as<uint32_t>(), c->scratch.as<uint32_t>(), c->tmp0.as<uint32_t>(),
+                                 c->tmp1.as<uint32_t>(), c->tmp2.as<unsigned char>(), c->d_counters, c->stream));
+    {
+      LaunchScope ls(c, K_MISC);
+      mb_zero_orphan_rows_kernel<<<(unsigned)((q1 - q0 + 7) / 8), 256, 0, c->stream>>>(
+          c->tmp2.as<uint32_t>(), q1 - q0, c->scratch.as<uint32_t>(), (uint32_t)(row_bytes / 4));
+    }
+    DMG_CUDA(cudaGetLastError());
+    DMG_CUDA(cudaMemcpyAsync(reinterpret_cast<unsigned char*>(out_bits) + q0 * row_bytes, c->scratch.p, (q1 - q0) * row_bytes,
+                             cudaMemcpyDeviceToHost, c->stream));
+    if (q1 < nq) DMG_CUDA(cudaStreamSynchronize(c->stream));   // the rows are reused by the next chunk
+  }
+  DMG_CUDA(cudaMemcpyAsync(out_win, c->tmp1.p, nq * 8, cudaMemcpyDeviceToHost, c->stream));
+  DMG_CUDA(cudaMemcpyAsync(out_counts, c->tmp0.p, nq * 4, cudaMemcpyDeviceToHost, c->stream));
+  DMG_TRY(fetch_counters(c));
+  c->stats.d2h_bytes += nq * row_bytes + nq * 12 + sizeof(DevCounters);
+  DMG_TRY(c->finish());
+  c->stats.edges_traversed = c->h_counters->edges;
+  c->stats.edges_read = c->h_counters->aux[0];
+  c->stats.rows_expanded = c->h_counters->rows;
+  publish_stats(c->stats);
+  return DMG_OK;
+}
+
 // ---- dmg_neighbors_batch_dev_static: the k-hop batch without a single allocation ---------------
 // Scratch for the small-project kernel chain (counters, scan status words, row sizes, per-query
 // window, staging rows) lives in this file-scope device array instead of cudaMalloc'ed buffers.

@@ -89,6 +89,9 @@ def lib():
             "dmg_neighbors_batch_dev": (i32, [vp, i32, i32, i32, u64, vp, vp, vp, vp, vp, u64, pu64]),
             "dmg_neighbors_batch_rows": (i32, [vp, i32, i32, i32, u64, vp, vp, C.POINTER(u32), vp, vp, u64, pu64]),
             "dmg_neighbors_batch_dev_static": (i32, [vp, i32, i32, i32, u64, vp, vp, vp, vp, vp, u64, pu64]),
+            "dmg_neighbors_batch_bits": (i32, [vp, i32, i32, i32, u64, vp, vp, C.POINTER(u32), C.POINTER(u32), vp, vp,
+                                                vp, u64, pu64]),
+            "dmg_bits_decode": (i32, [u32, u32, u64, vp, vp, vp, vp, vp, vp, u64, pu64, i32]),
             "dmg_closure": (i32, [vp, i32, u32, vp, vp, pu64]),
             "dmg_analysis_order": (i32, [vp, vp]),
             "dmg_closure_push_dev": (i32, [vp, i32, u32, u32, vp, vp, pu64]),
@@ -123,6 +126,24 @@ def lib():
             f.argtypes = args
         _lib = L
     return _lib
+
+
+def bits_decode(planes, plane_words, win, counts, bits, out=None, threads=0):
+    """dmg_bits_decode: bit rows -> (off u64[nq+1], ids u32[], hop u8[]) on the host."""
+    nq = counts.size
+    win = np.ascontiguousarray(win, np.uint32)
+    counts = np.ascontiguousarray(counts, np.uint32)
+    bits = np.ascontiguousarray(bits, np.uint32)
+    need = C.c_uint64(0)
+    if out is None:
+        total = int(counts.sum(dtype=np.uint64))
+        off = np.zeros(nq + 1, np.uint64)
+        ids, hop = np.zeros(max(total, 1), np.uint32), np.zeros(max(total, 1), np.uint8)
+    else:
+        off, ids, hop = out
+    _check(lib().dmg_bits_decode(planes, plane_words, nq, win.ctypes.data, counts.ctypes.data, bits.ctypes.data,
+                                 off.ctypes.data, ids.ctypes.data, hop.ctypes.data, ids.size, C.byref(need), threads))
+    return off, ids[:need.value], hop[:need.value]
 
 
 def device_count():
@@ -340,6 +361,27 @@ class Graph:
                                                C.byref(stride), win.ctypes.data, rows.ctypes.data, rows.size,
                                                C.byref(need)))
         return stride.value, win[:nq], rows[:need.value].reshape(nq, stride.value) if nq else rows[:0]
+
+    def neighbors_batch_bits(self, mode, k, exclude_sources, q_off, q_src, out=None):
+        """Bit rows: returns (planes, plane_words, win[nq,2], counts[nq], bits[nq, planes, plane_words])."""
+        q_off, q_src = _arr(q_off, np.uint32), _arr(q_src, np.uint32)
+        nq = q_off.size - 1
+        planes, words, need = C.c_uint32(0), C.c_uint32(0), C.c_uint64(0)
+        rc = self.L.dmg_neighbors_batch_bits(self.h, mode, k, int(exclude_sources), nq, _ptr(q_off), _ptr(q_src),
+                                             C.byref(planes), C.byref(words), None, None, None, 0, C.byref(need))
+        _check(rc, allow=(ECAP,))
+        if out is None:
+            win = np.zeros((max(nq, 1), 2), np.uint32)
+            counts = np.zeros(max(nq, 1), np.uint32)
+            bits = np.zeros(max(need.value // 4, 1), np.uint32)
+        else:
+            win, counts, bits = out
+        _check(self.L.dmg_neighbors_batch_bits(self.h, mode, k, int(exclude_sources), nq, _ptr(q_off), _ptr(q_src),
+                                               C.byref(planes), C.byref(words), win.ctypes.data, counts.ctypes.data,
+                                               bits.ctypes.data, bits.size * 4, C.byref(need)))
+        n_words = need.value // 4
+        return (planes.value, words.value, win[:nq], counts[:nq],
+                bits[:n_words].reshape(nq, planes.value, words.value) if nq else bits[:0])
 
     def neighbors_batch_dev_static(self, mode, k, exclude_sources, nq, d_q_off, d_q_src, d_out_off, d_out_ids,
                                    d_out_hop, cap):

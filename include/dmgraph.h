@@ -189,6 +189,27 @@ int32_t dmg_neighbors_batch_rows(dmg_graph* g, int32_t mode, int32_t k, int32_t 
                                  uint32_t* out_row_stride, uint32_t* out_win, uint8_t* out_rows,
                                  uint64_t cap_bytes, uint64_t* needed_bytes);
 
+/* Compact form of the same result -- what a host should use when it walks the neighbours instead of
+ * copying them (resolveNeighbors feeds every neighbour to a repository lookup, CCS:1583-1610): row q is
+ * *out_planes bit planes of *out_plane_words uint32 words over the vertices of the query's project
+ * (out_win[2q] = first vertex lo_q, out_win[2q+1] = vertex count); bit (v - lo_q) of plane b -- word
+ * (v - lo_q) >> 5, bit (v - lo_q) & 31 -- is bit b of hop(v), so hop(v) = sum_b plane_b[v] << b and
+ * 0 means "not a neighbour" (excluded sources included).  k <= 3 needs two planes: 512 bytes per query on
+ * 2,000-vertex projects against ~10 KB of (id, hop) pairs -- 20x fewer PCIe bytes on BASELINE config 2.
+ * out_counts[q] = number of neighbours of row q.  Needs projects of <= 4096 vertices and k <= 7
+ * (DMG_EINVAL otherwise).  cap_bytes / needed_bytes count bytes of out_bits.  dmg_bits_decode turns such
+ * rows into the packed rows of dmg_neighbors_batch on the host.                                      */
+int32_t dmg_neighbors_batch_bits(dmg_graph* g, int32_t mode, int32_t k, int32_t exclude_sources,
+                                 uint64_t n_queries, const uint32_t* q_off, const uint32_t* q_src,
+                                 uint32_t* out_planes, uint32_t* out_plane_words, uint32_t* out_win,
+                                 uint32_t* out_counts, uint32_t* out_bits, uint64_t cap_bytes,
+                                 uint64_t* needed_bytes);
+/* Host-side expansion of bit rows into CSR-shaped (id, hop) rows, ascending id (no device work; uses
+ * n_threads host threads, 0 = all).  out_off has n_queries + 1 entries; cap counts entries.          */
+int32_t dmg_bits_decode(uint32_t planes, uint32_t plane_words, uint64_t n_queries, const uint32_t* win,
+                        const uint32_t* counts, const uint32_t* bits, uint64_t* out_off, uint32_t* out_ids,
+                        uint8_t* out_hop, uint64_t cap, uint64_t* needed, int32_t n_threads);
+
 /* The same k-hop batch for callers that must not allocate.  It has no counterpart in the
  * reference.  Some hosts cannot afford, or are not allowed, a cudaMalloc on the query path: a
  * request thread with a latency budget (device allocation can stall behind all other work on the

@@ -143,3 +143,42 @@ def test_adjacency_tile_sum_above_u32(engine):
     assert need.value == 300 * (n - 1)
     assert np.array_equal(off, np.arange(301, dtype=np.uint64) * np.uint64(n - 1))
     g.release()
+
+
+# ---- bit rows (dmg_neighbors_batch_bits + dmg_bits_decode) -----------------------------------------
+@pytest.mark.parametrize("n_parts", [1, 5])
+def test_bit_rows_decode_to_the_packed_rows(engine, n_parts):
+    """The compact host-facing format carries exactly the sets and hops of dmg_neighbors_batch: decoded
+    on the host it must equal the oracle's rows, incl. queries with no valid source, sources of another
+    project, repeated sources, every mode, k up to 7 (three planes) and both exclude settings."""
+    rng = np.random.default_rng(40 + n_parts)
+    for trial in range(4):
+        n = int(rng.integers(40, 3000))
+        e = int(rng.integers(n, 10 * n))
+        cuts = np.sort(rng.choice(np.arange(1, n), size=n_parts - 1, replace=False)) if n_parts > 1 else []
+        part_off = np.concatenate([[0], cuts, [n]]).astype(np.uint32)
+        part_of = np.searchsorted(part_off, np.arange(n), side="right") - 1
+        src = rng.integers(0, n, e)
+        lo, hi = part_off[part_of[src]], part_off[part_of[src] + 1]
+        dst = lo + (rng.random(e) * (hi - lo)).astype(np.int64)
+        g = dmgraph.Graph(engine, n, src, dst, [], part_off=part_off)
+        o = ora.CsrOracle(n, src.astype(np.uint32), dst.astype(np.uint32), [], part_off)
+        nq = 700
+        cnt = rng.integers(0, 7, nq)
+        q_off = np.zeros(nq + 1, np.uint32)
+        np.cumsum(cnt, out=q_off[1:])
+        q_src = rng.integers(0, n + 3, int(q_off[-1])).astype(np.uint32)
+        for mode, k, excl in [(2, 2, 1), (2, 1, 1), (0, 3, 0), (1, 2, 1), (2, 5, 0), (0, 7, 1), (1, 1, 0)]:
+            planes, words, win, counts, bits = g.neighbors_batch_bits(mode, k, excl, q_off, q_src)
+            assert planes == (1 if k == 1 else 2 if k <= 3 else 3) and words * 32 >= g.info["max_part_vertices"]
+            off, ids, hop = dmgraph.bits_decode(planes, words, win, counts, bits)
+            woff, wids, whop, wte = o.khop_batch(mode, k, excl, q_off, q_src, threads=4)
+            assert np.array_equal(off, woff) and np.array_equal(ids, wids) and np.array_equal(hop, whop)
+            assert engine.last_stats()["edges_traversed"] == wte
+            empty = np.flatnonzero(counts == 0)
+            assert not bits[empty].any()                     # rows without neighbours are all zero
+        g.release()
+    with pytest.raises(dmgraph.DmgError) as ei:              # k beyond three planes: not this format
+        g2 = dmgraph.Graph(engine, 10, [0], [1], [])
+        g2.neighbors_batch_bits(2, 8, 1, np.array([0, 1], np.uint32), np.array([0], np.uint32))
+    assert ei.value.code == dmgraph.EINVAL
