@@ -1,6 +1,7 @@
 // Engine, call contexts, graph upload (GraphService lifecycle, GS:34-122) and small utilities.
 #include <algorithm>
 #include <new>
+#include <thread>
 
 #include "common.cuh"
 
@@ -181,88 +182,130 @@ static int32_t upload(T** d, const T* h, size_t n, uint64_t* bytes) {
 // index of an all-zero word the kernel keeps behind each set.  fwd_ptr gives the FORWARD degree of
 // the row's vertex for the TE count (the pull reads reverse rows).
 constexpr uint32_t ELL_ROW_CAP = 256;
+namespace {
+struct EllPart {   // one project's slices
+  std::vector<uint32_t> slice_len;   // steps (multiple of 4) of each slice
+  std::vector<uint32_t> vrow;
+  std::vector<uint16_t> data;
+};
+struct EllVR { uint32_t len, v, start; };
+
+void build_ell_project(EllPart& out, const std::vector<uint32_t>& ptr, const std::vector<uint32_t>& idx,
+                       const std::vector<uint32_t>& fwd_ptr, uint32_t lo, uint32_t hi, uint32_t pad_id) {
+  std::vector<EllVR> vr;
+  for (uint32_t v = lo; v < hi; ++v)
+    for (uint32_t b = ptr[v]; b < ptr[v + 1]; b += ELL_ROW_CAP) vr.push_back({std::min(ELL_ROW_CAP, ptr[v + 1] - b), v, b});
+  std::stable_sort(vr.begin(), vr.end(), [](const EllVR& a, const EllVR& b) { return a.len > b.len; });
+  while (vr.size() % 32) vr.push_back({0u, 0xFFFFFFFFu, 0u});
+  std::vector<uint16_t> bucket[8][8];   // [lane of the quarter][id % 8], reused
+  for (size_t s0 = 0; s0 < vr.size(); s0 += 32) {
+    const uint32_t L = (vr[s0].len + 3u) & ~3u;   // longest row of the slice, padded to whole uint2 steps
+    const size_t base = out.data.size();
+    out.data.resize(base + (size_t)L * 32, (uint16_t)pad_id);
+    out.slice_len.push_back(L);
+    for (uint32_t l = 0; l < 32; ++l) {
+      const EllVR& r = vr[s0 + l];
+      if (r.v == 0xFFFFFFFFu) {
+        out.vrow.push_back(0xFFFFu);
+        continue;
+      }
+      const uint32_t deg = std::min<uint32_t>(fwd_ptr[r.v + 1] - fwd_ptr[r.v], 0xFFFFu);
+      out.vrow.push_back((deg << 16) | (r.v - lo));
+    }
+    // Order inside a row is free (the kernel ORs), so it is chosen against shared-memory bank
+    // conflicts: a 16-byte set word of vertex id sits in bank group id % 8, and the eight lanes of a
+    // quarter warp are served together -- at every step each quarter gets eight ids of different
+    // groups while the rows still offer them.  Padding reads one of the eight zero words behind the
+    // set, again of an unused group.  (ncu, config 2: 23.7 M conflict cycles per launch before, 11.5 M after.)
+    for (uint32_t q8 = 0; q8 < 32; q8 += 8) {
+      for (uint32_t l = 0; l < 8; ++l) {
+        for (int b = 0; b < 8; ++b) bucket[l][b].clear();
+        const EllVR& r = vr[s0 + q8 + l];
+        if (r.v == 0xFFFFFFFFu) continue;
+        for (uint32_t j = 0; j < r.len; ++j) {
+          const uint16_t id = (uint16_t)(idx[r.start + j] - lo);
+          bucket[l][id & 7].push_back(id);
+        }
+      }
+      for (uint32_t j = 0; j < L; ++j) {
+        uint32_t used = 0;
+        int choice[8], order[8], nopt[8];
+        for (int l = 0; l < 8; ++l) {   // lanes with the fewest groups left choose first
+          order[l] = l;
+          nopt[l] = 0;
+          for (int b = 0; b < 8; ++b) nopt[l] += !bucket[l][b].empty();
+        }
+        std::sort(order, order + 8, [&](int x, int y) { return nopt[x] < nopt[y]; });
+        for (int oi = 0; oi < 8; ++oi) {
+          const int l = order[oi];
+          int best = -1, best_any = -1;
+          for (int b = 0; b < 8; ++b) {
+            if (bucket[l][b].empty()) continue;
+            if (best_any < 0 || bucket[l][b].size() > bucket[l][best_any].size()) best_any = b;
+            if (!(used & (1u << b)) && (best < 0 || bucket[l][b].size() > bucket[l][best].size())) best = b;
+          }
+          choice[l] = best >= 0 ? best : best_any;
+          if (choice[l] >= 0) used |= 1u << choice[l];
+        }
+        for (int l = 0; l < 8; ++l) {
+          uint16_t id;
+          if (choice[l] >= 0) {
+            id = bucket[l][choice[l]].back();
+            bucket[l][choice[l]].pop_back();
+          } else {
+            int b = 0;
+            while (b < 7 && (used & (1u << b))) ++b;
+            id = (uint16_t)(pad_id + b);   // words pad_id .. pad_id + 7 of every set are zero
+          }
+          out.data[base + ((size_t)(j >> 2) * 32 + q8 + l) * 4 + (j & 3)] = id;
+        }
+      }
+    }
+  }
+}
+}  // namespace
+
 static int32_t build_ell(dmg_graph::Ell* out, const std::vector<uint32_t>& ptr, const std::vector<uint32_t>& idx,
                          const std::vector<uint32_t>& fwd_ptr, const std::vector<uint32_t>& part, uint32_t pad_id,
                          uint64_t* bytes) {
   const size_t P = part.size() - 1;
+  std::vector<EllPart> parts(P);
+  {   // projects are independent: built on the host's threads, stitched in project order
+    const unsigned T = (unsigned)std::max<size_t>(1, std::min<size_t>(std::thread::hardware_concurrency(), P));
+    std::atomic<size_t> next{0};
+    std::atomic<bool> failed{false};
+    auto work = [&] {
+      try {
+        for (size_t p; (p = next.fetch_add(1)) < P;) build_ell_project(parts[p], ptr, idx, fwd_ptr, part[p], part[p + 1], pad_id);
+      } catch (const std::exception&) {
+        failed = true;
+      }
+    };
+    std::vector<std::thread> th;
+    for (unsigned t = 1; t < T; ++t) th.emplace_back(work);
+    work();
+    for (auto& x : th) x.join();
+    if (failed) {
+      set_error("graph upload: host out of memory");
+      return DMG_ENOMEM;
+    }
+  }
   std::vector<uint32_t> proj_slice(P + 1, 0), slice_off(1, 0), vrow;
   std::vector<uint16_t> data;
-  struct VR { uint32_t len, v, start; };
-  std::vector<VR> vr;
+  size_t n_data = 0, n_vrow = 0;
+  for (auto& ep : parts) {
+    n_data += ep.data.size();
+    n_vrow += ep.vrow.size();
+  }
+  data.reserve(std::max<size_t>(n_data, 4));
+  vrow.reserve(n_vrow);
   for (size_t p = 0; p < P; ++p) {
-    const uint32_t lo = part[p], hi = part[p + 1];
-    vr.clear();
-    for (uint32_t v = lo; v < hi; ++v)
-      for (uint32_t b = ptr[v]; b < ptr[v + 1]; b += ELL_ROW_CAP) vr.push_back({std::min(ELL_ROW_CAP, ptr[v + 1] - b), v, b});
-    std::stable_sort(vr.begin(), vr.end(), [](const VR& a, const VR& b) { return a.len > b.len; });
-    while (vr.size() % 32) vr.push_back({0u, 0xFFFFFFFFu, 0u});
-    for (size_t s0 = 0; s0 < vr.size(); s0 += 32) {
-      const uint32_t L = (vr[s0].len + 3u) & ~3u;   // longest row of the slice, padded to whole uint2 steps
-      const size_t base = data.size();
-      data.resize(base + (size_t)L * 32, (uint16_t)pad_id);
-      for (uint32_t l = 0; l < 32; ++l) {
-        const VR& r = vr[s0 + l];
-        if (r.v == 0xFFFFFFFFu) {
-          vrow.push_back(0xFFFFu);
-          continue;
-        }
-        const uint32_t deg = std::min<uint32_t>(fwd_ptr[r.v + 1] - fwd_ptr[r.v], 0xFFFFu);
-        vrow.push_back((deg << 16) | (r.v - lo));
-      }
-      // Order inside a row is free (the kernel ORs), so it is chosen against shared-memory bank
-      // conflicts: a 16-byte set word of vertex id sits in bank group id % 8, and the eight lanes of a
-      // quarter warp are served together -- at every step each quarter gets eight ids of different
-      // groups while the rows still offer them.  Padding reads one of the eight zero words behind the
-      // set, again of an unused group.  (ncu, config 2: 23.7 M conflict cycles per launch before.)
-      for (uint32_t q8 = 0; q8 < 32; q8 += 8) {
-        std::vector<uint16_t> bucket[8][8];   // [lane of the quarter][id % 8]
-        for (uint32_t l = 0; l < 8; ++l) {
-          const VR& r = vr[s0 + q8 + l];
-          if (r.v == 0xFFFFFFFFu) continue;
-          for (uint32_t j = 0; j < r.len; ++j) {
-            const uint16_t id = (uint16_t)(idx[r.start + j] - lo);
-            bucket[l][id & 7].push_back(id);
-          }
-        }
-        for (uint32_t j = 0; j < L; ++j) {
-          uint32_t used = 0;
-          int choice[8];
-          // lanes with the fewest groups left choose first
-          int order[8], nopt[8];
-          for (int l = 0; l < 8; ++l) {
-            order[l] = l;
-            nopt[l] = 0;
-            for (int b = 0; b < 8; ++b) nopt[l] += !bucket[l][b].empty();
-          }
-          std::sort(order, order + 8, [&](int x, int y) { return nopt[x] < nopt[y]; });
-          for (int oi = 0; oi < 8; ++oi) {
-            const int l = order[oi];
-            int best = -1, best_any = -1;
-            for (int b = 0; b < 8; ++b) {
-              if (bucket[l][b].empty()) continue;
-              if (best_any < 0 || bucket[l][b].size() > bucket[l][best_any].size()) best_any = b;
-              if (!(used & (1u << b)) && (best < 0 || bucket[l][b].size() > bucket[l][best].size())) best = b;
-            }
-            choice[l] = best >= 0 ? best : best_any;
-            if (choice[l] >= 0) used |= 1u << choice[l];
-          }
-          for (int l = 0; l < 8; ++l) {
-            uint16_t id;
-            if (choice[l] >= 0) {
-              id = bucket[l][choice[l]].back();
-              bucket[l][choice[l]].pop_back();
-            } else {
-              int b = 0;
-              while (b < 7 && (used & (1u << b))) ++b;
-              id = (uint16_t)(pad_id + b);   // words pad_id .. pad_id + 7 of every set are zero
-            }
-            data[base + ((size_t)(j >> 2) * 32 + q8 + l) * 4 + (j & 3)] = id;
-          }
-        }
-      }
-      slice_off.push_back((uint32_t)(data.size() / 4));
-    }
+    EllPart& ep = parts[p];
+    for (uint32_t L : ep.slice_len) slice_off.push_back(slice_off.back() + L * 32 / 4);   // uint2 units
+    vrow.insert(vrow.end(), ep.vrow.begin(), ep.vrow.end());
+    data.insert(data.end(), ep.data.begin(), ep.data.end());
     proj_slice[p + 1] = (uint32_t)(slice_off.size() - 1);
+    EllPart().data.swap(ep.data);
   }
   if (data.empty()) data.resize(4, (uint16_t)pad_id);
   out->entries = data.size();

@@ -447,12 +447,21 @@ __global__ void __launch_bounds__(256, 8) khop_emit_bits_kernel(const uint32_t* 
           t[b] >>= 1;
         }
         const uint32_t m = __ballot_sync(FULL, code != 0);
-        const uint32_t o = run + __popc(m & lt);
-        if (code && o < room) {
-          ids[o] = id;
-          hops[o] = (uint8_t)code;
+        if (m == FULL) {   // all 32 vertices are members (the common word when the hops cover the project):
+          const uint32_t o = run + lane;   // no rank to compute -- POPC issues at a quarter of the ALU rate
+          if (o < room) {
+            ids[o] = id;
+            hops[o] = (uint8_t)code;
+          }
+          run += 32;
+        } else if (m) {
+          const uint32_t o = run + __popc(m & lt);
+          if (code && o < room) {
+            ids[o] = id;
+            hops[o] = (uint8_t)code;
+          }
+          run += __popc(m);
         }
-        run += __popc(m);
       }
     }
   }
