@@ -86,39 +86,52 @@ struct SearchArgs {
 // and a 32-bit fingerprint; the filter index and the slot index are cheap functions of the fingerprint.
 struct KeyFp {
   unsigned long long key;
-  uint32_t fp;
+  uint32_t fp;    // compared in the slot table
+  uint32_t raw;   // what the filters are indexed by
 };
+// The per-position cost is what bounds the scan (ncu, config 3: ~185 thread instructions per byte
+// position before, most of them the five classes' hashes), so the classes share one incremental
+// hash: raw(4 bytes) = lo * A, raw(8) = raw(4) ^ hi * B, raw(12) = raw(8) ^ lo2 * C, raw(16) = raw(12) ^
+// hi2 * D -- one multiply per class -- and the first filter bit is simply raw's top bits.  Key and
+// fingerprint are only formed for the few positions that pass a filter.
+constexpr uint32_t HASH_A = 0x9E3779B1u, HASH_B = 0x85EBCA77u, HASH_C = 0xC2B2AE3Du, HASH_D = 0x27D4EB2Fu;
+__host__ __device__ __forceinline__ uint32_t class_raw(int cls, uint32_t lo, uint32_t hi, uint32_t lo2, uint32_t hi2) {
+  switch (cls) {
+    case 0: return (lo * HASH_A) ^ (hi * HASH_B) ^ (lo2 * HASH_C) ^ (hi2 * HASH_D);   // >= 16 bytes: first 16
+    case 1: return (lo * HASH_A) ^ (hi * HASH_B) ^ (lo2 * HASH_C);                    // 12..15: first 12
+    case 2: return (lo * HASH_A) ^ (hi * HASH_B);                                     // 8..11: first 8
+    case 3: return lo * HASH_A;                                                       // 4..7: first 4
+    default: return (lo & 0xFFFFFFu) * HASH_A;                                        // exactly 3
+  }
+}
 __host__ __device__ __forceinline__ KeyFp class_key(int cls, uint32_t lo, uint32_t hi, uint32_t lo2, uint32_t hi2) {
   KeyFp r;
   switch (cls) {
-    case 0:   // >= 16 bytes: first 16
-      r.key = ((unsigned long long)(hi ^ (lo2 * 0x85EBCA6Bu)) << 32) | (lo ^ (hi2 * 0xC2B2AE35u));
-      r.fp = (lo * 0x9E3779B1u) ^ (hi * 0x85EBCA77u) ^ (lo2 * 0xC2B2AE3Du) ^ (hi2 * 0x27D4EB2Fu);
-      break;
-    case 1:   // 12..15 bytes: first 12
-      r.key = ((unsigned long long)(hi ^ (lo2 * 0x85EBCA6Bu)) << 32) | lo;
-      r.fp = (lo * 0x9E3779B1u) ^ (hi * 0x85EBCA77u) ^ (lo2 * 0xC2B2AE3Du);
-      break;
-    case 2:   // 8..11 bytes: first 8
-      r.key = ((unsigned long long)hi << 32) | lo;
-      r.fp = (lo * 0x9E3779B1u) ^ (hi * 0x85EBCA77u);
-      break;
-    case 3:   // 4..7 bytes: first 4
-      r.key = lo;
-      r.fp = lo * 0x9E3779B1u;
-      break;
-    default:  // exactly 3 bytes
-      r.key = lo & 0xFFFFFFu;
-      r.fp = (lo & 0xFFFFFFu) * 0x9E3779B1u;
+    case 0: r.key = ((unsigned long long)(hi ^ (lo2 * 0x85EBCA6Bu)) << 32) | (lo ^ (hi2 * 0xC2B2AE35u)); break;
+    case 1: r.key = ((unsigned long long)(hi ^ (lo2 * 0x85EBCA6Bu)) << 32) | lo; break;
+    case 2: r.key = ((unsigned long long)hi << 32) | lo; break;
+    case 3: r.key = lo; break;
+    default: r.key = lo & 0xFFFFFFu;
   }
-  r.fp ^= r.fp >> 15;
+  r.raw = class_raw(cls, lo, hi, lo2, hi2);
+  r.fp = r.raw ^ (r.raw >> 15);
   return r;
 }
 __host__ __device__ __forceinline__ uint32_t hash_slot(uint32_t fp, uint32_t mask) {
   return ((fp * 0x2C1B3C6Du) >> 9) & mask;
 }
-__host__ __device__ __forceinline__ uint32_t hash_filter(uint32_t fp, uint32_t bits) {
-  return (fp * 0x297A2D39u) >> (32 - bits);
+__host__ __device__ __forceinline__ uint32_t hash_filter(uint32_t raw, uint32_t bits) { return raw >> (32 - bits); }
+// second, independent bit of the same filter: tested only when the first is set, so it costs nothing on
+// the 9 positions in 10 the first bit rejects, and squares the false-positive rate (ncu, config 3: a false
+// candidate pays a dependent 16-byte table load; at 10 filter bits per key that was ~18 per name)
+__host__ __device__ __forceinline__ uint32_t hash_filter2(uint32_t raw, uint32_t bits) {
+  return ((raw ^ (raw >> 13)) * 0x7FEB352Du) >> (32 - bits);
+}
+__device__ __forceinline__ bool filter_pass(const uint32_t* f, uint32_t raw, uint32_t bits) {
+  const uint32_t fi = hash_filter(raw, bits);
+  if (!((f[fi >> 5] >> (fi & 31)) & 1u)) return false;
+  const uint32_t fj = hash_filter2(raw, bits);
+  return (f[fj >> 5] >> (fj & 31)) & 1u;
 }
 __device__ __forceinline__ uint32_t table_find(const SlotTable& t, unsigned long long k, uint32_t fp) {
   uint32_t h = hash_slot(fp, t.mask);
@@ -148,10 +161,15 @@ __device__ __forceinline__ uint32_t match_name(const SearchArgs& a, const uint32
                                                const uint32_t* f8, const uint32_t* f4, const uint32_t* f3,
                                                uint32_t i, uint32_t n1, uint16_t* mine) {
     uint32_t nh = 0;
-    // a pattern may occur at several positions of the name: keep it once
+    // a pattern may occur at several positions of the name: keep it once.  64 bits in registers say
+    // "certainly not seen yet" for most hits; only a set bit sends the lane through its list.
+    unsigned long long seen = 0;
     auto add = [&](uint32_t u) {
-      for (uint32_t t = 0; t < nh && t < SM_HITBUF; ++t)
-        if (mine[t] == (uint16_t)u) return;
+      const unsigned long long bit = 1ull << ((u * 0x9E3779B1u) >> 26);
+      if (seen & bit)
+        for (uint32_t t = 0; t < nh && t < SM_HITBUF; ++t)
+          if (mine[t] == (uint16_t)u) return;
+      seen |= bit;
       if (nh < SM_HITBUF) mine[nh] = (uint16_t)u;
       ++nh;
     };
@@ -181,29 +199,27 @@ __device__ __forceinline__ uint32_t match_name(const SearchArgs& a, const uint32
           u = pi.next;
         }
       };
+      const bool any_long = (a.t16.present | a.t12.present) != 0, any8 = any_long || a.t8.present;
       for (uint32_t p = 0; p < len; ++p) {
         const uint32_t r = len - p;
         const uint32_t lo32 = sh ? __funnelshift_r(w0, w1, sh) : w0;
         const uint32_t hi32 = sh ? __funnelshift_r(w1, w2, sh) : w1;
         const unsigned long long k8 = ((unsigned long long)hi32 << 32) | lo32;
-        if ((a.t16.present | a.t12.present) && r >= 12) {
-          const uint32_t lo2 = sh ? __funnelshift_r(w2, w3, sh) : w2;
-          const uint32_t hi2 = sh ? __funnelshift_r(w3, w4, sh) : w3;
-          if (a.t16.present && r >= 16) {
-            const KeyFp kf = class_key(0, lo32, hi32, lo2, hi2);
-            const uint32_t fi = hash_filter(kf.fp, a.t16.fbits);
-            if ((f16[fi >> 5] >> (fi & 31)) & 1u) long_class(a.t16, kf, k8, r, p);
+        const uint32_t h4 = lo32 * HASH_A;
+        if (any8 && r >= 8) {
+          const uint32_t h8 = h4 ^ (hi32 * HASH_B);
+          if (any_long && r >= 12) {
+            const uint32_t lo2 = sh ? __funnelshift_r(w2, w3, sh) : w2;
+            const uint32_t h12 = h8 ^ (lo2 * HASH_C);
+            if (a.t16.present && r >= 16) {
+              const uint32_t hi2 = sh ? __funnelshift_r(w3, w4, sh) : w3;
+              if (filter_pass(f16, h12 ^ (hi2 * HASH_D), a.t16.fbits))
+                long_class(a.t16, class_key(0, lo32, hi32, lo2, hi2), k8, r, p);
+            }
+            if (a.t12.present && filter_pass(f12, h12, a.t12.fbits)) long_class(a.t12, class_key(1, lo32, hi32, lo2, 0u), k8, r, p);
           }
-          if (a.t12.present) {
-            const KeyFp kf = class_key(1, lo32, hi32, lo2, 0u);
-            const uint32_t fi = hash_filter(kf.fp, a.t12.fbits);
-            if ((f12[fi >> 5] >> (fi & 31)) & 1u) long_class(a.t12, kf, k8, r, p);
-          }
-        }
-        if (a.t8.present && r >= 8) {
-          const KeyFp kf = class_key(2, lo32, hi32, 0u, 0u);
-          const uint32_t fi = hash_filter(kf.fp, a.t8.fbits);
-          if ((f8[fi >> 5] >> (fi & 31)) & 1u) {
+          if (a.t8.present && filter_pass(f8, h8, a.t8.fbits)) {
+            const KeyFp kf = class_key(2, lo32, hi32, 0u, 0u);
             for (uint32_t u = table_find(a.t8, kf.key, kf.fp); u != PAT_NIL;) {
               const PatInfo pi = load_pat(a.pat, u);
               if (pi.len <= r) {
@@ -219,21 +235,18 @@ __device__ __forceinline__ uint32_t match_name(const SearchArgs& a, const uint32
             }
           }
         }
-        if (a.t4.present && r >= 4) {
+        if (a.t4.present && r >= 4 && filter_pass(f4, h4, a.t4.fbits)) {
           const KeyFp kf = class_key(3, lo32, 0u, 0u, 0u);
-          const uint32_t fi = hash_filter(kf.fp, a.t4.fbits);
-          if ((f4[fi >> 5] >> (fi & 31)) & 1u) {
-            for (uint32_t u = table_find(a.t4, kf.key, kf.fp); u != PAT_NIL;) {
-              const PatInfo pi = load_pat(a.pat, u);
-              if (pi.len <= r && (k8 & low_bytes_mask(pi.len)) == pi.pk8) add(u);
-              u = pi.next;
-            }
+          for (uint32_t u = table_find(a.t4, kf.key, kf.fp); u != PAT_NIL;) {
+            const PatInfo pi = load_pat(a.pat, u);
+            if (pi.len <= r && (k8 & low_bytes_mask(pi.len)) == pi.pk8) add(u);
+            u = pi.next;
           }
         }
         if (a.t3.present && r >= 3) {
-          const KeyFp kf = class_key(4, lo32, 0u, 0u, 0u);
-          const uint32_t fi = hash_filter(kf.fp, a.t3.fbits);
-          if ((f3[fi >> 5] >> (fi & 31)) & 1u) {
+          const uint32_t h3 = (lo32 & 0xFFFFFFu) * HASH_A;
+          if (filter_pass(f3, h3, a.t3.fbits)) {
+            const KeyFp kf = class_key(4, lo32, 0u, 0u, 0u);
             const uint32_t u = table_find(a.t3, kf.key, kf.fp);   // a 3-byte key is the whole pattern
             if (u != PAT_NIL) add(u);
           }
@@ -311,14 +324,13 @@ __global__ void __launch_bounds__(SM_THREADS) search_multi_kernel(const SearchAr
   uint32_t* my_cnt = (MODE == 2) ? nullptr : a.cnt + tile;   // element of pattern u: my_cnt[u * n_tiles]
   uint16_t* mine = s_hits[wib][lane];
 
+  // a hit goes to the row of the FIRST query that asked for the pattern; rows of queries repeating a
+  // text are copied from it afterwards (search_replicate_kernel) -- config 3 asks its short, high-hit
+  // substrings up to 15 times each: two thirds of the 250 M output entries are such copies
   auto write_rows = [&](uint32_t u, uint32_t id, uint32_t local) {
-    const uint4 raw = __ldg(reinterpret_cast<const uint4*>(a.prow + u));
-    unsigned long long pos = (((unsigned long long)raw.y << 32) | raw.x) + local;
+    const uint2 raw = __ldg(reinterpret_cast<const uint2*>(a.prow + u));
+    const unsigned long long pos = (((unsigned long long)raw.y << 32) | raw.x) + local;
     if (pos < a.cap) a.out_ids[pos] = id;
-    for (uint32_t t = 1; t < raw.z; ++t) {   // the same text asked more than once
-      pos = a.out_off[a.uq[raw.w + t]] + local;
-      if (pos < a.cap) a.out_ids[pos] = id;
-    }
   };
   auto deliver = [&](uint32_t u, uint32_t id) {
     if (MODE == 0) atomicAdd(&my_cnt[(size_t)u * a.n_tiles], 1u);
@@ -412,6 +424,21 @@ __global__ void search_rows_kernel(const uint32_t* __restrict__ uq_off, const ui
   prow[u] = r;
 }
 
+// Row of a query whose text an earlier query of the batch already asked: a copy of that query's row.
+// grid = (duplicate queries, slices); a block copies every gridDim.y-th 4096-entry piece of its row.
+__global__ void __launch_bounds__(256) search_replicate_kernel(const uint32_t* __restrict__ dup_q,
+                                                               const uint32_t* __restrict__ dup_first,
+                                                               const unsigned long long* __restrict__ out_off,
+                                                               uint32_t* out_ids, unsigned long long cap) {
+  const uint32_t q = dup_q[blockIdx.x], f = dup_first[blockIdx.x];
+  const unsigned long long src = out_off[f], dst = out_off[q], n = out_off[f + 1] - src;
+  for (unsigned long long p0 = (unsigned long long)blockIdx.y * 4096; p0 < n; p0 += (unsigned long long)gridDim.y * 4096) {
+    const unsigned long long p1 = min(n, p0 + 4096);
+    for (unsigned long long p = p0 + threadIdx.x; p < p1; p += blockDim.x)
+      if (dst + p < cap && src + p < cap) out_ids[dst + p] = out_ids[src + p];
+  }
+}
+
 __global__ void search_query_counts_kernel(const uint32_t* __restrict__ tot, const uint32_t* __restrict__ q2u,
                                            unsigned long long nq, uint32_t* qcnt) {
   const unsigned long long q = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x;
@@ -487,7 +514,7 @@ static void build_tables(uint64_t nq, const uint32_t* q_off, const uint8_t* q_by
   T.tiny1.assign(256, 0);
   struct KeyedPat {
     unsigned long long key;
-    uint32_t fp, u;
+    uint32_t fp, u, raw;
     bool operator<(const KeyedPat& o) const { return key != o.key ? key < o.key : (fp != o.fp ? fp < o.fp : u < o.u); }
   };
   std::vector<KeyedPat> cls[5];
@@ -508,7 +535,7 @@ static void build_tables(uint64_t nq, const uint32_t* q_off, const uint8_t* q_by
       for (size_t i = 8; i < p.size() && i < 16; ++i) k2 |= (unsigned long long)(uint8_t)p[i] << (8 * (i - 8));
       const int c = p.size() >= 16 ? 0 : p.size() >= 12 ? 1 : p.size() >= 8 ? 2 : p.size() >= 4 ? 3 : 4;
       const KeyFp kf = class_key(c, (uint32_t)k, (uint32_t)(k >> 32), (uint32_t)k2, c == 0 ? (uint32_t)(k2 >> 32) : 0u);
-      cls[c].push_back({kf.key, kf.fp, u});
+      cls[c].push_back({kf.key, kf.fp, u, kf.raw});
     }
   }
   T.poff[U] = (uint32_t)T.pbytes.size();
@@ -538,8 +565,9 @@ static void build_tables(uint64_t nq, const uint32_t* q_off, const uint8_t* q_by
       T.slot[c][h].first = v[i].u;
       T.slot[c][h].fp = v[i].fp;
       for (size_t t = i; t + 1 < j; ++t) T.pat[v[t].u].next = v[t + 1].u;   // patterns sharing the key
-      const uint32_t fi = hash_filter(v[i].fp, fb);
+      const uint32_t fi = hash_filter(v[i].raw, fb), fj = hash_filter2(v[i].raw, fb);
       T.filt[c][fi >> 5] |= 1u << (fi & 31);
+      T.filt[c][fj >> 5] |= 1u << (fj & 31);
       i = j;
     }
   }
@@ -583,7 +611,7 @@ int32_t run_search_multi(CallCtx* c, dmg_graph* g, int kind, uint32_t v_lo, uint
     sz(T.filt[k].size(), 4);
   }
   sz(U, 16); sz(U, 16); sz(3 * 65536, 4); sz(U + 1, 4); sz(T.pbytes.size(), 1);
-  sz(65536, 4); sz(256, 4); sz(U + 1, 4); sz(nq, 4); sz(nq, 4);
+  sz(65536, 4); sz(256, 4); sz(U + 1, 4); sz(nq, 4); sz(nq, 4); sz(nq, 4); sz(nq, 4);
   DMG_TRY(c->tmp0.reserve(need));
   size_t used = 0;
   SearchArgs a;
@@ -619,6 +647,17 @@ int32_t run_search_multi(CallCtx* c, dmg_graph* g, int kind, uint32_t v_lo, uint
   DMG_TRY(put(c, c->tmp0, &used, T.uq, &a.uq));
   const uint32_t* d_q2u = nullptr;
   DMG_TRY(put(c, c->tmp0, &used, T.q2u, &d_q2u));
+  // queries repeating the text of an earlier query (their rows are copies)
+  std::vector<uint32_t> dup_q, dup_first;
+  for (uint32_t u = 0; u < U; ++u)
+    for (uint32_t t = T.uq_off[u] + 1; t < T.uq_off[u + 1]; ++t) {
+      dup_q.push_back(T.uq[t]);
+      dup_first.push_back(T.uq[T.uq_off[u]]);
+    }
+  const uint32_t n_dup = (uint32_t)dup_q.size();
+  const uint32_t *d_dup_q = nullptr, *d_dup_first = nullptr;
+  DMG_TRY(put(c, c->tmp0, &used, dup_q, &d_dup_q));
+  DMG_TRY(put(c, c->tmp0, &used, dup_first, &d_dup_first));
   for (uint32_t x : T.tiny2) a.has2 |= x != 0;
   for (uint32_t x : T.tiny1) a.has1 |= x != 0;
   a.empty_plus1 = T.empty_plus1;
@@ -720,8 +759,14 @@ int32_t run_search_multi(CallCtx* c, dmg_graph* g, int kind, uint32_t v_lo, uint
       DMG_TRY(c->out_ids.reserve(std::max<uint64_t>(dev_cap, 1) * 4));
       a.out_ids = c->out_ids.as<uint32_t>();
       search_rows_kernel<<<(U + 255) / 256, 256, 0, c->stream>>>(a.uq_off, a.uq, a.out_off, U, a.prow);
-      LaunchScope ls(c, K_SEARCH_EMIT);
-      search_multi_kernel<1><<<blocks, SM_THREADS, smem, c->stream>>>(a);
+      {
+        LaunchScope ls(c, K_SEARCH_EMIT);
+        search_multi_kernel<1><<<blocks, SM_THREADS, smem, c->stream>>>(a);
+      }
+      if (n_dup) {
+        LaunchScope ls(c, K_SEARCH_EMIT);
+        search_replicate_kernel<<<dim3(n_dup, 32), 256, 0, c->stream>>>(d_dup_q, d_dup_first, a.out_off, a.out_ids, dev_cap);
+      }
     }
   }
   DMG_CUDA(cudaGetLastError());
