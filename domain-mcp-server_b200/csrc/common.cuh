@@ -150,6 +150,11 @@ struct CtxGuard {
 
 void publish_stats(const dmg_call_stats& s);   // thread-local "last call" record
 
+// traverse.cu: the k-hop batch on device buffers, on c->stream; counters land in c->h_counters once the
+// caller has synchronised.  Uses c->status / scratch / tmp0..tmp3.
+int32_t run_khop(CallCtx* c, dmg_graph* g, int mode, int k, int exclude, uint64_t nq, const uint32_t* d_q_off,
+                 const uint32_t* d_q_src, uint64_t* d_out_off, uint32_t* d_out_ids, uint8_t* d_out_hop, uint64_t cap);
+
 // Launch helper: counts the launch, brackets it with events when profiling is on.
 struct LaunchScope {
   CallCtx* c;
@@ -214,6 +219,8 @@ struct dmg_graph {
   uint32_t* d_method_off = nullptr;  // [V+1] optional method catalog (names only)
   uint32_t* d_mname_off = nullptr;   // [M+1]
   uint8_t* d_mname_lower = nullptr;
+  uint32_t* d_mexact_off = nullptr;  // [M+1] optional: method names as written (stack-trace frames match them exactly)
+  uint8_t* d_mexact = nullptr;
   uint32_t n_methods = 0;
   std::vector<uint32_t> h_endpoint_methods;   // catalog indices of HTTP endpoint methods, ascending
   std::vector<uint32_t> h_part_off, h_entry;

@@ -156,7 +156,7 @@ static void free_graph(dmg_graph* g) {
   cudaSetDevice(g->eng->device);
   for (void* p : {(void*)g->d_out_ptr, (void*)g->d_out_idx, (void*)g->d_in_ptr, (void*)g->d_in_idx,
                   (void*)g->d_und_ptr, (void*)g->d_und_idx, (void*)g->d_part_off, (void*)g->d_entry, (void*)g->d_entry_by_part, (void*)g->d_entry_bits, (void*)g->d_name_off,
-                  (void*)g->d_lower, (void*)g->d_names, (void*)g->d_full_tbl, (void*)g->d_simple_tbl, (void*)g->d_simple_next, (void*)g->d_method_off, (void*)g->d_mname_off, (void*)g->d_mname_lower})
+                  (void*)g->d_lower, (void*)g->d_names, (void*)g->d_full_tbl, (void*)g->d_simple_tbl, (void*)g->d_simple_next, (void*)g->d_method_off, (void*)g->d_mname_off, (void*)g->d_mname_lower, (void*)g->d_mexact_off, (void*)g->d_mexact})
     if (p) cudaFree(p);
   for (auto& el : g->ell)
     for (void* p : {(void*)el.d_proj_slice, (void*)el.d_slice_off, (void*)el.d_vrow, (void*)el.d_data})

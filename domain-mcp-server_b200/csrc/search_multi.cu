@@ -24,7 +24,7 @@ namespace dmg {
 
 constexpr int SM_THREADS = 256;          // 8 warps per CTA
 constexpr int SM_WARPS = SM_THREADS / 32;
-constexpr int SM_HITBUF = 64;            // distinct patterns of one name before the exhaustive fallback
+constexpr int SM_HITBUF = 32;            // distinct patterns of one name before the exhaustive fallback
 constexpr uint32_t SM_MAX_PATTERNS = 16384;   // per round (bounds the tile x pattern matrix)
 
 constexpr uint32_t PAT_NIL = 0xFFFFFFFFu;
@@ -154,124 +154,143 @@ __device__ __forceinline__ unsigned long long low_bytes_mask(uint32_t len) {
   return len >= 8 ? ~0ull : ((1ull << (8 * len)) - 1ull);
 }
 
-// Scans the name of this lane (vertex i, if i < n1) and collects the distinct patterns it contains in
-// `mine` (shared memory, SM_HITBUF entries).  Returns their number; a value above SM_HITBUF means the
-// list overflowed and the name has to be tested against every pattern.
-__device__ __forceinline__ uint32_t match_name(const SearchArgs& a, const uint32_t* f16, const uint32_t* f12,
-                                               const uint32_t* f8, const uint32_t* f4, const uint32_t* f3,
-                                               uint32_t i, uint32_t n1, uint16_t* mine) {
-    uint32_t nh = 0;
-    // a pattern may occur at several positions of the name: keep it once.  64 bits in registers say
-    // "certainly not seen yet" for most hits; only a set bit sends the lane through its list.
-    unsigned long long seen = 0;
-    auto add = [&](uint32_t u) {
-      const unsigned long long bit = 1ull << ((u * 0x9E3779B1u) >> 26);
-      if (seen & bit)
-        for (uint32_t t = 0; t < nh && t < SM_HITBUF; ++t)
-          if (mine[t] == (uint16_t)u) return;
-      seen |= bit;
-      if (nh < SM_HITBUF) mine[nh] = (uint16_t)u;
-      ++nh;
-    };
-    if (i < n1) {
-      const unsigned long long s = a.name_off[i], e = a.name_off[i + 1];
-      const uint32_t len = (uint32_t)min(e - s, 0xFFFFFFFFull);
-      if (a.empty_plus1) add(a.empty_plus1 - 1);
-      const uint8_t* wp = a.lower + (s & ~3ull);   // arena is zero padded: reading past e is safe
-      uint32_t sh = (uint32_t)(s & 3ull) * 8;
-      uint32_t w0 = __ldg(reinterpret_cast<const uint32_t*>(wp));
-      uint32_t w1 = __ldg(reinterpret_cast<const uint32_t*>(wp + 4));
-      uint32_t w2 = __ldg(reinterpret_cast<const uint32_t*>(wp + 8));
-      uint32_t w3 = __ldg(reinterpret_cast<const uint32_t*>(wp + 12));
-      uint32_t w4 = __ldg(reinterpret_cast<const uint32_t*>(wp + 16));
-      wp += 20;
-      // a pattern of the long classes: first 8 bytes already equal (or hashed): check the rest
-      auto long_class = [&](const SlotTable& tb, const KeyFp& kf, unsigned long long k8a, uint32_t r, uint32_t p) {
-        for (uint32_t u = table_find(tb, kf.key, kf.fp); u != PAT_NIL;) {
-          const PatInfo pi = load_pat(a.pat, u);
-          if (pi.len <= r && pi.pk8 == k8a) {
-            bool ok = true;
-            const uint8_t* pb = a.pbytes + a.poff[u];
-            const uint8_t* nb = a.lower + s + p;
-            for (uint32_t t = 8; t < pi.len && ok; ++t) ok = nb[t] == pb[t];
-            if (ok) add(u);
-          }
-          u = pi.next;
+// Matching is two phases per warp step of 32 names (lane = name), because the hit path -- slot
+// table probe, pattern record, verification -- diverges hopelessly when it runs inline: ncu on config 3
+// showed 13 of 32 lanes active and 83 % of the warp instructions spent there with one or two lanes on.
+//   scan     every lane walks its own name; a text position that passes a class's filter is only
+//            QUEUED as a candidate (class, position) in the lane's shared-memory queue
+//   resolve  the warp flattens the 32 queues and works them off 32 candidates at a time, all lanes
+//            busy: window bytes -> key -> slot table -> chain of pattern records -> verification; a
+//            match is appended to the hit list of the name it belongs to
+// after which every lane de-duplicates its own short list (a pattern may occur at several positions).
+constexpr int SM_CANDBUF = 48;                 // queued candidates of one name before the exhaustive fallback
+constexpr uint32_t CAND_POS_BITS = 13;         // candidate = class << 13 | position; longer names: fallback
+
+// phase 1: returns the number of candidates of name i (may exceed SM_CANDBUF: overflow)
+__device__ __forceinline__ uint32_t scan_candidates(const SearchArgs& a, const uint32_t* f16, const uint32_t* f12,
+                                                    const uint32_t* f8, const uint32_t* f4, const uint32_t* f3,
+                                                    unsigned long long s, uint32_t len, uint16_t* cand) {
+  uint32_t nc = 0;
+  auto push = [&](uint32_t cls, uint32_t p) {
+    if (nc < SM_CANDBUF) cand[nc] = (uint16_t)((cls << CAND_POS_BITS) | p);
+    ++nc;
+  };
+  if (len >= (1u << CAND_POS_BITS)) return SM_CANDBUF + 1;
+  const uint8_t* wp = a.lower + (s & ~3ull);   // arena is zero padded: reading past the end is safe
+  uint32_t sh = (uint32_t)(s & 3ull) * 8;
+  uint32_t w0 = __ldg(reinterpret_cast<const uint32_t*>(wp));
+  uint32_t w1 = __ldg(reinterpret_cast<const uint32_t*>(wp + 4));
+  uint32_t w2 = __ldg(reinterpret_cast<const uint32_t*>(wp + 8));
+  uint32_t w3 = __ldg(reinterpret_cast<const uint32_t*>(wp + 12));
+  uint32_t w4 = __ldg(reinterpret_cast<const uint32_t*>(wp + 16));
+  wp += 20;
+  const bool any_long = (a.t16.present | a.t12.present) != 0, any8 = any_long || a.t8.present;
+  for (uint32_t p = 0; p < len; ++p) {
+    const uint32_t r = len - p;
+    const uint32_t lo32 = sh ? __funnelshift_r(w0, w1, sh) : w0;
+    const uint32_t h4 = lo32 * HASH_A;
+    if (any8 && r >= 8) {
+      const uint32_t hi32 = sh ? __funnelshift_r(w1, w2, sh) : w1;
+      const uint32_t h8 = h4 ^ (hi32 * HASH_B);
+      if (any_long && r >= 12) {
+        const uint32_t lo2 = sh ? __funnelshift_r(w2, w3, sh) : w2;
+        const uint32_t h12 = h8 ^ (lo2 * HASH_C);
+        if (a.t16.present && r >= 16) {
+          const uint32_t hi2 = sh ? __funnelshift_r(w3, w4, sh) : w3;
+          if (filter_pass(f16, h12 ^ (hi2 * HASH_D), a.t16.fbits)) push(0, p);
         }
-      };
-      const bool any_long = (a.t16.present | a.t12.present) != 0, any8 = any_long || a.t8.present;
-      for (uint32_t p = 0; p < len; ++p) {
-        const uint32_t r = len - p;
-        const uint32_t lo32 = sh ? __funnelshift_r(w0, w1, sh) : w0;
-        const uint32_t hi32 = sh ? __funnelshift_r(w1, w2, sh) : w1;
-        const unsigned long long k8 = ((unsigned long long)hi32 << 32) | lo32;
-        const uint32_t h4 = lo32 * HASH_A;
-        if (any8 && r >= 8) {
-          const uint32_t h8 = h4 ^ (hi32 * HASH_B);
-          if (any_long && r >= 12) {
-            const uint32_t lo2 = sh ? __funnelshift_r(w2, w3, sh) : w2;
-            const uint32_t h12 = h8 ^ (lo2 * HASH_C);
-            if (a.t16.present && r >= 16) {
-              const uint32_t hi2 = sh ? __funnelshift_r(w3, w4, sh) : w3;
-              if (filter_pass(f16, h12 ^ (hi2 * HASH_D), a.t16.fbits))
-                long_class(a.t16, class_key(0, lo32, hi32, lo2, hi2), k8, r, p);
-            }
-            if (a.t12.present && filter_pass(f12, h12, a.t12.fbits)) long_class(a.t12, class_key(1, lo32, hi32, lo2, 0u), k8, r, p);
-          }
-          if (a.t8.present && filter_pass(f8, h8, a.t8.fbits)) {
-            const KeyFp kf = class_key(2, lo32, hi32, 0u, 0u);
-            for (uint32_t u = table_find(a.t8, kf.key, kf.fp); u != PAT_NIL;) {
-              const PatInfo pi = load_pat(a.pat, u);
-              if (pi.len <= r) {
-                bool ok = true;
-                if (pi.len > 8) {
-                  const uint8_t* pb = a.pbytes + a.poff[u];
-                  const uint8_t* nb = a.lower + s + p;
-                  for (uint32_t t = 8; t < pi.len && ok; ++t) ok = nb[t] == pb[t];
-                }
-                if (ok) add(u);
-              }
-              u = pi.next;
-            }
-          }
-        }
-        if (a.t4.present && r >= 4 && filter_pass(f4, h4, a.t4.fbits)) {
-          const KeyFp kf = class_key(3, lo32, 0u, 0u, 0u);
-          for (uint32_t u = table_find(a.t4, kf.key, kf.fp); u != PAT_NIL;) {
-            const PatInfo pi = load_pat(a.pat, u);
-            if (pi.len <= r && (k8 & low_bytes_mask(pi.len)) == pi.pk8) add(u);
-            u = pi.next;
-          }
-        }
-        if (a.t3.present && r >= 3) {
-          const uint32_t h3 = (lo32 & 0xFFFFFFu) * HASH_A;
-          if (filter_pass(f3, h3, a.t3.fbits)) {
-            const KeyFp kf = class_key(4, lo32, 0u, 0u, 0u);
-            const uint32_t u = table_find(a.t3, kf.key, kf.fp);   // a 3-byte key is the whole pattern
-            if (u != PAT_NIL) add(u);
-          }
-        }
-        if (a.has2 && r >= 2) {
-          const uint32_t u1 = a.tiny2[lo32 & 0xFFFFu];
-          if (u1) add(u1 - 1);
-        }
-        if (a.has1) {
-          const uint32_t u1 = a.tiny1[lo32 & 0xFFu];
-          if (u1) add(u1 - 1);
-        }
-        sh += 8;
-        if (sh == 32) {
-          sh = 0;
-          w0 = w1;
-          w1 = w2;
-          w2 = w3;
-          w3 = w4;
-          w4 = __ldg(reinterpret_cast<const uint32_t*>(wp));
-          wp += 4;
-        }
+        if (a.t12.present && filter_pass(f12, h12, a.t12.fbits)) push(1, p);
       }
+      if (a.t8.present && filter_pass(f8, h8, a.t8.fbits)) push(2, p);
     }
-    return nh;
+    if (a.t4.present && r >= 4 && filter_pass(f4, h4, a.t4.fbits)) push(3, p);
+    if (a.t3.present && r >= 3 && filter_pass(f3, (lo32 & 0xFFFFFFu) * HASH_A, a.t3.fbits)) push(4, p);
+    if (a.has2 && r >= 2 && a.tiny2[lo32 & 0xFFFFu]) push(5, p);
+    if (a.has1 && a.tiny1[lo32 & 0xFFu]) push(6, p);
+    sh += 8;
+    if (sh == 32) {
+      sh = 0;
+      w0 = w1;
+      w1 = w2;
+      w2 = w3;
+      w3 = w4;
+      w4 = __ldg(reinterpret_cast<const uint32_t*>(wp));
+      wp += 4;
+    }
+  }
+  return nc;
+}
+
+// phase 2, whole warp: `nc` = this lane's candidate count (<= SM_CANDBUF), s / len = this lane's name.
+// Matches go to hits[owner][...] with n_hits[owner] counting them (may run past SM_HITBUF: overflow).
+__device__ __forceinline__ void resolve_candidates(const SearchArgs& a, int lane, uint32_t nc, unsigned long long s,
+                                                   uint32_t len, const uint16_t (*cand)[SM_CANDBUF],
+                                                   uint16_t (*hits)[SM_HITBUF], uint32_t* n_hits, uint32_t* pref) {
+  const uint32_t inc = warp_incl_scan_u32(nc);
+  const uint32_t total = __shfl_sync(FULL, inc, 31);
+  pref[lane] = inc - nc;
+  __syncwarp();
+  for (uint32_t j0 = 0; j0 < total; j0 += 32) {
+    const uint32_t j = j0 + lane;
+    const bool valid = j < total;
+    uint32_t owner = 0;   // last lane whose first candidate is <= j
+    if (valid) {
+#pragma unroll
+      for (int st = 16; st > 0; st >>= 1)
+        if (pref[owner + st] <= j) owner += st;
+    }
+    const unsigned long long so = __shfl_sync(FULL, s, owner);
+    const uint32_t leno = __shfl_sync(FULL, len, owner);
+    if (!valid) continue;
+    const uint32_t c = cand[owner][j - pref[owner]];
+    const uint32_t cls = c >> CAND_POS_BITS, p = c & ((1u << CAND_POS_BITS) - 1u);
+    const uint32_t r = leno - p;
+    // 16 window bytes at so + p
+    const unsigned long long at = so + p;
+    const uint32_t* wp = reinterpret_cast<const uint32_t*>(a.lower + (at & ~3ull));
+    const uint32_t sh = (uint32_t)(at & 3ull) * 8;
+    const uint32_t w0 = __ldg(wp), w1 = __ldg(wp + 1), w2 = __ldg(wp + 2), w3 = __ldg(wp + 3), w4 = __ldg(wp + 4);
+    const uint32_t lo32 = sh ? __funnelshift_r(w0, w1, sh) : w0, hi32 = sh ? __funnelshift_r(w1, w2, sh) : w1;
+    const uint32_t lo2 = sh ? __funnelshift_r(w2, w3, sh) : w2, hi2 = sh ? __funnelshift_r(w3, w4, sh) : w3;
+    const unsigned long long k8 = ((unsigned long long)hi32 << 32) | lo32;
+    auto hit = [&](uint32_t u) {
+      const uint32_t slot = atomicAdd(&n_hits[owner], 1u);
+      if (slot < SM_HITBUF) hits[owner][slot] = (uint16_t)u;
+    };
+    if (cls >= 5) {
+      const uint32_t u1 = cls == 5 ? a.tiny2[lo32 & 0xFFFFu] : a.tiny1[lo32 & 0xFFu];
+      if (u1) hit(u1 - 1);
+      continue;
+    }
+    const SlotTable& tb = cls == 0 ? a.t16 : cls == 1 ? a.t12 : cls == 2 ? a.t8 : cls == 3 ? a.t4 : a.t3;
+    const KeyFp kf = class_key((int)cls, lo32, cls >= 3 ? 0u : hi32, cls >= 2 ? 0u : lo2, cls >= 1 ? 0u : hi2);
+    for (uint32_t u = table_find(tb, kf.key, kf.fp); u != PAT_NIL;) {
+      const PatInfo pi = load_pat(a.pat, u);
+      if (pi.len <= r && (k8 & low_bytes_mask(pi.len)) == pi.pk8) {   // first min(len, 8) bytes
+        bool ok = true;
+        if (pi.len > 8) {
+          const uint8_t* pb = a.pbytes + a.poff[u];
+          const uint8_t* nb = a.lower + at;
+          for (uint32_t t = 8; t < pi.len && ok; ++t) ok = nb[t] == pb[t];
+        }
+        if (ok) hit(u);
+      }
+      u = pi.next;
+    }
+  }
+  __syncwarp();
+}
+
+// every lane on its own list: keeps one copy of each pattern; returns the list length
+__device__ __forceinline__ uint32_t dedup_hits(uint16_t* mine, uint32_t n) {
+  for (uint32_t t = 1; t < n;) {
+    const uint16_t u = mine[t];
+    bool dup = false;
+    for (uint32_t t2 = 0; t2 < t && !dup; ++t2) dup = mine[t2] == u;
+    if (dup) mine[t] = mine[--n];
+    else ++t;
+  }
+  return n;
 }
 
 // every pattern against one name, by the whole warp (names whose list overflowed)
@@ -310,10 +329,15 @@ __global__ void __launch_bounds__(SM_THREADS) search_multi_kernel(const SearchAr
   uint32_t* f8 = f12 + a.filt_words12;
   uint32_t* f4 = f8 + a.filt_words8;
   uint32_t* f3 = f4 + a.filt_words4;
-  __shared__ uint16_t s_hits[SM_WARPS][32][SM_HITBUF];
   __shared__ uint32_t s_nh[SM_WARPS][32];
+  __shared__ uint32_t s_pref[SM_WARPS][32];
   const int tid = threadIdx.x, lane = tid & 31, wib = tid >> 5;
   const uint32_t fw = a.filt_words16 + a.filt_words12 + a.filt_words8 + a.filt_words4 + a.filt_words3;
+  // hit lists and candidate queues of the warps follow the filters in dynamic shared memory
+  typedef uint16_t HitLists[32][SM_HITBUF];
+  typedef uint16_t CandQueues[32][SM_CANDBUF];
+  HitLists* const s_hits = reinterpret_cast<HitLists*>(sm_u32 + ((fw + 3u) & ~3u));
+  CandQueues* const s_cand = reinterpret_cast<CandQueues*>(s_hits + SM_WARPS);
   for (uint32_t i = tid; i < fw; i += SM_THREADS) sm_u32[i] = a.filt[i];
   __syncthreads();
 
@@ -359,7 +383,26 @@ __global__ void __launch_bounds__(SM_THREADS) search_multi_kernel(const SearchAr
         continue;
       }
     }
-    const uint32_t nh = match_name(a, f16, f12, f8, f4, f3, i0 + lane, n1, mine);
+    uint32_t nh;
+    {
+      const uint32_t i = i0 + lane;
+      unsigned long long s = 0;
+      uint32_t len = 0, nc = 0;
+      if (i < n1) {
+        s = a.name_off[i];
+        len = (uint32_t)min(a.name_off[i + 1] - s, 0xFFFFFFFFull);
+        nc = scan_candidates(a, f16, f12, f8, f4, f3, s, len, s_cand[wib][lane]);
+      }
+      const bool cand_overflow = nc > SM_CANDBUF;
+      // the empty pattern is contained in every name (CCS:1513: "".contains)
+      if (i < n1 && a.empty_plus1) mine[0] = (uint16_t)(a.empty_plus1 - 1);
+      s_nh[wib][lane] = (i < n1 && a.empty_plus1) ? 1u : 0u;
+      __syncwarp();
+      resolve_candidates(a, lane, cand_overflow ? 0u : nc, s, len, s_cand[wib], s_hits[wib], s_nh[wib], s_pref[wib]);
+      const uint32_t raw_n = s_nh[wib][lane];
+      nh = (cand_overflow || raw_n > SM_HITBUF) ? SM_HITBUF + 1 : dedup_hits(mine, raw_n);
+    }
+    __syncwarp();
     s_nh[wib][lane] = nh;
     __syncwarp();
     if (MODE == 0) {
@@ -669,7 +712,8 @@ int32_t run_search_multi(CallCtx* c, dmg_graph* g, int kind, uint32_t v_lo, uint
   c->stats.h2d_bytes += used;
 
   const uint32_t range = v_hi - v_lo;
-  const size_t smem = (size_t)filt_all.size() * 4;
+  const size_t smem = (((size_t)filt_all.size() + 3) & ~size_t(3)) * 4 +
+                      (size_t)SM_WARPS * 32 * (SM_HITBUF + SM_CANDBUF) * sizeof(uint16_t);
   {
     DMG_CUDA(cudaFuncSetAttribute(search_multi_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     DMG_CUDA(cudaFuncSetAttribute(search_multi_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

@@ -1021,7 +1021,7 @@ static int32_t launch_bit_traversal(CallCtx* c, dmg_graph* g, int w64, int mode,
 
 // Runs the k-hop batch on device buffers on c->stream; leaves counters in c->h_counters after
 // the caller synchronises.
-static int32_t run_khop(CallCtx* c, dmg_graph* g, int mode, int k, int exclude, uint64_t nq,
+int32_t run_khop(CallCtx* c, dmg_graph* g, int mode, int k, int exclude, uint64_t nq,
                         const uint32_t* d_q_off, const uint32_t* d_q_src, uint64_t* d_out_off,
                         uint32_t* d_out_ids, uint8_t* d_out_hop, uint64_t cap) {
   Engine* e = c->eng;

@@ -91,6 +91,8 @@ def lib():
             "dmg_neighbors_batch_dev_static": (i32, [vp, i32, i32, i32, u64, vp, vp, vp, vp, vp, u64, pu64]),
             "dmg_neighbors_batch_bits": (i32, [vp, i32, i32, i32, u64, vp, vp, C.POINTER(u32), C.POINTER(u32), vp, vp,
                                                 vp, u64, pu64]),
+            "dmg_stacktrace_batch": (i32, [vp, i32, u64, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, u64, pu64]),
+            "dmg_graph_set_method_names": (i32, [vp, vp, vp]),
             "dmg_bits_decode": (i32, [u32, u32, u64, vp, vp, vp, vp, vp, vp, u64, pu64, i32]),
             "dmg_closure": (i32, [vp, i32, u32, vp, vp, pu64]),
             "dmg_analysis_order": (i32, [vp, vp]),
@@ -464,6 +466,48 @@ class Graph:
             np.cumsum([len(b) for b in enc], out=no[1:])
         lb = np.frombuffer(b"".join(enc) + b"\0", dtype=np.uint8).copy()
         _check(self.L.dmg_graph_set_methods(self.h, mo.ctypes.data, no.ctypes.data, lb.ctypes.data))
+
+    def set_method_names(self, methods_per_vertex):
+        """Method names as written (for dmg_stacktrace_batch); same catalog order as set_methods."""
+        enc = [m.encode("utf-8") for ms in methods_per_vertex for m in ms]
+        no = np.zeros(len(enc) + 1, np.uint32)
+        if enc:
+            np.cumsum([len(b) for b in enc], out=no[1:])
+        b = np.frombuffer(b"".join(enc) + b"\0", dtype=np.uint8).copy()
+        _check(self.L.dmg_graph_set_method_names(self.h, no.ctypes.data, b.ctypes.data))
+
+    def stacktrace_batch(self, traces, k=1):
+        """traces: list of lists of (class_name, method_name or None).  Returns (status u8[frames],
+        vertex u32[frames], method u32[frames], off u64[n+1], ids, hop)."""
+        frames = [f for t in traces for f in t]
+        n, nf = len(traces), len(frames)
+        t_off = np.zeros(n + 1, np.uint32)
+        if n:
+            np.cumsum([len(t) for t in traces], out=t_off[1:])
+
+        def pack(texts):
+            off = np.zeros(len(texts) + 1, np.uint32)
+            if texts:
+                np.cumsum([len(x) for x in texts], out=off[1:])
+            return off, np.frombuffer(b"".join(texts) + b"\0", dtype=np.uint8).copy()
+
+        cn_off, cn = pack([c.encode("utf-8") for c, _m in frames])
+        with_m = any(m is not None for _c, m in frames)
+        mn_off, mn = pack([(m or "").encode("utf-8") for _c, m in frames])
+        status = np.zeros(max(nf, 1), np.uint8)
+        vertex = np.zeros(max(nf, 1), np.uint32)
+        method = np.zeros(max(nf, 1), np.uint32)
+        off = np.zeros(n + 1, np.uint64)
+        need = C.c_uint64(0)
+        args = (self.h, k, n, t_off.ctypes.data, cn_off.ctypes.data, cn.ctypes.data,
+                mn_off.ctypes.data if with_m else None, mn.ctypes.data if with_m else None, status.ctypes.data,
+                vertex.ctypes.data, method.ctypes.data, off.ctypes.data)
+        rc = self.L.dmg_stacktrace_batch(*args, None, None, 0, C.byref(need))
+        _check(rc, allow=(ECAP,))
+        cap = need.value
+        ids, hop = np.zeros(max(cap, 1), np.uint32), np.zeros(max(cap, 1), np.uint8)
+        _check(self.L.dmg_stacktrace_batch(*args, ids.ctypes.data, hop.ctypes.data, cap, C.byref(need)))
+        return status[:nf], vertex[:nf], method[:nf], off, ids[:need.value], hop[:need.value]
 
     def set_methods_packed(self, method_off, name_off, lower_bytes):
         """Array form of set_methods for large catalogs (u32 offsets, lower-cased bytes)."""

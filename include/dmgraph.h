@@ -313,6 +313,33 @@ int32_t dmg_search_batch(dmg_graph* g, int32_t kind, uint32_t v_lo, uint32_t v_h
 int32_t dmg_lookup_batch(dmg_graph* g, int32_t kind, uint32_t v_lo, uint32_t v_hi, uint64_t n,
                          const uint32_t* t_off, const uint8_t* t_bytes, uint32_t* out_ids);
 
+/* ---- get_stack_trace_context, graph half, in one call --------------------
+ * Replaces the per-frame lookups and the neighbour resolution of CodeContextService.getStackTraceContext
+ * (CCS:1392-1446) and resolveNeighbors (CCS:1550-1578).  Trace t has frames t_off[t] .. t_off[t+1]; frame
+ * f has class name cn_bytes[cn_off[f] .. cn_off[f+1]) and, if mn_off is given, method name
+ * mn_bytes[mn_off[f] .. mn_off[f+1]) -- both as written (the reference matches them with SQL equality).
+ *   out_status[f]  DMG_FRAME_MISSING        no project holds the class        (CCS:1405-1410)
+ *                  DMG_FRAME_CLASS_MISSING  class known, method not           (CCS:1415-1423); only produced
+ *                                           when mn_off is given AND the graph has dmg_graph_set_method_names
+ *                  DMG_FRAME_FOUND          both found
+ *   out_vertex[f]  the class's vertex (the lowest id if two projects hold the same name; the reference's
+ *                  findOne() raises there, SURVEY quirk 11 -- a host concern), 0xFFFFFFFF if missing
+ *   out_method[f]  catalog index of the method, 0xFFFFFFFF if none (may be NULL)
+ *   row t          neighbours of the trace exactly as dmg_neighbors_batch(DMG_BOTH, k, exclude = 1) over the
+ *                  FOUND frames: the graph is the project of the first found frame (CCS:1426-1434); a found
+ *                  frame of another project takes part by name only (CCS:1563-1568).  k = 1 is the reference. */
+#define DMG_FRAME_MISSING 0
+#define DMG_FRAME_CLASS_MISSING 1
+#define DMG_FRAME_FOUND 2
+int32_t dmg_stacktrace_batch(dmg_graph* g, int32_t k, uint64_t n_traces, const uint32_t* t_off,
+                             const uint32_t* cn_off, const uint8_t* cn_bytes, const uint32_t* mn_off,
+                             const uint8_t* mn_bytes, uint8_t* out_status, uint32_t* out_vertex,
+                             uint32_t* out_method, uint64_t* out_off, uint32_t* out_ids, uint8_t* out_hop,
+                             uint64_t cap, uint64_t* needed);
+/* Method names as written (source_methods.method_name), entry m = bytes[name_off[m] .. name_off[m+1]);
+ * same catalog order as dmg_graph_set_methods, which must come first.                              */
+int32_t dmg_graph_set_method_names(dmg_graph* g, const uint32_t* name_off, const uint8_t* bytes);
+
 /* ---- Q1: graph_query execution (GQS:53-73, 111-150, 195-394) ---------------------------------
  * The DSL lexer (GraphQuery.parse, GQ:95-163) stays in the host; what reaches the engine is a
  * batch of already-tokenised operations.  Row i of the output answers ops[i]:

@@ -291,3 +291,35 @@ def method_check(graph, identifier, check_value):
         if ascii_lower(m) == low:
             return True, m
     return False, None
+
+
+# ---- CodeContextService.getStackTraceContext, graph half (CCS:1392-1446 + 1550-1578) ---------------
+FRAME_MISSING, FRAME_CLASS_MISSING, FRAME_FOUND = 0, 1, 2
+
+
+def stack_trace_context(graphs, methods, frames, k=1):
+    """graphs: list of (project_id, ProjectGraph) in registry order; methods: {class name: set of
+    method names} (source_methods rows; matching is SQL equality, case sensitive); frames: list of
+    (class_name, method_name).  Returns (statuses, neighbours {name: hop}).
+      - a frame whose class no project holds is MISSING (CCS:1405-1410); whose class is known but
+        whose method is not, CLASS_MISSING (CCS:1415-1423); else FOUND
+      - the project of the FIRST found frame is the graph neighbours are resolved in (CCS:1426-1434)
+      - M = class names of found frames; neighbours = union of resolve(m) minus M, on that one graph
+        (CCS:1558-1578): a found frame of another project takes part BY NAME only
+      - k > 1 iterates the same step level by level; k = 1 is the reference."""
+    status, project = [], None
+    for cls, meth in frames:
+        owner = next((pid for pid, g in graphs if g.contains(cls)), None)
+        if owner is None:
+            status.append(FRAME_MISSING)
+        elif methods is not None and meth not in methods.get(cls, ()):
+            status.append(FRAME_CLASS_MISSING)
+        else:
+            status.append(FRAME_FOUND)
+            if project is None:
+                project = owner
+    if project is None:
+        return status, {}
+    graph = next(g for pid, g in graphs if pid == project)
+    matched = [c for (c, _m), s in zip(frames, status) if s == FRAME_FOUND]
+    return status, khop(graph, matched, k, "both", True)

@@ -182,3 +182,71 @@ def test_bit_rows_decode_to_the_packed_rows(engine, n_parts):
         g2 = dmgraph.Graph(engine, 10, [0], [1], [])
         g2.neighbors_batch_bits(2, 8, 1, np.array([0, 1], np.uint32), np.array([0], np.uint32))
     assert ei.value.code == dmgraph.EINVAL
+
+
+# ---- get_stack_trace_context in one call (dmg_stacktrace_batch) -------------------------------------
+def test_stacktrace_batch_against_the_restatement(engine):
+    """Frame classification, project choice and neighbour rows against pyref.stack_trace_context
+    (CCS:1392-1446, 1550-1578): frames of unknown classes, known classes with unknown methods, frames of
+    a second project (by-name participation: one class name exists in two projects), repeated frames,
+    traces with no found frame, k = 1 (the reference) and k = 2."""
+    from oracle import pyref
+    rng = np.random.default_rng(12)
+    P, per = 3, 60
+    graphs, names, src, dst, meths = [], [], [], [], {}
+    for p in range(P):
+        g = pyref.ProjectGraph()
+        local = ["co.p%d.Cls%d" % (p, i) for i in range(per - 2)] + ["shared.Util", "shared.Base%d" % p]
+        for nm in local:
+            g.add_node(nm, nm + ".java")
+        for _ in range(300):
+            a, b = rng.integers(0, per, 2)
+            g.add_dependency(local[a], local[b])
+            src.append(p * per + a)
+            dst.append(p * per + b)
+        graphs.append(("proj%d" % p, g))
+        names += local
+    mlist = [["run", "Handle%d" % (v % 3)] if v % 4 else ["run"] for v in range(P * per)]
+    for v, nm in enumerate(names):
+        meths.setdefault(nm, set()).update(mlist[v])      # SQL table keyed by class NAME
+    off, arena = synth.pack_names(names)
+    part_off = np.arange(P + 1, dtype=np.uint32) * per
+    dg = dmgraph.Graph(engine, P * per, src, dst, [], part_off=part_off, name_off=off, name_bytes=arena)
+    dg.set_methods(mlist)
+    dg.set_method_names(mlist)
+    traces = []
+    for t in range(400):
+        fr = []
+        for _ in range(int(rng.integers(0, 9))):
+            r = rng.random()
+            if r < 0.15:
+                fr.append(("org.springframework.X%d" % rng.integers(0, 5), "invoke"))
+            elif r < 0.25:
+                fr.append(("shared.Util", "run"))
+            else:
+                v = int(rng.integers(0, P * per)) if rng.random() < 0.3 else int(rng.integers(0, per)) + per * (t % P)
+                m = ["run", "Handle%d" % (v % 3), "nosuch", "RUN"][int(rng.integers(0, 4))]
+                fr.append((names[v], m))
+        traces.append(fr)
+    for k in (1, 2):
+        status, vertex, method, o, ids, hop = dg.stacktrace_batch(traces, k)
+        f0 = 0
+        for t, fr in enumerate(traces):
+            want_status, want = pyref.stack_trace_context(graphs, meths, fr, k)
+            assert status[f0:f0 + len(fr)].tolist() == want_status
+            for j, (cls, _m) in enumerate(fr):
+                v = int(vertex[f0 + j])
+                assert (v == 0xFFFFFFFF) == (want_status[j] == pyref.FRAME_MISSING)
+                assert v == 0xFFFFFFFF or names[v] == cls
+                if want_status[j] == pyref.FRAME_FOUND:
+                    assert mlist[v][int(method[f0 + j]) - sum(len(x) for x in mlist[:v])] == fr[j][1]
+            a, b = int(o[t]), int(o[t + 1])
+            first = next((int(vertex[f0 + j]) for j in range(len(fr)) if want_status[j] == pyref.FRAME_FOUND), None)
+            lo = (first // per) * per if first is not None else 0
+            got = {names[lo:lo + per][int(i) - lo]: int(h) for i, h in zip(ids[a:b], hop[a:b])}
+            assert got == want, (t, k)
+            f0 += len(fr)
+    # without method names every known class is FOUND
+    status, *_ = dg.stacktrace_batch([[(names[3], None), ("nope.X", None)]], 1)
+    assert status.tolist() == [pyref.FRAME_FOUND, pyref.FRAME_MISSING]
+    dg.release()
