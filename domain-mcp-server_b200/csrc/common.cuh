@@ -198,6 +198,7 @@ struct dmg_graph {
   uint32_t* d_entry = nullptr;     // [n_entry] insertion order
   uint32_t* d_entry_by_part = nullptr;   // [n_entry] grouped by project, insertion order inside each
   uint32_t* d_entry_bits = nullptr;  // [ceil(V/32)]
+  uint8_t* d_vmeta = nullptr;        // [V] bits 0-6 host class-type code (0 = none), bit 7 entry point
   uint64_t* d_name_off = nullptr;  // [V+1] or null
   uint8_t* d_lower = nullptr;      // pre-lowered name arena (+32 B zero pad)
   uint8_t* d_names = nullptr;      // original name arena (exact identifier lookups are case sensitive)

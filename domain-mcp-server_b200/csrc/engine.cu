@@ -155,7 +155,7 @@ using namespace dmg;
 static void free_graph(dmg_graph* g) {
   cudaSetDevice(g->eng->device);
   for (void* p : {(void*)g->d_out_ptr, (void*)g->d_out_idx, (void*)g->d_in_ptr, (void*)g->d_in_idx,
-                  (void*)g->d_und_ptr, (void*)g->d_und_idx, (void*)g->d_part_off, (void*)g->d_entry, (void*)g->d_entry_by_part, (void*)g->d_entry_bits, (void*)g->d_name_off,
+                  (void*)g->d_und_ptr, (void*)g->d_und_idx, (void*)g->d_part_off, (void*)g->d_entry, (void*)g->d_entry_by_part, (void*)g->d_entry_bits, (void*)g->d_vmeta, (void*)g->d_name_off,
                   (void*)g->d_lower, (void*)g->d_names, (void*)g->d_full_tbl, (void*)g->d_simple_tbl, (void*)g->d_simple_next, (void*)g->d_method_off, (void*)g->d_mname_off, (void*)g->d_mname_lower, (void*)g->d_mexact_off, (void*)g->d_mexact})
     if (p) cudaFree(p);
   for (auto& el : g->ell)
@@ -342,6 +342,8 @@ static int32_t finish_upload_impl(dmg_engine* e, dmg_graph* g, uint32_t V, const
   int32_t st = DMG_OK;
   std::vector<uint32_t> ebits((V + 31) / 32 + 1, 0);
   for (uint32_t v : g->h_entry) ebits[v >> 5] |= 1u << (v & 31);
+  std::vector<uint8_t> vmeta(std::max<uint32_t>(V, 1), 0);   // class-type codes arrive with dmg_graph_set_class_types
+  for (uint32_t v : g->h_entry) vmeta[v] = 0x80u;
   // entry points grouped by project (stable, so each project keeps markAsEntryPoint order, PG:190-197):
   // executeEntrypoints (GQS:152-191) lists ONE project's graph
   const size_t P = part.size() - 1;
@@ -382,7 +384,8 @@ static int32_t finish_upload_impl(dmg_engine* e, dmg_graph* g, uint32_t V, const
       (st = upload(&g->d_part_off, part.data(), part.size(), &bytes)) != DMG_OK ||
       (st = upload(&g->d_entry, g->h_entry.data(), g->h_entry.size(), &bytes)) != DMG_OK ||
       (st = upload(&g->d_entry_by_part, entry_by_part.data(), entry_by_part.size(), &bytes)) != DMG_OK ||
-      (st = upload(&g->d_entry_bits, ebits.data(), ebits.size(), &bytes)) != DMG_OK) {
+      (st = upload(&g->d_entry_bits, ebits.data(), ebits.size(), &bytes)) != DMG_OK ||
+      (st = upload(&g->d_vmeta, vmeta.data(), vmeta.size(), &bytes)) != DMG_OK) {
     *g_freed = true;
     free_graph(g);
     return st;

@@ -43,6 +43,7 @@ __global__ void method_lookup_kernel(const uint32_t* __restrict__ method_off, co
 // list, a row of a k-hop group's buffers, a single resolved id): qx_describe_kernel writes the
 // segments and the row length, scan_counts_kernel turns lengths into out_off, qx_fill_kernel copies
 // the segments into the packed result, which leaves the device in ONE copy.
+constexpr uint32_t QX_IDS_ARE_VERTICES = 0x80000000u;   // flag in QxSeg::aux_const (its low byte is the aux value)
 struct QxSeg {
   const uint32_t* ids;
   const uint8_t* aux;   // nullptr: every entry gets aux_const
@@ -79,7 +80,7 @@ __global__ void __launch_bounds__(256) qx_describe_kernel(const QxArgs a) {
     case DMG_OP_OVERVIEW:
       if (known) {
         const uint32_t b = a.out_ptr[op.vertex];
-        r.s[0] = QxSeg{a.out_idx + b, nullptr, a.out_ptr[op.vertex + 1] - b, 0u};
+        r.s[0] = QxSeg{a.out_idx + b, nullptr, a.out_ptr[op.vertex + 1] - b, QX_IDS_ARE_VERTICES};
       }
       if (op.opcode == DMG_OP_DEPENDENCIES) break;
       // overview: dependencies (aux 0) then dependents (aux 1)
@@ -87,25 +88,26 @@ __global__ void __launch_bounds__(256) qx_describe_kernel(const QxArgs a) {
       if (known) {
         const uint32_t b = a.in_ptr[op.vertex];
         r.s[op.opcode == DMG_OP_OVERVIEW ? 1 : 0] =
-            QxSeg{a.in_idx + b, nullptr, a.in_ptr[op.vertex + 1] - b, op.opcode == DMG_OP_OVERVIEW ? 1u : 0u};
+            QxSeg{a.in_idx + b, nullptr, a.in_ptr[op.vertex + 1] - b,
+                  (op.opcode == DMG_OP_OVERVIEW ? 1u : 0u) | QX_IDS_ARE_VERTICES};
       }
       break;
     case DMG_OP_KHOP: {
       const uint32_t grp = a.ref_g[i];
       const unsigned long long at = a.ref_a[i];
       const uint32_t len = a.grp_ids[grp] ? a.ref_b[i] : 0u;
-      r.s[0] = QxSeg{a.grp_ids[grp] + at, a.grp_hop[grp] + at, len, 0u};
+      r.s[0] = QxSeg{a.grp_ids[grp] + at, a.grp_hop[grp] + at, len, QX_IDS_ARE_VERTICES};
       if (!a.grp_ids[grp]) r.s[0] = QxSeg{nullptr, nullptr, a.ref_b[i], 0u};   // sizing call: length only
       break;
     }
     // the op's project owns a contiguous slice of each list (host: ref_a = first entry, ref_b = length)
-    case DMG_OP_ENTRYPOINTS: r.s[0] = QxSeg{a.entry + a.ref_a[i], nullptr, a.ref_b[i], 0u}; break;
+    case DMG_OP_ENTRYPOINTS: r.s[0] = QxSeg{a.entry + a.ref_a[i], nullptr, a.ref_b[i], QX_IDS_ARE_VERTICES}; break;
     case DMG_OP_ENDPOINTS: r.s[0] = QxSeg{a.endpoints + a.ref_a[i], nullptr, a.ref_b[i], 0u}; break;
     case DMG_OP_RESOLVE_NAME:
     case DMG_OP_METHOD:
       // the resolved id sits in the low word of the op's ref_a slot
       r.s[0] = QxSeg{reinterpret_cast<const uint32_t*>(a.ref_a + i), nullptr, a.ref_b[i],
-                     op.opcode == DMG_OP_RESOLVE_NAME ? a.ref_g[i] : 0u};
+                     op.opcode == DMG_OP_RESOLVE_NAME ? (a.ref_g[i] | QX_IDS_ARE_VERTICES) : 0u};
       break;
     default: break;
   }
@@ -118,7 +120,8 @@ __global__ void __launch_bounds__(256) qx_describe_kernel(const QxArgs a) {
 __global__ void __launch_bounds__(256) qx_fill_kernel(const QxRow* __restrict__ rows,
                                                       const unsigned long long* __restrict__ out_off,
                                                       unsigned long long n_ops, uint32_t* out_ids, uint8_t* out_aux,
-                                                      unsigned long long total) {
+                                                      unsigned long long total, const uint8_t* __restrict__ vmeta,
+                                                      uint32_t V, uint8_t* out_meta) {
   constexpr unsigned long long CHUNK = 2048;
   const int lane = threadIdx.x & 31;
   const unsigned long long warp = (blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x) >> 5;
@@ -142,8 +145,11 @@ __global__ void __launch_bounds__(256) qx_fill_kernel(const QxRow* __restrict__ 
       uint32_t j = (uint32_t)(p - row_begin);
       const int sg = j < r.s[0].len ? 0 : 1;
       if (sg) j -= r.s[0].len;
-      out_ids[p] = r.s[sg].ids[j];
+      const uint32_t id = r.s[sg].ids[j];
+      out_ids[p] = id;
       out_aux[p] = r.s[sg].aux ? r.s[sg].aux[j] : (uint8_t)r.s[sg].aux_const;
+      // decoration (GQS:122-130, 308-316): class-type code + entry flag of a vertex id; 0 for catalog indices
+      if (out_meta) out_meta[p] = ((r.s[sg].aux_const & QX_IDS_ARE_VERTICES) && id < V) ? vmeta[id] : (uint8_t)0;
     }
   }
 }
@@ -226,8 +232,40 @@ int32_t dmg_graph_set_method_flags(dmg_graph* g, const uint8_t* flags) {
   return DMG_OK;
 }
 
+static int32_t query_batch_impl(dmg_graph* g, uint64_t n_ops, const dmg_query_op* ops, const uint8_t* text_bytes,
+                                uint64_t* out_off, uint32_t* out_ids, uint8_t* out_aux, uint8_t* out_meta, uint64_t cap,
+                                uint64_t* needed);
 int32_t dmg_query_batch(dmg_graph* g, uint64_t n_ops, const dmg_query_op* ops, const uint8_t* text_bytes,
                         uint64_t* out_off, uint32_t* out_ids, uint8_t* out_aux, uint64_t cap, uint64_t* needed) {
+  return query_batch_impl(g, n_ops, ops, text_bytes, out_off, out_ids, out_aux, nullptr, cap, needed);
+}
+int32_t dmg_query_batch_meta(dmg_graph* g, uint64_t n_ops, const dmg_query_op* ops, const uint8_t* text_bytes,
+                             uint64_t* out_off, uint32_t* out_ids, uint8_t* out_aux, uint8_t* out_meta, uint64_t cap,
+                             uint64_t* needed) {
+  return query_batch_impl(g, n_ops, ops, text_bytes, out_off, out_ids, out_aux, out_meta, cap, needed);
+}
+int32_t dmg_graph_set_class_types(dmg_graph* g, const uint8_t* codes) {
+  if (!g || (g->info.n_vertices && !codes)) {
+    set_error("dmg_graph_set_class_types: NULL argument");
+    return DMG_EINVAL;
+  }
+  const uint32_t V = g->info.n_vertices;
+  std::vector<uint8_t> meta(std::max<uint32_t>(V, 1), 0);
+  for (uint32_t v = 0; v < V; ++v) {
+    if (codes[v] > 127) {
+      set_error("dmg_graph_set_class_types: code %u of vertex %u exceeds 127", codes[v], v);
+      return DMG_EINVAL;
+    }
+    meta[v] = codes[v];
+  }
+  for (uint32_t v : g->h_entry) meta[v] |= 0x80u;   // isEntryPoint (PG:336-338)
+  DMG_CUDA(cudaSetDevice(g->eng->device));
+  DMG_CUDA(cudaMemcpy(g->d_vmeta, meta.data(), meta.size(), cudaMemcpyHostToDevice));
+  return DMG_OK;
+}
+static int32_t query_batch_impl(dmg_graph* g, uint64_t n_ops, const dmg_query_op* ops, const uint8_t* text_bytes,
+                                uint64_t* out_off, uint32_t* out_ids, uint8_t* out_aux, uint8_t* out_meta, uint64_t cap,
+                                uint64_t* needed) {
   if (!g || !out_off || !needed || (n_ops && !ops)) {
     set_error("dmg_query_batch: NULL argument");
     return DMG_EINVAL;
@@ -537,15 +575,18 @@ int32_t dmg_query_batch(dmg_graph* g, uint64_t n_ops, const dmg_query_op* ops, c
   if (total) {
     DMG_TRY(c->out_ids.reserve(total * 4));
     DMG_TRY(c->out_hop.reserve(total));
+    if (out_meta) DMG_TRY(c->tmp3.reserve(total));
     {
       LaunchScope ls(c, K_QUERY_ROWS);
       qx_fill_kernel<<<(unsigned)g->eng->sm_count * 8, 256, 0, c->stream>>>(
-          qa.rows, c->out_off.as<unsigned long long>(), n_ops, c->out_ids.as<uint32_t>(), c->out_hop.as<uint8_t>(), total);
+          qa.rows, c->out_off.as<unsigned long long>(), n_ops, c->out_ids.as<uint32_t>(), c->out_hop.as<uint8_t>(), total,
+          g->d_vmeta, g->info.n_vertices, out_meta ? c->tmp3.as<uint8_t>() : nullptr);
     }
     DMG_CUDA(cudaGetLastError());
     DMG_CUDA(cudaMemcpyAsync(out_ids, c->out_ids.p, total * 4, cudaMemcpyDeviceToHost, c->stream));
     DMG_CUDA(cudaMemcpyAsync(out_aux, c->out_hop.p, total, cudaMemcpyDeviceToHost, c->stream));
-    c->stats.d2h_bytes += total * 5;
+    if (out_meta) DMG_CUDA(cudaMemcpyAsync(out_meta, c->tmp3.p, total, cudaMemcpyDeviceToHost, c->stream));
+    c->stats.d2h_bytes += total * (out_meta ? 6 : 5);
   }
   return c->finish();
 }

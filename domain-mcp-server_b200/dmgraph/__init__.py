@@ -59,6 +59,12 @@ class CallStats(C.Structure):
                 ("device_ms", C.c_float), ("reserved", C.c_float)]
 
 
+class DistClosureStats(C.Structure):
+    _fields_ = [("levels", C.c_uint32), ("push_levels", C.c_uint32), ("pull_levels", C.c_uint32),
+                ("reserved", C.c_uint32), ("edges_read", C.c_uint64), ("exchanged_bytes_per_rank", C.c_uint64),
+                ("device_ms", C.c_float), ("reserved2", C.c_float)]
+
+
 _lib = None
 
 
@@ -93,6 +99,15 @@ def lib():
                                                 vp, u64, pu64]),
             "dmg_stacktrace_batch": (i32, [vp, i32, u64, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, u64, pu64]),
             "dmg_graph_set_method_names": (i32, [vp, vp, vp]),
+            "dmg_dist_create": (i32, [vp, i32, C.POINTER(vp)]),
+            "dmg_dist_destroy": (None, [vp]),
+            "dmg_dist_size": (i32, [vp]),
+            "dmg_dist_engine": (i32, [vp, i32, C.POINTER(vp)]),
+            "dmg_dist_graph_create": (i32, [vp, C.POINTER(GraphDesc), i32, C.POINTER(vp)]),
+            "dmg_dist_graph_release": (None, [vp]),
+            "dmg_dist_graph_part": (i32, [vp, i32, C.POINTER(vp), C.POINTER(u32), C.POINTER(u32)]),
+            "dmg_dist_neighbors_batch": (i32, [vp, i32, i32, i32, u64, vp, vp, vp, vp, vp, u64, pu64]),
+            "dmg_dist_closure": (i32, [vp, i32, u32, vp, vp, pu64, C.POINTER(DistClosureStats)]),
             "dmg_bits_decode": (i32, [u32, u32, u64, vp, vp, vp, vp, vp, vp, u64, pu64, i32]),
             "dmg_closure": (i32, [vp, i32, u32, vp, vp, pu64]),
             "dmg_analysis_order": (i32, [vp, vp]),
@@ -108,6 +123,8 @@ def lib():
             "dmg_lookup_batch": (i32, [vp, i32, u32, u32, u64, vp, vp, vp]),
             "dmg_query_batch": (i32, [vp, u64, vp, vp, vp, vp, vp, u64, pu64]),
             "dmg_graph_set_methods": (i32, [vp, vp, vp, vp]),
+            "dmg_query_batch_meta": (i32, [vp, u64, vp, vp, vp, vp, vp, vp, u64, pu64]),
+            "dmg_graph_set_class_types": (i32, [vp, vp]),
             "dmg_graph_set_method_flags": (i32, [vp, vp]),
             "dmg_last_call_stats": (i32, [vp, C.POINTER(CallStats)]),
             "dmg_profile_enable": (i32, [vp, i32]),
@@ -521,7 +538,17 @@ class Graph:
         f = np.ascontiguousarray(flags, dtype=np.uint8)
         _check(self.L.dmg_graph_set_method_flags(self.h, f.ctypes.data if f.size else None))
 
-    def query_batch(self, ops):
+    def set_class_types(self, codes):
+        c = np.ascontiguousarray(codes, dtype=np.uint8)
+        assert c.size == self.V
+        _check(self.L.dmg_graph_set_class_types(self.h, c.ctypes.data if c.size else None))
+
+    def query_batch_meta(self, ops):
+        """query_batch with the decoration column: rows of (ids, aux, meta)."""
+        rows = self.query_batch(ops, with_meta=True)
+        return rows
+
+    def query_batch(self, ops, with_meta=False):
         """ops: list of dicts {op, vertex?, mode?, k?, exclude?, text?(bytes), project?}; returns rows of (id, aux)."""
         n = len(ops)
         arr = (QueryOp * max(n, 1))()
@@ -543,6 +570,12 @@ class Graph:
         _check(rc, allow=(ECAP,))
         cap = need.value
         ids, aux = np.zeros(max(1, cap), np.uint32), np.zeros(max(1, cap), np.uint8)
+        if with_meta:
+            meta = np.zeros(max(1, cap), np.uint8)
+            _check(self.L.dmg_query_batch_meta(self.h, n, arr, tb.ctypes.data, off.ctypes.data, ids.ctypes.data,
+                                               aux.ctypes.data, meta.ctypes.data, cap, C.byref(need)))
+            return [(ids[int(off[i]):int(off[i + 1])].tolist(), aux[int(off[i]):int(off[i + 1])].tolist(),
+                     meta[int(off[i]):int(off[i + 1])].tolist()) for i in range(n)]
         _check(self.L.dmg_query_batch(self.h, n, arr, tb.ctypes.data, off.ctypes.data, ids.ctypes.data,
                                       aux.ctypes.data, cap, C.byref(need)))
         return [(ids[int(off[i]):int(off[i + 1])].tolist(), aux[int(off[i]):int(off[i + 1])].tolist())
@@ -604,3 +637,66 @@ class Graph:
         _check(self.L.dmg_search_batch(self.h, kind, v_lo, v_hi, nq, q_off.ctypes.data, qb.ctypes.data,
                                        off.ctypes.data, ids.ctypes.data, cap, C.byref(need)))
         return off, ids[:need.value]
+
+
+class Dist:
+    """dmg_dist: one engine per device of the box inside this process (include/dmgraph.h)."""
+
+    def __init__(self, n, devices=None):
+        self.L = lib()
+        self.h = C.c_void_p()
+        dv = (C.c_int32 * n)(*devices) if devices is not None else None
+        _check(self.L.dmg_dist_create(dv, n, C.byref(self.h)))
+        self.n = n
+
+    def close(self):
+        if self.h:
+            self.L.dmg_dist_destroy(self.h)
+            self.h = C.c_void_p()
+
+
+class DistGraph:
+    """A graph on every device of a Dist: replicated (query batches) or vertex-range partitioned (closure)."""
+
+    def __init__(self, dist, n_vertices, src, dst, entry=(), part_off=None, partitioned=False):
+        self.dist, self.L, self.V = dist, dist.L, int(n_vertices)
+        src, dst, entry = _arr(src, np.uint32), _arr(dst, np.uint32), _arr(entry, np.uint32)
+        d = GraphDesc()
+        d.n_vertices, d.n_edges, d.n_entry = self.V, int(src.size), int(entry.size)
+        d.edge_src, d.edge_dst, d.entry_ids = _ptr(src), _ptr(dst), _ptr(entry)
+        if part_off is not None:
+            po = _arr(part_off, np.uint32)
+            d.n_parts, d.part_off = int(po.size - 1), _ptr(po)
+        self.h = C.c_void_p()
+        _check(self.L.dmg_dist_graph_create(dist.h, C.byref(d), int(partitioned), C.byref(self.h)))
+
+    def release(self):
+        if self.h:
+            self.L.dmg_dist_graph_release(self.h)
+            self.h = C.c_void_p()
+
+    def neighbors_batch(self, mode, k, exclude_sources, q_off, q_src, out=None):
+        q_off, q_src = _arr(q_off, np.uint32), _arr(q_src, np.uint32)
+        nq = q_off.size - 1
+        need = C.c_uint64(0)
+        if out is None:
+            off = np.zeros(nq + 1, np.uint64)
+            rc = self.L.dmg_dist_neighbors_batch(self.h, mode, k, int(exclude_sources), nq, _ptr(q_off), _ptr(q_src),
+                                                 off.ctypes.data, None, None, 0, C.byref(need))
+            _check(rc, allow=(ECAP,))
+            ids, hop = np.zeros(max(1, need.value), np.uint32), np.zeros(max(1, need.value), np.uint8)
+        else:
+            off, ids, hop = out
+        _check(self.L.dmg_dist_neighbors_batch(self.h, mode, k, int(exclude_sources), nq, _ptr(q_off), _ptr(q_src),
+                                               off.ctypes.data, ids.ctypes.data, hop.ctypes.data, ids.size,
+                                               C.byref(need)))
+        return off, ids[:need.value], hop[:need.value]
+
+    def closure(self, direction, sources):
+        s = _arr(sources, np.uint32)
+        level = np.zeros(max(1, self.V), np.uint32)
+        reached, st = C.c_uint64(0), DistClosureStats()
+        _check(self.L.dmg_dist_closure(self.h, direction, s.size, _ptr(s), level.ctypes.data, C.byref(reached),
+                                       C.byref(st)))
+        return level[:self.V], reached.value, {f: getattr(st, f) for f, _ in DistClosureStats._fields_
+                                               if not f.startswith("reserved")}

@@ -388,6 +388,17 @@ typedef struct dmg_query_op {
 int32_t dmg_query_batch(dmg_graph* g, uint64_t n_ops, const dmg_query_op* ops, const uint8_t* text_bytes,
                         uint64_t* out_off, uint32_t* out_ids, uint8_t* out_aux, uint64_t cap, uint64_t* needed);
 
+/* Decorated rows: the same batch with one more byte per returned entry, so that
+ * vertexDeps / executeClasses rows (GQS:122-130, 308-316) need no nodeInfo / entry-point lookup per result
+ * on the host: out_meta = class-type code (bits 0-6, as given to dmg_graph_set_class_types; 0 = no
+ * nodeInfo) | 0x80 if the vertex is an entry point (PG:336-338).  Entries that are method-catalog indices
+ * (DMG_OP_METHOD, DMG_OP_ENDPOINTS) get 0.  description / sourceFile stay host strings indexed by the id. */
+int32_t dmg_query_batch_meta(dmg_graph* g, uint64_t n_ops, const dmg_query_op* ops, const uint8_t* text_bytes,
+                             uint64_t* out_off, uint32_t* out_ids, uint8_t* out_aux, uint8_t* out_meta,
+                             uint64_t cap, uint64_t* needed);
+/* One code per vertex (NodeInfo.classType, PG:504-510, as a host-defined enumeration 1..127; 0 = none). */
+int32_t dmg_graph_set_class_types(dmg_graph* g, const uint8_t* codes);
+
 /* Method catalog of a graph (ProjectGraph.methodInfoMap, PG:112; names only -- descriptions and
  * business logic stay host payload): methods of vertex v are catalog entries
  * [method_off[v], method_off[v+1]), entry m's lower-cased name is
@@ -397,6 +408,41 @@ int32_t dmg_graph_set_methods(dmg_graph* g, const uint32_t* method_off, const ui
 /* One byte per catalog entry; bit 0 = MethodInfo.isHttpEndpoint() (httpMethod and httpPath present,
  * PG:75-77).  Needs dmg_graph_set_methods first.                                                 */
 int32_t dmg_graph_set_method_flags(dmg_graph* g, const uint8_t* flags);
+
+/* ---- one process, N devices ------------------------------------------------------
+ * The reference is one JVM with one registry of graphs (GS:34-38): multi-GPU has to live behind this ABI,
+ * not in a launcher.  dmg_dist_create makes one engine per listed device (devices == NULL: 0 .. n-1).
+ *   replicated graph   (partitioned = 0) every device holds the whole graph; dmg_dist_neighbors_batch cuts
+ *                      the batch into n contiguous query ranges, one host thread per device, rows come back
+ *                      in query order exactly as from dmg_neighbors_batch.  No collective.
+ *   partitioned graph  (partitioned = 1) rank r owns a vertex range (multiples of 32) and the edges with
+ *                      an endpoint in it; dmg_dist_closure runs the BFS of analysisOrder (PG:390-421) level
+ *                      by level with an ncclAllGather of frontier bitmaps per level (communicators are
+ *                      created in-process on first use; NCCL is bound with dlopen).  out_level[v] = hop
+ *                      distance, DMG_LEVEL_UNREACHED if not reached -- identical to dmg_closure.
+ * NCCL missing or failing: DMG_ENCCL with the NCCL error text in dmg_last_error().                      */
+typedef struct dmg_dist dmg_dist;
+typedef struct dmg_dist_graph dmg_dist_graph;
+typedef struct dmg_dist_closure_stats {
+  uint32_t levels, push_levels, pull_levels, reserved;
+  uint64_t edges_read;                /* adjacency entries loaded, all ranks */
+  uint64_t exchanged_bytes_per_rank;  /* received through the allgathers */
+  float device_ms;                    /* CUDA events on rank 0's stream around the level loop */
+  float reserved2;
+} dmg_dist_closure_stats;
+int32_t dmg_dist_create(const int32_t* devices, int32_t n, dmg_dist** out);
+void dmg_dist_destroy(dmg_dist* d);
+int32_t dmg_dist_size(const dmg_dist* d);
+int32_t dmg_dist_engine(dmg_dist* d, int32_t rank, dmg_engine** out);
+int32_t dmg_dist_graph_create(dmg_dist* d, const dmg_graph_desc* desc, int32_t partitioned, dmg_dist_graph** out);
+void dmg_dist_graph_release(dmg_dist_graph* dg);
+int32_t dmg_dist_graph_part(const dmg_dist_graph* dg, int32_t rank, dmg_graph** out, uint32_t* v_lo, uint32_t* v_hi);
+int32_t dmg_dist_neighbors_batch(dmg_dist_graph* dg, int32_t mode, int32_t k, int32_t exclude_sources,
+                                 uint64_t n_queries, const uint32_t* q_off, const uint32_t* q_src,
+                                 uint64_t* out_off, uint32_t* out_ids, uint8_t* out_hop, uint64_t cap,
+                                 uint64_t* needed);
+int32_t dmg_dist_closure(dmg_dist_graph* dg, int32_t dir, uint32_t n_src, const uint32_t* src,
+                         uint32_t* out_level, uint64_t* reached, dmg_dist_closure_stats* stats);
 
 /* ---- measurement -----------------------------------------------------------------------------*/
 int32_t dmg_last_call_stats(dmg_engine* e, dmg_call_stats* out);

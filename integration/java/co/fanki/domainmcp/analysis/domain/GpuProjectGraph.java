@@ -15,23 +15,30 @@ import java.util.Map;
 import java.util.Set;
 
 /**
- * ProjectGraph whose read methods run on the GPU engine. NOT COMPILED in the dmgraph repository.
+ * GPU-side twin of one published {@link ProjectGraph}. NOT COMPILED in the dmgraph repository.
  *
- * <p>Build methods (addNode, addDependency, markAsEntryPoint, metadata) stay the inherited Java
- * maps; {@link #publish} freezes the graph, uploads it (ProjectGraph.java:160-197 rules are
- * re-applied by dmg_graph_create) and from then on dependencies / dependents / resolve /
- * analysisOrder and the identifier scans are single calls into libdmgraph.so. A published graph
- * is immutable, exactly like every graph GraphService holds (GraphService.java:118-122).</p>
+ * <p>{@code ProjectGraph} is {@code public final} (ProjectGraph.java:34), so this class does not extend
+ * it: it is a delegate the graph holds. The host edit is confined to ProjectGraph itself -- one field,
+ * one setter and a first line in each of the four read methods (see README.md in this directory):</p>
+ * <pre>
+ *   private GpuProjectGraph gpu;                                   // null until GraphService publishes
+ *   void attachGpu(GpuProjectGraph g) { this.gpu = g; }
+ *   public Set&lt;String&gt; dependencies(String id) { if (gpu != null) return gpu.dependencies(id); ...as before... }
+ * </pre>
+ * <p>Build methods (addNode, addDependency, markAsEntryPoint, metadata) stay the Java maps;
+ * {@link #publish} freezes the graph, uploads it (ProjectGraph.java:160-197 rules are re-applied by
+ * dmg_graph_create) and from then on dependencies / dependents / resolve / analysisOrder and the
+ * identifier scans are single calls into libdmgraph.so. A published graph is immutable, exactly like
+ * every graph GraphService holds (GraphService.java:118-122).</p>
  */
-public final class GpuProjectGraph extends ProjectGraph implements AutoCloseable {
+public final class GpuProjectGraph implements AutoCloseable {
 
     private final MemorySegment handle;          // dmg_graph*
     private final String[] names;                // vertex id -> identifier (nodes order)
     private final Map<String, Integer> index;    // identifier -> vertex id
 
-    private GpuProjectGraph(final ProjectGraph source, final MemorySegment theHandle,
-            final String[] theNames, final Map<String, Integer> theIndex) {
-        super(source);                           // copy constructor: one line to add to ProjectGraph
+    private GpuProjectGraph(final MemorySegment theHandle, final String[] theNames,
+            final Map<String, Integer> theIndex) {
         this.handle = theHandle;
         this.names = theNames;
         this.index = theIndex;
@@ -101,7 +108,7 @@ public final class GpuProjectGraph extends ProjectGraph implements AutoCloseable
             desc.set(java.lang.foreign.ValueLayout.ADDRESS, 72, MemorySegment.NULL);
             final MemorySegment out = arena.allocate(java.lang.foreign.ValueLayout.ADDRESS);
             DmGraphNative.check((int) DmGraphNative.GRAPH_CREATE.invokeExact(engine, desc, out));
-            return new GpuProjectGraph(graph, out.get(java.lang.foreign.ValueLayout.ADDRESS, 0), names, index);
+            return new GpuProjectGraph(out.get(java.lang.foreign.ValueLayout.ADDRESS, 0), names, index);
         } catch (final RuntimeException e) {
             throw e;
         } catch (final Throwable t) {
@@ -110,19 +117,16 @@ public final class GpuProjectGraph extends ProjectGraph implements AutoCloseable
     }
 
     /** ProjectGraph.java:299-305. */
-    @Override
     public Set<String> dependencies(final String identifier) {
         return row(DmGraphNative.OUT, identifier);
     }
 
     /** ProjectGraph.java:316-328 (no scan of every source any more). */
-    @Override
     public Set<String> dependents(final String identifier) {
         return row(DmGraphNative.IN, identifier);
     }
 
     /** ProjectGraph.java:359-378: dmg_neighbors_batch(BOTH, k = 1, exclude_sources = 0). */
-    @Override
     public Set<String> resolve(final String identifier) {
         final Integer v = identifier == null ? null : index.get(identifier);
         if (v == null) {
@@ -154,7 +158,6 @@ public final class GpuProjectGraph extends ProjectGraph implements AutoCloseable
     }
 
     /** ProjectGraph.java:390-421, exact order. */
-    @Override
     public List<String> analysisOrder() {
         if (names.length == 0) {
             return List.of();

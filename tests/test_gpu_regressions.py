@@ -250,3 +250,47 @@ def test_stacktrace_batch_against_the_restatement(engine):
     status, *_ = dg.stacktrace_batch([[(names[3], None), ("nope.X", None)]], 1)
     assert status.tolist() == [pyref.FRAME_FOUND, pyref.FRAME_MISSING]
     dg.release()
+
+
+# ---- decorated rows (dmg_query_batch_meta) -----------------------------------------------------------
+def test_query_batch_meta_decorates_vertex_rows(engine):
+    """vertexDeps / executeClasses attach classType and the entry flag per returned class (GQS:122-130,
+    308-316): the meta column must carry code | 0x80 * isEntryPoint for every vertex id of every row kind,
+    0 for method-catalog indices, and ids / aux must equal the plain call's."""
+    rng = np.random.default_rng(8)
+    n = 500
+    src, dst = rng.integers(0, n, 4000), rng.integers(0, n, 4000)
+    entry = rng.choice(n, 30, replace=False).astype(np.uint32)
+    names = ["a.b.C%d" % i for i in range(n)]
+    off, arena = synth.pack_names(names)
+    g = dmgraph.Graph(engine, n, src, dst, entry, name_off=off, name_bytes=arena)
+    codes = rng.integers(0, 6, n).astype(np.uint8)
+    want_meta = codes | (np.isin(np.arange(n), entry).astype(np.uint8) << 7)
+    meths = [["m%d" % j for j in range(v % 3)] for v in range(n)]
+    g.set_methods(meths)
+    g.set_method_flags([1] * sum(len(m) for m in meths))
+    ops = []
+    for v in rng.integers(0, n, 40):
+        v = int(v)
+        ops += [{"op": dmgraph.OP_DEPENDENCIES, "vertex": v}, {"op": dmgraph.OP_DEPENDENTS, "vertex": v},
+                {"op": dmgraph.OP_OVERVIEW, "vertex": v}, {"op": dmgraph.OP_KHOP, "vertex": v, "mode": 2, "k": 2},
+                {"op": dmgraph.OP_RESOLVE_NAME, "text": ("c%d" % v).encode()},
+                {"op": dmgraph.OP_METHOD, "vertex": v, "text": b"m0"}]
+    ops += [{"op": dmgraph.OP_ENTRYPOINTS}, {"op": dmgraph.OP_ENDPOINTS}]
+    plain = g.query_batch(ops)
+    before = g.query_batch_meta(ops)                       # before set_class_types: entry flag only
+    g.set_class_types(codes)
+    after = g.query_batch_meta(ops)
+    vertex_ops = {dmgraph.OP_DEPENDENCIES, dmgraph.OP_DEPENDENTS, dmgraph.OP_OVERVIEW, dmgraph.OP_KHOP,
+                  dmgraph.OP_RESOLVE_NAME, dmgraph.OP_ENTRYPOINTS}
+    seen_rows = 0
+    for o, (pi, pa), (bi, ba, bm), (ai, aa, am) in zip(ops, plain, before, after):
+        assert (pi, pa) == (bi, ba) == (ai, aa)
+        if o["op"] in vertex_ops:
+            assert am == [int(want_meta[i]) for i in ai]
+            assert bm == [int(want_meta[i]) & 0x80 for i in bi]
+            seen_rows += len(ai) > 0
+        else:
+            assert not any(am) and not any(bm)
+    assert seen_rows > 100
+    g.release()
