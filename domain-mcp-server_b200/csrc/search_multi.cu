@@ -4,9 +4,11 @@
 //   - the batch's distinct patterns are classed by length and keyed by their first 8 / 4 / 3 /
 //     2 / 1 bytes; per class a Bloom-style bitmap in shared memory rejects almost every text
 //     position, a small open-addressing table in L2 maps a surviving key to its patterns;
-//   - one warp owns a contiguous tile of names and walks it name by name; the 32 lanes cover
-//     the name's byte positions (aligned 4-byte loads + funnel shifts give every position its
-//     8-byte window), so the arena is read once, coalesced, whatever the number of queries;
+//   - one warp owns a contiguous tile of names; its 32 lanes take 32 consecutive names, ONE LANE PER
+//     NAME, each sliding a 20-byte window over its own name (aligned 4-byte loads + funnel shifts), so
+//     the arena is read once whatever the number of queries.  A position that passes a filter is only
+//     queued; the warp resolves the queued candidates together afterwards (see scan_candidates /
+//     resolve_candidates below);
 //   - ordered output without a sort: pass 1 counts hits per (tile, pattern); a column scan turns
 //     the counts into per-tile row cursors; pass 2 repeats the match and writes each hit at its
 //     cursor.  Tiles are name ranges in id order and a warp walks its tile in id order, so every

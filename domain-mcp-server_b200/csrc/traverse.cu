@@ -5,9 +5,10 @@
 // (in_ptr/in_idx, rows in ascending source id), project range table part_off.  Queries and
 // results are CSR-shaped (q_off/q_src -> out_off/out_ids/out_hop).
 //
-// Every kernel hands out work items through one atomic ticket and places its output with the
-// decoupled look-back allocator of common.cuh, so results come out packed, in query order and
-// in ONE pass over the graph data.
+// Work items are handed out through an atomic ticket.  Adjacency rows are placed with the decoupled
+// look-back allocator of common.cuh in one pass; k-hop results take three steps -- traverse into a
+// compact per-query form (bit rows, hop-byte staging rows, or cursor-ordered rows), scan the row sizes
+// into out_off, then emit / gather the packed rows in query order.
 #include <algorithm>
 #include <cstdlib>
 #include <atomic>
@@ -856,8 +857,8 @@ __global__ void __launch_bounds__(ADJ_THREADS) adjacency_kernel(const uint32_t* 
   }
 }
 
-// rows longer than ADJ_LONG_ROW: every CTA copies a slice of every such row (16-byte moves where
-// source and destination are co-aligned)
+// rows longer than ADJ_LONG_ROW: every CTA copies a slice of every such row, one 4-byte entry per thread
+// step (coalesced; source and destination offsets differ per row, so wider moves would need a peel)
 __global__ void __launch_bounds__(256) adjacency_long_kernel(const uint32_t* __restrict__ idx,
                                                              const unsigned long long* __restrict__ long_rows,
                                                              const DevCounters* ctr, uint32_t* out_ids,
