@@ -194,6 +194,8 @@ def main():
     ap.add_argument("--c5-vertices", type=int, default=4_000_000)
     ap.add_argument("--c5-edges", type=int, default=100_000_000)
     ap.add_argument("--parity-rows", type=int, default=4096)
+    ap.add_argument("--closure-vertices", type=int, default=4_000_000, help="N>1: partitioned-closure block (0 = skip)")
+    ap.add_argument("--closure-edges", type=int, default=100_000_000)
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     rank = int(os.environ.get("RANK", "0"))
@@ -466,6 +468,20 @@ def main():
                 blocks[name] = {"error": "%s: %s" % (type(ex).__name__, ex)}
             blocks[name]["block_wall_s"] = time.perf_counter() - t0
         line["configs"] = blocks
+    # ---- N > 1: the path's one exchange step, the partitioned closure over all N devices (rank 0 drives
+    # them through dmg_dist_* in ONE process, as the single-JVM host would; the other ranks wait) ----------
+    if world > 1 and args.closure_vertices:
+        barrier()
+        if rank == 0:
+            import bench_configs as bc
+            t0 = time.perf_counter()
+            try:
+                blk = bc.run_dist_closure(world, args.closure_vertices, args.closure_edges)
+            except Exception as ex:
+                blk = {"error": "%s: %s" % (type(ex).__name__, ex)}
+            blk["block_wall_s"] = time.perf_counter() - t0
+            line["closure"] = blk
+        barrier()
     if rank == 0:
         print(json.dumps(line), flush=True)
     eng.close()

@@ -13,6 +13,7 @@
 #include <cstddef>
 
 #include "common.cuh"
+#include "closure_pull.cuh"
 
 namespace dmg {
 
@@ -57,28 +58,13 @@ __global__ void __launch_bounds__(CP_THREADS) part_pull_kernel(const uint32_t* _
   unsigned long long te = 0;
   for (uint32_t w = w_lo + warp; w < w_hi; w += nwarps) {
     uint32_t todo = ~visited[w];
-    uint32_t found = 0;
-    while (todo) {
-      const uint32_t bpos = __ffs(todo) - 1;
-      todo &= todo - 1;
-      const uint32_t v = w * 32 + bpos;
-      if (v < v_lo || v >= v_hi) continue;
-      const uint32_t b = rptr[v], n = rptr[v + 1] - b;
-      for (uint32_t j0 = 0; j0 < n; j0 += 32) {
-        bool hit = false;
-        if (j0 + lane < n) {
-          const uint32_t u = ridx[b + j0 + lane];
-          hit = (frontier[u >> 5] >> (u & 31)) & 1u;
-        }
-        te += min(32u, n - j0);
-        if (__any_sync(FULL, hit)) {
-          found |= 1u << bpos;
-          break;
-        }
-      }
-    }
+    // vertices of the word outside [v_lo, v_hi) belong to a neighbouring rank (ranges start on a multiple
+    // of 32, so only the last word can be shared) or lie beyond V
+    if (w * 32 + 32 > v_hi) todo &= v_hi > w * 32 ? (0xFFFFFFFFu >> (32 - (v_hi - w * 32))) : 0u;
+    const uint32_t found = pull_word<false>(rptr, ridx, frontier, w, todo, v_hi, lane, &te);
     if (lane == 0) next_slice[w - w_lo] = found;
   }
+  te = warp_sum_u64(te);
   if (lane == 0 && te) atomicAdd(&ctr->edges, te);
 }
 

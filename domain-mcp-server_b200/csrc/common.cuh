@@ -77,6 +77,9 @@ enum KernelId : int {
   K_KHOP_WINDOWS,
   K_QUERY_ROWS,
   K_MISC,
+  K_KHOP1_ROWS,
+  K_KHOP_LARGE,
+  K_SEARCH_REPLICATE,
   K_COUNT
 };
 extern const char* const kKernelNames[K_COUNT];
@@ -128,6 +131,15 @@ struct Engine {
   size_t flush_bytes = 0;
   CallCtx* acquire();
   void release(CallCtx* c);
+  // Device blocks handed back by finished dmg_query_batch calls, kept for the next call: a k-hop group's
+  // rows are gigabytes, and a cudaMalloc + cudaFree pair per group and call costs more than the traversal
+  // that fills them.  Bounded by pool_limit bytes (a quarter of the device) and a handful of blocks.
+  std::mutex pool_mu;
+  std::vector<std::pair<void*, size_t>> pool;
+  size_t pool_bytes = 0, pool_limit = 0;
+  void* pool_take(size_t bytes, size_t* got);   // nullptr: device out of memory even after the pool was emptied
+  void pool_give(void* p, size_t bytes);
+  void pool_clear();
 };
 
 struct CtxGuard {

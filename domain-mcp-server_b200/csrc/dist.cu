@@ -6,19 +6,24 @@
 //                ranges, one host thread per device runs its range, rows are concatenated in query
 //                order.  No collective (C2-C4 of SURVEY.md 8e).
 //   partitioned  rank r owns vertices [v_lo, v_hi) and holds the edges with an endpoint there; the
-//                closure of PG:390-421 runs level by level: expand (push / pull kernels of
-//                closure_part.cu) -> ncclAllGather of frontier bitmaps over NVLink -> merge; one 8-byte
-//                read-back per level decides termination (C5 of SURVEY.md 8e).
+//                closure of PG:390-421 runs level by level (C5 of SURVEY.md 8e).  Where the devices can
+//                address each other's memory the whole closure is one persistent kernel per device that
+//                exchanges over NVLink peer memory (closure_p2p.cu); otherwise, or with DMG_DIST_NCCL=1,
+//                a level is expand (push / pull kernels of closure_part.cu) -> ncclAllGather of frontier
+//                bitmaps -> merge, with one 8-byte read-back per level deciding termination.
 // NCCL is bound at run time (dlopen of libnccl.so.2) so that a host which never goes multi-GPU needs no
 // NCCL, and a process that already loaded one (torch) keeps using that copy.  Failures: DMG_ENCCL.
 #include <dlfcn.h>
 #include <nccl.h>
 
 #include <algorithm>
+#include <cstddef>
+#include <cstdlib>
 #include <thread>
 #include <vector>
 
 #include "common.cuh"
+#include "closure_p2p.h"
 
 namespace dmg {
 
@@ -69,7 +74,11 @@ struct DistRank {
            *slice = nullptr, *level = nullptr, *src = nullptr;
   unsigned long long* counters = nullptr;   // [0] edges read, [1] |next|
   size_t src_cap = 0;
+  // peer-memory form: one block holding counts[2][P2P_MAX_RANKS] u64 | flags[P2P_MAX_RANKS] u32 | acc[4] u64 | result
+  unsigned char* p2p = nullptr;
 };
+constexpr size_t P2P_O_COUNTS = 0, P2P_O_FLAGS = 2 * P2P_MAX_RANKS * 8, P2P_O_ACC = P2P_O_FLAGS + 256,
+                 P2P_O_RESULT = P2P_O_ACC + 64, P2P_BLOCK = P2P_O_RESULT + 256;
 
 }  // namespace dmg
 
@@ -79,6 +88,7 @@ struct dmg_dist {
   std::vector<dmg_engine*> engines;
   std::vector<ncclComm_t> comms;            // empty until a partitioned graph needs them
   unsigned long long* h_flag = nullptr;     // pinned: |next| of the level
+  int peer_state = 0;                       // 0 not probed, 1 every pair has peer access, -1 some pair has not
 };
 
 struct dmg_dist_graph {
@@ -93,7 +103,7 @@ using namespace dmg;
 
 static void free_rank(DistRank& r) {
   for (void* p : {(void*)r.frontier, (void*)r.visited, (void*)r.next, (void*)r.contrib, (void*)r.gather, (void*)r.slice,
-                  (void*)r.level, (void*)r.src, (void*)r.counters})
+                  (void*)r.level, (void*)r.src, (void*)r.counters, (void*)r.p2p})
     if (p) cudaFree(p);
   if (r.stream) cudaStreamDestroy(r.stream);
   r = DistRank();
@@ -293,8 +303,40 @@ static int32_t ensure_rank_state(dmg_dist_graph* dg) {
     DMG_CUDA(cudaMalloc((void**)&k.slice, (size_t)dg->wr * 4 + 16));
     DMG_CUDA(cudaMalloc((void**)&k.level, (size_t)dg->wr * 32 * 4 + 16));
     DMG_CUDA(cudaMalloc((void**)&k.counters, 64));
+    DMG_CUDA(cudaMalloc((void**)&k.p2p, P2P_BLOCK));
   }
   return DMG_OK;
+}
+
+// Peer access between every pair of the box's devices (NVSwitch: all pairs), enabled once.
+static bool ensure_peer_access(dmg_dist* d) {
+  if (d->peer_state) return d->peer_state > 0;
+  d->peer_state = -1;
+  if (d->n > P2P_MAX_RANKS) return false;
+  for (int r = 0; r < d->n; ++r)
+    for (int p = 0; p < d->n; ++p) {
+      int can = 0;
+      if (p != r && (cudaDeviceCanAccessPeer(&can, d->devices[r], d->devices[p]) != cudaSuccess || !can)) {
+        cudaGetLastError();
+        return false;
+      }
+    }
+  for (int r = 0; r < d->n; ++r) {
+    if (cudaSetDevice(d->devices[r]) != cudaSuccess) return false;
+    int coop = 0;
+    if (cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, d->devices[r]) != cudaSuccess || !coop) return false;
+    for (int p = 0; p < d->n; ++p) {
+      if (p == r) continue;
+      const cudaError_t e = cudaDeviceEnablePeerAccess(d->devices[p], 0);
+      if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) {
+        cudaGetLastError();
+        return false;
+      }
+      cudaGetLastError();
+    }
+  }
+  d->peer_state = 1;
+  return true;
 }
 
 }  // namespace dmg
@@ -319,7 +361,9 @@ int32_t dmg_dist_closure(dmg_dist_graph* dg, int32_t dir, uint32_t n_src, const 
   }
   dmg_dist* d = dg->dist;
   NcclApi* api = nccl_api();
-  DMG_TRY(ensure_comms(d));
+  const char* force_nccl = getenv("DMG_DIST_NCCL");
+  const bool use_p2p = !(force_nccl && force_nccl[0] == '1') && ensure_peer_access(d);
+  if (!use_p2p) DMG_TRY(ensure_comms(d));
   DMG_TRY(ensure_rank_state(dg));
   const int N = d->n;
   const uint32_t V = dg->V, wr = dg->wr;
@@ -349,60 +393,135 @@ int32_t dmg_dist_closure(dmg_dist_graph* dg, int32_t dir, uint32_t n_src, const 
       DMG_CUDA(cudaMemcpyAsync(k.src, src, (size_t)n_src * 4, cudaMemcpyHostToDevice, k.stream));
       dist_sources_kernel<<<(n_src + 255) / 256, 256, 0, k.stream>>>(k.src, n_src, V, lo, hi, k.frontier, k.visited, k.level);
     }
-    if (r == 0) {
+    if (r == 0 && !use_p2p) {
       dist_popc_kernel<<<d->engines[0]->sm_count * 2, 256, 0, k.stream>>>(k.frontier, (uint32_t)W, k.counters + 1);
       DMG_CUDA(cudaMemcpyAsync(d->h_flag, k.counters + 1, 8, cudaMemcpyDeviceToHost, k.stream));
     }
     DMG_CUDA(cudaGetLastError());
   }
-  DMG_CUDA(cudaSetDevice(d->devices[0]));
-  DMG_CUDA(cudaStreamSynchronize(dg->ranks[0].stream));
-  uint64_t n_front = *d->h_flag, total = n_front;
+  uint64_t total = 0, exchanged = 0;
   uint32_t lvl = 1, push_levels = 0, pull_levels = 0;
-  uint64_t exchanged = 0;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
-  cudaEventCreate(&ev0);
-  cudaEventCreate(&ev1);
-  cudaEventRecord(ev0, dg->ranks[0].stream);
-  // ---- levels: expand -> allgather -> merge, all ranks issued from this thread -------------------------
-  while (n_front > 0) {
-    const bool push = n_front < (uint64_t)V / 32;
+  if (use_p2p) {
+    // ---- one persistent kernel per device, exchange through peer memory (closure_p2p.cu) ----------------
+    P2pArgs base;
+    memset(&base, 0, sizeof(base));
+    base.n = N;
+    base.V = V;
+    base.wr = wr;
+    base.spin_ns = 2000000000ull;   // a peer that is 2 s late for a barrier is not coming
     for (int r = 0; r < N; ++r) {
       DistRank& k = dg->ranks[r];
-      uint32_t lo, hi;
-      range(r, &lo, &hi);
+      base.frontier[r] = k.frontier;
+      base.visited[r] = k.visited;
+      base.next_slice[r] = k.slice;
+      base.counts[r] = reinterpret_cast<unsigned long long*>(k.p2p + P2P_O_COUNTS);
+      base.flags[r] = reinterpret_cast<uint32_t*>(k.p2p + P2P_O_FLAGS);
+    }
+    for (int r = 0; r < N; ++r) {   // every buffer a peer may touch is in its start state before anyone launches
+      DistRank& k = dg->ranks[r];
       DMG_CUDA(cudaSetDevice(d->devices[r]));
-      if (push) DMG_TRY(dmg_closure_push_async(dg->graphs[r], dir, lo, hi, k.frontier, k.contrib, k.counters, k.stream));
-      else DMG_TRY(dmg_closure_pull_async(dg->graphs[r], dir, lo, hi, k.frontier, k.visited, k.slice, k.counters, k.stream));
+      DMG_CUDA(cudaMemsetAsync(k.slice, 0, (size_t)wr * 4, k.stream));
+      DMG_CUDA(cudaMemsetAsync(k.p2p, 0, P2P_BLOCK, k.stream));
     }
-    DMG_NCCL(api->GroupStart());
     for (int r = 0; r < N; ++r) {
-      DistRank& k = dg->ranks[r];
-      if (push) DMG_NCCL(api->AllGather(k.contrib, k.gather, W, ncclUint32, d->comms[r], k.stream));
-      else DMG_NCCL(api->AllGather(k.slice, k.contrib, wr, ncclUint32, d->comms[r], k.stream));
-    }
-    DMG_NCCL(api->GroupEnd());
-    exchanged += push ? W * 4 * N : W * 4;
-    for (int r = 0; r < N; ++r) {
-      DistRank& k = dg->ranks[r];
-      uint32_t lo, hi;
-      range(r, &lo, &hi);
       DMG_CUDA(cudaSetDevice(d->devices[r]));
-      DMG_TRY(dmg_closure_merge_async(dg->graphs[r], lo, hi, lvl, push ? k.gather : k.contrib, push ? N : 1, (uint32_t)W,
-                                      k.visited, k.next, k.level, k.counters + 1, k.stream));
-      std::swap(k.frontier, k.next);
+      DMG_CUDA(cudaStreamSynchronize(dg->ranks[r].stream));
     }
-    // |next| is identical on every rank: rank 0's copy decides; the others run ahead into the next level
     DMG_CUDA(cudaSetDevice(d->devices[0]));
-    DMG_CUDA(cudaMemcpyAsync(d->h_flag, dg->ranks[0].counters + 1, 8, cudaMemcpyDeviceToHost, dg->ranks[0].stream));
+    DMG_CUDA(cudaEventCreate(&ev0));
+    DMG_CUDA(cudaEventCreate(&ev1));
+    DMG_CUDA(cudaEventRecord(ev0, dg->ranks[0].stream));
+    int32_t launch_rc = DMG_OK;
+    for (int r = 0; r < N && launch_rc == DMG_OK; ++r) {
+      DistRank& k = dg->ranks[r];
+      dmg_graph* g = dg->graphs[r];
+      P2pArgs a = base;
+      a.rank = r;
+      a.ptr = dir == DMG_OUT ? g->d_out_ptr : g->d_in_ptr;
+      a.idx = dir == DMG_OUT ? g->d_out_idx : g->d_in_idx;
+      a.rptr = dir == DMG_OUT ? g->d_in_ptr : g->d_out_ptr;
+      a.ridx = dir == DMG_OUT ? g->d_in_idx : g->d_out_idx;
+      a.level = k.level;
+      a.acc = reinterpret_cast<unsigned long long*>(k.p2p + P2P_O_ACC);
+      a.result = reinterpret_cast<P2pResult*>(k.p2p + P2P_O_RESULT);
+      if (cudaSetDevice(d->devices[r]) != cudaSuccess) launch_rc = DMG_ECUDA;
+      else launch_rc = closure_p2p_launch(a, d->engines[r]->sm_count, k.stream);
+    }
+    // (a rank that failed to launch leaves the others waiting at their first barrier until spin_ns runs out)
+    DMG_CUDA(cudaSetDevice(d->devices[0]));
+    DMG_CUDA(cudaEventRecord(ev1, dg->ranks[0].stream));
+    P2pResult res0{};
+    bool timed_out = false;
+    for (int r = 0; r < N; ++r) {
+      DistRank& k = dg->ranks[r];
+      P2pResult res{};
+      DMG_CUDA(cudaSetDevice(d->devices[r]));
+      DMG_CUDA(cudaStreamSynchronize(k.stream));
+      DMG_CUDA(cudaMemcpy(&res, k.p2p + P2P_O_RESULT, sizeof(res), cudaMemcpyDeviceToHost));
+      timed_out |= res.status != 0;
+      exchanged = std::max<uint64_t>(exchanged, res.sent_words * 4);
+      if (r == 0) res0 = res;
+    }
+    DMG_TRY(launch_rc);
+    if (timed_out) {
+      cudaEventDestroy(ev0);
+      cudaEventDestroy(ev1);
+      set_error("dmg_dist_closure: a device did not reach a level barrier within 2 s");
+      return DMG_ECUDA;
+    }
+    total = res0.reached;
+    lvl = res0.levels + 1;
+    push_levels = res0.push_levels;
+    pull_levels = res0.pull_levels;
+  } else {
+    DMG_CUDA(cudaSetDevice(d->devices[0]));
     DMG_CUDA(cudaStreamSynchronize(dg->ranks[0].stream));
-    n_front = *d->h_flag;
-    total += n_front;
-    (push ? push_levels : pull_levels)++;
-    ++lvl;
-    if (lvl > 0x7FFFFFFEu) break;
+    uint64_t n_front = *d->h_flag;
+    total = n_front;
+    cudaEventCreate(&ev0);
+    cudaEventCreate(&ev1);
+    cudaEventRecord(ev0, dg->ranks[0].stream);
+    // ---- levels: expand -> allgather -> merge, all ranks issued from this thread -------------------------
+    while (n_front > 0) {
+      const bool push = n_front < (uint64_t)V / 32;
+      for (int r = 0; r < N; ++r) {
+        DistRank& k = dg->ranks[r];
+        uint32_t lo, hi;
+        range(r, &lo, &hi);
+        DMG_CUDA(cudaSetDevice(d->devices[r]));
+        if (push) DMG_TRY(dmg_closure_push_async(dg->graphs[r], dir, lo, hi, k.frontier, k.contrib, k.counters, k.stream));
+        else DMG_TRY(dmg_closure_pull_async(dg->graphs[r], dir, lo, hi, k.frontier, k.visited, k.slice, k.counters, k.stream));
+      }
+      DMG_NCCL(api->GroupStart());
+      for (int r = 0; r < N; ++r) {
+        DistRank& k = dg->ranks[r];
+        if (push) DMG_NCCL(api->AllGather(k.contrib, k.gather, W, ncclUint32, d->comms[r], k.stream));
+        else DMG_NCCL(api->AllGather(k.slice, k.contrib, wr, ncclUint32, d->comms[r], k.stream));
+      }
+      DMG_NCCL(api->GroupEnd());
+      exchanged += push ? W * 4 * N : W * 4;
+      for (int r = 0; r < N; ++r) {
+        DistRank& k = dg->ranks[r];
+        uint32_t lo, hi;
+        range(r, &lo, &hi);
+        DMG_CUDA(cudaSetDevice(d->devices[r]));
+        DMG_TRY(dmg_closure_merge_async(dg->graphs[r], lo, hi, lvl, push ? k.gather : k.contrib, push ? N : 1, (uint32_t)W,
+                                        k.visited, k.next, k.level, k.counters + 1, k.stream));
+        std::swap(k.frontier, k.next);
+      }
+      // |next| is identical on every rank: rank 0's copy decides; the others run ahead into the next level
+      DMG_CUDA(cudaSetDevice(d->devices[0]));
+      DMG_CUDA(cudaMemcpyAsync(d->h_flag, dg->ranks[0].counters + 1, 8, cudaMemcpyDeviceToHost, dg->ranks[0].stream));
+      DMG_CUDA(cudaStreamSynchronize(dg->ranks[0].stream));
+      n_front = *d->h_flag;
+      total += n_front;
+      (push ? push_levels : pull_levels)++;
+      ++lvl;
+      if (lvl > 0x7FFFFFFEu) break;
+    }
+    cudaEventRecord(ev1, dg->ranks[0].stream);
   }
-  cudaEventRecord(ev1, dg->ranks[0].stream);
   // ---- gather the owners' level slices into the caller's array ------------------------------------------
   unsigned long long edges = 0;
   for (int r = 0; r < N; ++r) {
@@ -416,7 +535,8 @@ int32_t dmg_dist_closure(dmg_dist_graph* dg, int32_t dir, uint32_t n_src, const 
     DistRank& k = dg->ranks[r];
     DMG_CUDA(cudaSetDevice(d->devices[r]));
     unsigned long long e = 0;
-    DMG_CUDA(cudaMemcpyAsync(&e, k.counters, 8, cudaMemcpyDeviceToHost, k.stream));
+    const void* from = use_p2p ? (const void*)(k.p2p + P2P_O_RESULT + offsetof(P2pResult, edges)) : (const void*)k.counters;
+    DMG_CUDA(cudaMemcpyAsync(&e, from, 8, cudaMemcpyDeviceToHost, k.stream));
     DMG_CUDA(cudaStreamSynchronize(k.stream));
     edges += e;
   }
@@ -429,6 +549,7 @@ int32_t dmg_dist_closure(dmg_dist_graph* dg, int32_t dir, uint32_t n_src, const 
     stats->levels = lvl - 1;
     stats->push_levels = push_levels;
     stats->pull_levels = pull_levels;
+    stats->transport = use_p2p ? 1u : 0u;
     stats->edges_read = edges;
     stats->exchanged_bytes_per_rank = exchanged;
     stats->device_ms = ms;

@@ -32,7 +32,7 @@ void publish_stats(const dmg_call_stats& s) { g_last_stats = s; }
 const char* const kKernelNames[K_COUNT] = {
     "khop_small", "khop_global", "khop_emit", "scan_counts", "adjacency_gather", "entry_flags", "closure_init", "closure_topdown",
     "closure_bottomup", "order_degrees", "order_minslot", "order_claim", "order_tail", "search_scan",
-    "search_first", "search_emit", "khop_windows", "query_rows", "misc"};
+    "search_first", "search_emit", "khop_windows", "query_rows", "misc", "khop1_rows", "khop_large", "search_replicate"};
 
 int32_t DevBuf::reserve(size_t bytes) {
   if (bytes <= cap && p) return DMG_OK;
@@ -139,6 +139,64 @@ CallCtx* Engine::acquire() {
 void Engine::release(CallCtx* c) {
   std::lock_guard<std::mutex> lk(mu);
   free_ctx.push_back(c);
+}
+
+void* Engine::pool_take(size_t bytes, size_t* got) {
+  bytes = std::max<size_t>((bytes + 255) & ~size_t(255), 256);
+  {
+    std::lock_guard<std::mutex> lk(pool_mu);
+    size_t best = pool.size();
+    for (size_t i = 0; i < pool.size(); ++i)   // smallest block that is large enough and not wastefully so
+      if (pool[i].second >= bytes && pool[i].second <= 4 * bytes + (1u << 20) &&
+          (best == pool.size() || pool[i].second < pool[best].second))
+        best = i;
+    if (best != pool.size()) {
+      void* p = pool[best].first;
+      *got = pool[best].second;
+      pool_bytes -= pool[best].second;
+      pool.erase(pool.begin() + (long)best);
+      return p;
+    }
+  }
+  void* p = nullptr;
+  if (cudaMalloc(&p, bytes) != cudaSuccess) {
+    cudaGetLastError();
+    pool_clear();   // the kept blocks may be what is in the way
+    if (cudaMalloc(&p, bytes) != cudaSuccess) {
+      cudaGetLastError();
+      return nullptr;
+    }
+  }
+  *got = bytes;
+  return p;
+}
+void Engine::pool_give(void* p, size_t bytes) {
+  if (!p) return;
+  std::vector<void*> drop;
+  {
+    std::lock_guard<std::mutex> lk(pool_mu);
+    if (bytes > pool_limit) {
+      drop.push_back(p);
+    } else {
+      pool.emplace_back(p, bytes);
+      pool_bytes += bytes;
+      while (pool.size() > 12 || pool_bytes > pool_limit) {   // oldest first
+        drop.push_back(pool.front().first);
+        pool_bytes -= pool.front().second;
+        pool.erase(pool.begin());
+      }
+    }
+  }
+  for (void* d : drop) cudaFree(d);
+}
+void Engine::pool_clear() {
+  std::vector<std::pair<void*, size_t>> all;
+  {
+    std::lock_guard<std::mutex> lk(pool_mu);
+    all.swap(pool);
+    pool_bytes = 0;
+  }
+  for (auto& b : all) cudaFree(b.first);
 }
 
 __global__ void flush_kernel(uint4* p, size_t n, uint32_t salt) {
@@ -568,6 +626,7 @@ int32_t dmg_engine_create(const dmg_engine_opts* opts, dmg_engine** out) {
   e->sm_count = prop.multiProcessorCount;
   e->smem_optin = prop.sharedMemPerBlockOptin;
   e->l2_bytes = (size_t)prop.l2CacheSize;
+  e->pool_limit = (size_t)prop.totalGlobalMem / 4;
   if (opts && opts->scratch_bytes) e->scratch_budget = opts->scratch_bytes;
   *out = e;
   return DMG_OK;
@@ -582,6 +641,7 @@ void dmg_engine_destroy(dmg_engine* e) {
     delete c;
   }
   if (e->flush_buf) cudaFree(e->flush_buf);
+  e->pool_clear();
   delete e;
 }
 

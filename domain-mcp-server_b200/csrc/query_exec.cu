@@ -154,18 +154,30 @@ __global__ void __launch_bounds__(256) qx_fill_kernel(const QxRow* __restrict__ 
   }
 }
 
-// device allocation that frees itself on every exit path of the executor
+// device allocation that frees itself on every exit path of the executor; with an engine set, the
+// block comes from and goes back to the engine's pool instead of cudaMalloc / cudaFree
 struct DevMem {
   void* p = nullptr;
-  ~DevMem() {
-    if (p) cudaFree(p);
-  }
+  size_t got = 0;
+  Engine* pool = nullptr;
+  ~DevMem() { reset(); }
   void reset() {
-    if (p) cudaFree(p);
+    if (p) {
+      if (pool) pool->pool_give(p, got);
+      else cudaFree(p);
+    }
     p = nullptr;
   }
   int32_t alloc(size_t bytes) {
     reset();
+    if (pool) {
+      p = pool->pool_take(bytes, &got);
+      if (!p) {
+        set_error("dmg_query_batch: device out of memory (%zu bytes)", bytes);
+        return DMG_ENOMEM;
+      }
+      return DMG_OK;
+    }
     DMG_CUDA(cudaMalloc(&p, std::max<size_t>(bytes, 256)));
     return DMG_OK;
   }
@@ -350,6 +362,7 @@ static int32_t query_batch_impl(dmg_graph* g, uint64_t n_ops, const dmg_query_op
     while (b < khops.size() && !(khops[a].first < khops[b].first) && !(khops[b].first < khops[a].first)) ++b;
     const size_t m = b - a;
     std::unique_ptr<KGroup> kg(new KGroup);
+    kg->q.pool = kg->off.pool = kg->ids.pool = kg->hop.pool = g->eng;
     std::vector<uint32_t> q(2 * m + 1);   // q_off = 0..m, then q_src
     for (size_t j = 0; j <= m; ++j) q[j] = (uint32_t)j;
     for (size_t j = 0; j < m; ++j) q[m + 1 + j] = ops[khops[a + j].second].vertex;
@@ -368,6 +381,7 @@ static int32_t query_batch_impl(dmg_graph* g, uint64_t n_ops, const dmg_query_op
     if (guess) {
       size_t free_b = 0, total_b = 0;
       DMG_CUDA(cudaMemGetInfo(&free_b, &total_b));
+      free_b += g->eng->pool_bytes;   // kept blocks are there to be reused
       guess = std::min<uint64_t>(guess, free_b / 20);   // ids + hops here, the traversal's temporaries, and headroom
       guess = std::min<uint64_t>(guess, 1ull << 30);     // a caller with an "unbounded" capacity does not get 40 GB of guess
     }

@@ -57,8 +57,10 @@ struct SearchArgs {
   const uint8_t* lower;
   uint32_t v_lo, v_hi, per_tile, n_tiles;
   SlotTable t16, t12, t8, t4, t3;   // classes by pattern length: >=16, 12..15, 8..11, 4..7, 3
-  const uint32_t* filt;             // filters of the five classes, concatenated (words)
-  uint32_t filt_words16, filt_words12, filt_words8, filt_words4, filt_words3;
+  const uint32_t* filt;             // filters of the five classes, then the shared 4-byte prefix filter (words)
+  uint32_t filt_words16, filt_words12, filt_words8, filt_words4, filt_words3, filt_wordsP;
+  uint32_t fbitsP, presentP;        // prefix filter: 4-byte prefixes of every pattern of >= 4 bytes
+  unsigned long long lower_size;    // bytes of the arena that may be read (names + zero pad)
   const PatInfo* pat;               // [U]
   PatRow* prow;                     // [U] filled by search_rows_kernel once out_off is known
   const uint32_t* poff;
@@ -81,7 +83,19 @@ struct SearchArgs {
   unsigned long long* step_base;
   uint32_t* step_cnt;
   uint32_t steps_per_tile;
+  uint32_t* tile_flag;              // [n_tiles] 1 = some step of the tile is not in the log (emit re-matches the tile)
 };
+
+// A log entry carries everything the emit pass needs to place the hit without looking at its neighbours:
+// pattern (14 bits: SM_MAX_PATTERNS), name inside the 32-name step (5 bits) and the hit's rank among the
+// tile's hits of that pattern (13 bits: a tile holds at most LOG_MAX_TILE names) -- the value the count
+// pass's own counter returned.
+constexpr uint32_t LOG_U_BITS = 14, LOG_LANE_BITS = 5, LOG_IDX_SHIFT = LOG_U_BITS + LOG_LANE_BITS;
+constexpr uint32_t LOG_MAX_TILE = 1u << (32 - LOG_IDX_SHIFT);
+static_assert(SM_MAX_PATTERNS <= (1u << LOG_U_BITS), "pattern ids must fit the log entry");
+__device__ __forceinline__ uint32_t log_pack(uint32_t idx, uint32_t lane, uint32_t u) {
+  return (idx << LOG_IDX_SHIFT) | (lane << LOG_U_BITS) | u;
+}
 
 // Everything on the per-position path is 32-bit arithmetic (64-bit multiplies cost several
 // instructions each).  A class turns its window words into a table key (64 bits, compared exactly)
@@ -156,11 +170,18 @@ __device__ __forceinline__ unsigned long long low_bytes_mask(uint32_t len) {
   return len >= 8 ? ~0ull : ((1ull << (8 * len)) - 1ull);
 }
 
-// Matching is two phases per warp step of 32 names (lane = name), because the hit path -- slot
-// table probe, pattern record, verification -- diverges hopelessly when it runs inline: ncu on config 3
-// showed 13 of 32 lanes active and 83 % of the warp instructions spent there with one or two lanes on.
-//   scan     every lane walks its own name; a text position that passes a class's filter is only
-//            QUEUED as a candidate (class, position) in the lane's shared-memory queue
+// Matching is two phases per warp step of 32 consecutive names, because the hit path -- slot table
+// probe, pattern record, verification -- diverges hopelessly when it runs inline with the scan:
+//   scan     the warp sweeps the step's CONTIGUOUS byte range (names are packed back to back), 128
+//            bytes per iteration: a lane loads one aligned word (coalesced), gets the next four from its
+//            neighbours by shuffle and tests the four byte positions of its word.  All 32 lanes work
+//            whatever the lengths of the names (one lane per name left half of them idle: ncu counted
+//            16.5 active threads per instruction).  A position first asks ONE shared filter keyed on
+//            its 4 bytes (the 4-byte prefixes of every pattern of >= 4 bytes) and the 3-byte filter,
+//            both in shared memory; only a position that passes goes on to the length classes' own
+//            filters (global memory, L1-resident).  A survivor looks up the name it lies in (bisection
+//            over the step's 33 offsets in shared memory) and is QUEUED as a candidate (class, position)
+//            of that name if the name still has room for the class's shortest pattern there
 //   resolve  the warp flattens the 32 queues and works them off 32 candidates at a time, all lanes
 //            busy: window bytes -> key -> slot table -> chain of pattern records -> verification; a
 //            match is appended to the hit list of the name it belongs to
@@ -168,59 +189,80 @@ __device__ __forceinline__ unsigned long long low_bytes_mask(uint32_t len) {
 constexpr int SM_CANDBUF = 48;                 // queued candidates of one name before the exhaustive fallback
 constexpr uint32_t CAND_POS_BITS = 13;         // candidate = class << 13 | position; longer names: fallback
 
-// phase 1: returns the number of candidates of name i (may exceed SM_CANDBUF: overflow)
-__device__ __forceinline__ uint32_t scan_candidates(const SearchArgs& a, const uint32_t* f16, const uint32_t* f12,
-                                                    const uint32_t* f8, const uint32_t* f4, const uint32_t* f3,
-                                                    unsigned long long s, uint32_t len, uint16_t* cand) {
-  uint32_t nc = 0;
-  auto push = [&](uint32_t cls, uint32_t p) {
-    if (nc < SM_CANDBUF) cand[nc] = (uint16_t)((cls << CAND_POS_BITS) | p);
-    ++nc;
-  };
-  if (len >= (1u << CAND_POS_BITS)) return SM_CANDBUF + 1;
-  const uint8_t* wp = a.lower + (s & ~3ull);   // arena is zero padded: reading past the end is safe
-  uint32_t sh = (uint32_t)(s & 3ull) * 8;
-  uint32_t w0 = __ldg(reinterpret_cast<const uint32_t*>(wp));
-  uint32_t w1 = __ldg(reinterpret_cast<const uint32_t*>(wp + 4));
-  uint32_t w2 = __ldg(reinterpret_cast<const uint32_t*>(wp + 8));
-  uint32_t w3 = __ldg(reinterpret_cast<const uint32_t*>(wp + 12));
-  uint32_t w4 = __ldg(reinterpret_cast<const uint32_t*>(wp + 16));
-  wp += 20;
-  const bool any_long = (a.t16.present | a.t12.present) != 0, any8 = any_long || a.t8.present;
-  for (uint32_t p = 0; p < len; ++p) {
-    const uint32_t r = len - p;
-    const uint32_t lo32 = sh ? __funnelshift_r(w0, w1, sh) : w0;
-    const uint32_t h4 = lo32 * HASH_A;
-    if (any8 && r >= 8) {
-      const uint32_t hi32 = sh ? __funnelshift_r(w1, w2, sh) : w1;
-      const uint32_t h8 = h4 ^ (hi32 * HASH_B);
-      if (any_long && r >= 12) {
-        const uint32_t lo2 = sh ? __funnelshift_r(w2, w3, sh) : w2;
-        const uint32_t h12 = h8 ^ (lo2 * HASH_C);
-        if (a.t16.present && r >= 16) {
-          const uint32_t hi2 = sh ? __funnelshift_r(w3, w4, sh) : w3;
-          if (filter_pass(f16, h12 ^ (hi2 * HASH_D), a.t16.fbits)) push(0, p);
+__device__ __forceinline__ bool filter_pass_ldg(const uint32_t* __restrict__ f, uint32_t raw, uint32_t bits) {
+  const uint32_t fi = hash_filter(raw, bits);
+  if (!((__ldg(&f[fi >> 5]) >> (fi & 31)) & 1u)) return false;
+  const uint32_t fj = hash_filter2(raw, bits);
+  return (__ldg(&f[fj >> 5]) >> (fj & 31)) & 1u;
+}
+
+// phase 1, whole warp.  B0 / B1 = byte range of the step's names; s_start[l] = start of name l relative to
+// B0 (entries past the last name and s_start[32] hold B1 - B0); s_nc[l] = queue length of name l (may run
+// past SM_CANDBUF: overflow; preset beyond it for names that cannot be queued at all).
+__device__ __forceinline__ void scan_step(const SearchArgs& a, const uint32_t* fP, const uint32_t* f3, int lane,
+                                          unsigned long long B0, unsigned long long B1, const uint32_t* s_start,
+                                          uint32_t* s_nc, uint16_t (*cand)[SM_CANDBUF]) {
+  const uint32_t* __restrict__ g16 = a.filt;
+  const uint32_t* __restrict__ g12 = g16 + a.filt_words16;
+  const uint32_t* __restrict__ g8 = g12 + a.filt_words12;
+  const uint32_t* __restrict__ g4 = g8 + a.filt_words8;
+  const unsigned long long c0 = B0 & ~3ull;
+  const uint32_t* __restrict__ wbase = reinterpret_cast<const uint32_t*>(a.lower + c0);
+  const unsigned long long n_words = (a.lower_size - c0) >> 2;   // words that may be read from c0 on
+  const uint32_t span = (uint32_t)(B1 - B0);
+  uint32_t nxt = lane < n_words ? __ldg(wbase + lane) : 0u;
+  unsigned long long wi = 0;
+  for (unsigned long long c = c0; c < B1; c += 128, wi += 32) {
+    const uint32_t w0 = nxt;
+    nxt = wi + 32 + lane < n_words ? __ldg(wbase + wi + 32 + lane) : 0u;
+    // word lane + k of this chunk: lanes that run past the chunk take it from the next chunk's load
+    const uint32_t w1 = __shfl_sync(FULL, lane >= 1 ? w0 : nxt, (lane + 1) & 31);
+    const uint32_t w2 = __shfl_sync(FULL, lane >= 2 ? w0 : nxt, (lane + 2) & 31);
+    const uint32_t w3 = __shfl_sync(FULL, lane >= 3 ? w0 : nxt, (lane + 3) & 31);
+    const uint32_t w4 = __shfl_sync(FULL, lane >= 4 ? w0 : nxt, (lane + 4) & 31);
+    const long long rel0 = (long long)(c + 4ull * lane) - (long long)B0;   // first position of the lane, relative to B0
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const long long rel = rel0 + j;
+      if (rel < 0 || rel >= (long long)span) continue;
+      const uint32_t lo32 = j ? __funnelshift_r(w0, w1, 8 * j) : w0;
+      const uint32_t h4 = lo32 * HASH_A;
+      uint32_t cm = 0;   // classes whose filter the position passes: bit = class
+      if (a.presentP && filter_pass(fP, h4, a.fbitsP)) {
+        const uint32_t hi32 = j ? __funnelshift_r(w1, w2, 8 * j) : w1;
+        const uint32_t h8 = h4 ^ (hi32 * HASH_B);
+        if (a.t4.present && filter_pass_ldg(g4, h4, a.t4.fbits)) cm |= 1u << 3;
+        if (a.t8.present && filter_pass_ldg(g8, h8, a.t8.fbits)) cm |= 1u << 2;
+        if (a.t12.present | a.t16.present) {
+          const uint32_t lo2 = j ? __funnelshift_r(w2, w3, 8 * j) : w2;
+          const uint32_t h12 = h8 ^ (lo2 * HASH_C);
+          if (a.t12.present && filter_pass_ldg(g12, h12, a.t12.fbits)) cm |= 1u << 1;
+          if (a.t16.present) {
+            const uint32_t hi2 = j ? __funnelshift_r(w3, w4, 8 * j) : w3;
+            if (filter_pass_ldg(g16, h12 ^ (hi2 * HASH_D), a.t16.fbits)) cm |= 1u;
+          }
         }
-        if (a.t12.present && filter_pass(f12, h12, a.t12.fbits)) push(1, p);
       }
-      if (a.t8.present && filter_pass(f8, h8, a.t8.fbits)) push(2, p);
-    }
-    if (a.t4.present && r >= 4 && filter_pass(f4, h4, a.t4.fbits)) push(3, p);
-    if (a.t3.present && r >= 3 && filter_pass(f3, (lo32 & 0xFFFFFFu) * HASH_A, a.t3.fbits)) push(4, p);
-    if (a.has2 && r >= 2 && a.tiny2[lo32 & 0xFFFFu]) push(5, p);
-    if (a.has1 && a.tiny1[lo32 & 0xFFu]) push(6, p);
-    sh += 8;
-    if (sh == 32) {
-      sh = 0;
-      w0 = w1;
-      w1 = w2;
-      w2 = w3;
-      w3 = w4;
-      w4 = __ldg(reinterpret_cast<const uint32_t*>(wp));
-      wp += 4;
+      if (a.t3.present && filter_pass(f3, (lo32 & 0xFFFFFFu) * HASH_A, a.t3.fbits)) cm |= 1u << 4;
+      if (a.has2 && a.tiny2[lo32 & 0xFFFFu]) cm |= 1u << 5;
+      if (a.has1 && a.tiny1[lo32 & 0xFFu]) cm |= 1u << 6;
+      if (!cm) continue;
+      const uint32_t r0 = (uint32_t)rel;
+      uint32_t l = 0;   // the name the position lies in
+#pragma unroll
+      for (int st = 16; st > 0; st >>= 1)
+        if (s_start[l + st] <= r0) l += st;
+      const uint32_t pos = r0 - s_start[l], room = s_start[l + 1] - r0;
+      for (; cm; cm &= cm - 1) {
+        const uint32_t cls = __ffs(cm) - 1;
+        const uint32_t shortest = cls == 0 ? 16u : cls == 1 ? 12u : cls == 2 ? 8u : cls == 3 ? 4u : 7u - cls;   // 3, 2, 1
+        if (room < shortest) continue;
+        const uint32_t slot = atomicAdd(&s_nc[l], 1u);
+        if (slot < (uint32_t)SM_CANDBUF) cand[l][slot] = (uint16_t)((cls << CAND_POS_BITS) | pos);
+      }
     }
   }
-  return nc;
+  __syncwarp();
 }
 
 // phase 2, whole warp: `nc` = this lane's candidate count (<= SM_CANDBUF), s / len = this lane's name.
@@ -325,28 +367,34 @@ __device__ __forceinline__ void exhaustive_name(const SearchArgs& a, uint32_t id
 //   MODE 2  first: atomicMin per pattern
 template <int MODE>
 __global__ void __launch_bounds__(SM_THREADS) search_multi_kernel(const SearchArgs a) {
+  // dynamic shared memory: the two filters every position asks (4-byte prefix filter, 3-byte filter), then
+  // the warps' hit lists and candidate queues
   extern __shared__ __align__(16) uint32_t sm_u32[];
-  uint32_t* f16 = sm_u32;
-  uint32_t* f12 = f16 + a.filt_words16;
-  uint32_t* f8 = f12 + a.filt_words12;
-  uint32_t* f4 = f8 + a.filt_words8;
-  uint32_t* f3 = f4 + a.filt_words4;
+  uint32_t* fP = sm_u32;
+  uint32_t* f3 = fP + a.filt_wordsP;
   __shared__ uint32_t s_nh[SM_WARPS][32];
   __shared__ uint32_t s_pref[SM_WARPS][32];
+  __shared__ uint32_t s_start[SM_WARPS][36];
+  __shared__ uint32_t s_nc[SM_WARPS][32];
   const int tid = threadIdx.x, lane = tid & 31, wib = tid >> 5;
-  const uint32_t fw = a.filt_words16 + a.filt_words12 + a.filt_words8 + a.filt_words4 + a.filt_words3;
-  // hit lists and candidate queues of the warps follow the filters in dynamic shared memory
+  const uint32_t fw = a.filt_wordsP + a.filt_words3;
   typedef uint16_t HitLists[32][SM_HITBUF];
   typedef uint16_t CandQueues[32][SM_CANDBUF];
   HitLists* const s_hits = reinterpret_cast<HitLists*>(sm_u32 + ((fw + 3u) & ~3u));
   CandQueues* const s_cand = reinterpret_cast<CandQueues*>(s_hits + SM_WARPS);
-  for (uint32_t i = tid; i < fw; i += SM_THREADS) sm_u32[i] = a.filt[i];
+  {
+    const uint32_t* gP = a.filt + a.filt_words16 + a.filt_words12 + a.filt_words8 + a.filt_words4 + a.filt_words3;
+    const uint32_t* g3 = a.filt + a.filt_words16 + a.filt_words12 + a.filt_words8 + a.filt_words4;
+    for (uint32_t i = tid; i < a.filt_wordsP; i += SM_THREADS) fP[i] = gP[i];
+    for (uint32_t i = tid; i < a.filt_words3; i += SM_THREADS) f3[i] = g3[i];
+  }
   __syncthreads();
 
   const uint32_t tile = blockIdx.x * SM_WARPS + wib;
   if (tile >= a.n_tiles) return;
   const uint32_t n0 = a.v_lo + tile * a.per_tile;
   const uint32_t n1 = min(a.v_hi, n0 + a.per_tile);
+  if (MODE == 1 && !a.tile_flag[tile]) return;   // every step of the tile is in the log: search_emit_log_kernel
   uint32_t* my_cnt = (MODE == 2) ? nullptr : a.cnt + tile;   // element of pattern u: my_cnt[u * n_tiles]
   uint16_t* mine = s_hits[wib][lane];
 
@@ -374,13 +422,13 @@ __global__ void __launch_bounds__(SM_THREADS) search_multi_kernel(const SearchAr
           const uint32_t j = j0 + lane;
           const bool valid = j < logged;
           const uint32_t ent = valid ? a.log[b + j] : 0u;
-          const uint32_t u = ent & 0xFFFFu;
+          const uint32_t u = ent & ((1u << LOG_U_BITS) - 1u);
           const unsigned peers = __match_any_sync(FULL, valid ? u : (0x10000u + lane));
           const int leader = __ffs(peers) - 1;
           uint32_t base = 0;
           if (valid && lane == leader) base = atomicAdd(&my_cnt[(size_t)u * a.n_tiles], (uint32_t)__popc(peers));
           base = __shfl_sync(FULL, base, leader);
-          if (valid) write_rows(u, i0 + (ent >> 16), base + __popc(peers & lanemask_lt()));
+          if (valid) write_rows(u, i0 + ((ent >> LOG_U_BITS) & 31u), base + __popc(peers & lanemask_lt()));
         }
         continue;
       }
@@ -389,12 +437,23 @@ __global__ void __launch_bounds__(SM_THREADS) search_multi_kernel(const SearchAr
     {
       const uint32_t i = i0 + lane;
       unsigned long long s = 0;
-      uint32_t len = 0, nc = 0;
+      uint32_t len = 0;
       if (i < n1) {
         s = a.name_off[i];
         len = (uint32_t)min(a.name_off[i + 1] - s, 0xFFFFFFFFull);
-        nc = scan_candidates(a, f16, f12, f8, f4, f3, s, len, s_cand[wib][lane]);
       }
+      // the step's byte range and the names' starts inside it
+      const uint32_t n_valid = min(32u, n1 - i0);
+      const unsigned long long B0 = __shfl_sync(FULL, s, 0);
+      const unsigned long long B1 = __shfl_sync(FULL, s + len, (int)n_valid - 1);
+      const bool spans = B1 - B0 < (1ull << 31);
+      s_start[wib][lane] = (uint32_t)((i < n1 ? s : B1) - B0);
+      if (lane == 0) s_start[wib][32] = (uint32_t)(B1 - B0);
+      // names too long for a 13-bit position (or a step too long for 32-bit offsets) take the exhaustive path
+      s_nc[wib][lane] = (len >= (1u << CAND_POS_BITS) || !spans) ? (uint32_t)SM_CANDBUF + 1u : 0u;
+      __syncwarp();
+      if (spans) scan_step(a, fP, f3, lane, B0, B1, s_start[wib], s_nc[wib], s_cand[wib]);
+      const uint32_t nc = i < n1 ? s_nc[wib][lane] : 0u;
       const bool cand_overflow = nc > SM_CANDBUF;
       // the empty pattern is contained in every name (CCS:1513: "".contains)
       if (i < n1 && a.empty_plus1) mine[0] = (uint16_t)(a.empty_plus1 - 1);
@@ -408,19 +467,51 @@ __global__ void __launch_bounds__(SM_THREADS) search_multi_kernel(const SearchAr
     s_nh[wib][lane] = nh;
     __syncwarp();
     if (MODE == 0) {
-      // hit log: lists of the 32 names back to back, in lane order
+      // Counters and hit log in one sweep over the 32 lists laid back to back (lane order == name order),
+      // 32 hits per step with every lane busy: hits of one pattern inside a step take consecutive ranks
+      // from ONE add on the (pattern, tile) counter (__match_any_sync), and the rank goes into the log
+      // entry, so the emit pass places a logged hit without any cursor of its own.
       const bool overflow = __any_sync(FULL, nh > SM_HITBUF);
-      const uint32_t inc = warp_incl_scan_u32(nh);
-      const uint32_t tot = __shfl_sync(FULL, inc, 31);
-      unsigned long long b = 0;
-      if (lane == 0 && !overflow && tot) b = atomicAdd(a.log_used, (unsigned long long)tot);
-      b = __shfl_sync(FULL, b, 0);
-      const bool fits = !overflow && b + tot <= a.log_cap;
-      if (fits)
-        for (uint32_t t = 0; t < nh; ++t) a.log[b + (inc - nh) + t] = ((uint32_t)lane << 16) | mine[t];
-      if (lane == 0) {
-        a.step_base[step] = b;
-        a.step_cnt[step] = fits ? tot : 0xFFFFFFFFu;
+      if (!overflow) {
+        const uint32_t inc = warp_incl_scan_u32(nh);
+        const uint32_t tot = __shfl_sync(FULL, inc, 31);
+        s_pref[wib][lane] = inc - nh;
+        unsigned long long b = 0;
+        if (lane == 0 && tot) b = atomicAdd(a.log_used, (unsigned long long)tot);
+        b = __shfl_sync(FULL, b, 0);
+        bool fits = b + tot <= a.log_cap;
+        __syncwarp();
+        for (uint32_t e0 = 0; e0 < tot; e0 += 32) {
+          const uint32_t e = e0 + lane;
+          const bool valid = e < tot;
+          uint32_t owner = 0, u = 0;
+          if (valid) {
+#pragma unroll
+            for (int st = 16; st > 0; st >>= 1)
+              if (s_pref[wib][owner + st] <= e) owner += st;
+            u = s_hits[wib][owner][e - s_pref[wib][owner]];
+          }
+          const unsigned peers = __match_any_sync(FULL, valid ? u : (0x10000u + lane));
+          const int leader = __ffs(peers) - 1;
+          uint32_t base = 0;
+          if (valid && lane == leader) base = atomicAdd(&my_cnt[(size_t)u * a.n_tiles], (uint32_t)__popc(peers));
+          base = __shfl_sync(FULL, base, leader);
+          const uint32_t idx = base + __popc(peers & lanemask_lt());
+          if (__any_sync(FULL, valid && idx >= LOG_MAX_TILE)) fits = false;   // cannot happen while per_tile <= LOG_MAX_TILE
+          if (fits && valid) a.log[b + e] = log_pack(idx, owner, u);
+        }
+        if (lane == 0) {
+          a.step_base[step] = b;
+          a.step_cnt[step] = fits ? tot : 0xFFFFFFFFu;
+          if (!fits) a.tile_flag[tile] = 1;
+        }
+        __syncwarp();
+        continue;
+      }
+      if (lane == 0) {   // a name with more patterns than a list holds: the step is matched again by the emit pass
+        a.step_base[step] = 0;
+        a.step_cnt[step] = 0xFFFFFFFFu;
+        a.tile_flag[tile] = 1;
       }
     }
     // counters / rows / minima, in lane order == name order
@@ -435,6 +526,34 @@ __global__ void __launch_bounds__(SM_THREADS) search_multi_kernel(const SearchAr
       }
     }
     __syncwarp();
+  }
+}
+
+// Emit for tiles whose every step is in the log: a pure stream.  One warp per step; an entry knows its
+// pattern, its name and its rank among the tile's hits of the pattern, so
+//     position = row of the pattern's first query + hits of the pattern in earlier tiles + rank
+// needs no cursor, no atomics and no order between entries.
+__global__ void __launch_bounds__(256) search_emit_log_kernel(const SearchArgs a) {
+  const int lane = threadIdx.x & 31;
+  const size_t warp = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5, n_warps = ((size_t)gridDim.x * blockDim.x) >> 5;
+  const size_t n_steps = (size_t)a.n_tiles * a.steps_per_tile;
+  for (size_t step = warp; step < n_steps; step += n_warps) {
+    const uint32_t tile = (uint32_t)(step / a.steps_per_tile);
+    if (a.tile_flag[tile]) continue;
+    const uint32_t in_tile = (uint32_t)(step - (size_t)tile * a.steps_per_tile);
+    if (in_tile * 32u >= a.per_tile) continue;
+    const uint32_t i0 = a.v_lo + tile * a.per_tile + in_tile * 32u;
+    if (i0 >= a.v_hi) continue;
+    const uint32_t logged = a.step_cnt[step];
+    const unsigned long long b = a.step_base[step];
+    const uint32_t* __restrict__ tcnt = a.cnt + tile;
+    for (uint32_t j = lane; j < logged; j += 32) {
+      const uint32_t ent = __ldg(&a.log[b + j]);
+      const uint32_t u = ent & ((1u << LOG_U_BITS) - 1u);
+      const uint2 raw = __ldg(reinterpret_cast<const uint2*>(a.prow + u));
+      const unsigned long long pos = (((unsigned long long)raw.y << 32) | raw.x) + tcnt[(size_t)u * a.n_tiles] + (ent >> LOG_IDX_SHIFT);
+      if (pos < a.cap) a.out_ids[pos] = i0 + ((ent >> LOG_U_BITS) & 31u);
+    }
   }
 }
 
@@ -518,6 +637,8 @@ struct HostTables {
   std::vector<PatInfo> pat;
   std::vector<uint32_t> filt[5];
   uint32_t fbits[5] = {0, 0, 0, 0, 0};
+  std::vector<uint32_t> filtP;                   // 4-byte prefixes of every pattern of >= 4 bytes
+  uint32_t fbitsP = 12, presentP = 0;
   std::vector<uint32_t> poff;
   std::vector<uint8_t> pbytes;
   std::vector<uint32_t> tiny2, tiny1;
@@ -616,6 +737,25 @@ static void build_tables(uint64_t nq, const uint32_t* q_off, const uint8_t* q_by
       i = j;
     }
   }
+  {
+    // the filter every text position asks first: is there ANY pattern of >= 4 bytes starting with these 4?
+    std::vector<uint32_t> pre;
+    for (int c = 0; c < 4; ++c)
+      for (const KeyedPat& kp : cls[c]) pre.push_back((uint32_t)T.pat[kp.u].pk8);
+    std::sort(pre.begin(), pre.end());
+    pre.erase(std::unique(pre.begin(), pre.end()), pre.end());
+    uint32_t fb = 12;
+    while ((1ull << fb) < 32 * pre.size() && fb < 17u) ++fb;
+    T.fbitsP = fb;
+    T.presentP = !pre.empty();
+    T.filtP.assign((1u << fb) / 32, 0);
+    for (uint32_t k4 : pre) {
+      const uint32_t raw = class_raw(3, k4, 0, 0, 0);
+      const uint32_t fi = hash_filter(raw, fb), fj = hash_filter2(raw, fb);
+      T.filtP[fi >> 5] |= 1u << (fi & 31);
+      T.filtP[fj >> 5] |= 1u << (fj & 31);
+    }
+  }
   // pattern -> queries
   T.uq_off.assign(U + 1, 0);
   for (uint64_t q = 0; q < nq; ++q) ++T.uq_off[T.q2u[q] + 1];
@@ -655,6 +795,7 @@ int32_t run_search_multi(CallCtx* c, dmg_graph* g, int kind, uint32_t v_lo, uint
     sz(T.slot[k].size(), 16);
     sz(T.filt[k].size(), 4);
   }
+  sz(T.filtP.size(), 4);
   sz(U, 16); sz(U, 16); sz(3 * 65536, 4); sz(U + 1, 4); sz(T.pbytes.size(), 1);
   sz(65536, 4); sz(256, 4); sz(U + 1, 4); sz(nq, 4); sz(nq, 4); sz(nq, 4); sz(nq, 4);
   DMG_TRY(c->tmp0.reserve(need));
@@ -676,6 +817,10 @@ int32_t run_search_multi(CallCtx* c, dmg_graph* g, int kind, uint32_t v_lo, uint
   a.filt_words8 = (uint32_t)T.filt[2].size();
   a.filt_words4 = (uint32_t)T.filt[3].size();
   a.filt_words3 = (uint32_t)T.filt[4].size();
+  a.filt_wordsP = (uint32_t)T.filtP.size();
+  a.fbitsP = T.fbitsP;
+  a.presentP = T.presentP;
+  filt_all.insert(filt_all.end(), T.filtP.begin(), T.filtP.end());
   DMG_TRY(put(c, c->tmp0, &used, filt_all, &a.filt));
   DMG_TRY(put(c, c->tmp0, &used, T.pat, &a.pat));
   {
@@ -709,12 +854,13 @@ int32_t run_search_multi(CallCtx* c, dmg_graph* g, int kind, uint32_t v_lo, uint
   a.U = U;
   a.name_off = reinterpret_cast<const unsigned long long*>(g->d_name_off);
   a.lower = g->d_lower;
+  a.lower_size = g->info.name_bytes + 32;
   a.v_lo = v_lo;
   a.v_hi = v_hi;
   c->stats.h2d_bytes += used;
 
   const uint32_t range = v_hi - v_lo;
-  const size_t smem = (((size_t)filt_all.size() + 3) & ~size_t(3)) * 4 +
+  const size_t smem = (((size_t)a.filt_wordsP + a.filt_words3 + 3) & ~size_t(3)) * 4 +
                       (size_t)SM_WARPS * 32 * (SM_HITBUF + SM_CANDBUF) * sizeof(uint16_t);
   {
     DMG_CUDA(cudaFuncSetAttribute(search_multi_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -729,6 +875,11 @@ int32_t run_search_multi(CallCtx* c, dmg_graph* g, int kind, uint32_t v_lo, uint
   if (kind == DMG_SEARCH_CONTAINS_ALL)
     tiles = std::min<uint64_t>(tiles, std::max<uint64_t>(1, (1ull << 30) / (4ull * std::max<uint32_t>(U, 1))));
   tiles = std::max<uint64_t>(tiles, 1);
+  // a log entry has 13 bits for a hit's rank inside its tile (the matrix budget above wins on a huge range:
+  // such tiles then simply fall back to the matching emit pass)
+  if (kind == DMG_SEARCH_CONTAINS_ALL)
+    tiles = std::max<uint64_t>(tiles, std::min<uint64_t>(((uint64_t)range + LOG_MAX_TILE - 1) / LOG_MAX_TILE,
+                                                         std::max<uint64_t>(1, (1ull << 30) / (4ull * std::max<uint32_t>(U, 1)))));
   a.n_tiles = (uint32_t)tiles;
   a.per_tile = (uint32_t)((range + tiles - 1) / tiles);
   a.steps_per_tile = (a.per_tile + 31) / 32;
@@ -736,9 +887,11 @@ int32_t run_search_multi(CallCtx* c, dmg_graph* g, int kind, uint32_t v_lo, uint
     // hit log of the count pass: the emit pass streams it instead of matching again.  Sized for 32
     // hits per name; steps that do not fit are simply matched again by the emit pass.
     const size_t n_steps = (size_t)tiles * std::max<uint32_t>(a.steps_per_tile, 1);
-    DMG_TRY(c->tmp3.reserve(n_steps * 12 + 64));
+    DMG_TRY(c->tmp3.reserve(n_steps * 12 + 64 + (size_t)tiles * 4));
     a.step_base = c->tmp3.as<unsigned long long>();
     a.step_cnt = reinterpret_cast<uint32_t*>(a.step_base + n_steps);
+    a.tile_flag = a.step_cnt + ((n_steps + 3) & ~size_t(3));
+    DMG_CUDA(cudaMemsetAsync(a.tile_flag, 0, (size_t)tiles * 4, c->stream));
     a.log_used = &c->d_counters->aux[3];
     a.log_cap = 0;
     if (kind == DMG_SEARCH_CONTAINS_ALL && !sizes_only) {
@@ -806,11 +959,14 @@ int32_t run_search_multi(CallCtx* c, dmg_graph* g, int kind, uint32_t v_lo, uint
       a.out_ids = c->out_ids.as<uint32_t>();
       search_rows_kernel<<<(U + 255) / 256, 256, 0, c->stream>>>(a.uq_off, a.uq, a.out_off, U, a.prow);
       {
-        LaunchScope ls(c, K_SEARCH_EMIT);
+        // logged tiles stream out of the log; tiles with a step that is not in it (a name with more patterns
+        // than a list holds, log full) are matched again -- that kernel leaves at once for the others
+        LaunchScope ls(c, K_SEARCH_EMIT, true, 2);
+        search_emit_log_kernel<<<(unsigned)e->sm_count * 8, 256, 0, c->stream>>>(a);
         search_multi_kernel<1><<<blocks, SM_THREADS, smem, c->stream>>>(a);
       }
       if (n_dup) {
-        LaunchScope ls(c, K_SEARCH_EMIT);
+        LaunchScope ls(c, K_SEARCH_REPLICATE);
         search_replicate_kernel<<<dim3(n_dup, 32), 256, 0, c->stream>>>(d_dup_q, d_dup_first, a.out_off, a.out_ids, dev_cap);
       }
     }

@@ -494,7 +494,8 @@ constexpr int KG_BUCKETS = 1024;
 constexpr uint32_t KG_BUCKET_MAX = 48;   // longest bucket a single thread insertion-sorts
 
 __global__ void __launch_bounds__(KG_THREADS) khop_global_kernel(const KhopArgs a, uint32_t* sc_seen, uint32_t* sc_rank,
-                                                                 uint32_t* sc_queue, size_t seen_words, size_t qcap) {
+                                                                 uint32_t* sc_queue, size_t seen_words, size_t qcap,
+                                                                 const uint32_t* qlist, const uint32_t* qlist_n) {
   constexpr int THREADS = KG_THREADS, NW = THREADS / 32;
   extern __shared__ __align__(16) unsigned char kg_smem[];
   uint32_t* s_ids = reinterpret_cast<uint32_t*>(kg_smem);                    // [KG_SORT_CAP]
@@ -513,12 +514,15 @@ __global__ void __launch_bounds__(KG_THREADS) khop_global_kernel(const KhopArgs 
   const uint32_t* __restrict__ fptr = a.mode == DMG_BOTH ? a.und_ptr : (a.mode == DMG_OUT ? a.out_ptr : a.in_ptr);
   const uint32_t* __restrict__ fidx = a.mode == DMG_BOTH ? a.und_idx : (a.mode == DMG_OUT ? a.out_idx : a.in_idx);
   unsigned long long te = 0, rows = 0;
+  // list mode (the k = 1 queries khop1_warp_kernel handed on): tickets index the list
+  const unsigned long long n_run = qlist ? (unsigned long long)*qlist_n : a.nq;
 
   while (true) {
     if (tid == 0) s_q = atomicAdd(&a.ctr->ticket, 1ull);
     __syncthreads();
-    const unsigned long long q = s_q;
-    if (q >= a.nq) break;
+    const unsigned long long ticket = s_q;
+    if (ticket >= n_run) break;
+    const unsigned long long q = qlist ? qlist[ticket] : ticket;
     const uint32_t qb = a.q_off[q], qe = a.q_off[q + 1];
     if (tid == 0) {
       uint32_t lo, hi;
@@ -778,6 +782,10 @@ __global__ void __launch_bounds__(256) khop_gather_kernel(unsigned long long nq,
     }
   }
 }
+
+}  // namespace dmg
+#include "khop_large.cuh"
+namespace dmg {
 
 // ---------------------------------------------------------------------------------------------
 // adjacency_gather: rows of one CSR for a batch of ids (T0 dependencies / T1 dependents).
@@ -1160,24 +1168,55 @@ int32_t run_khop(CallCtx* c, dmg_graph* g, int mode, int k, int exclude, uint64_
       }
     }
   } else {
+    // Projects beyond the shared-memory classes.  k = 1 rows are unions of adjacency rows: one warp per
+    // query (khop1_warp_kernel), which hands hub rows / long source lists on to a CTA kernel.  That CTA
+    // kernel is khop_large_kernel while a project's claim bitmap fits one SM's shared memory, else
+    // khop_global_kernel with its bitmap in global memory.
     const size_t seen_words = (((size_t)maxp + 31) / 32 + 3) & ~size_t(3);
     const size_t qcap = 2 * (size_t)maxp;
-    const size_t per_block = 2 * seen_words * 4 + qcap * 4;   // claim bitmap, rank words, queue
+    const size_t kl_smem = large_kernel_smem(maxp);
+    const bool no_large = getenv("DMG_NO_KHOP_LARGE") != nullptr;   // differential tests: khop_global_kernel instead
+    // khop_large_kernel runs one query per SM; it pays off when a query has work for 1024 threads.  Short
+    // traversals (expected entries ~ degree^k below a few thousand) are chains of dependent steps: more,
+    // smaller CTAs in flight (khop_global_kernel) finish such a batch sooner (config 4, k = 2: 1.2 vs 2.5 ms).
+    const double deg = (double)g->info.n_edges * (mode == DMG_BOTH ? 2.0 : 1.0) / std::max<uint32_t>(g->info.n_vertices, 1);
+    double expect = 1.0;
+    for (int i = 0; i < k && expect < 1e9; ++i) expect *= std::max(deg, 1.0);
+    const char* force_large = getenv("DMG_FORCE_KHOP_LARGE");   // differential tests
+    const bool use_large = !no_large && kl_smem + 12 * 1024 <= e->smem_optin && (k == 1 || expect >= 4096.0 || force_large);
+    const size_t per_block = use_large ? qcap * 4 : 2 * seen_words * 4 + qcap * 4;   // (claim bitmap, rank words,) queue
     int occ = 0;
     const size_t kg_smem = (size_t)KG_SORT_CAP * 5 + (2 * (size_t)KG_BUCKETS + 8) * 4;
-    DMG_CUDA(cudaFuncSetAttribute(khop_global_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kg_smem));
-    DMG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, khop_global_kernel, KG_THREADS, kg_smem));
-    uint64_t grid = std::min<uint64_t>(nq, (uint64_t)e->sm_count * std::max(occ, 1));
-    // every CTA hits its claim bitmap and rank words at random: keep those of all resident CTAs
-    // inside ~3/4 of L2 (1M-vertex project on B200: 372 CTAs run 7.1 ms where 888 run 11 ms)
-    const uint64_t l2_fit = (uint64_t)e->l2_bytes * 3 / 4 / (2 * seen_words * 4);
-    grid = std::min<uint64_t>(grid, std::max<uint64_t>(l2_fit, (uint64_t)e->sm_count));
+    uint64_t grid;
+    if (use_large) {
+      DMG_CUDA(cudaFuncSetAttribute(khop_large_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kl_smem));
+      DMG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, khop_large_kernel, KL_THREADS, kl_smem));
+      grid = std::min<uint64_t>(nq, (uint64_t)e->sm_count * std::max(occ, 1));
+    } else {
+      DMG_CUDA(cudaFuncSetAttribute(khop_global_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kg_smem));
+      DMG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, khop_global_kernel, KG_THREADS, kg_smem));
+      grid = std::min<uint64_t>(nq, (uint64_t)e->sm_count * std::max(occ, 1));
+      // every CTA hits its claim bitmap and rank words at random: keep those of all resident CTAs
+      // inside ~3/4 of L2 (1M-vertex project on B200: 372 CTAs run 7.1 ms where 888 run 11 ms)
+      const uint64_t l2_fit = (uint64_t)e->l2_bytes * 3 / 4 / (2 * seen_words * 4);
+      grid = std::min<uint64_t>(grid, std::max<uint64_t>(l2_fit, (uint64_t)e->sm_count));
+    }
     grid = std::max<uint64_t>(1, std::min<uint64_t>(grid, e->scratch_budget / per_block));
-    DMG_TRY(c->scratch.reserve(grid * per_block));
-    uint32_t* sc_seen = c->scratch.as<uint32_t>();
-    uint32_t* sc_rank = sc_seen + grid * seen_words;
-    uint32_t* sc_queue = sc_rank + grid * seen_words;
-    DMG_CUDA(cudaMemsetAsync(sc_seen, 0, grid * seen_words * 4, c->stream));
+    const size_t defer_bytes = k == 1 ? ((nq * 4 + 255) & ~size_t(255)) + 256 : 0;
+    DMG_TRY(c->scratch.reserve(grid * per_block + defer_bytes));
+    uint32_t *sc_seen = nullptr, *sc_rank = nullptr, *sc_queue = c->scratch.as<uint32_t>();
+    if (!use_large) {
+      sc_seen = c->scratch.as<uint32_t>();
+      sc_rank = sc_seen + grid * seen_words;
+      sc_queue = sc_rank + grid * seen_words;
+      DMG_CUDA(cudaMemsetAsync(sc_seen, 0, grid * seen_words * 4, c->stream));
+    }
+    uint32_t *d_defer = nullptr, *d_ndefer = nullptr;
+    if (k == 1) {
+      d_ndefer = reinterpret_cast<uint32_t*>(c->scratch.as<unsigned char>() + grid * per_block);
+      d_defer = d_ndefer + 64;
+      DMG_CUDA(cudaMemsetAsync(d_ndefer, 0, 4, c->stream));
+    }
     // rows are first written in cursor order into temporaries of the caller's capacity
     DMG_TRY(c->tmp0.reserve(nq * 4));
     DMG_TRY(c->tmp1.reserve(nq * 8));
@@ -1187,10 +1226,19 @@ int32_t run_khop(CallCtx* c, dmg_graph* g, int mode, int k, int exclude, uint64_
     a.tmp_start = c->tmp1.as<unsigned long long>();
     a.tmp_ids = c->tmp2.as<uint32_t>();
     a.tmp_hop = c->tmp3.as<uint8_t>();
+    if (k == 1) {
+      LaunchScope ls(c, K_KHOP1_ROWS);
+      const uint64_t blocks = std::min<uint64_t>((nq + K1_WARPS - 1) / K1_WARPS, (uint64_t)e->sm_count * 8);
+      khop1_warp_kernel<<<(unsigned)std::max<uint64_t>(blocks, 1), K1_THREADS, 0, c->stream>>>(a, d_defer, d_ndefer);
+    }
     {
-      LaunchScope ls(c, K_KHOP_GLOBAL);
-      khop_global_kernel<<<(unsigned)grid, KG_THREADS, kg_smem, c->stream>>>(a, sc_seen, sc_rank, sc_queue, seen_words,
-                                                                           qcap);
+      LaunchScope ls(c, use_large ? K_KHOP_LARGE : K_KHOP_GLOBAL);
+      if (use_large)
+        khop_large_kernel<<<(unsigned)grid, KL_THREADS, kl_smem, c->stream>>>(a, sc_queue, qcap, (uint32_t)(kl_smem / 5),
+                                                                           d_defer, d_ndefer);
+      else
+        khop_global_kernel<<<(unsigned)grid, KG_THREADS, kg_smem, c->stream>>>(a, sc_seen, sc_rank, sc_queue, seen_words,
+                                                                             qcap, d_defer, d_ndefer);
     }
     {
       LaunchScope ls(c, K_SCAN_COUNTS);

@@ -61,7 +61,7 @@ class CallStats(C.Structure):
 
 class DistClosureStats(C.Structure):
     _fields_ = [("levels", C.c_uint32), ("push_levels", C.c_uint32), ("pull_levels", C.c_uint32),
-                ("reserved", C.c_uint32), ("edges_read", C.c_uint64), ("exchanged_bytes_per_rank", C.c_uint64),
+                ("transport", C.c_uint32), ("edges_read", C.c_uint64), ("exchanged_bytes_per_rank", C.c_uint64),
                 ("device_ms", C.c_float), ("reserved2", C.c_float)]
 
 

@@ -417,17 +417,24 @@ int32_t dmg_graph_set_method_flags(dmg_graph* g, const uint8_t* flags);
  *                      in query order exactly as from dmg_neighbors_batch.  No collective.
  *   partitioned graph  (partitioned = 1) rank r owns a vertex range (multiples of 32) and the edges with
  *                      an endpoint in it; dmg_dist_closure runs the BFS of analysisOrder (PG:390-421) level
- *                      by level with an ncclAllGather of frontier bitmaps per level (communicators are
- *                      created in-process on first use; NCCL is bound with dlopen).  out_level[v] = hop
+ *                      by level.  Transport 1 (devices with peer access to each other, the NVSwitch case):
+ *                      one persistent kernel per device for the whole closure; sparse levels send one
+ *                      4-byte remote reduction per newly met vertex into the owner's slice, owners store
+ *                      the changed frontier / visited words into every replica, two flag barriers per level
+ *                      in peer memory, no host round trip.  Transport 0 (no peer access, or DMG_DIST_NCCL=1
+ *                      in the environment): an ncclAllGather of frontier bitmaps per level (communicators
+ *                      are created in-process on first use; NCCL is bound with dlopen).  out_level[v] = hop
  *                      distance, DMG_LEVEL_UNREACHED if not reached -- identical to dmg_closure.
- * NCCL missing or failing: DMG_ENCCL with the NCCL error text in dmg_last_error().                      */
+ * NCCL missing or failing: DMG_ENCCL with the NCCL error text in dmg_last_error().  A device that does not
+ * reach a level barrier of transport 1 within 2 s ends the call with DMG_ECUDA instead of hanging.       */
 typedef struct dmg_dist dmg_dist;
 typedef struct dmg_dist_graph dmg_dist_graph;
 typedef struct dmg_dist_closure_stats {
-  uint32_t levels, push_levels, pull_levels, reserved;
+  uint32_t levels, push_levels, pull_levels;
+  uint32_t transport;                 /* 0 = NCCL allgather per level, 1 = persistent kernel over peer memory */
   uint64_t edges_read;                /* adjacency entries loaded, all ranks */
-  uint64_t exchanged_bytes_per_rank;  /* received through the allgathers */
-  float device_ms;                    /* CUDA events on rank 0's stream around the level loop */
+  uint64_t exchanged_bytes_per_rank;  /* transport 0: received through the allgathers; 1: largest sender's bytes */
+  float device_ms;                    /* CUDA events on rank 0's stream around the level loop / its kernel */
   float reserved2;
 } dmg_dist_closure_stats;
 int32_t dmg_dist_create(const int32_t* devices, int32_t n, dmg_dist** out);

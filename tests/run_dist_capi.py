@@ -2,7 +2,9 @@
 """Multi-GPU through the C ABI alone (dmg_dist_*: one process, N devices, NCCL bound by the library):
 run on a box with >= N GPUs, e.g.  gpurun --gpus 2 -- python tests/run_dist_capi.py --gpus 2
 Checks, against the oracle: (1) a config-2-shaped query batch sharded over N replicas, (2) the
-vertex-partitioned closure with per-level NCCL allgather.  One JSON line."""
+vertex-partitioned closure in both transports -- the persistent peer-memory kernel (default where the
+devices have peer access) and the per-level NCCL allgather (DMG_DIST_NCCL=1) -- on the config-5-shaped
+graph and on a sparse, deep one that stays on push levels.  One JSON line."""
 import argparse
 import json
 import os
@@ -54,19 +56,52 @@ gen_s = time.perf_counter() - t0
 t0 = time.perf_counter()
 pg = dmgraph.DistGraph(dist, big.n_vertices, big.src, big.dst, big.entry, partitioned=True)
 upload_s = time.perf_counter() - t0
-lvl, reached, st = pg.closure(dmgraph.OUT, big.entry)
 o = ora.CsrOracle(big.n_vertices, big.src, big.dst, big.entry)
 wlvl, wreached, wte = o.closure(0, big.entry)
-assert reached == wreached and np.array_equal(lvl, wlvl)
-best = None
-for _ in range(args.steps):
-    _l, _r, s = pg.closure(dmgraph.OUT, big.entry)
-    if best is None or s["device_ms"] < best["device_ms"]:
-        best = s
-out["partitioned_closure"] = {"vertices": big.n_vertices, "edges_drawn": big.n_edges, "reached": int(reached),
-                              "checked_against": "oracle", "matches": True, "generate_s": gen_s, "upload_s": upload_s,
-                              "definitional_edges": int(wte), **best,
-                              "gteps_definitional": wte / (best["device_ms"] * 1e-3) / 1e9}
+out["partitioned_closure"] = {"vertices": big.n_vertices, "edges_drawn": big.n_edges, "reached": int(wreached),
+                              "checked_against": "oracle", "generate_s": gen_s, "upload_s": upload_s,
+                              "definitional_edges": int(wte)}
+for name, env in (("peer_memory", None), ("nccl_allgather", "1")):
+    if env:
+        os.environ["DMG_DIST_NCCL"] = env
+    else:
+        os.environ.pop("DMG_DIST_NCCL", None)
+    lvl, reached, st = pg.closure(dmgraph.OUT, big.entry)
+    assert reached == wreached and np.array_equal(lvl, wlvl), name
+    best = None
+    for _ in range(args.steps):
+        _l, _r, s = pg.closure(dmgraph.OUT, big.entry)
+        assert _r == wreached
+        if best is None or s["device_ms"] < best["device_ms"]:
+            best = s
+    assert np.array_equal(_l, wlvl), name + " (repeat)"
+    out["partitioned_closure"][name] = {"matches": True, **best,
+                                        "gteps_definitional": wte / (best["device_ms"] * 1e-3) / 1e9}
+os.environ.pop("DMG_DIST_NCCL", None)
 pg.release()
+
+# (3) a sparse graph (average degree 3) from few sources, both directions: many push levels, vertex counts that
+# do not divide by 32 * N, sources in one rank's range only
+rng = np.random.Generator(np.random.PCG64(77))
+Vs = 1_000_003
+ss = rng.integers(0, Vs, 3 * Vs).astype(np.uint32)
+dd = rng.integers(0, Vs, 3 * Vs).astype(np.uint32)
+srcs = rng.integers(0, 5000, 7).astype(np.uint32)
+sp = dmgraph.DistGraph(dist, Vs, ss, dd, srcs, partitioned=True)
+o = ora.CsrOracle(Vs, ss, dd, srcs)
+out["sparse_closure"] = {"vertices": Vs, "edges_drawn": int(ss.size), "checked_against": "oracle"}
+for direction, dname in ((dmgraph.OUT, "out"), (dmgraph.IN, "in")):
+    wlvl, wreached, _ = o.closure(direction, srcs)
+    for name, env in (("peer_memory", None), ("nccl_allgather", "1")):
+        if env:
+            os.environ["DMG_DIST_NCCL"] = env
+        else:
+            os.environ.pop("DMG_DIST_NCCL", None)
+        for _ in range(2):
+            lvl, reached, st = sp.closure(direction, srcs)
+            assert reached == wreached and np.array_equal(lvl, wlvl), (dname, name)
+        out["sparse_closure"][dname + "_" + name] = {"matches": True, "reached": int(reached), **st}
+os.environ.pop("DMG_DIST_NCCL", None)
+sp.release()
 dist.close()
 print(json.dumps(out), flush=True)

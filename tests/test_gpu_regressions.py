@@ -35,11 +35,20 @@ def test_khop_global_last_vertices_of_project(engine, n):
     o = ora.CsrOracle(n, src, dst, entry)
     qs = np.concatenate([hubs, tail, rng.integers(0, n, 64)]).astype(np.uint32)
     q_off = np.arange(qs.size + 1, dtype=np.uint32)
-    for mode, k, excl in [(0, 1, 0), (1, 1, 0), (2, 1, 1), (0, 2, 0), (2, 2, 1), (2, 3, 0)]:
-        off, ids, hop = g.neighbors_batch(mode, k, excl, q_off, qs)
-        woff, wids, whop, _ = o.khop_batch(mode, k, excl, q_off, qs, threads=8)
-        assert np.array_equal(off, woff) and np.array_equal(ids, wids) and np.array_equal(hop, whop)
-        assert (ids == n - 1).any()
+    import os
+    # the kernel this case is about runs only where it is forced (projects this small otherwise take
+    # khop1_warp_kernel / khop_large_kernel); both routes have to give the oracle's rows
+    for force_global in (True, False):
+        if force_global:
+            os.environ["DMG_NO_KHOP_LARGE"] = "1"
+        try:
+            for mode, k, excl in [(0, 1, 0), (1, 1, 0), (2, 1, 1), (0, 2, 0), (2, 2, 1), (2, 3, 0)]:
+                off, ids, hop = g.neighbors_batch(mode, k, excl, q_off, qs)
+                woff, wids, whop, _ = o.khop_batch(mode, k, excl, q_off, qs, threads=8)
+                assert np.array_equal(off, woff) and np.array_equal(ids, wids) and np.array_equal(hop, whop)
+                assert (ids == n - 1).any()
+        finally:
+            os.environ.pop("DMG_NO_KHOP_LARGE", None)
     g.release()
 
 
