@@ -14,6 +14,7 @@
 
 #include "common.cuh"
 #include "closure_pull.cuh"
+#include "closure_p2p.h"
 
 namespace dmg {
 
@@ -94,19 +95,27 @@ __global__ void __launch_bounds__(CP_THREADS) part_merge_kernel(const uint32_t* 
   if ((threadIdx.x & 31) == 0 && c) atomicAdd(&ctr->total, (unsigned long long)c);
 }
 
-// sum of the row lengths of the frontier's vertices (the TE figure of a pull level)
-__global__ void __launch_bounds__(CP_THREADS) frontier_degree_kernel(const uint32_t* __restrict__ ptr, uint32_t words,
-                                                                     uint32_t V, const uint32_t* __restrict__ frontier,
-                                                                     DevCounters* ctr) {
-  const uint32_t w = blockIdx.x * blockDim.x + threadIdx.x;
+// depth 0, frontier 0 and visited from the source list (unknown ids are ignored, PG:194-196)
+__global__ void closure_sources_kernel(const uint32_t* __restrict__ src, uint32_t ns, uint32_t V, uint32_t* frontier,
+                                       uint32_t* visited, uint32_t* level) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= ns) return;
+  const uint32_t v = src[i];
+  if (v >= V) return;
+  atomicOr(&frontier[v >> 5], 1u << (v & 31));
+  atomicOr(&visited[v >> 5], 1u << (v & 31));
+  level[v] = 0;
+}
+
+// rows and adjacency entries of the traversal as PG:390-421 defines them: every reached vertex is
+// polled once and its whole row is looked at (the figures the closure reports beside what it READ)
+__global__ void __launch_bounds__(CP_THREADS) reached_degree_kernel(const uint32_t* __restrict__ ptr, uint32_t V,
+                                                                    const uint32_t* __restrict__ level, DevCounters* ctr) {
   unsigned long long te = 0, rows = 0;
-  if (w < words)
-    for (uint32_t b = frontier[w]; b; b &= b - 1) {
-      const uint32_t v = w * 32 + (__ffs(b) - 1);
-      if (v < V) {
-        te += ptr[v + 1] - ptr[v];
-        ++rows;
-      }
+  for (uint32_t v = blockIdx.x * blockDim.x + threadIdx.x; v < V; v += gridDim.x * blockDim.x)
+    if (level[v] != 0xFFFFFFFFu) {
+      te += ptr[v + 1] - ptr[v];
+      ++rows;
     }
   te = warp_sum_u64(te);
   rows = warp_sum_u64(rows);
@@ -116,72 +125,68 @@ __global__ void __launch_bounds__(CP_THREADS) frontier_degree_kernel(const uint3
   }
 }
 
-__global__ void source_bits_kernel(const uint32_t* __restrict__ src, uint32_t ns, uint32_t V, uint32_t* bits) {
-  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < ns && src[i] < V) atomicOr(&bits[src[i] >> 5], 1u << (src[i] & 31));
-}
-
-// Direction-optimising closure on one GPU over bitmaps: the same push / pull / merge kernels as
-// the partitioned closure with the whole vertex range owned here.  Leaves levels in `level`.
+// Direction-optimising closure on one GPU over bitmaps: the persistent kernel of the partitioned closure
+// (closure_p2p.cu) with ONE rank that owns every word -- the whole closure is one cooperative launch, its
+// levels meet at grid barriers, nothing returns to the host in between.  Leaves depths in `level`.
 int32_t closure_hybrid(CallCtx* c, dmg_graph* g, int dir, uint32_t n_src, const uint32_t* d_src, uint32_t* level,
                        uint64_t* reached, uint64_t* te_out, uint64_t* read_out, uint64_t* rows_out) {
   const uint32_t V = g->info.n_vertices, words = (V + 31) / 32;
   DMG_TRY(c->tmp1.reserve((size_t)words * 4 * 4 + 64));
+  DMG_TRY(c->tmp2.reserve(P2P_BLOCK));
   uint32_t* frontier = c->tmp1.as<uint32_t>();
   uint32_t* visited = frontier + words;
   uint32_t* next = visited + words;
-  uint32_t* contrib = next + words;
+  uint32_t* slice = next + words;
+  unsigned char* blk = c->tmp2.as<unsigned char>();
   DMG_CUDA(cudaMemsetAsync(frontier, 0, (size_t)words * 16, c->stream));
+  DMG_CUDA(cudaMemsetAsync(blk, 0, P2P_BLOCK, c->stream));
   DMG_CUDA(cudaMemsetAsync(level, 0xFF, (size_t)V * 4, c->stream));
-  const uint32_t* ptr = dir == DMG_OUT ? g->d_out_ptr : g->d_in_ptr;
-  const uint32_t* idx = dir == DMG_OUT ? g->d_out_idx : g->d_in_idx;
-  const uint32_t* rptr = dir == DMG_OUT ? g->d_in_ptr : g->d_out_ptr;
-  const uint32_t* ridx = dir == DMG_OUT ? g->d_in_idx : g->d_out_idx;
-  const unsigned wgrid = (words + CP_THREADS - 1) / CP_THREADS;
-  const unsigned xgrid = (unsigned)std::min<uint64_t>(((uint64_t)words * 32 + CP_THREADS - 1) / CP_THREADS,
-                                                      (uint64_t)g->eng->sm_count * 8);
-  auto merge = [&](uint32_t lvl, uint64_t* n_new) -> int32_t {
-    DMG_CUDA(cudaMemsetAsync(&c->d_counters->total, 0, 8, c->stream));
-    {
-      LaunchScope ls(c, K_MISC);
-      part_merge_kernel<<<wgrid, CP_THREADS, 0, c->stream>>>(contrib, 1, words, words, visited, next, 0, V, lvl, level,
-                                                             c->d_counters);
-    }
-    DMG_CUDA(cudaGetLastError());
-    DMG_CUDA(cudaMemcpyAsync(c->h_counters, c->d_counters, sizeof(DevCounters), cudaMemcpyDeviceToHost, c->stream));
-    DMG_CUDA(cudaStreamSynchronize(c->stream));
-    *n_new = c->h_counters->total;
-    return DMG_OK;
-  };
   DMG_CUDA(cudaMemsetAsync(c->d_counters, 0, sizeof(DevCounters), c->stream));
   if (n_src) {
     LaunchScope ls(c, K_CLOSURE_INIT);
-    source_bits_kernel<<<(n_src + 255) / 256, 256, 0, c->stream>>>(d_src, n_src, V, contrib);
+    closure_sources_kernel<<<(n_src + 255) / 256, 256, 0, c->stream>>>(d_src, n_src, V, frontier, visited, level);
   }
-  uint64_t n_front = 0, total = 0;
-  DMG_TRY(merge(0, &n_front));
-  total = n_front;
-  for (uint32_t lvl = 1; n_front > 0; ++lvl) {
-    std::swap(frontier, next);
-    {
-      LaunchScope ls(c, K_ORDER_DEG);
-      frontier_degree_kernel<<<wgrid, CP_THREADS, 0, c->stream>>>(ptr, words, V, frontier, c->d_counters);
-    }
-    if (n_front * 32 < V) {
-      DMG_CUDA(cudaMemsetAsync(contrib, 0, (size_t)words * 4, c->stream));
-      LaunchScope ls(c, K_CLOSURE_STEP);
-      part_push_kernel<<<xgrid, CP_THREADS, 0, c->stream>>>(ptr, idx, 0, words, 0, V, frontier, contrib, c->d_counters);
-    } else {
-      LaunchScope ls(c, K_CLOSURE_BOTTOMUP);
-      part_pull_kernel<<<xgrid, CP_THREADS, 0, c->stream>>>(rptr, ridx, 0, words, 0, V, frontier, visited, contrib,
-                                                            c->d_counters);
-    }
-    DMG_TRY(merge(lvl, &n_front));
-    total += n_front;
+  P2pArgs a;
+  memset(&a, 0, sizeof(a));
+  a.rank = 0;
+  a.n = 1;
+  a.V = V;
+  a.wr = words;
+  a.ptr = dir == DMG_OUT ? g->d_out_ptr : g->d_in_ptr;
+  a.idx = dir == DMG_OUT ? g->d_out_idx : g->d_in_idx;
+  a.rptr = dir == DMG_OUT ? g->d_in_ptr : g->d_out_ptr;
+  a.ridx = dir == DMG_OUT ? g->d_in_idx : g->d_out_idx;
+  a.frontier[0][0] = frontier;
+  a.frontier[1][0] = next;
+  a.visited[0] = visited;
+  a.next_slice[0] = slice;
+  a.counts[0] = reinterpret_cast<unsigned long long*>(blk + P2P_O_COUNTS);
+  a.flags[0] = reinterpret_cast<uint32_t*>(blk + P2P_O_FLAGS);
+  a.level = level;
+  a.acc = reinterpret_cast<unsigned long long*>(blk + P2P_O_ACC);
+  a.result = reinterpret_cast<P2pResult*>(blk + P2P_O_RESULT);
+  a.bar = reinterpret_cast<uint32_t*>(blk + P2P_O_BAR);
+  a.spin_ns = 2000000000ull;
+  {
+    LaunchScope ls(c, K_CLOSURE_STEP);
+    DMG_TRY(closure_p2p_launch(a, g->eng->sm_count, c->stream));
   }
-  *reached = total;
+  {
+    LaunchScope ls(c, K_ORDER_DEG);
+    reached_degree_kernel<<<g->eng->sm_count * 8, CP_THREADS, 0, c->stream>>>(a.ptr, V, level, c->d_counters);
+  }
+  DMG_CUDA(cudaGetLastError());
+  P2pResult res;
+  DMG_CUDA(cudaMemcpyAsync(c->h_counters, c->d_counters, sizeof(DevCounters), cudaMemcpyDeviceToHost, c->stream));
+  DMG_CUDA(cudaMemcpyAsync(&res, a.result, sizeof(res), cudaMemcpyDeviceToHost, c->stream));
+  DMG_CUDA(cudaStreamSynchronize(c->stream));
+  if (res.status) {
+    set_error("dmg_closure: the level barrier timed out");
+    return DMG_ECUDA;
+  }
+  *reached = res.reached;
   *te_out = c->h_counters->aux[0];
-  *read_out = c->h_counters->edges;
+  *read_out = res.edges;
   *rows_out = c->h_counters->rows;
   return DMG_OK;
 }

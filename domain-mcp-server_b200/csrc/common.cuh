@@ -167,12 +167,23 @@ void publish_stats(const dmg_call_stats& s);   // thread-local "last call" recor
 int32_t run_khop(CallCtx* c, dmg_graph* g, int mode, int k, int exclude, uint64_t nq, const uint32_t* d_q_off,
                  const uint32_t* d_q_src, uint64_t* d_out_off, uint32_t* d_out_ids, uint8_t* d_out_hop, uint64_t cap);
 
+// NVTX ranges (tracing): with DMG_NVTX=1 in the environment every launch scope and every
+// call is a named range on the host thread (nvtx3 is header-only and inert without a profiler attached).
+bool nvtx_enabled();
+void nvtx_push(const char* name);
+void nvtx_pop();
+
 // Launch helper: counts the launch, brackets it with events when profiling is on.
 struct LaunchScope {
   CallCtx* c;
   cudaEvent_t a = nullptr, b = nullptr;
   int kid;
+  bool nvtx = false;
   LaunchScope(CallCtx* ctx, int kernel_id, bool count = true, int launches = 1) : c(ctx), kid(kernel_id) {
+    if (nvtx_enabled()) {
+      nvtx_push(kKernelNames[kernel_id]);
+      nvtx = true;
+    }
     if (count) c->stats.kernel_launches += launches;
     if (c->eng->profile.load(std::memory_order_relaxed)) {
       a = c->get_event();
@@ -185,6 +196,7 @@ struct LaunchScope {
       cudaEventRecord(b, c->stream);
       c->prof.push_back({kid, a, b});
     }
+    if (nvtx) nvtx_pop();
   }
 };
 

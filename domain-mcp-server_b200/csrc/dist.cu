@@ -77,8 +77,7 @@ struct DistRank {
   // peer-memory form: one block holding counts[2][P2P_MAX_RANKS] u64 | flags[P2P_MAX_RANKS] u32 | acc[4] u64 | result
   unsigned char* p2p = nullptr;
 };
-constexpr size_t P2P_O_COUNTS = 0, P2P_O_FLAGS = 2 * P2P_MAX_RANKS * 8, P2P_O_ACC = P2P_O_FLAGS + 256,
-                 P2P_O_RESULT = P2P_O_ACC + 64, P2P_BLOCK = P2P_O_RESULT + 256;
+
 
 }  // namespace dmg
 
@@ -412,7 +411,8 @@ int32_t dmg_dist_closure(dmg_dist_graph* dg, int32_t dir, uint32_t n_src, const 
     base.spin_ns = 2000000000ull;   // a peer that is 2 s late for a barrier is not coming
     for (int r = 0; r < N; ++r) {
       DistRank& k = dg->ranks[r];
-      base.frontier[r] = k.frontier;
+      base.frontier[0][r] = k.frontier;
+      base.frontier[1][r] = k.next;
       base.visited[r] = k.visited;
       base.next_slice[r] = k.slice;
       base.counts[r] = reinterpret_cast<unsigned long long*>(k.p2p + P2P_O_COUNTS);
@@ -445,6 +445,7 @@ int32_t dmg_dist_closure(dmg_dist_graph* dg, int32_t dir, uint32_t n_src, const 
       a.level = k.level;
       a.acc = reinterpret_cast<unsigned long long*>(k.p2p + P2P_O_ACC);
       a.result = reinterpret_cast<P2pResult*>(k.p2p + P2P_O_RESULT);
+      a.bar = reinterpret_cast<uint32_t*>(k.p2p + P2P_O_BAR);
       if (cudaSetDevice(d->devices[r]) != cudaSuccess) launch_rc = DMG_ECUDA;
       else launch_rc = closure_p2p_launch(a, d->engines[r]->sm_count, k.stream);
     }

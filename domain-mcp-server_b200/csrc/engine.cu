@@ -1,4 +1,6 @@
 // Engine, call contexts, graph upload (GraphService lifecycle, GS:34-122) and small utilities.
+#include <nvtx3/nvToolsExt.h>
+
 #include <algorithm>
 #include <new>
 #include <thread>
@@ -86,7 +88,18 @@ cudaEvent_t CallCtx::get_event() {
   cudaEventCreate(&e);
   return e;
 }
+bool nvtx_enabled() {
+  static const bool on = [] {
+    const char* s = getenv("DMG_NVTX");
+    return s && s[0] == '1';
+  }();
+  return on;
+}
+void nvtx_push(const char* name) { nvtxRangePushA(name); }
+void nvtx_pop() { nvtxRangePop(); }
+
 int32_t CallCtx::begin() {
+  if (nvtx_enabled()) nvtx_push("dmg_call");
   memset(&stats, 0, sizeof(stats));
   DMG_CUDA(cudaSetDevice(eng->device));
   DMG_CUDA(cudaEventRecord(ev_begin, stream));
@@ -112,6 +125,7 @@ int32_t CallCtx::finish() {
     prof.clear();
   }
   publish_stats(stats);
+  if (nvtx_enabled()) nvtx_pop();
   return DMG_OK;
 }
 

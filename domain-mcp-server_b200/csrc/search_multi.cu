@@ -196,73 +196,106 @@ __device__ __forceinline__ bool filter_pass_ldg(const uint32_t* __restrict__ f, 
   return (__ldg(&f[fj >> 5]) >> (fj & 31)) & 1u;
 }
 
-// phase 1, whole warp.  B0 / B1 = byte range of the step's names; s_start[l] = start of name l relative to
-// B0 (entries past the last name and s_start[32] hold B1 - B0); s_nc[l] = queue length of name l (may run
-// past SM_CANDBUF: overflow; preset beyond it for names that cannot be queued at all).
-__device__ __forceinline__ void scan_step(const SearchArgs& a, const uint32_t* fP, const uint32_t* f3, int lane,
-                                          unsigned long long B0, unsigned long long B1, const uint32_t* s_start,
-                                          uint32_t* s_nc, uint16_t (*cand)[SM_CANDBUF]) {
+// Both probes of a filter without a branch between them (inside the sweep a branch would only make the
+// warp run both sides: some lane nearly always passes the first bit).
+__device__ __forceinline__ bool filter_pass2(const uint32_t* f, uint32_t raw, uint32_t bits) {
+  const uint32_t fi = hash_filter(raw, bits), fj = hash_filter2(raw, bits);
+  return ((f[fi >> 5] >> (fi & 31)) & (f[fj >> 5] >> (fj & 31)) & 1u) != 0;
+}
+
+constexpr uint32_t SM_WORK = 320;          // positions a warp parks before it works them off
+constexpr uint32_t WORK_P4 = 1u, WORK_3 = 2u, WORK_2 = 4u, WORK_1 = 8u;
+
+// phase 1b, whole warp: the parked positions, 32 at a time with every lane busy.  A position that passed
+// the prefix filter asks the length classes' own filters (global memory, L1-resident); what survives
+// finds its name by bisection over the step's offsets and is queued there.
+__device__ __forceinline__ void drain_work(const SearchArgs& a, int lane, unsigned long long B0, const uint32_t* work,
+                                           uint32_t n_work, const uint32_t* s_start, uint32_t* s_nc,
+                                           uint16_t (*cand)[SM_CANDBUF]) {
   const uint32_t* __restrict__ g16 = a.filt;
   const uint32_t* __restrict__ g12 = g16 + a.filt_words16;
   const uint32_t* __restrict__ g8 = g12 + a.filt_words12;
   const uint32_t* __restrict__ g4 = g8 + a.filt_words8;
+  for (uint32_t i = lane; i < n_work; i += 32) {
+    const uint32_t item = work[i], r0 = item >> 4, f = item & 15u;
+    uint32_t cm = (f & WORK_3 ? 1u << 4 : 0u) | (f & WORK_2 ? 1u << 5 : 0u) | (f & WORK_1 ? 1u << 6 : 0u);
+    if (f & WORK_P4) {
+      const unsigned long long at = B0 + r0;
+      const uint32_t* wp = reinterpret_cast<const uint32_t*>(a.lower + (at & ~3ull));   // zero padded past the end
+      const uint32_t sh = (uint32_t)(at & 3ull) * 8;
+      const uint32_t w0 = __ldg(wp), w1 = __ldg(wp + 1), w2 = __ldg(wp + 2), w3 = __ldg(wp + 3), w4 = __ldg(wp + 4);
+      const uint32_t lo32 = sh ? __funnelshift_r(w0, w1, sh) : w0, hi32 = sh ? __funnelshift_r(w1, w2, sh) : w1;
+      const uint32_t lo2 = sh ? __funnelshift_r(w2, w3, sh) : w2, hi2 = sh ? __funnelshift_r(w3, w4, sh) : w3;
+      const uint32_t h4 = lo32 * HASH_A, h8 = h4 ^ (hi32 * HASH_B), h12 = h8 ^ (lo2 * HASH_C);
+      if (a.t4.present && filter_pass_ldg(g4, h4, a.t4.fbits)) cm |= 1u << 3;
+      if (a.t8.present && filter_pass_ldg(g8, h8, a.t8.fbits)) cm |= 1u << 2;
+      if (a.t12.present && filter_pass_ldg(g12, h12, a.t12.fbits)) cm |= 1u << 1;
+      if (a.t16.present && filter_pass_ldg(g16, h12 ^ (hi2 * HASH_D), a.t16.fbits)) cm |= 1u;
+    }
+    if (!cm) continue;
+    uint32_t l = 0;   // the name the position lies in
+#pragma unroll
+    for (int st = 16; st > 0; st >>= 1)
+      if (s_start[l + st] <= r0) l += st;
+    const uint32_t pos = r0 - s_start[l], room = s_start[l + 1] - r0;
+    for (; cm; cm &= cm - 1) {
+      const uint32_t cls = __ffs(cm) - 1;
+      const uint32_t shortest = cls == 0 ? 16u : cls == 1 ? 12u : cls == 2 ? 8u : cls == 3 ? 4u : 7u - cls;   // 3, 2, 1
+      if (room < shortest) continue;
+      const uint32_t slot = atomicAdd(&s_nc[l], 1u);
+      if (slot < (uint32_t)SM_CANDBUF) cand[l][slot] = (uint16_t)((cls << CAND_POS_BITS) | pos);
+    }
+  }
+  __syncwarp();
+}
+
+// phase 1, whole warp.  B0 / B1 = byte range of the step's names; s_start[l] = start of name l relative to
+// B0 (entries past the last name and s_start[32] hold B1 - B0); s_nc[l] = queue length of name l (may run
+// past SM_CANDBUF: overflow; preset beyond it for names that cannot be queued at all).  The sweep itself
+// only asks the two shared-memory filters and PARKS the few positions that pass (work[], SM_WORK entries):
+// anything rarer than that would run with a handful of lanes if it ran inline.
+template <bool TINY>   // TINY: the batch has patterns of one or two bytes (their tables are asked per position)
+__device__ __forceinline__ void scan_step(const SearchArgs& a, const uint32_t* fP, const uint32_t* f3, int lane,
+                                          unsigned long long B0, unsigned long long B1, const uint32_t* s_start,
+                                          uint32_t* s_nc, uint16_t (*cand)[SM_CANDBUF], uint32_t* work) {
   const unsigned long long c0 = B0 & ~3ull;
   const uint32_t* __restrict__ wbase = reinterpret_cast<const uint32_t*>(a.lower + c0);
   const unsigned long long n_words = (a.lower_size - c0) >> 2;   // words that may be read from c0 on
   const uint32_t span = (uint32_t)(B1 - B0);
+  const unsigned lt = lanemask_lt();
   uint32_t nxt = lane < n_words ? __ldg(wbase + lane) : 0u;
+  uint32_t n_work = 0;
   unsigned long long wi = 0;
   for (unsigned long long c = c0; c < B1; c += 128, wi += 32) {
     const uint32_t w0 = nxt;
     nxt = wi + 32 + lane < n_words ? __ldg(wbase + wi + 32 + lane) : 0u;
-    // word lane + k of this chunk: lanes that run past the chunk take it from the next chunk's load
+    // the word after the lane's own: the neighbour's, or for lane 31 the first word of the next chunk
     const uint32_t w1 = __shfl_sync(FULL, lane >= 1 ? w0 : nxt, (lane + 1) & 31);
-    const uint32_t w2 = __shfl_sync(FULL, lane >= 2 ? w0 : nxt, (lane + 2) & 31);
-    const uint32_t w3 = __shfl_sync(FULL, lane >= 3 ? w0 : nxt, (lane + 3) & 31);
-    const uint32_t w4 = __shfl_sync(FULL, lane >= 4 ? w0 : nxt, (lane + 4) & 31);
-    const long long rel0 = (long long)(c + 4ull * lane) - (long long)B0;   // first position of the lane, relative to B0
+    const int rel0 = (int)((long long)(c + 4ull * lane) - (long long)B0);   // first position of the lane, relative to B0
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
-      const long long rel = rel0 + j;
-      if (rel < 0 || rel >= (long long)span) continue;
+      const int rel = rel0 + j;
       const uint32_t lo32 = j ? __funnelshift_r(w0, w1, 8 * j) : w0;
-      const uint32_t h4 = lo32 * HASH_A;
-      uint32_t cm = 0;   // classes whose filter the position passes: bit = class
-      if (a.presentP && filter_pass(fP, h4, a.fbitsP)) {
-        const uint32_t hi32 = j ? __funnelshift_r(w1, w2, 8 * j) : w1;
-        const uint32_t h8 = h4 ^ (hi32 * HASH_B);
-        if (a.t4.present && filter_pass_ldg(g4, h4, a.t4.fbits)) cm |= 1u << 3;
-        if (a.t8.present && filter_pass_ldg(g8, h8, a.t8.fbits)) cm |= 1u << 2;
-        if (a.t12.present | a.t16.present) {
-          const uint32_t lo2 = j ? __funnelshift_r(w2, w3, 8 * j) : w2;
-          const uint32_t h12 = h8 ^ (lo2 * HASH_C);
-          if (a.t12.present && filter_pass_ldg(g12, h12, a.t12.fbits)) cm |= 1u << 1;
-          if (a.t16.present) {
-            const uint32_t hi2 = j ? __funnelshift_r(w3, w4, 8 * j) : w3;
-            if (filter_pass_ldg(g16, h12 ^ (hi2 * HASH_D), a.t16.fbits)) cm |= 1u;
-          }
-        }
+      uint32_t f = 0;
+      if (a.presentP && filter_pass2(fP, lo32 * HASH_A, a.fbitsP)) f |= WORK_P4;
+      if (a.t3.present && filter_pass2(f3, (lo32 & 0xFFFFFFu) * HASH_A, a.t3.fbits)) f |= WORK_3;
+      if (TINY) {
+        if (a.has2 && a.tiny2[lo32 & 0xFFFFu]) f |= WORK_2;
+        if (a.has1 && a.tiny1[lo32 & 0xFFu]) f |= WORK_1;
       }
-      if (a.t3.present && filter_pass(f3, (lo32 & 0xFFFFFFu) * HASH_A, a.t3.fbits)) cm |= 1u << 4;
-      if (a.has2 && a.tiny2[lo32 & 0xFFFFu]) cm |= 1u << 5;
-      if (a.has1 && a.tiny1[lo32 & 0xFFu]) cm |= 1u << 6;
-      if (!cm) continue;
-      const uint32_t r0 = (uint32_t)rel;
-      uint32_t l = 0;   // the name the position lies in
-#pragma unroll
-      for (int st = 16; st > 0; st >>= 1)
-        if (s_start[l + st] <= r0) l += st;
-      const uint32_t pos = r0 - s_start[l], room = s_start[l + 1] - r0;
-      for (; cm; cm &= cm - 1) {
-        const uint32_t cls = __ffs(cm) - 1;
-        const uint32_t shortest = cls == 0 ? 16u : cls == 1 ? 12u : cls == 2 ? 8u : cls == 3 ? 4u : 7u - cls;   // 3, 2, 1
-        if (room < shortest) continue;
-        const uint32_t slot = atomicAdd(&s_nc[l], 1u);
-        if (slot < (uint32_t)SM_CANDBUF) cand[l][slot] = (uint16_t)((cls << CAND_POS_BITS) | pos);
-      }
+      if (rel < 0 || rel >= (int)span) f = 0;
+      const unsigned m = __ballot_sync(FULL, f != 0);
+      if (f) work[n_work + __popc(m & lt)] = ((uint32_t)rel << 4) | f;
+      n_work += __popc(m);
+    }
+    if (n_work > SM_WORK - 128) {
+      __syncwarp();
+      drain_work(a, lane, B0, work, n_work, s_start, s_nc, cand);
+      n_work = 0;
     }
   }
   __syncwarp();
+  drain_work(a, lane, B0, work, n_work, s_start, s_nc, cand);
 }
 
 // phase 2, whole warp: `nc` = this lane's candidate count (<= SM_CANDBUF), s / len = this lane's name.
@@ -313,9 +346,16 @@ __device__ __forceinline__ void resolve_candidates(const SearchArgs& a, int lane
       if (pi.len <= r && (k8 & low_bytes_mask(pi.len)) == pi.pk8) {   // first min(len, 8) bytes
         bool ok = true;
         if (pi.len > 8) {
-          const uint8_t* pb = a.pbytes + a.poff[u];
-          const uint8_t* nb = a.lower + at;
-          for (uint32_t t = 8; t < pi.len && ok; ++t) ok = nb[t] == pb[t];
+          // bytes 8.. four at a time: pattern words are 4-byte aligned (poff is), name words come from the
+          // aligned pair around them; bytes 8..15 are still in the window registers
+          const uint32_t* pw = reinterpret_cast<const uint32_t*>(a.pbytes + a.poff[u]);
+          for (uint32_t t = 8; t < pi.len && ok; t += 4) {
+            const uint32_t k = t >> 2;
+            const uint32_t nw = k == 2 ? lo2 : (k == 3 ? hi2 : (sh ? __funnelshift_r(__ldg(wp + k), __ldg(wp + k + 1), sh) : __ldg(wp + k)));
+            const uint32_t rem = pi.len - t;
+            const uint32_t mask = rem >= 4 ? 0xFFFFFFFFu : ((1u << (8 * rem)) - 1u);
+            ok = ((nw ^ __ldg(pw + k)) & mask) == 0;
+          }
         }
         if (ok) hit(u);
       }
@@ -376,6 +416,7 @@ __global__ void __launch_bounds__(SM_THREADS) search_multi_kernel(const SearchAr
   __shared__ uint32_t s_pref[SM_WARPS][32];
   __shared__ uint32_t s_start[SM_WARPS][36];
   __shared__ uint32_t s_nc[SM_WARPS][32];
+  __shared__ uint32_t s_work[SM_WARPS][SM_WORK];
   const int tid = threadIdx.x, lane = tid & 31, wib = tid >> 5;
   const uint32_t fw = a.filt_wordsP + a.filt_words3;
   typedef uint16_t HitLists[32][SM_HITBUF];
@@ -446,13 +487,16 @@ __global__ void __launch_bounds__(SM_THREADS) search_multi_kernel(const SearchAr
       const uint32_t n_valid = min(32u, n1 - i0);
       const unsigned long long B0 = __shfl_sync(FULL, s, 0);
       const unsigned long long B1 = __shfl_sync(FULL, s + len, (int)n_valid - 1);
-      const bool spans = B1 - B0 < (1ull << 31);
+      const bool spans = B1 - B0 < (1ull << 27);   // a parked position is 28 bits
       s_start[wib][lane] = (uint32_t)((i < n1 ? s : B1) - B0);
       if (lane == 0) s_start[wib][32] = (uint32_t)(B1 - B0);
       // names too long for a 13-bit position (or a step too long for 32-bit offsets) take the exhaustive path
       s_nc[wib][lane] = (len >= (1u << CAND_POS_BITS) || !spans) ? (uint32_t)SM_CANDBUF + 1u : 0u;
       __syncwarp();
-      if (spans) scan_step(a, fP, f3, lane, B0, B1, s_start[wib], s_nc[wib], s_cand[wib]);
+      if (spans) {
+        if (a.has2 | a.has1) scan_step<true>(a, fP, f3, lane, B0, B1, s_start[wib], s_nc[wib], s_cand[wib], s_work[wib]);
+        else scan_step<false>(a, fP, f3, lane, B0, B1, s_start[wib], s_nc[wib], s_cand[wib], s_work[wib]);
+      }
       const uint32_t nc = i < n1 ? s_nc[wib][lane] : 0u;
       const bool cand_overflow = nc > SM_CANDBUF;
       // the empty pattern is contained in every name (CCS:1513: "".contains)
@@ -688,8 +732,9 @@ static void build_tables(uint64_t nq, const uint32_t* q_off, const uint8_t* q_by
     const std::string& p = T.pats[u];
     T.pat[u].len = (uint32_t)p.size();
     T.pat[u].next = PAT_NIL;
-    T.poff[u] = (uint32_t)T.pbytes.size();
+    T.poff[u] = (uint32_t)T.pbytes.size();   // a multiple of 4: the verification compares words
     T.pbytes.insert(T.pbytes.end(), p.begin(), p.end());
+    T.pbytes.resize((T.pbytes.size() + 3) & ~size_t(3), 0);
     unsigned long long k = 0;
     for (size_t i = 0; i < p.size() && i < 8; ++i) k |= (unsigned long long)(uint8_t)p[i] << (8 * i);
     T.pat[u].pk8 = k;

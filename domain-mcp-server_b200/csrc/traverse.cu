@@ -793,7 +793,7 @@ namespace dmg {
 // copied warp-per-row.
 // ---------------------------------------------------------------------------------------------
 constexpr int ADJ_THREADS = 256;
-constexpr uint32_t ADJ_LONG_ROW = 2048;
+constexpr uint32_t ADJ_LONG_ROW = 512;
 
 __global__ void __launch_bounds__(ADJ_THREADS) adjacency_kernel(const uint32_t* __restrict__ ptr,
                                                                 const uint32_t* __restrict__ idx, uint32_t V,
@@ -865,19 +865,47 @@ __global__ void __launch_bounds__(ADJ_THREADS) adjacency_kernel(const uint32_t* 
   }
 }
 
-// rows longer than ADJ_LONG_ROW: every CTA copies a slice of every such row, one 4-byte entry per thread
-// step (coalesced; source and destination offsets differ per row, so wider moves would need a peel)
+// Rows longer than ADJ_LONG_ROW are copied in chunks of ADJ_CHUNK entries, one warp per chunk, whatever row
+// a chunk belongs to: a Zipf hub with 800 k dependents and a few hundred 600-entry rows then cost what
+// their entries cost (the previous kernel walked the long rows one after the other with the whole grid on
+// each: config 4's `dependents` batch spent most of its 0.26 ms there).
+constexpr uint32_t ADJ_CHUNK = 512;
+// chunk_off[i] = chunks of the long rows before row i (one CTA: there are at most n rows, usually a handful)
+__global__ void __launch_bounds__(1024) adjacency_long_scan_kernel(const unsigned long long* __restrict__ long_rows,
+                                                                   DevCounters* ctr, uint32_t* chunk_off) {
+  __shared__ uint32_t s_wsum[33];
+  const unsigned long long n_long = ctr->aux[1];
+  uint32_t run = 0;
+  for (unsigned long long i0 = 0; i0 < n_long; i0 += 1024) {
+    const unsigned long long i = i0 + threadIdx.x;
+    const uint32_t nch = i < n_long ? ((uint32_t)long_rows[2 * i] + ADJ_CHUNK - 1) / ADJ_CHUNK : 0u;
+    uint32_t tot;
+    const uint32_t off = block_excl_scan<1024>(nch, s_wsum, &tot);
+    if (i < n_long) chunk_off[i] = run + off;
+    run += tot;
+  }
+  if (threadIdx.x == 0) ctr->aux[3] = run;   // chunks in all
+}
 __global__ void __launch_bounds__(256) adjacency_long_kernel(const uint32_t* __restrict__ idx,
                                                              const unsigned long long* __restrict__ long_rows,
+                                                             const uint32_t* __restrict__ chunk_off,
                                                              const DevCounters* ctr, uint32_t* out_ids,
                                                              unsigned long long cap) {
-  const unsigned long long n_long = ctr->aux[1];
-  const unsigned long long gtid = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x;
-  const unsigned long long gsz = (unsigned long long)gridDim.x * blockDim.x;
-  for (unsigned long long r = 0; r < n_long; ++r) {
+  const int lane = threadIdx.x & 31;
+  const unsigned long long n_long = ctr->aux[1], n_chunks = ctr->aux[3];
+  const unsigned long long warp = (blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x) >> 5;
+  const unsigned long long n_warps = ((unsigned long long)gridDim.x * blockDim.x) >> 5;
+  for (unsigned long long c = warp; c < n_chunks; c += n_warps) {
+    unsigned long long r = 0, hi = n_long;   // last row whose first chunk is <= c
+    while (hi - r > 1) {
+      const unsigned long long mid = (r + hi) >> 1;
+      if (chunk_off[mid] <= c) r = mid; else hi = mid;
+    }
     const uint32_t st = (uint32_t)(long_rows[2 * r] >> 32), ln = (uint32_t)long_rows[2 * r];
     const unsigned long long o = long_rows[2 * r + 1];
-    for (unsigned long long j = gtid; j < ln; j += gsz)
+    const uint32_t j0 = (uint32_t)(c - chunk_off[r]) * ADJ_CHUNK, j1 = min(ln, j0 + ADJ_CHUNK);
+#pragma unroll 4
+    for (uint32_t j = j0 + lane; j < j1; j += 32)
       if (o + j < cap) out_ids[o + j] = idx[st + j];
   }
 }
@@ -1102,6 +1130,8 @@ int32_t run_khop(CallCtx* c, dmg_graph* g, int mode, int k, int exclude, uint64_
       }
       if (a.cap) {
         LaunchScope ls(c, K_KHOP_EMIT);
+        // about one query per warp, many small waves (a resident wave whose warps walk several queries with
+        // the next query's head loaded ahead was tried: 40 registers, 0.217 vs 0.175 ms)
         const uint64_t blocks = std::min<uint64_t>((q1 - q0 + 7) / 8, (uint64_t)e->sm_count * EM_GRID_PER_SM);
         with_planes(np, w64, [&](auto, auto emit) -> int32_t {
           emit<<<(unsigned)blocks, 256, 0, c->stream>>>(c->scratch.as<uint32_t>(), WB, q1 - q0, qwin + 2 * q0, counts + q0,
@@ -1727,6 +1757,7 @@ int32_t dmg_adjacency_batch(dmg_graph* g, int32_t dir, uint64_t n, const uint32_
   DMG_TRY(c->out_off.reserve((n + 1) * 8));
   DMG_TRY(c->status.reserve(n_tiles * 8));
   DMG_TRY(c->tmp0.reserve(n * 16));   // (start, len, out offset) of rows left to adjacency_long_kernel
+  DMG_TRY(c->tmp1.reserve(n * 4 + 16));   // their first chunk
   DMG_CUDA(cudaMemcpyAsync(c->q_src.p, ids, n * 4, cudaMemcpyHostToDevice, c->stream));
   c->stats.h2d_bytes += n * 4;
   const uint32_t* ptr = dir == DMG_OUT ? g->d_out_ptr : g->d_in_ptr;
@@ -1750,10 +1781,12 @@ int32_t dmg_adjacency_batch(dmg_graph* g, int32_t dir, uint64_t n, const uint32_
           c->tmp0.as<unsigned long long>());
     }
     if (use_cap) {
-      LaunchScope ls(c, K_ADJ_GATHER);
-      adjacency_long_kernel<<<g->eng->sm_count * 4, 256, 0, c->stream>>>(idx, c->tmp0.as<unsigned long long>(),
-                                                                       c->d_counters, c->out_ids.as<uint32_t>(),
-                                                                       use_cap);
+      LaunchScope ls(c, K_ADJ_GATHER, true, 2);
+      adjacency_long_scan_kernel<<<1, 1024, 0, c->stream>>>(c->tmp0.as<unsigned long long>(), c->d_counters,
+                                                            c->tmp1.as<uint32_t>());
+      adjacency_long_kernel<<<g->eng->sm_count * 8, 256, 0, c->stream>>>(idx, c->tmp0.as<unsigned long long>(),
+                                                                       c->tmp1.as<uint32_t>(), c->d_counters,
+                                                                       c->out_ids.as<uint32_t>(), use_cap);
     }
     DMG_CUDA(cudaGetLastError());
     DMG_TRY(fetch_counters(c));
