@@ -141,13 +141,14 @@ __global__ void __launch_bounds__(K1_THREADS) khop1_warp_kernel(const KhopArgs a
 
 // ---------------------------------------------------------------------------------------------------
 constexpr int KL_THREADS = 1024, KL_NW = KL_THREADS / 32;
-constexpr int KL_ILP = 4;             // adjacency entries in flight per lane
+constexpr int KL_ILP = 4;             // queue entries in flight per thread in the emit
 // dynamic shared memory: claim bitmap (W words, W a multiple of 128) + one rank word per quad of bitmap words
 static inline size_t large_kernel_smem(uint32_t maxp) {
   const size_t W = (((size_t)maxp + 31) / 32 + 127) & ~size_t(127);
   return W * 4 + (W / 4) * 4;
 }
 
+template <int XILP>   // adjacency entries in flight per lane while a level is expanded
 __global__ void __launch_bounds__(KL_THREADS, 1) khop_large_kernel(const KhopArgs a, uint32_t* sc_queue, size_t qcap,
                                                                     uint32_t W, const uint32_t* qlist,
                                                                     const uint32_t* qlist_n) {
@@ -242,10 +243,10 @@ __global__ void __launch_bounds__(KL_THREADS, 1) khop_large_kernel(const KhopArg
             r = l;
           }
           uint2 row = s_row[r];
-          for (uint32_t p0 = pbeg; p0 < pend; p0 += 32 * KL_ILP) {
-            uint32_t v[KL_ILP];
+          for (uint32_t p0 = pbeg; p0 < pend; p0 += 32 * XILP) {
+            uint32_t v[XILP];
 #pragma unroll
-            for (int j = 0; j < KL_ILP; ++j) {
+            for (int j = 0; j < XILP; ++j) {
               const uint32_t p = p0 + 32 * j + lane;
               v[j] = 0xFFFFFFFFu;
               if (p < pend) {
@@ -254,7 +255,7 @@ __global__ void __launch_bounds__(KL_THREADS, 1) khop_large_kernel(const KhopArg
               }
             }
 #pragma unroll
-            for (int j = 0; j < KL_ILP; ++j) {
+            for (int j = 0; j < XILP; ++j) {
               bool isnew = false;
               uint32_t x = 0;
               if (v[j] != 0xFFFFFFFFu) {
