@@ -141,14 +141,14 @@ __global__ void __launch_bounds__(K1_THREADS) khop1_warp_kernel(const KhopArgs a
 
 // ---------------------------------------------------------------------------------------------------
 constexpr int KL_THREADS = 1024, KL_NW = KL_THREADS / 32;
-constexpr int KL_ILP = 4;             // queue entries in flight per thread in the emit
+constexpr int KL_ILP = 4;             // adjacency / queue entries in flight per lane (8 measured the same)
+constexpr int KL_SEGR = 3;            // level boundaries kept in registers by the emit (k <= 4 needs no table walk)
 // dynamic shared memory: claim bitmap (W words, W a multiple of 128) + one rank word per quad of bitmap words
 static inline size_t large_kernel_smem(uint32_t maxp) {
   const size_t W = (((size_t)maxp + 31) / 32 + 127) & ~size_t(127);
   return W * 4 + (W / 4) * 4;
 }
 
-template <int XILP>   // adjacency entries in flight per lane while a level is expanded
 __global__ void __launch_bounds__(KL_THREADS, 1) khop_large_kernel(const KhopArgs a, uint32_t* sc_queue, size_t qcap,
                                                                     uint32_t W, const uint32_t* qlist,
                                                                     const uint32_t* qlist_n) {
@@ -243,10 +243,10 @@ __global__ void __launch_bounds__(KL_THREADS, 1) khop_large_kernel(const KhopArg
             r = l;
           }
           uint2 row = s_row[r];
-          for (uint32_t p0 = pbeg; p0 < pend; p0 += 32 * XILP) {
-            uint32_t v[XILP];
+          for (uint32_t p0 = pbeg; p0 < pend; p0 += 32 * KL_ILP) {
+            uint32_t v[KL_ILP];
 #pragma unroll
-            for (int j = 0; j < XILP; ++j) {
+            for (int j = 0; j < KL_ILP; ++j) {
               const uint32_t p = p0 + 32 * j + lane;
               v[j] = 0xFFFFFFFFu;
               if (p < pend) {
@@ -254,21 +254,29 @@ __global__ void __launch_bounds__(KL_THREADS, 1) khop_large_kernel(const KhopArg
                 v[j] = fidx[row.y + p];
               }
             }
+            // claim, then ONE reservation of queue slots for the step's KL_ILP x 32 entries (32 warps adding to
+            // one shared counter per 32 entries showed as the kernel's largest stall)
+            unsigned m[KL_ILP];
+            uint32_t cnt = 0;
 #pragma unroll
-            for (int j = 0; j < XILP; ++j) {
+            for (int j = 0; j < KL_ILP; ++j) {
               bool isnew = false;
-              uint32_t x = 0;
               if (v[j] != 0xFFFFFFFFu) {
-                x = v[j] - lo;
-                const uint32_t bit = 1u << (x & 31);
-                if (!(seen[x >> 5] & bit)) isnew = !(atomicOr(&seen[x >> 5], bit) & bit);
+                v[j] -= lo;
+                const uint32_t bit = 1u << (v[j] & 31);
+                if (!(seen[v[j] >> 5] & bit)) isnew = !(atomicOr(&seen[v[j] >> 5], bit) & bit);
               }
-              const unsigned m = __ballot_sync(FULL, isnew);
-              if (m) {
-                uint32_t pos = 0;
-                if (lane == 0) pos = atomicAdd(&s_tail, (uint32_t)__popc(m));
-                pos = __shfl_sync(FULL, pos, 0);
-                if (isnew) queue[pos + __popc(m & lanemask_lt())] = x;
+              m[j] = __ballot_sync(FULL, isnew);
+              cnt += __popc(m[j]);
+            }
+            if (cnt) {
+              uint32_t pos = 0;
+              if (lane == 0) pos = atomicAdd(&s_tail, cnt);
+              pos = __shfl_sync(FULL, pos, 0);
+#pragma unroll
+              for (int j = 0; j < KL_ILP; ++j) {
+                if ((m[j] >> lane) & 1u) queue[pos + __popc(m[j] & lanemask_lt())] = v[j];
+                pos += __popc(m[j]);
               }
             }
           }
@@ -323,6 +331,9 @@ __global__ void __launch_bounds__(KL_THREADS, 1) khop_large_kernel(const KhopArg
       }
       __syncthreads();
       const unsigned long long base = s_base;
+      uint32_t segr[KL_SEGR];   // ends of the first levels' queue segments, in registers
+#pragma unroll
+      for (int l = 1; l <= KL_SEGR; ++l) segr[l - 1] = s_seg[min(l, nlev)];
       // KL_ILP queue entries per thread and step: their (L2) loads are in flight together
       for (uint32_t i0 = 0; i0 < total; i0 += THREADS * KL_ILP) {
         uint32_t vv[KL_ILP];
@@ -336,8 +347,11 @@ __global__ void __launch_bounds__(KL_THREADS, 1) khop_large_kernel(const KhopArg
           const uint32_t v = vv[j];
           if (v == 0xFFFFFFFFu) continue;
           const uint32_t p = ns + i0 + j * THREADS + tid, w = v >> 5, gq = w >> 2;
-          int lv = 1;
-          while (lv < nlev && p >= s_seg[lv]) ++lv;
+          int lv = 1;   // level segments of the queue: p >= seg[l] puts the entry beyond level l
+#pragma unroll
+          for (int l = 1; l <= KL_SEGR; ++l) lv += (l < nlev && p >= segr[l - 1]) ? 1 : 0;
+          if (lv > KL_SEGR)   // deeper than the registers hold: walk the table
+            while (lv < nlev && p >= s_seg[lv]) ++lv;
           const uint4 x = seen4[gq];
           const uint32_t sub = w & 3u;
           uint32_t before = (sub > 0 ? __popc(x.x) : 0) + (sub > 1 ? __popc(x.y) : 0) + (sub > 2 ? __popc(x.z) : 0);

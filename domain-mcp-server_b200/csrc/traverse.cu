@@ -1219,9 +1219,8 @@ int32_t run_khop(CallCtx* c, dmg_graph* g, int mode, int k, int exclude, uint64_
     const size_t kg_smem = (size_t)KG_SORT_CAP * 5 + (2 * (size_t)KG_BUCKETS + 8) * 4;
     uint64_t grid;
     if (use_large) {
-      DMG_CUDA(cudaFuncSetAttribute(khop_large_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kl_smem));
-      DMG_CUDA(cudaFuncSetAttribute(khop_large_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kl_smem));
-      DMG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, khop_large_kernel<4>, KL_THREADS, kl_smem));
+      DMG_CUDA(cudaFuncSetAttribute(khop_large_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kl_smem));
+      DMG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, khop_large_kernel, KL_THREADS, kl_smem));
       grid = std::min<uint64_t>(nq, (uint64_t)e->sm_count * std::max(occ, 1));
     } else {
       DMG_CUDA(cudaFuncSetAttribute(khop_global_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kg_smem));
@@ -1264,13 +1263,9 @@ int32_t run_khop(CallCtx* c, dmg_graph* g, int mode, int k, int exclude, uint64_
     }
     {
       LaunchScope ls(c, use_large ? K_KHOP_LARGE : K_KHOP_GLOBAL);
-      const char* ilp = getenv("DMG_KL_ILP");   // tuning runs
-      if (use_large && ilp && ilp[0] == '8')
-        khop_large_kernel<8><<<(unsigned)grid, KL_THREADS, kl_smem, c->stream>>>(a, sc_queue, qcap, (uint32_t)(kl_smem / 5),
-                                                                              d_defer, d_ndefer);
-      else if (use_large)
-        khop_large_kernel<4><<<(unsigned)grid, KL_THREADS, kl_smem, c->stream>>>(a, sc_queue, qcap, (uint32_t)(kl_smem / 5),
-                                                                              d_defer, d_ndefer);
+      if (use_large)
+        khop_large_kernel<<<(unsigned)grid, KL_THREADS, kl_smem, c->stream>>>(a, sc_queue, qcap, (uint32_t)(kl_smem / 5),
+                                                                           d_defer, d_ndefer);
       else
         khop_global_kernel<<<(unsigned)grid, KG_THREADS, kg_smem, c->stream>>>(a, sc_seen, sc_rank, sc_queue, seen_words,
                                                                              qcap, d_defer, d_ndefer);

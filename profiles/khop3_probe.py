@@ -19,12 +19,10 @@ for b in budgets:
     eng = dmgraph.Engine(0, scratch_bytes=int(b * (1 << 30)))
     g = dmgraph.Graph(eng, sg.n_vertices, sg.src, sg.dst, sg.entry)
     eng.profile(True)
-    for ilp in os.environ.get("PROBE_KL_ILP", "4").split(","):      # e.g. PROBE_KL_ILP=4,8
-        os.environ["DMG_KL_ILP"] = ilp
-        for _ in range(2):
-            eng.profile_reset()
-            off, out, hop = g.neighbors_batch(dmgraph.OUT, k, 0, q_off, ids)
-        print("scratch GiB", b, "ilp", ilp, eng.last_stats())
-        print({k_: (int(v[0]), round(v[1] / v[0], 3)) for k_, v in eng.profile_table().items()}, flush=True)
+    for _ in range(2):
+        eng.profile_reset()
+        off, out, hop = g.neighbors_batch(dmgraph.OUT, k, 0, q_off, ids)
+    print("scratch GiB", b, eng.last_stats())
+    print({k_: (int(v[0]), round(v[1] / v[0], 3)) for k_, v in eng.profile_table().items()}, flush=True)
     g.release()
     eng.close()
