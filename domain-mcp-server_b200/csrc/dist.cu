@@ -583,18 +583,22 @@ extern "C" int32_t dmg_dist_neighbors_batch(dmg_dist_graph* dg, int32_t mode, in
   std::vector<int32_t> rc(N, DMG_OK);
   std::vector<std::string> err(N);
   std::vector<std::vector<uint32_t>> local_off(N);
+  // every replica gets its OWN row-offset array: n + 1 entries each, so neighbouring ranges would otherwise
+  // share one element of out_off (the end of one range is the start of the next) and race on it
+  std::vector<std::vector<uint64_t>> rank_off(N);
   auto run = [&](int r, int phase) {
     const uint64_t a = q_lo[r], b = q_lo[r + 1], n = b - a;
     if (!n) return;
     if (phase == 0) {
       local_off[r].resize(n + 1);
+      rank_off[r].assign(n + 1, 0);
       for (uint64_t i = 0; i <= n; ++i) local_off[r][i] = q_off[a + i] - q_off[a];
     }
     uint64_t nd = 0;
     const bool fetch = phase == 1;
     const uint64_t room = fetch ? cap - base[r] : 0;
     const int32_t st = dmg_neighbors_batch(dg->graphs[r], mode, k, exclude_sources, n, local_off[r].data(),
-                                           q_src + q_off[a], out_off + a, fetch ? out_ids + base[r] : nullptr,
+                                           q_src + q_off[a], rank_off[r].data(), fetch ? out_ids + base[r] : nullptr,
                                            fetch ? out_hop + base[r] : nullptr, room, &nd);
     need[r] = nd;
     if (st != DMG_OK && !(phase == 0 && st == DMG_ECAP)) {
@@ -618,7 +622,7 @@ extern "C" int32_t dmg_dist_neighbors_batch(dmg_dist_graph* dg, int32_t mode, in
       if (base[N] > cap || (base[N] && (!out_ids || !out_hop))) {
         // offsets are still meaningful: rebase them so the caller sees the global layout
         for (int r = 0; r < N; ++r)
-          for (uint64_t i = q_lo[r]; i < q_lo[r + 1]; ++i) out_off[i] += base[r];
+          for (uint64_t i = q_lo[r]; i < q_lo[r + 1]; ++i) out_off[i] = rank_off[r][i - q_lo[r]] + base[r];
         out_off[nq] = base[N];
         set_error("dmg_dist_neighbors_batch: capacity %llu < needed %llu", (unsigned long long)cap,
                   (unsigned long long)base[N]);
@@ -627,7 +631,7 @@ extern "C" int32_t dmg_dist_neighbors_batch(dmg_dist_graph* dg, int32_t mode, in
     }
   }
   for (int r = 0; r < N; ++r)
-    for (uint64_t i = q_lo[r]; i < q_lo[r + 1]; ++i) out_off[i] += base[r];
+    for (uint64_t i = q_lo[r]; i < q_lo[r + 1]; ++i) out_off[i] = rank_off[r][i - q_lo[r]] + base[r];
   out_off[nq] = base[N];
   return DMG_OK;
 }
