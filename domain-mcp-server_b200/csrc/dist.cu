@@ -14,7 +14,6 @@
 // NCCL is bound at run time (dlopen of libnccl.so.2) so that a host which never goes multi-GPU needs no
 // NCCL, and a process that already loaded one (torch) keeps using that copy.  Failures: DMG_ENCCL.
 #include <dlfcn.h>
-#include <nccl.h>
 
 #include <algorithm>
 #include <cstddef>
@@ -24,6 +23,7 @@
 
 #include "common.cuh"
 #include "closure_p2p.h"
+#include "dist_internal.h"
 
 namespace dmg {
 
@@ -67,42 +67,13 @@ static NcclApi* nccl_api() {
     }                                                                                               \
   } while (0)
 
-// per-rank state of the partitioned closure
-struct DistRank {
-  cudaStream_t stream = nullptr;
-  uint32_t *frontier = nullptr, *visited = nullptr, *next = nullptr, *contrib = nullptr, *gather = nullptr,
-           *slice = nullptr, *level = nullptr, *src = nullptr;
-  unsigned long long* counters = nullptr;   // [0] edges read, [1] |next|
-  size_t src_cap = 0;
-  // peer-memory form: one block holding counts[2][P2P_MAX_RANKS] u64 | flags[P2P_MAX_RANKS] u32 | acc[4] u64 | result
-  unsigned char* p2p = nullptr;
-};
-
-
 }  // namespace dmg
-
-struct dmg_dist {
-  int n = 0;
-  std::vector<int> devices;
-  std::vector<dmg_engine*> engines;
-  std::vector<ncclComm_t> comms;            // empty until a partitioned graph needs them
-  unsigned long long* h_flag = nullptr;     // pinned: |next| of the level
-  int peer_state = 0;                       // 0 not probed, 1 every pair has peer access, -1 some pair has not
-};
-
-struct dmg_dist_graph {
-  dmg_dist* dist = nullptr;
-  int partitioned = 0;
-  uint32_t V = 0, wr = 0;                   // wr = bitmap words owned per rank; padded width = wr * n
-  std::vector<dmg_graph*> graphs;           // one per rank
-  std::vector<dmg::DistRank> ranks;
-};
 
 using namespace dmg;
 
 static void free_rank(DistRank& r) {
   for (void* p : {(void*)r.frontier, (void*)r.visited, (void*)r.next, (void*)r.contrib, (void*)r.gather, (void*)r.slice,
-                  (void*)r.level, (void*)r.src, (void*)r.counters, (void*)r.p2p})
+                  (void*)r.level, (void*)r.src, (void*)r.counters, (void*)r.p2p, (void*)r.ord})
     if (p) cudaFree(p);
   if (r.stream) cudaStreamDestroy(r.stream);
   r = DistRank();
@@ -308,7 +279,7 @@ static int32_t ensure_rank_state(dmg_dist_graph* dg) {
 }
 
 // Peer access between every pair of the box's devices (NVSwitch: all pairs), enabled once.
-static bool ensure_peer_access(dmg_dist* d) {
+bool ensure_peer_access(dmg_dist* d) {
   if (d->peer_state) return d->peer_state > 0;
   d->peer_state = -1;
   if (d->n > P2P_MAX_RANKS) return false;

@@ -108,6 +108,7 @@ def lib():
             "dmg_dist_graph_part": (i32, [vp, i32, C.POINTER(vp), C.POINTER(u32), C.POINTER(u32)]),
             "dmg_dist_neighbors_batch": (i32, [vp, i32, i32, i32, u64, vp, vp, vp, vp, vp, u64, pu64]),
             "dmg_dist_closure": (i32, [vp, i32, u32, vp, vp, pu64, C.POINTER(DistClosureStats)]),
+            "dmg_dist_analysis_order": (i32, [vp, vp]),
             "dmg_bits_decode": (i32, [u32, u32, u64, vp, vp, vp, vp, vp, vp, u64, pu64, i32]),
             "dmg_closure": (i32, [vp, i32, u32, vp, vp, pu64]),
             "dmg_analysis_order": (i32, [vp, vp]),
@@ -414,6 +415,12 @@ class Graph:
         return rc, need.value
 
     # -- T5 ------------------------------------------------------------------------------------
+    def analysis_order(self):
+        """Exact analysisOrder of a partitioned graph (dmg_dist_analysis_order)."""
+        order = np.zeros(max(1, self.V), np.uint32)
+        _check(self.L.dmg_dist_analysis_order(self.h, order.ctypes.data))
+        return order[:self.V]
+
     def closure(self, direction, sources):
         s = _arr(sources, np.uint32)
         level = np.zeros(max(1, self.V), np.uint32)
@@ -691,6 +698,12 @@ class DistGraph:
                                                off.ctypes.data, ids.ctypes.data, hop.ctypes.data, ids.size,
                                                C.byref(need)))
         return off, ids[:need.value], hop[:need.value]
+
+    def analysis_order(self):
+        """Exact analysisOrder of a partitioned graph (dmg_dist_analysis_order)."""
+        order = np.zeros(max(1, self.V), np.uint32)
+        _check(self.L.dmg_dist_analysis_order(self.h, order.ctypes.data))
+        return order[:self.V]
 
     def closure(self, direction, sources):
         s = _arr(sources, np.uint32)

@@ -450,6 +450,13 @@ int32_t dmg_dist_neighbors_batch(dmg_dist_graph* dg, int32_t mode, int32_t k, in
                                  uint64_t* needed);
 int32_t dmg_dist_closure(dmg_dist_graph* dg, int32_t dir, uint32_t n_src, const uint32_t* src,
                          uint32_t* out_level, uint64_t* reached, dmg_dist_closure_stats* stats);
+/* analysisOrder() (PG:390-421) of a PARTITIONED graph, exactly as dmg_analysis_order gives it for one device:
+ * entry points in insertion order, then FIFO discovery order, then the unreached vertices in nodes order
+ * (PG:415-418).  Runs dmg_dist_closure for the depths, then orders level by level: the owner of a parent
+ * pushes (parent's place in its level, edge position) as a 64-bit minimum into the child's owner, counts and
+ * places its winning edges through peer memory.  out_order has n_vertices entries.  Needs peer access
+ * between all devices (DMG_EINVAL otherwise).                                                              */
+int32_t dmg_dist_analysis_order(dmg_dist_graph* dg, uint32_t* out_order);
 
 /* ---- measurement -----------------------------------------------------------------------------*/
 int32_t dmg_last_call_stats(dmg_engine* e, dmg_call_stats* out);

@@ -102,6 +102,12 @@ for direction, dname in ((dmgraph.OUT, "out"), (dmgraph.IN, "in")):
             assert reached == wreached and np.array_equal(lvl, wlvl), (dname, name)
         out["sparse_closure"][dname + "_" + name] = {"matches": True, "reached": int(reached), **st}
 os.environ.pop("DMG_DIST_NCCL", None)
+# (4) exact analysisOrder of the partitioned sparse graph (7 entry points) against the oracle's FIFO order
+t0 = time.perf_counter()
+got = sp.analysis_order()
+t_order = time.perf_counter() - t0
+assert np.array_equal(got, o.analysis_order())
+out["partitioned_analysis_order"] = {"vertices": Vs, "checked_against": "oracle", "matches": True, "wall_ms": 1e3 * t_order}
 sp.release()
 dist.close()
 print(json.dumps(out), flush=True)
