@@ -606,3 +606,69 @@ extern "C" int32_t dmg_dist_neighbors_batch(dmg_dist_graph* dg, int32_t mode, in
   out_off[nq] = base[N];
   return DMG_OK;
 }
+
+// ---- a graph_query batch over N replicas (BASELINE config 4: "query batches sharded across 8 GPUs") ------
+// Contiguous op ranges, one host thread per device.  Phase 1 sizes every range (dmg_query_batch without
+// output buffers: k-hop groups are counted, not fetched), phase 2 lets every replica write its rows straight
+// into the caller's arrays at the range's base.  Catalogs (methods, flags, class types) have to be set on
+// every replica (dmg_dist_graph_part hands out the per-device handles).
+extern "C" int32_t dmg_dist_query_batch(dmg_dist_graph* dg, uint64_t n_ops, const dmg_query_op* ops,
+                                        const uint8_t* text_bytes, uint64_t* out_off, uint32_t* out_ids, uint8_t* out_aux,
+                                        uint64_t cap, uint64_t* needed) {
+  if (!dg || !needed || !out_off || (n_ops && !ops)) {
+    set_error("dmg_dist_query_batch: NULL argument");
+    return DMG_EINVAL;
+  }
+  if (dg->partitioned) {
+    set_error("dmg_dist_query_batch: needs a replicated graph");
+    return DMG_EINVAL;
+  }
+  const int N = dg->dist->n;
+  *needed = 0;
+  out_off[0] = 0;
+  if (!n_ops) return DMG_OK;
+  std::vector<uint64_t> lo(N + 1), need(N, 0), base(N + 1, 0);
+  for (int r = 0; r <= N; ++r) lo[r] = n_ops * r / N;
+  std::vector<int32_t> rc(N, DMG_OK);
+  std::vector<std::string> err(N);
+  std::vector<std::vector<uint64_t>> rank_off(N);
+  auto run = [&](int r, int phase) {
+    const uint64_t a = lo[r], n = lo[r + 1] - a;
+    if (!n) return;
+    if (phase == 0) rank_off[r].assign(n + 1, 0);
+    uint64_t nd = 0;
+    const bool fetch = phase == 1;
+    const int32_t st = dmg_query_batch(dg->graphs[r], n, ops + a, text_bytes, rank_off[r].data(),
+                                       fetch ? out_ids + base[r] : nullptr, fetch ? out_aux + base[r] : nullptr,
+                                       fetch ? cap - base[r] : 0, &nd);
+    need[r] = nd;
+    if (st != DMG_OK && !(phase == 0 && st == DMG_ECAP)) {
+      rc[r] = st;
+      err[r] = dmg_last_error();
+    }
+  };
+  for (int phase = 0; phase < 2; ++phase) {
+    std::vector<std::thread> th;
+    for (int r = 1; r < N; ++r) th.emplace_back(run, r, phase);
+    run(0, phase);
+    for (auto& x : th) x.join();
+    for (int r = 0; r < N; ++r)
+      if (rc[r] != DMG_OK) {
+        set_error("rank %d: %s", r, err[r].c_str());
+        return rc[r];
+      }
+    if (phase == 0) {
+      for (int r = 0; r < N; ++r) base[r + 1] = base[r] + need[r];
+      *needed = base[N];
+      for (int r = 0; r < N; ++r)
+        for (uint64_t i = lo[r]; i < lo[r + 1]; ++i) out_off[i] = rank_off[r][i - lo[r]] + base[r];
+      out_off[n_ops] = base[N];
+      if (base[N] == 0) return DMG_OK;
+      if (base[N] > cap || !out_ids || !out_aux) {
+        set_error("dmg_dist_query_batch: capacity %llu < needed %llu", (unsigned long long)cap, (unsigned long long)base[N]);
+        return DMG_ECAP;
+      }
+    }
+  }
+  return DMG_OK;
+}

@@ -2,10 +2,28 @@
 #include <nvtx3/nvToolsExt.h>
 
 #include <algorithm>
+#include <chrono>
+#include <cstdlib>
 #include <new>
 #include <thread>
 
 #include "common.cuh"
+
+// DMG_UPLOAD_TIMING=1: phase times of an upload on stderr (diagnostics only; nothing is printed otherwise)
+namespace {
+struct UploadClock {
+  bool on;
+  std::chrono::steady_clock::time_point t0;
+  UploadClock() : on(getenv("DMG_UPLOAD_TIMING") != nullptr), t0(std::chrono::steady_clock::now()) {}
+  void tick(const char* what) {
+    if (!on) return;
+    const auto t1 = std::chrono::steady_clock::now();
+    fprintf(stderr, "[dmg upload] %-28s %8.1f ms\n", what, std::chrono::duration<double, std::milli>(t1 - t0).count());
+    t0 = t1;
+  }
+};
+}  // namespace
+
 
 namespace dmg {
 
@@ -432,21 +450,30 @@ static int32_t finish_upload_impl(dmg_engine* e, dmg_graph* g, uint32_t V, const
   // resolve() rows for mode BOTH: the out row followed by the in row of the same vertex, one
   // contiguous range per vertex (no de-duplication: a 2-cycle appears twice, the visited
   // set removes it, PG:366-375)
+  UploadClock clk;
   std::vector<uint32_t> und_ptr(V + 1, 0), und_idx;
   try {
     und_idx.resize(2 * out_idx.size());
-    for (uint32_t v = 0; v < V; ++v) {
-      uint32_t w = und_ptr[v];
-      for (uint32_t j = out_ptr[v]; j < out_ptr[v + 1]; ++j) und_idx[w++] = out_idx[j];
-      for (uint32_t j = in_ptr[v]; j < in_ptr[v + 1]; ++j) und_idx[w++] = in_idx[j];
-      und_ptr[v + 1] = w;
-    }
+    for (uint32_t v = 0; v <= V; ++v) und_ptr[v] = out_ptr[v] + in_ptr[v];
+    const unsigned T = (unsigned)std::max<size_t>(1, std::min<size_t>(std::thread::hardware_concurrency(), out_idx.size() / 65536 + 1));
+    auto rows = [&](unsigned t) {
+      for (uint32_t v = (uint32_t)((uint64_t)V * t / T), v1 = (uint32_t)((uint64_t)V * (t + 1) / T); v < v1; ++v) {
+        uint32_t w = und_ptr[v];
+        for (uint32_t j = out_ptr[v]; j < out_ptr[v + 1]; ++j) und_idx[w++] = out_idx[j];
+        for (uint32_t j = in_ptr[v]; j < in_ptr[v + 1]; ++j) und_idx[w++] = in_idx[j];
+      }
+    };
+    std::vector<std::thread> th;
+    for (unsigned t = 1; t < T; ++t) th.emplace_back(rows, t);
+    rows(0);
+    for (auto& x : th) x.join();
   } catch (const std::bad_alloc&) {
     *g_freed = true;
     delete g;
     set_error("dmg_graph_create: host out of memory");
     return DMG_ENOMEM;
   }
+  clk.tick("resolve rows");
   if ((st = upload(&g->d_und_ptr, und_ptr.data(), und_ptr.size(), &bytes)) != DMG_OK ||
       (st = upload(&g->d_und_idx, und_idx.data(), und_idx.size(), &bytes)) != DMG_OK ||
       (st = upload(&g->d_out_ptr, out_ptr.data(), out_ptr.size(), &bytes)) != DMG_OK ||
@@ -462,6 +489,7 @@ static int32_t finish_upload_impl(dmg_engine* e, dmg_graph* g, uint32_t V, const
     free_graph(g);
     return st;
   }
+  clk.tick("copies to the device");
   if (max_part <= 4096 && V > 0) {   // MB_MAX_WINDOW of khop_bits.cuh
     const uint32_t pad_id = (std::max<uint32_t>(max_part, 1) + 127u) & ~127u;
     if ((st = build_ell(&g->ell[0], und_ptr, und_idx, und_ptr, part, pad_id, &bytes)) != DMG_OK ||
@@ -473,6 +501,7 @@ static int32_t finish_upload_impl(dmg_engine* e, dmg_graph* g, uint32_t V, const
     }
     g->has_ell = true;
   }
+  clk.tick("sliced-ELL copies");
   uint64_t nbytes = 0;
   if (d->name_off) {
     nbytes = d->name_off[V];
@@ -659,6 +688,20 @@ void dmg_engine_destroy(dmg_engine* e) {
   delete e;
 }
 
+// Host threads of one CSR build: all of them when the build runs alone, an equal share when several
+// run side by side (dmg_dist_graph_create builds one graph per device concurrently).
+namespace {
+std::atomic<int> g_builds_running{0};
+struct BuildThreads {
+  unsigned n;
+  BuildThreads() {
+    const int others = g_builds_running.fetch_add(1) + 1;
+    n = std::max(1u, std::thread::hardware_concurrency() / (unsigned)others);
+  }
+  ~BuildThreads() { g_builds_running.fetch_sub(1); }
+};
+}  // namespace
+
 static int32_t graph_create_impl(dmg_engine* e, const dmg_graph_desc* d, dmg_graph** out);
 int32_t dmg_graph_create(dmg_engine* e, const dmg_graph_desc* d, dmg_graph** out) {
   try {
@@ -706,64 +749,183 @@ static int32_t graph_create_impl(dmg_engine* e, const dmg_graph_desc* d, dmg_gra
     return (uint32_t)(std::upper_bound(part.begin(), part.end(), v) - part.begin() - 1);
   };
 
-  // ---- host CSR build, O(V+E): stable counting sort by source, per-row stamp dedup ----------
+  // ---- host CSR build, O(V+E) work on all host threads ---------------------------------------------
+  // Stable counting sort by source + per-row de-duplication that keeps the FIRST occurrence
+  // (LinkedHashSet.add, PG:182).  Threads own contiguous SOURCE ranges of about equal edge counts: a
+  // thread streams the whole edge list in order and places the edges of its own rows, so insertion order
+  // is kept without per-thread cursors (T sequential reads of the source array cost far less than the
+  // cache-missing scatter they feed).  In-rows are built the same way from the kept edges, threads owning
+  // TARGET ranges (step 5).
   uint64_t dropped = 0, dups = 0;
   std::vector<uint32_t> out_ptr(V + 1, 0), in_ptr(V + 1, 0), out_idx, in_idx;
   dmg_graph* g = new (std::nothrow) dmg_graph();
   if (!g) return DMG_ENOMEM;
   g->eng = e;
   try {
+    UploadClock clk;
+    const BuildThreads bt;   // shares the host's threads with builds running beside this one (dmg_dist_graph_create)
+    const unsigned T = (unsigned)std::max<uint64_t>(1, std::min<uint64_t>(bt.n, E / 65536 + 1));
+    std::atomic<bool> failed{false};
+    auto run = [&](auto&& body) {   // body(t): thread index
+      std::vector<std::thread> th;
+      auto safe = [&](unsigned t) {
+        try {
+          body(t);
+        } catch (const std::exception&) {
+          failed = true;
+        }
+      };
+      for (unsigned t = 1; t < T; ++t) th.emplace_back(safe, t);
+      safe(0);
+      for (auto& x : th) x.join();
+      if (failed) throw std::bad_alloc();
+    };
+    const uint32_t* es = d->edge_src;
+    const uint32_t* ed = d->edge_dst;
+    // 1. valid edges per source (atomic increments: sources are spread, contention is rare)
     std::vector<uint32_t> cnt(V + 1, 0);
-    for (uint64_t i = 0; i < E; ++i) {
-      if (d->edge_src[i] >= V || d->edge_dst[i] >= V) {   // PG:179-181
-        ++dropped;
-        continue;
-      }
-      ++cnt[d->edge_src[i] + 1];
-    }
-    for (uint32_t v = 0; v < V; ++v) cnt[v + 1] += cnt[v];
-    std::vector<uint32_t> raw(cnt[V]);
-    {
-      std::vector<uint32_t> cur(cnt.begin(), cnt.end() - 1);
-      for (uint64_t i = 0; i < E; ++i) {
-        if (d->edge_src[i] >= V || d->edge_dst[i] >= V) continue;
-        raw[cur[d->edge_src[i]]++] = d->edge_dst[i];
-      }
-    }
-    std::vector<uint32_t> stamp(V, 0);   // stamp[t] == s+1  <=>  edge s->t already kept
-    out_idx.reserve(raw.size());
-    for (uint32_t s = 0; s < V; ++s) {
-      for (uint32_t j = cnt[s]; j < cnt[s + 1]; ++j) {
-        const uint32_t t = raw[j];
-        if (stamp[t] == s + 1) {   // PG:182 LinkedHashSet.add: first position wins
-          ++dups;
+    std::vector<uint64_t> t_dropped(T, 0);
+    run([&](unsigned t) {
+      const uint64_t a = E * t / T, b = E * (t + 1) / T;
+      uint64_t dr = 0;
+      for (uint64_t i = a; i < b; ++i) {
+        if (es[i] >= V || ed[i] >= V) {   // PG:179-181
+          ++dr;
           continue;
         }
-        stamp[t] = s + 1;
-        out_idx.push_back(t);
-        ++in_ptr[t + 1];
+        __atomic_fetch_add(&cnt[es[i] + 1], 1u, __ATOMIC_RELAXED);
       }
-      out_ptr[s + 1] = (uint32_t)out_idx.size();
-    }
-    for (uint32_t v = 0; v < V; ++v) in_ptr[v + 1] += in_ptr[v];
-    in_idx.resize(out_idx.size());
-    {
-      std::vector<uint32_t> cur(in_ptr.begin(), in_ptr.end() - 1);
-      for (uint32_t s = 0; s < V; ++s)   // ascending source id => canonical in-row order
-        for (uint32_t j = out_ptr[s]; j < out_ptr[s + 1]; ++j) in_idx[cur[out_idx[j]]++] = s;
-    }
-    if (part.size() > 2) {
-      for (uint32_t s = 0; s < V; ++s) {
-        if (out_ptr[s] == out_ptr[s + 1]) continue;
-        const uint32_t p = find_part(s);
-        for (uint32_t j = out_ptr[s]; j < out_ptr[s + 1]; ++j)
-          if (out_idx[j] < part[p] || out_idx[j] >= part[p + 1]) {
-            set_error("dmg_graph_create: edge %u->%u crosses project ranges", s, out_idx[j]);
-            delete g;
-            return DMG_EINVAL;
+      t_dropped[t] = dr;
+    });
+    for (uint64_t x : t_dropped) dropped += x;
+    clk.tick("count by source");
+    for (uint32_t v = 0; v < V; ++v) cnt[v + 1] += cnt[v];
+    const uint64_t kept_raw = cnt[V];
+    // source ranges of about equal edge counts
+    std::vector<uint32_t> lo_src(T + 1, V);
+    lo_src[0] = 0;
+    for (unsigned t = 1; t < T; ++t)
+      lo_src[t] = (uint32_t)(std::lower_bound(cnt.begin(), cnt.end(), (uint32_t)(kept_raw * t / T)) - cnt.begin());
+    for (unsigned t = 1; t <= T; ++t) lo_src[t] = std::max(lo_src[t], lo_src[t - 1]);
+    lo_src[T] = V;
+    // 2. stable placement, 3. de-duplication in place, kept entries per row in `keep`
+    std::vector<uint32_t> raw(kept_raw), keep(V + 1, 0);
+    std::vector<uint64_t> t_dups(T, 0);
+    run([&](unsigned t) {
+      const uint32_t s0 = lo_src[t], s1 = lo_src[t + 1];
+      if (s0 >= s1) return;
+      std::vector<uint32_t> cur(cnt.begin() + s0, cnt.begin() + s1);
+      for (uint64_t i = 0; i < E; ++i) {
+        const uint32_t s = es[i];
+        if (s < s0 || s >= s1 || ed[i] >= V) continue;
+        raw[cur[s - s0]++] = ed[i];
+      }
+      uint64_t du = 0;
+      std::vector<uint32_t> table;   // open addressing, for the few long rows
+      for (uint32_t s = s0; s < s1; ++s) {
+        const uint32_t b = cnt[s], n = cnt[s + 1] - b;
+        uint32_t w = 0;
+        if (n <= 48) {
+          for (uint32_t j = 0; j < n; ++j) {
+            const uint32_t x = raw[b + j];
+            bool seen = false;
+            for (uint32_t q = 0; q < w && !seen; ++q) seen = raw[b + q] == x;
+            if (!seen) raw[b + w++] = x;
           }
+        } else {
+          uint32_t size = 64;
+          while (size < 2 * n) size <<= 1;
+          table.assign(size, 0xFFFFFFFFu);
+          for (uint32_t j = 0; j < n; ++j) {
+            const uint32_t x = raw[b + j];
+            uint32_t h = (x * 0x9E3779B1u) & (size - 1);
+            while (table[h] != 0xFFFFFFFFu && table[h] != x) h = (h + 1) & (size - 1);
+            if (table[h] == x) continue;
+            table[h] = x;
+            raw[b + w++] = x;
+          }
+        }
+        du += n - w;
+        keep[s + 1] = w;
       }
+      t_dups[t] = du;
+    });
+    for (uint64_t x : t_dups) dups += x;
+    clk.tick("place + de-duplicate");
+    for (uint32_t v = 0; v < V; ++v) out_ptr[v + 1] = out_ptr[v] + keep[v + 1];
+    out_idx.resize(out_ptr[V]);
+    // 4. compact rows, check that no edge leaves its project
+    std::atomic<uint64_t> bad_edge{~0ull};
+    run([&](unsigned t) {
+      const uint32_t s0 = lo_src[t], s1 = lo_src[t + 1];
+      for (uint32_t s = s0; s < s1; ++s) {
+        const uint32_t n = out_ptr[s + 1] - out_ptr[s];
+        if (!n) continue;
+        const uint32_t* from = raw.data() + cnt[s];
+        uint32_t* to = out_idx.data() + out_ptr[s];
+        uint32_t plo = 0, phi = V;
+        if (part.size() > 2) {
+          const uint32_t p = find_part(s);
+          plo = part[p];
+          phi = part[p + 1];
+        }
+        for (uint32_t j = 0; j < n; ++j) {
+          const uint32_t x = from[j];
+          to[j] = x;
+          if (x < plo || x >= phi) {
+            uint64_t want = ~0ull;
+            bad_edge.compare_exchange_strong(want, ((uint64_t)s << 32) | x);
+          }
+        }
+      }
+    });
+    if (bad_edge.load() != ~0ull) {
+      set_error("dmg_graph_create: edge %u->%u crosses project ranges", (uint32_t)(bad_edge.load() >> 32),
+                (uint32_t)bad_edge.load());
+      delete g;
+      return DMG_EINVAL;
     }
+    std::vector<uint32_t>().swap(raw);
+    clk.tick("compact");
+    // 5. in-rows.  Import graphs have hubs (one class that 800 k others import): shared cursors would put
+    // every thread on the same few counters, and a scattered row would need a sort.  Instead threads own
+    // TARGET ranges and stream the kept edges in source order, twice: once to count (equal-width ranges),
+    // once to place (ranges of about equal in-edge counts) -- private counters, and a row comes out in
+    // ascending source id, its canonical order, by construction.
+    const uint64_t Ek = out_idx.size();
+    run([&](unsigned t) {
+      const uint32_t d0 = (uint32_t)((uint64_t)V * t / T), d1 = (uint32_t)((uint64_t)V * (t + 1) / T);
+      if (d0 >= d1) return;
+      const uint32_t* oi = out_idx.data();
+      uint32_t* deg = in_ptr.data() + 1;
+      for (uint64_t j = 0; j < Ek; ++j) {
+        const uint32_t x = oi[j];
+        if (x >= d0 && x < d1) ++deg[x];
+      }
+    });
+    for (uint32_t v = 0; v < V; ++v) in_ptr[v + 1] += in_ptr[v];
+    in_idx.resize(Ek);
+    {
+      std::vector<uint32_t> lo_dst(T + 1, V);
+      lo_dst[0] = 0;
+      for (unsigned t = 1; t < T; ++t)
+        lo_dst[t] = (uint32_t)(std::lower_bound(in_ptr.begin(), in_ptr.end(), (uint32_t)(Ek * t / T)) - in_ptr.begin());
+      for (unsigned t = 1; t <= T; ++t) lo_dst[t] = std::max(lo_dst[t], lo_dst[t - 1]);
+      lo_dst[T] = V;
+      run([&](unsigned t) {
+        const uint32_t d0 = lo_dst[t], d1 = lo_dst[t + 1];
+        if (d0 >= d1) return;
+        std::vector<uint32_t> cur(in_ptr.begin() + d0, in_ptr.begin() + d1);
+        const uint32_t* oi = out_idx.data();
+        uint32_t* ii = in_idx.data();
+        for (uint32_t sv = 0; sv < V; ++sv)
+          for (uint32_t j = out_ptr[sv], je = out_ptr[sv + 1]; j < je; ++j) {
+            const uint32_t x = oi[j];
+            if (x >= d0 && x < d1) ii[cur[x - d0]++] = sv;
+          }
+      });
+    }
+    clk.tick("in-rows (count + place)");
     // entry points: insertion order, unknown ids ignored, no duplicates (PG:190-197)
     std::vector<uint8_t> is_e(V, 0);
     for (uint32_t i = 0; i < d->n_entry; ++i) {

@@ -109,6 +109,7 @@ def lib():
             "dmg_dist_neighbors_batch": (i32, [vp, i32, i32, i32, u64, vp, vp, vp, vp, vp, u64, pu64]),
             "dmg_dist_closure": (i32, [vp, i32, u32, vp, vp, pu64, C.POINTER(DistClosureStats)]),
             "dmg_dist_analysis_order": (i32, [vp, vp]),
+            "dmg_dist_query_batch": (i32, [vp, u64, vp, vp, vp, vp, vp, u64, pu64]),
             "dmg_bits_decode": (i32, [u32, u32, u64, vp, vp, vp, vp, vp, vp, u64, pu64, i32]),
             "dmg_closure": (i32, [vp, i32, u32, vp, vp, pu64]),
             "dmg_analysis_order": (i32, [vp, vp]),
@@ -415,6 +416,37 @@ class Graph:
         return rc, need.value
 
     # -- T5 ------------------------------------------------------------------------------------
+    def part(self, rank):
+        """The per-device handle of `rank` as a Graph (borrowed: do not release it), e.g. to set the method
+        catalog on every replica."""
+        h = C.c_void_p()
+        _check(self.L.dmg_dist_graph_part(self.h, rank, C.byref(h), None, None))
+        g = Graph.__new__(Graph)
+        g.eng, g.L, g.h = None, self.L, h
+        info = GraphInfo()
+        _check(self.L.dmg_graph_info_get(h, C.byref(info)))
+        g.info = {f: getattr(info, f) for f, _ in GraphInfo._fields_}
+        g.V = g.info["n_vertices"]
+        return g
+
+    def query_batch_packed(self, ops, text, out=None):
+        """dmg_dist_query_batch: as Graph.query_batch_packed, the ops sharded over the replicas."""
+        ops = np.ascontiguousarray(ops, dtype=Graph.QUERY_OP_DTYPE)
+        tb = np.ascontiguousarray(text, dtype=np.uint8)
+        if tb.size == 0:
+            tb = np.zeros(1, np.uint8)
+        need = C.c_uint64(0)
+        if out is None:
+            off = np.zeros(ops.size + 1, np.uint64)
+            rc = self.L.dmg_dist_query_batch(self.h, ops.size, ops.ctypes.data, tb.ctypes.data, off.ctypes.data, None,
+                                             None, 0, C.byref(need))
+            _check(rc, allow=(ECAP,))
+            return need.value
+        off, ids, aux = out
+        _check(self.L.dmg_dist_query_batch(self.h, ops.size, ops.ctypes.data, tb.ctypes.data, off.ctypes.data,
+                                           ids.ctypes.data, aux.ctypes.data, ids.size, C.byref(need)))
+        return need.value
+
     def analysis_order(self):
         """Exact analysisOrder of a partitioned graph (dmg_dist_analysis_order)."""
         order = np.zeros(max(1, self.V), np.uint32)
@@ -665,7 +697,8 @@ class Dist:
 class DistGraph:
     """A graph on every device of a Dist: replicated (query batches) or vertex-range partitioned (closure)."""
 
-    def __init__(self, dist, n_vertices, src, dst, entry=(), part_off=None, partitioned=False):
+    def __init__(self, dist, n_vertices, src, dst, entry=(), part_off=None, partitioned=False, name_off=None,
+                 name_bytes=None, lower_bytes=None):
         self.dist, self.L, self.V = dist, dist.L, int(n_vertices)
         src, dst, entry = _arr(src, np.uint32), _arr(dst, np.uint32), _arr(entry, np.uint32)
         d = GraphDesc()
@@ -674,6 +707,12 @@ class DistGraph:
         if part_off is not None:
             po = _arr(part_off, np.uint32)
             d.n_parts, d.part_off = int(po.size - 1), _ptr(po)
+        if name_off is not None:
+            no, nb = _arr(name_off, np.uint64), _arr(name_bytes, np.uint8)
+            d.name_off, d.name_bytes = no.ctypes.data, (nb.ctypes.data if nb.size else None)
+            if lower_bytes is not None:
+                lb = _arr(lower_bytes, np.uint8)
+                d.lower_bytes = lb.ctypes.data if lb.size else None
         self.h = C.c_void_p()
         _check(self.L.dmg_dist_graph_create(dist.h, C.byref(d), int(partitioned), C.byref(self.h)))
 
@@ -698,6 +737,37 @@ class DistGraph:
                                                off.ctypes.data, ids.ctypes.data, hop.ctypes.data, ids.size,
                                                C.byref(need)))
         return off, ids[:need.value], hop[:need.value]
+
+    def part(self, rank):
+        """The per-device handle of `rank` as a Graph (borrowed: do not release it), e.g. to set the method
+        catalog on every replica."""
+        h = C.c_void_p()
+        _check(self.L.dmg_dist_graph_part(self.h, rank, C.byref(h), None, None))
+        g = Graph.__new__(Graph)
+        g.eng, g.L, g.h = None, self.L, h
+        info = GraphInfo()
+        _check(self.L.dmg_graph_info_get(h, C.byref(info)))
+        g.info = {f: getattr(info, f) for f, _ in GraphInfo._fields_}
+        g.V = g.info["n_vertices"]
+        return g
+
+    def query_batch_packed(self, ops, text, out=None):
+        """dmg_dist_query_batch: as Graph.query_batch_packed, the ops sharded over the replicas."""
+        ops = np.ascontiguousarray(ops, dtype=Graph.QUERY_OP_DTYPE)
+        tb = np.ascontiguousarray(text, dtype=np.uint8)
+        if tb.size == 0:
+            tb = np.zeros(1, np.uint8)
+        need = C.c_uint64(0)
+        if out is None:
+            off = np.zeros(ops.size + 1, np.uint64)
+            rc = self.L.dmg_dist_query_batch(self.h, ops.size, ops.ctypes.data, tb.ctypes.data, off.ctypes.data, None,
+                                             None, 0, C.byref(need))
+            _check(rc, allow=(ECAP,))
+            return need.value
+        off, ids, aux = out
+        _check(self.L.dmg_dist_query_batch(self.h, ops.size, ops.ctypes.data, tb.ctypes.data, off.ctypes.data,
+                                           ids.ctypes.data, aux.ctypes.data, ids.size, C.byref(need)))
+        return need.value
 
     def analysis_order(self):
         """Exact analysisOrder of a partitioned graph (dmg_dist_analysis_order)."""

@@ -448,6 +448,11 @@ int32_t dmg_dist_neighbors_batch(dmg_dist_graph* dg, int32_t mode, int32_t k, in
                                  uint64_t n_queries, const uint32_t* q_off, const uint32_t* q_src,
                                  uint64_t* out_off, uint32_t* out_ids, uint8_t* out_hop, uint64_t cap,
                                  uint64_t* needed);
+/* dmg_query_batch (GQS:53-73, 111-150, 195-394) over the replicas of a replicated graph: contiguous op
+ * ranges, one host thread per device, rows and offsets exactly as one dmg_query_batch call gives them.
+ * Method catalogs / flags / class types must have been set on every replica (dmg_dist_graph_part).      */
+int32_t dmg_dist_query_batch(dmg_dist_graph* dg, uint64_t n_ops, const dmg_query_op* ops, const uint8_t* text_bytes,
+                             uint64_t* out_off, uint32_t* out_ids, uint8_t* out_aux, uint64_t cap, uint64_t* needed);
 int32_t dmg_dist_closure(dmg_dist_graph* dg, int32_t dir, uint32_t n_src, const uint32_t* src,
                          uint32_t* out_level, uint64_t* reached, dmg_dist_closure_stats* stats);
 /* analysisOrder() (PG:390-421) of a PARTITIONED graph, exactly as dmg_analysis_order gives it for one device:

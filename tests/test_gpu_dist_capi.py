@@ -72,3 +72,34 @@ def test_partitioned_analysis_order_is_exact(dist, V, deg, n_entry):
         got = pg.analysis_order()
         assert np.array_equal(got, want)
     pg.release()
+
+
+def test_sharded_query_batch_equals_one_device(dist):
+    """dmg_dist_query_batch (config 4: DSL batches sharded over the replicas) gives the offsets, ids and aux
+    bytes of ONE dmg_query_batch call on one device, which tests/test_gpu_fullsize.py holds to the oracle
+    opcode by opcode; a sample of rows is checked against the oracle here as well."""
+    from oracle import checks
+    sg = synth.big_graph(30_000, 400_000, cap=200, entry_frac=0.01, seed=91, with_names=True)
+    V = sg.n_vertices
+    off, arena = synth.pack_names(sg.names)
+    low = np.frombuffer(bytes(arena).lower(), dtype=np.uint8).copy()
+    mo, no, mbytes = synth.method_catalog(V)
+    flags = np.repeat((np.random.Generator(np.random.PCG64(4)).random(V) < 0.02).astype(np.uint8), 10)
+    ops, text, kind = synth.c4_mix_ops(3000, sg.names, mbytes, dmgraph.Graph.QUERY_OP_DTYPE)
+    dg = dmgraph.DistGraph(dist, V, sg.src, sg.dst, sg.entry, name_off=off, name_bytes=arena, lower_bytes=low)
+    for r in range(dist.n):
+        part = dg.part(r)
+        part.set_methods_packed(mo, no, mbytes)
+        part.set_method_flags(flags)
+    need = dg.query_batch_packed(ops, text)
+    got = (np.zeros(len(ops) + 1, np.uint64), np.zeros(max(need, 1), np.uint32), np.zeros(max(need, 1), np.uint8))
+    assert dg.query_batch_packed(ops, text, out=got) == need
+    one = dg.part(0)
+    want = (np.zeros(len(ops) + 1, np.uint64), np.zeros(max(need, 1), np.uint32), np.zeros(max(need, 1), np.uint8))
+    assert one.query_batch_packed(ops, text, out=want) == need
+    assert all(np.array_equal(a, b) for a, b in zip(got, want))
+    o = ora.CsrOracle(V, sg.src, sg.dst, sg.entry)
+    rows = np.sort(np.random.Generator(np.random.PCG64(8)).choice(len(ops), 400, replace=False))
+    assert checks.check_query_mix(o, ops, text, got[0], got[1], got[2], off, low, mbytes,
+                                  np.flatnonzero(flags).astype(np.uint32), rows=rows) == rows.size
+    dg.release()
