@@ -303,3 +303,64 @@ def test_query_batch_meta_decorates_vertex_rows(engine):
             assert not any(am) and not any(bm)
     assert seen_rows > 100
     g.release()
+
+
+# ---- name scan: the corners of the byte sweep / parked positions / word-wise verification ----------
+def test_search_sweep_corner_cases(engine):
+    """Names of 0..3 bytes, a name longer than a candidate position holds (> 8191 bytes: exhaustive path), names
+    whose bytes repeat a pattern's prefix at every position (the parked-position list drains mid-step),
+    patterns of 4 k and 4 k + 1..3 bytes up to 40 (word-wise verification, partial last word), a pattern that
+    ends exactly where the arena ends, one-, two- and three-byte patterns, ranges that start and end inside a
+    32-name step.  Ordered hits against the oracle's contains() scan (CCS:1507-1526)."""
+    rng = np.random.default_rng(71)
+    alpha = np.frombuffer(b"abcdefgh", dtype=np.uint8)
+    names = []
+    for i in range(1500):
+        kind = i % 10
+        if kind == 0:
+            names.append("")
+        elif kind == 1:
+            names.append("ab"[: i % 3])
+        elif kind == 2:
+            names.append("abcabcabcabc" * (1 + i % 7))                    # every position starts "abc" / "bca" / "cab"
+        elif kind == 3 and i == 503:
+            names.append("x" * 4000 + "needle.in.a.long.name" + "y" * 5000)   # 9021 bytes
+        else:
+            names.append(bytes(alpha[rng.integers(0, 8, int(rng.integers(1, 90)))]).decode())
+    names.append("the.very.last.name.ends.with.this.exact.tail")
+    off, arena = synth.pack_names(names)
+    low = np.frombuffer(bytes(arena).lower(), dtype=np.uint8).copy()
+    g = dmgraph.Graph(engine, len(names), [], [], [], name_off=off, name_bytes=arena)
+    queries = [b"", b"a", b"h", b"ab", b"ca", b"abc", b"bca", b"abca", b"needle.in.a.long.name", b"in.a.long.nam",
+               b"this.exact.tail", b"ends.with.this.exact.tail", b"the.very.last.name.ends.with.this.exact.tail",
+               b"abcabcabcabcabcabcabcabc", b"abcabcabcabcabcabcabcabca", b"yyyyyyyyyyyyyyyyyyyyyyyyyyyyyyyyyyyyy", b"xy", b"tail."]
+    for i in range(60):                                                  # substrings of real names, 4..40 bytes
+        s = names[int(rng.integers(0, len(names)))].encode()
+        if len(s) >= 4:
+            a = int(rng.integers(0, len(s) - 3))
+            queries.append(s[a:a + int(rng.integers(4, 41))])
+    for kind in (0, 2):                                                  # CONTAINS_ALL, CONTAINS_FIRST
+        for (lo, hi) in [(0, None), (17, 1203), (500, 510), (len(names) - 1, len(names))]:
+            o, ids = g.search_batch(kind, queries, lo, hi)
+            wo, wids = ora.search_batch(off, low, queries, kind, lo, hi)
+            assert np.array_equal(o, wo) and np.array_equal(ids, wids), (kind, lo, hi)
+    g.release()
+
+
+# ---- closure: degenerate source sets on a graph large enough for the persistent kernel --------------
+def test_closure_degenerate_sources(engine):
+    """No sources, only unknown ids, one isolated source: dmg_closure on >= 32,768 vertices runs as one
+    cooperative launch whose level loop must not start (or must stop after one level)."""
+    V = 70_001
+    rng = np.random.default_rng(5)
+    src = rng.integers(1, V, 3 * V).astype(np.uint32)                    # vertex 0 has no edges either way
+    dst = rng.integers(1, V, 3 * V).astype(np.uint32)
+    g = dmgraph.Graph(engine, V, src, dst, [])
+    o = ora.CsrOracle(V, src, dst, [])
+    for s in ([], [V + 3, V + 9], [0], [0, 5, 5, V + 1]):
+        s = np.asarray(s, np.uint32)
+        for d in (dmgraph.OUT, dmgraph.IN):
+            lvl, reached = g.closure(d, s)
+            wl, wr, _ = o.closure(d, s)
+            assert reached == wr and np.array_equal(lvl, wl), (s.tolist(), d)
+    g.release()
