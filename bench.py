@@ -194,8 +194,10 @@ def main():
     ap.add_argument("--c5-vertices", type=int, default=4_000_000)
     ap.add_argument("--c5-edges", type=int, default=100_000_000)
     ap.add_argument("--parity-rows", type=int, default=4096)
-    ap.add_argument("--closure-vertices", type=int, default=4_000_000, help="N>1: partitioned-closure block (0 = skip)")
-    ap.add_argument("--closure-edges", type=int, default=100_000_000)
+    ap.add_argument("--closure-vertices", type=int, default=-1,
+                    help="N>1: partitioned-closure block; -1 = 2.5 M vertices / 62.5 M drawn edges PER GPU (weak "
+                         "scaling: N = 8 is BASELINE config 5 at full size, 20 M / 500 M), 0 = skip")
+    ap.add_argument("--closure-edges", type=int, default=0)
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     rank = int(os.environ.get("RANK", "0"))
@@ -470,6 +472,8 @@ def main():
         line["configs"] = blocks
     # ---- N > 1: the path's one exchange step, the partitioned closure over all N devices (rank 0 drives
     # them through dmg_dist_* in ONE process, as the single-JVM host would; the other ranks wait) ----------
+    if args.closure_vertices < 0:
+        args.closure_vertices, args.closure_edges = 2_500_000 * world, 62_500_000 * world
     if world > 1 and args.closure_vertices:
         import torch
         barrier()
