@@ -80,7 +80,6 @@ enum KernelId : int {
   K_KHOP1_ROWS,
   K_KHOP_LARGE,
   K_SEARCH_REPLICATE,
-  K_KHOP_MID,
   K_COUNT
 };
 extern const char* const kKernelNames[K_COUNT];

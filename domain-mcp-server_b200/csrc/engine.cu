@@ -52,7 +52,7 @@ void publish_stats(const dmg_call_stats& s) { g_last_stats = s; }
 const char* const kKernelNames[K_COUNT] = {
     "khop_small", "khop_global", "khop_emit", "scan_counts", "adjacency_gather", "entry_flags", "closure_init", "closure_topdown",
     "closure_bottomup", "order_degrees", "order_minslot", "order_claim", "order_tail", "search_scan",
-    "search_first", "search_emit", "khop_windows", "query_rows", "misc", "khop1_rows", "khop_large", "search_replicate", "khop_mid"};
+    "search_first", "search_emit", "khop_windows", "query_rows", "misc", "khop1_rows", "khop_large", "search_replicate"};
 
 int32_t DevBuf::reserve(size_t bytes) {
   if (bytes <= cap && p) return DMG_OK;

@@ -385,184 +385,4 @@ __global__ void __launch_bounds__(KL_THREADS, 1) khop_large_kernel(const KhopArg
 
 
 
-// ---------------------------------------------------------------------------------------------------
-// khop_mid_kernel: k >= 2 traversals that stay SMALL (expected entries ~ degree^k below a few thousand:
-// config 4, k = 2).  Such a query is a chain of short dependent steps; what finishes a batch of them
-// sooner is more queries in flight, so a query gets a 128-thread CTA whose whole state is 32 KB of
-// shared memory (7 CTAs per SM): an open-addressing hash set of the claimed vertices instead of a claim
-// bitmap over the project, and a queue of (vertex << 8 | hop) words that is bitonic-sorted in place at the
-// end -- vertex-major keys, so the row comes out in ascending id with its hop beside it.  A query that
-// outgrows the queue (KM_QCAP entries) is put on the device list for the CTA kernel, untouched.
-// Needs window-relative ids below 2^24 and k <= 255.
-constexpr int KM_THREADS = 128, KM_NW = KM_THREADS / 32;
-constexpr uint32_t KM_QCAP = 2048;            // sources + discoveries one query may hold
-constexpr uint32_t KM_HASH = 4096;            // slots of the claimed set (load <= 0.5)
-constexpr uint32_t KM_EMPTY = 0xFFFFFFFFu;
-
-__global__ void __launch_bounds__(KM_THREADS) khop_mid_kernel(const KhopArgs a, uint32_t* defer, uint32_t* n_defer) {
-  constexpr int THREADS = KM_THREADS, NW = KM_NW;
-  __shared__ uint32_t s_queue[2 * KM_QCAP];    // second half: room for the power-of-two padding of the sort
-  __shared__ uint32_t s_hash[KM_HASH];
-  __shared__ uint2 s_row[THREADS];
-  __shared__ uint32_t s_wsum[NW + 1];
-  __shared__ unsigned long long s_q, s_base;
-  __shared__ uint32_t s_lo, s_hi, s_tail, s_over;
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const uint32_t* __restrict__ fptr = a.mode == DMG_BOTH ? a.und_ptr : (a.mode == DMG_OUT ? a.out_ptr : a.in_ptr);
-  const uint32_t* __restrict__ fidx = a.mode == DMG_BOTH ? a.und_idx : (a.mode == DMG_OUT ? a.out_idx : a.in_idx);
-  unsigned long long te_all = 0, rows_all = 0;
-  auto wipe = [&]() {
-    uint4* h4 = reinterpret_cast<uint4*>(s_hash);
-    for (uint32_t i = tid; i < KM_HASH / 4; i += THREADS) h4[i] = make_uint4(KM_EMPTY, KM_EMPTY, KM_EMPTY, KM_EMPTY);
-  };
-  // claims x; true if it was not in the set
-  auto claim = [&](uint32_t x) {
-    uint32_t h = (x * 0x9E3779B1u) >> 20;   // 12 bits
-    while (true) {
-      const uint32_t old = atomicCAS(&s_hash[h], KM_EMPTY, x);
-      if (old == KM_EMPTY) return true;
-      if (old == x) return false;
-      h = (h + 1) & (KM_HASH - 1);
-    }
-  };
-  while (true) {
-    if (tid == 0) s_q = atomicAdd(&a.ctr->ticket, 1ull);
-    wipe();
-    __syncthreads();
-    const unsigned long long q = s_q;
-    if (q >= a.nq) break;
-    const uint32_t qb = a.q_off[q], qe = a.q_off[q + 1];
-    if (tid == 0) {
-      uint32_t lo, hi;
-      find_window(a, qb, qe, &lo, &hi);
-      s_lo = lo;
-      s_hi = hi;
-      s_tail = 0;
-      s_over = (qe - qb > KM_QCAP / 2 || hi - lo > (1u << 24)) ? 1u : 0u;
-    }
-    __syncthreads();
-    const uint32_t lo = s_lo, hi = s_hi;
-    if (!s_over) {
-      for (uint32_t i = qb + tid; i < qe; i += THREADS) {
-        const uint32_t s = a.q_src[i];
-        if (s >= lo && s < hi && claim(s - lo)) s_queue[atomicAdd(&s_tail, 1u)] = (s - lo) << 8;
-      }
-    }
-    __syncthreads();
-    const uint32_t ns = s_tail;
-    uint32_t head = 0, tail = ns;
-    if (!a.exclude && !s_over) {   // kept sources may be found again: only excluded sources stay claimed
-      __syncthreads();
-      wipe();
-    }
-    __syncthreads();
-    unsigned long long te = 0, rows = 0;
-    for (int lvl = 1; lvl <= a.k && head < tail && !s_over; ++lvl) {
-      for (uint32_t c0 = head; c0 < tail; c0 += THREADS) {
-        const uint32_t i = c0 + tid;
-        uint32_t b = 0, n = 0;
-        if (i < tail) {
-          const uint32_t u = lo + (s_queue[i] >> 8);
-          b = fptr[u];
-          n = fptr[u + 1] - b;
-        }
-        uint32_t T;
-        const uint32_t pre = block_excl_scan<THREADS>(n, s_wsum, &T);
-        s_row[tid] = make_uint2(pre + n, b - pre);
-        if (tid == 0) {
-          te += T;
-          rows += min(tail - c0, (uint32_t)THREADS);
-        }
-        __syncthreads();
-        const uint32_t Tq = (((T + NW - 1) / NW) + 31u) & ~31u;
-        const uint32_t pbeg = warp * Tq, pend = min(T, pbeg + Tq);
-        if (pbeg < pend) {
-          uint32_t r;
-          {
-            uint32_t l = 0, h = THREADS;
-            while (l < h) {
-              const uint32_t m = (l + h) >> 1;
-              if (s_row[m].x <= pbeg) l = m + 1; else h = m;
-            }
-            r = l;
-          }
-          uint2 row = s_row[r];
-          for (uint32_t p0 = pbeg; p0 < pend; p0 += 32) {
-            const uint32_t p = p0 + lane;
-            bool isnew = false;
-            uint32_t x = 0;
-            if (p < pend) {
-              while (row.x <= p) row = s_row[++r];
-              x = fidx[row.y + p] - lo;
-              isnew = claim(x);
-            }
-            const unsigned m = __ballot_sync(FULL, isnew);
-            if (m) {
-              uint32_t pos = 0;
-              if (lane == 0) pos = atomicAdd(&s_tail, (uint32_t)__popc(m));
-              pos = __shfl_sync(FULL, pos, 0);
-              const uint32_t at = pos + __popc(m & lanemask_lt());
-              if (isnew) {
-                if (at < KM_QCAP) s_queue[at] = (x << 8) | (uint32_t)lvl;
-                else s_over = 1;   // more than a CTA of this kind holds: the query goes to the CTA kernel
-              }
-            }
-          }
-        }
-        __syncthreads();
-      }
-      head = tail;
-      tail = min(s_tail, KM_QCAP);
-      __syncthreads();
-    }
-    if (s_over) {
-      if (tid == 0) defer[atomicAdd(n_defer, 1u)] = (uint32_t)q;
-      __syncthreads();
-      continue;
-    }
-    const uint32_t total = tail - ns;
-    if (tid == 0) {
-      const unsigned long long at = atomicAdd(&a.ctr->aux[3], (unsigned long long)total);
-      s_base = at;
-      a.tmp_start[q] = at;
-      a.counts[q] = total;
-      te_all += te;
-      rows_all += rows;
-    }
-    if (total) {
-      uint32_t P = 32;
-      while (P < total) P <<= 1;
-      uint32_t* key = s_queue + ns;
-      for (uint32_t i = total + tid; i < P; i += THREADS) key[i] = 0xFFFFFFFFu;
-      __syncthreads();
-      for (uint32_t size = 2; size <= P; size <<= 1)
-        for (uint32_t stride = size >> 1; stride; stride >>= 1) {
-          for (uint32_t t = tid; t < (P >> 1); t += THREADS) {
-            const uint32_t i = ((t & ~(stride - 1)) << 1) | (t & (stride - 1)), j = i | stride;
-            const uint32_t x = key[i], y = key[j];
-            if ((x > y) == ((i & size) == 0)) {
-              key[i] = y;
-              key[j] = x;
-            }
-          }
-          __syncthreads();
-        }
-      const unsigned long long base = s_base;
-      for (uint32_t i = tid; i < total; i += THREADS) {
-        const unsigned long long pos = base + i;
-        if (pos < a.cap) {
-          a.tmp_ids[pos] = lo + (key[i] >> 8);
-          a.tmp_hop[pos] = (uint8_t)(key[i] & 0xFFu);
-        }
-      }
-    }
-    __syncthreads();
-  }
-  if (tid == 0 && rows_all) {
-    atomicAdd(&a.ctr->edges, te_all);
-    atomicAdd(&a.ctr->aux[0], te_all);
-    atomicAdd(&a.ctr->rows, rows_all);
-  }
-}
-
 }  // namespace dmg

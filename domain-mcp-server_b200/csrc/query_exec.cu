@@ -135,28 +135,6 @@ __global__ void __launch_bounds__(256) qx_fill_kernel(const QxRow* __restrict__ 
     }
     unsigned long long row_begin = out_off[q], row_end = out_off[q + 1];
     QxRow r = rows[q];
-    {
-      // most chunks of a large result lie inside ONE segment of ONE row (a k-hop row is thousands of entries
-      // long): that case is a plain copy -- no row walk, eight independent loads per lane in flight
-      const unsigned long long j0 = P - row_begin;
-      const int sg = j0 < r.s[0].len ? 0 : 1;
-      const unsigned long long in_seg = sg ? j0 - r.s[0].len : j0;
-      if (r.s[sg].len - in_seg >= Pend - P && (sg == 1 || row_end >= Pend)) {
-        const uint32_t* __restrict__ src = r.s[sg].ids + in_seg;
-        const uint8_t* __restrict__ sax = r.s[sg].aux ? r.s[sg].aux + in_seg : nullptr;
-        const uint8_t axc = (uint8_t)r.s[sg].aux_const;
-        const bool vert = (r.s[sg].aux_const & QX_IDS_ARE_VERTICES) != 0;
-        const uint32_t n = (uint32_t)(Pend - P);
-#pragma unroll 8
-        for (uint32_t t = lane; t < n; t += 32) {
-          const uint32_t id = src[t];
-          out_ids[P + t] = id;
-          out_aux[P + t] = sax ? sax[t] : axc;
-          if (out_meta) out_meta[P + t] = (vert && id < V) ? vmeta[id] : (uint8_t)0;
-        }
-        continue;
-      }
-    }
     for (unsigned long long p = P + lane; p < Pend; p += 32) {
       while (p >= row_end) {
         ++q;

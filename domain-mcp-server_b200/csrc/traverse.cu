@@ -1213,12 +1213,7 @@ int32_t run_khop(CallCtx* c, dmg_graph* g, int mode, int k, int exclude, uint64_
     double expect = 1.0;
     for (int i = 0; i < k && expect < 1e9; ++i) expect *= std::max(deg, 1.0);
     const char* force_large = getenv("DMG_FORCE_KHOP_LARGE");   // differential tests
-    // ... and before any CTA kernel, khop_mid_kernel takes those short traversals with a 128-thread CTA per
-    // query (7 per SM); what outgrows its queue is handed on, like the hub rows of k = 1.  The CTA kernel
-    // behind khop1 / khop_mid works off their list: khop_large_kernel wherever the bitmap fits.
-    const bool use_mid = k >= 2 && k <= 255 && expect < 4096.0 && maxp <= (1u << 24) && !force_large &&
-                         getenv("DMG_NO_KHOP_MID") == nullptr;
-    const bool listed = k == 1 || use_mid;   // the CTA kernel runs in list mode
+    const bool listed = k == 1;   // the CTA kernel then works off khop1_warp_kernel's list
     const bool use_large = !no_large && kl_smem + 12 * 1024 <= e->smem_optin && (listed || expect >= 4096.0 || force_large);
     const size_t per_block = use_large ? qcap * 4 : 2 * seen_words * 4 + qcap * 4;   // (claim bitmap, rank words,) queue
     int occ = 0;
@@ -1266,16 +1261,6 @@ int32_t run_khop(CallCtx* c, dmg_graph* g, int mode, int k, int exclude, uint64_
       LaunchScope ls(c, K_KHOP1_ROWS);
       const uint64_t blocks = std::min<uint64_t>((nq + K1_WARPS - 1) / K1_WARPS, (uint64_t)e->sm_count * 8);
       khop1_warp_kernel<<<(unsigned)std::max<uint64_t>(blocks, 1), K1_THREADS, 0, c->stream>>>(a, d_defer, d_ndefer);
-    }
-    if (use_mid) {
-      {
-        LaunchScope ls(c, K_KHOP_MID);
-        int occ_mid = 1;
-        DMG_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_mid, khop_mid_kernel, KM_THREADS, 0));
-        const uint64_t blocks = std::min<uint64_t>(nq, (uint64_t)e->sm_count * std::max(occ_mid, 1));
-        khop_mid_kernel<<<(unsigned)std::max<uint64_t>(blocks, 1), KM_THREADS, 0, c->stream>>>(a, d_defer, d_ndefer);
-      }
-      DMG_CUDA(cudaMemsetAsync(&c->d_counters->ticket, 0, 8, c->stream));   // the list has its own tickets
     }
     {
       LaunchScope ls(c, use_large ? K_KHOP_LARGE : K_KHOP_GLOBAL);
