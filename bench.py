@@ -368,6 +368,15 @@ def main():
     h_bits, p6 = eng.pinned(np.uint32, nq * planes * words)
     h_win, p7 = eng.pinned(np.uint32, nq * 2)
     h_cnt, p8 = eng.pinned(np.uint32, nq)
+    # (a) the bit-row call alone, (b) the call followed by the host expansion: two loops, because a consumer of
+    # (a) does not run the expansion in between (its 650 MB of streaming stores were seen to slow the next call)
+    only_ms = 0.0
+    for it in range(2 + args.steps):
+        barrier()
+        t0 = time.perf_counter()
+        g.neighbors_batch_bits(dmgraph.BOTH, K_HOPS, 1, h_q_off, h_q_src, out=(h_win.reshape(nq, 2), h_cnt, h_bits))
+        if it >= 2:
+            only_ms += 1e3 * (time.perf_counter() - t0)
     bits_ms, dec_ms, bits_d2h = 0.0, 0.0, 0
     for it in range(2 + args.steps):
         barrier()
@@ -382,7 +391,9 @@ def main():
             bits_ms += 1e3 * (t1 - t0)
             dec_ms += 1e3 * (t2 - t1)
     assert int(h_off[-1]) == cap
-    bits_ms_max, both_ms_max = allmax(bits_ms), allmax(bits_ms + dec_ms)
+    both_ms_max = allmax(bits_ms + dec_ms)
+    only_ms_max = allmax(only_ms)
+    bits_ms_max = allmax(bits_ms)
     h_bits_check = (h_off.copy(), h_ids.copy(), h_hop.copy()) if (rank == 0 and not args.no_cpu_baseline) else None
     clocks = sampler.stop()
 
@@ -431,8 +442,8 @@ def main():
             "e2e_packed": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d),
                            "d2h_bytes_per_step": int(d2h), "ms_per_step": e2e_ms_max / args.steps,
                            "call": "dmg_neighbors_batch (packed (id, hop) rows over PCIe)"},
-            "e2e_bits_only": {"value": total_queries / (bits_ms_max * 1e-3), "unit": UNIT,
-                              "ms_per_step": bits_ms_max / args.steps, "d2h_bytes_per_step": int(bits_d2h),
+            "e2e_bits_only": {"value": total_queries / (only_ms_max * 1e-3), "unit": UNIT,
+                              "ms_per_step": only_ms_max / args.steps, "d2h_bytes_per_step": int(bits_d2h),
                               "call": "dmg_neighbors_batch_bits alone: a host that walks the neighbours reads the "
                                       "planes directly"},
             "gpu_launches": int(launches), "clocks": clocks,

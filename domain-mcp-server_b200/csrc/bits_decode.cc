@@ -5,6 +5,7 @@
 
 #include <algorithm>
 #include <cstdint>
+#include <cstdlib>
 #include <thread>
 #include <vector>
 
@@ -58,6 +59,33 @@ __attribute__((target("avx512f,avx512bw,avx512vl,avx512vbmi2"))) void decode_row
   }
 }
 
+// Streaming form for large results: a thread expands its rows into a small staging buffer that stays in
+// its cache and moves it to the destination with non-temporal 64-byte stores -- the destination lines are
+// written once and never read, so fetching them for ownership (which a normal store does) only doubles
+// the memory traffic of a job that is bound by exactly that.  `flush` keeps the destination cursor on a
+// 64-byte boundary between calls: what does not fill a line waits in the staging buffer for the next one.
+template <class T>
+struct NtStream {
+  static constexpr size_t LINE = 64 / sizeof(T);
+  T* dst;            // next destination element
+  T* stage;          // staging buffer (capacity given by the caller)
+  size_t n = 0;      // staged elements
+  __attribute__((target("avx512f"))) void flush(bool final) {
+    size_t i = 0;
+    while (i < n && (reinterpret_cast<uintptr_t>(dst) & 63)) *dst++ = stage[i++];   // up to the first line boundary
+    for (; i + LINE <= n; i += LINE, dst += LINE)
+      _mm512_stream_si512(reinterpret_cast<__m512i*>(dst), _mm512_loadu_si512(stage + i));
+    if (final) {
+      while (i < n) *dst++ = stage[i++];
+      n = 0;
+    } else {
+      const size_t rest = n - i;
+      for (size_t k = 0; k < rest; ++k) stage[k] = stage[i + k];
+      n = rest;
+    }
+  }
+};
+
 }  // namespace
 
 extern "C" int32_t dmg_bits_decode(uint32_t planes, uint32_t plane_words, uint64_t nq, const uint32_t* win,
@@ -83,7 +111,43 @@ extern "C" int32_t dmg_bits_decode(uint32_t planes, uint32_t plane_words, uint64
   const size_t row_words = (size_t)planes * plane_words;
   static const bool simd = __builtin_cpu_supports("avx512f") && __builtin_cpu_supports("avx512bw") &&
                            __builtin_cpu_supports("avx512vl") && __builtin_cpu_supports("avx512vbmi2");
+  static const bool streaming = [] {
+    const char* e = getenv("DMG_DECODE_NT");   // "0": plain stores (A/B runs)
+    return !(e && e[0] == '0');
+  }();
+  constexpr size_t STAGE = 8192;   // entries staged per thread (32 KB of ids + 8 KB of hops: stays in L2)
+  auto work_nt = [&](uint64_t a, uint64_t b) {
+    std::vector<uint32_t> sid(STAGE + 64);
+    std::vector<uint8_t> shp(STAGE + 64);
+    NtStream<uint32_t> si{out_ids + out_off[a], sid.data()};
+    NtStream<uint8_t> sh{out_hop + out_off[a], shp.data()};
+    for (uint64_t q = a; q < b; ++q) {
+      const uint32_t cnt = counts[q];
+      if (!cnt) continue;
+      if (si.n + cnt > STAGE || cnt > STAGE) {
+        si.flush(false);
+        sh.flush(false);
+      }
+      const uint32_t lo = win[2 * q], nw = (win[2 * q + 1] + 31) >> 5;
+      const uint32_t* row = bits + q * row_words;
+      if (cnt > STAGE - 64) {   // a row larger than the staging buffer goes straight to its place
+        si.flush(true);
+        sh.flush(true);
+        decode_row_avx512(planes, plane_words, lo, nw, row, si.dst, sh.dst);
+        si.dst += cnt;
+        sh.dst += cnt;
+        continue;
+      }
+      decode_row_avx512(planes, plane_words, lo, nw, row, si.stage + si.n, sh.stage + sh.n);
+      si.n += cnt;
+      sh.n += cnt;
+    }
+    si.flush(true);
+    sh.flush(true);
+    _mm_sfence();
+  };
   auto work = [&](uint64_t a, uint64_t b) {
+    if (simd && streaming && out_off[b] - out_off[a] >= (1u << 16)) return work_nt(a, b);
     for (uint64_t q = a; q < b; ++q) {
       if (!counts[q]) continue;
       const uint32_t lo = win[2 * q], nw = (win[2 * q + 1] + 31) >> 5;

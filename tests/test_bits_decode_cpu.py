@@ -50,3 +50,29 @@ def test_bits_decode_capacity_answer():
         assert False, "expected DMG_ECAP"
     except dmgraph.DmgError as e:
         assert e.code == dmgraph.ECAP
+
+
+def test_bits_decode_streaming_path_on_a_large_result():
+    """Results of more than 65,536 entries per thread go through the staged non-temporal stores: odd destination
+    alignments (rows of odd lengths shift every thread's first byte), rows larger than the staging buffer, empty
+    rows in between.  Expected arrays come from numpy on the same hop matrix."""
+    rng = np.random.default_rng(4)
+    for planes, wn, nq, dens in [(2, 2000, 900, 0.994), (3, 4096, 150, 1.0), (1, 333, 4000, 0.7), (2, 12000, 60, 0.9)]:
+        words = (wn + 31) // 32 + 3
+        hop = rng.integers(1, 1 << planes, (nq, wn)).astype(np.uint8)
+        hop[rng.random((nq, wn)) >= dens] = 0
+        hop[rng.integers(0, nq, nq // 10)] = 0                           # some empty rows
+        lo = rng.integers(0, 1 << 20, nq).astype(np.uint32)
+        win = np.stack([lo, np.full(nq, wn, np.uint32)], axis=1).astype(np.uint32)
+        bits = np.zeros((nq, planes, words), np.uint32)
+        pad = np.zeros((nq, words * 32), np.uint8)
+        for b in range(planes):
+            pad[:, :wn] = (hop >> b) & 1
+            bits[:, b, :] = np.packbits(pad.reshape(nq, words, 32), axis=2, bitorder="little").view(np.uint32).reshape(nq, words)
+        counts = (hop != 0).sum(1).astype(np.uint32)
+        r, c = np.nonzero(hop)
+        want_ids, want_hop = (lo[r] + c).astype(np.uint32), hop[r, c]
+        for threads in (1, 3, 0):
+            off, ids, hp = dmgraph.bits_decode(planes, words, win, counts, bits, threads=threads)
+            assert np.array_equal(off, np.concatenate([[0], np.cumsum(counts, dtype=np.uint64)]))
+            assert np.array_equal(ids, want_ids) and np.array_equal(hp, want_hop), (planes, wn, threads)
