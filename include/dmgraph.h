@@ -205,7 +205,10 @@ int32_t dmg_neighbors_batch_bits(dmg_graph* g, int32_t mode, int32_t k, int32_t 
                                  uint32_t* out_counts, uint32_t* out_bits, uint64_t cap_bytes,
                                  uint64_t* needed_bytes);
 /* Host-side expansion of bit rows into CSR-shaped (id, hop) rows, ascending id (no device work; uses
- * n_threads host threads, 0 = all).  out_off has n_queries + 1 entries; cap counts entries.          */
+ * n_threads host threads, 0 = all).  out_off has n_queries + 1 entries; cap counts entries.  Large results
+ * are written with non-temporal stores from a per-thread staging buffer, and the bit rows that have been
+ * consumed are flushed from the CPU caches (their contents are untouched): the buffer is normally the
+ * target of the next dmg_neighbors_batch_bits copy, which is several times slower into cached lines.  */
 int32_t dmg_bits_decode(uint32_t planes, uint32_t plane_words, uint64_t n_queries, const uint32_t* win,
                         const uint32_t* counts, const uint32_t* bits, uint64_t* out_off, uint32_t* out_ids,
                         uint8_t* out_hop, uint64_t cap, uint64_t* needed, int32_t n_threads);
