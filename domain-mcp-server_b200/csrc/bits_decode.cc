@@ -94,24 +94,16 @@ struct NtStream {
 
 }  // namespace
 
-extern "C" int32_t dmg_bits_decode(uint32_t planes, uint32_t plane_words, uint64_t nq, const uint32_t* win,
-                                   const uint32_t* counts, const uint32_t* bits, uint64_t* out_off, uint32_t* out_ids,
-                                   uint8_t* out_hop, uint64_t cap, uint64_t* needed, int32_t n_threads) {
-  if (!out_off || !needed || (nq && (!win || !counts || !bits)) || planes < 1 || planes > 8) {
-    dmg::set_error("dmg_bits_decode: bad argument");
-    return DMG_EINVAL;
-  }
-  uint64_t total = 0;
-  for (uint64_t q = 0; q < nq; ++q) {
-    out_off[q] = total;
-    total += counts[q];
-  }
-  out_off[nq] = total;
-  *needed = total;
-  if (total > cap || (total && (!out_ids || !out_hop))) {
-    dmg::set_error("dmg_bits_decode: capacity %llu < needed %llu", (unsigned long long)cap, (unsigned long long)total);
-    return DMG_ECAP;
-  }
+namespace dmg {
+
+// Rows [q_begin, q_end) of a bit-row result into out_ids / out_hop at out_off[q] (out_off already holds the
+// offsets of these rows and of row q_end).  All arrays are indexed by absolute query.  Used by dmg_bits_decode
+// and by dmg_neighbors_batch, which expands the chunks of a batch while later chunks are still on the device.
+void bits_decode_rows(uint32_t planes, uint32_t plane_words, uint64_t q_begin, uint64_t q_end, const uint32_t* win,
+                      const uint32_t* counts, const uint32_t* bits, const uint64_t* out_off, uint32_t* out_ids,
+                      uint8_t* out_hop, int32_t n_threads) {
+  if (q_end <= q_begin) return;
+  const uint64_t nq = q_end - q_begin, total = out_off[q_end] - out_off[q_begin];
   int T = n_threads > 0 ? n_threads : (int)std::thread::hardware_concurrency();
   T = (int)std::max<uint64_t>(1, std::min<uint64_t>((uint64_t)std::max(T, 1), nq / 64 + 1));
   const size_t row_words = (size_t)planes * plane_words;
@@ -173,19 +165,43 @@ extern "C" int32_t dmg_bits_decode(uint32_t planes, uint32_t plane_words, uint64
     }
   };
   if (T == 1) {
-    work(0, nq);
+    work(q_begin, q_end);
   } else {
     // split by output volume, not by query count
     std::vector<std::thread> th;
-    uint64_t a = 0;
+    uint64_t a = q_begin;
     for (int t = 0; t < T; ++t) {
-      const uint64_t want = total / T * (t + 1);
-      uint64_t b = t == T - 1 ? nq : (uint64_t)(std::upper_bound(out_off, out_off + nq + 1, want) - out_off);
-      b = std::min(std::max(b, a), nq);
+      const uint64_t want = out_off[q_begin] + total / T * (t + 1);
+      uint64_t b = t == T - 1 ? q_end
+                              : (uint64_t)(std::upper_bound(out_off + q_begin, out_off + q_end + 1, want) - out_off);
+      b = std::min(std::max(b, a), q_end);
       if (b > a) th.emplace_back(work, a, b);
       a = b;
     }
     for (auto& x : th) x.join();
   }
+}
+
+}  // namespace dmg
+
+extern "C" int32_t dmg_bits_decode(uint32_t planes, uint32_t plane_words, uint64_t nq, const uint32_t* win,
+                                   const uint32_t* counts, const uint32_t* bits, uint64_t* out_off, uint32_t* out_ids,
+                                   uint8_t* out_hop, uint64_t cap, uint64_t* needed, int32_t n_threads) {
+  if (!out_off || !needed || (nq && (!win || !counts || !bits)) || planes < 1 || planes > 8) {
+    dmg::set_error("dmg_bits_decode: bad argument");
+    return DMG_EINVAL;
+  }
+  uint64_t total = 0;
+  for (uint64_t q = 0; q < nq; ++q) {
+    out_off[q] = total;
+    total += counts[q];
+  }
+  out_off[nq] = total;
+  *needed = total;
+  if (total > cap || (total && (!out_ids || !out_hop))) {
+    dmg::set_error("dmg_bits_decode: capacity %llu < needed %llu", (unsigned long long)cap, (unsigned long long)total);
+    return DMG_ECAP;
+  }
+  dmg::bits_decode_rows(planes, plane_words, 0, nq, win, counts, bits, out_off, out_ids, out_hop, n_threads);
   return DMG_OK;
 }

@@ -104,6 +104,9 @@ struct CallCtx {
   DevBuf status, scratch, q_off, q_src, q_bytes, out_off, out_ids, out_hop, tmp0, tmp1, tmp2, tmp3;
   DevCounters* d_counters = nullptr;
   DevCounters* h_counters = nullptr;   // pinned
+  void* h_pin = nullptr;               // pinned staging of the host-pointer calls that expand on the host
+  size_t h_pin_cap = 0;
+  int32_t reserve_pinned(size_t bytes);   // grows, never shrinks; contents are not preserved
   dmg_call_stats stats{};
   struct ProfEv { int kid; cudaEvent_t a, b; };
   std::vector<ProfEv> prof;            // events recorded during this call
@@ -161,6 +164,11 @@ struct CtxGuard {
 };
 
 void publish_stats(const dmg_call_stats& s);   // thread-local "last call" record
+
+// bits_decode.cc: rows [q_begin, q_end) of a bit-row result into packed (id, hop) rows on the host
+void bits_decode_rows(uint32_t planes, uint32_t plane_words, uint64_t q_begin, uint64_t q_end, const uint32_t* win,
+                      const uint32_t* counts, const uint32_t* bits, const uint64_t* out_off, uint32_t* out_ids,
+                      uint8_t* out_hop, int32_t n_threads);
 
 // traverse.cu: the k-hop batch on device buffers, on c->stream; counters land in c->h_counters once the
 // caller has synchronised.  Uses c->status / scratch / tmp0..tmp3.

@@ -92,9 +92,19 @@ void CallCtx::destroy() {
   }
   if (d_counters) cudaFree(d_counters);
   if (h_counters) cudaFreeHost(h_counters);
+  if (h_pin) cudaFreeHost(h_pin);
   if (ev_begin) cudaEventDestroy(ev_begin);
   if (ev_end) cudaEventDestroy(ev_end);
   if (stream) cudaStreamDestroy(stream);
+}
+int32_t CallCtx::reserve_pinned(size_t bytes) {
+  if (bytes <= h_pin_cap && h_pin) return DMG_OK;
+  if (h_pin) cudaFreeHost(h_pin);
+  h_pin = nullptr;
+  h_pin_cap = 0;
+  DMG_CUDA(cudaMallocHost(&h_pin, std::max<size_t>(bytes, 4096)));
+  h_pin_cap = std::max<size_t>(bytes, 4096);
+  return DMG_OK;
 }
 cudaEvent_t CallCtx::get_event() {
   if (!ev_pool.empty()) {

@@ -1684,6 +1684,93 @@ int32_t dmg_neighbors_batch_dev_static(dmg_graph* g, int32_t mode, int32_t k, in
   return rc;
 }
 
+// dmg_neighbors_batch on small projects, large batches: the packed (id, hop) rows are ~20x the bytes of the
+// bit rows they come from (config 2: 652 MB vs 34 MB per batch), and PCIe is what the host-pointer call waits
+// for.  So the batch crosses the bus as bit rows and is expanded by the host's threads (bits_decode.cc)
+// straight into the caller's arrays (very large batches in chunks, the expansion of one chunk running while
+// the next is traversed and copied).  Same rows, offsets and capacity answer as the device-side emit.
+static int32_t neighbors_batch_via_bits(CallCtx* c, dmg_graph* g, int w64, int mode, int k, int exclude, uint64_t nq,
+                                        const uint32_t* q_off, const uint32_t* q_src, uint64_t n_src, uint64_t* out_off,
+                                        uint32_t* out_ids, uint8_t* out_hop, uint64_t cap, uint64_t* needed) {
+  Engine* e = g->eng;
+  const uint32_t maxp = std::max<uint32_t>(g->info.max_part_vertices, 1);
+  const uint32_t WB = ((maxp + 127u) & ~127u) / 32;
+  const int np = hop_planes(k);
+  const size_t row_words = (size_t)np * WB, row_bytes = row_words * 4;
+  // one chunk per 262,144 queries: with smaller chunks the expansion of one overlapped the copy of the next,
+  // but eight thread start-ups and eight short expansions cost more than the 1 ms of copy they hid
+  // (config 2: 6.1 ms in eight chunks, 5.1 ms in one)
+  const uint64_t n_chunks = std::max<uint64_t>(1, std::min<uint64_t>(8, nq / 262144));
+  const uint64_t chunk = (nq + n_chunks - 1) / n_chunks;
+  const MbLayout L(chunk, g->info.n_parts, 64u * (uint32_t)w64);
+  DMG_TRY(c->q_off.reserve((nq + 1) * 4));
+  DMG_TRY(c->q_src.reserve(n_src * 4));
+  DMG_TRY(c->scratch.reserve(nq * row_bytes));
+  DMG_TRY(c->tmp0.reserve(nq * 4));
+  DMG_TRY(c->tmp1.reserve(nq * 8));
+  DMG_TRY(c->tmp2.reserve(L.bytes));
+  const size_t o_win = (nq * row_bytes + 255) & ~size_t(255), o_cnt = (o_win + nq * 8 + 255) & ~size_t(255);
+  DMG_TRY(c->reserve_pinned(o_cnt + nq * 4));
+  unsigned char* pin = static_cast<unsigned char*>(c->h_pin);
+  uint32_t* h_bits = reinterpret_cast<uint32_t*>(pin);
+  uint32_t* h_win = reinterpret_cast<uint32_t*>(pin + o_win);
+  uint32_t* h_cnt = reinterpret_cast<uint32_t*>(pin + o_cnt);
+  DMG_CUDA(cudaMemcpyAsync(c->q_off.p, q_off, (nq + 1) * 4, cudaMemcpyHostToDevice, c->stream));
+  if (n_src) DMG_CUDA(cudaMemcpyAsync(c->q_src.p, q_src, n_src * 4, cudaMemcpyHostToDevice, c->stream));
+  c->stats.h2d_bytes += (nq + 1) * 4 + n_src * 4;
+  DMG_TRY(reset_counters(c));
+  std::vector<cudaEvent_t> done;
+  for (uint64_t q0 = 0; q0 < nq; q0 += chunk) {
+    const uint64_t q1 = std::min<uint64_t>(nq, q0 + chunk);
+    if (q0) DMG_CUDA(cudaMemsetAsync(&c->d_counters->ticket, 0, 8, c->stream));
+    DMG_TRY(launch_bit_traversal(c, g, w64, mode, k, exclude, q0, q1, c->q_off.as<uint32_t>(), c->q_src.as<uint32_t>(),
+                                 c->scratch.as<uint32_t>() + q0 * row_words, c->tmp0.as<uint32_t>(),
+                                 c->tmp1.as<uint32_t>(), c->tmp2.as<unsigned char>(), c->d_counters, c->stream));
+    DMG_CUDA(cudaGetLastError());
+    DMG_CUDA(cudaMemcpyAsync(h_cnt + q0, c->tmp0.as<uint32_t>() + q0, (q1 - q0) * 4, cudaMemcpyDeviceToHost, c->stream));
+    DMG_CUDA(cudaMemcpyAsync(h_win + 2 * q0, c->tmp1.as<uint32_t>() + 2 * q0, (q1 - q0) * 8, cudaMemcpyDeviceToHost, c->stream));
+    DMG_CUDA(cudaMemcpyAsync(h_bits + q0 * row_words, c->scratch.as<uint32_t>() + q0 * row_words, (q1 - q0) * row_bytes,
+                             cudaMemcpyDeviceToHost, c->stream));
+    cudaEvent_t ev = c->get_event();
+    DMG_CUDA(cudaEventRecord(ev, c->stream));
+    done.push_back(ev);
+  }
+  DMG_TRY(fetch_counters(c));
+  c->stats.d2h_bytes += nq * row_bytes + nq * 12 + sizeof(DevCounters);
+  // the host follows the device chunk by chunk (a row of a query without a valid source has count 0 and is
+  // never read, so those rows need no zeroing here)
+  uint64_t total = 0;
+  bool fits = out_ids && out_hop;
+  size_t ci = 0;
+  int32_t rc = DMG_OK;
+  for (uint64_t q0 = 0; q0 < nq; q0 += chunk, ++ci) {
+    const uint64_t q1 = std::min<uint64_t>(nq, q0 + chunk);
+    if (cudaEventSynchronize(done[ci]) != cudaSuccess) rc = cuda_fail(cudaGetLastError(), "cudaEventSynchronize", __FILE__, __LINE__);
+    if (rc != DMG_OK) break;
+    for (uint64_t q = q0; q < q1; ++q) {
+      out_off[q] = total;
+      total += h_cnt[q];
+    }
+    out_off[q1] = total;
+    if (fits && total <= cap) bits_decode_rows((uint32_t)np, WB, q0, q1, h_win, h_cnt, h_bits, out_off, out_ids, out_hop, 0);
+    else fits = false;
+  }
+  for (cudaEvent_t ev : done) c->ev_pool.push_back(ev);
+  DMG_TRY(rc);
+  *needed = total;
+  c->stats.results = total;
+  DMG_CUDA(cudaStreamSynchronize(c->stream));
+  c->stats.edges_traversed = c->h_counters->edges;
+  c->stats.edges_read = c->h_counters->aux[0];
+  c->stats.rows_expanded = c->h_counters->rows;
+  DMG_TRY(c->finish());
+  if (total > cap || (total && !fits)) {
+    set_error("dmg_neighbors_batch: capacity %llu < needed %llu", (unsigned long long)cap, (unsigned long long)total);
+    return DMG_ECAP;
+  }
+  return DMG_OK;
+}
+
 int32_t dmg_neighbors_batch(dmg_graph* g, int32_t mode, int32_t k, int32_t exclude_sources, uint64_t nq,
                             const uint32_t* q_off, const uint32_t* q_src, uint64_t* out_off, uint32_t* out_ids,
                             uint8_t* out_hop, uint64_t cap, uint64_t* needed) {
@@ -1700,6 +1787,17 @@ int32_t dmg_neighbors_batch(dmg_graph* g, int32_t mode, int32_t k, int32_t exclu
   CallCtx* c = cg.c;
   if (!c) return DMG_ECUDA;
   DMG_TRY(c->begin());
+  if (const int w64 = bit_parallel_w64(g, k)) {
+    // fetch calls of large batches on small projects cross the bus as bit rows (DMG_HOST_PACKED=1: the packed
+    // rows of the device-side emit instead, for A/B runs)
+    const uint32_t WBq = ((std::max<uint32_t>(g->info.max_part_vertices, 1) + 127u) & ~127u) / 32;
+    const uint64_t bits_bytes = nq * (uint64_t)hop_planes(k) * WBq * 4;
+    const bool host_packed = getenv("DMG_HOST_PACKED") != nullptr;
+    if (!host_packed && out_ids && out_hop && cap && nq >= 2048 && bits_bytes <= (1ull << 30) &&
+        bits_bytes <= g->eng->scratch_budget)
+      return neighbors_batch_via_bits(c, g, w64, mode, k, exclude_sources, nq, q_off, q_src, n_src, out_off, out_ids,
+                                      out_hop, cap, needed);
+  }
   // a row can never exceed its project, so the device buffers are bounded even for a huge cap
   const uint64_t row_max = g->info.max_part_vertices;
   uint64_t dev_cap = (!out_ids || !out_hop) ? 0 : cap;

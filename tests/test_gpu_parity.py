@@ -159,7 +159,9 @@ def test_khop_large_batch(engine):
         woff, wids, whop, wte = o.khop_batch(mode, k, excl, q_off, q_src, threads=8)
         assert np.array_equal(off, woff) and np.array_equal(ids, wids) and np.array_equal(hop, whop)
         assert engine.last_stats()["edges_traversed"] == wte
-        assert engine.last_stats()["d2h_bytes"] >= 5 * ids.size
+        # a large batch on small projects crosses PCIe as bit rows (expanded by the library's host threads): far
+        # fewer bytes than the 5 per entry of the packed rows, but never none
+        assert 0 < engine.last_stats()["d2h_bytes"] < 5 * ids.size
     with pytest.raises(dmgraph.DmgError) as ei:
         g.neighbors_batch(2, 2, 1, q_off, q_src, cap=int(woff[-1]) // 2)
     assert ei.value.code == dmgraph.ECAP
