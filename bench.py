@@ -428,7 +428,8 @@ def main():
             assert all(np.array_equal(x, y) for x, y in zip(h_call_check, res[:3])), \
                 "bench: the rows of the host-pointer call differ from the oracle"
             parity = {"rows": int(nq), "against": "oracle csr, whole batch (ids, hops, offsets bit-exact), both the "
-                                                  "resident packed result and the decoded bit rows of the e2e call"}
+                                                  "resident packed result, the rows delivered by the e2e call (dmg_neighbors_batch) and the "
+                                                  "rows of dmg_neighbors_batch_bits + dmg_bits_decode"}
         else:
             from oracle import oracle as ora
             o = ora.CsrOracle(sg.n_vertices, sg.src, sg.dst, sg.entry, sg.part_off)
