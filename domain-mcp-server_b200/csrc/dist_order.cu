@@ -27,7 +27,6 @@
 
 namespace dmg {
 
-constexpr unsigned long long ORD_KEY_NONE = ~0ull;
 
 struct OrdArgs {
   int rank, n;

@@ -1692,7 +1692,6 @@ int32_t dmg_neighbors_batch_dev_static(dmg_graph* g, int32_t mode, int32_t k, in
 static int32_t neighbors_batch_via_bits(CallCtx* c, dmg_graph* g, int w64, int mode, int k, int exclude, uint64_t nq,
                                         const uint32_t* q_off, const uint32_t* q_src, uint64_t n_src, uint64_t* out_off,
                                         uint32_t* out_ids, uint8_t* out_hop, uint64_t cap, uint64_t* needed) {
-  Engine* e = g->eng;
   const uint32_t maxp = std::max<uint32_t>(g->info.max_part_vertices, 1);
   const uint32_t WB = ((maxp + 127u) & ~127u) / 32;
   const int np = hop_planes(k);
