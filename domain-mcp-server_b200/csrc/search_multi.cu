@@ -186,7 +186,7 @@ __device__ __forceinline__ unsigned long long low_bytes_mask(uint32_t len) {
 //            busy: window bytes -> key -> slot table -> chain of pattern records -> verification; a
 //            match is appended to the hit list of the name it belongs to
 // after which every lane de-duplicates its own short list (a pattern may occur at several positions).
-constexpr int SM_CANDBUF = 48;                 // queued candidates of one name before the exhaustive fallback
+constexpr int SM_CANDBUF = 40;                 // queued candidates of one name before the exhaustive fallback
 constexpr uint32_t CAND_POS_BITS = 13;         // candidate = class << 13 | position; longer names: fallback
 
 __device__ __forceinline__ bool filter_pass_ldg(const uint32_t* __restrict__ f, uint32_t raw, uint32_t bits) {
@@ -203,7 +203,7 @@ __device__ __forceinline__ bool filter_pass2(const uint32_t* f, uint32_t raw, ui
   return ((f[fi >> 5] >> (fi & 31)) & (f[fj >> 5] >> (fj & 31)) & 1u) != 0;
 }
 
-constexpr uint32_t SM_WORK = 320;          // positions a warp parks before it works them off
+constexpr uint32_t SM_WORK = 192;          // positions a warp parks before it works them off
 constexpr uint32_t WORK_P4 = 1u, WORK_3 = 2u, WORK_2 = 4u, WORK_1 = 8u;
 
 // phase 1b, whole warp: the parked positions, 32 at a time with every lane busy.  A position that passed
@@ -302,10 +302,10 @@ __device__ __forceinline__ void scan_step(const SearchArgs& a, const uint32_t* f
 // Matches go to hits[owner][...] with n_hits[owner] counting them (may run past SM_HITBUF: overflow).
 __device__ __forceinline__ void resolve_candidates(const SearchArgs& a, int lane, uint32_t nc, unsigned long long s,
                                                    uint32_t len, const uint16_t (*cand)[SM_CANDBUF],
-                                                   uint16_t (*hits)[SM_HITBUF], uint32_t* n_hits, uint32_t* pref) {
+                                                   uint16_t (*hits)[SM_HITBUF], uint32_t* n_hits, uint16_t* pref) {
   const uint32_t inc = warp_incl_scan_u32(nc);
   const uint32_t total = __shfl_sync(FULL, inc, 31);
-  pref[lane] = inc - nc;
+  pref[lane] = (uint16_t)(inc - nc);
   __syncwarp();
   for (uint32_t j0 = 0; j0 < total; j0 += 32) {
     const uint32_t j = j0 + lane;
@@ -413,7 +413,7 @@ __global__ void __launch_bounds__(SM_THREADS) search_multi_kernel(const SearchAr
   uint32_t* fP = sm_u32;
   uint32_t* f3 = fP + a.filt_wordsP;
   __shared__ uint32_t s_nh[SM_WARPS][32];
-  __shared__ uint32_t s_pref[SM_WARPS][32];
+  __shared__ uint16_t s_pref[SM_WARPS][32];   // (u16 / the sizes above: four CTAs of config 3 fit an SM by 128 bytes)
   __shared__ uint32_t s_start[SM_WARPS][36];
   __shared__ uint32_t s_nc[SM_WARPS][32];
   __shared__ uint32_t s_work[SM_WARPS][SM_WORK];
@@ -519,7 +519,7 @@ __global__ void __launch_bounds__(SM_THREADS) search_multi_kernel(const SearchAr
       if (!overflow) {
         const uint32_t inc = warp_incl_scan_u32(nh);
         const uint32_t tot = __shfl_sync(FULL, inc, 31);
-        s_pref[wib][lane] = inc - nh;
+        s_pref[wib][lane] = (uint16_t)(inc - nh);
         unsigned long long b = 0;
         if (lane == 0 && tot) b = atomicAdd(a.log_used, (unsigned long long)tot);
         b = __shfl_sync(FULL, b, 0);
